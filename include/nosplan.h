@@ -1,0 +1,150 @@
+/*
+ * nosplan.h -- C-ABI of the B200-native partition-planning engine (libnosplan.so).
+ *
+ * This is the boundary a cgo shim binds.  The reference (WindowsXp-Beta/nos,
+ * v0.1.2) is 100 % Go and has no FFI of its own, so every entry point below names the Go interface
+ * it stands behind (paths relative to the reference root).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every buffer is caller-allocated HOST memory unless a function
+ *     says otherwise; nothing is retained after a call returns (cgo pointer rules);
+ *   - every function returns 0 on success or a negative NOSPLAN_E* code; nosplan_last_error(h)
+ *     returns a message for the last failure on that handle;
+ *   - a handle owns its CUDA stream and a device arena reused across calls; one call at a time per
+ *     handle, distinct handles may be used from different threads (the MIG and MPS controllers of
+ *     the reference run up to two Plan() calls at once, cmd/gpupartitioner/gpupartitioner.go:215-250);
+ *   - there is no CPU fallback: without a CUDA device nosplan_create fails with NOSPLAN_E_CUDA.
+ *
+ * Packed snapshot ("SoA") layout
+ *   Profiles are interned by the caller into ids 0..K-1, K <= NOSPLAN_MAX_PROFILES, in canonical
+ *   order: MIG ascending profile name, MPS ascending (size GB, name).  Wherever the reference
+ *   iterates a Go map of profiles and the order is observable, the engine visits ids ascending.
+ *   Nodes are given in byte-wise ascending name order (core/snapshot.go:126-128); GPUs of a node in
+ *   the order of the reference's Node.GPUs slice.  A Go map is a (count, key-present) pair here:
+ *   counts in a [16] uint8 row, presence in a 16-bit mask (zero-valued keys matter:
+ *   pkg/gpu/mig/gpu.go:141,243,249-251).
+ *   Node resources are int64 rows of R = 3 + K + n_other columns:
+ *     0 cpu (milli)  1 memory  2 ephemeral-storage  3..3+K-1 slice resource of profile id  3+K.. other scalars
+ */
+#ifndef NOSPLAN_H
+#define NOSPLAN_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NOSPLAN_MAX_PROFILES 16
+#define NOSPLAN_MAX_GEOMS    32   /* allowed geometries per GPU model */
+#define NOSPLAN_MAX_GPUS     16   /* GPUs per node */
+#define NOSPLAN_MAX_OTHER    12   /* non-slice scalar resource columns */
+
+#define NOSPLAN_KIND_MIG 0
+#define NOSPLAN_KIND_MPS 1
+
+/* Filter simulation (core/planner.go:178-207 canSchedulePod).  NONE / REJECT_ALL reproduce the
+ * constant statuses of the reference's mocked framework (core/planner_test.go:467-480);
+ * RESOURCES_FIT is NodeResourcesFit of k8s.io/kubernetes v1.25.4 restated. */
+#define NOSPLAN_FILTER_NONE          0
+#define NOSPLAN_FILTER_REJECT_ALL    1
+#define NOSPLAN_FILTER_RESOURCES_FIT 2
+
+#define NOSPLAN_OK          0
+#define NOSPLAN_E_INVALID  -1   /* malformed input (sizes, ids out of range) */
+#define NOSPLAN_E_CUDA     -2   /* CUDA runtime failure, message in nosplan_last_error */
+#define NOSPLAN_E_LIMIT    -3   /* input exceeds a compiled-in limit */
+#define NOSPLAN_E_NOMEM    -4
+
+typedef struct nosplan nosplan_t;
+
+/* Replaces: the inputs core.Planner.Plan reads through core.Snapshot (internal/partitioning/core/
+ * interface.go:53-65), i.e. map[string]*mig.Node / *slicing.Node with their framework.NodeInfo, and
+ * mig.GetKnownGeometries() (pkg/gpu/mig/known_configs.go:152-157). */
+typedef struct nosplan_snapshot {
+    int32_t kind;                      /* NOSPLAN_KIND_* */
+    int32_t n_profiles;                /* K */
+    const int32_t* profile_mem_gb;     /* [K] MIG: digits of `\d+gb` (mig/profile.go:70-75); MPS: slice size GB */
+    const int32_t* profile_gi;         /* [K] MIG: digits of `\d+g`  (mig/profile.go:77-82); MPS: 0 */
+    /* MIG allowed geometries per GPU model (runtime data, never compiled in); unused for MPS */
+    int32_t n_models;
+    const int32_t* model_geom_offset;  /* [n_models+1] row range of each model in geom_counts */
+    const uint8_t* geom_counts;        /* [rows][16] count per profile id, 0 = profile not in the geometry */
+    /* nodes */
+    int32_t n_nodes;                   /* N */
+    int32_t gpus_per_node;             /* G: row stride of the per-GPU arrays (max GPUs of any node) */
+    const int32_t* node_gpu_count;     /* [N] <= G */
+    const int32_t* gpu_model;          /* [N*G] model id (MIG) */
+    const int32_t* gpu_index;          /* [N*G] GPUIndex reported back in the plan */
+    const int32_t* gpu_memory_gb;      /* [N*G] MPS: GPU memory GB (pkg/gpu/util.go:58-73) */
+    const uint8_t* gpu_used;           /* [N*G][16] */
+    const uint8_t* gpu_free;           /* [N*G][16] */
+    const uint16_t* gpu_used_mask;     /* [N*G] key presence of the used map */
+    const uint16_t* gpu_free_mask;     /* [N*G] key presence of the free map */
+    int32_t n_other;                   /* non-slice scalar columns */
+    const int64_t* node_alloc;         /* [N][R] NodeInfo.Allocatable */
+    const int64_t* node_requested;     /* [N][R] NodeInfo.Requested */
+    const int32_t* node_allowed_pods;  /* [N] Allocatable.AllowedPodNumber */
+    const int32_t* node_num_pods;      /* [N] len(NodeInfo.Pods) */
+} nosplan_snapshot;
+
+/* Replaces: candidatePods []v1.Pod of Plan (core/planner.go:67) after resource.ComputePodRequest
+ * (pkg/resource/resource.go:127-146).  Pods are given in the caller's ORIGINAL order; the engine
+ * applies NewPodSorter (core/util.go:34-73) itself. */
+typedef struct nosplan_pods {
+    int32_t n_pods;                    /* P */
+    const int32_t* priority;           /* [P] corev1.PodPriority */
+    const int32_t* tracker_key;        /* [P] dense id of namespace/name; duplicates share one SliceTracker entry (core/tracker.go:38-47) */
+    const int64_t* base;               /* [P][3] cpu milli, memory, ephemeral */
+    const int32_t* scalar_ptr;         /* [P+1] CSR over the scalar entries of each pod */
+    const int32_t* scalar_col;         /* [nnz] resource column (>= 3); ascending within a pod */
+    const int64_t* scalar_qty;         /* [nnz] quantity (a present key may be 0) */
+} nosplan_pods;
+
+/* Replaces: state.PartitioningState inside core.PartitioningPlan (internal/partitioning/state/
+ * partitioning.go:24-40): per GPU the resource->count map of used+free devices; zero-count keys kept. */
+typedef struct nosplan_partitioning {
+    uint8_t* gpu_count;                /* [N*G][16] */
+    uint16_t* gpu_mask;                /* [N*G] */
+} nosplan_partitioning;
+
+typedef struct nosplan_stats {
+    int64_t candidates;                /* (visited candidate node, pod) pairs == logical tryAddPod calls */
+    int64_t visited_nodes;
+    int64_t geometry_evals;            /* (geometry, required profile) pairs scored, mig/gpu.go:164-165 */
+    int64_t placements;                /* successful tryAddPod */
+    int64_t candidate_nodes;           /* len(GetCandidateNodes()) */
+    int32_t lacking_at_start;          /* number of lacking profiles after NewSliceTracker */
+    int32_t lacking_at_end;
+    float   ms_h2d, ms_kernels, ms_d2h;/* CUDA-event times of the last call */
+    int32_t kernel_launches;
+    int32_t reserved;
+} nosplan_stats;
+
+/* Create an engine bound to one CUDA device.  Replaces: mig.NewPlanner / mps.NewPlanner
+ * (internal/partitioning/mig/factory.go:31-37, mps/factory.go:44-50). */
+int nosplan_create(int cuda_device, nosplan_t** out);
+void nosplan_destroy(nosplan_t* h);
+const char* nosplan_last_error(const nosplan_t* h);
+
+/* One Plan() call, host buffers in, host buffers out (H2D + kernels + D2H).
+ * Replaces: core.Planner.Plan (internal/partitioning/core/interface.go:27-29, planner.go:67-153).
+ * prefilter_ok: [P] PreFilter verdict per pod in original order, NULL = all Success
+ * (the verdict is a per-pod constant during one Plan(), see nosplan_quota_prefilter). */
+int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods* pods,
+                 const uint8_t* prefilter_ok, int32_t filter_mode,
+                 nosplan_partitioning* out, nosplan_stats* stats);
+
+/* The same call split in three so the planning kernels can be timed with the snapshot resident in
+ * HBM: upload() packs and copies, run() launches the kernels on the handle's stream (repeatable),
+ * download() copies the plan back.  cuda_stream of the handle is exposed for CUDA-event timing. */
+int nosplan_upload(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods* pods,
+                   const uint8_t* prefilter_ok, int32_t filter_mode);
+int nosplan_run(nosplan_t* h);
+int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats);
+void* nosplan_stream(nosplan_t* h);    /* cudaStream_t */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NOSPLAN_H */

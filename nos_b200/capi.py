@@ -1,0 +1,216 @@
+"""ctypes binding of include/nosplan.h.
+
+`Engine` wraps libnosplan.so (the CUDA product).  It fails loudly if the library is missing or no CUDA
+device is present: there is no CPU fallback.  The struct builders are also used by the test-suite to
+call the CPU oracle (oracle/libnosoracle.so) with the very same packed buffers.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Tuple
+
+import numpy as np
+
+from .packing import PackedPods, PackedSnapshot
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnosplan.so")
+
+EXPORTED_SYMBOLS = [
+    "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_plan",
+    "nosplan_upload", "nosplan_run", "nosplan_download", "nosplan_stream",
+]
+
+
+class CSnapshot(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int32), ("n_profiles", C.c_int32),
+        ("profile_mem_gb", C.c_void_p), ("profile_gi", C.c_void_p),
+        ("n_models", C.c_int32), ("model_geom_offset", C.c_void_p), ("geom_counts", C.c_void_p),
+        ("n_nodes", C.c_int32), ("gpus_per_node", C.c_int32),
+        ("node_gpu_count", C.c_void_p), ("gpu_model", C.c_void_p), ("gpu_index", C.c_void_p),
+        ("gpu_memory_gb", C.c_void_p), ("gpu_used", C.c_void_p), ("gpu_free", C.c_void_p),
+        ("gpu_used_mask", C.c_void_p), ("gpu_free_mask", C.c_void_p),
+        ("n_other", C.c_int32), ("node_alloc", C.c_void_p), ("node_requested", C.c_void_p),
+        ("node_allowed_pods", C.c_void_p), ("node_num_pods", C.c_void_p),
+    ]
+
+
+class CPods(C.Structure):
+    _fields_ = [
+        ("n_pods", C.c_int32), ("priority", C.c_void_p), ("tracker_key", C.c_void_p), ("base", C.c_void_p),
+        ("scalar_ptr", C.c_void_p), ("scalar_col", C.c_void_p), ("scalar_qty", C.c_void_p),
+    ]
+
+
+class CPartitioning(C.Structure):
+    _fields_ = [("gpu_count", C.c_void_p), ("gpu_mask", C.c_void_p)]
+
+
+class CStats(C.Structure):
+    _fields_ = [
+        ("candidates", C.c_int64), ("visited_nodes", C.c_int64), ("geometry_evals", C.c_int64),
+        ("placements", C.c_int64), ("candidate_nodes", C.c_int64),
+        ("lacking_at_start", C.c_int32), ("lacking_at_end", C.c_int32),
+        ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float),
+        ("kernel_launches", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+
+
+def _ptr(a: np.ndarray, dtype) -> Tuple[int, np.ndarray]:
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a.ctypes.data, a
+
+
+def c_snapshot(s: PackedSnapshot):
+    """-> (CSnapshot, keepalive list).  The arrays must stay alive while the struct is in use."""
+    keep = []
+
+    def p(a, dt):
+        addr, arr = _ptr(a, dt)
+        keep.append(arr)
+        return addr
+
+    cs = CSnapshot()
+    cs.kind, cs.n_profiles = s.kind, s.n_profiles
+    cs.profile_mem_gb, cs.profile_gi = p(s.profile_mem_gb, np.int32), p(s.profile_gi, np.int32)
+    cs.n_models = len(s.models)
+    cs.model_geom_offset, cs.geom_counts = p(s.model_geom_offset, np.int32), p(s.geom_counts, np.uint8)
+    cs.n_nodes, cs.gpus_per_node = s.n_nodes, s.gpus_per_node
+    cs.node_gpu_count = p(s.node_gpu_count, np.int32)
+    cs.gpu_model, cs.gpu_index = p(s.gpu_model, np.int32), p(s.gpu_index, np.int32)
+    cs.gpu_memory_gb = p(s.gpu_memory_gb, np.int32)
+    cs.gpu_used, cs.gpu_free = p(s.gpu_used, np.uint8), p(s.gpu_free, np.uint8)
+    cs.gpu_used_mask, cs.gpu_free_mask = p(s.gpu_used_mask, np.uint16), p(s.gpu_free_mask, np.uint16)
+    cs.n_other = len(s.other_resources)
+    cs.node_alloc, cs.node_requested = p(s.node_alloc, np.int64), p(s.node_requested, np.int64)
+    cs.node_allowed_pods, cs.node_num_pods = p(s.node_allowed_pods, np.int32), p(s.node_num_pods, np.int32)
+    return cs, keep
+
+
+def c_pods(pp: PackedPods):
+    keep = []
+
+    def p(a, dt):
+        addr, arr = _ptr(a, dt)
+        keep.append(arr)
+        return addr
+
+    cp = CPods()
+    cp.n_pods = pp.n_pods
+    cp.priority, cp.tracker_key = p(pp.priority, np.int32), p(pp.tracker_key, np.int32)
+    cp.base = p(pp.base, np.int64)
+    cp.scalar_ptr, cp.scalar_col = p(pp.scalar_ptr, np.int32), p(pp.scalar_col, np.int32)
+    cp.scalar_qty = p(pp.scalar_qty, np.int64)
+    return cp, keep
+
+
+def alloc_partitioning(s: PackedSnapshot):
+    n = max(1, s.n_nodes * s.gpus_per_node)
+    cnt = np.zeros((n, 16), np.uint8)
+    msk = np.zeros(n, np.uint16)
+    cp = CPartitioning(cnt.ctypes.data, msk.ctypes.data)
+    return cp, cnt, msk
+
+
+class NosplanError(RuntimeError):
+    pass
+
+
+def load_library(path: str = LIB_PATH) -> C.CDLL:
+    if not os.path.exists(path):
+        raise NosplanError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    lib.nosplan_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.nosplan_create.restype = C.c_int
+    lib.nosplan_destroy.argtypes = [C.c_void_p]
+    lib.nosplan_destroy.restype = None
+    lib.nosplan_last_error.argtypes = [C.c_void_p]
+    lib.nosplan_last_error.restype = C.c_char_p
+    lib.nosplan_plan.argtypes = [C.c_void_p, C.POINTER(CSnapshot), C.POINTER(CPods), C.c_void_p, C.c_int32,
+                                 C.POINTER(CPartitioning), C.POINTER(CStats)]
+    lib.nosplan_plan.restype = C.c_int
+    lib.nosplan_upload.argtypes = [C.c_void_p, C.POINTER(CSnapshot), C.POINTER(CPods), C.c_void_p, C.c_int32]
+    lib.nosplan_upload.restype = C.c_int
+    lib.nosplan_run.argtypes = [C.c_void_p]
+    lib.nosplan_run.restype = C.c_int
+    lib.nosplan_download.argtypes = [C.c_void_p, C.POINTER(CPartitioning), C.POINTER(CStats)]
+    lib.nosplan_download.restype = C.c_int
+    lib.nosplan_stream.argtypes = [C.c_void_p]
+    lib.nosplan_stream.restype = C.c_void_p
+    return lib
+
+
+class Engine:
+    """One nosplan handle on one CUDA device (nosplan_create .. nosplan_destroy)."""
+
+    def __init__(self, device: int = 0, lib_path: str = LIB_PATH):
+        self.h = None
+        self.lib = load_library(lib_path)
+        h = C.c_void_p()
+        rc = self.lib.nosplan_create(device, C.byref(h))
+        if rc != 0 or not h.value:
+            raise NosplanError(f"nosplan_create(device={device}) failed with {rc}: no usable CUDA device "
+                               "(libnosplan has no CPU fallback)")
+        self.h = h
+        self._snap = None
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.lib.nosplan_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            msg = self.lib.nosplan_last_error(self.h)
+            raise NosplanError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    @staticmethod
+    def _pre(prefilter_ok, n):
+        if prefilter_ok is None:
+            return None, None
+        a = np.ascontiguousarray(np.asarray(prefilter_ok, dtype=np.uint8).reshape(n))
+        return a.ctypes.data, a
+
+    def plan(self, snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0):
+        """nosplan_plan: host buffers in, host buffers out.  -> (gpu_count [N*G,16], gpu_mask [N*G], stats dict)"""
+        cs, k1 = c_snapshot(snap)
+        cp, k2 = c_pods(pods)
+        out, cnt, msk = alloc_partitioning(snap)
+        st = CStats()
+        pre, k3 = self._pre(prefilter_ok, pods.n_pods)
+        rc = self.lib.nosplan_plan(self.h, C.byref(cs), C.byref(cp), pre, filter_mode, C.byref(out), C.byref(st))
+        self._check(rc, "nosplan_plan")
+        del k1, k2, k3
+        return cnt, msk, st.as_dict()
+
+    def upload(self, snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0):
+        cs, k1 = c_snapshot(snap)
+        cp, k2 = c_pods(pods)
+        pre, k3 = self._pre(prefilter_ok, pods.n_pods)
+        self._check(self.lib.nosplan_upload(self.h, C.byref(cs), C.byref(cp), pre, filter_mode), "nosplan_upload")
+        self._snap = snap
+        del k1, k2, k3
+
+    def run(self):
+        self._check(self.lib.nosplan_run(self.h), "nosplan_run")
+
+    def download(self):
+        out, cnt, msk = alloc_partitioning(self._snap)
+        st = CStats()
+        self._check(self.lib.nosplan_download(self.h, C.byref(out), C.byref(st)), "nosplan_download")
+        return cnt, msk, st.as_dict()
+
+    def stream(self) -> int:
+        return int(self.lib.nosplan_stream(self.h) or 0)

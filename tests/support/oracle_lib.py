@@ -1,0 +1,57 @@
+"""ctypes wrapper of the CPU oracle (oracle/libnosoracle.so) -- test infrastructure."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from nos_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+FAITHFUL, INCREMENTAL = 0, 1
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(ORACLE_DIR, "libnosoracle.so")
+        srcs = [os.path.join(ORACLE_DIR, f) for f in ("nos_oracle.cpp", "nos_quota_oracle.cpp")] + \
+               [os.path.join(ROOT, "include", "nosplan.h")]
+        if not os.path.exists(path) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs if os.path.exists(s)):
+            subprocess.check_call(["make", "-C", ORACLE_DIR, "-s"])
+        _lib = C.CDLL(path)
+        _lib.nos_oracle_plan.argtypes = [C.POINTER(capi.CSnapshot), C.POINTER(capi.CPods), C.c_void_p, C.c_int32, C.c_int32,
+                                         C.POINTER(capi.CPartitioning), C.POINTER(capi.CStats), C.POINTER(C.c_double)]
+        _lib.nos_oracle_plan.restype = C.c_int
+        _lib.nos_oracle_sort_pods.argtypes = [C.POINTER(capi.CSnapshot), C.POINTER(capi.CPods), C.c_void_p]
+        _lib.nos_oracle_sort_pods.restype = C.c_int
+    return _lib
+
+
+def plan(snap, pods, prefilter_ok=None, filter_mode=0, mode=INCREMENTAL):
+    """-> (gpu_count, gpu_mask, stats dict, seconds)"""
+    cs, k1 = capi.c_snapshot(snap)
+    cp, k2 = capi.c_pods(pods)
+    out, cnt, msk = capi.alloc_partitioning(snap)
+    st = capi.CStats()
+    sec = C.c_double()
+    pre = None
+    if prefilter_ok is not None:
+        pa = np.ascontiguousarray(np.asarray(prefilter_ok, dtype=np.uint8))
+        pre = pa.ctypes.data
+    rc = lib().nos_oracle_plan(C.byref(cs), C.byref(cp), pre, filter_mode, mode, C.byref(out), C.byref(st), C.byref(sec))
+    if rc != 0:
+        raise RuntimeError(f"nos_oracle_plan -> {rc}")
+    return cnt, msk, st.as_dict(), sec.value
+
+
+def sort_pods(snap, pods):
+    cs, k1 = capi.c_snapshot(snap)
+    cp, k2 = capi.c_pods(pods)
+    order = np.zeros(max(1, pods.n_pods), np.int32)
+    rc = lib().nos_oracle_sort_pods(C.byref(cs), C.byref(cp), order.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"nos_oracle_sort_pods -> {rc}")
+    return order[:pods.n_pods]
