@@ -1,0 +1,437 @@
+// C-ABI of libnosplan.so (include/nosplan.h): handle, host-side preparation (NewPodSorter order, runs of
+// identical slice requests, one staged H2D copy), kernel launches, D2H of the plan.
+// There is no CPU planning path in this file: everything the reference's Plan() computes per node and per
+// pod happens in the kernels of prepass.cu / sweep.cu.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "nosplan_dev.cuh"
+
+namespace nsp {
+void launch_prepass(const DevProblem& pb, cudaStream_t st);
+void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
+cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
+cudaError_t sweep_prepare_device();
+int sweep_max_keys();
+}  // namespace nsp
+
+using namespace nsp;
+
+struct nosplan {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {};
+    // device arena + pinned staging (grown on demand, reused across calls)
+    unsigned char* d_arena = nullptr; size_t d_cap = 0;
+    unsigned char* h_stage = nullptr; size_t h_cap = 0;
+    unsigned char* h_out = nullptr; size_t h_out_cap = 0;
+    // current problem
+    bool uploaded = false, ran = false;
+    DevProblem pb{};
+    int32_t* d_cand_idx = nullptr;
+    unsigned char* d_work = nullptr; size_t work_bytes = 0;
+    size_t out_count_bytes = 0, out_mask_bytes = 0;
+    int launches = 0;
+    std::string err;
+};
+
+namespace {
+
+int fail(nosplan* h, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (h) h->err = buf;
+    return code;
+}
+
+#define CU(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return fail(h, NOSPLAN_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
+
+inline size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// ---- Go 1.18 sort.SliceStable (sort/zsortfunc.go stable_func / insertionSort_func / symMerge_func / rotate_func),
+// restated so that NewPodSorter (core/util.go:34-73) gives the reference's order even where its comparator is
+// not a strict weak order (mig/profile.go:84-96).
+template <class Less>
+struct GoStable {
+    int* d; int n; Less less;
+    bool lt(int i, int j) { return less(d[i], d[j]); }
+    void sw(int i, int j) { int t = d[i]; d[i] = d[j]; d[j] = t; }
+    void insertion(int a, int b) { for (int i = a + 1; i < b; ++i) for (int j = i; j > a && lt(j, j - 1); --j) sw(j, j - 1); }
+    void swap_range(int a, int b, int c) { for (int i = 0; i < c; ++i) sw(a + i, b + i); }
+    void rotate(int a, int m, int b) {
+        int i = m - a, j = b - m;
+        while (i != j) { if (i > j) { swap_range(m - i, m, j); i -= j; } else { swap_range(m - i, m + j - i, i); j -= i; } }
+        swap_range(m - i, m, i);
+    }
+    void sym_merge(int a, int m, int b) {
+        if (m - a == 1) {
+            int i = m, j = b;
+            while (i < j) { int h = (int)((unsigned)(i + j) >> 1); if (lt(h, a)) i = h + 1; else j = h; }
+            for (int k = a; k < i - 1; ++k) sw(k, k + 1);
+            return;
+        }
+        if (b - m == 1) {
+            int i = a, j = m;
+            while (i < j) { int h = (int)((unsigned)(i + j) >> 1); if (!lt(m, h)) i = h + 1; else j = h; }
+            for (int k = m; k > i; --k) sw(k, k - 1);
+            return;
+        }
+        int mid = (int)((unsigned)(a + b) >> 1), nn = mid + m, start, r;
+        if (m > mid) { start = nn - b; r = mid; } else { start = a; r = m; }
+        int p = nn - 1;
+        while (start < r) { int c = (int)((unsigned)(start + r) >> 1); if (!lt(p - c, c)) start = c + 1; else r = c; }
+        int end = nn - start;
+        if (start < m && m < end) rotate(start, m, end);
+        if (a < start && start < mid) sym_merge(a, start, mid);
+        if (mid < end && end < b) sym_merge(mid, end, b);
+    }
+    void run() {
+        int block = 20, a = 0, b = block;
+        while (b <= n) { insertion(a, b); a = b; b += block; }
+        insertion(a, n);
+        while (block < n) {
+            a = 0; b = 2 * block;
+            while (b <= n) { sym_merge(a, a + block, b); a = b; b += 2 * block; }
+            int m = a + block;
+            if (m < n) sym_merge(a, m, n);
+            block *= 2;
+        }
+    }
+};
+
+struct Layout {            // byte offsets into the arena / staging buffer
+    size_t model_off, geom, node_gpu_count, gpu_model, gpu_mem, gpu_used, gpu_free, gpu_umask, gpu_fmask,
+        node_alloc, node_req, node_allowed, node_npods,
+        pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, upload_end,
+        tot, lack, stats, entry_lack, work_end, cand_flag, cand_idx, out_count, out_mask, total;
+};
+
+int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes) {
+    if (dev_bytes > h->d_cap) {
+        if (h->d_arena) CU(h, cudaFree(h->d_arena));
+        h->d_arena = nullptr; h->d_cap = 0;
+        size_t cap = dev_bytes + dev_bytes / 4 + (1 << 20);
+        CU(h, cudaMalloc(&h->d_arena, cap));
+        h->d_cap = cap;
+    }
+    if (stage_bytes > h->h_cap) {
+        if (h->h_stage) CU(h, cudaFreeHost(h->h_stage));
+        h->h_stage = nullptr; h->h_cap = 0;
+        size_t cap = stage_bytes + stage_bytes / 4 + (1 << 20);
+        CU(h, cudaMallocHost(&h->h_stage, cap));
+        h->h_cap = cap;
+    }
+    if (out_bytes > h->h_out_cap) {
+        if (h->h_out) CU(h, cudaFreeHost(h->h_out));
+        h->h_out = nullptr; h->h_out_cap = 0;
+        size_t cap = out_bytes + out_bytes / 4 + 4096;
+        CU(h, cudaMallocHost(&h->h_out, cap));
+        h->h_out_cap = cap;
+    }
+    return NOSPLAN_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nosplan_create(int cuda_device, nosplan_t** out) {
+    if (!out) return NOSPLAN_E_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || cuda_device < 0 || cuda_device >= n) return NOSPLAN_E_CUDA;
+    nosplan* h = new (std::nothrow) nosplan();
+    if (!h) return NOSPLAN_E_NOMEM;
+    h->device = cuda_device;
+    if (cudaSetDevice(cuda_device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        sweep_prepare_device() != cudaSuccess) {
+        delete h;
+        return NOSPLAN_E_CUDA;
+    }
+    for (auto& e : h->ev)
+        if (cudaEventCreate(&e) != cudaSuccess) { delete h; return NOSPLAN_E_CUDA; }
+    *out = h;
+    return NOSPLAN_OK;
+}
+
+void nosplan_destroy(nosplan_t* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->d_arena) cudaFree(h->d_arena);
+    if (h->h_stage) cudaFreeHost(h->h_stage);
+    if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+const char* nosplan_last_error(const nosplan_t* h) { return h ? h->err.c_str() : "null handle"; }
+
+void* nosplan_stream(nosplan_t* h) { return h ? (void*)h->stream : nullptr; }
+
+int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
+                   int32_t filter_mode) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!s || !pods) return fail(h, NOSPLAN_E_INVALID, "null snapshot or pods");
+    h->uploaded = h->ran = false;
+    const int K = s->n_profiles, N = s->n_nodes, G = s->gpus_per_node, P = pods->n_pods;
+    const int R = 3 + K + s->n_other;
+    if (s->kind != NOSPLAN_KIND_MIG && s->kind != NOSPLAN_KIND_MPS) return fail(h, NOSPLAN_E_INVALID, "unknown kind %d", s->kind);
+    if (filter_mode < 0 || filter_mode > NOSPLAN_FILTER_RESOURCES_FIT) return fail(h, NOSPLAN_E_INVALID, "unknown filter mode %d", filter_mode);
+    if (K < 0 || N < 0 || P < 0 || G < 1 || s->n_other < 0) return fail(h, NOSPLAN_E_INVALID, "negative size");
+    if (K > NOSPLAN_MAX_PROFILES) return fail(h, NOSPLAN_E_LIMIT, "%d profiles > NOSPLAN_MAX_PROFILES", K);
+    if (G > NOSPLAN_MAX_GPUS) return fail(h, NOSPLAN_E_LIMIT, "%d GPUs per node > NOSPLAN_MAX_GPUS", G);
+    if (s->n_other > NOSPLAN_MAX_OTHER) return fail(h, NOSPLAN_E_LIMIT, "%d other resources > NOSPLAN_MAX_OTHER", s->n_other);
+    const bool mig = s->kind == NOSPLAN_KIND_MIG;
+    const int n_models = mig ? s->n_models : 0;
+    const int n_rows = (mig && n_models > 0) ? s->model_geom_offset[n_models] : 0;
+    if (n_models > MAX_MODELS) return fail(h, NOSPLAN_E_LIMIT, "%d GPU models > %d", n_models, MAX_MODELS);
+    if (n_rows > MAX_ROWS) return fail(h, NOSPLAN_E_LIMIT, "%d geometry rows > %d", n_rows, MAX_ROWS);
+    for (int m = 0; m < n_models; ++m) {
+        const int c = s->model_geom_offset[m + 1] - s->model_geom_offset[m];
+        if (c < 0 || c > NOSPLAN_MAX_GEOMS) return fail(h, NOSPLAN_E_LIMIT, "model %d has %d geometries > NOSPLAN_MAX_GEOMS", m, c);
+    }
+    for (int i = 0; i < N; ++i) {
+        if (s->node_gpu_count[i] < 0 || s->node_gpu_count[i] > G) return fail(h, NOSPLAN_E_INVALID, "node %d: gpu count out of range", i);
+        if (mig)
+            for (int j = 0; j < s->node_gpu_count[i]; ++j) {
+                const int m = s->gpu_model[(size_t)i * G + j];
+                if (m < 0 || m >= n_models) return fail(h, NOSPLAN_E_INVALID, "node %d gpu %d: model id out of range", i, j);
+            }
+    }
+    if ((long long)N * std::max(P, 1) > (1ll << 62)) return fail(h, NOSPLAN_E_LIMIT, "problem too large");
+
+    // ---- per-pod sort keys and validation
+    const int nnz = P > 0 ? pods->scalar_ptr[P] : 0;
+    std::vector<int> first_prof(P, -1);
+    std::vector<uint32_t> flags(P, 0);
+    int n_keys = 0;
+    for (int i = 0; i < P; ++i) {
+        const int a = pods->scalar_ptr[i], b = pods->scalar_ptr[i + 1];
+        if (a > b || b > nnz) return fail(h, NOSPLAN_E_INVALID, "pod %d: bad scalar_ptr", i);
+        bool other = false; int prev = 2;
+        for (int e = a; e < b; ++e) {
+            const int col = pods->scalar_col[e];
+            if (col < 3 || col >= R || col <= prev) return fail(h, NOSPLAN_E_INVALID, "pod %d: scalar columns must be in [3,R) and ascending", i);
+            prev = col;
+            if (col < 3 + K) {
+                if (first_prof[i] < 0) first_prof[i] = col - 3;
+                if (pods->scalar_qty[e] <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
+            } else other = true;
+        }
+        uint32_t f = 0;
+        if (!prefilter_ok || prefilter_ok[i]) f |= PF_PRE_OK;
+        if (other) f |= PF_HAS_OTHER;
+        if (a == b && pods->base[3 * (size_t)i] == 0 && pods->base[3 * (size_t)i + 1] == 0 && pods->base[3 * (size_t)i + 2] == 0) f |= PF_ZERO_REQ;
+        flags[i] = f;
+        const int k = pods->tracker_key[i];
+        if (k < 0 || k >= P) return fail(h, NOSPLAN_E_INVALID, "pod %d: tracker_key out of range", i);
+        n_keys = std::max(n_keys, k + 1);
+    }
+    if (n_keys > sweep_max_keys()) return fail(h, NOSPLAN_E_LIMIT, "%d tracker keys > %d", n_keys, sweep_max_keys());
+
+    // ---- NewPodSorter (core/util.go:34-73)
+    std::vector<int> order(P);
+    for (int i = 0; i < P; ++i) order[i] = i;
+    {
+        const int32_t* prio = pods->priority; const int32_t* pmem = s->profile_mem_gb; const int32_t* pgi = s->profile_gi;
+        const int* fp = first_prof.data();
+        auto less = [=](int a, int b) {
+            if (prio[a] != prio[b]) return prio[a] > prio[b];
+            if (fp[a] < 0 || fp[b] < 0) return false;
+            if (pmem[fp[a]] < pmem[fp[b]]) return true;                       // SmallerThan: mig/profile.go:84-96, slicing/profile.go:36-42
+            return mig && pgi[fp[a]] < pgi[fp[b]];
+        };
+        GoStable<decltype(less)> gs{order.data(), P, less};
+        gs.run();
+    }
+
+    // ---- runs of identical slice requests in sorted order
+    std::vector<RunRec> runs;
+    auto same_slices = [&](int x, int y) {
+        int ex = pods->scalar_ptr[x], ey = pods->scalar_ptr[y];
+        const int bx = pods->scalar_ptr[x + 1], by = pods->scalar_ptr[y + 1];
+        for (;;) {
+            const bool sx = ex < bx && pods->scalar_col[ex] < 3 + K, sy = ey < by && pods->scalar_col[ey] < 3 + K;
+            if (!sx || !sy) return sx == sy;
+            if (pods->scalar_col[ex] != pods->scalar_col[ey] || pods->scalar_qty[ex] != pods->scalar_qty[ey]) return false;
+            ++ex; ++ey;
+        }
+    };
+    for (int si = 0; si < P; ++si) {
+        const int oi = order[si];
+        if (si > 0 && same_slices(order[si - 1], oi)) { runs.back().len++; continue; }
+        RunRec r; std::memset(&r, 0, sizeof r);
+        r.start = si; r.len = 1;
+        for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1] && pods->scalar_col[e] < 3 + K; ++e) {
+            const long long q = pods->scalar_qty[e];
+            r.q[pods->scalar_col[e] - 3] = (uint16_t)std::min<long long>(q, 65535);   // device counts are <= 255: anything larger can never fit
+            r.n_ent++;
+        }
+        runs.push_back(r);
+    }
+    const int n_runs = (int)runs.size();
+
+    // ---- layout
+    Layout L; size_t o = 0;
+    auto put = [&](size_t& field, size_t bytes) { field = o; o = al(o + bytes); };
+    const size_t NG = (size_t)N * G;
+    put(L.model_off, sizeof(int32_t) * (n_models + 1));
+    put(L.geom, 16 * (size_t)n_rows);
+    put(L.node_gpu_count, 4 * (size_t)N);
+    put(L.gpu_model, 4 * NG); put(L.gpu_mem, 4 * NG);
+    put(L.gpu_used, 16 * NG); put(L.gpu_free, 16 * NG);
+    put(L.gpu_umask, 2 * NG); put(L.gpu_fmask, 2 * NG);
+    put(L.node_alloc, 8 * (size_t)N * R); put(L.node_req, 8 * (size_t)N * R);
+    put(L.node_allowed, 4 * (size_t)N); put(L.node_npods, 4 * (size_t)N);
+    put(L.pod_cpu, 8 * (size_t)P); put(L.pod_mem, 8 * (size_t)P); put(L.pod_eph, 8 * (size_t)P);
+    put(L.pod_key, 4 * (size_t)P); put(L.pod_flags, 4 * (size_t)P);
+    put(L.pod_sptr, 4 * ((size_t)P + 1)); put(L.pod_scol, 4 * (size_t)nnz); put(L.pod_sqty, 8 * (size_t)nnz);
+    put(L.runs, sizeof(RunRec) * (size_t)n_runs);
+    L.upload_end = o;
+    put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats)); put(L.entry_lack, 4 * (size_t)n_keys * KP);
+    L.work_end = o;
+    put(L.cand_flag, (size_t)N); put(L.cand_idx, 4 * (size_t)N);
+    put(L.out_count, 16 * NG); put(L.out_mask, 2 * NG);
+    L.total = o;
+
+    CU(h, cudaSetDevice(h->device));
+    const size_t out_bytes = al(16 * NG) + al(2 * NG) + al(sizeof(DevStats));
+    int rc = ensure(h, L.total, L.upload_end, out_bytes);
+    if (rc != NOSPLAN_OK) return rc;
+
+    // ---- stage (one pinned buffer, one H2D copy)
+    unsigned char* S = h->h_stage;
+    if (n_models > 0) std::memcpy(S + L.model_off, s->model_geom_offset, sizeof(int32_t) * (n_models + 1));
+    else std::memset(S + L.model_off, 0, sizeof(int32_t));
+    if (n_rows) std::memcpy(S + L.geom, s->geom_counts, 16 * (size_t)n_rows);
+    if (N) {
+        std::memcpy(S + L.node_gpu_count, s->node_gpu_count, 4 * (size_t)N);
+        std::memcpy(S + L.gpu_model, s->gpu_model, 4 * NG);
+        std::memcpy(S + L.gpu_mem, s->gpu_memory_gb, 4 * NG);
+        std::memcpy(S + L.gpu_used, s->gpu_used, 16 * NG);
+        std::memcpy(S + L.gpu_free, s->gpu_free, 16 * NG);
+        std::memcpy(S + L.gpu_umask, s->gpu_used_mask, 2 * NG);
+        std::memcpy(S + L.gpu_fmask, s->gpu_free_mask, 2 * NG);
+        std::memcpy(S + L.node_alloc, s->node_alloc, 8 * (size_t)N * R);
+        std::memcpy(S + L.node_req, s->node_requested, 8 * (size_t)N * R);
+        std::memcpy(S + L.node_allowed, s->node_allowed_pods, 4 * (size_t)N);
+        std::memcpy(S + L.node_npods, s->node_num_pods, 4 * (size_t)N);
+    }
+    {
+        long long* cpu = (long long*)(S + L.pod_cpu); long long* mem = (long long*)(S + L.pod_mem); long long* eph = (long long*)(S + L.pod_eph);
+        int32_t* key = (int32_t*)(S + L.pod_key); uint32_t* fl = (uint32_t*)(S + L.pod_flags);
+        int32_t* sptr = (int32_t*)(S + L.pod_sptr); int32_t* scol = (int32_t*)(S + L.pod_scol); long long* sqty = (long long*)(S + L.pod_sqty);
+        int w = 0;
+        for (int si = 0; si < P; ++si) {
+            const int oi = order[si];
+            cpu[si] = pods->base[3 * (size_t)oi]; mem[si] = pods->base[3 * (size_t)oi + 1]; eph[si] = pods->base[3 * (size_t)oi + 2];
+            key[si] = pods->tracker_key[oi]; fl[si] = flags[oi];
+            sptr[si] = w;
+            for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1]; ++e) { scol[w] = pods->scalar_col[e]; sqty[w] = pods->scalar_qty[e]; ++w; }
+        }
+        sptr[P] = w;
+        if (n_runs) std::memcpy(S + L.runs, runs.data(), sizeof(RunRec) * (size_t)n_runs);
+    }
+
+    CU(h, cudaEventRecord(h->ev[0], h->stream));
+    CU(h, cudaMemcpyAsync(h->d_arena, S, L.upload_end, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemsetAsync(h->d_arena + L.out_count, 0, L.total - L.out_count, h->stream));
+    CU(h, cudaEventRecord(h->ev[1], h->stream));
+
+    // ---- device problem description
+    DevProblem& pb = h->pb;
+    std::memset(&pb, 0, sizeof pb);
+    unsigned char* A = h->d_arena;
+    pb.kind = s->kind; pb.K = K; pb.R = R; pb.n_other = s->n_other;
+    pb.N = N; pb.G = G; pb.P = P; pb.n_keys = n_keys; pb.n_runs = n_runs; pb.filter_mode = filter_mode;
+    pb.n_models = n_models; pb.n_rows = n_rows;
+    for (int p = 0; p < KP; ++p) { pb.pmem[p] = p < K ? s->profile_mem_gb[p] : 0; pb.pgi[p] = p < K ? s->profile_gi[p] : 0; }
+    pb.model_off = (const int32_t*)(A + L.model_off); pb.geom = (const uint4*)(A + L.geom);
+    pb.node_gpu_count = (const int32_t*)(A + L.node_gpu_count);
+    pb.gpu_model = (const int32_t*)(A + L.gpu_model); pb.gpu_mem = (const int32_t*)(A + L.gpu_mem);
+    pb.gpu_used = (const uint4*)(A + L.gpu_used); pb.gpu_free = (const uint4*)(A + L.gpu_free);
+    pb.gpu_umask = (const uint16_t*)(A + L.gpu_umask); pb.gpu_fmask = (const uint16_t*)(A + L.gpu_fmask);
+    pb.node_alloc = (const long long*)(A + L.node_alloc); pb.node_req = (const long long*)(A + L.node_req);
+    pb.node_allowed_pods = (const int32_t*)(A + L.node_allowed); pb.node_num_pods = (const int32_t*)(A + L.node_npods);
+    pb.pod_cpu = (const long long*)(A + L.pod_cpu); pb.pod_mem = (const long long*)(A + L.pod_mem); pb.pod_eph = (const long long*)(A + L.pod_eph);
+    pb.pod_key = (const int32_t*)(A + L.pod_key); pb.pod_flags = (const uint32_t*)(A + L.pod_flags);
+    pb.pod_sptr = (const int32_t*)(A + L.pod_sptr); pb.pod_scol = (const int32_t*)(A + L.pod_scol); pb.pod_sqty = (const long long*)(A + L.pod_sqty);
+    pb.runs = (const RunRec*)(A + L.runs);
+    pb.tot = (long long*)(A + L.tot); pb.lack = (int32_t*)(A + L.lack); pb.stats = (DevStats*)(A + L.stats);
+    pb.entry_lack = (int32_t*)(A + L.entry_lack);
+    pb.cand_flag = (uint8_t*)(A + L.cand_flag);
+    pb.out_count = (uint4*)(A + L.out_count); pb.out_mask = (uint16_t*)(A + L.out_mask);
+    h->d_cand_idx = (int32_t*)(A + L.cand_idx);
+    h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot;
+    h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
+    h->uploaded = true;
+    return NOSPLAN_OK;
+}
+
+int nosplan_run(nosplan_t* h) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_run before nosplan_upload");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaEventRecord(h->ev[2], h->stream));
+    CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
+    launch_prepass(h->pb, h->stream);
+    launch_tracker_init(h->pb, h->stream);
+    CU(h, cudaGetLastError());
+    CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
+    CU(h, cudaEventRecord(h->ev[3], h->stream));
+    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1;
+    h->ran = true;
+    return NOSPLAN_OK;
+}
+
+int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->ran) return fail(h, NOSPLAN_E_INVALID, "nosplan_download before nosplan_run");
+    CU(h, cudaSetDevice(h->device));
+    unsigned char* O = h->h_out;
+    const size_t o_mask = al(h->out_count_bytes), o_stats = o_mask + al(h->out_mask_bytes);
+    CU(h, cudaEventRecord(h->ev[4], h->stream));
+    if (h->out_count_bytes) {
+        CU(h, cudaMemcpyAsync(O, h->pb.out_count, h->out_count_bytes, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaMemcpyAsync(O + o_mask, h->pb.out_mask, h->out_mask_bytes, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CU(h, cudaMemcpyAsync(O + o_stats, h->pb.stats, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaEventRecord(h->ev[5], h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    if (out && h->out_count_bytes) {
+        if (!out->gpu_count || !out->gpu_mask) return fail(h, NOSPLAN_E_INVALID, "null output buffers");
+        std::memcpy(out->gpu_count, O, h->out_count_bytes);
+        std::memcpy(out->gpu_mask, O + o_mask, h->out_mask_bytes);
+    }
+    if (stats) {
+        DevStats ds; std::memcpy(&ds, O + o_stats, sizeof ds);
+        std::memset(stats, 0, sizeof *stats);
+        stats->candidates = ds.candidates; stats->visited_nodes = ds.visited_nodes; stats->geometry_evals = ds.geometry_evals;
+        stats->placements = ds.placements; stats->candidate_nodes = ds.candidate_nodes;
+        stats->lacking_at_start = ds.lacking_at_start; stats->lacking_at_end = ds.lacking_at_end;
+        cudaEventElapsedTime(&stats->ms_h2d, h->ev[0], h->ev[1]);
+        cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
+        cudaEventElapsedTime(&stats->ms_d2h, h->ev[4], h->ev[5]);
+        stats->kernel_launches = h->launches;
+    }
+    return NOSPLAN_OK;
+}
+
+int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods* pods, const uint8_t* prefilter_ok,
+                 int32_t filter_mode, nosplan_partitioning* out, nosplan_stats* stats) {
+    int rc = nosplan_upload(h, snap, pods, prefilter_ok, filter_mode);
+    if (rc != NOSPLAN_OK) return rc;
+    rc = nosplan_run(h);
+    if (rc != NOSPLAN_OK) return rc;
+    return nosplan_download(h, out, stats);
+}
+
+}  // extern "C"

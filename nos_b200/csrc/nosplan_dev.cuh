@@ -1,0 +1,93 @@
+// Device-side problem description shared by the planning kernels (sm_100a).
+// Layout notes are in DESIGN.md section "Data layout in HBM".
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/nosplan.h"
+
+namespace nsp {
+
+constexpr int KP = NOSPLAN_MAX_PROFILES;                                   // 16 profile slots
+constexpr int RMAX = 3 + NOSPLAN_MAX_PROFILES + NOSPLAN_MAX_OTHER;         // resource columns
+constexpr int MAX_ROWS = 256;                                              // geometry rows cached in smem (all models)
+constexpr int MAX_MODELS = 32;
+constexpr int RUN_CACHE = 64;                                              // runs whose first chunk of pods lives in smem
+
+// per-pod flags (sorted order)
+constexpr uint32_t PF_PRE_OK = 1u;      // PreFilter verdict (capacity_scheduling.go:190-278 is a per-pod constant)
+constexpr uint32_t PF_HAS_OTHER = 2u;   // requests a non-slice scalar resource
+constexpr uint32_t PF_ZERO_REQ = 4u;    // all-zero request (NodeResourcesFit short-circuit)
+
+// A run = maximal stretch of consecutive pods (in NewPodSorter order) with the same slice request.
+struct __align__(16) RunRec {
+    int32_t start, len;
+    uint16_t q[KP];        // requested quantity per profile id, 0 = not requested
+    uint16_t n_ent;        // number of requested profiles
+    uint16_t pad[3];
+};
+static_assert(sizeof(RunRec) == 48, "RunRec layout");
+
+struct DevStats {
+    long long candidates, visited_nodes, geometry_evals, placements, candidate_nodes;
+    int lacking_at_start, lacking_at_end;
+};
+
+struct DevProblem {
+    int kind, K, R, n_other;
+    int N, G, P, n_keys, n_runs, filter_mode;
+    int n_models, n_rows;
+    int32_t pmem[KP], pgi[KP];
+    // geometry tables
+    const int32_t* model_off;        // [n_models+1]
+    const uint4* geom;               // [n_rows] 16 counts
+    // snapshot
+    const int32_t* node_gpu_count;   // [N]
+    const int32_t* gpu_model;        // [N*G]
+    const int32_t* gpu_mem;          // [N*G]
+    const uint4* gpu_used;           // [N*G]
+    const uint4* gpu_free;           // [N*G]
+    const uint16_t* gpu_umask;       // [N*G]
+    const uint16_t* gpu_fmask;       // [N*G]
+    const long long* node_alloc;     // [N][R]
+    const long long* node_req;       // [N][R]
+    const int32_t* node_allowed_pods;
+    const int32_t* node_num_pods;
+    // pods in sorted order
+    const long long* pod_cpu;        // [P]
+    const long long* pod_mem;
+    const long long* pod_eph;
+    const int32_t* pod_key;
+    const uint32_t* pod_flags;
+    const int32_t* pod_sptr;         // [P+1] CSR of scalar entries
+    const int32_t* pod_scol;
+    const long long* pod_sqty;
+    const RunRec* runs;              // [n_runs]
+    // work area (zeroed before each run)
+    long long* tot;                  // [KP] sum over nodes of (alloc - requested) per slice column
+    int32_t* lack;                   // [KP] SliceTracker.lackingSlices
+    int32_t* entry_lack;             // [n_keys][KP] lackingSlicesLookup
+    uint8_t* cand_flag;              // [N] HasFreeCapacity
+    // outputs
+    uint4* out_count;                // [N*G]
+    uint16_t* out_mask;              // [N*G]
+    DevStats* stats;
+};
+
+__device__ __forceinline__ unsigned byte_of(const uint4& v, int p) {
+    unsigned w = (p < 8) ? ((p < 4) ? v.x : v.y) : ((p < 12) ? v.z : v.w);
+    return (w >> ((p & 3) * 8)) & 0xffu;
+}
+
+__device__ __forceinline__ uint16_t nz_mask(const uint4& v) {
+    uint16_t m = 0;
+#pragma unroll
+    for (int p = 0; p < KP; ++p) m |= (uint16_t)((byte_of(v, p) != 0) << p);
+    return m;
+}
+
+__device__ __forceinline__ uint4 add_bytes(const uint4& a, const uint4& b) {
+    return make_uint4(__vadd4(a.x, b.x), __vadd4(a.y, b.y), __vadd4(a.z, b.z), __vadd4(a.w, b.w));
+}
+
+}  // namespace nsp

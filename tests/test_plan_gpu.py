@@ -1,0 +1,146 @@
+"""Parity of the CUDA planner (libnosplan.so through the C-ABI) against the oracle -- bit-exact plans and counters."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import nos_model as m
+from nos_b200 import capi, packing as pk, synth
+from nos_b200.geometries import DEFAULT_KNOWN_GEOMETRIES, HELM_KNOWN_GEOMETRIES
+from support import oracle_lib as ol
+from support import randcases as rc
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+PLAN = json.load(open(os.path.join(GOLD, "planner_plan.json")))["cases"]
+COUNTERS = ("candidates", "visited_nodes", "placements", "geometry_evals", "candidate_nodes", "lacking_at_start", "lacking_at_end")
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import __graft_entry__ as g
+    g.build()
+    e = capi.Engine(0)
+    yield e
+    e.close()
+
+
+def check(eng, snap, pods, pre, fm, what=""):
+    cnt, msk, st = eng.plan(snap, pods, pre, fm)
+    ocnt, omsk, ost, _ = ol.plan(snap, pods, pre, fm, ol.INCREMENTAL)
+    assert np.array_equal(msk, omsk), f"{what}: key masks differ"
+    assert np.array_equal(cnt, ocnt), f"{what}: counts differ"
+    for k in COUNTERS:
+        assert st[k] == ost[k], f"{what}: {k} {st[k]} != {ost[k]}"
+    return st
+
+
+@pytest.mark.parametrize("c", PLAN, ids=[f"{c['kind']}:{c['name'][:50]}" for c in PLAN])
+def test_golden_planner(eng, c):
+    kind = pk.KIND_BY_NAME[c["kind"]]
+    nodes = pk.nodes_from_v1(kind, c["nodes"], m.DEFAULT_KNOWN_GEOMETRIES)
+    s, p = pk.pack(kind, nodes, c["pods"], m.DEFAULT_KNOWN_GEOMETRIES)
+    fm = pk.FILTER_NONE if c["filter_ok"] else pk.FILTER_REJECT_ALL
+    cnt, msk, _ = eng.plan(s, p, [1 if c["prefilter_ok"] else 0] * p.n_pods, fm)
+    got = sorted((0 if c["kind"] == "mig" else i, tuple(sorted(r.items()))) for gl in pk.unpack_plan(s, cnt, msk).values() for i, r in gl)
+    exp = sorted((0 if c["kind"] == "mig" else e["gpu_index"], tuple(sorted(e["resources"].items()))) for e in c["expected"])
+    assert got == exp
+
+
+def _has_zero_qty_slice(kind, pods):
+    for p in pods:
+        for r, q in pk.compute_pod_request(p).items():
+            if q <= 0 and pk.slice_profile_of(kind, r) is not None:
+                return True
+    return False
+
+
+@pytest.mark.parametrize("block", range(8))
+def test_random_small_vs_oracle(eng, block):
+    placed = 0
+    for seed in range(block * 400, (block + 1) * 400):
+        kind_name, nodes, pods, pre, fmode = rc.rand_case(seed)
+        kind = pk.KIND_BY_NAME[kind_name]
+        if _has_zero_qty_slice(kind, pods):
+            continue
+        s, p = pk.pack(kind, nodes, pods, m.DEFAULT_KNOWN_GEOMETRIES)
+        st = check(eng, s, p, pre, fmode, f"seed {seed}")
+        placed += st["placements"] > 0
+    assert placed > 30
+
+
+@pytest.mark.parametrize("fm", [pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT], ids=["none", "fit"])
+@pytest.mark.parametrize("shape", [(1, 1, 10), (8, 8, 40), (64, 8, 256), (200, 8, 1000), (333, 5, 777)])
+def test_synth_mig(eng, shape, fm):
+    for regime in ("saturating", "satisfiable"):
+        s, p = synth.mig_cluster(*shape, seed=0xC2 + shape[0], regime=regime)
+        check(eng, s, p, None, fm, f"mig {shape} {regime}")
+
+
+@pytest.mark.parametrize("fm", [pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT], ids=["none", "fit"])
+@pytest.mark.parametrize("shape", [(1, 1, 10), (8, 8, 40), (64, 8, 256), (200, 8, 1000)])
+def test_synth_mps(eng, shape, fm):
+    for regime in ("saturating", "satisfiable"):
+        s, p = synth.mps_cluster(*shape, seed=0xC3 + shape[0], regime=regime)
+        check(eng, s, p, None, fm, f"mps {shape} {regime}")
+
+
+def test_helm_table_order(eng):
+    """Same model, production table (different row order -> different canonical tie-breaks)."""
+    s, p = synth.mig_cluster(100, 8, 500, seed=7, known=HELM_KNOWN_GEOMETRIES, model="NVIDIA-A100-80GB-PCIe")
+    check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "helm table")
+
+
+def test_config_c2_full_size(eng):
+    """BASELINE config #2: 1,000 nodes x 8 A100-80GB, 5,000 pending pods."""
+    s, p = synth.mig_cluster(1000, 8, 5000, seed=0xC2)
+    for fm in (pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT):
+        st = check(eng, s, p, None, fm, "C2")
+        assert st["candidates"] == 5_000_000
+
+
+def test_config_c3_full_size(eng):
+    """BASELINE config #3: 5,000 nodes x 8 GPUs MPS, 20,000 pending pods."""
+    s, p = synth.mps_cluster(5000, 8, 20000, seed=0xC3)
+    st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "C3")
+    assert st["candidates"] == st["visited_nodes"] * 20000
+
+
+def test_north_star_size_properties(eng):
+    """10k nodes x 8 GPUs, 10k pods: compared with the incremental oracle and through size-independent
+    properties: used devices are never deleted, geometry of every touched GPU is an allowed one, idempotence of
+    a second call on the same handle."""
+    s, p = synth.mig_cluster(10000, 8, 10000, seed=0xC5)
+    st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "10k x 10k")
+    assert st["candidates"] == st["visited_nodes"] * 10000
+    cnt, msk, st1 = eng.plan(s, p, None, pk.FILTER_RESOURCES_FIT)
+    cnt2, msk2, st2 = eng.plan(s, p, None, pk.FILTER_RESOURCES_FIT)
+    assert np.array_equal(cnt, cnt2) and np.array_equal(msk, msk2)
+    assert (cnt.astype(int) >= s.gpu_used.astype(int)).all()
+    init = s.gpu_used + s.gpu_free
+    changed = (cnt != init).any(1)
+    rows = {tuple(r) for r in s.geom_counts}
+    assert changed.any()
+    assert all(tuple(r) in rows for r in cnt[changed])
+
+
+def test_prefilter_vector_and_duplicates(eng):
+    s, p = synth.mig_cluster(50, 4, 300, seed=11)
+    rng = np.random.default_rng(3)
+    pre = (rng.random(300) < 0.7).astype(np.uint8)
+    p.tracker_key[:] = rng.integers(0, 40, 300)          # many pods share a namespace/name
+    check(eng, s, p, pre, pk.FILTER_RESOURCES_FIT, "prefilter+dups")
+    check(eng, s, p, pre, pk.FILTER_REJECT_ALL, "reject all")
+
+
+def test_errors_are_reported_not_crashes(eng):
+    s, p = synth.mig_cluster(4, 2, 8, seed=1)
+    p.scalar_qty[0] = 0
+    with pytest.raises(capi.NosplanError):
+        eng.plan(s, p, None, 0)
+    p.scalar_qty[0] = 1
+    with pytest.raises(capi.NosplanError):
+        eng.plan(s, p, None, 7)
+    eng.plan(s, p, None, 0)                               # the handle stays usable
