@@ -539,7 +539,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
         st->candidates = st_visited * pb.P;
         st->geometry_evals = st_evals;
         st->placements = st_place;
-        st->candidate_nodes = n_cand;
+        st->candidate_nodes = lack_start > 0 ? n_cand : 0;   // GetCandidateNodes is not reached on the early return (planner.go:80-83)
         st->lacking_at_start = lack_start;
     }
     const int lack_end = __popc(__ballot_sync(FULL, lack > 0));
