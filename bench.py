@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""bench.py -- planner candidates/sec and Plan() latency on a synthetic 10k-node snapshot (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is one Plan() over the packed snapshot: prepass + tracker-init + sweep kernels (nosplan_run).
+`value` is measured with the snapshot already resident in HBM (CUDA events on the engine's stream, L2 flushed
+between iterations); `e2e` is the same Plan() through nosplan_plan with HOST buffers, i.e. including the H2D
+copy of the snapshot and the D2H copy of the plan, by wall clock.  One JSON line is printed by rank 0.
+
+--impl reference times the reference's own algorithm on the host cores: the reference is Go and there is no Go
+toolchain on the box, so it is the faithful C++ port (oracle/nos_oracle.cpp, NOS_ORACLE_FAITHFUL: re-sums every
+node per gate check and clones every node per fork, like core/snapshot.go) on a bounded sub-snapshot of the
+same recipe.  Plan() is single-goroutine in the reference, so it runs on one core.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (kind, nodes, gpus/node, pods, seed)
+    "mig-10k": ("mig", 10000, 8, 10000, 0xC5),      # north star: 10k-node x 8-GPU MIG snapshot, 10k pending pods
+    "mig-c2": ("mig", 1000, 8, 5000, 0xC2),         # BASELINE config #2
+    "mps-c3": ("mps", 5000, 8, 20000, 0xC3),        # BASELINE config #3
+    "mig-100k": ("mig", 100000, 8, 10000, 0xC5),    # scale sweep upper end
+}
+FILTER_RESOURCES_FIT = 2
+
+
+def make_workload(name, seed_offset=0, nodes=None, pods=None):
+    from nos_b200 import synth
+    kind, n, g, p, seed = WORKLOADS[name]
+    n = nodes or n
+    p = pods or p
+    if kind == "mig":
+        return synth.mig_cluster(n, g, p, seed=seed + seed_offset, regime="saturating")
+    return synth.mps_cluster(n, g, p, seed=seed + seed_offset, regime="saturating")
+
+
+def algorithmic_bytes(snap, pods):
+    """Compulsory traffic of one Plan(): every input element read once, every output written once, with the
+    logical row sizes of SURVEY.md section 8(d): 256 B/node (G=8), 32 B/pod, 16 B/GPU of output, tables."""
+    n, g, p = snap.n_nodes, snap.gpus_per_node, pods.n_pods
+    b_node = g * 16 + 48 + 8 + 64
+    return n * b_node + p * 32 + int(snap.geom_counts.size) + n * g * 16
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic():
+    """dram bytes per sweep launch from the committed ncu capture, if any (profiles/sweep_traffic.json)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "sweep_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, f"/tmp/nosplan_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 8:
+                continue
+            try:
+                sm.append(float(parts[0])); smax = float(parts[1])
+            except ValueError:
+                continue
+            for nme, val in zip(names, parts[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference(args):
+    """The reference algorithm (faithful port) on the host: bounded sub-snapshot of the same recipe."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import __graft_entry__ as g
+    if not os.path.exists(os.path.join(ROOT, "oracle", "libnosoracle.so")):
+        g.build()
+    from support import oracle_lib as ol
+    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
+    budget = 90.0 / max(1, args.steps + args.warmup)
+    n = int(max(100, min(1000, (budget / 1.0e-7) ** (1.0 / 3.0))))       # faithful cost ~ 2e-8 s * N^2 * P, P = N * p_full/n_full
+    n = min(n, n_full)
+    p = max(10, int(round(n * p_full / n_full)))
+    snap, pods = make_workload(args.workload, nodes=n, pods=p)
+    times, cands = [], 0
+    for i in range(args.warmup + args.steps):
+        _, _, st, sec = ol.plan(snap, pods, None, FILTER_RESOURCES_FIT, ol.FAITHFUL)
+        if i >= args.warmup:
+            times.append(sec)
+            cands = st["candidates"]
+    total = sum(times)
+    value = cands * len(times) / total if total > 0 else 0.0
+    sample = (f"faithful C++ port of core.Planner.Plan (O(N^2 P): re-sum all nodes per gate, clone all nodes per fork) on a "
+              f"{n}-node x {gg}-GPU, {p}-pod sub-snapshot of the {args.workload} recipe; single thread (Plan() is single-goroutine; "
+              f"Go toolchain absent so the Go planner itself cannot run)")
+    line = {
+        "impl": "reference", "metric": "planner_candidates_per_sec", "value": value, "unit": "candidates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / max(1, len(times)),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": {"workload": args.workload, "nodes": n_full, "gpus_per_node": gg, "pods": p_full, "regime": "saturating",
+                   "filter": "resources_fit", "sample_nodes": n, "sample_pods": p},
+        "cpu_baseline": {"value": value, "unit": "candidates/s", "cores": 1, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    import __graft_entry__ as g
+    from nos_b200 import capi
+    if not os.path.exists(g.LIB):
+        g.build()
+
+    # node-sharding of ONE Plan() needs the speculative sweep (DESIGN.md "Multi-GPU"); until then every rank plans an
+    # independent snapshot of the same shape (replicas): weak scaling, no data-path collective.
+    snap, pods = make_workload(args.workload, seed_offset=rank)
+    eng = capi.Engine(local)
+    eng.upload(snap, pods, None, FILTER_RESOURCES_FIT)
+    ext = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")     # > 126 MB L2
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def one_step(timed):
+        with torch.cuda.stream(ext):
+            flush.zero_()
+        s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
+        s.record(ext)
+        eng.run()
+        e.record(ext)
+        _, _, st = eng.download()           # synchronises; outside the timed pair of events
+        return s.elapsed_time(e), st
+
+    for _ in range(max(3, args.warmup)):
+        one_step(False)
+    sampler = ClockSampler(local)
+    sync_all()
+    sampler.start()
+    step_ms, sweep_ms, st = [], [], None
+    for _ in range(args.steps):
+        ms, st = one_step(True)
+        step_ms.append(ms); sweep_ms.append(st["ms_sweep"])
+    sync_all()
+    # ---- end to end: host buffers in, host buffers out, wall clock (H2D + kernels + D2H inside)
+    for _ in range(2):
+        eng.plan(snap, pods, None, FILTER_RESOURCES_FIT)
+    sync_all()
+    e2e_s = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        _, _, est = eng.plan(snap, pods, None, FILTER_RESOURCES_FIT)
+        e2e_s.append(time.perf_counter() - t0)
+    sync_all()
+    clocks = sampler.stop()
+
+    total_ms = float(sum(step_ms))
+    e2e_total = float(sum(e2e_s))
+    cands = int(st["candidates"])
+    if world > 1:
+        t = torch.tensor([total_ms, e2e_total], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e2e_total = float(t[0]), float(t[1])
+        c = torch.tensor([cands], dtype=torch.int64, device=f"cuda:{local}")
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        cands_all = int(c[0])
+    else:
+        cands_all = cands
+    if rank != 0:
+        eng.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    value = cands_all * args.steps / (total_ms / 1e3)
+    e2e_value = cands_all * args.steps / e2e_total
+    peak, peak_src = measured_peak()
+    b_plan = algorithmic_bytes(snap, pods)
+    sweep_avg_ms = float(np.mean(sweep_ms))
+    achieved = b_plan / (sweep_avg_ms / 1e3) / 1e9
+    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
+    line = {
+        "metric": "planner_candidates_per_sec", "value": value, "unit": "candidates/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": {"workload": args.workload, "kind": kind, "nodes": n_full, "gpus_per_node": gg, "pods": p_full,
+                   "regime": "saturating", "filter": "resources_fit", "parallelism": f"replicas x{world}",
+                   "l2": "flushed between iterations (256 MiB device write)", "candidates_per_plan": cands,
+                   "visited_nodes": int(st["visited_nodes"]), "placements": int(st["placements"])},
+        "plan_p50_ms": float(np.median(step_ms)), "plan_p95_ms": float(np.percentile(step_ms, 95)),
+        "kernel_ms": {"prepass": float(st["ms_prepass"]), "tracker_init": float(st["ms_tracker"]), "sweep": sweep_avg_ms},
+        "roofline": {"bound": "hbm", "kernel": "k_plan_sweep", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": recorded_traffic(), "algorithmic_bytes": b_plan, "peak_source": peak_src},
+        "e2e": {"value": e2e_value, "unit": "candidates/s", "h2d_bytes_per_step": int(est["h2d_bytes"]),
+                "d2h_bytes_per_step": int(est["d2h_bytes"]), "ms_per_step": 1e3 * e2e_total / args.steps,
+                "ms_h2d": float(est["ms_h2d"]), "ms_kernels": float(est["ms_kernels"]), "ms_d2h": float(est["ms_d2h"])},
+        "gpu_launches": int(st["kernel_launches"]) * args.steps,
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        from support import oracle_lib as ol
+        n = min(n_full, 450)
+        p = max(10, int(round(n * p_full / n_full)))
+        ssnap, spods = make_workload(args.workload, nodes=n, pods=p)
+        _, _, ost, sec = ol.plan(ssnap, spods, None, FILTER_RESOURCES_FIT, ol.FAITHFUL)
+        _, _, ist, isec = ol.plan(snap, pods, None, FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+        line["cpu_baseline"] = {
+            "value": ost["candidates"] / sec, "unit": "candidates/s", "cores": 1, "kind": "port",
+            "sample": f"faithful C++ port of the reference algorithm (O(N^2 P)) on a {n}-node x {gg}-GPU, {p}-pod sub-snapshot "
+                      f"of the same recipe, {sec:.1f} s on one core; cost per candidate grows linearly with N",
+            "incremental_full_size": {"value": ist["candidates"] / isec, "seconds": isec,
+                                      "note": "same plan via running totals (oracle incremental mode), full workload, one core"}}
+    print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="mig-10k", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

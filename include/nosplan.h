@@ -116,9 +116,11 @@ typedef struct nosplan_stats {
     int64_t candidate_nodes;           /* len(GetCandidateNodes()) */
     int32_t lacking_at_start;          /* number of lacking profiles after NewSliceTracker */
     int32_t lacking_at_end;
-    float   ms_h2d, ms_kernels, ms_d2h;/* CUDA-event times of the last call */
+    float   ms_h2d, ms_kernels, ms_d2h;/* CUDA-event times of the last call (ms_kernels = whole run()) */
+    float   ms_prepass, ms_tracker, ms_sweep; /* per-kernel CUDA-event times inside ms_kernels */
     int32_t kernel_launches;
     int32_t reserved;
+    int64_t h2d_bytes, d2h_bytes;      /* bytes copied by upload() / download() */
 } nosplan_stats;
 
 /* Create an engine bound to one CUDA device.  Replaces: mig.NewPlanner / mps.NewPlanner

@@ -54,7 +54,9 @@ class CStats(C.Structure):
         ("placements", C.c_int64), ("candidate_nodes", C.c_int64),
         ("lacking_at_start", C.c_int32), ("lacking_at_end", C.c_int32),
         ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float),
+        ("ms_prepass", C.c_float), ("ms_tracker", C.c_float), ("ms_sweep", C.c_float),
         ("kernel_launches", C.c_int32), ("reserved", C.c_int32),
+        ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
     ]
 
     def as_dict(self):

@@ -25,7 +25,7 @@ using namespace nsp;
 struct nosplan {
     int device = -1;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {};
+    cudaEvent_t ev[8] = {};
     // device arena + pinned staging (grown on demand, reused across calls)
     unsigned char* d_arena = nullptr; size_t d_cap = 0;
     unsigned char* h_stage = nullptr; size_t h_cap = 0;
@@ -37,6 +37,7 @@ struct nosplan {
     unsigned char* d_work = nullptr; size_t work_bytes = 0;
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
+    size_t h2d_bytes = 0;
     std::string err;
 };
 
@@ -206,7 +207,6 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
                 if (m < 0 || m >= n_models) return fail(h, NOSPLAN_E_INVALID, "node %d gpu %d: model id out of range", i, j);
             }
     }
-    if ((long long)N * std::max(P, 1) > (1ll << 62)) return fail(h, NOSPLAN_E_LIMIT, "problem too large");
 
     // ---- per-pod sort keys and validation
     const int nnz = P > 0 ? pods->scalar_ptr[P] : 0;
@@ -372,6 +372,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     h->d_cand_idx = (int32_t*)(A + L.cand_idx);
     h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot;
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
+    h->h2d_bytes = L.upload_end;
     h->uploaded = true;
     return NOSPLAN_OK;
 }
@@ -383,7 +384,9 @@ int nosplan_run(nosplan_t* h) {
     CU(h, cudaEventRecord(h->ev[2], h->stream));
     CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
     launch_prepass(h->pb, h->stream);
+    CU(h, cudaEventRecord(h->ev[6], h->stream));
     launch_tracker_init(h->pb, h->stream);
+    CU(h, cudaEventRecord(h->ev[7], h->stream));
     CU(h, cudaGetLastError());
     CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
@@ -420,7 +423,12 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         cudaEventElapsedTime(&stats->ms_h2d, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
         cudaEventElapsedTime(&stats->ms_d2h, h->ev[4], h->ev[5]);
+        cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
+        cudaEventElapsedTime(&stats->ms_tracker, h->ev[6], h->ev[7]);
+        cudaEventElapsedTime(&stats->ms_sweep, h->ev[7], h->ev[3]);
         stats->kernel_launches = h->launches;
+        stats->h2d_bytes = (int64_t)h->h2d_bytes;
+        stats->d2h_bytes = (int64_t)(h->out_count_bytes + h->out_mask_bytes + sizeof(DevStats));
     }
     return NOSPLAN_OK;
 }
