@@ -3,6 +3,7 @@
 // There is no CPU planning path in this file: everything the reference's Plan() computes per node and per
 // pod happens in the kernels of prepass.cu / sweep.cu.
 #include <algorithm>
+#include <climits>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -16,6 +17,7 @@ namespace nsp {
 void launch_prepass(const DevProblem& pb, cudaStream_t st);
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
+cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st);
 cudaError_t sweep_prepare_device();
 int sweep_max_keys();
 }  // namespace nsp
@@ -25,7 +27,7 @@ using namespace nsp;
 struct nosplan {
     int device = -1;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[8] = {};
+    cudaEvent_t ev[9] = {};
     // device arena + pinned staging (grown on demand, reused across calls)
     unsigned char* d_arena = nullptr; size_t d_cap = 0;
     unsigned char* h_stage = nullptr; size_t h_cap = 0;
@@ -109,8 +111,9 @@ struct GoStable {
 struct Layout {            // byte offsets into the arena / staging buffer
     size_t model_off, geom, node_gpu_count, gpu_model, gpu_mem, gpu_used, gpu_free, gpu_umask, gpu_fmask,
         node_alloc, node_req, node_allowed, node_npods,
-        pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, upload_end,
-        tot, lack, stats, entry_lack, work_end, cand_flag, cand_idx, out_count, out_mask, total;
+        pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
+        cmin_cpu, cmin_mem, cmin_eph, upload_end,
+        tot, lack, stats, maxfree, gflags, acc, placed, entry_lack, work_end, cand_flag, cand_idx, out_count, out_mask, total;
 };
 
 int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes) {
@@ -279,6 +282,27 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     }
     const int n_runs = (int)runs.size();
 
+    // ---- per-chunk (32 pods, run-relative) minima of the requests of the PreFilter-ok pods: lets the kernels skip
+    //      chunks in which no pod can pass NodeResourcesFit.  An all-zero request passes regardless (fit.go short-circuit).
+    std::vector<int32_t> run_chunk_off(n_runs + 1, 0);
+    for (int r = 0; r < n_runs; ++r) run_chunk_off[r + 1] = run_chunk_off[r] + (runs[r].len + 31) / 32;
+    const int n_chunks = run_chunk_off[n_runs];
+    std::vector<long long> cmin(3 * (size_t)n_chunks, LLONG_MAX);
+    bool single_profile_classes = true;
+    for (int r = 0; r < n_runs; ++r) {
+        if (runs[r].n_ent > 1) single_profile_classes = false;
+        for (int l = 0; l < runs[r].len; ++l) {
+            const int oi = order[runs[r].start + l];
+            if (!(flags[oi] & PF_PRE_OK)) continue;
+            const size_t c = (size_t)run_chunk_off[r] + l / 32;
+            const bool z = (flags[oi] & PF_ZERO_REQ) != 0;
+            for (int k = 0; k < 3; ++k) {
+                const long long v = z ? LLONG_MIN : pods->base[3 * (size_t)oi + k];
+                cmin[k * (size_t)n_chunks + c] = std::min(cmin[k * (size_t)n_chunks + c], v);
+            }
+        }
+    }
+
     // ---- layout
     Layout L; size_t o = 0;
     auto put = [&](size_t& field, size_t bytes) { field = o; o = al(o + bytes); };
@@ -295,8 +319,12 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     put(L.pod_key, 4 * (size_t)P); put(L.pod_flags, 4 * (size_t)P);
     put(L.pod_sptr, 4 * ((size_t)P + 1)); put(L.pod_scol, 4 * (size_t)nnz); put(L.pod_sqty, 8 * (size_t)nnz);
     put(L.runs, sizeof(RunRec) * (size_t)n_runs);
+    put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
+    put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
     L.upload_end = o;
-    put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats)); put(L.entry_lack, 4 * (size_t)n_keys * KP);
+    put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats));
+    put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.placed, 4 * (((size_t)n_keys + 31) / 32));
+    put(L.entry_lack, 4 * (size_t)n_keys * KP);
     L.work_end = o;
     put(L.cand_flag, (size_t)N); put(L.cand_idx, 4 * (size_t)N);
     put(L.out_count, 16 * NG); put(L.out_mask, 2 * NG);
@@ -339,6 +367,12 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         }
         sptr[P] = w;
         if (n_runs) std::memcpy(S + L.runs, runs.data(), sizeof(RunRec) * (size_t)n_runs);
+        std::memcpy(S + L.run_chunk_off, run_chunk_off.data(), 4 * ((size_t)n_runs + 1));
+        if (n_chunks) {
+            std::memcpy(S + L.cmin_cpu, cmin.data(), 8 * (size_t)n_chunks);
+            std::memcpy(S + L.cmin_mem, cmin.data() + n_chunks, 8 * (size_t)n_chunks);
+            std::memcpy(S + L.cmin_eph, cmin.data() + 2 * (size_t)n_chunks, 8 * (size_t)n_chunks);
+        }
     }
 
     CU(h, cudaEventRecord(h->ev[0], h->stream));
@@ -365,6 +399,24 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     pb.pod_key = (const int32_t*)(A + L.pod_key); pb.pod_flags = (const uint32_t*)(A + L.pod_flags);
     pb.pod_sptr = (const int32_t*)(A + L.pod_sptr); pb.pod_scol = (const int32_t*)(A + L.pod_scol); pb.pod_sqty = (const long long*)(A + L.pod_sqty);
     pb.runs = (const RunRec*)(A + L.runs);
+    pb.run_chunk_off = (const int32_t*)(A + L.run_chunk_off);
+    pb.cmin_cpu = (const long long*)(A + L.cmin_cpu); pb.cmin_mem = (const long long*)(A + L.cmin_mem); pb.cmin_eph = (const long long*)(A + L.cmin_eph);
+    pb.n_chunks = n_chunks;
+    pb.fast_eligible = single_profile_classes ? 1 : 0;
+    {   // M_p: most devices of profile p one GPU can hold
+        int mem_max = 0;
+        if (!mig) for (size_t x = 0; x < NG; ++x) mem_max = std::max(mem_max, s->gpu_memory_gb[x]);
+        for (int p = 0; p < KP; ++p) {
+            int m = 0;
+            if (p < K) {
+                if (mig) for (int r = 0; r < n_rows; ++r) m = std::max(m, (int)s->geom_counts[16 * (size_t)r + p]);
+                else m = s->profile_mem_gb[p] > 0 ? mem_max / s->profile_mem_gb[p] : -1;
+            }
+            pb.sat_m[p] = m;
+        }
+    }
+    pb.maxfree = (int32_t*)(A + L.maxfree); pb.gflags = (int32_t*)(A + L.gflags);
+    pb.acc = (unsigned long long*)(A + L.acc); pb.placed = (unsigned*)(A + L.placed);
     pb.tot = (long long*)(A + L.tot); pb.lack = (int32_t*)(A + L.lack); pb.stats = (DevStats*)(A + L.stats);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
     pb.cand_flag = (uint8_t*)(A + L.cand_flag);
@@ -388,9 +440,11 @@ int nosplan_run(nosplan_t* h) {
     launch_tracker_init(h->pb, h->stream);
     CU(h, cudaEventRecord(h->ev[7], h->stream));
     CU(h, cudaGetLastError());
+    CU(h, launch_parallel(h->pb, h->stream));
+    CU(h, cudaEventRecord(h->ev[8], h->stream));
     CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
-    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1;
+    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     h->ran = true;
     return NOSPLAN_OK;
 }
@@ -425,7 +479,9 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         cudaEventElapsedTime(&stats->ms_d2h, h->ev[4], h->ev[5]);
         cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
         cudaEventElapsedTime(&stats->ms_tracker, h->ev[6], h->ev[7]);
-        cudaEventElapsedTime(&stats->ms_sweep, h->ev[7], h->ev[3]);
+        cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
+        cudaEventElapsedTime(&stats->ms_sweep, h->ev[8], h->ev[3]);
+        stats->path = ds.path;
         stats->kernel_launches = h->launches;
         stats->h2d_bytes = (int64_t)h->h2d_bytes;
         stats->d2h_bytes = (int64_t)(h->out_count_bytes + h->out_mask_bytes + sizeof(DevStats));

@@ -31,6 +31,7 @@ static_assert(sizeof(RunRec) == 48, "RunRec layout");
 struct DevStats {
     long long candidates, visited_nodes, geometry_evals, placements, candidate_nodes;
     int lacking_at_start, lacking_at_end;
+    int path, pad;             // 1: node-parallel pass stood, 0: sequential sweep
 };
 
 struct DevProblem {
@@ -63,11 +64,23 @@ struct DevProblem {
     const int32_t* pod_scol;
     const long long* pod_sqty;
     const RunRec* runs;              // [n_runs]
+    const int32_t* run_chunk_off;    // [n_runs+1] first 32-pod chunk of each run in the chunk-min arrays
+    const long long* cmin_cpu;       // [n_chunks] min request over the PreFilter-ok pods of the chunk (LLONG_MAX: none)
+    const long long* cmin_mem;
+    const long long* cmin_eph;
+    int n_chunks;
+    // node-parallel fast path (see sweep.cu): host-side eligibility and saturation bound per profile
+    int fast_eligible;               // every pod class requests at most one slice profile
+    int32_t sat_m[KP];               // M_p: most devices of profile p one GPU can hold (table rows / memory)
     // work area (zeroed before each run)
     long long* tot;                  // [KP] sum over nodes of (alloc - requested) per slice column
     int32_t* lack;                   // [KP] SliceTracker.lackingSlices
     int32_t* entry_lack;             // [n_keys][KP] lackingSlicesLookup
     uint8_t* cand_flag;              // [N] HasFreeCapacity
+    int32_t* maxfree;                // [KP] max free count of a profile on any GPU at t0 (work area)
+    int32_t* gflags;                 // [4]  [0] some node's Allocatable/Requested disagree with its GPUs' used/free
+    unsigned* placed;                // [(n_keys+31)/32] tracker keys placed by the node-parallel pass
+    unsigned long long* acc;         // [4]  placements, geometry evals, visited, candidate nodes of the node-parallel pass
     // outputs
     uint4* out_count;                // [N*G]
     uint16_t* out_mask;              // [N*G]

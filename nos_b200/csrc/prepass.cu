@@ -7,6 +7,8 @@
 //                              pkg/gpu/slicing/node.go:208-215)
 //                          (c) cluster totals  sum(Allocatable - Requested)  per slice resource
 //                              (core/snapshot.go:132-141) reduced warp -> block -> one int64 atomic per column
+//                          (d) for the node-parallel fast path: the largest free count of each profile on any GPU
+//                              and whether every node's Allocatable/Requested agree with its GPUs' used/free maps
 //   k_tracker_init  one thread per pod: lacking slices against the t0 totals, NewSliceTracker (core/tracker.go:34-57)
 #include "nosplan_dev.cuh"
 
@@ -17,6 +19,7 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
     __shared__ uint16_t s_gmask[MAX_ROWS];
     __shared__ int s_off[MAX_MODELS + 1];
     __shared__ long long s_acc[8][KP];
+    __shared__ int s_maxfree[8][KP];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool mig = pb.kind == NOSPLAN_KIND_MIG;
@@ -31,6 +34,8 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
     __syncthreads();
 
     long long acc = 0;
+    int maxfree = 0;
+    bool inconsistent = false;
     const int warps_total = gridDim.x * (blockDim.x >> 5);
     for (int i = blockIdx.x * (blockDim.x >> 5) + warp; i < pb.N; i += warps_total) {
         const int ng = pb.node_gpu_count[i];
@@ -65,15 +70,30 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
         if (lane == 0) pb.cand_flag[i] = any != 0;
         if (lane < pb.K) {
             const size_t o = (size_t)i * pb.R + 3 + lane;
-            acc += pb.node_alloc[o] - pb.node_req[o];
+            const long long a = pb.node_alloc[o], r = pb.node_req[o];
+            acc += a - r;
+            long long sum_free = 0, sum_used = 0;
+            const uint8_t* fb = reinterpret_cast<const uint8_t*>(pb.gpu_free) + (size_t)i * pb.G * 16 + lane;
+            const uint8_t* ub = reinterpret_cast<const uint8_t*>(pb.gpu_used) + (size_t)i * pb.G * 16 + lane;
+            for (int g = 0; g < ng; ++g) {
+                const int f = fb[16 * g];
+                sum_free += f; sum_used += ub[16 * g];
+                maxfree = max(maxfree, f);
+            }
+            // gate (core/snapshot.go:132-165) can only be implied by GPU.AddPod feasibility if the node accounts agree
+            inconsistent |= (a - r < sum_free) || (r > sum_used);
         }
     }
-    if (lane < KP) s_acc[warp][lane] = acc;
+    if (__any_sync(0xffffffffu, inconsistent) && lane == 0) atomicOr(&pb.gflags[0], 1);
+    if (lane < KP) { s_acc[warp][lane] = acc; s_maxfree[warp][lane] = maxfree; }
     __syncthreads();
     if (warp == 0 && lane < pb.K) {
         long long t = 0;
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_acc[w][lane];
         if (t != 0) atomicAdd((unsigned long long*)&pb.tot[lane], (unsigned long long)t);
+        int mf = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) mf = max(mf, s_maxfree[w][lane]);
+        if (mf > 0) atomicMax(&pb.maxfree[lane], mf);
     }
 }
 

@@ -1,8 +1,6 @@
-// k_plan_sweep -- the sequential node sweep of planner.Plan (internal/partitioning/core/planner.go:92-150)
-// as ONE persistent kernel: the loop-carried state (lacking-slices vector, cluster-wide free totals,
-// tracker entries already removed, "a Commit happened") never leaves the SM.
+// The node sweep of planner.Plan (internal/partitioning/core/planner.go:92-150) on sm_100a.
 //
-// One warp walks the candidate nodes in name order.  Per node:
+// process_node<>  everything the reference does for ONE candidate node, executed by one warp:
 //   1. Node.UpdateGeometryFor (pkg/gpu/mig/node.go:145-177 / pkg/gpu/slicing/node.go:120-152): GPUs in order;
 //      MIG: lanes = allowed geometries of the GPU model (table staged in shared memory), each lane scores its
 //      geometry (pkg/gpu/mig/gpu.go:164-191), warp arg-max with the canonical tie-break (lowest table index),
@@ -11,12 +9,28 @@
 //   2. the pod loop (planner.go:116-141 tryAddPod) over RUNS of identical slice requests instead of single pods.
 //      Gate (core/snapshot.go:132-165), NodeResourcesFit on the slice columns and GPU.AddPod feasibility are
 //      class-level and only ever get tighter while one node is processed, so a run whose class fails is skipped
-//      whole, and inside a feasible run 32 pods are tested per step: warp prefix sums of cpu/memory/ephemeral
-//      requests give every lane the node state it would see if all earlier lanes were placed; the first lane that
-//      fails under that hypothesis splits the step, so the result is exactly the sequential first-fit.
-//   3. Commit / Revert bookkeeping including the aliasing rules of the reference's object graph (see the state
-//      rules in oracle/nos_oracle.cpp plan_incremental and DESIGN.md).
-// The next candidate node is prefetched into registers while the current one is processed.
+//      whole; inside a feasible run, per-chunk minima of the pods' cpu/memory/ephemeral requests skip 32-pod
+//      chunks that cannot hold a fitting pod, and a loaded chunk is resolved with warp prefix sums: every lane
+//      tests its pod against the node state it would see if all earlier lanes were placed, the first lane that
+//      fails under that hypothesis splits the step -- exactly the sequential first-fit.
+//   3. Commit / Revert bookkeeping including the aliasing rules of the reference's object graph (state rules
+//      written out in oracle/nos_oracle.cpp plan_incremental and DESIGN.md).
+//
+// Two drivers share it:
+//   k_plan_parallel  node-parallel pass, one warp per candidate node over the whole GPU.  Exact only under three
+//                    conditions it checks itself: every pod class requests at most one profile; every node's
+//                    Allocatable/Requested agree with its GPUs (then the cluster-wide gate is implied by AddPod
+//                    feasibility and the running totals drop out); and the lacking-slices vector is SATURATED,
+//                    lack[p] > (G+2)*M_p, so that min(cand-used, lack) and the lack>free tests cannot see its exact
+//                    value.  Then no state is carried from node to node except the set of tracker keys already
+//                    removed, which is collected in a bitmap and turned into the final lacking vector afterwards.
+//   k_plan_sweep     verifies the saturation hypothesis a posteriori (lack only decreases, so checking its final value
+//                    is enough); if it held, the parallel result stands.  Otherwise -- and whenever the fast path is
+//                    not applicable -- it discards it and walks the candidate nodes sequentially with one warp and the
+//                    full loop-carried state (lacking vector, cluster totals, removed entries, "a Commit happened")
+//                    in registers / shared memory, prefetching the next node while the current one is processed.
+#include <climits>
+
 #include "nosplan_dev.cuh"
 
 namespace nsp {
@@ -25,6 +39,7 @@ namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
 constexpr long long CAP_INF = (1ll << 40);
+constexpr int SATURATED = INT_MAX / 2;
 
 struct SNode {
     uint4 used[NOSPLAN_MAX_GPUS];
@@ -35,7 +50,29 @@ struct SNode {
     int ng, allowed, npods, idx;
 };
 
-struct NodeRegs {          // one node spread over the lanes of a warp (prefetch registers)
+struct WarpScratch {       // per-warp shared memory
+    SNode nd;
+    int req[KP];
+    long long Dg[KP], allocF[KP], reqF[KP];
+};
+
+struct Tables {            // CTA-wide shared memory, read-only after the prologue
+    uint4 geom[MAX_ROWS];
+    uint16_t gmask[MAX_ROWS];
+    int off[MAX_MODELS + 1];
+};
+
+struct PodCache {          // first 32 pods of the first RUN_CACHE runs (sequential driver only)
+    long long (*cpu)[32];
+    long long (*mem)[32];
+    long long (*eph)[32];
+    int (*key)[32];
+    unsigned (*flag)[32];
+    const RunRec* runs;    // shared-memory copy of the first n_cached run records
+    int n_cached;
+};
+
+struct NodeRegs {          // one node spread over the lanes of a warp
     uint4 used, fre;
     int um, fm, model, mem;
     long long alloc, req;
@@ -66,7 +103,7 @@ __device__ __forceinline__ void store_node(SNode& nd, const NodeRegs& r, int i, 
         nd.umask[lane] = (uint16_t)r.um; nd.fmask[lane] = (uint16_t)r.fm;
         nd.model[lane] = r.model; nd.mem[lane] = r.mem;
     }
-    nd.alloc[lane] = r.alloc; nd.req[lane] = r.req;     // lane < 32 <= RMAX+1
+    nd.alloc[lane] = r.alloc; nd.req[lane] = r.req;     // lane < 32 == RMAX+1
     if (lane == 0) { nd.ng = r.ng; nd.allowed = r.allowed; nd.npods = r.npods; nd.idx = i; }
 }
 
@@ -79,7 +116,6 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
 }
 __device__ __forceinline__ int warp_sum_int(int v) { return __reduce_add_sync(FULL, v); }
 
-// exclusive prefix sum over the lanes of a warp
 __device__ __forceinline__ long long warp_excl_ll(long long v, int lane) {
     long long s = v;
 #pragma unroll
@@ -101,18 +137,17 @@ __device__ __forceinline__ int warp_excl_int(int v, int lane) {
 
 // ---------------------------------------------------------------- MIG GPU.UpdateGeometryFor (mig/gpu.go:158-212)
 // lanes = geometries of the GPU's model.  `required` lives in lane p (p < 16).  Returns updated (warp-uniform).
-__device__ __forceinline__ bool mig_gpu_update(SNode& nd, int g, int required, int lane, int K,
-                                               const uint4* s_geom, const uint16_t* s_gmask, const int* s_off,
+__device__ __forceinline__ bool mig_gpu_update(SNode& nd, int g, int required, int lane, int K, const Tables& tb,
                                                int* s_req, long long& evals) {
     if (lane < KP) s_req[lane] = required;
     __syncwarp();
     const int m = nd.model[g];
-    const int r0 = s_off[m], nrows = s_off[m + 1] - r0;
+    const int r0 = tb.off[m], nrows = tb.off[m + 1] - r0;
     const int n_req = __popc(__ballot_sync(FULL, required > 0));
     evals += (long long)nrows * n_req;
     unsigned key = 0;
     if (lane < nrows) {
-        const uint4 row = s_geom[r0 + lane];
+        const uint4 row = tb.geom[r0 + lane];
         const uint4 used = nd.used[g], fre = nd.free_[g];
         const unsigned um = nd.umask[g];
         bool can = true;                                   // CanApplyGeometry (:97-110) for an allowed row
@@ -139,10 +174,10 @@ __device__ __forceinline__ bool mig_gpu_update(SNode& nd, int g, int required, i
     if (best == 0) return false;
     const int br = r0 + 31 - (int)(best & 31u);            // strict > in table order == lowest index among max
     if (lane < KP) {                                        // ApplyGeometry (:132-152): lanes = profiles
-        const unsigned rw = byte_of(s_geom[br], lane), us = byte_of(nd.used[g], lane);
+        const unsigned rw = byte_of(tb.geom[br], lane), us = byte_of(nd.used[g], lane);
         bytes(nd.free_[g])[lane] = (uint8_t)(rw ? rw - us : 0);
     }
-    if (lane == 0) nd.fmask[g] = s_gmask[br];
+    if (lane == 0) nd.fmask[g] = tb.gmask[br];
     __syncwarp();
     return true;
 }
@@ -151,7 +186,7 @@ __device__ __forceinline__ bool mig_gpu_update(SNode& nd, int g, int required, i
 // lanes = profiles (ids ascend by (size, name)).  Returns updated (warp-uniform).
 __device__ __forceinline__ bool mps_gpu_update(SNode& nd, int g, int required, int lane, const DevProblem& pb) {
     const int size = lane < pb.K ? pb.pmem[lane] : 0;
-    int used = lane < KP ? (int)bytes(nd.used[g])[lane] : 0;
+    const int used = lane < KP ? (int)bytes(nd.used[g])[lane] : 0;
     int fre = lane < KP ? (int)bytes(nd.free_[g])[lane] : 0;
     unsigned fmask = nd.fmask[g];
     const int mem = nd.mem[g];
@@ -194,12 +229,22 @@ __device__ __forceinline__ bool mps_gpu_update(SNode& nd, int g, int required, i
     return updated;
 }
 
-// SliceTracker.Remove (core/tracker.go:67-88): lanes = profiles.  s_removed caches "entry already emptied".
-__device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, unsigned* s_removed, int& lack, int lane) {
-    const unsigned w = s_removed[key >> 5];
+// SliceTracker.Remove (core/tracker.go:67-88).
+//   sequential driver: `removed` is a shared-memory bitmap of emptied entries; lanes = profiles subtract the entry.
+//   parallel driver:   only the global "placed" bitmap is set; the lacking vector is rebuilt from it afterwards.
+template <bool PAR>
+__device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, unsigned* removed, int& lack, int lane) {
+    if (PAR) {
+        if (lane == 0) {
+            const unsigned bit = 1u << (key & 31);
+            if (!(removed[key >> 5] & bit)) atomicOr(&removed[key >> 5], bit);
+        }
+        return;
+    }
+    const unsigned w = removed[key >> 5];
     if (w >> (key & 31) & 1) return;
     __syncwarp();
-    if (lane == 0) s_removed[key >> 5] = w | (1u << (key & 31));
+    if (lane == 0) removed[key >> 5] = w | (1u << (key & 31));
     if (lane < KP) {
         const int e = pb.entry_lack[(size_t)key * KP + lane];
         if (e > 0) lack -= e;
@@ -207,186 +252,118 @@ __device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, un
     __syncwarp();
 }
 
-}  // namespace
-
-// ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* cand_idx) {
-    extern __shared__ __align__(16) unsigned char s_dyn[];
-    __shared__ uint4 s_geom[MAX_ROWS];
-    __shared__ uint16_t s_gmask[MAX_ROWS];
-    __shared__ int s_off[MAX_MODELS + 1];
-    __shared__ SNode s_node[2];
-    __shared__ RunRec s_runs[RUN_CACHE];
-    __shared__ int s_req[KP];
-    __shared__ long long s_Dg[KP], s_allocF[KP], s_reqF[KP];
-    __shared__ int s_scan[256];
-    __shared__ int s_ncand;
-
-    // dynamic shared memory: first chunk (32 pods) of every cached run, then the tracker "entry removed" bitmap
-    typedef long long (*chunk_ll)[32];
-    typedef int (*chunk_i)[32];
-    typedef unsigned (*chunk_u)[32];
-    chunk_ll s_ccpu = reinterpret_cast<chunk_ll>(s_dyn);
-    chunk_ll s_cmem = s_ccpu + RUN_CACHE;
-    chunk_ll s_ceph = s_cmem + RUN_CACHE;
-    chunk_i s_ckey = reinterpret_cast<chunk_i>(s_ceph + RUN_CACHE);
-    chunk_u s_cflag = reinterpret_cast<chunk_u>(s_ckey + RUN_CACHE);
-    unsigned* s_removed = reinterpret_cast<unsigned*>(s_cflag + RUN_CACHE);      // [(n_keys+31)/32]
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// One candidate node, start to finish.  `ws.nd` holds the node.  Returns the number of pods added.
+//   lack      lane p: SliceTracker.lackingSlices[p] (PAR: SATURATED on the lacking profiles, never modified)
+//   D         lane p: cluster-wide sum(Allocatable - Requested) of slice column p (unused when PAR)
+template <bool PAR>
+__device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& ws, const Tables& tb, const PodCache* pc,
+                                            unsigned* removed, int& lack, long long& D, bool& committed,
+                                            long long& st_evals, long long& st_place, int lane) {
+    SNode& nd = ws.nd;
     const bool mig = pb.kind == NOSPLAN_KIND_MIG;
-    const int K = pb.K;
+    const int K = pb.K, fm = pb.filter_mode;
+    const int ng = nd.ng, node_i = nd.idx;
+    const long long oldA = (lane < K) ? nd.alloc[3 + lane] : 0;
+    const long long oldR = (lane < K) ? nd.req[3 + lane] : 0;
 
-    // ---------------- prologue (whole CTA): tables, run cache, candidate compaction in name order
-    if (mig) {
-        for (int r = tid; r < pb.n_rows; r += blockDim.x) { uint4 row = pb.geom[r]; s_geom[r] = row; s_gmask[r] = nz_mask(row); }
-        for (int m = tid; m <= pb.n_models; m += blockDim.x) s_off[m] = pb.model_off[m];
-    }
-    for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x) s_removed[w] = 0;
-    const int n_cached = min(pb.n_runs, RUN_CACHE);
-    for (int r = tid; r < n_cached; r += blockDim.x) s_runs[r] = pb.runs[r];
-    __syncthreads();
-    for (int t = tid; t < n_cached * 32; t += blockDim.x) {
-        const int r = t >> 5, l = t & 31;
-        if (l < s_runs[r].len) {
-            const int s = s_runs[r].start + l;
-            s_ccpu[r][l] = pb.pod_cpu[s]; s_cmem[r][l] = pb.pod_mem[s]; s_ceph[r][l] = pb.pod_eph[s];
-            s_ckey[r][l] = pb.pod_key[s]; s_cflag[r][l] = pb.pod_flags[s];
+    // ---- 1. Node.UpdateGeometryFor
+    int required = lack;
+    bool upd = false;
+    for (int g = 0; g < ng; ++g) {
+        bool u;
+        if (mig) u = mig_gpu_update(nd, g, required, lane, K, tb, ws.req, st_evals);
+        else {
+            st_evals += __popc(__ballot_sync(FULL, required > 0));
+            u = mps_gpu_update(nd, g, required, lane, pb);
+        }
+        upd |= u;
+        if (!PAR && lane < KP) {
+            const int f = (int)bytes(nd.free_[g])[lane];
+            if ((nd.fmask[g] >> lane & 1) && required > 0) required = max(0, required - f);
         }
     }
-    {   // ordered compaction of candidate flags -> cand_idx (GetCandidateNodes, core/snapshot.go:119-130)
-        int base = 0;
-        for (int c0 = 0; c0 < pb.N; c0 += blockDim.x) {
-            const int i = c0 + tid;
-            const int f = (i < pb.N) ? pb.cand_flag[i] : 0;
-            s_scan[tid] = f;
-            __syncthreads();
-            for (int o = 1; o < (int)blockDim.x; o <<= 1) {
-                int v = (tid >= o) ? s_scan[tid - o] : 0;
-                __syncthreads();
-                s_scan[tid] += v;
-                __syncthreads();
-            }
-            if (f) cand_idx[base + s_scan[tid] - 1] = i;
-            base += s_scan[blockDim.x - 1];
-            __syncthreads();
-        }
-        if (tid == 0) s_ncand = base;
-    }
-    __threadfence_block();
-    __syncthreads();
-    if (warp != 0) return;
-
-    // ---------------- the chain (warp 0)
-    const int n_cand = s_ncand;
-    int lack = (lane < KP) ? pb.lack[lane] : 0;                    // lane p: lackingSlices[p]
-    long long D = (lane < KP) ? pb.tot[lane] : 0;                  // lane p: sum(alloc - requested) of slice column p
-    bool committed = false;
-    long long st_visited = 0, st_evals = 0, st_place = 0;
-    const int lack_start = __popc(__ballot_sync(FULL, lack > 0));
-    const int fm = pb.filter_mode;
-
-    NodeRegs nr;
-    if (n_cand > 0 && lack_start > 0) {
-        load_node(pb, cand_idx[0], lane, nr);
-        store_node(s_node[0], nr, cand_idx[0], lane);
-    }
+    long long newA = 0;                                        // computeScalarResources (mig/node.go:179-195)
+    if (lane < K)
+        for (int g = 0; g < ng; ++g) newA += (long long)bytes(nd.used[g])[lane] + bytes(nd.free_[g])[lane];
+    const long long allocF = upd ? newA : oldA;                // Allocatable of the forked entry the pods are added to
+    if (lane < KP) { ws.allocF[lane] = allocF; ws.reqF[lane] = oldR; ws.Dg[lane] = PAR ? 0 : D - oldA + allocF; }
+    long long remc = nd.alloc[0] - nd.req[0], remm = nd.alloc[1] - nd.req[1], reme = nd.alloc[2] - nd.req[2];
+    const bool podcount_ok = nd.npods + 1 <= nd.allowed;
+    const bool fit = fm == NOSPLAN_FILTER_RESOURCES_FIT;
     __syncwarp();
 
-    for (int c = 0; c < n_cand && lack_start > 0; ++c) {
-        if (__ballot_sync(FULL, lack > 0) == 0) break;             // planner.go:94-97
-        SNode& nd = s_node[c & 1];
-        const bool have_next = c + 1 < n_cand;
-        int next_i = 0;
-        if (have_next) { next_i = cand_idx[c + 1]; load_node(pb, next_i, lane, nr); }   // prefetch (consumed at loop end)
-
-        ++st_visited;
-        const int ng = nd.ng, node_i = nd.idx;
-        const long long oldA = (lane < K) ? nd.alloc[3 + lane] : 0;
-        const long long oldR = (lane < K) ? nd.req[3 + lane] : 0;
-
-        // ---- 1. Node.UpdateGeometryFor
-        int required = lack;
-        bool upd = false;
-        for (int g = 0; g < ng; ++g) {
-            bool u;
-            if (mig) u = mig_gpu_update(nd, g, required, lane, K, s_geom, s_gmask, s_off, s_req, st_evals);
-            else {
-                st_evals += __popc(__ballot_sync(FULL, required > 0));
-                u = mps_gpu_update(nd, g, required, lane, pb);
-            }
-            upd |= u;
-            if (lane < KP) {
-                const int f = (int)bytes(nd.free_[g])[lane];
-                if ((nd.fmask[g] >> lane & 1) && required > 0) required = max(0, required - f);
-            }
+    // ---- 2. the pod loop, run by run
+    int added = 0;
+    const bool all_fail = (fm == NOSPLAN_FILTER_REJECT_ALL) || (fit && !podcount_ok);
+    for (int ri = 0; ri < pb.n_runs && !all_fail; ++ri) {
+        const bool cached = pc && ri < pc->n_cached;
+        const RunRec* rr = cached ? &pc->runs[ri] : &pb.runs[ri];
+        const int rstart = rr->start, rend = rr->start + rr->len, n_ent = rr->n_ent;
+        const int q_l = (lane < KP) ? (int)rr->q[lane] : 0;
+        // class-level tests; all of them only get tighter while this node is processed
+        bool ok_l = true;
+        if (q_l > 0) {
+            if (!PAR) ok_l = ws.Dg[lane] >= q_l;                                            // gate, snapshot.go:132-165
+            if (fit) ok_l = ok_l && (q_l <= ws.allocF[lane] - ws.reqF[lane]);
         }
-        long long newA = 0;                                        // computeScalarResources (mig/node.go:179-195)
-        if (lane < K)
-            for (int g = 0; g < ng; ++g) newA += (long long)bytes(nd.used[g])[lane] + bytes(nd.free_[g])[lane];
-        const long long allocF = upd ? newA : oldA;                // the forked entry the pods are added to
-        if (lane < KP) { s_allocF[lane] = allocF; s_reqF[lane] = oldR; s_Dg[lane] = D - oldA + allocF; }
-        long long remc = nd.alloc[0] - nd.req[0], remm = nd.alloc[1] - nd.req[1], reme = nd.alloc[2] - nd.req[2];
-        const bool podcount_ok = nd.npods + 1 <= nd.allowed;
-        __syncwarp();
+        if (!__all_sync(FULL, ok_l)) continue;
 
-        // ---- 2. the pod loop, run by run
-        int added = 0;
-        const bool all_fail = (fm == NOSPLAN_FILTER_REJECT_ALL) || (fm == NOSPLAN_FILTER_RESOURCES_FIT && !podcount_ok);
-        for (int ri = 0; ri < pb.n_runs && !all_fail; ++ri) {
-            const RunRec* rr = (ri < RUN_CACHE) ? &s_runs[ri] : &pb.runs[ri];
-            const int rstart = rr->start, rend = rr->start + rr->len, n_ent = rr->n_ent;
-            const int q_l = (lane < KP) ? (int)rr->q[lane] : 0;
-            // class-level tests; all of them only get tighter while this node is processed
-            bool ok_l = true;
-            if (q_l > 0) {
-                ok_l = s_Dg[lane] >= q_l;                                                       // gate, snapshot.go:132-165
-                if (fm == NOSPLAN_FILTER_RESOURCES_FIT) ok_l = ok_l && (q_l <= s_allocF[lane] - s_reqF[lane]);
+        if (n_ent <= 1) {
+            // ---------- single-profile (or slice-less) class: bulk first-fit
+            const unsigned emask = __ballot_sync(FULL, q_l > 0);
+            const int p = n_ent ? __ffs(emask) - 1 : 0;
+            const int q = n_ent ? __shfl_sync(FULL, q_l, p) : 0;
+            long long cap = CAP_INF;
+            if (n_ent) {
+                const int cg = (lane < ng) ? (int)bytes(nd.free_[lane])[p] / q : 0;           // GPU.AddPod feasibility
+                cap = warp_sum_int(cg);
+                if (!PAR) cap = min(cap, ws.Dg[p] / q);
+                if (fit) cap = min(cap, (ws.allocF[p] - ws.reqF[p]) / q);
             }
-            if (!__all_sync(FULL, ok_l)) continue;
-
-            if (n_ent <= 1) {
-                // ---------- single-profile (or slice-less) class: bulk first-fit
-                const unsigned emask = __ballot_sync(FULL, q_l > 0);
-                const int p = n_ent ? __ffs(emask) - 1 : 0;
-                const int q = n_ent ? __shfl_sync(FULL, q_l, p) : 0;
-                long long cap = CAP_INF;
-                if (n_ent) {
-                    const int cg = (lane < ng) ? (int)bytes(nd.free_[lane])[p] / q : 0;       // GPU.AddPod feasibility
-                    cap = warp_sum_int(cg);
-                    cap = min(cap, s_Dg[p] / q);
-                    if (fm == NOSPLAN_FILTER_RESOURCES_FIT) cap = min(cap, (s_allocF[p] - s_reqF[p]) / q);
-                }
-                for (int cursor = rstart; cursor < rend && cap > 0; cursor += 32) {
+            if (cap <= 0) continue;
+            const int c0 = pb.run_chunk_off[ri], nch = pb.run_chunk_off[ri + 1] - c0;
+            for (int cb = 0; cb < nch && cap > 0; cb += 32) {
+                // chunk minima of 32 chunks at a time: a chunk whose cheapest eligible pod does not fit is skipped
+                long long mc = LLONG_MAX, mm = LLONG_MAX, me = LLONG_MAX;
+                if (cb + lane < nch) { mc = pb.cmin_cpu[c0 + cb + lane]; mm = pb.cmin_mem[c0 + cb + lane]; me = pb.cmin_eph[c0 + cb + lane]; }
+                int cdone = 0;
+                while (cap > 0) {
+                    bool pass = mc != LLONG_MAX && lane >= cdone;
+                    if (fit) pass = pass && mc <= remc && mm <= remm && me <= reme;
+                    const unsigned pm = __ballot_sync(FULL, pass);
+                    if (pm == 0) break;
+                    const int cl = __ffs(pm) - 1;
+                    cdone = cl + 1;
+                    const int cursor = rstart + (cb + cl) * 32;
                     const int s = cursor + lane;
                     const bool in = s < rend;
                     long long cpu = 0, mem = 0, eph = 0; int key = 0; unsigned fl = 0;
                     if (in) {
-                        if (ri < RUN_CACHE && cursor == rstart) {
-                            cpu = s_ccpu[ri][lane]; mem = s_cmem[ri][lane]; eph = s_ceph[ri][lane];
-                            key = s_ckey[ri][lane]; fl = s_cflag[ri][lane];
+                        if (cached && cursor == rstart) {
+                            cpu = pc->cpu[ri][lane]; mem = pc->mem[ri][lane]; eph = pc->eph[ri][lane];
+                            key = pc->key[ri][lane]; fl = pc->flag[ri][lane];
                         } else {
                             cpu = pb.pod_cpu[s]; mem = pb.pod_mem[s]; eph = pb.pod_eph[s];
                             key = pb.pod_key[s]; fl = pb.pod_flags[s];
                         }
                     }
-                    const bool fit = fm == NOSPLAN_FILTER_RESOURCES_FIT;
                     const bool slow = in && fit && (fl & PF_HAS_OTHER);
+                    const bool zero = (fl & PF_ZERO_REQ) != 0;
                     int from = 0;
                     while (from < 32 && cap > 0) {
                         // pods with other scalar resources take the exact per-pod path; they split the step
                         const unsigned slow_m = __ballot_sync(FULL, slow && lane >= from);
                         const int stop = slow_m ? __ffs(slow_m) - 1 : 32;
-                        const bool zero = (fl & PF_ZERO_REQ) != 0;
                         bool valid = in && lane >= from && lane < stop && (fl & PF_PRE_OK);
-                        if (fit) valid = valid && (zero || (cpu <= remc && mem <= remm && eph <= reme));  // can never pass later
+                        if (fit) valid = valid && (zero || (cpu <= remc && mem <= remm && eph <= reme));   // can never pass later
                         const unsigned vm = __ballot_sync(FULL, valid);
                         if (vm == 0 && stop == 32) break;
                         const int rank = __popc(vm & ((1u << lane) - 1));
                         const bool cand = valid && rank < cap;
                         bool test = cand;
-                        const long long ccpu = cand ? cpu : 0, cmem = cand ? mem : 0, ceph = cand ? eph : 0;
                         if (fit) {
-                            const long long ec = warp_excl_ll(ccpu, lane), em = warp_excl_ll(cmem, lane), ee = warp_excl_ll(ceph, lane);
+                            const long long ec = warp_excl_ll(cand ? cpu : 0, lane), em = warp_excl_ll(cand ? mem : 0, lane),
+                                            ee = warp_excl_ll(cand ? eph : 0, lane);
                             test = cand && (zero || (cpu <= remc - ec && mem <= remm - em && eph <= reme - ee));
                         }
                         const unsigned failm = __ballot_sync(FULL, cand && !test);
@@ -406,14 +383,14 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
                                     bytes(nd.used[lane])[p] += (uint8_t)(take * q);
                                     nd.umask[lane] |= (uint16_t)(1u << p);
                                 }
-                                if (lane == 0) { s_reqF[p] += (long long)n * q; s_Dg[p] -= (long long)n * q; }
+                                if (lane == 0) { ws.reqF[p] += (long long)n * q; ws.Dg[p] -= (long long)n * q; }
                                 cap -= n;
                             }
                             unsigned todo = accm;                          // tracker.Remove per placed pod
                             while (todo) {
                                 const int l = __ffs(todo) - 1;
                                 todo &= todo - 1;
-                                tracker_remove(pb, __shfl_sync(FULL, key, l), s_removed, lack, lane);
+                                tracker_remove<PAR>(pb, __shfl_sync(FULL, key, l), removed, lack, lane);
                             }
                             added += n; st_place += n;
                             __syncwarp();
@@ -448,10 +425,10 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
                                         bytes(nd.free_[lane])[p] -= (uint8_t)q; bytes(nd.used[lane])[p] += (uint8_t)q;
                                         nd.umask[lane] |= (uint16_t)(1u << p);
                                     }
-                                    if (lane == 0) { s_reqF[p] += q; s_Dg[p] -= q; }
+                                    if (lane == 0) { ws.reqF[p] += q; ws.Dg[p] -= q; }
                                     cap -= 1;
                                 }
-                                tracker_remove(pb, pkey, s_removed, lack, lane);
+                                tracker_remove<PAR>(pb, pkey, removed, lack, lane);
                                 ++added; ++st_place;
                                 __syncwarp();
                             }
@@ -461,78 +438,259 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
                         break;
                     }
                 }
-            } else {
-                // ---------- multi-profile class: exact per-pod path (GPU.AddPod keeps partial moves, mig/gpu.go:234-245)
-                for (int s = rstart; s < rend; ++s) {
-                    const unsigned fl = pb.pod_flags[s];
-                    const long long cpu = pb.pod_cpu[s], mem = pb.pod_mem[s], eph = pb.pod_eph[s];
-                    // gate + class-level fit again (state may have changed inside this run)
-                    bool okc = true;
-                    if (q_l > 0) {
-                        okc = s_Dg[lane] >= q_l;
-                        if (fm == NOSPLAN_FILTER_RESOURCES_FIT) okc = okc && (q_l <= s_allocF[lane] - s_reqF[lane]);
+            }
+        } else {
+            // ---------- multi-profile class: exact per-pod path (GPU.AddPod keeps partial moves, mig/gpu.go:234-245)
+            for (int s = rstart; s < rend; ++s) {
+                const unsigned fl = pb.pod_flags[s];
+                const long long cpu = pb.pod_cpu[s], mem = pb.pod_mem[s], eph = pb.pod_eph[s];
+                bool okc = true;                                   // gate + class-level fit again (state moves inside the run)
+                if (q_l > 0) {
+                    if (!PAR) okc = ws.Dg[lane] >= q_l;
+                    if (fit) okc = okc && (q_l <= ws.allocF[lane] - ws.reqF[lane]);
+                }
+                if (!__all_sync(FULL, okc)) break;                 // every later pod of the run fails the same way
+                bool ok = (fl & PF_PRE_OK) != 0;
+                if (fit) {
+                    ok = ok && cpu <= remc && mem <= remm && eph <= reme;
+                    if (ok && (fl & PF_HAS_OTHER)) {
+                        if (lane == 0)
+                            for (int e = pb.pod_sptr[s]; e < pb.pod_sptr[s + 1]; ++e) {
+                                const int col = pb.pod_scol[e];
+                                if (col >= 3 + K && pb.pod_sqty[e] > nd.alloc[col] - nd.req[col]) ok = false;
+                            }
+                        ok = __shfl_sync(FULL, (int)ok, 0) != 0;
                     }
-                    if (!__all_sync(FULL, okc)) break;                     // every later pod of the run fails the same way
-                    bool ok = (fl & PF_PRE_OK) != 0;
-                    if (fm == NOSPLAN_FILTER_RESOURCES_FIT) {
-                        ok = ok && cpu <= remc && mem <= remm && eph <= reme;
-                        if (ok && (fl & PF_HAS_OTHER)) {
-                            if (lane == 0)
-                                for (int e = pb.pod_sptr[s]; e < pb.pod_sptr[s + 1]; ++e) {
-                                    const int col = pb.pod_scol[e];
-                                    if (col >= 3 + K && pb.pod_sqty[e] > nd.alloc[col] - nd.req[col]) ok = false;
-                                }
-                            ok = __shfl_sync(FULL, (int)ok, 0) != 0;
-                        }
+                }
+                if (!ok) continue;
+                bool placed = false, dirty = false;                // Node.AddPod: GPUs in order, profiles ascending
+                for (int g = 0; g < ng && !placed; ++g) {
+                    const int fr = (lane < KP) ? (int)bytes(nd.free_[g])[lane] : 0;
+                    const unsigned bad = __ballot_sync(FULL, q_l > 0 && fr < q_l);
+                    const unsigned want = __ballot_sync(FULL, q_l > 0);
+                    const unsigned mv = bad ? (want & ((1u << (__ffs(bad) - 1)) - 1)) : want;   // moved before the first failure
+                    if (mv >> lane & 1) {
+                        bytes(nd.free_[g])[lane] -= (uint8_t)q_l; bytes(nd.used[g])[lane] += (uint8_t)q_l;
                     }
-                    if (!ok) continue;
-                    // Node.AddPod: GPUs in order, profiles ascending, partial moves kept
-                    bool placed = false, dirty = false;
-                    for (int g = 0; g < ng && !placed; ++g) {
-                        const int fr = (lane < KP) ? (int)bytes(nd.free_[g])[lane] : 0;
-                        const unsigned bad = __ballot_sync(FULL, q_l > 0 && fr < q_l);
-                        const unsigned want = __ballot_sync(FULL, q_l > 0);
-                        const unsigned mv = bad ? (want & ((1u << (__ffs(bad) - 1)) - 1)) : want;   // profiles moved before the first failure
-                        if (mv >> lane & 1) {
-                            bytes(nd.free_[g])[lane] -= (uint8_t)q_l; bytes(nd.used[g])[lane] += (uint8_t)q_l;
-                        }
-                        if (lane == 0 && mv) nd.umask[g] |= (uint16_t)mv;
-                        dirty |= mv != 0;
-                        placed = bad == 0;
-                        __syncwarp();
-                    }
-                    if (!placed) { if (!dirty) break; else continue; }     // clean failure repeats for the rest of the run
-                    remc -= cpu; remm -= mem; reme -= eph;
-                    if (q_l > 0) { s_reqF[lane] += q_l; s_Dg[lane] -= q_l; }
-                    if (lane == 0 && (fl & PF_HAS_OTHER))
-                        for (int e = pb.pod_sptr[s]; e < pb.pod_sptr[s + 1]; ++e) {
-                            const int col = pb.pod_scol[e];
-                            if (col >= 3 + K) nd.req[col] += pb.pod_sqty[e];
-                        }
-                    tracker_remove(pb, pb.pod_key[s], s_removed, lack, lane);
-                    ++added; ++st_place;
+                    if (lane == 0 && mv) nd.umask[g] |= (uint16_t)mv;
+                    dirty |= mv != 0;
+                    placed = bad == 0;
                     __syncwarp();
+                }
+                if (!placed) { if (!dirty) break; else continue; }   // a clean failure repeats for the rest of the run
+                remc -= cpu; remm -= mem; reme -= eph;
+                if (q_l > 0) { ws.reqF[lane] += q_l; ws.Dg[lane] -= q_l; }
+                if (lane == 0 && (fl & PF_HAS_OTHER))
+                    for (int e = pb.pod_sptr[s]; e < pb.pod_sptr[s + 1]; ++e) {
+                        const int col = pb.pod_scol[e];
+                        if (col >= 3 + K) nd.req[col] += pb.pod_sqty[e];
+                    }
+                tracker_remove<PAR>(pb, pb.pod_key[s], removed, lack, lane);
+                ++added; ++st_place;
+                __syncwarp();
+            }
+        }
+    }
+
+    // ---- 3. Commit / Revert (planner.go:144-149) with the object-graph aliasing rules
+    if (added > 0) {
+        if (!PAR && lane < KP) D = ws.Dg[lane];
+        committed = true;
+        if (upd && lane < ng) {                                // partitioningState[n] = GetPartitioning(n) (planner.go:138)
+            const int x = node_i * pb.G + lane;
+            pb.out_count[x] = add_bytes(nd.used[lane], nd.free_[lane]);
+            pb.out_mask[x] = nd.umask[lane] | nd.fmask[lane];
+        }
+    } else if (!PAR && !committed) {
+        D += newA - oldA;                                      // the mutated original is still what the snapshot holds
+    }
+    __syncwarp();
+    return added;
+}
+
+__device__ __forceinline__ void load_tables(const DevProblem& pb, Tables& tb, int tid, int nthreads) {
+    if (pb.kind != NOSPLAN_KIND_MIG) return;
+    for (int r = tid; r < pb.n_rows; r += nthreads) { uint4 row = pb.geom[r]; tb.geom[r] = row; tb.gmask[r] = nz_mask(row); }
+    for (int m = tid; m <= pb.n_models; m += nthreads) tb.off[m] = pb.model_off[m];
+}
+
+// Is the node-parallel pass applicable?  lane p evaluates profile p; warp-uniform result.
+// Saturation bound: one GPU holds at most M_p devices of profile p (allowed geometries / memory, or its t0 free
+// count), a node has at most G GPUs, so lack[p] > (G+2)*M_p keeps every comparison against `required` one-sided.
+__device__ __forceinline__ bool fast_applicable(const DevProblem& pb, int lack_p, int lane) {
+    bool ok = true;
+    if (lane < KP && lack_p > 0) {
+        const long long m = max(pb.sat_m[lane], pb.maxfree[lane]);
+        ok = pb.sat_m[lane] >= 0 && (long long)lack_p > (long long)(pb.G + 2) * m;
+    }
+    const bool any_lack = __ballot_sync(FULL, lane < KP && lack_p > 0) != 0;
+    return __all_sync(FULL, ok) && any_lack && pb.fast_eligible && pb.gflags[0] == 0;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------------------
+// node-parallel pass: grid-stride, one warp per candidate node
+__global__ void __launch_bounds__(128) k_plan_parallel(DevProblem pb) {
+    __shared__ Tables tb;
+    __shared__ WarpScratch ws_all[4];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
+    if (!fast_applicable(pb, lack0, lane)) return;
+    load_tables(pb, tb, tid, blockDim.x);
+    __syncthreads();
+
+    WarpScratch& ws = ws_all[warp];
+    int lack = lack0 > 0 ? SATURATED : 0;
+    long long D = 0, st_evals = 0, st_place = 0, visited = 0;
+    bool committed = true;
+    const int warps_total = gridDim.x * (blockDim.x >> 5);
+    for (int i = blockIdx.x * (blockDim.x >> 5) + warp; i < pb.N; i += warps_total) {
+        if (!pb.cand_flag[i]) continue;
+        NodeRegs nr;
+        load_node(pb, i, lane, nr);
+        store_node(ws.nd, nr, i, lane);
+        __syncwarp();
+        ++visited;
+        process_node<true>(pb, ws, tb, nullptr, pb.placed, lack, D, committed, st_evals, st_place, lane);
+    }
+    if (lane == 0 && visited) {
+        atomicAdd(&pb.acc[0], (unsigned long long)st_place);
+        atomicAdd(&pb.acc[1], (unsigned long long)st_evals);
+        atomicAdd(&pb.acc[2], (unsigned long long)visited);
+    }
+}
+
+// verification of the node-parallel pass, or the sequential sweep
+__global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* cand_idx) {
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    __shared__ Tables tb;
+    __shared__ WarpScratch ws2[2];
+    __shared__ RunRec s_runs[RUN_CACHE];
+    __shared__ int s_scan[256];
+    __shared__ int s_ncand, s_fast_ok;
+    __shared__ int s_lackend[KP];
+
+    typedef long long (*chunk_ll)[32];
+    typedef int (*chunk_i)[32];
+    typedef unsigned (*chunk_u)[32];
+    PodCache pc;
+    pc.cpu = reinterpret_cast<chunk_ll>(s_dyn);
+    pc.mem = pc.cpu + RUN_CACHE;
+    pc.eph = pc.mem + RUN_CACHE;
+    pc.key = reinterpret_cast<chunk_i>(pc.eph + RUN_CACHE);
+    pc.flag = reinterpret_cast<chunk_u>(pc.key + RUN_CACHE);
+    pc.runs = s_runs;
+    pc.n_cached = min(pb.n_runs, RUN_CACHE);
+    unsigned* s_removed = reinterpret_cast<unsigned*>(pc.flag + RUN_CACHE);      // [(n_keys+31)/32]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
+    const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0));
+
+    // ---------------- did the node-parallel pass run, and did its hypothesis hold to the end?
+    if (fast_applicable(pb, lack0, lane)) {
+        if (tid < KP) s_lackend[tid] = pb.lack[tid];
+        __syncthreads();
+        for (int k = tid; k < pb.n_keys; k += blockDim.x)
+            if (pb.placed[k >> 5] >> (k & 31) & 1)
+                for (int p = 0; p < pb.K; ++p) {
+                    const int e = pb.entry_lack[(size_t)k * KP + p];
+                    if (e > 0) atomicSub(&s_lackend[p], e);
+                }
+        __syncthreads();
+        if (warp == 0) {
+            const int le = (lane < KP) ? s_lackend[lane] : 0;
+            const bool ok = fast_applicable(pb, lack0 > 0 ? le : 0, lane) &&
+                            __all_sync(FULL, !(lane < KP && lack0 > 0) || le > 0);
+            if (lane == 0) s_fast_ok = ok;
+            if (ok) {
+                const int lack_end = __popc(__ballot_sync(FULL, le > 0));
+                if (lane == 0) {
+                    DevStats* st = pb.stats;
+                    st->visited_nodes = (long long)pb.acc[2];
+                    st->candidates = (long long)pb.acc[2] * pb.P;
+                    st->geometry_evals = (long long)pb.acc[1];
+                    st->placements = (long long)pb.acc[0];
+                    st->candidate_nodes = (long long)pb.acc[2];
+                    st->lacking_at_start = lack_start;
+                    st->lacking_at_end = lack_end;
+                    st->path = 1;
                 }
             }
         }
-
-        // ---- 3. Commit / Revert (planner.go:144-149) with the object-graph aliasing rules
-        if (added > 0) {
-            if (lane < KP) D = s_Dg[lane];
-            committed = true;
-            if (upd && lane < ng) {                                // partitioningState[n] = GetPartitioning(n) (planner.go:138)
-                const int x = node_i * pb.G + lane;
-                pb.out_count[x] = add_bytes(nd.used[lane], nd.free_[lane]);
-                pb.out_mask[x] = nd.umask[lane] | nd.fmask[lane];
+        __syncthreads();
+        if (s_fast_ok) return;
+        // hypothesis failed: discard the speculative plan (restore GetPartitioningState) and fall through
+        for (int x = tid; x < pb.N * pb.G; x += blockDim.x) {
+            const int i = x / pb.G, j = x - i * pb.G;
+            if (j < pb.node_gpu_count[i]) {
+                pb.out_count[x] = add_bytes(pb.gpu_used[x], pb.gpu_free[x]);
+                pb.out_mask[x] = pb.gpu_umask[x] | pb.gpu_fmask[x];
             }
-        } else if (!committed) {
-            D += newA - oldA;                                      // the mutated original is still what the snapshot holds
         }
-        __syncwarp();
-        if (have_next) store_node(s_node[(c + 1) & 1], nr, next_i, lane);
-        __syncwarp();
+        __syncthreads();
     }
 
+    // ---------------- sequential sweep.  prologue (whole CTA): tables, run cache, candidate compaction in name order
+    load_tables(pb, tb, tid, blockDim.x);
+    for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x) s_removed[w] = 0;
+    for (int r = tid; r < pc.n_cached; r += blockDim.x) s_runs[r] = pb.runs[r];
+    __syncthreads();
+    for (int t = tid; t < pc.n_cached * 32; t += blockDim.x) {
+        const int r = t >> 5, l = t & 31;
+        if (l < s_runs[r].len) {
+            const int s = s_runs[r].start + l;
+            pc.cpu[r][l] = pb.pod_cpu[s]; pc.mem[r][l] = pb.pod_mem[s]; pc.eph[r][l] = pb.pod_eph[s];
+            pc.key[r][l] = pb.pod_key[s]; pc.flag[r][l] = pb.pod_flags[s];
+        }
+    }
+    {   // ordered compaction of candidate flags -> cand_idx (GetCandidateNodes, core/snapshot.go:119-130)
+        int base = 0;
+        for (int c0 = 0; c0 < pb.N; c0 += blockDim.x) {
+            const int i = c0 + tid;
+            const int f = (i < pb.N) ? pb.cand_flag[i] : 0;
+            s_scan[tid] = f;
+            __syncthreads();
+            for (int o = 1; o < (int)blockDim.x; o <<= 1) {
+                int v = (tid >= o) ? s_scan[tid - o] : 0;
+                __syncthreads();
+                s_scan[tid] += v;
+                __syncthreads();
+            }
+            if (f) cand_idx[base + s_scan[tid] - 1] = i;
+            base += s_scan[blockDim.x - 1];
+            __syncthreads();
+        }
+        if (tid == 0) s_ncand = base;
+    }
+    __syncthreads();
+    if (warp != 0) return;
+
+    // ---------------- the chain (warp 0)
+    const int n_cand = s_ncand;
+    int lack = lack0;                                              // lane p: lackingSlices[p]
+    long long D = (lane < KP) ? pb.tot[lane] : 0;                  // lane p: sum(alloc - requested) of slice column p
+    bool committed = false;
+    long long st_visited = 0, st_evals = 0, st_place = 0;
+
+    NodeRegs nr;
+    if (n_cand > 0 && lack_start > 0) {
+        load_node(pb, cand_idx[0], lane, nr);
+        store_node(ws2[0].nd, nr, cand_idx[0], lane);
+    }
+    __syncwarp();
+    for (int c = 0; c < n_cand && lack_start > 0; ++c) {
+        if (__ballot_sync(FULL, lack > 0) == 0) break;             // planner.go:94-97
+        const bool have_next = c + 1 < n_cand;
+        int next_i = 0;
+        if (have_next) { next_i = cand_idx[c + 1]; load_node(pb, next_i, lane, nr); }   // prefetch, consumed below
+        ++st_visited;
+        process_node<false>(pb, ws2[c & 1], tb, &pc, s_removed, lack, D, committed, st_evals, st_place, lane);
+        if (have_next) store_node(ws2[(c + 1) & 1].nd, nr, next_i, lane);
+        __syncwarp();
+    }
+    const int lack_end = __popc(__ballot_sync(FULL, lack > 0));
     if (lane == 0) {
         DevStats* st = pb.stats;
         st->visited_nodes = st_visited;
@@ -541,12 +699,12 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
         st->placements = st_place;
         st->candidate_nodes = lack_start > 0 ? n_cand : 0;   // GetCandidateNodes is not reached on the early return (planner.go:80-83)
         st->lacking_at_start = lack_start;
+        st->lacking_at_end = lack_end;
+        st->path = 0;
     }
-    const int lack_end = __popc(__ballot_sync(FULL, lack > 0));
-    if (lane == 0) pb.stats->lacking_at_end = lack_end;
 }
 
-constexpr size_t SWEEP_DYN_MAX = 200 * 1024;
+constexpr size_t SWEEP_DYN_MAX = 160 * 1024;
 constexpr size_t SWEEP_CHUNK_BYTES = (size_t)RUN_CACHE * 32 * (8 + 8 + 8 + 4 + 4);
 
 size_t sweep_dyn_smem(const DevProblem& pb) { return SWEEP_CHUNK_BYTES + (size_t)((pb.n_keys + 31) / 32) * 4 + 16; }
@@ -556,6 +714,15 @@ int sweep_max_keys() { return (int)((SWEEP_DYN_MAX - SWEEP_CHUNK_BYTES - 16) / 4
 
 cudaError_t sweep_prepare_device() {
     return cudaFuncSetAttribute(k_plan_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SWEEP_DYN_MAX);
+}
+
+cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st) {
+    if (!pb.fast_eligible || pb.N == 0 || pb.P == 0) return cudaSuccess;
+    int blocks = (pb.N + 3) / 4;
+    const int max_blocks = 148 * 8;
+    if (blocks > max_blocks) blocks = max_blocks;
+    k_plan_parallel<<<blocks, 128, 0, st>>>(pb);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st) {

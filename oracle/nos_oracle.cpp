@@ -230,7 +230,7 @@ bool node_update_geometry(const Ctx& c, Node& n, const int32_t* lack, int64_t& e
 
 // Node.AddPod (mig/node.go:201-210): first GPU that takes the pod; Requested grows through the shared
 // pointer, the Pods append is lost on the NodeInfo value copy
-bool node_add_pod(const Ctx& c, Node& n, const PodReq& pr) {
+bool node_add_pod(const Ctx&, Node& n, const PodReq& pr) {
     for (int j = 0; j < n.ng; ++j) {
         if (gpu_add_pod(n.g[j], pr)) {
             for (int k = 0; k < 3; ++k) n.req[k] += pr.base[k];

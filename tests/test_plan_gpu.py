@@ -144,3 +144,28 @@ def test_errors_are_reported_not_crashes(eng):
     with pytest.raises(capi.NosplanError):
         eng.plan(s, p, None, 7)
     eng.plan(s, p, None, 0)                               # the handle stays usable
+
+
+def test_paths_taken(eng):
+    """The node-parallel pass must be the one that produced the saturating plans, the sequential sweep the others."""
+    s, p = synth.mig_cluster(200, 8, 1000, seed=5)
+    st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "saturating")
+    assert st["path"] == 1
+    s, p = synth.mig_cluster(200, 8, 1000, seed=5, regime="satisfiable")
+    st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "satisfiable")
+    assert st["path"] == 0
+    # inconsistent node accounts -> the cluster-wide gate matters -> sequential
+    s, p = synth.mig_cluster(200, 8, 1000, seed=5)
+    s.node_requested[7, 3] += 5
+    st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "inconsistent")
+    assert st["path"] == 0
+
+
+def test_saturation_hypothesis_fails_a_posteriori(eng):
+    """lack starts just above the saturation bound (G+2)*M = 70 and is driven below it by the placements: the
+    node-parallel result must be discarded and the sequential sweep must produce the plan."""
+    for n_pods in (71, 75, 90, 150):
+        s, p = synth.mig_cluster(12, 8, n_pods, seed=9, demand=["1g.10gb"], demand_probs=[1.0])
+        st = check(eng, s, p, None, pk.FILTER_NONE, f"posteriori {n_pods}")
+        assert st["lacking_at_start"] == 1
+    assert st["path"] in (0, 1)
