@@ -52,7 +52,7 @@ struct SNode {
 
 struct WarpScratch {       // per-warp shared memory
     SNode nd;
-    int req[KP];
+    uint4 pack[2];         // min(required, 255) and the required >= 256 mask, one byte per profile
     long long Dg[KP], allocF[KP], reqF[KP];
 };
 
@@ -60,15 +60,17 @@ struct Tables {            // CTA-wide shared memory, read-only after the prolog
     uint4 geom[MAX_ROWS];
     uint16_t gmask[MAX_ROWS];
     int off[MAX_MODELS + 1];
+    int max_rows;          // most geometries of any model
 };
 
-struct PodCache {          // first 32 pods of the first RUN_CACHE runs (sequential driver only)
+struct PodCache {          // run records of the first RUN_CACHE runs; first 32 pods of each (sequential driver only)
     long long (*cpu)[32];
     long long (*mem)[32];
     long long (*eph)[32];
     int (*key)[32];
     unsigned (*flag)[32];
     const RunRec* runs;    // shared-memory copy of the first n_cached run records
+    const int* chunk_off;  // shared-memory copy of run_chunk_off for those runs
     int n_cached;
 };
 
@@ -136,50 +138,92 @@ __device__ __forceinline__ int warp_excl_int(int v, int lane) {
 }
 
 // ---------------------------------------------------------------- MIG GPU.UpdateGeometryFor (mig/gpu.go:158-212)
-// lanes = geometries of the GPU's model.  `required` lives in lane p (p < 16).  Returns updated (warp-uniform).
-__device__ __forceinline__ bool mig_gpu_update(SNode& nd, int g, int required, int lane, int K, const Tables& tb,
-                                               int* s_req, long long& evals) {
-    if (lane < KP) s_req[lane] = required;
+// Scoring of one allowed geometry against one GPU, 4 profiles per 32-bit word with byte-SIMD integer ops:
+//   score = sum_p [required[p] > 0 and free[p] < required[p]] * max(0, min(row[p] - used[p], required[p]))
+// `rq` holds min(required, 255) per byte (exact: row - used <= 255), `big` 0xff where required >= 256 (then
+// free < required always).  CanApplyGeometry (:97-110) for an allowed row is row[p] >= used[p] for every p.
+struct ReqPack { uint4 rq, big; int n_req; };
+
+__device__ __forceinline__ unsigned score_word(unsigned row, unsigned used, unsigned fre, unsigned rq, unsigned big) {
+    const unsigned m = __vminu4(__vsubus4(row, used), rq);
+    return __vsadu4(m & (__vcmpltu4(fre, rq) | big), 0u);
+}
+
+__device__ __forceinline__ unsigned score_row(const uint4& row, const uint4& used, const uint4& fre, const ReqPack& rp, int K) {
+    const bool can = (__vcmpgeu4(row.x, used.x) & __vcmpgeu4(row.y, used.y) & __vcmpgeu4(row.z, used.z) & __vcmpgeu4(row.w, used.w)) == 0xffffffffu;
+    unsigned score = score_word(row.x, used.x, fre.x, rp.rq.x, rp.big.x);
+    if (K > 4) score += score_word(row.y, used.y, fre.y, rp.rq.y, rp.big.y);
+    if (K > 8) score += score_word(row.z, used.z, fre.z, rp.rq.z, rp.big.z) + score_word(row.w, used.w, fre.w, rp.rq.w, rp.big.w);
+    return can ? score : 0u;
+}
+
+// lane p (< 16) holds required[p]; every lane gets the packed form through shared memory
+__device__ __forceinline__ ReqPack pack_required(int required, int lane, uint4* s_pack) {
+    uint8_t* b = reinterpret_cast<uint8_t*>(s_pack);
+    if (lane < KP) { b[lane] = (uint8_t)min(max(required, 0), 255); b[16 + lane] = required >= 256 ? 0xff : 0; }
     __syncwarp();
+    ReqPack rp;
+    rp.rq = s_pack[0]; rp.big = s_pack[1];
+    rp.n_req = __popc(__ballot_sync(FULL, required > 0));
+    __syncwarp();
+    return rp;
+}
+
+// ApplyGeometry (:132-152) of table row `br` on GPU g by the 16 lanes `pl` = 0..15 of the caller's segment
+__device__ __forceinline__ void apply_row(SNode& nd, int g, int br, int pl, const Tables& tb) {
+    const unsigned rw = byte_of(tb.geom[br], pl), us = byte_of(nd.used[g], pl);
+    bytes(nd.free_[g])[pl] = (uint8_t)(rw ? rw - us : 0);                     // zero kept (:141)
+    if (pl == 0) nd.fmask[g] = tb.gmask[br];
+}
+
+// One GPU: lanes = geometries of the GPU's model.  Returns updated (warp-uniform).
+__device__ __forceinline__ bool mig_gpu_update(SNode& nd, int g, const ReqPack& rp, int lane, int K, const Tables& tb,
+                                               long long& evals) {
     const int m = nd.model[g];
     const int r0 = tb.off[m], nrows = tb.off[m + 1] - r0;
-    const int n_req = __popc(__ballot_sync(FULL, required > 0));
-    evals += (long long)nrows * n_req;
+    evals += (long long)nrows * rp.n_req;
     unsigned key = 0;
     if (lane < nrows) {
-        const uint4 row = tb.geom[r0 + lane];
-        const uint4 used = nd.used[g], fre = nd.free_[g];
-        const unsigned um = nd.umask[g];
-        bool can = true;                                   // CanApplyGeometry (:97-110) for an allowed row
-        int score = 0;
-#pragma unroll
-        for (int p = 0; p < KP; ++p) {
-            const int rw = (int)byte_of(row, p), us = (int)byte_of(used, p);
-            if ((um >> p & 1) && rw < us) can = false;
-        }
-#pragma unroll
-        for (int p = 0; p < KP; ++p) {
-            if (p < K) {
-                const int rq = s_req[p];
-                const int rw = (int)byte_of(row, p), us = (int)byte_of(used, p), fr = (int)byte_of(fre, p);
-                if (rq > 0 && fr < rq) {
-                    const int n = min(rw - us, rq);
-                    if (n > 0) score += n;
-                }
-            }
-        }
-        if (can && score > 0) key = ((unsigned)score << 5) | (unsigned)(31 - lane);
+        const unsigned score = score_row(tb.geom[r0 + lane], nd.used[g], nd.free_[g], rp, K);
+        if (score) key = (score << 5) | (unsigned)(31 - lane);
     }
     const unsigned best = __reduce_max_sync(FULL, key);
     if (best == 0) return false;
     const int br = r0 + 31 - (int)(best & 31u);            // strict > in table order == lowest index among max
-    if (lane < KP) {                                        // ApplyGeometry (:132-152): lanes = profiles
-        const unsigned rw = byte_of(tb.geom[br], lane), us = byte_of(nd.used[g], lane);
-        bytes(nd.free_[g])[lane] = (uint8_t)(rw ? rw - us : 0);
-    }
-    if (lane == 0) nd.fmask[g] = tb.gmask[br];
+    if (lane < KP) apply_row(nd, g, br, lane, tb);
     __syncwarp();
     return true;
+}
+
+// All GPUs of a node at once -- valid only when `required` is not consumed from GPU to GPU (saturated lacking
+// vector, node-parallel pass).  Lanes = (GPU, geometry) pairs, S lanes per GPU, 32/S GPUs per step.
+__device__ __forceinline__ bool mig_node_update_all(SNode& nd, int ng, const ReqPack& rp, int lane, int K, const Tables& tb,
+                                                    long long& evals) {
+    const int S = tb.max_rows <= 16 ? 16 : 32;
+    const int sub = lane / S, r = lane - sub * S;
+    const unsigned segmask = S == 32 ? FULL : (0xffffu << (16 * sub));
+    bool upd = false;
+    for (int g0 = 0; g0 < ng; g0 += 32 / S) {
+        const int g = g0 + sub;
+        unsigned key = 0;
+        int r0 = 0;
+        if (g < ng) {
+            const int m = nd.model[g];
+            r0 = tb.off[m];
+            const int nrows = tb.off[m + 1] - r0;
+            if (r == 0) evals += (long long)nrows * rp.n_req;
+            if (r < nrows) {
+                const unsigned score = score_row(tb.geom[r0 + r], nd.used[g], nd.free_[g], rp, K);
+                if (score) key = (score << 5) | (unsigned)(31 - r);
+            }
+        }
+        const unsigned best = __reduce_max_sync(segmask, key);
+        if (best != 0 && r < KP) apply_row(nd, g, r0 + 31 - (int)(best & 31u), r, tb);
+        upd |= __any_sync(FULL, best != 0);
+        __syncwarp();
+    }
+    evals = warp_sum_ll(evals);                                // per-segment partial counts -> warp total
+    return upd;
 }
 
 // ---------------------------------------------------------------- MPS GPU.UpdateGeometryFor (slicing/gpu.go:162-232)
@@ -269,17 +313,26 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     // ---- 1. Node.UpdateGeometryFor
     int required = lack;
     bool upd = false;
-    for (int g = 0; g < ng; ++g) {
-        bool u;
-        if (mig) u = mig_gpu_update(nd, g, required, lane, K, tb, ws.req, st_evals);
-        else {
-            st_evals += __popc(__ballot_sync(FULL, required > 0));
-            u = mps_gpu_update(nd, g, required, lane, pb);
-        }
-        upd |= u;
-        if (!PAR && lane < KP) {
-            const int f = (int)bytes(nd.free_[g])[lane];
-            if ((nd.fmask[g] >> lane & 1) && required > 0) required = max(0, required - f);
+    if (PAR && mig) {
+        const ReqPack rp = pack_required(required, lane, ws.pack);
+        long long ev = 0;
+        upd = mig_node_update_all(nd, ng, rp, lane, K, tb, ev);
+        st_evals += ev;
+    } else {
+        for (int g = 0; g < ng; ++g) {
+            bool u;
+            if (mig) {
+                const ReqPack rp = pack_required(required, lane, ws.pack);
+                u = mig_gpu_update(nd, g, rp, lane, K, tb, st_evals);
+            } else {
+                st_evals += __popc(__ballot_sync(FULL, required > 0));
+                u = mps_gpu_update(nd, g, required, lane, pb);
+            }
+            upd |= u;
+            if (!PAR && lane < KP) {
+                const int f = (int)bytes(nd.free_[g])[lane];
+                if ((nd.fmask[g] >> lane & 1) && required > 0) required = max(0, required - f);
+            }
         }
     }
     long long newA = 0;                                        // computeScalarResources (mig/node.go:179-195)
@@ -296,8 +349,9 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     int added = 0;
     const bool all_fail = (fm == NOSPLAN_FILTER_REJECT_ALL) || (fit && !podcount_ok);
     for (int ri = 0; ri < pb.n_runs && !all_fail; ++ri) {
-        const bool cached = pc && ri < pc->n_cached;
-        const RunRec* rr = cached ? &pc->runs[ri] : &pb.runs[ri];
+        const bool rcached = ri < pc->n_cached;
+        const bool cached = rcached && pc->cpu != nullptr;
+        const RunRec* rr = rcached ? &pc->runs[ri] : &pb.runs[ri];
         const int rstart = rr->start, rend = rr->start + rr->len, n_ent = rr->n_ent;
         const int q_l = (lane < KP) ? (int)rr->q[lane] : 0;
         // class-level tests; all of them only get tighter while this node is processed
@@ -321,7 +375,8 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                 if (fit) cap = min(cap, (ws.allocF[p] - ws.reqF[p]) / q);
             }
             if (cap <= 0) continue;
-            const int c0 = pb.run_chunk_off[ri], nch = pb.run_chunk_off[ri + 1] - c0;
+            const int c0 = rcached ? pc->chunk_off[ri] : pb.run_chunk_off[ri];
+            const int nch = (rr->len + 31) >> 5;
             for (int cb = 0; cb < nch && cap > 0; cb += 32) {
                 // chunk minima of 32 chunks at a time: a chunk whose cheapest eligible pod does not fit is skipped
                 long long mc = LLONG_MAX, mm = LLONG_MAX, me = LLONG_MAX;
@@ -386,11 +441,18 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                                 if (lane == 0) { ws.reqF[p] += (long long)n * q; ws.Dg[p] -= (long long)n * q; }
                                 cap -= n;
                             }
-                            unsigned todo = accm;                          // tracker.Remove per placed pod
-                            while (todo) {
-                                const int l = __ffs(todo) - 1;
-                                todo &= todo - 1;
-                                tracker_remove<PAR>(pb, __shfl_sync(FULL, key, l), removed, lack, lane);
+                            if (PAR) {                                     // tracker.Remove per placed pod
+                                if (acc) {
+                                    const unsigned bit = 1u << (key & 31);
+                                    if (!(removed[key >> 5] & bit)) atomicOr(&removed[key >> 5], bit);
+                                }
+                            } else {
+                                unsigned todo = accm;
+                                while (todo) {
+                                    const int l = __ffs(todo) - 1;
+                                    todo &= todo - 1;
+                                    tracker_remove<PAR>(pb, __shfl_sync(FULL, key, l), removed, lack, lane);
+                                }
                             }
                             added += n; st_place += n;
                             __syncwarp();
@@ -512,6 +574,11 @@ __device__ __forceinline__ void load_tables(const DevProblem& pb, Tables& tb, in
     if (pb.kind != NOSPLAN_KIND_MIG) return;
     for (int r = tid; r < pb.n_rows; r += nthreads) { uint4 row = pb.geom[r]; tb.geom[r] = row; tb.gmask[r] = nz_mask(row); }
     for (int m = tid; m <= pb.n_models; m += nthreads) tb.off[m] = pb.model_off[m];
+    if (tid == 0) {
+        int mr = 0;
+        for (int m = 0; m < pb.n_models; ++m) mr = max(mr, pb.model_off[m + 1] - pb.model_off[m]);
+        tb.max_rows = mr;
+    }
 }
 
 // Is the node-parallel pass applicable?  lane p evaluates profile p; warp-uniform result.
@@ -534,10 +601,16 @@ __device__ __forceinline__ bool fast_applicable(const DevProblem& pb, int lack_p
 __global__ void __launch_bounds__(128) k_plan_parallel(DevProblem pb) {
     __shared__ Tables tb;
     __shared__ WarpScratch ws_all[4];
+    __shared__ RunRec s_runs[RUN_CACHE];
+    __shared__ int s_choff[RUN_CACHE];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
     if (!fast_applicable(pb, lack0, lane)) return;
     load_tables(pb, tb, tid, blockDim.x);
+    PodCache pc;
+    pc.cpu = nullptr; pc.mem = nullptr; pc.eph = nullptr; pc.key = nullptr; pc.flag = nullptr;
+    pc.runs = s_runs; pc.chunk_off = s_choff; pc.n_cached = min(pb.n_runs, RUN_CACHE);
+    for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
     __syncthreads();
 
     WarpScratch& ws = ws_all[warp];
@@ -552,7 +625,7 @@ __global__ void __launch_bounds__(128) k_plan_parallel(DevProblem pb) {
         store_node(ws.nd, nr, i, lane);
         __syncwarp();
         ++visited;
-        process_node<true>(pb, ws, tb, nullptr, pb.placed, lack, D, committed, st_evals, st_place, lane);
+        process_node<true>(pb, ws, tb, &pc, pb.placed, lack, D, committed, st_evals, st_place, lane);
     }
     if (lane == 0 && visited) {
         atomicAdd(&pb.acc[0], (unsigned long long)st_place);
@@ -567,6 +640,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     __shared__ Tables tb;
     __shared__ WarpScratch ws2[2];
     __shared__ RunRec s_runs[RUN_CACHE];
+    __shared__ int s_choff[RUN_CACHE];
     __shared__ int s_scan[256];
     __shared__ int s_ncand, s_fast_ok;
     __shared__ int s_lackend[KP];
@@ -581,6 +655,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     pc.key = reinterpret_cast<chunk_i>(pc.eph + RUN_CACHE);
     pc.flag = reinterpret_cast<chunk_u>(pc.key + RUN_CACHE);
     pc.runs = s_runs;
+    pc.chunk_off = s_choff;
     pc.n_cached = min(pb.n_runs, RUN_CACHE);
     unsigned* s_removed = reinterpret_cast<unsigned*>(pc.flag + RUN_CACHE);      // [(n_keys+31)/32]
 
@@ -635,7 +710,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     // ---------------- sequential sweep.  prologue (whole CTA): tables, run cache, candidate compaction in name order
     load_tables(pb, tb, tid, blockDim.x);
     for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x) s_removed[w] = 0;
-    for (int r = tid; r < pc.n_cached; r += blockDim.x) s_runs[r] = pb.runs[r];
+    for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
     __syncthreads();
     for (int t = tid; t < pc.n_cached * 32; t += blockDim.x) {
         const int r = t >> 5, l = t & 31;
@@ -712,15 +787,20 @@ size_t sweep_dyn_smem(const DevProblem& pb) { return SWEEP_CHUNK_BYTES + (size_t
 // largest number of tracker keys (distinct namespace/name of pending pods) the shared-memory bitmap can hold
 int sweep_max_keys() { return (int)((SWEEP_DYN_MAX - SWEEP_CHUNK_BYTES - 16) / 4) * 32; }
 
+static int g_par_blocks = 148 * 4;
+
 cudaError_t sweep_prepare_device() {
+    int dev = 0, sms = 148, per_sm = 4;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_plan_parallel, 128, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+    g_par_blocks = sms * per_sm;                               // one resident wave, grid-stride over the nodes
     return cudaFuncSetAttribute(k_plan_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SWEEP_DYN_MAX);
 }
 
 cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st) {
     if (!pb.fast_eligible || pb.N == 0 || pb.P == 0) return cudaSuccess;
     int blocks = (pb.N + 3) / 4;
-    const int max_blocks = 148 * 8;
-    if (blocks > max_blocks) blocks = max_blocks;
+    if (blocks > g_par_blocks) blocks = g_par_blocks;
     k_plan_parallel<<<blocks, 128, 0, st>>>(pb);
     return cudaGetLastError();
 }
