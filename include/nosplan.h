@@ -147,6 +147,22 @@ int nosplan_run(nosplan_t* h);
 int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats);
 void* nosplan_stream(nosplan_t* h);    /* cudaStream_t */
 
+/* No counterpart in the reference.  The tracker initialisation of Plan() -- lacking[p] summed over the pods, and the
+ * number of distinct pod keys that lack any slice -- for callers that may not allocate device memory: processes
+ * sharing the GPU with latency-sensitive streams (cudaMalloc/cudaFree synchronise the whole device) or running inside a
+ * fixed device-memory reservation.  All pointers are DEVICE pointers owned by the caller; pods in the nosplan_pods
+ * layout (tracker_key, scalar_ptr/col/qty), d_totals = [16] int64 sum over nodes of (allocatable - requested) per slice
+ * column, outputs d_lack = [16] int32 and d_lacking_entries = [1] int32.  The per-key working table lives in a static
+ * device array of NOSPLAN_STATIC_MAX_KEYS rows (1 MiB per GPU, kept until the process exits): n_keys above that is
+ * refused with NOSPLAN_E_LIMIT.  The table is shared by every call on that GPU -- overlapping calls race -- and is
+ * cleared per call.  Work is enqueued on cuda_stream, no synchronisation, no allocation; the first call on a GPU
+ * resolves the table's device address and should be made outside stream capture.  errbuf (optional) gets a message. */
+#define NOSPLAN_STATIC_MAX_KEYS 16384
+int nosplan_lacking_static(int cuda_device, void* cuda_stream, int32_t n_pods, int32_t n_keys, int32_t n_profiles,
+                           const int32_t* d_tracker_key, const int32_t* d_scalar_ptr, const int32_t* d_scalar_col,
+                           const int64_t* d_scalar_qty, const int64_t* d_totals, int32_t* d_lack,
+                           int32_t* d_lacking_entries, char* errbuf, int32_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,9 @@ LIB_PATH = os.path.join(_HERE, "libnosplan.so")
 EXPORTED_SYMBOLS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_plan",
     "nosplan_upload", "nosplan_run", "nosplan_download", "nosplan_stream",
+    "nosplan_lacking_static",
 ]
+STATIC_MAX_KEYS = 16384
 
 
 class CSnapshot(C.Structure):
@@ -146,7 +148,19 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_download.restype = C.c_int
     lib.nosplan_stream.argtypes = [C.c_void_p]
     lib.nosplan_stream.restype = C.c_void_p
+    lib.nosplan_lacking_static.argtypes = [C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]
+    lib.nosplan_lacking_static.restype = C.c_int
     return lib
+
+
+def lacking_static(lib, device, stream, n_pods, n_keys, n_profiles, d_key, d_ptr, d_col, d_qty, d_totals, d_lack, d_entries):
+    """nosplan_lacking_static on raw device addresses (ints).  Allocates nothing on the device; asynchronous on `stream`.
+    Returns (rc, message)."""
+    buf = C.create_string_buffer(256)
+    rc = lib.nosplan_lacking_static(device, stream, n_pods, n_keys, n_profiles, d_key, d_ptr, d_col, d_qty, d_totals,
+                                    d_lack, d_entries, buf, 256)
+    return rc, buf.value.decode()
 
 
 class Engine:
