@@ -163,6 +163,72 @@ int nosplan_lacking_static(int cuda_device, void* cuda_stream, int32_t n_pods, i
                            const int64_t* d_scalar_qty, const int64_t* d_totals, int32_t* d_lack,
                            int32_t* d_lacking_entries, char* errbuf, int32_t errbuf_len);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * ElasticQuota accounting (pkg/scheduler/plugins/capacityscheduling/elasticquotainfo.go, capacity_scheduling.go:190-278,
+ * pkg/gpu/util/resource.go:60-86, internal/controllers/elasticquota/elasticquota.go:38-118).
+ * Quota resource columns: 0 cpu (milli)  1 memory  2 ephemeral-storage  3 pods  4.. scalar resources, Rq <= 16.
+ * Key presence of a scalar in a framework.Resource / ResourceList is a bit in a 32-bit mask (bit c = column c;
+ * bit 31 = the whole Resource is non-nil). */
+#define NOSPLAN_QUOTA_MAX_RES 16
+#define NOSPLAN_QUOTA_NONNIL  0x80000000u
+
+#define NOSPLAN_PREFILTER_SUCCESS  0
+#define NOSPLAN_PREFILTER_OVER_MAX 1   /* Unschedulable: quota used + request > Max (capacity_scheduling.go:257-266) */
+#define NOSPLAN_PREFILTER_OVER_MIN 2   /* Unschedulable: aggregated used + request > aggregated Min (:268-275) */
+
+/* Replaces: ElasticQuotaInfos, the namespace -> *ElasticQuotaInfo map (elasticquotainfo.go:31-72).  A
+ * CompositeElasticQuota is one quota row referenced by several namespaces and is counted once per namespace by the
+ * aggregates, exactly like the same pointer stored under several map keys (:68-72). */
+typedef struct nosplan_quotas {
+    int32_t n_quotas;                  /* E */
+    int32_t n_res;                     /* Rq */
+    int32_t n_namespaces;              /* NS */
+    int32_t gpu_memory_col;            /* column of nos.nebuly.com/gpu-memory (>= 4), -1 = not tracked */
+    const int32_t* ns_quota;           /* [NS] quota row of the namespace, -1 = not subject to any quota */
+    const int64_t* min;                /* [E][Rq] */
+    const int64_t* max;                /* [E][Rq] */
+    const int64_t* used_init;          /* [E][Rq] Used before the pods below are reserved; NULL = zeros */
+    const uint32_t* min_mask;          /* [E] */
+    const uint32_t* max_mask;          /* [E] */
+    const uint32_t* used_mask;         /* [E] scalar keys present in used_init */
+    const uint8_t* max_enforced;       /* [E] ElasticQuotaInfo.MaxEnforced */
+    const int64_t* gpu_memory_coeff;   /* [Rq] GB of gpu-memory one unit of column c stands for: NvidiaGPUDeviceMemoryGB for
+                                          nvidia.com/gpu, the profile's GB for nvidia.com/mig-*, else 0 (pkg/gpu/util/resource.go:70-86) */
+} nosplan_quotas;
+
+/* Replaces: []*v1.Pod after resource.ComputePodRequest; the engine adds the gpu-memory scalar itself (Q2). */
+typedef struct nosplan_quota_pods {
+    int32_t n_pods;
+    const int32_t* ns;                 /* [P] namespace id */
+    const int64_t* request;            /* [P][Rq] plain request (column gpu_memory_col is ignored on input) */
+    const uint32_t* request_mask;      /* [P] scalar keys present in the request; NULL = the non-zero ones.  reserveResource
+                                          makes every requested key present in Used, even with quantity 0 (:197-199) */
+    const int32_t* priority;           /* [P]  *Spec.Priority                (operator labelling only, may be NULL otherwise) */
+    const int64_t* creation_ts;        /* [P]  CreationTimestamp, unix s     (operator labelling only) */
+    const int32_t* name_rank;          /* [P]  rank of the pod name in byte order (operator labelling only) */
+} nosplan_quota_pods;
+
+typedef struct nosplan_quota_out {     /* every pointer may be NULL = not wanted */
+    int64_t* used;                     /* [E][Rq] Used after reserveResource of every running pod (:194-200, 276-292) */
+    uint32_t* used_mask;               /* [E] scalar keys present in that Used */
+    int64_t* agg_min;                  /* [Rq] getAggregatedMin (:154-163) */
+    int64_t* agg_used;                 /* [Rq] getAggregatedUsed (:165-174) */
+    int64_t* agg_overquota;            /* [Rq] getAggregatedOverquotas (:145-152) */
+    uint32_t* agg_masks;               /* [3]  scalar key sets of the three aggregates */
+    int64_t* guaranteed;               /* [E][Rq] GetGuaranteedOverquotas of every quota (:81-119), float64 like the reference */
+    uint8_t* prefilter;                /* [P_pending] NOSPLAN_PREFILTER_* (capacity_scheduling.go:190-278) */
+    uint8_t* over_quota;               /* [P_running] operator label: 1 = over-quota (elasticquota.go:38-72) */
+    int64_t* operator_used;            /* [E][Rq] status.used as the operator computes it (restricted to the keys of Min) */
+    int32_t* ambiguous_order;          /* [1] != 0: two pods of one quota tie on (creationTimestamp, priority) with requests that
+                                          the reference's partial-order comparator cannot rank consistently */
+} nosplan_quota_out;
+
+/* Recompute the quota state from scratch for E quotas, the running pods (reserved into Used) and the pending pods
+ * (PreFilter verdict each).  Host buffers in and out.  Replaces, as one batch: addPod/reserveResource event handling,
+ * the aggregate getters, GetGuaranteedOverquotas, the quota part of PreFilter and PatchPodsAndComputeUsedQuota. */
+int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
+                            const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats);
+
 #ifdef __cplusplus
 }
 #endif

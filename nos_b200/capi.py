@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libnosplan.so")
 EXPORTED_SYMBOLS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_plan",
     "nosplan_upload", "nosplan_run", "nosplan_download", "nosplan_stream",
-    "nosplan_lacking_static",
+    "nosplan_lacking_static", "nosplan_quota_recompute",
 ]
 STATIC_MAX_KEYS = 16384
 
@@ -151,6 +151,10 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_lacking_static.argtypes = [C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]
     lib.nosplan_lacking_static.restype = C.c_int
+    from . import quota_packing as qp
+    lib.nosplan_quota_recompute.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(qp.CQuotaPods), C.POINTER(qp.CQuotaPods),
+                                            C.POINTER(qp.CQuotaOut), C.POINTER(CStats)]
+    lib.nosplan_quota_recompute.restype = C.c_int
     return lib
 
 
@@ -231,3 +235,17 @@ class Engine:
 
     def stream(self) -> int:
         return int(self.lib.nosplan_stream(self.h) or 0)
+
+    def quota_recompute(self, pq, running=None, pending=None):
+        """nosplan_quota_recompute -> (dict of arrays as QuotaResult.trimmed(), stats dict)"""
+        from . import quota_packing as qp
+        cq, k1 = qp.c_quotas(pq)
+        cr, k2 = qp.c_quota_pods(running)
+        cp, k3 = qp.c_quota_pods(pending)
+        res = qp.QuotaResult(pq, running.n_pods if running else 0, pending.n_pods if pending else 0)
+        out = res.c_struct()
+        st = CStats()
+        rc = self.lib.nosplan_quota_recompute(self.h, C.byref(cq), C.byref(cr), C.byref(cp), C.byref(out), C.byref(st))
+        self._check(rc, "nosplan_quota_recompute")
+        del k1, k2, k3
+        return res.trimmed(), st.as_dict()

@@ -24,6 +24,14 @@ int sweep_max_keys();
 
 using namespace nsp;
 
+struct nosplan_quota_ctx;
+extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                            const nosplan_quotas* qs, const nosplan_quota_pods* running,
+                                            const nosplan_quota_pods* pending, nosplan_quota_out* out, float* ms_h2d, float* ms_k,
+                                            float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes);
+extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx);
+extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new();
+
 struct nosplan {
     int device = -1;
     cudaStream_t stream = nullptr;
@@ -40,6 +48,7 @@ struct nosplan {
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
     size_t h2d_bytes = 0;
+    nosplan_quota_ctx* qctx = nullptr;
     std::string err;
 };
 
@@ -172,6 +181,7 @@ void nosplan_destroy(nosplan_t* h) {
     if (h->d_arena) cudaFree(h->d_arena);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->qctx) nosplan_quota_ctx_free(h->qctx);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -496,6 +506,21 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
     rc = nosplan_run(h);
     if (rc != NOSPLAN_OK) return rc;
     return nosplan_download(h, out, stats);
+}
+
+int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
+                            const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
+    const int rc = nosplan_quota_recompute_impl(h->device, h->stream, h->qctx, &h->err, quotas, running, pending, out, &a, &b, &c,
+                                                &launches, &hb, &db);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
+        stats->h2d_bytes = hb; stats->d2h_bytes = db;
+    }
+    return rc;
 }
 
 }  // extern "C"

@@ -1,0 +1,481 @@
+// ElasticQuota accounting kernels (sm_100a) and nosplan_quota_recompute.
+//
+//   k_quota_used       reserveResource of every running pod into its quota row (elasticquotainfo.go:194-200, 276-292), with
+//                      the gpu-memory scalar of pkg/gpu/util/resource.go:60-86 computed on the fly.  Half a warp per pod
+//                      (lane = resource column, so consecutive pods are one coalesced read), block-private int64 table in
+//                      shared memory, one global atomic per touched (quota, column) per block.
+//   k_quota_aggregate  getAggregatedMin / Used / Overquotas over the namespace -> quota map (a composite quota counts once
+//                      per namespace, :68-72, 145-174) and GetGuaranteedOverquotas of every quota (:81-119) in IEEE double
+//                      with explicit round-to-nearest mul/div (no FMA contraction), floor, and amd64 int64() semantics.
+//   k_quota_prefilter  the quota part of CapacityScheduling.PreFilter per pending pod (capacity_scheduling.go:190-278).
+//   k_label_*          the operator's in-quota / over-quota labelling (internal/controllers/elasticquota/elasticquota.go:
+//                      38-118): pods ordered by (quota, creationTimestamp, priority) with three stable LSD radix passes
+//                      (CUB), ties resolved with the reference's request / name comparator, then a per-quota running sum
+//                      (block scan per resource column) compared with Min.
+#include <climits>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include "nosplan_dev.cuh"
+
+namespace nsp {
+
+constexpr int QR = NOSPLAN_QUOTA_MAX_RES;
+constexpr unsigned SCALAR_BITS = 0x7ffffff0u;
+
+struct DevQuota {
+    int E, R, NS, gm, Pr, Pp;
+    const int32_t* ns_quota;
+    const long long *qmin, *qmax, *used_init;
+    const uint32_t *min_mask, *max_mask, *used_mask_in;
+    const uint8_t* max_enforced;
+    long long coeff[QR];
+    // running pods
+    const int32_t* r_ns; const long long* r_req; const uint32_t* r_mask;
+    const int32_t* r_prio; const long long* r_ts; const int32_t* r_rank;
+    // pending pods
+    const int32_t* p_ns; const long long* p_req; const uint32_t* p_mask;
+    // outputs / work
+    long long* used; uint32_t* used_mask;
+    long long *agg_min, *agg_used, *agg_over; uint32_t* agg_masks;
+    long long* guaranteed; uint8_t* prefilter; uint8_t* over_quota; long long* operator_used; int32_t* ambiguous;
+    // labelling work
+    unsigned long long *key_a, *key_b; int32_t *val_a, *val_b; int32_t* seg_count; int32_t* seg_off;
+};
+
+__device__ __forceinline__ long long go_int64(double x) {       // int64(f) as compiled for amd64 (CVTTSD2SQ)
+    if (!(x == x) || x >= 9223372036854775808.0 || x < -9223372036854775808.0) return LLONG_MIN;
+    return (long long)x;
+}
+__device__ __forceinline__ double approx_f64(int c, long long v) {   // Quantity.AsApproximateFloat64 (cpu: milli * Pow10(-3))
+    return c == 0 ? __dmul_rn((double)v, 1e-3) : (double)v;
+}
+
+// quota request of pod i, column `c` held by lane c of a 16-lane segment; returns the request mask (segment-uniform)
+__device__ __forceinline__ long long pod_request16(const DevQuota& q, const long long* req, const uint32_t* mask, int i, int c,
+                                                   unsigned segmask, uint32_t& rmask) {
+    long long v = (c < q.R && c != q.gm) ? req[(size_t)i * q.R + c] : 0;
+    long long g = (c < q.R) ? q.coeff[c] * v : 0;
+#pragma unroll
+    for (int o = 8; o; o >>= 1) g += __shfl_xor_sync(segmask, g, o, 16);
+    uint32_t m;
+    if (mask) m = mask[i] & SCALAR_BITS;
+    else {
+        m = (c >= 4 && v != 0) ? (1u << c) : 0;
+#pragma unroll
+        for (int o = 8; o; o >>= 1) m |= __shfl_xor_sync(segmask, m, o, 16);
+    }
+    if (q.gm >= 0) { m |= 1u << q.gm; if (c == q.gm) v = g; }
+    rmask = m;
+    return v;
+}
+
+__global__ void __launch_bounds__(256) k_quota_used(DevQuota q, int use_smem) {
+    extern __shared__ long long s_tab[];       // [E*R] when use_smem
+    const int tid = threadIdx.x, c = tid & 15, sub = (tid >> 4) & 1;
+    const unsigned segmask = 0xffffu << (16 * sub);
+    if (use_smem) {
+        for (int x = tid; x < q.E * q.R; x += blockDim.x) s_tab[x] = 0;
+        __syncthreads();
+    }
+    const int pods_per_block = blockDim.x / 16;
+    for (int i0 = blockIdx.x * pods_per_block; i0 < q.Pr; i0 += gridDim.x * pods_per_block) {
+        const int i = i0 + (tid >> 4);
+        if (i < q.Pr) {                                  // whole 16-lane segment takes the same branch
+            const int ns = q.r_ns[i];
+            const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+            uint32_t rmask;
+            const long long v = pod_request16(q, q.r_req, q.r_mask, i, c, segmask, rmask);
+            if (e >= 0) {
+                const bool take = c < q.R && (c == 0 || c == 1 || (c >= 4 && (rmask >> c & 1)));   // Memory, MilliCPU, scalars only
+                if (take && v != 0) {
+                    if (use_smem) atomicAdd((unsigned long long*)&s_tab[e * q.R + c], (unsigned long long)v);
+                    else atomicAdd((unsigned long long*)&q.used[(size_t)e * q.R + c], (unsigned long long)v);
+                }
+                if (c == 0 && (rmask & ~q.used_mask[e])) atomicOr(&q.used_mask[e], rmask);
+            }
+        }
+    }
+    if (use_smem) {
+        __syncthreads();
+        for (int x = tid; x < q.E * q.R; x += blockDim.x)
+            if (s_tab[x] != 0) atomicAdd((unsigned long long*)&q.used[x], (unsigned long long)s_tab[x]);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_quota_aggregate(DevQuota q) {
+    __shared__ long long s_min[16][QR], s_used[16][QR], s_over[16][QR];
+    __shared__ unsigned s_m[3];
+    __shared__ long long a_min[QR], a_used[QR], a_over[QR];
+    const int tid = threadIdx.x, c = tid & 15, j = tid >> 4;
+    if (tid < 3) s_m[tid] = 0;
+    __syncthreads();
+    long long mn = 0, us = 0, ov = 0;
+    unsigned mm = 0, um = 0, om = 0;
+    for (int ns = j; ns < q.NS; ns += 16) {
+        const int e = q.ns_quota[ns];
+        if (e < 0) continue;
+        const bool has_min = (q.min_mask[e] & NOSPLAN_QUOTA_NONNIL) != 0;
+        if (c < q.R) {
+            const long long m = has_min ? q.qmin[(size_t)e * q.R + c] : 0, u = q.used[(size_t)e * q.R + c];
+            mn += m; us += u;
+            ov += max(0ll, m - u);                          // SubtractNonNegative, then Sum (:145-152)
+        }
+        if (c == 0) {
+            const unsigned mk = has_min ? (q.min_mask[e] & SCALAR_BITS) : 0;
+            mm |= mk; um |= q.used_mask[e]; om |= mk | q.used_mask[e];
+        }
+    }
+    s_min[j][c] = mn; s_used[j][c] = us; s_over[j][c] = ov;
+    if (c == 0) { atomicOr(&s_m[0], mm); atomicOr(&s_m[1], um); atomicOr(&s_m[2], om); }
+    __syncthreads();
+    if (tid < QR) {
+        long long a = 0, b = 0, d = 0;
+        for (int k = 0; k < 16; ++k) { a += s_min[k][tid]; b += s_used[k][tid]; d += s_over[k][tid]; }
+        a_min[tid] = a; a_used[tid] = b; a_over[tid] = d;
+        if (tid < q.R) { q.agg_min[tid] = a; q.agg_used[tid] = b; q.agg_over[tid] = d; }
+    }
+    if (tid < 3) q.agg_masks[tid] = s_m[tid];
+    __syncthreads();
+    const unsigned omask = s_m[2];
+    for (int x = tid; x < q.E * q.R; x += blockDim.x) {     // GetGuaranteedOverquotas of every quota (:81-119)
+        const int e = x / q.R, cc = x - e * q.R;
+        const bool has_min = (q.min_mask[e] & NOSPLAN_QUOTA_NONNIL) != 0;
+        const bool in_min = has_min && (cc < 4 || (q.min_mask[e] >> cc & 1));
+        double pct = 0.0;
+        if (in_min && a_min[cc] > 0) pct = __ddiv_rn(approx_f64(cc, q.qmin[x]), approx_f64(cc, a_min[cc]));
+        const bool in_res = cc < 4 || (omask >> cc & 1);
+        q.guaranteed[x] = in_res ? go_int64(floor(__dmul_rn((double)a_over[cc], pct))) : 0;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_quota_prefilter(DevQuota q) {
+    const int tid = threadIdx.x, c = tid & 15, sub = (tid >> 4) & 1;
+    const unsigned segmask = 0xffffu << (16 * sub);
+    const int i = blockIdx.x * (blockDim.x / 16) + (tid >> 4);
+    if (i >= q.Pp) return;
+    const int ns = q.p_ns[i];
+    const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+    uint32_t rmask;
+    const long long v = pod_request16(q, q.p_req, q.p_mask, i, c, segmask, rmask);
+    uint8_t code = NOSPLAN_PREFILTER_SUCCESS;
+    if (e >= 0) {
+        // sumGreaterThan (:319-339): cpu and memory always, scalars only if present in y
+        bool over_max = false, over_min = false;
+        if (c < q.R && c != 2 && c != 3) {
+            const bool in_max = c < 2 || (q.max_mask[e] >> c & 1);
+            over_max = in_max && v + q.used[(size_t)e * q.R + c] > q.qmax[(size_t)e * q.R + c];
+            const bool in_min = c < 2 || (q.agg_masks[0] >> c & 1);
+            over_min = in_min && q.agg_used[c] + v > q.agg_min[c];
+        }
+        const unsigned bm = __ballot_sync(segmask, over_max) & segmask, bn = __ballot_sync(segmask, over_min) & segmask;
+        if (q.max_enforced[e] && bm) code = NOSPLAN_PREFILTER_OVER_MAX;
+        else if (bn) code = NOSPLAN_PREFILTER_OVER_MIN;
+    }
+    if (c == 0) q.prefilter[i] = code;
+}
+
+// ---------------------------------------------------------------- operator labelling
+__global__ void __launch_bounds__(256) k_label_keys(DevQuota q, int pass) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= q.Pr) return;
+    if (pass == 0) {                                       // least significant key: priority (biased to unsigned)
+        q.key_a[i] = (unsigned long long)((long long)q.r_prio[i] - (long long)INT_MIN);
+        q.val_a[i] = i;
+    }
+}
+__global__ void __launch_bounds__(256) k_label_rekey(DevQuota q, const int32_t* vals, unsigned long long* keys, int pass) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= q.Pr) return;
+    const int i = vals[x];
+    if (pass == 1) keys[x] = (unsigned long long)q.r_ts[i] ^ 0x8000000000000000ull;      // creationTimestamp
+    else {                                                                                // quota row; no quota -> sorted last
+        const int ns = q.r_ns[i];
+        const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+        keys[x] = e < 0 ? (unsigned long long)q.E : (unsigned long long)e;
+        if (e >= 0) atomicAdd(&q.seg_count[e], 1); else q.over_quota[i] = 0;
+    }
+}
+__global__ void k_label_offsets(DevQuota q) {                  // exclusive scan of the per-quota counts (single thread block)
+    __shared__ int s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < q.E; base += blockDim.x) {
+        const int e = base + threadIdx.x;
+        const int cnt = e < q.E ? q.seg_count[e] : 0;
+        __shared__ int s[256];
+        s[threadIdx.x] = cnt;
+        __syncthreads();
+        for (int o = 1; o < (int)blockDim.x; o <<= 1) {
+            const int v = threadIdx.x >= o ? s[threadIdx.x - o] : 0;
+            __syncthreads();
+            s[threadIdx.x] += v;
+            __syncthreads();
+        }
+        if (e < q.E) q.seg_off[e] = s_carry + s[threadIdx.x] - cnt;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) s_carry += s[threadIdx.x];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) q.seg_off[q.E] = s_carry;
+}
+
+__device__ __forceinline__ long long quota_req_scalar(const DevQuota& q, int i, int c) {   // one column, thread-serial
+    if (c != q.gm) return q.r_req[(size_t)i * q.R + c];
+    long long g = 0;
+    for (int k = 0; k < q.R; ++k) if (k != q.gm) g += q.coeff[k] * q.r_req[(size_t)i * q.R + k];
+    return g;
+}
+// the comparator's 3rd and 4th keys (elasticquota.go:93-103) for pods that tie on (creationTimestamp, priority)
+__device__ bool tie_less(const DevQuota& q, int a, int b, bool* ambiguous) {
+    bool equal = true, a_le_b = true, b_le_a = true;
+    for (int c = 0; c < q.R; ++c) {
+        const long long x = quota_req_scalar(q, a, c), y = quota_req_scalar(q, b, c);
+        equal &= x == y; a_le_b &= x <= y; b_le_a &= y <= x;
+    }
+    if (!equal) { if (a_le_b == b_le_a) *ambiguous = true; return a_le_b; }
+    return q.r_rank[a] < q.r_rank[b];
+}
+// one thread per tie group (same quota, creationTimestamp, priority): stable insertion sort with the comparator
+__global__ void __launch_bounds__(256) k_label_ties(DevQuota q, int32_t* order) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n_in_quota = q.seg_off[q.E];                     // pods without a quota sort last and are not touched
+    if (x >= n_in_quota) return;
+    auto same = [&](int u, int v) {
+        const int a = order[u], b = order[v];
+        return q.ns_quota[q.r_ns[a]] == q.ns_quota[q.r_ns[b]] && q.r_ts[a] == q.r_ts[b] && q.r_prio[a] == q.r_prio[b];
+    };
+    if (x > 0 && same(x - 1, x)) return;                       // not a group leader
+    int end = x + 1;
+    while (end < n_in_quota && same(x, end)) ++end;
+    if (end - x < 2) return;
+    bool amb = false;
+    for (int i = x + 1; i < end; ++i) {
+        const int v = order[i];
+        int j = i;
+        while (j > x && tie_less(q, v, order[j - 1], &amb)) { order[j] = order[j - 1]; --j; }
+        order[j] = v;
+    }
+    for (int i = x; i < end && !amb; ++i)                      // the partial order must be a chain inside the group
+        for (int j = i + 1; j < end; ++j) { bool t = false; tie_less(q, order[i], order[j], &t); amb |= t; }
+    if (amb) *q.ambiguous = 1;
+}
+// one block per quota: running sum of the requests in order, in-quota iff used <= min on every key of Min
+__global__ void __launch_bounds__(256) k_label_scan(DevQuota q, const int32_t* order) {
+    __shared__ long long s_warp[8][QR];
+    __shared__ long long s_carry[QR];
+    const int e = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int beg = q.seg_off[e], end = q.seg_off[e + 1];
+    const unsigned mm = q.min_mask[e];
+    if (tid < QR) s_carry[tid] = 0;
+    __syncthreads();
+    for (int base = beg; base < end; base += blockDim.x) {
+        const int x = base + tid;
+        const int i = x < end ? order[x] : -1;
+        long long v[QR];
+#pragma unroll
+        for (int c = 0; c < QR; ++c) v[c] = (i >= 0 && c < q.R) ? quota_req_scalar(q, i, c) : 0;
+#pragma unroll
+        for (int c = 0; c < QR; ++c) {                          // inclusive scan across the warp, per column
+            if (c >= q.R) break;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long t = __shfl_up_sync(0xffffffffu, v[c], o);
+                if (lane >= o) v[c] += t;
+            }
+            if (lane == 31) s_warp[warp][c] = v[c];
+        }
+        __syncthreads();
+        bool in_quota = true;
+#pragma unroll
+        for (int c = 0; c < QR; ++c) {
+            long long pre = s_carry[c];
+            for (int w = 0; w < warp; ++w) pre += s_warp[w][c];
+            v[c] += pre;
+            if (c < q.R && (mm >> c & 1) && v[c] > q.qmin[(size_t)e * q.R + c]) in_quota = false;
+        }
+        if (i >= 0) q.over_quota[i] = in_quota ? 0 : 1;
+        __syncthreads();
+        if (tid == blockDim.x - 1) {
+#pragma unroll
+            for (int c = 0; c < QR; ++c) s_carry[c] = v[c];
+        }
+        __syncthreads();
+    }
+    if (tid < q.R) q.operator_used[(size_t)e * q.R + tid] = (mm >> tid & 1) ? s_carry[tid] : 0;
+}
+
+}  // namespace nsp
+
+using namespace nsp;
+
+// host side --------------------------------------------------------------------------------------------------
+struct nosplan_quota_ctx {
+    unsigned char* d = nullptr; size_t d_cap = 0;
+    unsigned char* hs = nullptr; size_t hs_cap = 0;
+};
+
+extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                            const nosplan_quotas* qs, const nosplan_quota_pods* running,
+                                            const nosplan_quota_pods* pending, nosplan_quota_out* out, float* ms_h2d, float* ms_k,
+                                            float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes) {
+    auto fail = [&](int code, const char* msg, const char* detail = "") { if (err) *err = std::string(msg) + detail; return code; };
+#define QCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(NOSPLAN_E_CUDA, #call ": ", cudaGetErrorString(e_)); } while (0)
+    if (!qs || !out) return fail(NOSPLAN_E_INVALID, "null quotas or out");
+    const int E = qs->n_quotas, R = qs->n_res, NS = qs->n_namespaces;
+    const int Pr = running ? running->n_pods : 0, Pp = pending ? pending->n_pods : 0;
+    if (R < 4 || R > QR) return fail(NOSPLAN_E_LIMIT, "n_res must be in [4, NOSPLAN_QUOTA_MAX_RES]");
+    if (E < 0 || NS < 0 || Pr < 0 || Pp < 0) return fail(NOSPLAN_E_INVALID, "negative size");
+    if (qs->gpu_memory_col >= R || (qs->gpu_memory_col >= 0 && qs->gpu_memory_col < 4)) return fail(NOSPLAN_E_INVALID, "gpu_memory_col out of range");
+    for (int ns = 0; ns < NS; ++ns) if (qs->ns_quota[ns] >= E) return fail(NOSPLAN_E_INVALID, "ns_quota out of range");
+    const bool want_label = (out->over_quota || out->operator_used || out->ambiguous_order) && Pr > 0 && E > 0;
+    if (want_label && (!running->priority || !running->creation_ts || !running->name_rank))
+        return fail(NOSPLAN_E_INVALID, "operator labelling needs priority, creation_ts and name_rank of the running pods");
+    QCU(cudaSetDevice(device));
+
+    // ---- layout
+    size_t o = 0;
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    auto put = [&](size_t bytes) { size_t at = o; o = al(o + bytes); return at; };
+    const size_t ER = (size_t)E * R;
+    const size_t o_nsq = put(4 * (size_t)NS), o_min = put(8 * ER), o_max = put(8 * ER), o_uin = put(8 * ER),
+                 o_mm = put(4 * (size_t)E), o_xm = put(4 * (size_t)E), o_um = put(4 * (size_t)E), o_enf = put((size_t)E),
+                 o_rns = put(4 * (size_t)Pr), o_rreq = put(8 * (size_t)Pr * R), o_rmask = put(4 * (size_t)Pr),
+                 o_rprio = put(4 * (size_t)Pr), o_rts = put(8 * (size_t)Pr), o_rrank = put(4 * (size_t)Pr),
+                 o_pns = put(4 * (size_t)Pp), o_preq = put(8 * (size_t)Pp * R), o_pmask = put(4 * (size_t)Pp);
+    const size_t upload_end = o;
+    // outputs (contiguous, one D2H)
+    const size_t o_used = put(8 * ER), o_umask = put(4 * (size_t)E), o_amin = put(8 * QR), o_aused = put(8 * QR), o_aover = put(8 * QR),
+                 o_amask = put(16), o_guar = put(8 * ER), o_pref = put((size_t)Pp), o_over = put((size_t)Pr), o_opused = put(8 * ER),
+                 o_amb = put(16);
+    const size_t out_end = o;
+    const size_t o_keya = put(8 * (size_t)Pr), o_keyb = put(8 * (size_t)Pr), o_vala = put(4 * (size_t)Pr), o_valb = put(4 * (size_t)Pr),
+                 o_segc = put(4 * ((size_t)E + 1)), o_sego = put(4 * ((size_t)E + 2));
+    size_t cub_bytes = 0;
+    if (want_label) {
+        cub::DoubleBuffer<unsigned long long> dk(nullptr, nullptr); cub::DoubleBuffer<int32_t> dv(nullptr, nullptr);
+        QCU(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk, dv, Pr, 0, 64, st));
+    }
+    const size_t o_cub = put(cub_bytes + 256);
+    const size_t total = o;
+    if (total > ctx->d_cap) {
+        if (ctx->d) QCU(cudaFree(ctx->d));
+        ctx->d = nullptr; ctx->d_cap = 0;
+        QCU(cudaMalloc(&ctx->d, total + total / 4 + (1 << 20)));
+        ctx->d_cap = total + total / 4 + (1 << 20);
+    }
+    const size_t stage_need = std::max(upload_end, out_end - upload_end);
+    if (stage_need > ctx->hs_cap) {
+        if (ctx->hs) QCU(cudaFreeHost(ctx->hs));
+        ctx->hs = nullptr; ctx->hs_cap = 0;
+        QCU(cudaMallocHost(&ctx->hs, stage_need + stage_need / 4 + (1 << 20)));
+        ctx->hs_cap = stage_need + stage_need / 4 + (1 << 20);
+    }
+    unsigned char* S = ctx->hs; unsigned char* A = ctx->d;
+    auto cp = [&](size_t at, const void* src, size_t bytes) { if (bytes) { if (src) std::memcpy(S + at, src, bytes); else std::memset(S + at, 0, bytes); } };
+    cp(o_nsq, qs->ns_quota, 4 * (size_t)NS); cp(o_min, qs->min, 8 * ER); cp(o_max, qs->max, 8 * ER); cp(o_uin, qs->used_init, 8 * ER);
+    cp(o_mm, qs->min_mask, 4 * (size_t)E); cp(o_xm, qs->max_mask, 4 * (size_t)E); cp(o_um, qs->used_mask, 4 * (size_t)E);
+    cp(o_enf, qs->max_enforced, (size_t)E);
+    for (int e = 0; e < E; ++e) reinterpret_cast<uint32_t*>(S + o_um)[e] &= SCALAR_BITS;    // key set of the scalars only
+    if (Pr) {
+        cp(o_rns, running->ns, 4 * (size_t)Pr); cp(o_rreq, running->request, 8 * (size_t)Pr * R);
+        cp(o_rmask, running->request_mask, 4 * (size_t)Pr); cp(o_rprio, running->priority, 4 * (size_t)Pr);
+        cp(o_rts, running->creation_ts, 8 * (size_t)Pr); cp(o_rrank, running->name_rank, 4 * (size_t)Pr);
+    }
+    if (Pp) { cp(o_pns, pending->ns, 4 * (size_t)Pp); cp(o_preq, pending->request, 8 * (size_t)Pp * R); cp(o_pmask, pending->request_mask, 4 * (size_t)Pp); }
+
+    cudaEvent_t ev[4];
+    for (auto& e : ev) QCU(cudaEventCreate(&e));
+    QCU(cudaEventRecord(ev[0], st));
+    QCU(cudaMemcpyAsync(A, S, upload_end, cudaMemcpyHostToDevice, st));
+    QCU(cudaMemsetAsync(A + upload_end, 0, total - upload_end, st));
+    QCU(cudaEventRecord(ev[1], st));
+
+    DevQuota q; std::memset(&q, 0, sizeof q);
+    q.E = E; q.R = R; q.NS = NS; q.gm = qs->gpu_memory_col; q.Pr = Pr; q.Pp = Pp;
+    q.ns_quota = (const int32_t*)(A + o_nsq); q.qmin = (const long long*)(A + o_min); q.qmax = (const long long*)(A + o_max);
+    q.used_init = (const long long*)(A + o_uin); q.min_mask = (const uint32_t*)(A + o_mm); q.max_mask = (const uint32_t*)(A + o_xm);
+    q.used_mask_in = (const uint32_t*)(A + o_um); q.max_enforced = (const uint8_t*)(A + o_enf);
+    for (int c = 0; c < QR; ++c) q.coeff[c] = (c < R && qs->gpu_memory_coeff) ? qs->gpu_memory_coeff[c] : 0;
+    q.r_ns = (const int32_t*)(A + o_rns); q.r_req = (const long long*)(A + o_rreq);
+    q.r_mask = (running && running->request_mask) ? (const uint32_t*)(A + o_rmask) : nullptr;
+    q.r_prio = (const int32_t*)(A + o_rprio); q.r_ts = (const long long*)(A + o_rts); q.r_rank = (const int32_t*)(A + o_rrank);
+    q.p_ns = (const int32_t*)(A + o_pns); q.p_req = (const long long*)(A + o_preq);
+    q.p_mask = (pending && pending->request_mask) ? (const uint32_t*)(A + o_pmask) : nullptr;
+    q.used = (long long*)(A + o_used); q.used_mask = (uint32_t*)(A + o_umask);
+    q.agg_min = (long long*)(A + o_amin); q.agg_used = (long long*)(A + o_aused); q.agg_over = (long long*)(A + o_aover);
+    q.agg_masks = (uint32_t*)(A + o_amask); q.guaranteed = (long long*)(A + o_guar); q.prefilter = (uint8_t*)(A + o_pref);
+    q.over_quota = (uint8_t*)(A + o_over); q.operator_used = (long long*)(A + o_opused); q.ambiguous = (int32_t*)(A + o_amb);
+    q.key_a = (unsigned long long*)(A + o_keya); q.key_b = (unsigned long long*)(A + o_keyb);
+    q.val_a = (int32_t*)(A + o_vala); q.val_b = (int32_t*)(A + o_valb);
+    q.seg_count = (int32_t*)(A + o_segc); q.seg_off = (int32_t*)(A + o_sego);
+
+    int n_launch = 0;
+    // Used starts from used_init (scalar key set from used_mask)
+    if (ER) QCU(cudaMemcpyAsync(q.used, q.used_init, 8 * ER, cudaMemcpyDeviceToDevice, st));
+    if (E) QCU(cudaMemcpyAsync(q.used_mask, q.used_mask_in, 4 * (size_t)E, cudaMemcpyDeviceToDevice, st));
+    if (Pr && E) {
+        const size_t tab = 8 * ER;
+        const int use_smem = tab <= 96 * 1024;
+        QCU(cudaFuncSetAttribute(k_quota_used, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        int blocks = (Pr + 15) / 16;
+        if (blocks > 148 * 4) blocks = 148 * 4;
+        k_quota_used<<<blocks, 256, use_smem ? tab : 0, st>>>(q, use_smem);
+        ++n_launch;
+    }
+    k_quota_aggregate<<<1, 256, 0, st>>>(q);
+    ++n_launch;
+    if (Pp) { k_quota_prefilter<<<(Pp + 15) / 16, 256, 0, st>>>(q); ++n_launch; }
+    if (want_label) {
+        // stable LSD radix sort: priority, then creationTimestamp, then quota row
+        const int gb = (Pr + 255) / 256;
+        k_label_keys<<<gb, 256, 0, st>>>(q, 0);
+        cub::DoubleBuffer<unsigned long long> dk(q.key_a, q.key_b); cub::DoubleBuffer<int32_t> dv(q.val_a, q.val_b);
+        size_t tb = cub_bytes;
+        QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, 32, st));
+        k_label_rekey<<<gb, 256, 0, st>>>(q, dv.Current(), dk.Current(), 1);
+        QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, 64, st));
+        k_label_rekey<<<gb, 256, 0, st>>>(q, dv.Current(), dk.Current(), 2);
+        int ebits = 1; while ((1ll << ebits) <= E) ++ebits;
+        QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, ebits, st));
+        k_label_offsets<<<1, 256, 0, st>>>(q);
+        k_label_ties<<<gb, 256, 0, st>>>(q, dv.Current());
+        k_label_scan<<<E, 256, 0, st>>>(q, dv.Current());
+        n_launch += 9;
+    }
+    QCU(cudaGetLastError());
+    QCU(cudaEventRecord(ev[2], st));
+    QCU(cudaMemcpyAsync(S, A + upload_end, out_end - upload_end, cudaMemcpyDeviceToHost, st));
+    QCU(cudaEventRecord(ev[3], st));
+    QCU(cudaStreamSynchronize(st));
+    auto back = [&](void* dst, size_t at, size_t bytes) { if (dst && bytes) std::memcpy(dst, S + (at - upload_end), bytes); };
+    back(out->used, o_used, 8 * ER); back(out->used_mask, o_umask, 4 * (size_t)E);
+    back(out->agg_min, o_amin, 8 * (size_t)R); back(out->agg_used, o_aused, 8 * (size_t)R); back(out->agg_overquota, o_aover, 8 * (size_t)R);
+    back(out->agg_masks, o_amask, 12); back(out->guaranteed, o_guar, 8 * ER); back(out->prefilter, o_pref, (size_t)Pp);
+    if (want_label) { back(out->over_quota, o_over, (size_t)Pr); back(out->operator_used, o_opused, 8 * ER); back(out->ambiguous_order, o_amb, 4); }
+    else {
+        if (out->over_quota && Pr) std::memset(out->over_quota, 0, (size_t)Pr);
+        if (out->operator_used && ER) std::memset(out->operator_used, 0, 8 * ER);
+        if (out->ambiguous_order) *out->ambiguous_order = 0;
+    }
+    if (ms_h2d) cudaEventElapsedTime(ms_h2d, ev[0], ev[1]);
+    if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
+    if (ms_d2h) cudaEventElapsedTime(ms_d2h, ev[2], ev[3]);
+    for (auto& e : ev) cudaEventDestroy(e);
+    if (launches) *launches = n_launch;
+    if (h2d_bytes) *h2d_bytes = (long long)upload_end;
+    if (d2h_bytes) *d2h_bytes = (long long)(out_end - upload_end);
+    return NOSPLAN_OK;
+#undef QCU
+}
+
+extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx) {
+    if (!ctx) return;
+    if (ctx->d) cudaFree(ctx->d);
+    if (ctx->hs) cudaFreeHost(ctx->hs);
+    delete ctx;
+}
+extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new() { return new nosplan_quota_ctx(); }

@@ -204,3 +204,48 @@ def to_logical(snap: pk.PackedSnapshot, pods: pk.PackedPods):
             c[cols[int(pods.scalar_col[e])]] = int(pods.scalar_qty[e])
         lpods.append({"namespace": ns, "name": nm, "priority": int(pods.priority[i]), "containers": [c]})
     return nodes, lpods
+
+
+def quota_state(n_quotas: int, n_running: int, n_pending: int, seed: int, nvidia_gpu_memory_gb: int = 32, zipf_s: float = 1.1):
+    """BASELINE config #4 recipe in packed form: n_quotas ElasticQuotas (10 % composite over 2-4 namespaces), Min of
+    cpu U{8..256} cores / memory / gpu-memory U{40..640}, Max = 2*Min enforced on half of them; running and pending pods
+    with namespaces ~ Zipf(s), unique creation timestamps, C2 priorities and requests plus nvidia.com/gpu U{0..2}.
+    -> (PackedQuotas, PackedQuotaPods running, PackedQuotaPods pending)"""
+    from . import quota_packing as qp
+    cols = ["cpu", "memory", "ephemeral-storage", "pods", "nos.nebuly.com/gpu-memory", "nvidia.com/gpu"]
+    R, gm, gc = len(cols), 4, 5
+    E = n_quotas
+    composite = _uniform(seed, E, 1) < 0.10
+    n_ns_of = np.where(composite, _randint(seed, E, 2, 2, 4), 1)
+    ns_first = np.concatenate([[0], np.cumsum(n_ns_of)])[:-1]
+    NS = int(n_ns_of.sum()) + 1                                   # + one namespace without quota
+    ns_quota = np.full(NS, -1, np.int32)
+    for e in range(E):
+        ns_quota[ns_first[e]:ns_first[e] + n_ns_of[e]] = e
+    mn = np.zeros((E, R), np.int64)
+    mn[:, 0] = _randint(seed, E, 3, 8, 256) * 1000
+    mn[:, 1] = _randint(seed, E, 4, 16, 2048) << 30
+    mn[:, gm] = _randint(seed, E, 5, 40, 640)
+    mx = 2 * mn
+    enforced = (_uniform(seed, E, 6) < 0.5).astype(np.uint8)
+    bits = np.uint32(qp.NONNIL | 0b11 | (1 << gm))
+    pq = qp.PackedQuotas([f"eq-{e}" for e in range(E)], [f"ns-{i}" for i in range(NS)], cols, gm, ns_quota, mn, mx,
+                         np.zeros((E, R), np.int64), np.full(E, bits, np.uint32), np.full(E, bits, np.uint32),
+                         np.full(E, qp.NONNIL, np.uint32), enforced, np.array([0, 0, 0, 0, 0, nvidia_gpu_memory_gb], np.int64))
+
+    w = 1.0 / np.arange(1, NS + 1, dtype=np.float64) ** zipf_s
+    cdf = np.cumsum(w / w.sum())
+    perm = np.argsort(splitmix64(seed, NS, 7))                    # which namespace is the popular one is random
+
+    def pods(P, stream, t0):
+        ns = perm[np.searchsorted(cdf, _uniform(seed, P, stream), side="right").clip(0, NS - 1)].astype(np.int32)
+        req = np.zeros((P, R), np.int64)
+        req[:, 0] = _randint(seed, P, stream + 1, 100, 4000)
+        req[:, 1] = _randint(seed, P, stream + 2, 1, 32) << 30
+        req[:, gc] = _randint(seed, P, stream + 3, 0, 2)
+        prio = np.array([0, 100, 1000], np.int32)[_choice(seed, P, stream + 4, [.7, .2, .1])]
+        ts = t0 + np.argsort(splitmix64(seed, P, stream + 5)).astype(np.int64)          # unique timestamps
+        return qp.PackedQuotaPods([f"ns/pod-{i}" for i in range(P)], ns, req, np.full(P, 1 << gc, np.uint32), prio, ts,
+                                  np.arange(P, dtype=np.int32))
+
+    return pq, pods(n_running, 20, 1_700_000_000), pods(n_pending, 40, 1_800_000_000)

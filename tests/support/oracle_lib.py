@@ -55,3 +55,24 @@ def sort_pods(snap, pods):
     if rc != 0:
         raise RuntimeError(f"nos_oracle_sort_pods -> {rc}")
     return order[:pods.n_pods]
+
+
+def quota(pq, running=None, pending=None):
+    """CPU quota oracle on packed quota structs -> dict of arrays (see nos_b200.quota_packing.QuotaResult.trimmed)."""
+    from nos_b200 import quota_packing as qp
+    L = lib()
+    L.nos_oracle_quota.argtypes = [C.POINTER(qp.CQuotas), C.POINTER(qp.CQuotaPods), C.POINTER(qp.CQuotaPods),
+                                   C.POINTER(qp.CQuotaOut), C.POINTER(C.c_double)]
+    L.nos_oracle_quota.restype = C.c_int
+    cq, k1 = qp.c_quotas(pq)
+    cr, k2 = qp.c_quota_pods(running)
+    cp, k3 = qp.c_quota_pods(pending)
+    res = qp.QuotaResult(pq, running.n_pods if running else 0, pending.n_pods if pending else 0)
+    out = res.c_struct()
+    sec = C.c_double()
+    rc = L.nos_oracle_quota(C.byref(cq), C.byref(cr), C.byref(cp), C.byref(out), C.byref(sec))
+    if rc != 0:
+        raise RuntimeError(f"nos_oracle_quota -> {rc}")
+    d = res.trimmed()
+    d["seconds"] = sec.value
+    return d

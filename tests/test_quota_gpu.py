@@ -1,0 +1,98 @@
+"""Parity of the CUDA quota engine (nosplan_quota_recompute through the C-ABI) with the oracle: int64 fields bit-exact,
+the float64 guaranteed-overquota path bit-exact too (same IEEE operations in the same order)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from nos_b200 import capi, quota_packing as qp, synth
+from support import oracle_lib as ol
+from support import quotacases as qc
+
+pytestmark = pytest.mark.gpu
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "quota.json")))
+FIELDS = ("used", "used_mask", "agg_min", "agg_used", "agg_overquota", "agg_masks", "guaranteed", "prefilter", "over_quota",
+          "operator_used", "ambiguous_order")
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import __graft_entry__ as g
+    g.build()
+    e = capi.Engine(0)
+    yield e
+    e.close()
+
+
+def compare(got, exp, what):
+    for k in FIELDS:
+        assert np.array_equal(got[k], exp[k]), f"{what}: {k}\n{got[k]}\n{exp[k]}"
+
+
+def dense(pq, d):
+    return np.array([d.get(c, 0) for c in pq.columns], np.int64)
+
+
+def test_golden_guaranteed_overquotas(eng):
+    for c in GOLD["guaranteed_overquotas"][1:]:
+        quotas = {k: {"namespaces": [k], **v} for k, v in c["quotas"].items()}
+        pq, _ = qp.pack_quotas(quotas, [], 16)
+        r, _ = eng.quota_recompute(pq)
+        assert np.array_equal(r["guaranteed"][pq.names.index(c["quota"])], dense(pq, c["expected"])), c["name"]
+
+
+def test_golden_aggregated_and_reserve(eng):
+    for c in GOLD["aggregated_overquotas"][1:]:
+        quotas = {k: {"namespaces": [k], **v} for k, v in c["quotas"].items()}
+        pq, _ = qp.pack_quotas(quotas, [], 16)
+        assert np.array_equal(eng.quota_recompute(pq)[0]["agg_overquota"], dense(pq, c["expected"])), c["name"]
+    for c in GOLD["reserve"]:
+        quotas = {"eq": {"namespaces": ["ns"], "min": {}, "used": dict(c["used"])}}
+        pods = [{"namespace": "ns", "name": f"p{i}", "request": dict(p)} for i, p in enumerate(c["pods"])]
+        pq, (run,) = qp.pack_quotas(quotas, [pods], c["gpu_memory_gb"])
+        assert np.array_equal(eng.quota_recompute(pq, run)[0]["used"][0], dense(pq, c["expected"]))
+
+
+def test_golden_prefilter(eng):
+    for c in GOLD["prefilter"]:
+        pods = [{"namespace": p["namespace"], "name": f"p{i}", "request": {"memory": p["memory"], "cpu": p["cpu"], "nvidia.com/gpu": p["gpu"]}}
+                for i, p in enumerate(c["pods"])]
+        pq, (pend,) = qp.pack_quotas(c["quotas"], [pods], c["gpu_memory_gb"])
+        r, _ = eng.quota_recompute(pq, None, pend)
+        assert [int(x != 0) for x in r["prefilter"]] == c["expected"], c["name"]
+
+
+@pytest.mark.parametrize("block", range(4))
+def test_random_vs_oracle(eng, block):
+    for seed in range(block * 200, (block + 1) * 200):
+        quotas, running, pending, gb = qc.rand_quota_case(seed, unique_ts=(seed % 3 != 0))
+        pq, (run, pend) = qp.pack_quotas(quotas, [running, pending], gb)
+        got, _ = eng.quota_recompute(pq, run, pend)
+        exp = ol.quota(pq, run, pend)
+        compare(got, exp, f"seed {seed}")
+
+
+def test_config_c4_full_size(eng):
+    """BASELINE config #4: 500 ElasticQuotas / namespaces, 100,000 pods."""
+    pq, run, pend = synth.quota_state(500, 100_000, 10_000, seed=0xC4)
+    got, st = eng.quota_recompute(pq, run, pend)
+    exp = ol.quota(pq, run, pend)
+    compare(got, exp, "C4")
+    assert got["ambiguous_order"] == 0
+    # size-independent properties: used is a checksum of the requests; aggregates are sums of rows weighted by namespaces
+    e_of = pq.ns_quota[run.ns]
+    assert got["used"][:, 0].sum() == run.request[e_of >= 0, 0].sum()
+    w = np.bincount(pq.ns_quota[pq.ns_quota >= 0], minlength=500)
+    assert np.array_equal(got["agg_min"], (pq.min * w[:, None]).sum(0))
+    assert (got["guaranteed"] >= 0).all() and (got["guaranteed"].sum(0) <= got["agg_overquota"] * w.max()).all()
+    assert 0 < got["over_quota"].sum() < 100_000 and (got["prefilter"] <= 2).all()
+
+
+def test_zero_sizes(eng):
+    pq, run, pend = synth.quota_state(3, 0, 0, seed=1)
+    got, _ = eng.quota_recompute(pq, run, pend)
+    compare(got, ol.quota(pq, run, pend), "no pods")
+    pq, (run,) = qp.pack_quotas({}, [[{"namespace": "a", "name": "p", "request": {"cpu": 1}}]], 16)
+    got, _ = eng.quota_recompute(pq, run)
+    compare(got, ol.quota(pq, run), "no quotas")
