@@ -229,6 +229,31 @@ typedef struct nosplan_quota_out {     /* every pointer may be NULL = not wanted
 int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
                             const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats);
 
+/* First pass of preemptor.SelectVictimsOnNode (capacity_scheduling.go:511-596) for ONE preemptor over MANY nodes: which
+ * pods of each node become potential victims under the quota predicates.  Upstream fans SelectVictimsOnNode out per
+ * node, each on its own clone of the quota snapshot; removing a victim un-reserves its request in that clone
+ * (RemovePod extension :311-321), so the pods of one node are evaluated in order and the nodes independently.
+ * Pods are grouped by node (node_ptr CSR) and, inside a node, given in the order of the reference's sort (:516, least
+ * important first).  quotas->used_init / used_mask hold the CURRENT Used of every quota (e.g. nosplan_quota_out.used).
+ * The Filter re-check and the reprieve loop (:598-673) stay on the caller's side. */
+typedef struct nosplan_victim_query {
+    int32_t preemptor_ns;              /* namespace id of the preemptor pod */
+    int32_t preemptor_priority;
+    const int64_t* nominated_in_eq;    /* [Rq] PreFilterState.nominatedPodsReqInEQWithPodReq (the pod's own quota request
+                                          included, gpu-memory column already filled) */
+    int32_t n_nodes;
+    const int32_t* node_ptr;           /* [n_nodes+1] */
+    int32_t n_pods;
+    const int32_t* ns;                 /* [n_pods] */
+    const int32_t* priority;           /* [n_pods] */
+    const uint8_t* over_quota;         /* [n_pods] pod carries the label nos.nebuly.com/capacity=over-quota (pkg/util/pod/pod.go:31-36) */
+    const int64_t* request;            /* [n_pods][Rq] plain request (gpu-memory added by the engine) */
+    const uint32_t* request_mask;      /* [n_pods] or NULL */
+} nosplan_victim_query;
+
+int nosplan_quota_victims(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_victim_query* query,
+                          uint8_t* victim /* [n_pods] out: 1 = potential victim */, nosplan_stats* stats);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libnosplan.so")
 EXPORTED_SYMBOLS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_plan",
     "nosplan_upload", "nosplan_run", "nosplan_download", "nosplan_stream",
-    "nosplan_lacking_static", "nosplan_quota_recompute",
+    "nosplan_lacking_static", "nosplan_quota_recompute", "nosplan_quota_victims",
 ]
 STATIC_MAX_KEYS = 16384
 
@@ -155,6 +155,9 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_quota_recompute.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(qp.CQuotaPods), C.POINTER(qp.CQuotaPods),
                                             C.POINTER(qp.CQuotaOut), C.POINTER(CStats)]
     lib.nosplan_quota_recompute.restype = C.c_int
+    from . import victim_packing as vp
+    lib.nosplan_quota_victims.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(vp.CVictimQuery), C.c_void_p, C.POINTER(CStats)]
+    lib.nosplan_quota_victims.restype = C.c_int
     return lib
 
 
@@ -235,6 +238,18 @@ class Engine:
 
     def stream(self) -> int:
         return int(self.lib.nosplan_stream(self.h) or 0)
+
+    def quota_victims(self, pq, query):
+        """nosplan_quota_victims -> (victim flags [n_pods] uint8, stats dict).  pq.used_init / used_mask = current Used."""
+        from . import quota_packing as qp
+        cq, k1 = qp.c_quotas(pq)
+        cv, k2 = query.c_struct()
+        victim = np.zeros(max(1, query.n_pods), np.uint8)
+        st = CStats()
+        rc = self.lib.nosplan_quota_victims(self.h, C.byref(cq), C.byref(cv), victim.ctypes.data, C.byref(st))
+        self._check(rc, "nosplan_quota_victims")
+        del k1, k2
+        return victim[:query.n_pods], st.as_dict()
 
     def quota_recompute(self, pq, running=None, pending=None):
         """nosplan_quota_recompute -> (dict of arrays as QuotaResult.trimmed(), stats dict)"""

@@ -31,6 +31,9 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
                                             float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes);
 extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx);
 extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new();
+extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                          const nosplan_quotas* qs, const nosplan_victim_query* vq, uint8_t* victim,
+                                          float* ms_k, int* launches);
 
 struct nosplan {
     int device = -1;
@@ -519,6 +522,19 @@ int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const no
         std::memset(stats, 0, sizeof *stats);
         stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
         stats->h2d_bytes = hb; stats->d2h_bytes = db;
+    }
+    return rc;
+}
+
+int nosplan_quota_victims(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_victim_query* query, uint8_t* victim,
+                          nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    float ms = 0; int launches = 0;
+    const int rc = nosplan_quota_victims_impl(h->device, h->stream, h->qctx, &h->err, quotas, query, victim, &ms, &launches);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_kernels = ms; stats->kernel_launches = launches;
     }
     return rc;
 }

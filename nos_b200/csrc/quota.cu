@@ -313,10 +313,7 @@ __global__ void __launch_bounds__(256) k_label_scan(DevQuota q, const int32_t* o
 using namespace nsp;
 
 // host side --------------------------------------------------------------------------------------------------
-struct nosplan_quota_ctx {
-    unsigned char* d = nullptr; size_t d_cap = 0;
-    unsigned char* hs = nullptr; size_t hs_cap = 0;
-};
+#include "quota_ctx.cuh"
 
 extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                             const nosplan_quotas* qs, const nosplan_quota_pods* running,
@@ -361,19 +358,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     }
     const size_t o_cub = put(cub_bytes + 256);
     const size_t total = o;
-    if (total > ctx->d_cap) {
-        if (ctx->d) QCU(cudaFree(ctx->d));
-        ctx->d = nullptr; ctx->d_cap = 0;
-        QCU(cudaMalloc(&ctx->d, total + total / 4 + (1 << 20)));
-        ctx->d_cap = total + total / 4 + (1 << 20);
-    }
-    const size_t stage_need = std::max(upload_end, out_end - upload_end);
-    if (stage_need > ctx->hs_cap) {
-        if (ctx->hs) QCU(cudaFreeHost(ctx->hs));
-        ctx->hs = nullptr; ctx->hs_cap = 0;
-        QCU(cudaMallocHost(&ctx->hs, stage_need + stage_need / 4 + (1 << 20)));
-        ctx->hs_cap = stage_need + stage_need / 4 + (1 << 20);
-    }
+    QCU(quota_ctx_ensure(ctx, total, std::max(upload_end, out_end - upload_end)));
     unsigned char* S = ctx->hs; unsigned char* A = ctx->d;
     auto cp = [&](size_t at, const void* src, size_t bytes) { if (bytes) { if (src) std::memcpy(S + at, src, bytes); else std::memset(S + at, 0, bytes); } };
     cp(o_nsq, qs->ns_quota, 4 * (size_t)NS); cp(o_min, qs->min, 8 * ER); cp(o_max, qs->max, 8 * ER); cp(o_uin, qs->used_init, 8 * ER);

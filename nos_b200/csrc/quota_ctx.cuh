@@ -1,0 +1,29 @@
+// Device / pinned-host scratch shared by the quota entry points of one handle (grown on demand, reused across calls).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstddef>
+
+struct nosplan_quota_ctx {
+    unsigned char* d = nullptr; size_t d_cap = 0;
+    unsigned char* hs = nullptr; size_t hs_cap = 0;
+};
+
+// returns cudaSuccess or the failing call's error; buffers are only ever grown
+inline cudaError_t quota_ctx_ensure(nosplan_quota_ctx* ctx, size_t dev_bytes, size_t host_bytes) {
+    cudaError_t e;
+    if (dev_bytes > ctx->d_cap) {
+        if (ctx->d && (e = cudaFree(ctx->d)) != cudaSuccess) return e;
+        ctx->d = nullptr; ctx->d_cap = 0;
+        const size_t cap = dev_bytes + dev_bytes / 4 + (1 << 20);
+        if ((e = cudaMalloc(&ctx->d, cap)) != cudaSuccess) return e;
+        ctx->d_cap = cap;
+    }
+    if (host_bytes > ctx->hs_cap) {
+        if (ctx->hs && (e = cudaFreeHost(ctx->hs)) != cudaSuccess) return e;
+        ctx->hs = nullptr; ctx->hs_cap = 0;
+        const size_t cap = host_bytes + host_bytes / 4 + (1 << 20);
+        if ((e = cudaMallocHost(&ctx->hs, cap)) != cudaSuccess) return e;
+        ctx->hs_cap = cap;
+    }
+    return cudaSuccess;
+}

@@ -252,3 +252,70 @@ def patch_pods_and_compute_used(pods: List[Pod], quota_min: Dict[str, int], quot
         in_quota = _lte_on_keys_of_b(used, quota_min)
         labels.append((pod.key(), not in_quota))
     return {k: v for k, v in used.items() if k in quota_min}, labels
+
+
+# ------------------------------------------------------------------------------------------------------------
+# preemption, first pass of SelectVictimsOnNode (capacity_scheduling.go:511-596): which pods of a node become
+# potential victims.  Every node works on its own clone of the quota snapshot; removing a victim un-reserves its request
+# there (RemovePod extension :311-321 -> deletePodIfPresent), so later pods of the same node see the updated Used.
+# `node_pods` must already be in the order the reference's sort gives (least important first, :516).
+# ------------------------------------------------------------------------------------------------------------
+def clone_infos(infos: ElasticQuotaInfos) -> ElasticQuotaInfos:
+    # elasticquotainfo.go:37-43 clones every map entry separately, so the namespaces of a composite quota become
+    # DISTINCT objects in the snapshot: un-reserving a victim only touches the copy of the victim's own namespace.
+    out = ElasticQuotaInfos()
+    for ns, e in infos.items():
+        out[ns] = ElasticQuotaInfo(e.name, list(e.namespaces), e.min.clone() if e.min else None, e.max.clone() if e.max else None,
+                                   e.used.clone() if e.used else None, e.max_enforced, set(e.pods))
+    return out
+
+
+def over_quota_label(pod: Pod) -> bool:  # pkg/util/pod/pod.go:31-36
+    return pod.labels.get("nos.nebuly.com/capacity") == "over-quota"
+
+
+def select_potential_victims(infos: ElasticQuotaInfos, preemptor: Pod, nominated_in_eq: Resource, node_pods: List[Pod],
+                             nvidia_gpu_memory_gb: int) -> List[bool]:
+    snap = clone_infos(infos)
+    prio = pod_priority(preemptor)
+    pre_eq = snap.get(preemptor.namespace)
+    victims = [False] * len(node_pods)
+
+    def remove(pv: Pod):
+        e = snap.get(pv.namespace)
+        if e is not None:
+            e.unreserve(resource_from_list(quota_pod_request(pv, nvidia_gpu_memory_gb)))   # pod assumed accounted (present)
+
+    if pre_eq is not None:
+        more_than_min = pre_eq.used_over_min_with(nominated_in_eq)
+        for i, pv in enumerate(node_pods):
+            pv_eq = snap.get(pv.namespace)
+            if pv_eq is None:
+                continue
+            if more_than_min:
+                if pv.namespace == preemptor.namespace:
+                    if pod_priority(pv) < prio:
+                        victims[i] = True
+                        remove(pv)
+                    continue
+                if not over_quota_label(pv):
+                    continue
+                g = snap.guaranteed_overquotas(preemptor.namespace)
+                min_plus_g = res_sum(g, pre_eq.min)
+                if pre_eq.used_lte_with(min_plus_g, nominated_in_eq):
+                    pg = snap.guaranteed_overquotas(pv.namespace)
+                    pv_min_plus_g = res_sum(pg, pv_eq.min)
+                    if pv_eq.used_over(pv_min_plus_g):
+                        victims[i] = True
+                        remove(pv)
+            else:
+                if pv.namespace != preemptor.namespace and pv_eq.used_over_min() and over_quota_label(pv):
+                    victims[i] = True
+                    remove(pv)
+    else:
+        for i, pv in enumerate(node_pods):
+            if pv.namespace in snap:
+                continue
+            if pod_priority(pv) < prio:
+                victims[i] = True
+    return victims

@@ -17,7 +17,7 @@ def lib():
     global _lib
     if _lib is None:
         path = os.path.join(ORACLE_DIR, "libnosoracle.so")
-        srcs = [os.path.join(ORACLE_DIR, f) for f in ("nos_oracle.cpp", "nos_quota_oracle.cpp")] + \
+        srcs = [os.path.join(ORACLE_DIR, f) for f in ("nos_oracle.cpp", "nos_quota_oracle.cpp", "nos_victims_oracle.cpp")] + \
                [os.path.join(ROOT, "include", "nosplan.h")]
         if not os.path.exists(path) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs if os.path.exists(s)):
             subprocess.check_call(["make", "-C", ORACLE_DIR, "-s"])
