@@ -170,13 +170,21 @@ def run_ours(args):
     if not os.path.exists(g.LIB):
         g.build()
 
-    # node-sharding of ONE Plan() needs the speculative sweep (DESIGN.md "Multi-GPU"); until then every rank plans an
-    # independent snapshot of the same shape (replicas): weak scaling, no data-path collective.
-    snap, pods = make_workload(args.workload, seed_offset=rank)
+    # N > 1: ONE Plan() over a snapshot of world x nodes (per-GPU node count fixed: weak scaling), node-sharded: every rank
+    # uploads the same snapshot, runs the node-parallel pass on its slice of the name-ordered node list, and the ranks
+    # exchange one all-gather of counters + placed-key bitmap (NCCL), then all-gather the plan rows (nos_b200/sharded.py).
+    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
+    snap, pods = make_workload(args.workload, nodes=n_full * world)
     eng = capi.Engine(local)
     eng.upload(snap, pods, None, FILTER_RESOURCES_FIT)
-    ext = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local))
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")     # > 126 MB L2
+    dev = torch.device("cuda", local)
+    ext = torch.cuda.ExternalStream(eng.stream(), device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    planner = None
+    if world > 1:
+        from nos_b200 import sharded
+        planner = sharded.ShardedPlanner(eng, rank, world, dev)
+        planner.prepare(snap.n_nodes, snap.gpus_per_node)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -189,7 +197,10 @@ def run_ours(args):
             flush.zero_()
         s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
         s.record(ext)
-        eng.run()
+        if planner is None:
+            eng.run()
+        else:
+            planner.run(gather_plan=True)
         e.record(ext)
         _, _, st = eng.download()           # synchronises; outside the timed pair of events
         return s.elapsed_time(e), st
@@ -204,14 +215,21 @@ def run_ours(args):
         ms, st = one_step(True)
         step_ms.append(ms); sweep_ms.append(st["ms_sweep"]); par_ms.append(st["ms_parallel"])
     sync_all()
-    # ---- end to end: host buffers in, host buffers out, wall clock (H2D + kernels + D2H inside)
+    # ---- end to end: host buffers in, host buffers out, wall clock (H2D + kernels [+ collectives] + D2H inside)
+    def e2e_once():
+        if planner is None:
+            return eng.plan(snap, pods, None, FILTER_RESOURCES_FIT)[2]
+        eng.upload(snap, pods, None, FILTER_RESOURCES_FIT)
+        planner.run(gather_plan=True)
+        return eng.download()[2]
+
     for _ in range(2):
-        eng.plan(snap, pods, None, FILTER_RESOURCES_FIT)
+        e2e_once()
     sync_all()
     e2e_s = []
     for _ in range(args.steps):
         t0 = time.perf_counter()
-        _, _, est = eng.plan(snap, pods, None, FILTER_RESOURCES_FIT)
+        est = e2e_once()
         e2e_s.append(time.perf_counter() - t0)
     sync_all()
     clocks = sampler.stop()
@@ -223,11 +241,7 @@ def run_ours(args):
         t = torch.tensor([total_ms, e2e_total], dtype=torch.float64, device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms, e2e_total = float(t[0]), float(t[1])
-        c = torch.tensor([cands], dtype=torch.int64, device=f"cuda:{local}")
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        cands_all = int(c[0])
-    else:
-        cands_all = cands
+    cands_all = cands                      # visited nodes (all ranks) x pods: already the whole job
     if rank != 0:
         eng.close()
         if world > 1:
@@ -243,18 +257,19 @@ def run_ours(args):
     dom_name = "k_plan_parallel" if st["path"] == 1 else "k_plan_sweep"
     dom_ms = float(np.mean(par_ms)) if st["path"] == 1 else sweep_avg_ms
     achieved = b_plan / (dom_ms / 1e3) / 1e9
-    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
     line = {
         "metric": "planner_candidates_per_sec", "value": value, "unit": "candidates/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": {"workload": args.workload, "kind": kind, "nodes": n_full, "gpus_per_node": gg, "pods": p_full,
-                   "regime": "saturating", "filter": "resources_fit", "parallelism": f"replicas x{world}",
+        "config": {"workload": args.workload, "kind": kind, "nodes": n_full * world, "gpus_per_node": gg, "pods": p_full,
+                   "regime": "saturating", "filter": "resources_fit",
+                   "parallelism": "single GPU" if world == 1 else f"node-sharded x{world}: {n_full} nodes per GPU, one all-gather of "
+                                  f"{planner.nbytes} B per rank on the data path + all-gather of the plan rows",
                    "l2": "flushed between iterations (256 MiB device write)", "candidates_per_plan": cands,
                    "visited_nodes": int(st["visited_nodes"]), "placements": int(st["placements"])},
         "plan_p50_ms": float(np.median(step_ms)), "plan_p95_ms": float(np.percentile(step_ms, 95)),
         "kernel_ms": {"prepass": float(st["ms_prepass"]), "tracker_init": float(st["ms_tracker"]), "parallel": float(np.mean(par_ms)),
-                      "sweep_or_verify": sweep_avg_ms, "path": "node-parallel" if st["path"] == 1 else "sequential"},
+                      "verify_or_sweep" if world == 1 else "exchange+verify": sweep_avg_ms, "path": "node-parallel" if st["path"] == 1 else "sequential"},
         "roofline": {"bound": "hbm", "kernel": dom_name, "kernel_ms": dom_ms, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": recorded_traffic(), "algorithmic_bytes": b_plan, "peak_source": peak_src},
         "e2e": {"value": e2e_value, "unit": "candidates/s", "h2d_bytes_per_step": int(est["h2d_bytes"]),

@@ -147,6 +147,24 @@ int nosplan_run(nosplan_t* h);
 int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats);
 void* nosplan_stream(nosplan_t* h);    /* cudaStream_t */
 
+/* Node-sharded Plan() over `world` ranks -- one handle per rank (one process per GPU), the SAME snapshot uploaded on
+ * every rank (the reference's Plan() is single-process, core/planner.go:67-153, so there is no
+ * counterpart call).  Each rank runs the node-parallel pass on its slice [rank*N/world, (rank+1)*N/world) of the
+ * name-ordered node list.  The only data-path exchange is one all-gather of nosplan_shard_exchange_bytes() per rank:
+ * 4 counters and the bitmap of tracker keys its nodes placed.
+ *   begin(): cluster totals and tracker initialisation (replicated: cheaper than a collective), node-parallel pass on
+ *            the slice; the rank's block is written to the DEVICE buffer d_exchange (caller-owned, e.g. a torch tensor);
+ *   the caller all-gathers the blocks (NCCL) into d_gathered [world][exchange_bytes] on the handle's stream;
+ *   end():   OR / sum of the blocks, verification of the saturation hypothesis; if it fails, or the pass is not
+ *            applicable, every rank runs the full sequential sweep (identical result on every rank).
+ * After end(), nosplan_download works as usual; rows of nodes outside the rank's slice hold the initial state unless the
+ * sequential sweep ran (stats.path == 0), in which case the plan is complete on every rank.  nosplan_device_outputs
+ * exposes the device rows so the slices can be all-gathered without a host round trip. */
+int64_t nosplan_shard_exchange_bytes(nosplan_t* h);
+int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_exchange, int64_t exchange_bytes);
+int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world);
+int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count /* [N*G][16] u8 */, void** d_gpu_mask /* [N*G] u16 */);
+
 /* No counterpart in the reference.  The tracker initialisation of Plan() -- lacking[p] summed over the pods, and the
  * number of distinct pod keys that lack any slice -- for callers that may not allocate device memory: processes
  * sharing the GPU with latency-sensitive streams (cudaMalloc/cudaFree synchronise the whole device) or running inside a

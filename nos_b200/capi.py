@@ -21,6 +21,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_plan",
     "nosplan_upload", "nosplan_run", "nosplan_download", "nosplan_stream",
     "nosplan_lacking_static", "nosplan_quota_recompute", "nosplan_quota_victims",
+    "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
 ]
 STATIC_MAX_KEYS = 16384
 
@@ -155,6 +156,14 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_quota_recompute.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(qp.CQuotaPods), C.POINTER(qp.CQuotaPods),
                                             C.POINTER(qp.CQuotaOut), C.POINTER(CStats)]
     lib.nosplan_quota_recompute.restype = C.c_int
+    lib.nosplan_shard_exchange_bytes.argtypes = [C.c_void_p]
+    lib.nosplan_shard_exchange_bytes.restype = C.c_int64
+    lib.nosplan_shard_begin.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64]
+    lib.nosplan_shard_begin.restype = C.c_int
+    lib.nosplan_shard_end.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
+    lib.nosplan_shard_end.restype = C.c_int
+    lib.nosplan_device_outputs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+    lib.nosplan_device_outputs.restype = C.c_int
     from . import victim_packing as vp
     lib.nosplan_quota_victims.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(vp.CVictimQuery), C.c_void_p, C.POINTER(CStats)]
     lib.nosplan_quota_victims.restype = C.c_int
@@ -238,6 +247,24 @@ class Engine:
 
     def stream(self) -> int:
         return int(self.lib.nosplan_stream(self.h) or 0)
+
+    # ---- node-sharded Plan() (one Engine per rank; see nos_b200/sharded.py for the collective around it)
+    def shard_exchange_bytes(self) -> int:
+        n = int(self.lib.nosplan_shard_exchange_bytes(self.h))
+        if n < 0:
+            raise NosplanError("nosplan_shard_exchange_bytes before nosplan_upload")
+        return n
+
+    def shard_begin(self, rank: int, world: int, d_exchange: int, nbytes: int):
+        self._check(self.lib.nosplan_shard_begin(self.h, rank, world, d_exchange, nbytes), "nosplan_shard_begin")
+
+    def shard_end(self, d_gathered: int, world: int):
+        self._check(self.lib.nosplan_shard_end(self.h, d_gathered, world), "nosplan_shard_end")
+
+    def device_outputs(self):
+        a, b = C.c_void_p(), C.c_void_p()
+        self._check(self.lib.nosplan_device_outputs(self.h, C.byref(a), C.byref(b)), "nosplan_device_outputs")
+        return int(a.value or 0), int(b.value or 0)
 
     def quota_victims(self, pq, query):
         """nosplan_quota_victims -> (victim flags [n_pods] uint8, stats dict).  pq.used_init / used_mask = current Used."""

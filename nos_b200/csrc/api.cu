@@ -18,6 +18,7 @@ void launch_prepass(const DevProblem& pb, cudaStream_t st);
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
 cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st);
+void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, cudaStream_t st);
 cudaError_t sweep_prepare_device();
 int sweep_max_keys();
 }  // namespace nsp
@@ -398,6 +399,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     std::memset(&pb, 0, sizeof pb);
     unsigned char* A = h->d_arena;
     pb.kind = s->kind; pb.K = K; pb.R = R; pb.n_other = s->n_other;
+    pb.node_lo = 0; pb.node_hi = N;
     pb.N = N; pb.G = G; pb.P = P; pb.n_keys = n_keys; pb.n_runs = n_runs; pb.filter_mode = filter_mode;
     pb.n_models = n_models; pb.n_rows = n_rows;
     for (int p = 0; p < KP; ++p) { pb.pmem[p] = p < K ? s->profile_mem_gb[p] : 0; pb.pgi[p] = p < K ? s->profile_gi[p] : 0; }
@@ -459,6 +461,60 @@ int nosplan_run(nosplan_t* h) {
     CU(h, cudaEventRecord(h->ev[3], h->stream));
     h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     h->ran = true;
+    return NOSPLAN_OK;
+}
+
+// ---- node-sharded Plan() over `world` ranks (one handle per rank, the same snapshot uploaded on each) --------------
+int64_t nosplan_shard_exchange_bytes(nosplan_t* h) {
+    if (!h || !h->uploaded) return -1;
+    return 32 + 8 * ((((int64_t)h->pb.n_keys + 31) / 32 + 1) / 2);     // 4 u64 counters + bitmap words, 8-byte granular
+}
+
+int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_exchange, int64_t exchange_bytes) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_shard_begin before nosplan_upload");
+    if (world < 1 || rank < 0 || rank >= world) return fail(h, NOSPLAN_E_INVALID, "rank %d of %d", rank, world);
+    const int64_t need = nosplan_shard_exchange_bytes(h);
+    if (!d_exchange || exchange_bytes < need) return fail(h, NOSPLAN_E_INVALID, "exchange buffer smaller than %lld bytes", (long long)need);
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaEventRecord(h->ev[2], h->stream));
+    CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
+    CU(h, cudaMemsetAsync(d_exchange, 0, (size_t)need, h->stream));
+    launch_prepass(h->pb, h->stream);                       // replicated: cheaper than exchanging the totals
+    CU(h, cudaEventRecord(h->ev[6], h->stream));
+    launch_tracker_init(h->pb, h->stream);
+    CU(h, cudaEventRecord(h->ev[7], h->stream));
+    DevProblem shard = h->pb;                               // this rank's slice of the name-ordered node list
+    const int chunk = (h->pb.N + world - 1) / world;        // equal-sized slices (the last may be short) so the rows all-gather
+    shard.node_lo = std::min(h->pb.N, rank * chunk);
+    shard.node_hi = std::min(h->pb.N, shard.node_lo + chunk);
+    shard.acc = static_cast<unsigned long long*>(d_exchange);
+    shard.placed = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(d_exchange) + 32);
+    CU(h, cudaGetLastError());
+    CU(h, launch_parallel(shard, h->stream));
+    CU(h, cudaEventRecord(h->ev[8], h->stream));
+    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
+    return NOSPLAN_OK;
+}
+
+int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_shard_end before nosplan_upload");
+    if (!d_gathered || world < 1) return fail(h, NOSPLAN_E_INVALID, "null gathered buffer");
+    CU(h, cudaSetDevice(h->device));
+    launch_shard_combine(h->pb, d_gathered, world, (size_t)nosplan_shard_exchange_bytes(h), h->stream);
+    CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
+    CU(h, cudaEventRecord(h->ev[3], h->stream));
+    h->launches += 2;
+    h->ran = true;
+    return NOSPLAN_OK;
+}
+
+int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count, void** d_gpu_mask) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_device_outputs before nosplan_upload");
+    if (d_gpu_count) *d_gpu_count = h->pb.out_count;
+    if (d_gpu_mask) *d_gpu_mask = h->pb.out_mask;
     return NOSPLAN_OK;
 }
 

@@ -38,6 +38,7 @@ struct DevProblem {
     int kind, K, R, n_other;
     int N, G, P, n_keys, n_runs, filter_mode;
     int n_models, n_rows;
+    int node_lo, node_hi;            // node range of the node-parallel pass on this rank (whole snapshot: 0, N)
     int32_t pmem[KP], pgi[KP];
     // geometry tables
     const int32_t* model_off;        // [n_models+1]

@@ -618,7 +618,7 @@ __global__ void __launch_bounds__(128) k_plan_parallel(DevProblem pb) {
     long long D = 0, st_evals = 0, st_place = 0, visited = 0;
     bool committed = true;
     const int warps_total = gridDim.x * (blockDim.x >> 5);
-    for (int i = blockIdx.x * (blockDim.x >> 5) + warp; i < pb.N; i += warps_total) {
+    for (int i = pb.node_lo + blockIdx.x * (blockDim.x >> 5) + warp; i < pb.node_hi; i += warps_total) {
         if (!pb.cand_flag[i]) continue;
         NodeRegs nr;
         load_node(pb, i, lane, nr);
@@ -798,11 +798,34 @@ cudaError_t sweep_prepare_device() {
 }
 
 cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st) {
-    if (!pb.fast_eligible || pb.N == 0 || pb.P == 0) return cudaSuccess;
-    int blocks = (pb.N + 3) / 4;
+    if (!pb.fast_eligible || pb.N == 0 || pb.P == 0 || pb.node_hi <= pb.node_lo) return cudaSuccess;
+    int blocks = (pb.node_hi - pb.node_lo + 3) / 4;
     if (blocks > g_par_blocks) blocks = g_par_blocks;
     k_plan_parallel<<<blocks, 128, 0, st>>>(pb);
     return cudaGetLastError();
+}
+
+// Node-sharded Plan(): every rank ran the node-parallel pass on its own node range and all-gathered its
+// [acc (4 x u64) | placed bitmap] block; OR the bitmaps and sum the counters into this rank's work area.
+__global__ void __launch_bounds__(256) k_shard_combine(DevProblem pb, const unsigned char* gathered, int world, size_t stride) {
+    const int words = (pb.n_keys + 31) / 32;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x < words) {
+        unsigned w = 0;
+        for (int r = 0; r < world; ++r) w |= reinterpret_cast<const unsigned*>(gathered + r * stride + 32)[x];
+        pb.placed[x] = w;
+    }
+    if (x < 4) {
+        unsigned long long a = 0;
+        for (int r = 0; r < world; ++r) a += reinterpret_cast<const unsigned long long*>(gathered + r * stride)[x];
+        pb.acc[x] = a;
+    }
+}
+
+void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, cudaStream_t st) {
+    const int words = (pb.n_keys + 31) / 32;
+    const int n = words > 4 ? words : 4;
+    k_shard_combine<<<(n + 255) / 256, 256, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world, stride);
 }
 
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st) {

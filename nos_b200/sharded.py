@@ -1,0 +1,97 @@
+"""Node-sharded Plan() across the GPUs of one box: one process per GPU, one Engine per process, the same snapshot
+uploaded on every rank, the node-parallel pass split by node range, ONE all-gather of a few KB (counters + bitmap of
+placed tracker keys) on the data path, and an all-gather of the plan rows at the end.
+
+The collective is injectable so the protocol can be driven without NCCL: tests emulate several ranks on one GPU by
+concatenating the ranks' blocks, and a gloo world_size-2 test covers the torch.distributed plumbing on CPU.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+import numpy as np
+
+
+def shard_range(n_nodes: int, rank: int, world: int) -> Tuple[int, int]:
+    """Slice of the name-ordered node list owned by `rank` (same rule as nosplan_shard_begin): equal chunks of
+    ceil(N/world) nodes, the last possibly short or empty."""
+    chunk = (n_nodes + world - 1) // world
+    lo = min(n_nodes, rank * chunk)
+    return lo, min(n_nodes, lo + chunk)
+
+
+class _DevArray:
+    """Zero-copy view of device memory owned by libnosplan, for torch.as_tensor."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def combine_blocks(blocks: np.ndarray, n_keys: int):
+    """Host restatement of k_shard_combine, for tests: blocks [world][bytes] uint8 -> (acc[4] uint64, placed bitmap words)."""
+    world = blocks.shape[0]
+    words = (n_keys + 31) // 32
+    acc = np.zeros(4, np.uint64)
+    placed = np.zeros(words, np.uint32)
+    for r in range(world):
+        acc += blocks[r, :32].view(np.uint64)
+        placed |= blocks[r, 32:32 + 4 * words].view(np.uint32)
+    return acc, placed
+
+
+class ShardedPlanner:
+    """Drives nosplan_shard_begin / all-gather / nosplan_shard_end on one rank.
+
+    all_gather(dst, src): fills dst ([world * len(src)] uint8 device tensor) with every rank's src; default is
+    torch.distributed.all_gather_into_tensor on `group`."""
+
+    def __init__(self, engine, rank: int, world: int, device, group=None, all_gather: Optional[Callable] = None):
+        import torch
+        self.torch = torch
+        self.engine, self.rank, self.world, self.device, self.group = engine, rank, world, device, group
+        self._all_gather = all_gather or self._dist_all_gather
+        self.local = self.gathered = None
+
+    def _dist_all_gather(self, dst, src):
+        import torch.distributed as dist
+        dist.all_gather_into_tensor(dst, src, group=self.group)
+
+    def prepare(self, n_nodes: int, gpus_per_node: int):
+        """Call after engine.upload(): sizes the exchange buffers and maps the engine's device output rows."""
+        t = self.torch
+        nb = self.engine.shard_exchange_bytes()
+        self.nbytes = nb
+        self.local = t.zeros(self.nbytes, dtype=t.uint8, device=self.device)
+        self.gathered = t.zeros(self.world * self.nbytes, dtype=t.uint8, device=self.device)
+        self.N, self.G = n_nodes, gpus_per_node
+        self.chunk = (n_nodes + self.world - 1) // self.world
+        d_cnt, d_msk = self.engine.device_outputs()
+        rows = max(1, n_nodes * gpus_per_node)
+        self.out_count = t.as_tensor(_DevArray(d_cnt, (rows, 16), "|u1"), device=self.device)
+        self.out_mask = t.as_tensor(_DevArray(d_msk, (rows,), "<i2"), device=self.device)
+        cr = self.chunk * gpus_per_node
+        self.row_local = t.zeros((cr, 18), dtype=t.uint8, device=self.device)          # 16 count bytes + 2 mask bytes per GPU
+        self.row_all = t.zeros((self.world * cr, 18), dtype=t.uint8, device=self.device)
+
+    def run(self, gather_plan: bool = True):
+        """One Plan().  Everything is enqueued on the engine's stream; nothing synchronises the host."""
+        t = self.torch
+        stream = t.cuda.ExternalStream(self.engine.stream(), device=self.device)
+        with t.cuda.stream(stream):
+            self.engine.shard_begin(self.rank, self.world, self.local.data_ptr(), self.nbytes)
+            self._all_gather(self.gathered, self.local)
+            self.engine.shard_end(self.gathered.data_ptr(), self.world)
+            if gather_plan and self.N > 0:
+                lo, hi = shard_range(self.N, self.rank, self.world)
+                n = (hi - lo) * self.G
+                self.row_local.zero_()
+                if n:
+                    self.row_local[:n, :16] = self.out_count[lo * self.G:hi * self.G]
+                    self.row_local[:n, 16:] = self.out_mask[lo * self.G:hi * self.G].view(t.uint8).view(n, 2)
+                self._all_gather(self.row_all.view(-1), self.row_local.view(-1))
+
+    def plan(self):
+        """Host copy of the gathered plan -> (gpu_count [N*G,16] uint8, gpu_mask [N*G] uint16).  Valid when the
+        node-parallel pass stood (stats path == 1); after a sequential fallback use engine.download() instead."""
+        rows = self.row_all[: self.N * self.G].cpu().numpy()
+        return rows[:, :16].copy(), rows[:, 16:].copy().view(np.uint16).reshape(-1)

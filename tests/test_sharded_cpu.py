@@ -1,0 +1,77 @@
+"""Host-side plumbing of the node-sharded Plan() under torch.distributed (gloo, world_size 2, CPU): shard ranges, the
+all-gather of the per-rank blocks and their OR / sum combination.  The CUDA engine is replaced by a stand-in that fills
+the block the way k_plan_parallel does; the kernels themselves are covered by tests/test_sharded_gpu.py."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from nos_b200 import sharded
+
+
+def test_shard_ranges_cover_once():
+    for n in (0, 1, 7, 8, 9, 1000, 10_001):
+        for w in (1, 2, 3, 8):
+            seen = []
+            for r in range(w):
+                lo, hi = sharded.shard_range(n, r, w)
+                assert 0 <= lo <= hi <= n
+                seen += list(range(lo, hi))
+            assert seen == list(range(n))
+
+
+class FakeEngine:
+    """Stands in for capi.Engine on CPU: records what the ShardedPlanner passes around."""
+
+    def __init__(self, rank, n_keys, placed_keys, counters):
+        self.rank, self.n_keys, self.placed_keys, self.counters = rank, n_keys, placed_keys, counters
+        self.ended_with = None
+
+    def shard_exchange_bytes(self):
+        return 32 + 8 * (((self.n_keys + 31) // 32 + 1) // 2)
+
+
+def _worker(rank, world, port, n_keys, q):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(100 + rank)
+    keys = rng.choice(n_keys, size=n_keys // 3, replace=False)
+    eng = FakeEngine(rank, n_keys, keys, [10 + rank, 20 + rank, 30 + rank, 0])
+    nb = eng.shard_exchange_bytes()
+    block = np.zeros(nb, np.uint8)
+    block[:32].view(np.uint64)[:] = eng.counters
+    words = block[32:].view(np.uint32)
+    for k in keys:
+        words[k >> 5] |= np.uint32(1 << (k & 31))
+    local = torch.from_numpy(block.copy())
+    gathered = torch.zeros(world * nb, dtype=torch.uint8)
+    planner = sharded.ShardedPlanner(eng, rank, world, torch.device("cpu"))
+    planner._dist_all_gather(gathered, local)                       # the collective the GPU path uses (NCCL there)
+    acc, placed = sharded.combine_blocks(gathered.numpy().reshape(world, nb), n_keys)
+    q.put((rank, acc.tolist(), placed.tolist(), sorted(int(k) for k in keys)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_all_gather_and_combine():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    world, n_keys = 2, 1000
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_keys, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    res.sort()
+    union = set(res[0][3]) | set(res[1][3])
+    for rank, acc, placed, _ in res:
+        assert acc[:3] == [21, 41, 61]                               # sums of the two ranks' counters
+        got = {32 * w + b for w, v in enumerate(placed) for b in range(32) if v >> b & 1}
+        assert got == union                                          # OR of the bitmaps
