@@ -68,10 +68,14 @@ class ShardedPlanner:
         d_cnt, d_msk = self.engine.device_outputs()
         rows = max(1, n_nodes * gpus_per_node)
         self.out_count = t.as_tensor(_DevArray(d_cnt, (rows, 16), "|u1"), device=self.device)
-        self.out_mask = t.as_tensor(_DevArray(d_msk, (rows,), "<i2"), device=self.device)
+        self.out_mask = t.as_tensor(_DevArray(d_msk, (rows, 2), "|u1"), device=self.device)    # u16 as byte pairs: NCCL has no int16
         cr = self.chunk * gpus_per_node
-        self.row_local = t.zeros((cr, 18), dtype=t.uint8, device=self.device)          # 16 count bytes + 2 mask bytes per GPU
-        self.row_all = t.zeros((self.world * cr, 18), dtype=t.uint8, device=self.device)
+        self.even = n_nodes % self.world == 0 and n_nodes > 0        # slices all-gather straight out of the engine's rows
+        self.count_all = t.zeros((self.world * cr, 16), dtype=t.uint8, device=self.device)
+        self.mask_all = t.zeros((self.world * cr, 2), dtype=t.uint8, device=self.device)
+        if not self.even:
+            self.count_local = t.zeros((cr, 16), dtype=t.uint8, device=self.device)
+            self.mask_local = t.zeros((cr, 2), dtype=t.uint8, device=self.device)
 
     def run(self, gather_plan: bool = True):
         """One Plan().  Everything is enqueued on the engine's stream; nothing synchronises the host."""
@@ -83,15 +87,19 @@ class ShardedPlanner:
             self.engine.shard_end(self.gathered.data_ptr(), self.world)
             if gather_plan and self.N > 0:
                 lo, hi = shard_range(self.N, self.rank, self.world)
-                n = (hi - lo) * self.G
-                self.row_local.zero_()
-                if n:
-                    self.row_local[:n, :16] = self.out_count[lo * self.G:hi * self.G]
-                    self.row_local[:n, 16:] = self.out_mask[lo * self.G:hi * self.G].view(t.uint8).view(n, 2)
-                self._all_gather(self.row_all.view(-1), self.row_local.view(-1))
+                a, b = lo * self.G, hi * self.G
+                if self.even:
+                    self._all_gather(self.count_all.view(-1), self.out_count[a:b].reshape(-1))
+                    self._all_gather(self.mask_all.view(-1), self.out_mask[a:b].reshape(-1))
+                else:
+                    self.count_local.zero_(); self.mask_local.zero_()
+                    self.count_local[:b - a] = self.out_count[a:b]
+                    self.mask_local[:b - a] = self.out_mask[a:b]
+                    self._all_gather(self.count_all.view(-1), self.count_local.view(-1))
+                    self._all_gather(self.mask_all.view(-1), self.mask_local.view(-1))
 
     def plan(self):
         """Host copy of the gathered plan -> (gpu_count [N*G,16] uint8, gpu_mask [N*G] uint16).  Valid when the
         node-parallel pass stood (stats path == 1); after a sequential fallback use engine.download() instead."""
-        rows = self.row_all[: self.N * self.G].cpu().numpy()
-        return rows[:, :16].copy(), rows[:, 16:].copy().view(np.uint16).reshape(-1)
+        n = self.N * self.G
+        return self.count_all[:n].cpu().numpy(), self.mask_all[:n].cpu().numpy().copy().view(np.uint16).reshape(-1)
