@@ -180,11 +180,11 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     ext = torch.cuda.ExternalStream(eng.stream(), device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
-    planner = None
-    if world > 1:
-        from nos_b200 import sharded
-        planner = sharded.ShardedPlanner(eng, rank, world, dev)
-        planner.prepare(snap.n_nodes, snap.gpus_per_node)
+    sharded_run = world > 1
+    if sharded_run:                          # collectives are issued by the library itself (one grouped NCCL launch per Plan)
+        uid = [eng.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.shard_init(rank, world, uid[0])
 
     def sync_all():
         torch.cuda.synchronize()
@@ -197,12 +197,12 @@ def run_ours(args):
             flush.zero_()
         s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
         s.record(ext)
-        if planner is None:
-            eng.run()
+        if sharded_run:
+            eng.run_sharded(True)
         else:
-            planner.run(gather_plan=True)
+            eng.run()
         e.record(ext)
-        _, _, st = eng.download()           # synchronises; outside the timed pair of events
+        _, _, st = eng.download_sharded() if sharded_run else eng.download()   # synchronises; outside the timed pair of events
         return s.elapsed_time(e), st
 
     for _ in range(max(3, args.warmup)):
@@ -217,11 +217,11 @@ def run_ours(args):
     sync_all()
     # ---- end to end: host buffers in, host buffers out, wall clock (H2D + kernels [+ collectives] + D2H inside)
     def e2e_once():
-        if planner is None:
+        if not sharded_run:
             return eng.plan(snap, pods, None, FILTER_RESOURCES_FIT)[2]
         eng.upload(snap, pods, None, FILTER_RESOURCES_FIT)
-        planner.run(gather_plan=True)
-        return eng.download()[2]
+        eng.run_sharded(True)
+        return eng.download_sharded()[2]
 
     for _ in range(2):
         e2e_once()
@@ -264,7 +264,7 @@ def run_ours(args):
         "config": {"workload": args.workload, "kind": kind, "nodes": n_full * world, "gpus_per_node": gg, "pods": p_full,
                    "regime": "saturating", "filter": "resources_fit",
                    "parallelism": "single GPU" if world == 1 else f"node-sharded x{world}: {n_full} nodes per GPU, one all-gather of "
-                                  f"{planner.nbytes} B per rank on the data path + all-gather of the plan rows",
+                                  f"{eng.shard_exchange_bytes()} B per rank on the data path + all-gather of the plan rows, one grouped NCCL launch",
                    "l2": "flushed between iterations (256 MiB device write)", "candidates_per_plan": cands,
                    "visited_nodes": int(st["visited_nodes"]), "placements": int(st["placements"])},
         "plan_p50_ms": float(np.median(step_ms)), "plan_p95_ms": float(np.percentile(step_ms, 95)),

@@ -165,6 +165,15 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
 int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world);
 int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count /* [N*G][16] u8 */, void** d_gpu_mask /* [N*G] u16 */);
 
+/* The same protocol with the collectives issued by the library itself (NCCL resolved with dlopen at run time): rank 0
+ * obtains an id with nosplan_nccl_unique_id and hands its 128 bytes to the other ranks by any means; every rank calls
+ * nosplan_shard_init once, then per Plan(): nosplan_upload, nosplan_run_sharded (begin + ONE grouped NCCL launch with the
+ * exchange block and, if gather_plan, the plan rows + end), nosplan_download_sharded (complete plan on every rank). */
+int nosplan_nccl_unique_id(uint8_t* out128);
+int nosplan_shard_init(nosplan_t* h, int32_t rank, int32_t world, const uint8_t* id128);
+int nosplan_run_sharded(nosplan_t* h, int32_t gather_plan);
+int nosplan_download_sharded(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats);
+
 /* No counterpart in the reference.  The tracker initialisation of Plan() -- lacking[p] summed over the pods, and the
  * number of distinct pod keys that lack any slice -- for callers that may not allocate device memory: processes
  * sharing the GPU with latency-sensitive streams (cudaMalloc/cudaFree synchronise the whole device) or running inside a

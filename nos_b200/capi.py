@@ -22,6 +22,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_upload", "nosplan_run", "nosplan_download", "nosplan_stream",
     "nosplan_lacking_static", "nosplan_quota_recompute", "nosplan_quota_victims",
     "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
+    "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
 ]
 STATIC_MAX_KEYS = 16384
 
@@ -164,6 +165,14 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_shard_end.restype = C.c_int
     lib.nosplan_device_outputs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
     lib.nosplan_device_outputs.restype = C.c_int
+    lib.nosplan_nccl_unique_id.argtypes = [C.c_void_p]
+    lib.nosplan_nccl_unique_id.restype = C.c_int
+    lib.nosplan_shard_init.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
+    lib.nosplan_shard_init.restype = C.c_int
+    lib.nosplan_run_sharded.argtypes = [C.c_void_p, C.c_int32]
+    lib.nosplan_run_sharded.restype = C.c_int
+    lib.nosplan_download_sharded.argtypes = [C.c_void_p, C.POINTER(CPartitioning), C.POINTER(CStats)]
+    lib.nosplan_download_sharded.restype = C.c_int
     from . import victim_packing as vp
     lib.nosplan_quota_victims.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(vp.CVictimQuery), C.c_void_p, C.POINTER(CStats)]
     lib.nosplan_quota_victims.restype = C.c_int
@@ -260,6 +269,26 @@ class Engine:
 
     def shard_end(self, d_gathered: int, world: int):
         self._check(self.lib.nosplan_shard_end(self.h, d_gathered, world), "nosplan_shard_end")
+
+    def nccl_unique_id(self) -> bytes:
+        buf = (C.c_uint8 * 128)()
+        rc = self.lib.nosplan_nccl_unique_id(buf)
+        if rc != 0:
+            raise NosplanError(f"nosplan_nccl_unique_id failed ({rc}): libnccl.so.2 not loadable")
+        return bytes(buf)
+
+    def shard_init(self, rank: int, world: int, unique_id: bytes):
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._check(self.lib.nosplan_shard_init(self.h, rank, world, buf), "nosplan_shard_init")
+
+    def run_sharded(self, gather_plan: bool = True):
+        self._check(self.lib.nosplan_run_sharded(self.h, 1 if gather_plan else 0), "nosplan_run_sharded")
+
+    def download_sharded(self):
+        out, cnt, msk = alloc_partitioning(self._snap)
+        st = CStats()
+        self._check(self.lib.nosplan_download_sharded(self.h, C.byref(out), C.byref(st)), "nosplan_download_sharded")
+        return cnt, msk, st.as_dict()
 
     def device_outputs(self):
         a, b = C.c_void_p(), C.c_void_p()

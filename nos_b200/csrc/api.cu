@@ -36,34 +36,13 @@ extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_q
                                           const nosplan_quotas* qs, const nosplan_victim_query* vq, uint8_t* victim,
                                           float* ms_k, int* launches);
 
-struct nosplan {
-    int device = -1;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[9] = {};
-    // device arena + pinned staging (grown on demand, reused across calls)
-    unsigned char* d_arena = nullptr; size_t d_cap = 0;
-    unsigned char* h_stage = nullptr; size_t h_cap = 0;
-    unsigned char* h_out = nullptr; size_t h_out_cap = 0;
-    // current problem
-    bool uploaded = false, ran = false;
-    DevProblem pb{};
-    int32_t* d_cand_idx = nullptr;
-    unsigned char* d_work = nullptr; size_t work_bytes = 0;
-    size_t out_count_bytes = 0, out_mask_bytes = 0;
-    int launches = 0;
-    size_t h2d_bytes = 0;
-    nosplan_quota_ctx* qctx = nullptr;
-    std::string err;
-};
+#include "handle.cuh"
+
+extern "C" void nosplan_shard_ctx_free(nosplan_shard_ctx* c);
 
 namespace {
 
-int fail(nosplan* h, int code, const char* fmt, ...) {
-    char buf[512];
-    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
-    if (h) h->err = buf;
-    return code;
-}
+#define fail nosplan_fail
 
 #define CU(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
     return fail(h, NOSPLAN_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
@@ -156,6 +135,13 @@ int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes) {
 
 }  // namespace
 
+int nosplan_fail(nosplan* h, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (h) h->err = buf;
+    return code;
+}
+
 extern "C" {
 
 int nosplan_create(int cuda_device, nosplan_t** out) {
@@ -186,6 +172,7 @@ void nosplan_destroy(nosplan_t* h) {
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->qctx) nosplan_quota_ctx_free(h->qctx);
+    if (h->sctx) nosplan_shard_ctx_free(h->sctx);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }

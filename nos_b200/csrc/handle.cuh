@@ -1,0 +1,31 @@
+// The engine handle behind nosplan_t (include/nosplan.h).  Internal to libnosplan.
+#pragma once
+#include <string>
+
+#include "nosplan_dev.cuh"
+
+struct nosplan_quota_ctx;
+struct nosplan_shard_ctx;          // in-library NCCL state of the node-sharded Plan() (shard_nccl.cu)
+
+struct nosplan {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[9] = {};
+    // device arena + pinned staging (grown on demand, reused across calls)
+    unsigned char* d_arena = nullptr; size_t d_cap = 0;
+    unsigned char* h_stage = nullptr; size_t h_cap = 0;
+    unsigned char* h_out = nullptr; size_t h_out_cap = 0;
+    // current problem
+    bool uploaded = false, ran = false;
+    nsp::DevProblem pb{};
+    int32_t* d_cand_idx = nullptr;
+    unsigned char* d_work = nullptr; size_t work_bytes = 0;
+    size_t out_count_bytes = 0, out_mask_bytes = 0;
+    int launches = 0;
+    size_t h2d_bytes = 0;
+    nosplan_quota_ctx* qctx = nullptr;
+    nosplan_shard_ctx* sctx = nullptr;
+    std::string err;
+};
+
+int nosplan_fail(nosplan* h, int code, const char* fmt, ...);

@@ -1,0 +1,192 @@
+// Node-sharded Plan() with the collectives issued from inside the library: one grouped NCCL call carrying the three
+// all-gathers of a step (exchange block, plan count rows, plan mask rows) on the handle's stream, so a sharded Plan() costs
+// one host call.  NCCL is resolved at run time (dlopen of libnccl.so.2), so single-GPU users carry no NCCL dependency
+// and, inside a torch process, the already loaded NCCL is reused.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+
+#include "handle.cuh"
+
+extern "C" {
+int64_t nosplan_shard_exchange_bytes(nosplan_t* h);
+int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_exchange, int64_t exchange_bytes);
+int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world);
+}
+
+namespace {
+
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+
+NcclApi& nccl() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        api.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!api.lib) api.lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!api.lib) return;
+        auto sym = [&](const char* n) { return dlsym(api.lib, n); };
+        api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+        api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+        api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+        api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+        api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
+        api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
+        api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+        api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GroupStart && api.GroupEnd;
+    });
+    return api;
+}
+
+inline size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
+
+}  // namespace
+
+struct nosplan_shard_ctx {
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
+    unsigned char* d = nullptr; size_t cap = 0;
+    size_t o_local_x = 0, o_gather_x = 0, o_local_cnt = 0, o_local_msk = 0, o_cnt_all = 0, o_msk_all = 0;
+    size_t xb = 0, chunk_rows = 0;
+    bool gathered = false;
+};
+
+#define SCU(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return nosplan_fail(h, NOSPLAN_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
+#define SNC(h, call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) \
+    return nosplan_fail(h, NOSPLAN_E_CUDA, "%s: %s", #call, nccl().GetErrorString ? nccl().GetErrorString(r_) : "nccl error"); } while (0)
+
+extern "C" void nosplan_shard_ctx_free(nosplan_shard_ctx* c) {
+    if (!c) return;
+    if (c->comm && nccl().ok) nccl().CommDestroy(c->comm);
+    if (c->d) cudaFree(c->d);
+    delete c;
+}
+
+extern "C" int nosplan_nccl_unique_id(uint8_t* out128) {
+    if (!out128) return NOSPLAN_E_INVALID;
+    if (!nccl().ok) return NOSPLAN_E_CUDA;
+    ncclUniqueId id;
+    if (nccl().GetUniqueId(&id) != ncclSuccess) return NOSPLAN_E_CUDA;
+    static_assert(sizeof(id) == 128, "ncclUniqueId size");
+    std::memcpy(out128, &id, 128);
+    return NOSPLAN_OK;
+}
+
+extern "C" int nosplan_shard_init(nosplan_t* h, int32_t rank, int32_t world, const uint8_t* id128) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!nccl().ok) return nosplan_fail(h, NOSPLAN_E_CUDA, "libnccl.so.2 not found or incomplete");
+    if (!id128 || world < 1 || rank < 0 || rank >= world) return nosplan_fail(h, NOSPLAN_E_INVALID, "rank %d of %d", rank, world);
+    SCU(h, cudaSetDevice(h->device));
+    if (h->sctx) { nosplan_shard_ctx_free(h->sctx); h->sctx = nullptr; }
+    nosplan_shard_ctx* c = new nosplan_shard_ctx();
+    c->rank = rank; c->world = world;
+    ncclUniqueId id; std::memcpy(&id, id128, 128);
+    ncclResult_t r = nccl().CommInitRank(&c->comm, world, id, rank);
+    if (r != ncclSuccess) { delete c; return nosplan_fail(h, NOSPLAN_E_CUDA, "ncclCommInitRank: %s", nccl().GetErrorString(r)); }
+    h->sctx = c;
+    return NOSPLAN_OK;
+}
+
+extern "C" int nosplan_run_sharded(nosplan_t* h, int32_t gather_plan) {
+    if (!h) return NOSPLAN_E_INVALID;
+    nosplan_shard_ctx* c = h->sctx;
+    if (!c) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sharded before nosplan_shard_init");
+    if (!h->uploaded) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sharded before nosplan_upload");
+    SCU(h, cudaSetDevice(h->device));
+    const int N = h->pb.N, G = h->pb.G, W = c->world;
+    const size_t xb = (size_t)nosplan_shard_exchange_bytes(h);
+    const size_t chunk = (size_t)((N + W - 1) / W), rows = chunk * G;
+    size_t o = 0;
+    auto put = [&](size_t bytes) { size_t at = o; o = al(o + bytes); return at; };
+    c->xb = xb; c->chunk_rows = rows;
+    c->o_local_x = put(xb); c->o_gather_x = put(xb * W);
+    c->o_local_cnt = put(rows * 16); c->o_local_msk = put(rows * 2);
+    c->o_cnt_all = put(rows * 16 * W); c->o_msk_all = put(rows * 2 * W);
+    if (o > c->cap) {
+        if (c->d) SCU(h, cudaFree(c->d));
+        c->d = nullptr; c->cap = 0;
+        SCU(h, cudaMalloc(&c->d, o + o / 4 + (1 << 20)));
+        c->cap = o + o / 4 + (1 << 20);
+    }
+    int rc = nosplan_shard_begin(h, c->rank, W, c->d + c->o_local_x, (int64_t)xb);
+    if (rc != NOSPLAN_OK) return rc;
+    const int lo = std::min(N, c->rank * (int)chunk), hi = std::min(N, lo + (int)chunk);
+    const unsigned char* send_cnt = reinterpret_cast<const unsigned char*>(h->pb.out_count) + (size_t)lo * G * 16;
+    const unsigned char* send_msk = reinterpret_cast<const unsigned char*>(h->pb.out_mask) + (size_t)lo * G * 2;
+    const bool do_gather = gather_plan && rows > 0;
+    if (do_gather && (size_t)(hi - lo) != chunk) {              // short last slice: pad through a staging copy
+        SCU(h, cudaMemsetAsync(c->d + c->o_local_cnt, 0, rows * 16, h->stream));
+        SCU(h, cudaMemsetAsync(c->d + c->o_local_msk, 0, rows * 2, h->stream));
+        if (hi > lo) {
+            SCU(h, cudaMemcpyAsync(c->d + c->o_local_cnt, send_cnt, (size_t)(hi - lo) * G * 16, cudaMemcpyDeviceToDevice, h->stream));
+            SCU(h, cudaMemcpyAsync(c->d + c->o_local_msk, send_msk, (size_t)(hi - lo) * G * 2, cudaMemcpyDeviceToDevice, h->stream));
+        }
+        send_cnt = c->d + c->o_local_cnt; send_msk = c->d + c->o_local_msk;
+    }
+    // one grouped launch: exchange block + (speculative) plan rows.  If the verification below rejects the pass, the
+    // gathered rows are stale and stats.path == 0 tells the caller that every rank holds the complete plan instead.
+    SNC(h, nccl().GroupStart());
+    SNC(h, nccl().AllGather(c->d + c->o_local_x, c->d + c->o_gather_x, xb, ncclUint8, c->comm, h->stream));
+    if (do_gather) {
+        SNC(h, nccl().AllGather(send_cnt, c->d + c->o_cnt_all, rows * 16, ncclUint8, c->comm, h->stream));
+        SNC(h, nccl().AllGather(send_msk, c->d + c->o_msk_all, rows * 2, ncclUint8, c->comm, h->stream));
+    }
+    SNC(h, nccl().GroupEnd());
+    c->gathered = do_gather;
+    rc = nosplan_shard_end(h, c->d + c->o_gather_x, W);
+    if (rc == NOSPLAN_OK) h->launches += 1;                      // the grouped NCCL kernel
+    return rc;
+}
+
+// Like nosplan_download, but takes the plan rows from the all-gathered buffers when the node-parallel pass stood.
+extern "C" int nosplan_download_sharded(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    nosplan_shard_ctx* c = h->sctx;
+    if (!c || !h->ran) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_download_sharded before nosplan_run_sharded");
+    SCU(h, cudaSetDevice(h->device));
+    nsp::DevStats ds;
+    SCU(h, cudaMemcpyAsync(h->h_out, h->pb.stats, sizeof ds, cudaMemcpyDeviceToHost, h->stream));
+    SCU(h, cudaStreamSynchronize(h->stream));
+    std::memcpy(&ds, h->h_out, sizeof ds);
+    const size_t nb_cnt = h->out_count_bytes, nb_msk = h->out_mask_bytes;
+    if (out && nb_cnt) {
+        if (!out->gpu_count || !out->gpu_mask) return nosplan_fail(h, NOSPLAN_E_INVALID, "null output buffers");
+        const bool from_gather = ds.path == 1 && c->gathered;
+        const void* src_cnt = from_gather ? (const void*)(c->d + c->o_cnt_all) : (const void*)h->pb.out_count;
+        const void* src_msk = from_gather ? (const void*)(c->d + c->o_msk_all) : (const void*)h->pb.out_mask;
+        SCU(h, cudaMemcpyAsync(h->h_out, src_cnt, nb_cnt, cudaMemcpyDeviceToHost, h->stream));
+        SCU(h, cudaMemcpyAsync(h->h_out + al(nb_cnt), src_msk, nb_msk, cudaMemcpyDeviceToHost, h->stream));
+        SCU(h, cudaStreamSynchronize(h->stream));
+        std::memcpy(out->gpu_count, h->h_out, nb_cnt);
+        std::memcpy(out->gpu_mask, h->h_out + al(nb_cnt), nb_msk);
+    }
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->candidates = ds.candidates; stats->visited_nodes = ds.visited_nodes; stats->geometry_evals = ds.geometry_evals;
+        stats->placements = ds.placements; stats->candidate_nodes = ds.candidate_nodes;
+        stats->lacking_at_start = ds.lacking_at_start; stats->lacking_at_end = ds.lacking_at_end;
+        stats->path = ds.path; stats->kernel_launches = h->launches;
+        cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
+        cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
+        cudaEventElapsedTime(&stats->ms_tracker, h->ev[6], h->ev[7]);
+        cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
+        cudaEventElapsedTime(&stats->ms_sweep, h->ev[8], h->ev[3]);
+        stats->h2d_bytes = (int64_t)h->h2d_bytes;
+        stats->d2h_bytes = (int64_t)(nb_cnt + nb_msk + sizeof ds);
+    }
+    return NOSPLAN_OK;
+}

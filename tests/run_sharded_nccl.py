@@ -1,6 +1,7 @@
 """Multi-GPU parity check of the node-sharded Plan() over real NCCL (not collected by pytest: launch with
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tests/run_sharded_nccl.py
-Every rank compares the gathered plan with the CPU oracle and prints one line."""
+Both drivers are exercised -- collectives issued by torch.distributed (nos_b200/sharded.py) and by the library itself
+(nosplan_run_sharded) -- and every rank compares the gathered plan with the CPU oracle and prints one line per case."""
 import os
 import sys
 
@@ -15,31 +16,39 @@ import torch.distributed as dist
 from nos_b200 import capi, packing as pk, sharded, synth
 from support import oracle_lib as ol
 
+KEYS = ("candidates", "visited_nodes", "placements", "geometry_evals", "lacking_at_end")
+
 
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    eng = capi.Engine(local)
+    uid = [eng.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    eng.shard_init(rank, world, uid[0])
     ok = True
     for shape, regime in (((4000, 8, 3000), "saturating"), ((1001, 8, 2000), "saturating"), ((500, 8, 900), "satisfiable")):
         snap, pods = synth.mig_cluster(*shape, seed=31, regime=regime)
-        eng = capi.Engine(local)
+        ocnt, omsk, ost, _ = ol.plan(snap, pods, None, pk.FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+        # (a) collectives through torch.distributed
         eng.upload(snap, pods, None, pk.FILTER_RESOURCES_FIT)
         pl = sharded.ShardedPlanner(eng, rank, world, dev)
         pl.prepare(snap.n_nodes, snap.gpus_per_node)
         pl.run(gather_plan=True)
         cnt_l, msk_l, st = eng.download()
-        ocnt, omsk, ost, _ = ol.plan(snap, pods, None, pk.FILTER_RESOURCES_FIT, ol.INCREMENTAL)
-        if st["path"] == 1:
-            cnt, msk = pl.plan()
-        else:
-            cnt, msk = cnt_l, msk_l
-        same = np.array_equal(cnt, ocnt) and np.array_equal(msk, omsk) and all(
-            st[k] == ost[k] for k in ("candidates", "visited_nodes", "placements", "geometry_evals", "lacking_at_end"))
-        ok &= same
-        print(f"rank {rank}/{world} {shape} {regime}: path={st['path']} parity={'OK' if same else 'MISMATCH'}", flush=True)
-        eng.close()
+        cnt, msk = pl.plan() if st["path"] == 1 else (cnt_l, msk_l)
+        same_a = np.array_equal(cnt, ocnt) and np.array_equal(msk, omsk) and all(st[k] == ost[k] for k in KEYS)
+        # (b) collectives inside the library
+        eng.upload(snap, pods, None, pk.FILTER_RESOURCES_FIT)
+        eng.run_sharded(True)
+        cnt, msk, st2 = eng.download_sharded()
+        same_b = np.array_equal(cnt, ocnt) and np.array_equal(msk, omsk) and all(st2[k] == ost[k] for k in KEYS)
+        ok &= same_a and same_b
+        print(f"rank {rank}/{world} {shape} {regime}: path={st['path']}/{st2['path']} torch-collectives={'OK' if same_a else 'MISMATCH'} "
+              f"library-collectives={'OK' if same_b else 'MISMATCH'}", flush=True)
+    eng.close()
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
