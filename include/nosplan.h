@@ -138,6 +138,12 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
                  const uint8_t* prefilter_ok, int32_t filter_mode,
                  nosplan_partitioning* out, nosplan_stats* stats);
 
+/* Host-only: the pod order the engine derives before uploading.  Replaces: NewPodSorter(...).Sort (core/util.go:34-73):
+ * stable by priority descending, then by SmallerThan of the first requested profile.  order_out[k] = index of the k-th pod.
+ * Where that comparator is a strict weak order on the pods present, a counting sort is used (every stable sort agrees);
+ * otherwise Go 1.18's sort.SliceStable (insertion sort of 20 + symMerge) is executed step for step.  Needs no GPU. */
+int nosplan_host_pod_order(const nosplan_snapshot* snap, const nosplan_pods* pods, int32_t* order_out);
+
 /* The same call split in three so the planning kernels can be timed with the snapshot resident in
  * HBM: upload() packs and copies, run() launches the kernels on the handle's stream (repeatable),
  * download() copies the plan back.  cuda_stream of the handle is exposed for CUDA-event timing. */

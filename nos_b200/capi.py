@@ -23,7 +23,22 @@ EXPORTED_SYMBOLS = [
     "nosplan_lacking_static", "nosplan_quota_recompute", "nosplan_quota_victims",
     "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
+    "nosplan_host_pod_order",
 ]
+
+
+def host_pod_order(snap: PackedSnapshot, pods: PackedPods, lib_path: str = None) -> np.ndarray:
+    """nosplan_host_pod_order: NewPodSorter order as the engine computes it (host only, no GPU needed)."""
+    lib = C.CDLL(lib_path or LIB_PATH)
+    lib.nosplan_host_pod_order.argtypes = [C.POINTER(CSnapshot), C.POINTER(CPods), C.c_void_p]
+    lib.nosplan_host_pod_order.restype = C.c_int
+    cs, k1 = c_snapshot(snap)
+    cp, k2 = c_pods(pods)
+    order = np.zeros(max(1, pods.n_pods), np.int32)
+    rc = lib.nosplan_host_pod_order(C.byref(cs), C.byref(cp), order.ctypes.data)
+    if rc != 0:
+        raise NosplanError(f"nosplan_host_pod_order failed ({rc})")
+    return order[:pods.n_pods]
 STATIC_MAX_KEYS = 16384
 
 
@@ -114,6 +129,27 @@ def c_pods(pp: PackedPods):
     cp.scalar_ptr, cp.scalar_col = p(pp.scalar_ptr, np.int32), p(pp.scalar_col, np.int32)
     cp.scalar_qty = p(pp.scalar_qty, np.int64)
     return cp, keep
+
+
+_PINNED_FIELDS = ("node_gpu_count", "gpu_model", "gpu_index", "gpu_memory_gb", "gpu_used", "gpu_free", "gpu_used_mask",
+                  "gpu_free_mask", "node_alloc", "node_requested", "node_allowed_pods", "node_num_pods")
+
+
+def pin_snapshot(s: PackedSnapshot) -> PackedSnapshot:
+    """Copy of `s` whose per-node arrays live in page-locked host memory (allocated through torch), so nosplan_upload can
+    DMA them without staging.  The torch tensors are kept alive on the returned object."""
+    import copy
+
+    import torch
+    out = copy.copy(s)
+    keep = []
+    for name in _PINNED_FIELDS:
+        a = np.ascontiguousarray(getattr(s, name))
+        t = torch.from_numpy(a.view(np.uint8).reshape(-1).copy() if a.size else np.zeros(0, np.uint8)).pin_memory()
+        keep.append(t)
+        setattr(out, name, t.numpy().view(a.dtype).reshape(a.shape))
+    out._pinned_keep = keep
+    return out
 
 
 def alloc_partitioning(s: PackedSnapshot):

@@ -3,7 +3,9 @@
 // There is no CPU planning path in this file: everything the reference's Plan() computes per node and per
 // pod happens in the kernels of prepass.cu / sweep.cu.
 #include <algorithm>
+#include <chrono>
 #include <climits>
+#include <cstdlib>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -135,6 +137,93 @@ int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes) {
 
 }  // namespace
 
+// NewPodSorter (core/util.go:34-73): order[k] = original index of the k-th pod.  first_prof[i] = lowest requested profile id
+// of pod i (the canonical "first key" of the reference's map iteration) or -1.
+static void pod_order(const nosplan_snapshot* s, const nosplan_pods* pods, const int* first_prof_ptr, std::vector<int>& order) {
+    const int P = pods->n_pods, K = s->n_profiles;
+    const bool mig = s->kind == NOSPLAN_KIND_MIG;
+    order.resize(P);
+    for (int i = 0; i < P; ++i) order[i] = i;
+    const int* fp = first_prof_ptr;
+        const int32_t* prio = pods->priority; const int32_t* pmem = s->profile_mem_gb; const int32_t* pgi = s->profile_gi;
+        auto smaller = [=](int x, int y) {                                    // SmallerThan: mig/profile.go:84-96, slicing/profile.go:36-42
+            if (pmem[x] < pmem[y]) return true;
+            return mig && pgi[x] < pgi[y];
+        };
+        // Fast path.  Where the comparator is a strict weak order on the pods present, EVERY stable sort returns what Go's
+        // sort.SliceStable returns, so a counting sort by (priority desc, profile rank) is exact.  That needs (a) SmallerThan
+        // restricted to the first-requested profiles present to be asymmetric with transitive incomparability, and (b) no
+        // priority level mixing slice-less pods (incomparable to everything) with pods of two different profile ranks.
+        bool swo = true;
+        int rank_of[KP];
+        {
+            bool present[KP] = {false};
+            for (int i = 0; i < P; ++i) if (fp[i] >= 0) present[fp[i]] = true;
+            for (int x = 0; x < K && swo; ++x) for (int y = 0; y < K && swo; ++y) {
+                if (!present[x] || !present[y]) continue;
+                if (smaller(x, y) && smaller(y, x)) swo = false;
+                for (int z = 0; z < K && swo; ++z) {
+                    if (!present[z]) continue;
+                    if (smaller(x, y) && smaller(y, z) && !smaller(x, z)) swo = false;
+                    const bool ixy = !smaller(x, y) && !smaller(y, x), iyz = !smaller(y, z) && !smaller(z, y), ixz = !smaller(x, z) && !smaller(z, x);
+                    if (ixy && iyz && !ixz) swo = false;
+                }
+            }
+            for (int x = 0; x < K; ++x) {
+                rank_of[x] = 0;
+                if (present[x]) for (int y = 0; y < K; ++y) if (present[y] && smaller(y, x)) ++rank_of[x];
+            }
+        }
+        std::vector<std::pair<long long, int>> keyed;          // (sort key, original index) of one stable counting sort
+        if (swo) {
+            struct Level { int lo = INT_MAX, hi = INT_MIN; bool slice_less = false; };
+            std::vector<std::pair<int32_t, Level>> levels;      // distinct priorities are few: linear probe with last-hit cache
+            size_t last = 0;
+            auto level_of = [&](int32_t p) -> Level& {
+                if (last < levels.size() && levels[last].first == p) return levels[last].second;
+                for (size_t k = 0; k < levels.size(); ++k) if (levels[k].first == p) { last = k; return levels[k].second; }
+                levels.emplace_back(p, Level()); last = levels.size() - 1;
+                return levels.back().second;
+            };
+            for (int i = 0; i < P && levels.size() <= 4096; ++i) {
+                Level& l = level_of(prio[i]);
+                if (fp[i] < 0) l.slice_less = true;
+                else { l.lo = std::min(l.lo, rank_of[fp[i]]); l.hi = std::max(l.hi, rank_of[fp[i]]); }
+            }
+            if (levels.size() > 4096) swo = false;              // pathological: leave it to the general sort
+            for (auto& kv : levels) if (kv.second.slice_less && kv.second.lo < kv.second.hi) swo = false;
+            if (swo) {
+                // all pods of a level with slice-less members are equivalent (single rank): key = priority only there
+                // counting sort (stable) by (priority desc, rank asc)
+                std::vector<int> by_prio(levels.size());
+                for (size_t k = 0; k < levels.size(); ++k) by_prio[k] = (int)k;
+                std::sort(by_prio.begin(), by_prio.end(), [&](int a, int b) { return levels[a].first > levels[b].first; });
+                std::vector<int> pos_of_level(levels.size());
+                for (size_t k = 0; k < levels.size(); ++k) pos_of_level[by_prio[k]] = (int)k;
+                const int stride = KP + 1;
+                std::vector<int> count(levels.size() * stride + 1, 0), bucket(P);
+                for (int i = 0; i < P; ++i) {
+                    Level& l = level_of(prio[i]);
+                    const int r = (l.slice_less || fp[i] < 0) ? 0 : rank_of[fp[i]];
+                    bucket[i] = pos_of_level[last] * stride + r;
+                    ++count[bucket[i] + 1];
+                }
+                for (size_t k = 1; k < count.size(); ++k) count[k] += count[k - 1];
+                for (int i = 0; i < P; ++i) order[count[bucket[i]]++] = i;
+                (void)keyed;
+            }
+        }
+        if (!swo) {
+            auto less = [=](int a, int b) {
+                if (prio[a] != prio[b]) return prio[a] > prio[b];
+                if (fp[a] < 0 || fp[b] < 0) return false;
+                return smaller(fp[a], fp[b]);
+            };
+            GoStable<decltype(less)> gs{order.data(), P, less};
+            gs.run();
+        }
+}
+
 int nosplan_fail(nosplan* h, int code, const char* fmt, ...) {
     char buf[512];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
@@ -181,11 +270,34 @@ const char* nosplan_last_error(const nosplan_t* h) { return h ? h->err.c_str() :
 
 void* nosplan_stream(nosplan_t* h) { return h ? (void*)h->stream : nullptr; }
 
+int nosplan_host_pod_order(const nosplan_snapshot* s, const nosplan_pods* pods, int32_t* order_out) {
+    if (!s || !pods || (!order_out && pods->n_pods > 0)) return NOSPLAN_E_INVALID;
+    const int P = pods->n_pods, K = s->n_profiles;
+    if (K < 0 || K > NOSPLAN_MAX_PROFILES || P < 0) return NOSPLAN_E_INVALID;
+    std::vector<int> first_prof(P, -1), order;
+    for (int i = 0; i < P; ++i)
+        for (int e = pods->scalar_ptr[i]; e < pods->scalar_ptr[i + 1]; ++e)
+            if (pods->scalar_col[e] >= 3 && pods->scalar_col[e] < 3 + K) { first_prof[i] = pods->scalar_col[e] - 3; break; }
+    pod_order(s, pods, first_prof.data(), order);
+    for (int i = 0; i < P; ++i) order_out[i] = order[i];
+    return NOSPLAN_OK;
+}
+
 int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
                    int32_t filter_mode) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!s || !pods) return fail(h, NOSPLAN_E_INVALID, "null snapshot or pods");
     h->uploaded = h->ran = false;
+    // NOSPLAN_TRACE=1: per-phase host microseconds of this call on stderr
+    static const bool trace = getenv("NOSPLAN_TRACE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto t_prev = now();
+    auto lap = [&](const char* what) {
+        if (!trace) return;
+        auto t = now();
+        fprintf(stderr, "[nosplan_upload] %-12s %8.1f us\n", what, std::chrono::duration<double, std::micro>(t - t_prev).count());
+        t_prev = t;
+    };
     const int K = s->n_profiles, N = s->n_nodes, G = s->gpus_per_node, P = pods->n_pods;
     const int R = 3 + K + s->n_other;
     if (s->kind != NOSPLAN_KIND_MIG && s->kind != NOSPLAN_KIND_MPS) return fail(h, NOSPLAN_E_INVALID, "unknown kind %d", s->kind);
@@ -212,6 +324,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
             }
     }
 
+    lap("validate");
     // ---- per-pod sort keys and validation
     const int nnz = P > 0 ? pods->scalar_ptr[P] : 0;
     std::vector<int> first_prof(P, -1);
@@ -241,22 +354,12 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     }
     if (n_keys > sweep_max_keys()) return fail(h, NOSPLAN_E_LIMIT, "%d tracker keys > %d", n_keys, sweep_max_keys());
 
+    lap("pod keys");
     // ---- NewPodSorter (core/util.go:34-73)
-    std::vector<int> order(P);
-    for (int i = 0; i < P; ++i) order[i] = i;
-    {
-        const int32_t* prio = pods->priority; const int32_t* pmem = s->profile_mem_gb; const int32_t* pgi = s->profile_gi;
-        const int* fp = first_prof.data();
-        auto less = [=](int a, int b) {
-            if (prio[a] != prio[b]) return prio[a] > prio[b];
-            if (fp[a] < 0 || fp[b] < 0) return false;
-            if (pmem[fp[a]] < pmem[fp[b]]) return true;                       // SmallerThan: mig/profile.go:84-96, slicing/profile.go:36-42
-            return mig && pgi[fp[a]] < pgi[fp[b]];
-        };
-        GoStable<decltype(less)> gs{order.data(), P, less};
-        gs.run();
-    }
+    std::vector<int> order;
+    pod_order(s, pods, first_prof.data(), order);
 
+    lap("sort");
     // ---- runs of identical slice requests in sorted order
     std::vector<RunRec> runs;
     auto same_slices = [&](int x, int y) {
@@ -304,6 +407,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         }
     }
 
+    lap("runs+chunks");
     // ---- layout
     Layout L; size_t o = 0;
     auto put = [&](size_t& field, size_t bytes) { field = o; o = al(o + bytes); };
@@ -336,23 +440,30 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     int rc = ensure(h, L.total, L.upload_end, out_bytes);
     if (rc != NOSPLAN_OK) return rc;
 
+    lap("layout+alloc");
     // ---- stage (one pinned buffer, one H2D copy)
     unsigned char* S = h->h_stage;
     if (n_models > 0) std::memcpy(S + L.model_off, s->model_geom_offset, sizeof(int32_t) * (n_models + 1));
     else std::memset(S + L.model_off, 0, sizeof(int32_t));
     if (n_rows) std::memcpy(S + L.geom, s->geom_counts, 16 * (size_t)n_rows);
+    // The node arrays are most of the bytes.  If the caller keeps them in page-locked memory (cudaHostAlloc /
+    // cudaHostRegister), the DMA engine reads them where they are; otherwise they go through the pinned staging buffer.
+    struct Seg { size_t off; const void* src; size_t bytes; bool direct; };
+    Seg segs[11] = {
+        {L.node_gpu_count, s->node_gpu_count, 4 * (size_t)N, false}, {L.gpu_model, s->gpu_model, 4 * NG, false},
+        {L.gpu_mem, s->gpu_memory_gb, 4 * NG, false}, {L.gpu_used, s->gpu_used, 16 * NG, false}, {L.gpu_free, s->gpu_free, 16 * NG, false},
+        {L.gpu_umask, s->gpu_used_mask, 2 * NG, false}, {L.gpu_fmask, s->gpu_free_mask, 2 * NG, false},
+        {L.node_alloc, s->node_alloc, 8 * (size_t)N * R, false}, {L.node_req, s->node_requested, 8 * (size_t)N * R, false},
+        {L.node_allowed, s->node_allowed_pods, 4 * (size_t)N, false}, {L.node_npods, s->node_num_pods, 4 * (size_t)N, false}};
+    bool any_direct = false;
     if (N) {
-        std::memcpy(S + L.node_gpu_count, s->node_gpu_count, 4 * (size_t)N);
-        std::memcpy(S + L.gpu_model, s->gpu_model, 4 * NG);
-        std::memcpy(S + L.gpu_mem, s->gpu_memory_gb, 4 * NG);
-        std::memcpy(S + L.gpu_used, s->gpu_used, 16 * NG);
-        std::memcpy(S + L.gpu_free, s->gpu_free, 16 * NG);
-        std::memcpy(S + L.gpu_umask, s->gpu_used_mask, 2 * NG);
-        std::memcpy(S + L.gpu_fmask, s->gpu_free_mask, 2 * NG);
-        std::memcpy(S + L.node_alloc, s->node_alloc, 8 * (size_t)N * R);
-        std::memcpy(S + L.node_req, s->node_requested, 8 * (size_t)N * R);
-        std::memcpy(S + L.node_allowed, s->node_allowed_pods, 4 * (size_t)N);
-        std::memcpy(S + L.node_npods, s->node_num_pods, 4 * (size_t)N);
+        for (Seg& g : segs) {
+            cudaPointerAttributes at;
+            g.direct = g.bytes >= 4096 && cudaPointerGetAttributes(&at, g.src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+            if (g.direct) any_direct = true;
+            else std::memcpy(S + g.off, g.src, g.bytes);
+        }
+        (void)cudaGetLastError();
     }
     {
         long long* cpu = (long long*)(S + L.pod_cpu); long long* mem = (long long*)(S + L.pod_mem); long long* eph = (long long*)(S + L.pod_eph);
@@ -376,8 +487,21 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         }
     }
 
+    lap("stage");
     CU(h, cudaEventRecord(h->ev[0], h->stream));
-    CU(h, cudaMemcpyAsync(h->d_arena, S, L.upload_end, cudaMemcpyHostToDevice, h->stream));
+    if (!any_direct) CU(h, cudaMemcpyAsync(h->d_arena, S, L.upload_end, cudaMemcpyHostToDevice, h->stream));
+    else {
+        // staged ranges around and between the direct segments, then the direct segments themselves
+        size_t from = 0;
+        for (const Seg& g : segs) {
+            if (!g.direct) continue;
+            if (g.off > from) CU(h, cudaMemcpyAsync(h->d_arena + from, S + from, g.off - from, cudaMemcpyHostToDevice, h->stream));
+            CU(h, cudaMemcpyAsync(h->d_arena + g.off, g.src, g.bytes, cudaMemcpyHostToDevice, h->stream));
+            from = al(g.off + g.bytes);
+        }
+        if (L.upload_end > from) CU(h, cudaMemcpyAsync(h->d_arena + from, S + from, L.upload_end - from, cudaMemcpyHostToDevice, h->stream));
+    }
+    h->direct_h2d = any_direct;
     CU(h, cudaMemsetAsync(h->d_arena + L.out_count, 0, L.total - L.out_count, h->stream));
     CU(h, cudaEventRecord(h->ev[1], h->stream));
 
@@ -426,8 +550,10 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     h->d_cand_idx = (int32_t*)(A + L.cand_idx);
     h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot;
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
+    lap("enqueue h2d");
     h->h2d_bytes = L.upload_end;
     h->uploaded = true;
+    if (any_direct && !h->in_plan) CU(h, cudaStreamSynchronize(h->stream));   // nothing of the caller's is read after return
     return NOSPLAN_OK;
 }
 
@@ -547,10 +673,13 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
 
 int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods* pods, const uint8_t* prefilter_ok,
                  int32_t filter_mode, nosplan_partitioning* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    h->in_plan = true;                               // download() below synchronises before this call returns
     int rc = nosplan_upload(h, snap, pods, prefilter_ok, filter_mode);
-    if (rc != NOSPLAN_OK) return rc;
+    h->in_plan = false;
+    if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); return rc; }
     rc = nosplan_run(h);
-    if (rc != NOSPLAN_OK) return rc;
+    if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); return rc; }
     return nosplan_download(h, out, stats);
 }
 
