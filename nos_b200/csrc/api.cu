@@ -107,7 +107,7 @@ struct Layout {            // byte offsets into the arena / staging buffer
         node_alloc, node_req, node_allowed, node_npods,
         pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
         cmin_cpu, cmin_mem, cmin_eph, upload_end,
-        tot, lack, stats, maxfree, gflags, acc, placed, entry_lack, work_end, cand_flag, cand_idx, out_count, out_mask, total;
+        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, placed, entry_lack, work_end, cand_flag, cand_idx, out_count, out_mask, total;
 };
 
 int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes) {
@@ -381,6 +381,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
             const long long q = pods->scalar_qty[e];
             r.q[pods->scalar_col[e] - 3] = (uint16_t)std::min<long long>(q, 65535);   // device counts are <= 255: anything larger can never fit
             r.n_ent++;
+            r.p_single = (uint16_t)(pods->scalar_col[e] - 3);
         }
         runs.push_back(r);
     }
@@ -428,7 +429,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
     L.upload_end = o;
     put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats));
-    put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.placed, 4 * (((size_t)n_keys + 31) / 32));
+    put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.lack_dec, 4 * KP); put(L.next_node, 16); put(L.placed, 4 * (((size_t)n_keys + 31) / 32));
     put(L.entry_lack, 4 * (size_t)n_keys * KP);
     L.work_end = o;
     put(L.cand_flag, (size_t)N); put(L.cand_idx, 4 * (size_t)N);
@@ -543,6 +544,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     }
     pb.maxfree = (int32_t*)(A + L.maxfree); pb.gflags = (int32_t*)(A + L.gflags);
     pb.acc = (unsigned long long*)(A + L.acc); pb.placed = (unsigned*)(A + L.placed);
+    pb.lack_dec = (int32_t*)(A + L.lack_dec); pb.next_node = (int32_t*)(A + L.next_node); pb.whole_snapshot = 1;
     pb.tot = (long long*)(A + L.tot); pb.lack = (int32_t*)(A + L.lack); pb.stats = (DevStats*)(A + L.stats);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
     pb.cand_flag = (uint8_t*)(A + L.cand_flag);
@@ -598,6 +600,7 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
     launch_tracker_init(h->pb, h->stream);
     CU(h, cudaEventRecord(h->ev[7], h->stream));
     DevProblem shard = h->pb;                               // this rank's slice of the name-ordered node list
+    shard.whole_snapshot = 0;
     const int chunk = (h->pb.N + world - 1) / world;        // equal-sized slices (the last may be short) so the rows all-gather
     shard.node_lo = std::min(h->pb.N, rank * chunk);
     shard.node_hi = std::min(h->pb.N, shard.node_lo + chunk);
@@ -616,7 +619,9 @@ int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world) {
     if (!d_gathered || world < 1) return fail(h, NOSPLAN_E_INVALID, "null gathered buffer");
     CU(h, cudaSetDevice(h->device));
     launch_shard_combine(h->pb, d_gathered, world, (size_t)nosplan_shard_exchange_bytes(h), h->stream);
-    CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
+    DevProblem verify = h->pb;
+    verify.whole_snapshot = 0;                               // final lacking vector comes from the OR-ed bitmap
+    CU(h, launch_sweep(verify, h->d_cand_idx, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
     h->launches += 2;
     h->ran = true;

@@ -24,7 +24,8 @@ struct __align__(16) RunRec {
     int32_t start, len;
     uint16_t q[KP];        // requested quantity per profile id, 0 = not requested
     uint16_t n_ent;        // number of requested profiles
-    uint16_t pad[3];
+    uint16_t p_single;     // the profile id when n_ent == 1
+    uint16_t pad[2];
 };
 static_assert(sizeof(RunRec) == 48, "RunRec layout");
 
@@ -82,6 +83,9 @@ struct DevProblem {
     int32_t* gflags;                 // [4]  [0] some node's Allocatable/Requested disagree with its GPUs' used/free
     unsigned* placed;                // [(n_keys+31)/32] tracker keys placed by the node-parallel pass
     unsigned long long* acc;         // [4]  placements, geometry evals, visited, candidate nodes of the node-parallel pass
+    int32_t* lack_dec;               // [KP] lacking quantities removed by the node-parallel pass (single-rank runs)
+    int32_t* next_node;              // [1]  work counter of the node-parallel pass
+    int whole_snapshot;              // the node-parallel pass covers every node on this rank (no exchange needed)
     // outputs
     uint4* out_count;                // [N*G]
     uint16_t* out_mask;              // [N*G]

@@ -150,11 +150,15 @@ __device__ __forceinline__ unsigned score_word(unsigned row, unsigned used, unsi
 }
 
 __device__ __forceinline__ unsigned score_row(const uint4& row, const uint4& used, const uint4& fre, const ReqPack& rp, int K) {
-    const bool can = (__vcmpgeu4(row.x, used.x) & __vcmpgeu4(row.y, used.y) & __vcmpgeu4(row.z, used.z) & __vcmpgeu4(row.w, used.w)) == 0xffffffffu;
+    // bytes of profiles >= K are zero in row, used and free, so only the words below K matter
+    unsigned can = __vcmpgeu4(row.x, used.x);
     unsigned score = score_word(row.x, used.x, fre.x, rp.rq.x, rp.big.x);
-    if (K > 4) score += score_word(row.y, used.y, fre.y, rp.rq.y, rp.big.y);
-    if (K > 8) score += score_word(row.z, used.z, fre.z, rp.rq.z, rp.big.z) + score_word(row.w, used.w, fre.w, rp.rq.w, rp.big.w);
-    return can ? score : 0u;
+    if (K > 4) { can &= __vcmpgeu4(row.y, used.y); score += score_word(row.y, used.y, fre.y, rp.rq.y, rp.big.y); }
+    if (K > 8) {
+        can &= __vcmpgeu4(row.z, used.z) & __vcmpgeu4(row.w, used.w);
+        score += score_word(row.z, used.z, fre.z, rp.rq.z, rp.big.z) + score_word(row.w, used.w, fre.w, rp.rq.w, rp.big.w);
+    }
+    return can == 0xffffffffu ? score : 0u;
 }
 
 // lane p (< 16) holds required[p]; every lane gets the packed form through shared memory
@@ -281,7 +285,11 @@ __device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, un
     if (PAR) {
         if (lane == 0) {
             const unsigned bit = 1u << (key & 31);
-            if (!(removed[key >> 5] & bit)) atomicOr(&removed[key >> 5], bit);
+            if (!(removed[key >> 5] & bit) && !(atomicOr(&removed[key >> 5], bit) & bit) && pb.whole_snapshot)
+                for (int pp = 0; pp < pb.K; ++pp) {
+                    const int e = pb.entry_lack[(size_t)key * KP + pp];
+                    if (e > 0) atomicAdd(&pb.lack_dec[pp], e);
+                }
         }
         return;
     }
@@ -344,6 +352,11 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     const bool podcount_ok = nd.npods + 1 <= nd.allowed;
     const bool fit = fm == NOSPLAN_FILTER_RESOURCES_FIT;
     __syncwarp();
+    // profiles with at least one free device on some GPU of the node: a single-profile class outside this set cannot place
+    // a pod (GPU.AddPod needs free >= q >= 1), and the set only shrinks while the node is processed
+    uint4 any_free = make_uint4(0, 0, 0, 0);
+    for (int g = 0; g < ng; ++g) { const uint4 f = nd.free_[g]; any_free.x |= f.x; any_free.y |= f.y; any_free.z |= f.z; any_free.w |= f.w; }
+    const unsigned feas = nz_mask(any_free);
 
     // ---- 2. the pod loop, run by run
     int added = 0;
@@ -352,7 +365,9 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
         const bool rcached = ri < pc->n_cached;
         const bool cached = rcached && pc->cpu != nullptr;
         const RunRec* rr = rcached ? &pc->runs[ri] : &pb.runs[ri];
-        const int rstart = rr->start, rend = rr->start + rr->len, n_ent = rr->n_ent;
+        const int n_ent = rr->n_ent;
+        if (n_ent == 1 && !(feas >> rr->p_single & 1)) continue;
+        const int rstart = rr->start, rend = rr->start + rr->len;
         const int q_l = (lane < KP) ? (int)rr->q[lane] : 0;
         // class-level tests; all of them only get tighter while this node is processed
         bool ok_l = true;
@@ -444,7 +459,13 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                             if (PAR) {                                     // tracker.Remove per placed pod
                                 if (acc) {
                                     const unsigned bit = 1u << (key & 31);
-                                    if (!(removed[key >> 5] & bit)) atomicOr(&removed[key >> 5], bit);
+                                    if (!(removed[key >> 5] & bit) && !(atomicOr(&removed[key >> 5], bit) & bit) && pb.whole_snapshot) {
+                                        // this lane set the bit: it owns the entry's one and only removal (tracker.go:78-86)
+                                        for (int pp = 0; pp < K; ++pp) {
+                                            const int e = pb.entry_lack[(size_t)key * KP + pp];
+                                            if (e > 0) atomicAdd(&pb.lack_dec[pp], e);
+                                        }
+                                    }
                                 }
                             } else {
                                 unsigned todo = accm;
@@ -617,8 +638,12 @@ __global__ void __launch_bounds__(128) k_plan_parallel(DevProblem pb) {
     int lack = lack0 > 0 ? SATURATED : 0;
     long long D = 0, st_evals = 0, st_place = 0, visited = 0;
     bool committed = true;
-    const int warps_total = gridDim.x * (blockDim.x >> 5);
-    for (int i = pb.node_lo + blockIdx.x * (blockDim.x >> 5) + warp; i < pb.node_hi; i += warps_total) {
+    // dynamic distribution: nodes differ a lot in cost (how many runs are feasible), so warps pull the next node
+    for (;;) {
+        int i = 0;
+        if (lane == 0) i = pb.node_lo + atomicAdd(pb.next_node, 1);
+        i = __shfl_sync(FULL, i, 0);
+        if (i >= pb.node_hi) break;
         if (!pb.cand_flag[i]) continue;
         NodeRegs nr;
         load_node(pb, i, lane, nr);
@@ -665,9 +690,9 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
 
     // ---------------- did the node-parallel pass run, and did its hypothesis hold to the end?
     if (fast_applicable(pb, lack0, lane)) {
-        if (tid < KP) s_lackend[tid] = pb.lack[tid];
+        if (tid < KP) s_lackend[tid] = pb.lack[tid] - (pb.whole_snapshot ? pb.lack_dec[tid] : 0);
         __syncthreads();
-        for (int k = tid; k < pb.n_keys; k += blockDim.x)
+        for (int k = tid; !pb.whole_snapshot && k < pb.n_keys; k += blockDim.x)
             if (pb.placed[k >> 5] >> (k & 31) & 1)
                 for (int p = 0; p < pb.K; ++p) {
                     const int e = pb.entry_lack[(size_t)k * KP + p];
