@@ -15,7 +15,7 @@ import numpy as np
 from .packing import PackedPods, PackedSnapshot
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnosplan.so")
+LIB_PATH = os.environ.get("NOSPLAN_LIB") or os.path.join(_HERE, "libnosplan.so")
 
 EXPORTED_SYMBOLS = [
     "nosplan_create", "nosplan_destroy", "nosplan_last_error", "nosplan_plan",
