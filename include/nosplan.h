@@ -152,6 +152,9 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pod
 int nosplan_run(nosplan_t* h);
 int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats);
 void* nosplan_stream(nosplan_t* h);    /* cudaStream_t */
+/* CUDA events between the kernels of a run feed the per-kernel times of nosplan_stats (default on); switching them off
+ * removes their few microseconds from a Plan(). */
+int nosplan_set_kernel_events(nosplan_t* h, int32_t on);
 
 /* Node-sharded Plan() over `world` ranks -- one handle per rank (one process per GPU), the SAME snapshot uploaded on
  * every rank (the reference's Plan() is single-process, core/planner.go:67-153, so there is no

@@ -23,7 +23,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_lacking_static", "nosplan_quota_recompute", "nosplan_quota_victims",
     "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
-    "nosplan_host_pod_order",
+    "nosplan_host_pod_order", "nosplan_set_kernel_events",
 ]
 
 
@@ -289,6 +289,10 @@ class Engine:
         st = CStats()
         self._check(self.lib.nosplan_download(self.h, C.byref(out), C.byref(st)), "nosplan_download")
         return cnt, msk, st.as_dict()
+
+    def set_kernel_events(self, on: bool):
+        self.lib.nosplan_set_kernel_events.argtypes = [C.c_void_p, C.c_int32]
+        self._check(self.lib.nosplan_set_kernel_events(self.h, 1 if on else 0), "nosplan_set_kernel_events")
 
     def stream(self) -> int:
         return int(self.lib.nosplan_stream(self.h) or 0)

@@ -266,6 +266,12 @@ void nosplan_destroy(nosplan_t* h) {
     delete h;
 }
 
+int nosplan_set_kernel_events(nosplan_t* h, int32_t on) {
+    if (!h) return NOSPLAN_E_INVALID;
+    h->kernel_events = on != 0;
+    return NOSPLAN_OK;
+}
+
 const char* nosplan_last_error(const nosplan_t* h) { return h ? h->err.c_str() : "null handle"; }
 
 void* nosplan_stream(nosplan_t* h) { return h ? (void*)h->stream : nullptr; }
@@ -343,6 +349,8 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
                 if (pods->scalar_qty[e] <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
             } else other = true;
         }
+        if (pods->base[3 * (size_t)i] < 0 || pods->base[3 * (size_t)i + 1] < 0 || pods->base[3 * (size_t)i + 2] < 0)
+            return fail(h, NOSPLAN_E_INVALID, "pod %d: negative cpu / memory / ephemeral-storage request", i);
         uint32_t f = 0;
         if (!prefilter_ok || prefilter_ok[i]) f |= PF_PRE_OK;
         if (other) f |= PF_HAS_OTHER;
@@ -566,12 +574,12 @@ int nosplan_run(nosplan_t* h) {
     CU(h, cudaEventRecord(h->ev[2], h->stream));
     CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
     launch_prepass(h->pb, h->stream);
-    CU(h, cudaEventRecord(h->ev[6], h->stream));
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
     launch_tracker_init(h->pb, h->stream);
-    CU(h, cudaEventRecord(h->ev[7], h->stream));
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[7], h->stream));
     CU(h, cudaGetLastError());
     CU(h, launch_parallel(h->pb, h->stream));
-    CU(h, cudaEventRecord(h->ev[8], h->stream));
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
     CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
     h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
@@ -596,9 +604,9 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
     CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
     CU(h, cudaMemsetAsync(d_exchange, 0, (size_t)need, h->stream));
     launch_prepass(h->pb, h->stream);                       // replicated: cheaper than exchanging the totals
-    CU(h, cudaEventRecord(h->ev[6], h->stream));
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
     launch_tracker_init(h->pb, h->stream);
-    CU(h, cudaEventRecord(h->ev[7], h->stream));
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[7], h->stream));
     DevProblem shard = h->pb;                               // this rank's slice of the name-ordered node list
     shard.whole_snapshot = 0;
     const int chunk = (h->pb.N + world - 1) / world;        // equal-sized slices (the last may be short) so the rows all-gather
@@ -608,7 +616,7 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
     shard.placed = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(d_exchange) + 32);
     CU(h, cudaGetLastError());
     CU(h, launch_parallel(shard, h->stream));
-    CU(h, cudaEventRecord(h->ev[8], h->stream));
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
     h->launches = (h->pb.N > 0) + (h->pb.P > 0) + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     return NOSPLAN_OK;
 }
@@ -664,10 +672,12 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         cudaEventElapsedTime(&stats->ms_h2d, h->ev[0], h->ev[1]);
         cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
         cudaEventElapsedTime(&stats->ms_d2h, h->ev[4], h->ev[5]);
-        cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
-        cudaEventElapsedTime(&stats->ms_tracker, h->ev[6], h->ev[7]);
-        cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
-        cudaEventElapsedTime(&stats->ms_sweep, h->ev[8], h->ev[3]);
+        if (h->kernel_events) {
+            cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
+            cudaEventElapsedTime(&stats->ms_tracker, h->ev[6], h->ev[7]);
+            cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
+            cudaEventElapsedTime(&stats->ms_sweep, h->ev[8], h->ev[3]);
+        }
         stats->path = ds.path;
         stats->kernel_launches = h->launches;
         stats->h2d_bytes = (int64_t)h->h2d_bytes;

@@ -17,6 +17,7 @@ struct nosplan {
     unsigned char* h_out = nullptr; size_t h_out_cap = 0;
     // current problem
     bool uploaded = false, ran = false;
+    bool kernel_events = true;                  // CUDA events between the kernels of a run (per-kernel times in nosplan_stats)
     bool in_plan = false, direct_h2d = false;   // H2D straight from page-locked caller memory (see nosplan_upload)
     nsp::DevProblem pb{};
     int32_t* d_cand_idx = nullptr;

@@ -384,7 +384,8 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
             const int q = n_ent ? __shfl_sync(FULL, q_l, p) : 0;
             long long cap = CAP_INF;
             if (n_ent) {
-                const int cg = (lane < ng) ? (int)bytes(nd.free_[lane])[p] / q : 0;           // GPU.AddPod feasibility
+                const int fr0 = (lane < ng) ? (int)bytes(nd.free_[lane])[p] : 0;
+                const int cg = q == 1 ? fr0 : fr0 / q;                                        // GPU.AddPod feasibility
                 cap = warp_sum_int(cg);
                 if (!PAR) cap = min(cap, ws.Dg[p] / q);
                 if (fit) cap = min(cap, (ws.allocF[p] - ws.reqF[p]) / q);
@@ -430,22 +431,30 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                         if (vm == 0 && stop == 32) break;
                         const int rank = __popc(vm & ((1u << lane) - 1));
                         const bool cand = valid && rank < cap;
-                        bool test = cand;
+                        // totals of the candidates first: if they all fit together (the common case) no prefix sums are needed
+                        long long sc = 0, sm = 0, se = 0;
+                        int firstfail = 32;
                         if (fit) {
-                            const long long ec = warp_excl_ll(cand ? cpu : 0, lane), em = warp_excl_ll(cand ? mem : 0, lane),
-                                            ee = warp_excl_ll(cand ? eph : 0, lane);
-                            test = cand && (zero || (cpu <= remc - ec && mem <= remm - em && eph <= reme - ee));
+                            sc = warp_sum_ll(cand ? cpu : 0); sm = warp_sum_ll(cand ? mem : 0); se = warp_sum_ll(cand ? eph : 0);
+                            if (sc > remc || sm > remm || se > reme) {
+                                const long long ec = warp_excl_ll(cand ? cpu : 0, lane), em = warp_excl_ll(cand ? mem : 0, lane),
+                                                ee = warp_excl_ll(cand ? eph : 0, lane);
+                                const bool test = cand && (zero || (cpu <= remc - ec && mem <= remm - em && eph <= reme - ee));
+                                const unsigned failm = __ballot_sync(FULL, cand && !test);
+                                if (failm) {
+                                    firstfail = __ffs(failm) - 1;
+                                    sc = __shfl_sync(FULL, ec, firstfail); sm = __shfl_sync(FULL, em, firstfail); se = __shfl_sync(FULL, ee, firstfail);
+                                }
+                            }
                         }
-                        const unsigned failm = __ballot_sync(FULL, cand && !test);
-                        const int firstfail = failm ? __ffs(failm) - 1 : 32;
                         const bool acc = cand && lane < firstfail;
                         const unsigned accm = __ballot_sync(FULL, acc);
                         const int n = __popc(accm);
                         if (n > 0) {
-                            const long long sc = warp_sum_ll(acc ? cpu : 0), sm = warp_sum_ll(acc ? mem : 0), se = warp_sum_ll(acc ? eph : 0);
                             remc -= sc; remm -= sm; reme -= se;
                             if (n_ent) {                                   // first-fit over GPUs (mig/node.go:201-210)
-                                const int cg = (lane < ng) ? (int)bytes(nd.free_[lane])[p] / q : 0;
+                                const int fr1 = (lane < ng) ? (int)bytes(nd.free_[lane])[p] : 0;
+                                const int cg = q == 1 ? fr1 : fr1 / q;
                                 const int ex = warp_excl_int(cg, lane);
                                 const int take = max(0, min(cg, n - ex));
                                 if (lane < ng && take > 0) {
