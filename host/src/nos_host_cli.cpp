@@ -1,0 +1,128 @@
+// nos_host_cli -- line-oriented driver of the C++ host mirror, used by the tests to run the reference's own table
+// tests (tests/golden/*.json) through nos::core::Planner without a Go toolchain.
+//
+// stdin (tokens separated by blanks; names carry no blanks):
+//   kind mig|mps            filter <NOSPLAN_FILTER_*>        prefilter <0|1>   (constant PreFilter verdict)
+//   geometry <model> <profile>=<n>,...   (replaces the default table; one line per allowed geometry)
+//   node <name> | nilnode <key>          label <k> <v>   annotation <k> <v>   allocatable <res> <n>   requested <res> <n>
+//   numpods <n>
+//   pod <namespace> <name> <priority|->  container <res>=<n>,...|-   init <res>=<n>,...|-
+//   run plan | run pack | run state | run diff
+// stdout: `run plan`  -> "node <name>" / "gpu <index> <res>=<n>,..." lines, then "stats ..." ;
+//         `run pack`  -> one "<array> v v v" line per packed buffer;  `run state` -> the snapshot's current state;
+//         `run diff`  -> plan, then "apply <node>" per node Actuator.Apply would partition and "changed <node>".
+// Any nos::Error ends the run with "error <message>" and exit status 1.
+#include <cstdio>
+#include <iostream>
+#include <sstream>
+
+#include "nos/host.hpp"
+
+using namespace nos;
+
+static ResourceList parse_list(const std::string& s) {
+    ResourceList rl;
+    if (s == "-") return rl;
+    std::stringstream ss(s);
+    std::string item;
+    while (std::getline(ss, item, ',')) {
+        size_t eq = item.rfind('=');
+        if (eq == std::string::npos) throw Error("bad resource item " + item);
+        rl[item.substr(0, eq)] = std::stoll(item.substr(eq + 1));
+    }
+    return rl;
+}
+
+template <class T> static void dump(const char* name, const std::vector<T>& v) {
+    std::cout << name;
+    for (auto& x : v) std::cout << ' ' << (long long)x;
+    std::cout << '\n';
+}
+static void dump(const char* name, const std::vector<std::string>& v) {
+    std::cout << name;
+    for (auto& x : v) std::cout << ' ' << x;
+    std::cout << '\n';
+}
+static void print_state(const state::PartitioningState& st) {
+    for (auto& [name, np] : st) {
+        std::cout << "node " << name << '\n';
+        for (auto& g : np.GPUs) {
+            std::cout << "gpu " << g.GPUIndex << ' ';
+            bool first = true;
+            for (auto& [r, q] : g.Resources) { std::cout << (first ? "" : ",") << r << '=' << q; first = false; }
+            if (first) std::cout << '-';
+            std::cout << '\n';
+        }
+    }
+}
+
+int main() {
+    core::Kind kind = core::Kind::MIG;
+    core::SchedulerFramework fw;
+    int constPre = 1;
+    state::ClusterState cluster;
+    framework::NodeInfo* cur = nullptr;
+    std::vector<v1::Pod> pods;
+    mig::KnownGeometries custom;
+    std::string line, mode;
+    try {
+        while (std::getline(std::cin, line)) {
+            std::stringstream ss(line);
+            std::string cmd, a, b, c;
+            if (!(ss >> cmd) || cmd[0] == '#') continue;
+            ss >> a >> b >> c;
+            if (cmd == "kind") kind = a == "mps" ? core::Kind::MPS : core::Kind::MIG;
+            else if (cmd == "filter") fw.filterMode = std::stoi(a);
+            else if (cmd == "prefilter") constPre = std::stoi(a);
+            else if (cmd == "geometry") { gpu::Geometry g; for (auto& [p, q] : parse_list(b)) g[p] = (int)q; custom[a].push_back(g); }
+            else if (cmd == "node") { cur = &cluster[a]; cur->node = v1::Node{}; cur->node->name = a; }
+            else if (cmd == "nilnode") { cur = &cluster[a]; cur->node.reset(); }
+            else if (cmd == "label") cur->node->labels[a] = b;
+            else if (cmd == "annotation") cur->node->annotations[a] = b;
+            else if (cmd == "allocatable") cur->node->allocatable[a] = std::stoll(b);
+            else if (cmd == "requested") cur->requested[a] = std::stoll(b);
+            else if (cmd == "numpods") cur->numPods = std::stoi(a);
+            else if (cmd == "pod") { v1::Pod p; p.ns = a; p.name = b; if (c != "-" && !c.empty()) p.priority = std::stoi(c); pods.push_back(p); }
+            else if (cmd == "container") pods.back().containers.push_back({parse_list(a)});
+            else if (cmd == "init") pods.back().initContainers.push_back({parse_list(a)});
+            else if (cmd == "run") { mode = a; break; }
+            else throw Error("unknown directive " + cmd);
+        }
+        if (!custom.empty()) mig::SetKnownGeometries(custom);
+        core::Snapshot snap = core::TakeSnapshot(kind, cluster);
+        if (mode == "state") { print_state(snap.GetPartitioningState()); return 0; }
+        if (mode == "pack") {
+            core::Packed pk = core::Pack(snap, pods);
+            dump("profiles", pk.profiles); dump("models", pk.models); dump("others", pk.others); dump("node_names", pk.nodeNames);
+            dump("pod_keys", pk.podKeys);
+            dump("profile_mem_gb", pk.profileMemGB); dump("profile_gi", pk.profileGi); dump("model_geom_offset", pk.modelGeomOffset);
+            dump("geom_counts", pk.geomCounts); dump("gpus_per_node", std::vector<int>{pk.G});
+            dump("node_gpu_count", pk.nodeGpuCount); dump("gpu_model", pk.gpuModel); dump("gpu_index", pk.gpuIndex);
+            dump("gpu_memory_gb", pk.gpuMemoryGB); dump("gpu_used", pk.gpuUsed); dump("gpu_free", pk.gpuFree);
+            dump("gpu_used_mask", pk.gpuUsedMask); dump("gpu_free_mask", pk.gpuFreeMask);
+            dump("node_alloc", pk.nodeAlloc); dump("node_requested", pk.nodeRequested);
+            dump("node_allowed_pods", pk.nodeAllowedPods); dump("node_num_pods", pk.nodeNumPods);
+            dump("priority", pk.podPriority); dump("tracker_key", pk.podTrackerKey); dump("base", pk.podBase);
+            dump("scalar_ptr", pk.scalarPtr); dump("scalar_col", pk.scalarCol); dump("scalar_qty", pk.scalarQty);
+            return 0;
+        }
+        if (mode == "plan" || mode == "diff") {
+            if (!constPre) fw.preFilter = [](const v1::Pod&) { return false; };
+            core::Planner planner(kind, fw, 0);
+            core::PartitioningPlan plan = planner.Plan(snap, pods);
+            print_state(plan.DesiredState);
+            const nosplan_stats& st = planner.LastStats();
+            std::cout << "stats candidates=" << st.candidates << " visited_nodes=" << st.visited_nodes << " placements=" << st.placements
+                      << " geometry_evals=" << st.geometry_evals << " candidate_nodes=" << st.candidate_nodes << '\n';
+            if (mode == "diff") {
+                for (auto& n : core::NodesToPartition(snap, plan, false)) std::cout << "apply " << n << '\n';
+                for (auto& n : core::NodesToPartition(snap, plan, true)) std::cout << "changed " << n << '\n';
+            }
+            return 0;
+        }
+        throw Error("no run directive");
+    } catch (const std::exception& e) {
+        std::cout << "error " << e.what() << '\n';
+        return 1;
+    }
+}

@@ -295,7 +295,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     if (!s || !pods) return fail(h, NOSPLAN_E_INVALID, "null snapshot or pods");
     h->uploaded = h->ran = false;
     // NOSPLAN_TRACE=1: per-phase host microseconds of this call on stderr
-    static const bool trace = getenv("NOSPLAN_TRACE") != nullptr;
+    const bool trace = getenv("NOSPLAN_TRACE") != nullptr;
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto t_prev = now();
     auto lap = [&](const char* what) {

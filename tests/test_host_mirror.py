@@ -1,0 +1,157 @@
+"""C++ host mirror (host/): the reference's planner-facing Go types restated above the C-ABI.  CPU tests check the parsing
+and packing against the Python packer; GPU tests run the reference's own planner table tests through nos::core::Planner."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import nos_model as m
+from nos_b200 import packing as pk
+from support import hostcli as hc
+from support import randcases as rc
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PLAN = json.load(open(os.path.join(HERE, "golden", "planner_plan.json")))["cases"]
+
+
+@pytest.fixture(scope="module", autouse=True)
+def built():
+    import __graft_entry__ as g
+    g.build()
+
+
+def _same_pack(d, s, p):
+    ints = lambda k: [int(x) for x in d[k]]
+    assert d["profiles"] == s.profiles and d["models"] == s.models and d["others"] == s.other_resources
+    assert d["node_names"] == s.node_names and d["pod_keys"] == list(dict.fromkeys(p.keys))
+    for k, a in [("profile_mem_gb", s.profile_mem_gb), ("profile_gi", s.profile_gi), ("model_geom_offset", s.model_geom_offset),
+                 ("geom_counts", s.geom_counts), ("node_gpu_count", s.node_gpu_count), ("gpu_model", s.gpu_model),
+                 ("gpu_index", s.gpu_index), ("gpu_memory_gb", s.gpu_memory_gb), ("gpu_used", s.gpu_used), ("gpu_free", s.gpu_free),
+                 ("gpu_used_mask", s.gpu_used_mask), ("gpu_free_mask", s.gpu_free_mask), ("node_alloc", s.node_alloc),
+                 ("node_requested", s.node_requested), ("node_allowed_pods", s.node_allowed_pods), ("node_num_pods", s.node_num_pods),
+                 ("priority", p.priority), ("tracker_key", p.tracker_key), ("base", p.base), ("scalar_ptr", p.scalar_ptr),
+                 ("scalar_col", p.scalar_col), ("scalar_qty", p.scalar_qty)]:
+        assert ints(k) == [int(x) for x in np.asarray(a).reshape(-1)], k
+    assert int(d["gpus_per_node"][0]) == s.gpus_per_node
+
+
+@pytest.mark.parametrize("c", PLAN, ids=[f"{c['kind']}:{c['name'][:50]}" for c in PLAN])
+def test_pack_matches_python_packer_on_golden(c):
+    kind = pk.KIND_BY_NAME[c["kind"]]
+    s, p = pk.pack(kind, pk.nodes_from_v1(kind, c["nodes"], m.DEFAULT_KNOWN_GEOMETRIES), c["pods"], m.DEFAULT_KNOWN_GEOMETRIES)
+    code, out = hc.run(hc.to_text(c["kind"], c["nodes"], c["pods"], "pack"))
+    assert code == 0, out
+    _same_pack(hc.parse_pack(out), s, p)
+
+
+def test_pack_matches_python_packer_on_random():
+    n = 0
+    for seed in range(400):
+        kind_name, nodes, pods, pre, fmode = rc.rand_case(seed)
+        v1n = hc.logical_to_v1(kind_name, nodes)
+        if v1n is None:
+            continue
+        kind = pk.KIND_BY_NAME[kind_name]
+        s, p = pk.pack(kind, pk.nodes_from_v1(kind, v1n, m.DEFAULT_KNOWN_GEOMETRIES), pods, m.DEFAULT_KNOWN_GEOMETRIES)
+        code, out = hc.run(hc.to_text(kind_name, v1n, pods, "pack"))
+        assert code == 0, out
+        _same_pack(hc.parse_pack(out), s, p)
+        n += 1
+    assert n > 100
+
+
+def test_annotation_parsing_quirks():
+    # pkg/gpu/annotation.go:29-104: wrong part counts, non-numeric index or value, unknown status and spec annotations are skipped;
+    # the status word is case-insensitive; pkg/gpu/annotation_test.go
+    node = {"name": "n1", "labels": {pk.LABEL_PARTITIONING: "mig", pk.LABEL_PRODUCT: "NVIDIA-A30", pk.LABEL_COUNT: "3"},
+            "annotations": {"nos.nebuly.com/status-gpu-0-1g.6gb-free": "4",
+                            "nos.nebuly.com/status-gpu-1-2g.12gb-USED": "1",
+                            "nos.nebuly.com/status-gpu-1-1g.6gb-free": "0",
+                            "nos.nebuly.com/status-gpu-x-1g.6gb-free": "1",
+                            "nos.nebuly.com/status-gpu-1-1g.6gb-bogus": "1",
+                            "nos.nebuly.com/status-gpu-1-1g.6gb-free-extra": "1",
+                            "nos.nebuly.com/status-gpu-2-4g.24gb-unknown": "1",
+                            "nos.nebuly.com/status-gpu-0-2g.12gb-free": "one",
+                            "nos.nebuly.com/spec-gpu-0-4g.24gb": "1",
+                            "unrelated": "7"}}
+    code, out = hc.run(hc.to_text("mig", [node], [], "state"))
+    assert code == 0, out
+    st, _, _ = hc.parse_state(out)
+    # GPU 2 has only an `unknown` annotation: it exists (annotated) with empty maps
+    assert st == {"n1": [(0, {"nvidia.com/mig-1g.6gb": 4}), (1, {"nvidia.com/mig-1g.6gb": 0, "nvidia.com/mig-2g.12gb": 1}), (2, {})]}
+    exp = pk.nodes_from_v1(pk.KIND_MIG, [node], m.DEFAULT_KNOWN_GEOMETRIES)[0]
+    assert [(g["index"], g["used"], g["free"]) for g in exp["gpus"]] == [(0, {}, {"1g.6gb": 4}), (1, {"2g.12gb": 1}, {"1g.6gb": 0}), (2, {}, {})]
+
+
+@pytest.mark.parametrize("labels,msg", [
+    ({pk.LABEL_PARTITIONING: "mig", pk.LABEL_COUNT: "1"}, "missing label nvidia.com/gpu.product"),
+    ({pk.LABEL_PARTITIONING: "mig", pk.LABEL_PRODUCT: "NVIDIA-A30"}, "missing label nvidia.com/gpu.count"),
+    ({pk.LABEL_PARTITIONING: "mig", pk.LABEL_PRODUCT: "NVIDIA-A30", pk.LABEL_COUNT: "two"}, "invalid syntax"),
+    ({pk.LABEL_PARTITIONING: "mig", pk.LABEL_PRODUCT: "H900", pk.LABEL_COUNT: "1"}, "not associated with any known GPU"),
+    ({pk.LABEL_PARTITIONING: "mps", pk.LABEL_PRODUCT: "NVIDIA-A30", pk.LABEL_COUNT: "1"}, "missing label nvidia.com/gpu.memory"),
+])
+def test_new_node_errors_like_the_reference(labels, msg):
+    # mig.NewNode / slicing.NewNode error returns (pkg/gpu/mig/node.go:40-63, pkg/gpu/util.go:30-73, mig/gpu.go:43-55)
+    code, out = hc.run(hc.to_text(labels[pk.LABEL_PARTITIONING], [{"name": "n1", "labels": labels}], [], "state"))
+    assert code == 1 and out.startswith("error ") and msg in out, out
+
+
+def test_nodes_of_the_other_kind_and_nil_nodes_are_skipped():
+    nodes = [{"name": "a", "labels": {pk.LABEL_PARTITIONING: "mps", pk.LABEL_PRODUCT: "x", pk.LABEL_COUNT: "1", pk.LABEL_MEMORY: "40000"}},
+             {"name": "b", "labels": {pk.LABEL_PRODUCT: "NVIDIA-A30"}},
+             {"name": "c", "labels": {pk.LABEL_PARTITIONING: "mig", pk.LABEL_PRODUCT: "NVIDIA-A30", pk.LABEL_COUNT: "1"}}]
+    code, out = hc.run(hc.to_text("mig", nodes, [], "state").replace("run state", "nilnode zz\nrun state"))
+    assert code == 0 and list(hc.parse_state(out)[0]) == ["c"], out
+
+
+def test_memory_gb_is_ceil_of_mb_over_1000():
+    # pkg/gpu/util.go:59-73
+    node = {"name": "n", "labels": {pk.LABEL_PARTITIONING: "mps", pk.LABEL_PRODUCT: "x", pk.LABEL_COUNT: "1", pk.LABEL_MEMORY: "81920"}}
+    code, out = hc.run(hc.to_text("mps", [node], [], "pack"))
+    assert code == 0 and hc.parse_pack(out)["gpu_memory_gb"] == ["82"], out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("c", PLAN, ids=[f"{c['kind']}:{c['name'][:50]}" for c in PLAN])
+def test_golden_planner_through_cpp_planner(c):
+    """internal/partitioning/core/planner_test.go:43-854 run through nos::core::Planner::Plan."""
+    fm = pk.FILTER_NONE if c["filter_ok"] else pk.FILTER_REJECT_ALL
+    code, out = hc.run(hc.to_text(c["kind"], c["nodes"], c["pods"], "plan", fm, c["prefilter_ok"]))
+    assert code == 0, out
+    st, _, _ = hc.parse_state(out)
+    got = sorted((0 if c["kind"] == "mig" else i, tuple(sorted(r.items()))) for gl in st.values() for i, r in gl)
+    exp = sorted((0 if c["kind"] == "mig" else e["gpu_index"], tuple(sorted(e["resources"].items()))) for e in c["expected"])
+    assert got == exp
+
+
+@pytest.mark.gpu
+def test_random_cases_through_cpp_planner_vs_oracle():
+    from support import oracle_lib as ol
+    n = 0
+    for seed in range(300):
+        kind_name, nodes, pods, pre, fmode = rc.rand_case(seed)
+        v1n = hc.logical_to_v1(kind_name, nodes)
+        if v1n is None or len(set(pre)) > 1:
+            continue
+        kind = pk.KIND_BY_NAME[kind_name]
+        if any(q <= 0 and pk.slice_profile_of(kind, r) is not None for p in pods for r, q in pk.compute_pod_request(p).items()):
+            continue
+        s, p = pk.pack(kind, pk.nodes_from_v1(kind, v1n, m.DEFAULT_KNOWN_GEOMETRIES), pods, m.DEFAULT_KNOWN_GEOMETRIES)
+        ocnt, omsk, ost, _ = ol.plan(s, p, pre, fmode, ol.INCREMENTAL)
+        code, out = hc.run(hc.to_text(kind_name, v1n, pods, "diff", fmode, pre[0] if pre else 1))
+        assert code == 0, out
+        st, stats, extra = hc.parse_state(out)
+        assert st == pk.unpack_plan(s, ocnt, omsk), f"seed {seed}"
+        for k in ("candidates", "visited_nodes", "placements", "geometry_evals"):
+            assert stats[k] == ost[k], (seed, k)
+        # Actuator.Apply decision (core/actuator.go:39-66) and the changed-only refinement
+        cur = pk.unpack_plan(s, s.gpu_used + s.gpu_free, s.gpu_used_mask | s.gpu_free_mask)
+        canon = lambda gl: sorted((i, tuple(sorted(r.items()))) for i, r in gl)
+        same = all(canon(cur[k]) == canon(st[k]) for k in st)
+        applied = [t[1] for t in extra if t[0] == "apply"]
+        changed = [t[1] for t in extra if t[0] == "changed"]
+        assert applied == ([] if same or not st else sorted(st))
+        assert changed == ([] if same else [k for k in sorted(st) if canon(cur[k]) != canon(st[k])])
+        n += 1
+    assert n > 60

@@ -23,3 +23,15 @@ def raw():
     eng.lib.nosplan_upload(eng.h, C.byref(cs[0]), C.byref(cp[0]), None, 2)
 print("raw upload ms", t(raw))
 os.environ["NOSPLAN_TRACE"] = "1"
+sys.stderr.flush()
+for pinned in (False, True):
+    if pinned:
+        snap = capi.pin_snapshot(snap)
+        for _ in range(3): eng.plan(snap, pods, None, 2)
+        print("plan (node arrays page-locked) ms", t(lambda: eng.plan(snap, pods, None, 2)))
+    print("---- trace of one nosplan_plan, pinned =", pinned, flush=True)
+    os.environ["NOSPLAN_TRACE"] = "1"
+    t0 = time.perf_counter(); eng.plan(snap, pods, None, 2); t1 = time.perf_counter()
+    del os.environ["NOSPLAN_TRACE"]
+    sys.stderr.flush()
+    print("that call: %.1f us" % (1e6 * (t1 - t0)), flush=True)
