@@ -152,12 +152,33 @@ def pin_snapshot(s: PackedSnapshot) -> PackedSnapshot:
     return out
 
 
-def alloc_partitioning(s: PackedSnapshot):
+def alloc_partitioning(s: PackedSnapshot, out=None):
     n = max(1, s.n_nodes * s.gpus_per_node)
-    cnt = np.zeros((n, 16), np.uint8)
-    msk = np.zeros(n, np.uint16)
+    if out is None:
+        cnt = np.zeros((n, 16), np.uint8)
+        msk = np.zeros(n, np.uint16)
+    else:
+        cnt, msk = out
+        assert cnt.dtype == np.uint8 and cnt.shape == (n, 16) and msk.dtype == np.uint16 and msk.shape == (n,)
+        assert cnt.flags.c_contiguous and msk.flags.c_contiguous
     cp = CPartitioning(cnt.ctypes.data, msk.ctypes.data)
     return cp, cnt, msk
+
+
+def pinned_partitioning(s: PackedSnapshot):
+    """Plan output buffers in page-locked host memory (through torch): nosplan_download DMAs into them directly.
+    -> (gpu_count [N*G,16] u8, gpu_mask [N*G] u16); pass as out= to Engine.plan / download."""
+    import torch
+    n = max(1, s.n_nodes * s.gpus_per_node)
+    tc = torch.zeros(n * 16, dtype=torch.uint8).pin_memory()
+    tm = torch.zeros(n * 2, dtype=torch.uint8).pin_memory()
+    cnt = tc.numpy().reshape(n, 16)
+    msk = tm.numpy().view(np.uint16)
+    _KEEP_PINNED.append((tc, tm))
+    return cnt, msk
+
+
+_KEEP_PINNED = []
 
 
 class NosplanError(RuntimeError):
@@ -261,11 +282,11 @@ class Engine:
         a = np.ascontiguousarray(np.asarray(prefilter_ok, dtype=np.uint8).reshape(n))
         return a.ctypes.data, a
 
-    def plan(self, snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0):
+    def plan(self, snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0, out=None):
         """nosplan_plan: host buffers in, host buffers out.  -> (gpu_count [N*G,16], gpu_mask [N*G], stats dict)"""
         cs, k1 = c_snapshot(snap)
         cp, k2 = c_pods(pods)
-        out, cnt, msk = alloc_partitioning(snap)
+        out, cnt, msk = alloc_partitioning(snap, out)
         st = CStats()
         pre, k3 = self._pre(prefilter_ok, pods.n_pods)
         rc = self.lib.nosplan_plan(self.h, C.byref(cs), C.byref(cp), pre, filter_mode, C.byref(out), C.byref(st))
@@ -284,8 +305,8 @@ class Engine:
     def run(self):
         self._check(self.lib.nosplan_run(self.h), "nosplan_run")
 
-    def download(self):
-        out, cnt, msk = alloc_partitioning(self._snap)
+    def download(self, out=None):
+        out, cnt, msk = alloc_partitioning(self._snap, out)
         st = CStats()
         self._check(self.lib.nosplan_download(self.h, C.byref(out), C.byref(st)), "nosplan_download")
         return cnt, msk, st.as_dict()

@@ -104,10 +104,10 @@ struct GoStable {
 
 struct Layout {            // byte offsets into the arena / staging buffer
     size_t model_off, geom, node_gpu_count, gpu_model, gpu_mem, gpu_used, gpu_free, gpu_umask, gpu_fmask,
-        node_alloc, node_req, node_allowed, node_npods,
+        node_alloc, node_req, node_allowed, node_npods, nodes_end,
+        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, work_end, cand_flag, cand_idx, out_count, out_mask, out_end,
         pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
-        cmin_cpu, cmin_mem, cmin_eph, upload_end,
-        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, placed, entry_lack, work_end, cand_flag, cand_idx, out_count, out_mask, total;
+        cmin_cpu, cmin_mem, cmin_eph, upload_end, placed, entry_lack, total;
 };
 
 int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes) {
@@ -174,43 +174,46 @@ static void pod_order(const nosplan_snapshot* s, const nosplan_pods* pods, const
                 if (present[x]) for (int y = 0; y < K; ++y) if (present[y] && smaller(y, x)) ++rank_of[x];
             }
         }
-        std::vector<std::pair<long long, int>> keyed;          // (sort key, original index) of one stable counting sort
         if (swo) {
-            struct Level { int lo = INT_MAX, hi = INT_MIN; bool slice_less = false; };
-            std::vector<std::pair<int32_t, Level>> levels;      // distinct priorities are few: linear probe with last-hit cache
+            // one pass: priority level of every pod (distinct priorities are few: linear probe with a last-hit cache) and, per
+            // level, which profile ranks occur and whether slice-less pods do
+            struct Level { int32_t prio; unsigned ranks; bool slice_less; };
+            std::vector<Level> levels;
+            std::vector<uint16_t> lvl(P);
             size_t last = 0;
-            auto level_of = [&](int32_t p) -> Level& {
-                if (last < levels.size() && levels[last].first == p) return levels[last].second;
-                for (size_t k = 0; k < levels.size(); ++k) if (levels[k].first == p) { last = k; return levels[k].second; }
-                levels.emplace_back(p, Level()); last = levels.size() - 1;
-                return levels.back().second;
-            };
-            for (int i = 0; i < P && levels.size() <= 4096; ++i) {
-                Level& l = level_of(prio[i]);
-                if (fp[i] < 0) l.slice_less = true;
-                else { l.lo = std::min(l.lo, rank_of[fp[i]]); l.hi = std::max(l.hi, rank_of[fp[i]]); }
+            for (int i = 0; i < P; ++i) {
+                const int32_t p = prio[i];
+                if (last >= levels.size() || levels[last].prio != p) {
+                    size_t k = 0;
+                    while (k < levels.size() && levels[k].prio != p) ++k;
+                    if (k == levels.size()) {
+                        if (levels.size() >= 4096) { swo = false; break; }   // pathological: leave it to the general sort
+                        levels.push_back(Level{p, 0u, false});
+                    }
+                    last = k;
+                }
+                lvl[i] = (uint16_t)last;
+                if (fp[i] < 0) levels[last].slice_less = true; else levels[last].ranks |= 1u << rank_of[fp[i]];
             }
-            if (levels.size() > 4096) swo = false;              // pathological: leave it to the general sort
-            for (auto& kv : levels) if (kv.second.slice_less && kv.second.lo < kv.second.hi) swo = false;
+            // a level mixing slice-less pods (incomparable to everything) with two different ranks breaks transitivity
+            for (auto& l : levels) if (l.slice_less && (l.ranks & (l.ranks - 1))) swo = false;
             if (swo) {
-                // all pods of a level with slice-less members are equivalent (single rank): key = priority only there
-                // counting sort (stable) by (priority desc, rank asc)
+                // stable counting sort by (priority desc, rank asc); levels with slice-less members have a single bucket
                 std::vector<int> by_prio(levels.size());
                 for (size_t k = 0; k < levels.size(); ++k) by_prio[k] = (int)k;
-                std::sort(by_prio.begin(), by_prio.end(), [&](int a, int b) { return levels[a].first > levels[b].first; });
-                std::vector<int> pos_of_level(levels.size());
-                for (size_t k = 0; k < levels.size(); ++k) pos_of_level[by_prio[k]] = (int)k;
+                std::sort(by_prio.begin(), by_prio.end(), [&](int a, int b) { return levels[a].prio > levels[b].prio; });
                 const int stride = KP + 1;
+                std::vector<int> base_of_level(levels.size());
+                for (size_t k = 0; k < levels.size(); ++k) base_of_level[by_prio[k]] = (int)k * stride;
                 std::vector<int> count(levels.size() * stride + 1, 0), bucket(P);
                 for (int i = 0; i < P; ++i) {
-                    Level& l = level_of(prio[i]);
+                    const Level& l = levels[lvl[i]];
                     const int r = (l.slice_less || fp[i] < 0) ? 0 : rank_of[fp[i]];
-                    bucket[i] = pos_of_level[last] * stride + r;
+                    bucket[i] = base_of_level[lvl[i]] + r;
                     ++count[bucket[i] + 1];
                 }
                 for (size_t k = 1; k < count.size(); ++k) count[k] += count[k - 1];
                 for (int i = 0; i < P; ++i) order[count[bucket[i]]++] = i;
-                (void)keyed;
             }
         }
         if (!swo) {
@@ -229,6 +232,35 @@ int nosplan_fail(nosplan* h, int code, const char* fmt, ...) {
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
     if (h) h->err = buf;
     return code;
+}
+
+// event-timed phases of the last call: the H2D copies (nodes, then pods), the kernels (node-only part, then the rest)
+void nosplan_phase_times(nosplan* h, nosplan_stats* stats) {
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, h->ev[0], h->ev[1]); cudaEventElapsedTime(&b, h->ev[9], h->ev[10]);
+    stats->ms_h2d = a + b;
+    if (getenv("NOSPLAN_TRACE")) {
+        float c = 0, d = 0, e = 0;
+        cudaEventElapsedTime(&c, h->ev[0], h->ev[3]);
+        if (h->split_run) { cudaEventElapsedTime(&d, h->ev[1], h->ev[9]); cudaEventElapsedTime(&e, h->ev[10], h->ev[3]); }
+        for (int k = 0; k < h->dbg_n; ++k) {
+            float t = 0;
+            cudaEventElapsedTime(&t, k ? h->dbg_ev[k - 1] : h->ev[0], h->dbg_ev[k]);
+            fprintf(stderr, "[nosplan gpu]   copy %2d %8zu B %s %7.1f us\n", k, h->dbg_bytes[k], h->dbg_direct[k] ? "direct" : "staged", 1e3 * t);
+        }
+        fprintf(stderr, "[nosplan gpu] h2d nodes %.1f us, gap to pod copy %.1f us, h2d pods %.1f us, pod copy -> last kernel %.1f us, first copy -> last kernel %.1f us\n",
+                1e3 * a, 1e3 * d, 1e3 * b, 1e3 * e, 1e3 * c);
+    }
+    if (h->split_run) {
+        cudaEventElapsedTime(&a, h->ev[2], h->ev[6]); cudaEventElapsedTime(&b, h->ev[11], h->ev[3]);
+        stats->ms_kernels = a + b;
+    } else cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
+    if (h->kernel_events) {
+        cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
+        cudaEventElapsedTime(&stats->ms_tracker, h->ev[h->split_run ? 11 : 6], h->ev[7]);
+        cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
+        cudaEventElapsedTime(&stats->ms_sweep, h->ev[8], h->ev[3]);
+    }
 }
 
 extern "C" {
@@ -289,11 +321,24 @@ int nosplan_host_pod_order(const nosplan_snapshot* s, const nosplan_pods* pods, 
     return NOSPLAN_OK;
 }
 
+// Kernels that need only the node arrays: work-area reset + k_prepass.  nosplan_plan issues them as soon as the node DMA
+// is queued, so they run while the host is still ordering the pods.
+static int run_pre(nosplan* h, bool split) {
+    CU(h, cudaEventRecord(h->ev[2], h->stream));
+    CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
+    launch_prepass(h->pb, h->stream);
+    if (split || h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
+    CU(h, cudaGetLastError());
+    h->pre_done = split;                     // split: the pod-dependent kernels follow later, after the pod DMA
+    h->split_run = split;
+    return NOSPLAN_OK;
+}
+
 int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
                    int32_t filter_mode) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!s || !pods) return fail(h, NOSPLAN_E_INVALID, "null snapshot or pods");
-    h->uploaded = h->ran = false;
+    h->uploaded = h->ran = h->pre_done = false;
     // NOSPLAN_TRACE=1: per-phase host microseconds of this call on stderr
     const bool trace = getenv("NOSPLAN_TRACE") != nullptr;
     auto now = [] { return std::chrono::steady_clock::now(); };
@@ -322,102 +367,20 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         if (c < 0 || c > NOSPLAN_MAX_GEOMS) return fail(h, NOSPLAN_E_LIMIT, "model %d has %d geometries > NOSPLAN_MAX_GEOMS", m, c);
     }
     for (int i = 0; i < N; ++i) {
-        if (s->node_gpu_count[i] < 0 || s->node_gpu_count[i] > G) return fail(h, NOSPLAN_E_INVALID, "node %d: gpu count out of range", i);
-        if (mig)
-            for (int j = 0; j < s->node_gpu_count[i]; ++j) {
-                const int m = s->gpu_model[(size_t)i * G + j];
-                if (m < 0 || m >= n_models) return fail(h, NOSPLAN_E_INVALID, "node %d gpu %d: model id out of range", i, j);
-            }
+        const int ng = s->node_gpu_count[i];
+        if (ng < 0 || ng > G) return fail(h, NOSPLAN_E_INVALID, "node %d: gpu count out of range", i);
+        if (mig) {
+            const int32_t* gm = s->gpu_model + (size_t)i * G;
+            unsigned bad = 0;
+            for (int j = 0; j < ng; ++j) bad |= (unsigned)gm[j] >= (unsigned)n_models;
+            if (bad) return fail(h, NOSPLAN_E_INVALID, "node %d: GPU model id out of range", i);
+        }
     }
-
-    lap("validate");
-    // ---- per-pod sort keys and validation
     const int nnz = P > 0 ? pods->scalar_ptr[P] : 0;
-    std::vector<int> first_prof(P, -1);
-    std::vector<uint32_t> flags(P, 0);
-    int n_keys = 0;
-    for (int i = 0; i < P; ++i) {
-        const int a = pods->scalar_ptr[i], b = pods->scalar_ptr[i + 1];
-        if (a > b || b > nnz) return fail(h, NOSPLAN_E_INVALID, "pod %d: bad scalar_ptr", i);
-        bool other = false; int prev = 2;
-        for (int e = a; e < b; ++e) {
-            const int col = pods->scalar_col[e];
-            if (col < 3 || col >= R || col <= prev) return fail(h, NOSPLAN_E_INVALID, "pod %d: scalar columns must be in [3,R) and ascending", i);
-            prev = col;
-            if (col < 3 + K) {
-                if (first_prof[i] < 0) first_prof[i] = col - 3;
-                if (pods->scalar_qty[e] <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
-            } else other = true;
-        }
-        if (pods->base[3 * (size_t)i] < 0 || pods->base[3 * (size_t)i + 1] < 0 || pods->base[3 * (size_t)i + 2] < 0)
-            return fail(h, NOSPLAN_E_INVALID, "pod %d: negative cpu / memory / ephemeral-storage request", i);
-        uint32_t f = 0;
-        if (!prefilter_ok || prefilter_ok[i]) f |= PF_PRE_OK;
-        if (other) f |= PF_HAS_OTHER;
-        if (a == b && pods->base[3 * (size_t)i] == 0 && pods->base[3 * (size_t)i + 1] == 0 && pods->base[3 * (size_t)i + 2] == 0) f |= PF_ZERO_REQ;
-        flags[i] = f;
-        const int k = pods->tracker_key[i];
-        if (k < 0 || k >= P) return fail(h, NOSPLAN_E_INVALID, "pod %d: tracker_key out of range", i);
-        n_keys = std::max(n_keys, k + 1);
-    }
-    if (n_keys > sweep_max_keys()) return fail(h, NOSPLAN_E_LIMIT, "%d tracker keys > %d", n_keys, sweep_max_keys());
+    if (nnz < 0) return fail(h, NOSPLAN_E_INVALID, "negative scalar entry count");
+    lap("validate");
 
-    lap("pod keys");
-    // ---- NewPodSorter (core/util.go:34-73)
-    std::vector<int> order;
-    pod_order(s, pods, first_prof.data(), order);
-
-    lap("sort");
-    // ---- runs of identical slice requests in sorted order
-    std::vector<RunRec> runs;
-    auto same_slices = [&](int x, int y) {
-        int ex = pods->scalar_ptr[x], ey = pods->scalar_ptr[y];
-        const int bx = pods->scalar_ptr[x + 1], by = pods->scalar_ptr[y + 1];
-        for (;;) {
-            const bool sx = ex < bx && pods->scalar_col[ex] < 3 + K, sy = ey < by && pods->scalar_col[ey] < 3 + K;
-            if (!sx || !sy) return sx == sy;
-            if (pods->scalar_col[ex] != pods->scalar_col[ey] || pods->scalar_qty[ex] != pods->scalar_qty[ey]) return false;
-            ++ex; ++ey;
-        }
-    };
-    for (int si = 0; si < P; ++si) {
-        const int oi = order[si];
-        if (si > 0 && same_slices(order[si - 1], oi)) { runs.back().len++; continue; }
-        RunRec r; std::memset(&r, 0, sizeof r);
-        r.start = si; r.len = 1;
-        for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1] && pods->scalar_col[e] < 3 + K; ++e) {
-            const long long q = pods->scalar_qty[e];
-            r.q[pods->scalar_col[e] - 3] = (uint16_t)std::min<long long>(q, 65535);   // device counts are <= 255: anything larger can never fit
-            r.n_ent++;
-            r.p_single = (uint16_t)(pods->scalar_col[e] - 3);
-        }
-        runs.push_back(r);
-    }
-    const int n_runs = (int)runs.size();
-
-    // ---- per-chunk (32 pods, run-relative) minima of the requests of the PreFilter-ok pods: lets the kernels skip
-    //      chunks in which no pod can pass NodeResourcesFit.  An all-zero request passes regardless (fit.go short-circuit).
-    std::vector<int32_t> run_chunk_off(n_runs + 1, 0);
-    for (int r = 0; r < n_runs; ++r) run_chunk_off[r + 1] = run_chunk_off[r] + (runs[r].len + 31) / 32;
-    const int n_chunks = run_chunk_off[n_runs];
-    std::vector<long long> cmin(3 * (size_t)n_chunks, LLONG_MAX);
-    bool single_profile_classes = true;
-    for (int r = 0; r < n_runs; ++r) {
-        if (runs[r].n_ent > 1) single_profile_classes = false;
-        for (int l = 0; l < runs[r].len; ++l) {
-            const int oi = order[runs[r].start + l];
-            if (!(flags[oi] & PF_PRE_OK)) continue;
-            const size_t c = (size_t)run_chunk_off[r] + l / 32;
-            const bool z = (flags[oi] & PF_ZERO_REQ) != 0;
-            for (int k = 0; k < 3; ++k) {
-                const long long v = z ? LLONG_MIN : pods->base[3 * (size_t)oi + k];
-                cmin[k * (size_t)n_chunks + c] = std::min(cmin[k * (size_t)n_chunks + c], v);
-            }
-        }
-    }
-
-    lap("runs+chunks");
-    // ---- layout
+    // ---- layout, part 1: every section whose size does not depend on the pods' contents
     Layout L; size_t o = 0;
     auto put = [&](size_t& field, size_t bytes) { field = o; o = al(o + bytes); };
     const size_t NG = (size_t)N * G;
@@ -429,34 +392,34 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     put(L.gpu_umask, 2 * NG); put(L.gpu_fmask, 2 * NG);
     put(L.node_alloc, 8 * (size_t)N * R); put(L.node_req, 8 * (size_t)N * R);
     put(L.node_allowed, 4 * (size_t)N); put(L.node_npods, 4 * (size_t)N);
-    put(L.pod_cpu, 8 * (size_t)P); put(L.pod_mem, 8 * (size_t)P); put(L.pod_eph, 8 * (size_t)P);
-    put(L.pod_key, 4 * (size_t)P); put(L.pod_flags, 4 * (size_t)P);
-    put(L.pod_sptr, 4 * ((size_t)P + 1)); put(L.pod_scol, 4 * (size_t)nnz); put(L.pod_sqty, 8 * (size_t)nnz);
-    put(L.runs, sizeof(RunRec) * (size_t)n_runs);
-    put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
-    put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
-    L.upload_end = o;
+    L.nodes_end = o;
     put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats));
-    put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.lack_dec, 4 * KP); put(L.next_node, 16); put(L.placed, 4 * (((size_t)n_keys + 31) / 32));
-    put(L.entry_lack, 4 * (size_t)n_keys * KP);
+    put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.lack_dec, 4 * KP); put(L.next_node, 16);
+    put(L.placed, 4 * (((size_t)P + 31) / 32));             // tracker tables: sized for P keys (keys <= P), reset with the rest
+    put(L.entry_lack, 4 * (size_t)P * KP);
     L.work_end = o;
     put(L.cand_flag, (size_t)N); put(L.cand_idx, 4 * (size_t)N);
     put(L.out_count, 16 * NG); put(L.out_mask, 2 * NG);
-    L.total = o;
-
+    L.out_end = o;
+    put(L.pod_cpu, 8 * (size_t)P); put(L.pod_mem, 8 * (size_t)P); put(L.pod_eph, 8 * (size_t)P);
+    put(L.pod_key, 4 * (size_t)P); put(L.pod_flags, 4 * (size_t)P);
+    put(L.pod_sptr, 4 * ((size_t)P + 1)); put(L.pod_scol, 4 * (size_t)nnz); put(L.pod_sqty, 8 * (size_t)nnz);
+    const size_t part1_end = o;
+    // part 2 (runs, chunk minima) is laid out once the pods are ordered; the arena is sized from bounds: runs <= P, chunks <= P
+    const size_t bound = part1_end + al(sizeof(RunRec) * (size_t)P) + al(4 * ((size_t)P + 1)) + 3 * al(8 * (size_t)P) + 4096;
     CU(h, cudaSetDevice(h->device));
     const size_t out_bytes = al(16 * NG) + al(2 * NG) + al(sizeof(DevStats));
-    int rc = ensure(h, L.total, L.upload_end, out_bytes);
+    int rc = ensure(h, bound, bound, out_bytes);
     if (rc != NOSPLAN_OK) return rc;
-
     lap("layout+alloc");
-    // ---- stage (one pinned buffer, one H2D copy)
+
+    // ---- node arrays first: their DMA runs while the host orders the pods.  If the caller keeps them in page-locked memory
+    //      (cudaHostAlloc / cudaHostRegister) the copy engine reads them where they are; otherwise they pass through staging.
     unsigned char* S = h->h_stage;
+    unsigned char* A = h->d_arena;
     if (n_models > 0) std::memcpy(S + L.model_off, s->model_geom_offset, sizeof(int32_t) * (n_models + 1));
     else std::memset(S + L.model_off, 0, sizeof(int32_t));
     if (n_rows) std::memcpy(S + L.geom, s->geom_counts, 16 * (size_t)n_rows);
-    // The node arrays are most of the bytes.  If the caller keeps them in page-locked memory (cudaHostAlloc /
-    // cudaHostRegister), the DMA engine reads them where they are; otherwise they go through the pinned staging buffer.
     struct Seg { size_t off; const void* src; size_t bytes; bool direct; };
     Seg segs[11] = {
         {L.node_gpu_count, s->node_gpu_count, 4 * (size_t)N, false}, {L.gpu_model, s->gpu_model, 4 * NG, false},
@@ -467,60 +430,43 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     bool any_direct = false;
     if (N) {
         for (Seg& g : segs) {
+            // small arrays are cheaper to memcpy into staging than to give a DMA descriptor of their own
             cudaPointerAttributes at;
-            g.direct = g.bytes >= 4096 && cudaPointerGetAttributes(&at, g.src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+            g.direct = g.bytes >= (128u << 10) && cudaPointerGetAttributes(&at, g.src) == cudaSuccess && at.type == cudaMemoryTypeHost;
             if (g.direct) any_direct = true;
             else std::memcpy(S + g.off, g.src, g.bytes);
         }
         (void)cudaGetLastError();
     }
-    {
-        long long* cpu = (long long*)(S + L.pod_cpu); long long* mem = (long long*)(S + L.pod_mem); long long* eph = (long long*)(S + L.pod_eph);
-        int32_t* key = (int32_t*)(S + L.pod_key); uint32_t* fl = (uint32_t*)(S + L.pod_flags);
-        int32_t* sptr = (int32_t*)(S + L.pod_sptr); int32_t* scol = (int32_t*)(S + L.pod_scol); long long* sqty = (long long*)(S + L.pod_sqty);
-        int w = 0;
-        for (int si = 0; si < P; ++si) {
-            const int oi = order[si];
-            cpu[si] = pods->base[3 * (size_t)oi]; mem[si] = pods->base[3 * (size_t)oi + 1]; eph[si] = pods->base[3 * (size_t)oi + 2];
-            key[si] = pods->tracker_key[oi]; fl[si] = flags[oi];
-            sptr[si] = w;
-            for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1]; ++e) { scol[w] = pods->scalar_col[e]; sqty[w] = pods->scalar_qty[e]; ++w; }
-        }
-        sptr[P] = w;
-        if (n_runs) std::memcpy(S + L.runs, runs.data(), sizeof(RunRec) * (size_t)n_runs);
-        std::memcpy(S + L.run_chunk_off, run_chunk_off.data(), 4 * ((size_t)n_runs + 1));
-        if (n_chunks) {
-            std::memcpy(S + L.cmin_cpu, cmin.data(), 8 * (size_t)n_chunks);
-            std::memcpy(S + L.cmin_mem, cmin.data() + n_chunks, 8 * (size_t)n_chunks);
-            std::memcpy(S + L.cmin_eph, cmin.data() + 2 * (size_t)n_chunks, 8 * (size_t)n_chunks);
-        }
-    }
-
-    lap("stage");
     CU(h, cudaEventRecord(h->ev[0], h->stream));
-    if (!any_direct) CU(h, cudaMemcpyAsync(h->d_arena, S, L.upload_end, cudaMemcpyHostToDevice, h->stream));
-    else {
-        // staged ranges around and between the direct segments, then the direct segments themselves
+    {
         size_t from = 0;
+        h->dbg_n = 0;
+        auto mark = [&](size_t bytes, bool direct) {          // NOSPLAN_TRACE: one event per copy
+            if (!trace || h->dbg_n >= 32) return;
+            if (!h->dbg_ev[h->dbg_n]) cudaEventCreate(&h->dbg_ev[h->dbg_n]);
+            cudaEventRecord(h->dbg_ev[h->dbg_n], h->stream);
+            h->dbg_bytes[h->dbg_n] = bytes; h->dbg_direct[h->dbg_n] = direct; h->dbg_n++;
+        };
         for (const Seg& g : segs) {
             if (!g.direct) continue;
-            if (g.off > from) CU(h, cudaMemcpyAsync(h->d_arena + from, S + from, g.off - from, cudaMemcpyHostToDevice, h->stream));
-            CU(h, cudaMemcpyAsync(h->d_arena + g.off, g.src, g.bytes, cudaMemcpyHostToDevice, h->stream));
+            if (g.off > from) { CU(h, cudaMemcpyAsync(A + from, S + from, g.off - from, cudaMemcpyHostToDevice, h->stream)); mark(g.off - from, false); }
+            CU(h, cudaMemcpyAsync(A + g.off, g.src, g.bytes, cudaMemcpyHostToDevice, h->stream));
+            mark(g.bytes, true);
             from = al(g.off + g.bytes);
         }
-        if (L.upload_end > from) CU(h, cudaMemcpyAsync(h->d_arena + from, S + from, L.upload_end - from, cudaMemcpyHostToDevice, h->stream));
+        if (L.nodes_end > from) CU(h, cudaMemcpyAsync(A + from, S + from, L.nodes_end - from, cudaMemcpyHostToDevice, h->stream));
     }
     h->direct_h2d = any_direct;
-    CU(h, cudaMemsetAsync(h->d_arena + L.out_count, 0, L.total - L.out_count, h->stream));
+    CU(h, cudaMemsetAsync(A + L.out_count, 0, L.out_end - L.out_count, h->stream));
     CU(h, cudaEventRecord(h->ev[1], h->stream));
 
-    // ---- device problem description
+    // ---- device problem description, node side
     DevProblem& pb = h->pb;
     std::memset(&pb, 0, sizeof pb);
-    unsigned char* A = h->d_arena;
     pb.kind = s->kind; pb.K = K; pb.R = R; pb.n_other = s->n_other;
     pb.node_lo = 0; pb.node_hi = N;
-    pb.N = N; pb.G = G; pb.P = P; pb.n_keys = n_keys; pb.n_runs = n_runs; pb.filter_mode = filter_mode;
+    pb.N = N; pb.G = G; pb.P = P; pb.filter_mode = filter_mode;
     pb.n_models = n_models; pb.n_rows = n_rows;
     for (int p = 0; p < KP; ++p) { pb.pmem[p] = p < K ? s->profile_mem_gb[p] : 0; pb.pgi[p] = p < K ? s->profile_gi[p] : 0; }
     pb.model_off = (const int32_t*)(A + L.model_off); pb.geom = (const uint4*)(A + L.geom);
@@ -530,6 +476,142 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     pb.gpu_umask = (const uint16_t*)(A + L.gpu_umask); pb.gpu_fmask = (const uint16_t*)(A + L.gpu_fmask);
     pb.node_alloc = (const long long*)(A + L.node_alloc); pb.node_req = (const long long*)(A + L.node_req);
     pb.node_allowed_pods = (const int32_t*)(A + L.node_allowed); pb.node_num_pods = (const int32_t*)(A + L.node_npods);
+    pb.maxfree = (int32_t*)(A + L.maxfree); pb.gflags = (int32_t*)(A + L.gflags);
+    pb.acc = (unsigned long long*)(A + L.acc);
+    pb.lack_dec = (int32_t*)(A + L.lack_dec); pb.next_node = (int32_t*)(A + L.next_node); pb.whole_snapshot = 1;
+    pb.tot = (long long*)(A + L.tot); pb.lack = (int32_t*)(A + L.lack); pb.stats = (DevStats*)(A + L.stats);
+    pb.cand_flag = (uint8_t*)(A + L.cand_flag);
+    pb.out_count = (uint4*)(A + L.out_count); pb.out_mask = (uint16_t*)(A + L.out_mask);
+    h->d_cand_idx = (int32_t*)(A + L.cand_idx);
+    h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot;
+    h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
+    if (h->in_plan) { rc = run_pre(h, true); if (rc != NOSPLAN_OK) return rc; }
+    lap("nodes queued");
+
+    // ---- pods, pass 1 (original order): validation, flags, first requested profile, class key of the slice request
+    //      (equal keys <=> identical slice requests; CLS_MULTI = compare the entries)
+    constexpr unsigned long long CLS_MULTI = ~0ull;
+    std::vector<int>& first_prof = h->v_first_prof; first_prof.assign(P, -1);
+    std::vector<uint32_t>& flags = h->v_flags; flags.resize(P);
+    std::vector<unsigned long long>& cls = h->v_cls; cls.resize(P);
+    int n_keys = 0;
+    for (int i = 0; i < P; ++i) {
+        const int a = pods->scalar_ptr[i], b = pods->scalar_ptr[i + 1];
+        if (a > b || b > nnz) return fail(h, NOSPLAN_E_INVALID, "pod %d: bad scalar_ptr", i);
+        bool other = false; int prev = 2, n_slice = 0;
+        unsigned long long ck = 0;
+        for (int e = a; e < b; ++e) {
+            const int col = pods->scalar_col[e];
+            if (col < 3 || col >= R || col <= prev) return fail(h, NOSPLAN_E_INVALID, "pod %d: scalar columns must be in [3,R) and ascending", i);
+            prev = col;
+            if (col < 3 + K) {
+                const long long q = pods->scalar_qty[e];
+                if (q <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
+                if (first_prof[i] < 0) first_prof[i] = col - 3;
+                ck = (++n_slice == 1 && q < (1ll << 40)) ? (((unsigned long long)(col - 2)) << 40 | (unsigned long long)q) : CLS_MULTI;
+            } else other = true;
+        }
+        cls[i] = ck;
+        const long long bc = pods->base[3 * (size_t)i], bm = pods->base[3 * (size_t)i + 1], be = pods->base[3 * (size_t)i + 2];
+        if ((bc | bm | be) < 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: negative cpu / memory / ephemeral-storage request", i);
+        uint32_t f = 0;
+        if (!prefilter_ok || prefilter_ok[i]) f |= PF_PRE_OK;
+        if (other) f |= PF_HAS_OTHER;
+        if (a == b && (bc | bm | be) == 0) f |= PF_ZERO_REQ;
+        flags[i] = f;
+        const int k = pods->tracker_key[i];
+        if (k < 0 || k >= P) return fail(h, NOSPLAN_E_INVALID, "pod %d: tracker_key out of range", i);
+        n_keys = std::max(n_keys, k + 1);
+    }
+    if (n_keys > sweep_max_keys()) return fail(h, NOSPLAN_E_LIMIT, "%d tracker keys > %d", n_keys, sweep_max_keys());
+    lap("pod keys");
+
+    // ---- NewPodSorter (core/util.go:34-73)
+    std::vector<int>& order = h->v_order;
+    pod_order(s, pods, first_prof.data(), order);
+    lap("sort");
+
+    // ---- pass 2 (sorted order), fused: pods into staging, runs of identical slice requests, and per-chunk (32 pods,
+    //      run-relative) minima of the requests of the PreFilter-ok pods -- the kernels skip chunks in which no pod can pass
+    //      NodeResourcesFit.  An all-zero request passes regardless (fit.go short-circuit): its minimum is LLONG_MIN.
+    std::vector<RunRec>& runs = h->v_runs; runs.clear();
+    std::vector<int32_t>& run_chunk_off = h->v_chunk_off; run_chunk_off.clear();
+    std::vector<long long>& cmin = h->v_cmin; cmin.clear();                  // [chunk][3]
+    auto same_entries = [&](int x, int y) {
+        int ex = pods->scalar_ptr[x], ey = pods->scalar_ptr[y];
+        const int bx = pods->scalar_ptr[x + 1], by = pods->scalar_ptr[y + 1];
+        for (;;) {
+            const bool sx = ex < bx && pods->scalar_col[ex] < 3 + K, sy = ey < by && pods->scalar_col[ey] < 3 + K;
+            if (!sx || !sy) return sx == sy;
+            if (pods->scalar_col[ex] != pods->scalar_col[ey] || pods->scalar_qty[ex] != pods->scalar_qty[ey]) return false;
+            ++ex; ++ey;
+        }
+    };
+    bool single_profile_classes = true;
+    {
+        long long* cpu = (long long*)(S + L.pod_cpu); long long* mem = (long long*)(S + L.pod_mem); long long* eph = (long long*)(S + L.pod_eph);
+        int32_t* key = (int32_t*)(S + L.pod_key); uint32_t* fl = (uint32_t*)(S + L.pod_flags);
+        int32_t* sptr = (int32_t*)(S + L.pod_sptr); int32_t* scol = (int32_t*)(S + L.pod_scol); long long* sqty = (long long*)(S + L.pod_sqty);
+        int w = 0, prev_oi = -1, in_run = 0;
+        long long* cm = nullptr;
+        for (int si = 0; si < P; ++si) {
+            const int oi = order[si];
+            const bool same = si > 0 && cls[oi] == cls[prev_oi] && (cls[oi] != CLS_MULTI || same_entries(prev_oi, oi));
+            if (!same) {
+                RunRec r; std::memset(&r, 0, sizeof r);
+                r.start = si;
+                for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1] && pods->scalar_col[e] < 3 + K; ++e) {
+                    const long long q = pods->scalar_qty[e];
+                    r.q[pods->scalar_col[e] - 3] = (uint16_t)std::min<long long>(q, 65535);   // device counts are <= 255: anything larger can never fit
+                    r.n_ent++;
+                    r.p_single = (uint16_t)(pods->scalar_col[e] - 3);
+                }
+                if (r.n_ent > 1) single_profile_classes = false;
+                runs.push_back(r);
+                run_chunk_off.push_back((int32_t)(cmin.size() / 3));
+                in_run = 0;
+            }
+            if ((in_run & 31) == 0) { cmin.insert(cmin.end(), 3, LLONG_MAX); cm = cmin.data() + cmin.size() - 3; }
+            ++in_run; runs.back().len = in_run;
+            prev_oi = oi;
+            const long long bc = pods->base[3 * (size_t)oi], bm = pods->base[3 * (size_t)oi + 1], be = pods->base[3 * (size_t)oi + 2];
+            const uint32_t f = flags[oi];
+            if (f & PF_PRE_OK) {
+                const bool z = (f & PF_ZERO_REQ) != 0;
+                cm[0] = std::min(cm[0], z ? LLONG_MIN : bc); cm[1] = std::min(cm[1], z ? LLONG_MIN : bm); cm[2] = std::min(cm[2], z ? LLONG_MIN : be);
+            }
+            cpu[si] = bc; mem[si] = bm; eph[si] = be;
+            key[si] = pods->tracker_key[oi]; fl[si] = f;
+            sptr[si] = w;
+            for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1]; ++e) { scol[w] = pods->scalar_col[e]; sqty[w] = pods->scalar_qty[e]; ++w; }
+        }
+        sptr[P] = w;
+    }
+    const int n_runs = (int)runs.size();
+    const int n_chunks = (int)(cmin.size() / 3);
+    run_chunk_off.push_back(n_chunks);
+    lap("runs+stage");
+
+    // ---- layout, part 2
+    o = part1_end;
+    put(L.runs, sizeof(RunRec) * (size_t)n_runs);
+    put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
+    put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
+    L.upload_end = o;
+    L.total = o;
+    if (L.total > bound) return fail(h, NOSPLAN_E_NOMEM, "internal: arena bound exceeded");
+    if (n_runs) std::memcpy(S + L.runs, runs.data(), sizeof(RunRec) * (size_t)n_runs);
+    std::memcpy(S + L.run_chunk_off, run_chunk_off.data(), 4 * ((size_t)n_runs + 1));
+    {
+        long long* c0 = (long long*)(S + L.cmin_cpu); long long* c1 = (long long*)(S + L.cmin_mem); long long* c2 = (long long*)(S + L.cmin_eph);
+        for (int c = 0; c < n_chunks; ++c) { c0[c] = cmin[3 * (size_t)c]; c1[c] = cmin[3 * (size_t)c + 1]; c2[c] = cmin[3 * (size_t)c + 2]; }
+    }
+    CU(h, cudaEventRecord(h->ev[9], h->stream));
+    CU(h, cudaMemcpyAsync(A + L.pod_cpu, S + L.pod_cpu, L.upload_end - L.pod_cpu, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaEventRecord(h->ev[10], h->stream));
+
+    // ---- device problem description, pod side
+    pb.n_keys = n_keys; pb.n_runs = n_runs;
     pb.pod_cpu = (const long long*)(A + L.pod_cpu); pb.pod_mem = (const long long*)(A + L.pod_mem); pb.pod_eph = (const long long*)(A + L.pod_eph);
     pb.pod_key = (const int32_t*)(A + L.pod_key); pb.pod_flags = (const uint32_t*)(A + L.pod_flags);
     pb.pod_sptr = (const int32_t*)(A + L.pod_sptr); pb.pod_scol = (const int32_t*)(A + L.pod_scol); pb.pod_sqty = (const long long*)(A + L.pod_sqty);
@@ -550,31 +632,18 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
             pb.sat_m[p] = m;
         }
     }
-    pb.maxfree = (int32_t*)(A + L.maxfree); pb.gflags = (int32_t*)(A + L.gflags);
-    pb.acc = (unsigned long long*)(A + L.acc); pb.placed = (unsigned*)(A + L.placed);
-    pb.lack_dec = (int32_t*)(A + L.lack_dec); pb.next_node = (int32_t*)(A + L.next_node); pb.whole_snapshot = 1;
-    pb.tot = (long long*)(A + L.tot); pb.lack = (int32_t*)(A + L.lack); pb.stats = (DevStats*)(A + L.stats);
+    pb.placed = (unsigned*)(A + L.placed);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
-    pb.cand_flag = (uint8_t*)(A + L.cand_flag);
-    pb.out_count = (uint4*)(A + L.out_count); pb.out_mask = (uint16_t*)(A + L.out_mask);
-    h->d_cand_idx = (int32_t*)(A + L.cand_idx);
-    h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot;
-    h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
-    lap("enqueue h2d");
-    h->h2d_bytes = L.upload_end;
+    lap("pods queued");
+    h->h2d_bytes = L.nodes_end + (L.upload_end - L.pod_cpu);
     h->uploaded = true;
     if (any_direct && !h->in_plan) CU(h, cudaStreamSynchronize(h->stream));   // nothing of the caller's is read after return
     return NOSPLAN_OK;
 }
 
-int nosplan_run(nosplan_t* h) {
-    if (!h) return NOSPLAN_E_INVALID;
-    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_run before nosplan_upload");
-    CU(h, cudaSetDevice(h->device));
-    CU(h, cudaEventRecord(h->ev[2], h->stream));
-    CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
-    launch_prepass(h->pb, h->stream);
-    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
+// Kernels that need the pods: tracker tables reset, k_tracker_init, node-parallel pass, verification / sequential sweep.
+static int run_post(nosplan* h) {
+    if (h->split_run) CU(h, cudaEventRecord(h->ev[11], h->stream));
     launch_tracker_init(h->pb, h->stream);
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[7], h->stream));
     CU(h, cudaGetLastError());
@@ -585,6 +654,15 @@ int nosplan_run(nosplan_t* h) {
     h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     h->ran = true;
     return NOSPLAN_OK;
+}
+
+int nosplan_run(nosplan_t* h) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_run before nosplan_upload");
+    CU(h, cudaSetDevice(h->device));
+    int rc = run_pre(h, false);
+    if (rc != NOSPLAN_OK) return rc;
+    return run_post(h);
 }
 
 // ---- node-sharded Plan() over `world` ranks (one handle per rank, the same snapshot uploaded on each) --------------
@@ -600,11 +678,9 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
     const int64_t need = nosplan_shard_exchange_bytes(h);
     if (!d_exchange || exchange_bytes < need) return fail(h, NOSPLAN_E_INVALID, "exchange buffer smaller than %lld bytes", (long long)need);
     CU(h, cudaSetDevice(h->device));
-    CU(h, cudaEventRecord(h->ev[2], h->stream));
-    CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
+    int rc = run_pre(h, false);                             // prepass replicated: cheaper than exchanging the totals
+    if (rc != NOSPLAN_OK) return rc;
     CU(h, cudaMemsetAsync(d_exchange, 0, (size_t)need, h->stream));
-    launch_prepass(h->pb, h->stream);                       // replicated: cheaper than exchanging the totals
-    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
     launch_tracker_init(h->pb, h->stream);
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[7], h->stream));
     DevProblem shard = h->pb;                               // this rank's slice of the name-ordered node list
@@ -650,16 +726,25 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
     CU(h, cudaSetDevice(h->device));
     unsigned char* O = h->h_out;
     const size_t o_mask = al(h->out_count_bytes), o_stats = o_mask + al(h->out_mask_bytes);
+    const bool want = out && h->out_count_bytes;
+    if (want && (!out->gpu_count || !out->gpu_mask)) return fail(h, NOSPLAN_E_INVALID, "null output buffers");
+    // page-locked caller buffers receive the plan straight from the copy engine; pageable ones go through pinned staging
+    bool direct = false;
+    if (want) {
+        cudaPointerAttributes a1, a2;
+        direct = cudaPointerGetAttributes(&a1, out->gpu_count) == cudaSuccess && a1.type == cudaMemoryTypeHost &&
+                 cudaPointerGetAttributes(&a2, out->gpu_mask) == cudaSuccess && a2.type == cudaMemoryTypeHost;
+        (void)cudaGetLastError();
+    }
     CU(h, cudaEventRecord(h->ev[4], h->stream));
     if (h->out_count_bytes) {
-        CU(h, cudaMemcpyAsync(O, h->pb.out_count, h->out_count_bytes, cudaMemcpyDeviceToHost, h->stream));
-        CU(h, cudaMemcpyAsync(O + o_mask, h->pb.out_mask, h->out_mask_bytes, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaMemcpyAsync(direct ? (void*)out->gpu_count : (void*)O, h->pb.out_count, h->out_count_bytes, cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaMemcpyAsync(direct ? (void*)out->gpu_mask : (void*)(O + o_mask), h->pb.out_mask, h->out_mask_bytes, cudaMemcpyDeviceToHost, h->stream));
     }
     CU(h, cudaMemcpyAsync(O + o_stats, h->pb.stats, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaEventRecord(h->ev[5], h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
-    if (out && h->out_count_bytes) {
-        if (!out->gpu_count || !out->gpu_mask) return fail(h, NOSPLAN_E_INVALID, "null output buffers");
+    if (want && !direct) {
         std::memcpy(out->gpu_count, O, h->out_count_bytes);
         std::memcpy(out->gpu_mask, O + o_mask, h->out_mask_bytes);
     }
@@ -669,15 +754,8 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         stats->candidates = ds.candidates; stats->visited_nodes = ds.visited_nodes; stats->geometry_evals = ds.geometry_evals;
         stats->placements = ds.placements; stats->candidate_nodes = ds.candidate_nodes;
         stats->lacking_at_start = ds.lacking_at_start; stats->lacking_at_end = ds.lacking_at_end;
-        cudaEventElapsedTime(&stats->ms_h2d, h->ev[0], h->ev[1]);
-        cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
+        nosplan_phase_times(h, stats);
         cudaEventElapsedTime(&stats->ms_d2h, h->ev[4], h->ev[5]);
-        if (h->kernel_events) {
-            cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
-            cudaEventElapsedTime(&stats->ms_tracker, h->ev[6], h->ev[7]);
-            cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
-            cudaEventElapsedTime(&stats->ms_sweep, h->ev[8], h->ev[3]);
-        }
         stats->path = ds.path;
         stats->kernel_launches = h->launches;
         stats->h2d_bytes = (int64_t)h->h2d_bytes;
@@ -693,7 +771,7 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
     int rc = nosplan_upload(h, snap, pods, prefilter_ok, filter_mode);
     h->in_plan = false;
     if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); return rc; }
-    rc = nosplan_run(h);
+    rc = h->pre_done ? run_post(h) : nosplan_run(h);       // upload() already queued the node-only kernels
     if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); return rc; }
     return nosplan_download(h, out, stats);
 }

@@ -1,6 +1,7 @@
 // The engine handle behind nosplan_t (include/nosplan.h).  Internal to libnosplan.
 #pragma once
 #include <string>
+#include <vector>
 
 #include "nosplan_dev.cuh"
 
@@ -10,7 +11,7 @@ struct nosplan_shard_ctx;          // in-library NCCL state of the node-sharded 
 struct nosplan {
     int device = -1;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[9] = {};
+    cudaEvent_t ev[12] = {};
     // device arena + pinned staging (grown on demand, reused across calls)
     unsigned char* d_arena = nullptr; size_t d_cap = 0;
     unsigned char* h_stage = nullptr; size_t h_cap = 0;
@@ -21,13 +22,24 @@ struct nosplan {
     bool in_plan = false, direct_h2d = false;   // H2D straight from page-locked caller memory (see nosplan_upload)
     nsp::DevProblem pb{};
     int32_t* d_cand_idx = nullptr;
-    unsigned char* d_work = nullptr; size_t work_bytes = 0;
+    unsigned char* d_work = nullptr; size_t work_bytes = 0;      // totals, lacking vector, counters, tracker tables: reset before k_prepass
+    bool pre_done = false, split_run = false;                    // nosplan_plan queued the node-only kernels from inside upload()
+    // host scratch reused across calls
+    std::vector<int> v_first_prof, v_order;
+    std::vector<uint32_t> v_flags;
+    std::vector<unsigned long long> v_cls;
+    std::vector<nsp::RunRec> v_runs;
+    std::vector<int32_t> v_chunk_off;
+    std::vector<long long> v_cmin;
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
     size_t h2d_bytes = 0;
     nosplan_quota_ctx* qctx = nullptr;
     nosplan_shard_ctx* sctx = nullptr;
     std::string err;
+    // NOSPLAN_TRACE=1 only: one event per H2D copy of the node arrays
+    cudaEvent_t dbg_ev[32] = {}; size_t dbg_bytes[32] = {}; bool dbg_direct[32] = {}; int dbg_n = 0;
 };
 
 int nosplan_fail(nosplan* h, int code, const char* fmt, ...);
+void nosplan_phase_times(nosplan* h, nosplan_stats* stats);

@@ -180,13 +180,7 @@ extern "C" int nosplan_download_sharded(nosplan_t* h, nosplan_partitioning* out,
         stats->placements = ds.placements; stats->candidate_nodes = ds.candidate_nodes;
         stats->lacking_at_start = ds.lacking_at_start; stats->lacking_at_end = ds.lacking_at_end;
         stats->path = ds.path; stats->kernel_launches = h->launches;
-        cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
-        if (h->kernel_events) {
-            cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
-            cudaEventElapsedTime(&stats->ms_tracker, h->ev[6], h->ev[7]);
-            cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
-            cudaEventElapsedTime(&stats->ms_sweep, h->ev[8], h->ev[3]);
-        }
+        nosplan_phase_times(h, stats);
         stats->h2d_bytes = (int64_t)h->h2d_bytes;
         stats->d2h_bytes = (int64_t)(nb_cnt + nb_msk + sizeof ds);
     }

@@ -29,6 +29,8 @@ for pinned in (False, True):
         snap = capi.pin_snapshot(snap)
         for _ in range(3): eng.plan(snap, pods, None, 2)
         print("plan (node arrays page-locked) ms", t(lambda: eng.plan(snap, pods, None, 2)))
+        hout = capi.pinned_partitioning(snap)
+        print("plan (+ plan buffers page-locked) ms", t(lambda: eng.plan(snap, pods, None, 2, out=hout)))
     print("---- trace of one nosplan_plan, pinned =", pinned, flush=True)
     os.environ["NOSPLAN_TRACE"] = "1"
     t0 = time.perf_counter(); eng.plan(snap, pods, None, 2); t1 = time.perf_counter()
