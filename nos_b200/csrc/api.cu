@@ -548,6 +548,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         }
     };
     bool single_profile_classes = true;
+    long long any_eph = 0;
     {
         long long* cpu = (long long*)(S + L.pod_cpu); long long* mem = (long long*)(S + L.pod_mem); long long* eph = (long long*)(S + L.pod_eph);
         int32_t* key = (int32_t*)(S + L.pod_key); uint32_t* fl = (uint32_t*)(S + L.pod_flags);
@@ -580,7 +581,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
                 const bool z = (f & PF_ZERO_REQ) != 0;
                 cm[0] = std::min(cm[0], z ? LLONG_MIN : bc); cm[1] = std::min(cm[1], z ? LLONG_MIN : bm); cm[2] = std::min(cm[2], z ? LLONG_MIN : be);
             }
-            cpu[si] = bc; mem[si] = bm; eph[si] = be;
+            cpu[si] = bc; mem[si] = bm; eph[si] = be; any_eph |= be;
             key[si] = pods->tracker_key[oi]; fl[si] = f;
             sptr[si] = w;
             for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1]; ++e) { scol[w] = pods->scalar_col[e]; sqty[w] = pods->scalar_qty[e]; ++w; }
@@ -620,6 +621,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     pb.cmin_cpu = (const long long*)(A + L.cmin_cpu); pb.cmin_mem = (const long long*)(A + L.cmin_mem); pb.cmin_eph = (const long long*)(A + L.cmin_eph);
     pb.n_chunks = n_chunks;
     pb.fast_eligible = single_profile_classes ? 1 : 0;
+    pb.no_eph = any_eph == 0 ? 1 : 0;
     {   // M_p: most devices of profile p one GPU can hold
         int mem_max = 0;
         if (!mig) for (size_t x = 0; x < NG; ++x) mem_max = std::max(mem_max, s->gpu_memory_gb[x]);

@@ -72,6 +72,7 @@ struct DevProblem {
     const long long* cmin_eph;
     int n_chunks;
     // node-parallel fast path (see sweep.cu): host-side eligibility and saturation bound per profile
+    int no_eph;                      // no pod requests ephemeral storage (the kernels then skip that column's sums)
     int fast_eligible;               // every pod class requests at most one slice profile
     int32_t sat_m[KP];               // M_p: most devices of profile p one GPU can hold (table rows / memory)
     // work area (zeroed before each run)
@@ -97,11 +98,13 @@ __device__ __forceinline__ unsigned byte_of(const uint4& v, int p) {
     return (w >> ((p & 3) * 8)) & 0xffu;
 }
 
+// bit p set <=> byte p of v is non-zero.  Per word: 0xff where the byte is non-zero, then the four byte MSBs are gathered
+// into the low nibble by one multiplication (bits 7,15,23,31 -> 28..31).
+__device__ __forceinline__ unsigned nz_nibble(unsigned w) {
+    return ((__vcmpne4(w, 0u) & 0x80808080u) * 0x00204081u) >> 28;
+}
 __device__ __forceinline__ uint16_t nz_mask(const uint4& v) {
-    uint16_t m = 0;
-#pragma unroll
-    for (int p = 0; p < KP; ++p) m |= (uint16_t)((byte_of(v, p) != 0) << p);
-    return m;
+    return (uint16_t)(nz_nibble(v.x) | (nz_nibble(v.y) << 4) | (nz_nibble(v.z) << 8) | (nz_nibble(v.w) << 12));
 }
 
 __device__ __forceinline__ uint4 add_bytes(const uint4& a, const uint4& b) {

@@ -1,6 +1,7 @@
 // Snapshot pre-pass and tracker initialisation kernels (grid-wide, HBM streaming).
 //
-//   k_prepass       one warp per node (grid-stride): reads every node row once with 128-bit loads,
+//   k_prepass       tiles of 32 nodes per block: phase 1 one thread per GPU row (consecutive threads read consecutive
+//                   128-bit rows), phase 2 one thread per (node, profile) pair over the rows staged in shared memory,
 //                   emits  (a) the initial partitioning state  GetPartitioningState  (core/snapshot.go:66-72,
 //                              internal/partitioning/mig/partitition_calculator.go:30-46)
 //                          (b) the candidate flag  HasFreeCapacity  (pkg/gpu/mig/node.go:124-139,
@@ -14,68 +15,91 @@
 
 namespace nsp {
 
+constexpr int PRE_NODES = 32;                        // nodes per tile
+constexpr int PRE_ROWS = PRE_NODES * NOSPLAN_MAX_GPUS; // GPU rows per tile at most
+
 __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
     __shared__ uint4 s_geom[MAX_ROWS];
     __shared__ uint16_t s_gmask[MAX_ROWS];
     __shared__ int s_off[MAX_MODELS + 1];
+    __shared__ uint4 s_used[PRE_ROWS], s_free[PRE_ROWS];     // the tile's GPU rows, zero where the node has no such GPU
+    __shared__ uint8_t s_hasfree[PRE_ROWS];
     __shared__ long long s_acc[8][KP];
     __shared__ int s_maxfree[8][KP];
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool mig = pb.kind == NOSPLAN_KIND_MIG;
+    const int G = pb.G, K = pb.K;
     if (mig) {
-        for (int r = threadIdx.x; r < pb.n_rows; r += blockDim.x) {
+        for (int r = tid; r < pb.n_rows; r += blockDim.x) {
             uint4 row = pb.geom[r];
             s_geom[r] = row;
             s_gmask[r] = nz_mask(row);
         }
-        for (int m = threadIdx.x; m <= pb.n_models; m += blockDim.x) s_off[m] = pb.model_off[m];
+        for (int m = tid; m <= pb.n_models; m += blockDim.x) s_off[m] = pb.model_off[m];
     }
     __syncthreads();
 
+    // this thread's profile in phase 2 never changes: (node-in-tile, profile) pairs are laid out 16 profiles per node
+    const int my_p = tid & (KP - 1);
     long long acc = 0;
     int maxfree = 0;
     bool inconsistent = false;
-    const int warps_total = gridDim.x * (blockDim.x >> 5);
-    for (int i = blockIdx.x * (blockDim.x >> 5) + warp; i < pb.N; i += warps_total) {
-        const int ng = pb.node_gpu_count[i];
-        bool has_free = false;
-        if (lane < ng) {
-            const int x = i * pb.G + lane;
-            const uint4 used = pb.gpu_used[x], fre = pb.gpu_free[x];
-            const uint16_t um = pb.gpu_umask[x], fm = pb.gpu_fmask[x];
-            const uint4 cnt = add_bytes(used, fre);
-            const uint16_t gm = um | fm;
-            pb.out_count[x] = cnt;
-            pb.out_mask[x] = gm;
-            if (mig) {
-                has_free = fm != 0;
-                if (!has_free) {                     // AllowsGeometry(GetGeometry()) (mig/gpu.go:215-222)
-                    const int m = pb.gpu_model[x];
-                    bool allowed = false;
-                    for (int r = s_off[m]; r < s_off[m + 1]; ++r) {
-                        const uint4 row = s_geom[r];
-                        allowed |= (s_gmask[r] == gm) && row.x == cnt.x && row.y == cnt.y && row.z == cnt.z && row.w == cnt.w;
+    const int n_tiles = (pb.N + PRE_NODES - 1) / PRE_NODES;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int node0 = tile * PRE_NODES;
+        const int rows = PRE_NODES * G;
+        // ---- phase 1: one thread per GPU row, consecutive threads read consecutive rows (128-bit loads)
+        for (int r = tid; r < rows; r += blockDim.x) {
+            const int nl = r / G, j = r - nl * G, i = node0 + nl;
+            uint4 used = make_uint4(0, 0, 0, 0), fre = used;
+            bool has_free = false;
+            if (i < pb.N && j < pb.node_gpu_count[i]) {
+                const int x = i * G + j;
+                used = pb.gpu_used[x]; fre = pb.gpu_free[x];
+                const uint16_t um = pb.gpu_umask[x], fm = pb.gpu_fmask[x];
+                const uint4 cnt = add_bytes(used, fre);
+                const uint16_t gm = um | fm;
+                pb.out_count[x] = cnt;
+                pb.out_mask[x] = gm;
+                if (mig) {
+                    has_free = fm != 0;
+                    if (!has_free) {                     // AllowsGeometry(GetGeometry()) (mig/gpu.go:215-222)
+                        const int m = pb.gpu_model[x];
+                        bool allowed = false;
+                        for (int q = s_off[m]; q < s_off[m + 1]; ++q) {
+                            const uint4 row = s_geom[q];
+                            allowed |= (s_gmask[q] == gm) && row.x == cnt.x && row.y == cnt.y && row.z == cnt.z && row.w == cnt.w;
+                        }
+                        has_free = !allowed;
                     }
-                    has_free = !allowed;
-                }
-            } else {                                 // slicing GPU.HasFreeCapacity (slicing/gpu.go:131-136)
-                int tot = 0;
+                } else {                                 // slicing GPU.HasFreeCapacity (slicing/gpu.go:131-136)
+                    int tot = 0;
 #pragma unroll
-                for (int p = 0; p < KP; ++p) tot += pb.pmem[p] * (int)byte_of(cnt, p);
-                has_free = fm != 0 || (pb.gpu_mem[x] - tot >= 1);
+                    for (int p = 0; p < KP; ++p) tot += pb.pmem[p] * (int)byte_of(cnt, p);
+                    has_free = fm != 0 || (pb.gpu_mem[x] - tot >= 1);
+                }
             }
+            s_used[r] = used; s_free[r] = fre; s_hasfree[r] = has_free;
         }
-        const unsigned any = __ballot_sync(0xffffffffu, has_free);
-        if (lane == 0) pb.cand_flag[i] = any != 0;
-        if (lane < pb.K) {
-            const size_t o = (size_t)i * pb.R + 3 + lane;
+        __syncthreads();
+        // ---- phase 2a: HasFreeCapacity of the node = any of its GPUs
+        if (tid < PRE_NODES && node0 + tid < pb.N) {
+            bool any = false;
+            for (int j = 0; j < G; ++j) any |= s_hasfree[tid * G + j] != 0;
+            pb.cand_flag[node0 + tid] = any;
+        }
+        // ---- phase 2b: (node, profile) pairs: totals, largest free count, node accounts vs GPU maps
+        for (int pr = tid; pr < PRE_NODES * KP; pr += blockDim.x) {
+            const int nl = pr / KP, i = node0 + nl;          // pr % KP == my_p
+            if (i >= pb.N || my_p >= K) continue;
+            const size_t o = (size_t)i * pb.R + 3 + my_p;
             const long long a = pb.node_alloc[o], r = pb.node_req[o];
             acc += a - r;
-            long long sum_free = 0, sum_used = 0;
-            const uint8_t* fb = reinterpret_cast<const uint8_t*>(pb.gpu_free) + (size_t)i * pb.G * 16 + lane;
-            const uint8_t* ub = reinterpret_cast<const uint8_t*>(pb.gpu_used) + (size_t)i * pb.G * 16 + lane;
-            for (int g = 0; g < ng; ++g) {
+            int sum_free = 0, sum_used = 0;
+            const uint8_t* fb = reinterpret_cast<const uint8_t*>(s_free + nl * G) + my_p;
+            const uint8_t* ub = reinterpret_cast<const uint8_t*>(s_used + nl * G) + my_p;
+            for (int g = 0; g < G; ++g) {
                 const int f = fb[16 * g];
                 sum_free += f; sum_used += ub[16 * g];
                 maxfree = max(maxfree, f);
@@ -83,11 +107,15 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
             // gate (core/snapshot.go:132-165) can only be implied by GPU.AddPod feasibility if the node accounts agree
             inconsistent |= (a - r < sum_free) || (r > sum_used);
         }
+        __syncthreads();
     }
     if (__any_sync(0xffffffffu, inconsistent) && lane == 0) atomicOr(&pb.gflags[0], 1);
+    // lanes p and p+16 of a warp hold the same profile
+    acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+    maxfree = max(maxfree, __shfl_xor_sync(0xffffffffu, maxfree, 16));
     if (lane < KP) { s_acc[warp][lane] = acc; s_maxfree[warp][lane] = maxfree; }
     __syncthreads();
-    if (warp == 0 && lane < pb.K) {
+    if (warp == 0 && lane < K) {
         long long t = 0;
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_acc[w][lane];
         if (t != 0) atomicAdd((unsigned long long*)&pb.tot[lane], (unsigned long long)t);
@@ -124,7 +152,7 @@ __global__ void __launch_bounds__(256) k_tracker_init(DevProblem pb) {
 
 void launch_prepass(const DevProblem& pb, cudaStream_t st) {
     if (pb.N > 0) {
-        int blocks = (pb.N + 7) / 8;
+        int blocks = (pb.N + PRE_NODES - 1) / PRE_NODES;      // one tile of 32 nodes per block, grid-stride beyond 8 waves
         if (blocks > 148 * 8) blocks = 148 * 8;
         k_prepass<<<blocks, 256, 0, st>>>(pb);
     }

@@ -72,7 +72,19 @@ struct PodCache {          // run records of the first RUN_CACHE runs; first 32 
     const RunRec* runs;    // shared-memory copy of the first n_cached run records
     const int* chunk_off;  // shared-memory copy of run_chunk_off for those runs
     int n_cached;
+    // bit r of prof_runs[p]: cached run r requests profile p and nothing else; prof_runs[KP]: slice-less or multi-profile runs
+    const unsigned long long* prof_runs;
 };
+
+// built by the whole CTA once the run records are in shared memory (RUN_CACHE == 64 runs == one 64-bit word per profile)
+__device__ __forceinline__ void build_run_masks(const RunRec* s_runs, int n_cached, unsigned long long* s_masks, int tid, int nthreads) {
+    for (int p = tid; p <= KP; p += nthreads) s_masks[p] = 0;
+    __syncthreads();
+    for (int r = tid; r < n_cached; r += nthreads)
+        atomicOr(&s_masks[s_runs[r].n_ent == 1 ? s_runs[r].p_single : KP], 1ull << r);
+    __syncthreads();
+}
+static_assert(RUN_CACHE == 64, "one 64-bit word of runs per profile");
 
 struct NodeRegs {          // one node spread over the lanes of a warp
     uint4 used, fre;
@@ -117,6 +129,14 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
     return v;
 }
 __device__ __forceinline__ int warp_sum_int(int v) { return __reduce_add_sync(FULL, v); }
+// sum of 32 NON-NEGATIVE int64 with the 32-bit warp-reduce unit: three 21-bit limbs, each limb sum < 2^26
+__device__ __forceinline__ long long warp_sum_nonneg_ll(long long v) {
+    const unsigned long long u = (unsigned long long)v;
+    const unsigned s0 = __reduce_add_sync(FULL, (unsigned)(u & 0x1fffffu));
+    const unsigned s1 = __reduce_add_sync(FULL, (unsigned)((u >> 21) & 0x1fffffu));
+    const unsigned s2 = __reduce_add_sync(FULL, (unsigned)(u >> 42));
+    return (long long)((unsigned long long)s0 + ((unsigned long long)s1 << 21) + ((unsigned long long)s2 << 42));
+}
 
 __device__ __forceinline__ long long warp_excl_ll(long long v, int lane) {
     long long s = v;
@@ -350,6 +370,8 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     if (lane < KP) { ws.allocF[lane] = allocF; ws.reqF[lane] = oldR; ws.Dg[lane] = PAR ? 0 : D - oldA + allocF; }
     long long remc = nd.alloc[0] - nd.req[0], remm = nd.alloc[1] - nd.req[1], reme = nd.alloc[2] - nd.req[2];
     const bool podcount_ok = nd.npods + 1 <= nd.allowed;
+    // no pod requests ephemeral storage and the node is not over-committed on it: every `0 <= reme` test holds
+    const bool use_eph = !(pb.no_eph && reme >= 0);
     const bool fit = fm == NOSPLAN_FILTER_RESOURCES_FIT;
     __syncwarp();
     // profiles with at least one free device on some GPU of the node: a single-profile class outside this set cannot place
@@ -361,12 +383,20 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     // ---- 2. the pod loop, run by run
     int added = 0;
     const bool all_fail = (fm == NOSPLAN_FILTER_REJECT_ALL) || (fit && !podcount_ok);
-    for (int ri = 0; ri < pb.n_runs && !all_fail; ++ri) {
+    // cached runs: only those whose single profile has a free device somewhere on the node (plus slice-less / multi-profile ones)
+    unsigned long long live = pc->prof_runs[KP];
+    for (unsigned f = feas; f; f &= f - 1) live |= pc->prof_runs[__ffs(f) - 1];
+    int next_uncached = pc->n_cached;
+    while (!all_fail) {
+        int ri;
+        if (live) { ri = __ffsll((long long)live) - 1; live &= live - 1; }
+        else if (next_uncached < pb.n_runs) ri = next_uncached++;
+        else break;
         const bool rcached = ri < pc->n_cached;
         const bool cached = rcached && pc->cpu != nullptr;
         const RunRec* rr = rcached ? &pc->runs[ri] : &pb.runs[ri];
         const int n_ent = rr->n_ent;
-        if (n_ent == 1 && !(feas >> rr->p_single & 1)) continue;
+        if (!rcached && n_ent == 1 && !(feas >> rr->p_single & 1)) continue;
         const int rstart = rr->start, rend = rr->start + rr->len;
         const int q_l = (lane < KP) ? (int)rr->q[lane] : 0;
         // class-level tests; all of them only get tighter while this node is processed
@@ -396,7 +426,10 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
             for (int cb = 0; cb < nch && cap > 0; cb += 32) {
                 // chunk minima of 32 chunks at a time: a chunk whose cheapest eligible pod does not fit is skipped
                 long long mc = LLONG_MAX, mm = LLONG_MAX, me = LLONG_MAX;
-                if (cb + lane < nch) { mc = pb.cmin_cpu[c0 + cb + lane]; mm = pb.cmin_mem[c0 + cb + lane]; me = pb.cmin_eph[c0 + cb + lane]; }
+                if (cb + lane < nch) {
+                    mc = pb.cmin_cpu[c0 + cb + lane]; mm = pb.cmin_mem[c0 + cb + lane];
+                    me = use_eph ? pb.cmin_eph[c0 + cb + lane] : 0;        // !use_eph: reme >= 0, the test below holds
+                }
                 int cdone = 0;
                 while (cap > 0) {
                     bool pass = mc != LLONG_MAX && lane >= cdone;
@@ -414,7 +447,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                             cpu = pc->cpu[ri][lane]; mem = pc->mem[ri][lane]; eph = pc->eph[ri][lane];
                             key = pc->key[ri][lane]; fl = pc->flag[ri][lane];
                         } else {
-                            cpu = pb.pod_cpu[s]; mem = pb.pod_mem[s]; eph = pb.pod_eph[s];
+                            cpu = pb.pod_cpu[s]; mem = pb.pod_mem[s]; if (use_eph) eph = pb.pod_eph[s];
                             key = pb.pod_key[s]; fl = pb.pod_flags[s];
                         }
                     }
@@ -435,10 +468,11 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                         long long sc = 0, sm = 0, se = 0;
                         int firstfail = 32;
                         if (fit) {
-                            sc = warp_sum_ll(cand ? cpu : 0); sm = warp_sum_ll(cand ? mem : 0); se = warp_sum_ll(cand ? eph : 0);
+                            sc = warp_sum_nonneg_ll(cand ? cpu : 0); sm = warp_sum_nonneg_ll(cand ? mem : 0);
+                            se = use_eph ? warp_sum_nonneg_ll(cand ? eph : 0) : 0;
                             if (sc > remc || sm > remm || se > reme) {
                                 const long long ec = warp_excl_ll(cand ? cpu : 0, lane), em = warp_excl_ll(cand ? mem : 0, lane),
-                                                ee = warp_excl_ll(cand ? eph : 0, lane);
+                                                ee = use_eph ? warp_excl_ll(cand ? eph : 0, lane) : 0;
                                 const bool test = cand && (zero || (cpu <= remc - ec && mem <= remm - em && eph <= reme - ee));
                                 const unsigned failm = __ballot_sync(FULL, cand && !test);
                                 if (failm) {
@@ -628,26 +662,33 @@ __device__ __forceinline__ bool fast_applicable(const DevProblem& pb, int lack_p
 
 // ------------------------------------------------------------------------------------------------------------
 // node-parallel pass: grid-stride, one warp per candidate node
-__global__ void __launch_bounds__(128) k_plan_parallel(DevProblem pb) {
+#ifndef PAR_MIN_BLOCKS
+#define PAR_MIN_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProblem pb) {
     __shared__ Tables tb;
     __shared__ WarpScratch ws_all[4];
     __shared__ RunRec s_runs[RUN_CACHE];
     __shared__ int s_choff[RUN_CACHE];
+    __shared__ unsigned long long s_masks[KP + 1];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
     if (!fast_applicable(pb, lack0, lane)) return;
     load_tables(pb, tb, tid, blockDim.x);
     PodCache pc;
     pc.cpu = nullptr; pc.mem = nullptr; pc.eph = nullptr; pc.key = nullptr; pc.flag = nullptr;
-    pc.runs = s_runs; pc.chunk_off = s_choff; pc.n_cached = min(pb.n_runs, RUN_CACHE);
+    pc.runs = s_runs; pc.chunk_off = s_choff; pc.n_cached = min(pb.n_runs, RUN_CACHE); pc.prof_runs = s_masks;
     for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
     __syncthreads();
+    build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
 
     WarpScratch& ws = ws_all[warp];
     int lack = lack0 > 0 ? SATURATED : 0;
     long long D = 0, st_evals = 0, st_place = 0, visited = 0;
     bool committed = true;
-    // dynamic distribution: nodes differ a lot in cost (how many runs are feasible), so warps pull the next node
+    // dynamic distribution: nodes differ a lot in cost (how many runs are feasible), so warps pull the next node.  Pulling
+    // ahead of need (to hide the counter's round trip or to prefetch rows) was measured slower: with ~3 nodes per warp the
+    // reserved nodes wait behind a busy warp while other warps idle.
     for (;;) {
         int i = 0;
         if (lane == 0) i = pb.node_lo + atomicAdd(pb.next_node, 1);
@@ -676,6 +717,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     __shared__ RunRec s_runs[RUN_CACHE];
     __shared__ int s_choff[RUN_CACHE];
     __shared__ int s_scan[256];
+    __shared__ unsigned long long s_masks[KP + 1];
     __shared__ int s_ncand, s_fast_ok;
     __shared__ int s_lackend[KP];
 
@@ -691,6 +733,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     pc.runs = s_runs;
     pc.chunk_off = s_choff;
     pc.n_cached = min(pb.n_runs, RUN_CACHE);
+    pc.prof_runs = s_masks;
     unsigned* s_removed = reinterpret_cast<unsigned*>(pc.flag + RUN_CACHE);      // [(n_keys+31)/32]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -746,6 +789,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x) s_removed[w] = 0;
     for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
     __syncthreads();
+    build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
     for (int t = tid; t < pc.n_cached * 32; t += blockDim.x) {
         const int r = t >> 5, l = t & 31;
         if (l < s_runs[r].len) {
