@@ -171,11 +171,15 @@ def run_ours(args):
     if not os.path.exists(g.LIB):
         g.build()
 
-    # N > 1: ONE Plan() over a snapshot of world x nodes (per-GPU node count fixed: weak scaling), node-sharded: every rank
-    # uploads the same snapshot, runs the node-parallel pass on its slice of the name-ordered node list, and the ranks
-    # exchange one all-gather of counters + placed-key bitmap (NCCL), then all-gather the plan rows (nos_b200/sharded.py).
+    # N > 1: ONE Plan() over a snapshot of world x nodes (per-GPU node count fixed: weak scaling) in slice mode: every rank
+    # holds ONLY its own slice of the name-ordered node list (H2D, k_prepass, node-parallel pass and plan rows are per-rank
+    # work); two NCCL all-gathers per Plan(): 256 B of cluster totals per rank, then counters + placed-key bitmap.
     kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
     snap, pods = make_workload(args.workload, nodes=n_full * world)
+    if world > 1:
+        from nos_b200 import sharded
+        full_snap = snap
+        snap = sharded.slice_snapshot(full_snap, rank * n_full, (rank + 1) * n_full, pad_to=n_full)
     eng = capi.Engine(local)
     eng.upload(snap, pods, None, FILTER_RESOURCES_FIT)
     dev = torch.device("cuda", local)
@@ -196,14 +200,16 @@ def run_ours(args):
     def one_step(timed):
         with torch.cuda.stream(ext):
             flush.zero_()
+        if sharded_run:                      # ranks enter the step together: a late peer would otherwise be timed as NCCL wait
+            sync_all()
         s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
         s.record(ext)
         if sharded_run:
-            eng.run_sharded(True)
+            eng.run_sliced()
         else:
             eng.run()
         e.record(ext)
-        _, _, st = eng.download_sharded() if sharded_run else eng.download()   # synchronises; outside the timed pair of events
+        _, _, st = eng.download()            # synchronises; outside the timed pair of events
         return s.elapsed_time(e), st
 
     for _ in range(max(3, args.warmup)):
@@ -231,8 +237,8 @@ def run_ours(args):
         if not sharded_run:
             return eng.plan(hsnap, pods, None, FILTER_RESOURCES_FIT, out=hout)[2]
         eng.upload(hsnap, pods, None, FILTER_RESOURCES_FIT)
-        eng.run_sharded(True)
-        return eng.download_sharded()[2]
+        eng.run_sliced()
+        return eng.download(out=hout)[2]
 
     for _ in range(2):
         e2e_once()
@@ -262,7 +268,7 @@ def run_ours(args):
     value = cands_all * args.steps / (total_ms / 1e3)
     e2e_value = cands_all * args.steps / e2e_total
     peak, peak_src = measured_peak()
-    b_plan = algorithmic_bytes(snap, pods)
+    b_plan = algorithmic_bytes(snap, pods)       # per GPU: its own node rows and the (replicated) pods
     sweep_avg_ms = float(np.mean(sweep_ms))
     # dominant kernel: the node-parallel pass when it produced the plan, else the sequential sweep
     dom_name = "k_plan_parallel" if st["path"] == 1 else "k_plan_sweep"
@@ -274,12 +280,14 @@ def run_ours(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
         "config": {"workload": args.workload, "kind": kind, "nodes": n_full * world, "gpus_per_node": gg, "pods": p_full,
                    "regime": "saturating", "filter": "resources_fit",
-                   "parallelism": "single GPU" if world == 1 else f"node-sharded x{world}: {n_full} nodes per GPU, one all-gather of "
-                                  f"{eng.shard_exchange_bytes()} B per rank on the data path + all-gather of the plan rows, one grouped NCCL launch",
+                   "parallelism": "single GPU" if world == 1 else f"node-sliced x{world}: each GPU holds {n_full} nodes; two NCCL all-gathers "
+                                  f"per Plan() (256 B of cluster totals, then {eng.shard_exchange_bytes()} B of counters + placed-key bitmap per rank); "
+                                  f"plan rows stay on their rank",
                    "l2": "flushed between iterations (256 MiB device write)", "candidates_per_plan": cands,
                    "visited_nodes": int(st["visited_nodes"]), "placements": int(st["placements"])},
         "plan_p50_ms": float(np.median(step_ms)), "plan_p95_ms": float(np.percentile(step_ms, 95)),
-        "kernel_ms": {"prepass": float(st["ms_prepass"]), "tracker_init": float(st["ms_tracker"]), "parallel": float(np.mean(par_ms)),
+        "kernel_ms": {"prepass": float(st["ms_prepass"]), "tracker_init" if world == 1 else "totals_exchange+tracker_init": float(st["ms_tracker"]),
+                      "parallel": float(np.mean(par_ms)),
                       "verify_or_sweep" if world == 1 else "exchange+verify": sweep_avg_ms, "path": "node-parallel" if st["path"] == 1 else "sequential"},
         "roofline": {"bound": "hbm", "kernel": dom_name, "kernel_ms": dom_ms, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": recorded_traffic(dom_name) if (args.workload == "mig-10k" and world == 1) else None, "algorithmic_bytes": b_plan, "peak_source": peak_src},
@@ -288,7 +296,7 @@ def run_ours(args):
                 "ms_h2d": float(est["ms_h2d"]), "ms_kernels": float(est["ms_kernels"]), "ms_d2h": float(est["ms_d2h"]),
                 "host_buffers": "caller's node arrays and plan buffers page-locked and DMA'd in place; pod arrays (pageable) re-ordered by "
                                 "NewPodSorter into pinned staging while the node DMA and k_prepass run"
-                                if world == 1 else "node arrays page-locked and DMA'd in place; plan gathered through pinned staging"},
+                                if world == 1 else "per rank: its slice's node arrays and plan rows page-locked and DMA'd in place"},
         "gpu_launches": int(st["kernel_launches"]) * args.steps,
         "clocks": clocks,
     }

@@ -183,6 +183,25 @@ int nosplan_shard_init(nosplan_t* h, int32_t rank, int32_t world, const uint8_t*
 int nosplan_run_sharded(nosplan_t* h, int32_t gather_plan);
 int nosplan_download_sharded(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats);
 
+/* Slice mode: every rank uploads ONLY its own contiguous slice of the name-ordered node list (rank order == name order;
+ * the same pods, profiles and geometry tables everywhere), so H2D, k_prepass and the plan rows are per-rank work and the
+ * job scales weakly.  Two small exchanges per Plan(): the slice's cluster totals (one NOSPLAN_SLICE_TOTALS_BYTES block per
+ * rank: sums of allocatable - requested per slice resource, largest free counts, consistency flags) between k_prepass
+ * and the tracker, then the exchange block of the replicated protocol above.
+ *   slice_begin(): totals of the slice -> d_totals (device, caller-owned);   caller all-gathers into [world][256];
+ *   slice_mid():   folds the gathered totals, tracker initialisation, node-parallel pass on the slice -> d_exchange;
+ *   caller all-gathers the exchange blocks, then nosplan_shard_end() as above; nosplan_download() returns the slice's rows
+ *   and the job-wide counters.
+ * The sequential sweep needs the whole snapshot on one GPU: where the node-parallel pass does not apply (or its
+ * hypothesis fails a posteriori) nosplan_download returns NOSPLAN_SLICED_NOT_APPLICABLE on EVERY rank (same data, same
+ * verdict) and the caller plans that problem unsharded (nosplan_plan on the whole snapshot, or the replicated protocol).
+ * nosplan_run_sliced does the three steps with the library's own NCCL communicator (nosplan_shard_init). */
+#define NOSPLAN_SLICE_TOTALS_BYTES 256
+#define NOSPLAN_SLICED_NOT_APPLICABLE 1
+int nosplan_slice_begin(nosplan_t* h, void* d_totals);
+int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes);
+int nosplan_run_sliced(nosplan_t* h);
+
 /* No counterpart in the reference.  The tracker initialisation of Plan() -- lacking[p] summed over the pods, and the
  * number of distinct pod keys that lack any slice -- for callers that may not allocate device memory: processes
  * sharing the GPU with latency-sensitive streams (cudaMalloc/cudaFree synchronise the whole device) or running inside a

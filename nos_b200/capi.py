@@ -24,7 +24,10 @@ EXPORTED_SYMBOLS = [
     "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
+    "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced",
 ]
+SLICE_TOTALS_BYTES = 256
+SLICED_NOT_APPLICABLE = 1
 
 
 def host_pod_order(snap: PackedSnapshot, pods: PackedPods, lib_path: str = None) -> np.ndarray:
@@ -185,6 +188,10 @@ class NosplanError(RuntimeError):
     pass
 
 
+class SlicedNotApplicable(NosplanError):
+    """nosplan_download returned NOSPLAN_SLICED_NOT_APPLICABLE (same verdict on every rank)."""
+
+
 def load_library(path: str = LIB_PATH) -> C.CDLL:
     if not os.path.exists(path):
         raise NosplanError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
@@ -230,6 +237,12 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_run_sharded.restype = C.c_int
     lib.nosplan_download_sharded.argtypes = [C.c_void_p, C.POINTER(CPartitioning), C.POINTER(CStats)]
     lib.nosplan_download_sharded.restype = C.c_int
+    lib.nosplan_slice_begin.argtypes = [C.c_void_p, C.c_void_p]
+    lib.nosplan_slice_begin.restype = C.c_int
+    lib.nosplan_slice_mid.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64]
+    lib.nosplan_slice_mid.restype = C.c_int
+    lib.nosplan_run_sliced.argtypes = [C.c_void_p]
+    lib.nosplan_run_sliced.restype = C.c_int
     from . import victim_packing as vp
     lib.nosplan_quota_victims.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(vp.CVictimQuery), C.c_void_p, C.POINTER(CStats)]
     lib.nosplan_quota_victims.restype = C.c_int
@@ -308,8 +321,20 @@ class Engine:
     def download(self, out=None):
         out, cnt, msk = alloc_partitioning(self._snap, out)
         st = CStats()
-        self._check(self.lib.nosplan_download(self.h, C.byref(out), C.byref(st)), "nosplan_download")
+        rc = self.lib.nosplan_download(self.h, C.byref(out), C.byref(st))
+        if rc == SLICED_NOT_APPLICABLE:      # slice mode only: this problem needs the whole snapshot on one GPU
+            raise SlicedNotApplicable("the node-parallel pass does not apply: plan this problem unsharded")
+        self._check(rc, "nosplan_download")
         return cnt, msk, st.as_dict()
+
+    def slice_begin(self, d_totals: int):
+        self._check(self.lib.nosplan_slice_begin(self.h, d_totals), "nosplan_slice_begin")
+
+    def slice_mid(self, rank: int, world: int, d_totals_gathered: int, d_exchange: int, nbytes: int):
+        self._check(self.lib.nosplan_slice_mid(self.h, rank, world, d_totals_gathered, d_exchange, nbytes), "nosplan_slice_mid")
+
+    def run_sliced(self):
+        self._check(self.lib.nosplan_run_sliced(self.h), "nosplan_run_sliced")
 
     def set_kernel_events(self, on: bool):
         self.lib.nosplan_set_kernel_events.argtypes = [C.c_void_p, C.c_int32]

@@ -21,6 +21,8 @@ void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
 cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st);
 void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, cudaStream_t st);
+void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st);
+void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, cudaStream_t st);
 cudaError_t sweep_prepare_device();
 int sweep_max_keys();
 }  // namespace nsp
@@ -465,7 +467,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     DevProblem& pb = h->pb;
     std::memset(&pb, 0, sizeof pb);
     pb.kind = s->kind; pb.K = K; pb.R = R; pb.n_other = s->n_other;
-    pb.node_lo = 0; pb.node_hi = N;
+    pb.node_lo = 0; pb.node_hi = N; pb.slice_mode = 0;
     pb.N = N; pb.G = G; pb.P = P; pb.filter_mode = filter_mode;
     pb.n_models = n_models; pb.n_rows = n_rows;
     for (int p = 0; p < KP; ++p) { pb.pmem[p] = p < K ? s->profile_mem_gb[p] : 0; pb.pgi[p] = p < K ? s->profile_gi[p] : 0; }
@@ -622,17 +624,10 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     pb.n_chunks = n_chunks;
     pb.fast_eligible = single_profile_classes ? 1 : 0;
     pb.no_eph = any_eph == 0 ? 1 : 0;
-    {   // M_p: most devices of profile p one GPU can hold
-        int mem_max = 0;
-        if (!mig) for (size_t x = 0; x < NG; ++x) mem_max = std::max(mem_max, s->gpu_memory_gb[x]);
-        for (int p = 0; p < KP; ++p) {
-            int m = 0;
-            if (p < K) {
-                if (mig) for (int r = 0; r < n_rows; ++r) m = std::max(m, (int)s->geom_counts[16 * (size_t)r + p]);
-                else m = s->profile_mem_gb[p] > 0 ? mem_max / s->profile_mem_gb[p] : -1;
-            }
-            pb.sat_m[p] = m;
-        }
+    for (int p = 0; p < KP; ++p) {   // MIG M_p: most devices of profile p in any allowed geometry (MPS: derived on the device from gflags[1])
+        int m = 0;
+        if (mig && p < K) for (int r = 0; r < n_rows; ++r) m = std::max(m, (int)s->geom_counts[16 * (size_t)r + p]);
+        pb.sat_m[p] = m;
     }
     pb.placed = (unsigned*)(A + L.placed);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
@@ -662,6 +657,7 @@ int nosplan_run(nosplan_t* h) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_run before nosplan_upload");
     CU(h, cudaSetDevice(h->device));
+    h->pb.slice_mode = 0;
     int rc = run_pre(h, false);
     if (rc != NOSPLAN_OK) return rc;
     return run_post(h);
@@ -680,6 +676,7 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
     const int64_t need = nosplan_shard_exchange_bytes(h);
     if (!d_exchange || exchange_bytes < need) return fail(h, NOSPLAN_E_INVALID, "exchange buffer smaller than %lld bytes", (long long)need);
     CU(h, cudaSetDevice(h->device));
+    h->pb.slice_mode = 0;
     int rc = run_pre(h, false);                             // prepass replicated: cheaper than exchanging the totals
     if (rc != NOSPLAN_OK) return rc;
     CU(h, cudaMemsetAsync(d_exchange, 0, (size_t)need, h->stream));
@@ -696,6 +693,43 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
     CU(h, launch_parallel(shard, h->stream));
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
     h->launches = (h->pb.N > 0) + (h->pb.P > 0) + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
+    return NOSPLAN_OK;
+}
+
+// ---- slice mode: every rank uploaded ONLY its own slice of the name-ordered node list -------------------------------
+int nosplan_slice_begin(nosplan_t* h, void* d_totals) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_slice_begin before nosplan_upload");
+    if (!d_totals) return fail(h, NOSPLAN_E_INVALID, "null totals buffer");
+    CU(h, cudaSetDevice(h->device));
+    h->pb.slice_mode = 1;
+    int rc = run_pre(h, false);                             // cluster totals of the slice
+    if (rc != NOSPLAN_OK) return rc;
+    launch_slice_pack_totals(h->pb, d_totals, h->stream);
+    CU(h, cudaGetLastError());
+    h->launches = (h->pb.N > 0) + 1;
+    return NOSPLAN_OK;
+}
+
+int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded || !h->pb.slice_mode) return fail(h, NOSPLAN_E_INVALID, "nosplan_slice_mid before nosplan_slice_begin");
+    if (world < 1 || rank < 0 || rank >= world) return fail(h, NOSPLAN_E_INVALID, "rank %d of %d", rank, world);
+    const int64_t need = nosplan_shard_exchange_bytes(h);
+    if (!d_totals_gathered || !d_exchange || exchange_bytes < need) return fail(h, NOSPLAN_E_INVALID, "exchange buffer smaller than %lld bytes", (long long)need);
+    CU(h, cudaSetDevice(h->device));
+    launch_slice_combine_totals(h->pb, d_totals_gathered, world, h->stream);   // cluster-wide totals on every rank
+    CU(h, cudaMemsetAsync(d_exchange, 0, (size_t)need, h->stream));
+    launch_tracker_init(h->pb, h->stream);
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[7], h->stream));
+    DevProblem shard = h->pb;                               // the whole local snapshot IS this rank's slice
+    shard.whole_snapshot = 0;
+    shard.acc = static_cast<unsigned long long*>(d_exchange);
+    shard.placed = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(d_exchange) + 32);
+    CU(h, cudaGetLastError());
+    CU(h, launch_parallel(shard, h->stream));
+    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
+    h->launches += 1 + (h->pb.P > 0) + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     return NOSPLAN_OK;
 }
 
@@ -762,6 +796,10 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         stats->kernel_launches = h->launches;
         stats->h2d_bytes = (int64_t)h->h2d_bytes;
         stats->d2h_bytes = (int64_t)(h->out_count_bytes + h->out_mask_bytes + sizeof(DevStats));
+    }
+    if (h->pb.slice_mode) {
+        DevStats ds; std::memcpy(&ds, O + o_stats, sizeof ds);
+        if (ds.pad) return NOSPLAN_SLICED_NOT_APPLICABLE;
     }
     return NOSPLAN_OK;
 }

@@ -74,7 +74,8 @@ struct DevProblem {
     // node-parallel fast path (see sweep.cu): host-side eligibility and saturation bound per profile
     int no_eph;                      // no pod requests ephemeral storage (the kernels then skip that column's sums)
     int fast_eligible;               // every pod class requests at most one slice profile
-    int32_t sat_m[KP];               // M_p: most devices of profile p one GPU can hold (table rows / memory)
+    int32_t sat_m[KP];               // MIG: M_p, most devices of profile p one GPU can hold (allowed-geometry rows); MPS: from gflags[1]
+    int slice_mode;                  // this rank holds only its own slice of the node list: no sequential sweep is possible here
     // work area (zeroed before each run)
     long long* tot;                  // [KP] sum over nodes of (alloc - requested) per slice column
     int32_t* lack;                   // [KP] SliceTracker.lackingSlices
@@ -82,6 +83,7 @@ struct DevProblem {
     uint8_t* cand_flag;              // [N] HasFreeCapacity
     int32_t* maxfree;                // [KP] max free count of a profile on any GPU at t0 (work area)
     int32_t* gflags;                 // [4]  [0] some node's Allocatable/Requested disagree with its GPUs' used/free
+                                     //      [1] largest GPU memory GB of any GPU (MPS: bounds the devices one GPU can hold)
     unsigned* placed;                // [(n_keys+31)/32] tracker keys placed by the node-parallel pass
     unsigned long long* acc;         // [4]  placements, geometry evals, visited, candidate nodes of the node-parallel pass
     int32_t* lack_dec;               // [KP] lacking quantities removed by the node-parallel pass (single-rank runs)

@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
     // this thread's profile in phase 2 never changes: (node-in-tile, profile) pairs are laid out 16 profiles per node
     const int my_p = tid & (KP - 1);
     long long acc = 0;
-    int maxfree = 0;
+    int maxfree = 0, maxmem = 0;
     bool inconsistent = false;
     const int n_tiles = (pb.N + PRE_NODES - 1) / PRE_NODES;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -77,7 +77,9 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
                     int tot = 0;
 #pragma unroll
                     for (int p = 0; p < KP; ++p) tot += pb.pmem[p] * (int)byte_of(cnt, p);
-                    has_free = fm != 0 || (pb.gpu_mem[x] - tot >= 1);
+                    const int gm_ = pb.gpu_mem[x];
+                    maxmem = max(maxmem, gm_);
+                    has_free = fm != 0 || (gm_ - tot >= 1);
                 }
             }
             s_used[r] = used; s_free[r] = fre; s_hasfree[r] = has_free;
@@ -110,6 +112,8 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
         __syncthreads();
     }
     if (__any_sync(0xffffffffu, inconsistent) && lane == 0) atomicOr(&pb.gflags[0], 1);
+    maxmem = __reduce_max_sync(0xffffffffu, maxmem);
+    if (maxmem > 0 && lane == 0) atomicMax(&pb.gflags[1], maxmem);
     // lanes p and p+16 of a warp hold the same profile
     acc += __shfl_xor_sync(0xffffffffu, acc, 16);
     maxfree = max(maxfree, __shfl_xor_sync(0xffffffffu, maxfree, 16));
@@ -148,6 +152,42 @@ __global__ void __launch_bounds__(256) k_tracker_init(DevProblem pb) {
     }
     __syncthreads();
     if (threadIdx.x < KP && s_lack[threadIdx.x] != 0) atomicAdd(&pb.lack[threadIdx.x], s_lack[threadIdx.x]);
+}
+
+// Slice mode (every rank holds its own slice of the node list): what k_prepass reduced over the slice is exchanged as one
+// 256-byte block per rank -- [tot int64 x16 | maxfree int32 x16 | gflags int32 x4] -- and folded back: sums, maxima, OR.
+__global__ void k_slice_pack_totals(DevProblem pb, unsigned char* block) {
+    const int t = threadIdx.x;
+    if (t < KP) reinterpret_cast<long long*>(block)[t] = pb.tot[t];
+    if (t < KP) reinterpret_cast<int32_t*>(block + 128)[t] = pb.maxfree[t];
+    if (t < 4) reinterpret_cast<int32_t*>(block + 192)[t] = pb.gflags[t];
+}
+
+__global__ void k_slice_combine_totals(DevProblem pb, const unsigned char* gathered, int world) {
+    const int t = threadIdx.x;
+    if (t < KP) {
+        long long s = 0; int m = 0;
+        for (int r = 0; r < world; ++r) {
+            s += reinterpret_cast<const long long*>(gathered + (size_t)r * 256)[t];
+            m = max(m, reinterpret_cast<const int32_t*>(gathered + (size_t)r * 256 + 128)[t]);
+        }
+        pb.tot[t] = s; pb.maxfree[t] = m;
+    }
+    if (t < 4) {
+        int f = 0;
+        for (int r = 0; r < world; ++r) {
+            const int v = reinterpret_cast<const int32_t*>(gathered + (size_t)r * 256 + 192)[t];
+            f = t == 0 ? (f | v) : max(f, v);
+        }
+        pb.gflags[t] = f;
+    }
+}
+
+void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st) {
+    k_slice_pack_totals<<<1, 32, 0, st>>>(pb, static_cast<unsigned char*>(block));
+}
+void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, cudaStream_t st) {
+    k_slice_combine_totals<<<1, 32, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world);
 }
 
 void launch_prepass(const DevProblem& pb, cudaStream_t st) {

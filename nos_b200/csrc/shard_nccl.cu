@@ -15,6 +15,8 @@ extern "C" {
 int64_t nosplan_shard_exchange_bytes(nosplan_t* h);
 int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_exchange, int64_t exchange_bytes);
 int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world);
+int nosplan_slice_begin(nosplan_t* h, void* d_totals);
+int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes);
 }
 
 namespace {
@@ -149,6 +151,38 @@ extern "C" int nosplan_run_sharded(nosplan_t* h, int32_t gather_plan) {
     c->gathered = do_gather;
     rc = nosplan_shard_end(h, c->d + c->o_gather_x, W);
     if (rc == NOSPLAN_OK) h->launches += 1;                      // the grouped NCCL kernel
+    return rc;
+}
+
+// Slice mode with the library's own collectives: two small all-gathers per Plan() -- the 256-byte totals block between
+// k_prepass and k_tracker_init, and the exchange block after the node-parallel pass.  The plan rows stay on their rank.
+extern "C" int nosplan_run_sliced(nosplan_t* h) {
+    if (!h) return NOSPLAN_E_INVALID;
+    nosplan_shard_ctx* c = h->sctx;
+    if (!c) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sliced before nosplan_shard_init");
+    if (!h->uploaded) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sliced before nosplan_upload");
+    SCU(h, cudaSetDevice(h->device));
+    const int W = c->world;
+    const size_t xb = (size_t)nosplan_shard_exchange_bytes(h), tb = NOSPLAN_SLICE_TOTALS_BYTES;
+    size_t o = 0;
+    auto put = [&](size_t bytes) { size_t at = o; o = al(o + bytes); return at; };
+    const size_t o_t = put(tb), o_t_all = put(tb * W);
+    c->xb = xb; c->chunk_rows = 0; c->gathered = false;
+    c->o_local_x = put(xb); c->o_gather_x = put(xb * W);
+    if (o > c->cap) {
+        if (c->d) SCU(h, cudaFree(c->d));
+        c->d = nullptr; c->cap = 0;
+        SCU(h, cudaMalloc(&c->d, o + o / 4 + (1 << 20)));
+        c->cap = o + o / 4 + (1 << 20);
+    }
+    int rc = nosplan_slice_begin(h, c->d + o_t);
+    if (rc != NOSPLAN_OK) return rc;
+    SNC(h, nccl().AllGather(c->d + o_t, c->d + o_t_all, tb, ncclUint8, c->comm, h->stream));
+    rc = nosplan_slice_mid(h, c->rank, W, c->d + o_t_all, c->d + c->o_local_x, (int64_t)xb);
+    if (rc != NOSPLAN_OK) return rc;
+    SNC(h, nccl().AllGather(c->d + c->o_local_x, c->d + c->o_gather_x, xb, ncclUint8, c->comm, h->stream));
+    rc = nosplan_shard_end(h, c->d + c->o_gather_x, W);
+    if (rc == NOSPLAN_OK) h->launches += 2;                      // the two NCCL kernels
     return rc;
 }
 

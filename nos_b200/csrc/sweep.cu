@@ -651,8 +651,10 @@ __device__ __forceinline__ void load_tables(const DevProblem& pb, Tables& tb, in
 __device__ __forceinline__ bool fast_applicable(const DevProblem& pb, int lack_p, int lane) {
     bool ok = true;
     if (lane < KP && lack_p > 0) {
-        const long long m = max(pb.sat_m[lane], pb.maxfree[lane]);
-        ok = pb.sat_m[lane] >= 0 && (long long)lack_p > (long long)(pb.G + 2) * m;
+        int sat = pb.sat_m[lane];
+        if (pb.kind == NOSPLAN_KIND_MPS) sat = pb.pmem[lane] > 0 ? pb.gflags[1] / pb.pmem[lane] : -1;   // devices of this size a GPU can hold
+        const long long m = max(sat, pb.maxfree[lane]);
+        ok = sat >= 0 && (long long)lack_p > (long long)(pb.G + 2) * m;
     }
     const bool any_lack = __ballot_sync(FULL, lane < KP && lack_p > 0) != 0;
     return __all_sync(FULL, ok) && any_lack && pb.fast_eligible && pb.gflags[0] == 0;
@@ -784,6 +786,17 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
         __syncthreads();
     }
 
+    if (pb.slice_mode) {
+        // this rank holds only its slice of the node list: the sequential chain cannot run here.  Report it (path 0, no
+        // visits); the caller plans this problem unsharded (nosplan_download_sliced returns NOSPLAN_SLICED_NOT_APPLICABLE).
+        if (tid == 0) {
+            DevStats* st = pb.stats;
+            st->visited_nodes = 0; st->candidates = 0; st->geometry_evals = 0; st->placements = 0; st->candidate_nodes = 0;
+            st->lacking_at_start = lack_start; st->lacking_at_end = lack_start; st->path = 0;
+            st->pad = lack_start > 0;       // nothing lacking: the unchanged state IS the plan (planner.go:80-83)
+        }
+        return;
+    }
     // ---------------- sequential sweep.  prologue (whole CTA): tables, run cache, candidate compaction in name order
     load_tables(pb, tb, tid, blockDim.x);
     for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x) s_removed[w] = 0;

@@ -103,3 +103,63 @@ class ShardedPlanner:
         node-parallel pass stood (stats path == 1); after a sequential fallback use engine.download() instead."""
         n = self.N * self.G
         return self.count_all[:n].cpu().numpy(), self.mask_all[:n].cpu().numpy().copy().view(np.uint16).reshape(-1)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# slice mode: every rank holds ONLY its own slice of the node list
+# ---------------------------------------------------------------------------------------------------------------------
+_PER_NODE = ("node_gpu_count", "node_alloc", "node_requested", "node_allowed_pods", "node_num_pods")
+_PER_GPU = ("gpu_model", "gpu_index", "gpu_memory_gb", "gpu_used", "gpu_free", "gpu_used_mask", "gpu_free_mask")
+
+
+def slice_snapshot(snap, lo: int, hi: int, pad_to: int = 0):
+    """Nodes [lo, hi) of a packed snapshot as a snapshot of its own (same profiles, models and geometry tables), padded
+    with GPU-less, resource-less nodes up to `pad_to` nodes so that every rank of a sliced job holds the same count."""
+    import copy
+    out = copy.copy(snap)
+    G = snap.gpus_per_node
+    n = max(hi - lo, pad_to)
+
+    def take(a, a_lo, a_hi, rows):
+        a = np.asarray(a)
+        piece = a[a_lo:a_hi]
+        if len(piece) < rows:
+            piece = np.concatenate([piece, np.zeros((rows - len(piece),) + a.shape[1:], a.dtype)])
+        return np.ascontiguousarray(piece)
+
+    for f in _PER_NODE:
+        setattr(out, f, take(getattr(snap, f), lo, hi, n))
+    for f in _PER_GPU:
+        setattr(out, f, take(getattr(snap, f), lo * G, hi * G, n * G))
+    out.node_names = list(snap.node_names[lo:hi]) + [f"~pad-{k}" for k in range(n - (hi - lo))]
+    return out
+
+
+class SlicedPlanner:
+    """Drives nosplan_slice_begin / all-gather / nosplan_slice_mid / all-gather / nosplan_shard_end on one rank whose engine
+    was given only that rank's slice (slice_snapshot).  all_gather as in ShardedPlanner."""
+
+    def __init__(self, engine, rank: int, world: int, device, group=None, all_gather: Optional[Callable] = None):
+        import torch
+        self.torch = torch
+        self.engine, self.rank, self.world, self.device, self.group = engine, rank, world, device, group
+        self._all_gather = all_gather or ShardedPlanner._dist_all_gather.__get__(self)
+
+    def prepare(self):
+        """Call after engine.upload()."""
+        t = self.torch
+        self.nbytes = self.engine.shard_exchange_bytes()
+        self.tot_local = t.zeros(256, dtype=t.uint8, device=self.device)
+        self.tot_all = t.zeros(self.world * 256, dtype=t.uint8, device=self.device)
+        self.local = t.zeros(self.nbytes, dtype=t.uint8, device=self.device)
+        self.gathered = t.zeros(self.world * self.nbytes, dtype=t.uint8, device=self.device)
+
+    def run(self):
+        t = self.torch
+        stream = t.cuda.ExternalStream(self.engine.stream(), device=self.device)
+        with t.cuda.stream(stream):
+            self.engine.slice_begin(self.tot_local.data_ptr())
+            self._all_gather(self.tot_all, self.tot_local)
+            self.engine.slice_mid(self.rank, self.world, self.tot_all.data_ptr(), self.local.data_ptr(), self.nbytes)
+            self._all_gather(self.gathered, self.local)
+            self.engine.shard_end(self.gathered.data_ptr(), self.world)

@@ -45,9 +45,32 @@ def main():
         eng.run_sharded(True)
         cnt, msk, st2 = eng.download_sharded()
         same_b = np.array_equal(cnt, ocnt) and np.array_equal(msk, omsk) and all(st2[k] == ost[k] for k in KEYS)
-        ok &= same_a and same_b
+        # (c) slice mode: this rank uploads only its own slice; torch collectives, then the library's own
+        chunk = (snap.n_nodes + world - 1) // world
+        lo, hi = sharded.shard_range(snap.n_nodes, rank, world)
+        sl = sharded.slice_snapshot(snap, lo, hi, pad_to=chunk)
+        G = snap.gpus_per_node
+        same_c = True
+        for driver in ("torch", "library"):
+            eng.upload(sl, pods, None, pk.FILTER_RESOURCES_FIT)
+            if driver == "torch":
+                sp = sharded.SlicedPlanner(eng, rank, world, dev)
+                sp.prepare()
+                sp.run()
+            else:
+                eng.run_sliced()
+            try:
+                cnt, msk, st3 = eng.download()
+                n = (hi - lo) * G
+                same_c &= st3["path"] == st["path"] and all(st3[k] == ost[k] for k in KEYS)
+                same_c &= np.array_equal(cnt[:n], ocnt[lo * G:hi * G]) and np.array_equal(msk[:n], omsk[lo * G:hi * G])
+                if st3["path"] == 0:                      # nothing lacking: the unchanged state is the plan
+                    same_c &= ost["lacking_at_start"] == 0
+            except capi.SlicedNotApplicable:
+                same_c &= st["path"] == 0 and ost["lacking_at_start"] > 0   # the sequential sweep is needed: same verdict on every rank
+        ok &= same_a and same_b and same_c
         print(f"rank {rank}/{world} {shape} {regime}: path={st['path']}/{st2['path']} torch-collectives={'OK' if same_a else 'MISMATCH'} "
-              f"library-collectives={'OK' if same_b else 'MISMATCH'}", flush=True)
+              f"library-collectives={'OK' if same_b else 'MISMATCH'} sliced={'OK' if same_c else 'MISMATCH'}", flush=True)
     eng.close()
     dist.barrier()
     dist.destroy_process_group()

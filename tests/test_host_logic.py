@@ -43,3 +43,21 @@ def test_pod_order_full_size_fast_path():
     got = capi.host_pod_order(s, p)
     assert np.array_equal(got, ol.sort_pods(s, p))
     assert sorted(got.tolist()) == list(range(20000))
+
+
+def test_slice_snapshot_partitions_and_pads():
+    from nos_b200 import sharded, synth
+    snap, _ = synth.mig_cluster(23, 4, 10, seed=3)
+    G = snap.gpus_per_node
+    chunk = (23 + 3) // 4
+    seen = 0
+    for r in range(4):
+        lo, hi = sharded.shard_range(23, r, 4)
+        sl = sharded.slice_snapshot(snap, lo, hi, pad_to=chunk)
+        assert sl.n_nodes == chunk and sl.gpu_used.shape == (chunk * G, 16) and sl.node_alloc.shape == (chunk, snap.n_res)
+        assert np.array_equal(sl.gpu_free[:(hi - lo) * G], snap.gpu_free[lo * G:hi * G])
+        assert np.array_equal(sl.node_requested[:hi - lo], snap.node_requested[lo:hi])
+        assert not sl.node_gpu_count[hi - lo:].any() and not sl.node_alloc[hi - lo:].any()      # padding: GPU-less, resource-less
+        assert sl.profiles == snap.profiles and sl.geom_counts is snap.geom_counts
+        seen += hi - lo
+    assert seen == 23

@@ -55,3 +55,82 @@ def test_sharded_equals_single(world):
         acc, placed = sharded.combine_blocks(blocks, pods.n_pods)
         if stats[0]["path"] == 1:
             assert int(acc[0]) == ost["placements"] and int(acc[2]) == ost["visited_nodes"]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# slice mode: every "rank" uploads only its own slice of the node list
+def run_sliced_emulated(snap, pods, fm, world):
+    import torch
+    dev = torch.device("cuda", 0)
+    chunk = (snap.n_nodes + world - 1) // world
+    engines, planners, slices = [], [], []
+    for r in range(world):
+        lo, hi = sharded.shard_range(snap.n_nodes, r, world)
+        sl = sharded.slice_snapshot(snap, lo, hi, pad_to=chunk)
+        e = capi.Engine(0)
+        e.upload(sl, pods, None, fm)
+        p = sharded.SlicedPlanner(e, r, world, dev, all_gather=lambda dst, src: None)
+        p.prepare()
+        engines.append(e); planners.append(p); slices.append((lo, hi))
+    for e, p in zip(engines, planners):
+        e.slice_begin(p.tot_local.data_ptr())
+    torch.cuda.synchronize()
+    tot_all = torch.cat([p.tot_local for p in planners])                # first all-gather: totals blocks
+    for r, (e, p) in enumerate(zip(engines, planners)):
+        e.slice_mid(r, world, tot_all.data_ptr(), p.local.data_ptr(), p.nbytes)
+    torch.cuda.synchronize()
+    gathered = torch.cat([p.local for p in planners])                   # second all-gather: exchange blocks
+    out = []
+    for r, e in enumerate(engines):
+        e.shard_end(gathered.data_ptr(), world)
+        try:
+            cnt, msk, st = e.download()
+            out.append((cnt, msk, st))
+        except capi.SlicedNotApplicable:
+            out.append(None)
+    for e in engines:
+        e.close()
+    return out, slices
+
+
+def check_sliced(snap, pods, fm, world):
+    """Slice mode against the oracle: same counters and this rank's rows where the node-parallel pass stands (or nothing is
+    lacking), the NOT_APPLICABLE verdict on every rank where the single-GPU engine needs its sequential sweep."""
+    ocnt, omsk, ost, _ = ol.plan(snap, pods, None, fm, ol.INCREMENTAL)
+    e = capi.Engine(0)
+    single_path = e.plan(snap, pods, None, fm)[2]["path"]
+    e.close()
+    out, slices = run_sliced_emulated(snap, pods, fm, world)
+    G = snap.gpus_per_node
+    if single_path == 0 and ost["lacking_at_start"] > 0:
+        assert all(o is None for o in out)
+        return "needs-full"
+    for (cnt, msk, st), (lo, hi) in zip(out, slices):
+        assert st["path"] == single_path
+        for k in ("candidates", "visited_nodes", "placements", "geometry_evals", "lacking_at_start", "lacking_at_end"):
+            assert st[k] == ost[k], (world, k, st[k], ost[k])
+        n = (hi - lo) * G
+        assert np.array_equal(cnt[:n], ocnt[lo * G:hi * G]) and np.array_equal(msk[:n], omsk[lo * G:hi * G])
+    return "parallel" if single_path == 1 else "nothing-lacking"
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+@pytest.mark.parametrize("kind", ["mig", "mps"])
+def test_sliced_equals_single(world, kind):
+    gen = synth.mig_cluster if kind == "mig" else synth.mps_cluster
+    seen = set()
+    for shape in ((203, 8, 1000), (64, 4, 300), (37, 8, 500)):
+        snap, pods = gen(*shape, seed=91 + world, regime="saturating")
+        seen.add(check_sliced(snap, pods, pk.FILTER_RESOURCES_FIT, world))
+    assert "parallel" in seen
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sliced_reports_when_the_sequential_sweep_is_needed(world):
+    seen = set()
+    for seed in range(5, 11):           # satisfiable demand: unsaturated lacking vector, or nothing lacking at all (planner.go:80-83)
+        snap, pods = synth.mig_cluster(150, 8, 700, seed=seed, regime="satisfiable")
+        seen.add(check_sliced(snap, pods, pk.FILTER_RESOURCES_FIT, world))
+    snap, pods = synth.mig_cluster(60, 8, 2, seed=3, regime="saturating")      # two pods: lacking but far from saturated
+    seen.add(check_sliced(snap, pods, pk.FILTER_NONE, world))
+    assert "needs-full" in seen
