@@ -77,6 +77,7 @@ class ClockSampler:
         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
+        """index: GPU index, or a comma-separated list (one nvidia-smi process polls them all)."""
         self.index, self.proc, self.path = index, None, f"/tmp/nosplan_clocks_{os.getpid()}.csv"
 
     def start(self):
@@ -214,9 +215,11 @@ def run_ours(args):
 
     for _ in range(max(3, args.warmup)):
         one_step(False)
-    sampler = ClockSampler(local)
+    # one poller for the whole job (rank 0, every GPU of the job): NVML queries from 8 processes at once perturb the launches
+    sampler = ClockSampler(",".join(str(i) for i in range(world))) if rank == 0 else None
     sync_all()
-    sampler.start()
+    if sampler:
+        sampler.start()
     step_ms, sweep_ms, par_ms, st = [], [], [], None
     eng.set_kernel_events(False)             # the timed steps run without the library's per-kernel events ...
     for _ in range(args.steps):
@@ -249,7 +252,7 @@ def run_ours(args):
         est = e2e_once()
         e2e_s.append(time.perf_counter() - t0)
     sync_all()
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler else None
 
     total_ms = float(sum(step_ms))
     e2e_total = float(sum(e2e_s))
