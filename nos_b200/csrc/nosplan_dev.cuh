@@ -95,6 +95,21 @@ struct DevProblem {
     DevStats* stats;
 };
 
+// Programmatic dependent launch: a kernel launched with this helper may become resident while its predecessor on the stream
+// is still running; it must call cudaGridDependencySynchronize() before touching anything the predecessor writes.
+// Predecessors call cudaTriggerProgrammaticLaunchCompletion() early to allow it.  Saves the launch latency between the
+// short kernels of one Plan().
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 __device__ __forceinline__ unsigned byte_of(const uint4& v, int p) {
     unsigned w = (p < 8) ? ((p < 4) ? v.x : v.y) : ((p < 12) ? v.z : v.w);
     return (w >> ((p & 3) * 8)) & 0xffu;

@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
     __shared__ long long s_acc[8][KP];
     __shared__ int s_maxfree[8][KP];
 
+    cudaTriggerProgrammaticLaunchCompletion();           // k_tracker_init may become resident; it waits for this grid itself
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool mig = pb.kind == NOSPLAN_KIND_MIG;
     const int G = pb.G, K = pb.K;
@@ -131,9 +132,11 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
 
 __global__ void __launch_bounds__(256) k_tracker_init(DevProblem pb) {
     __shared__ int s_lack[KP];
+    cudaTriggerProgrammaticLaunchCompletion();
     if (threadIdx.x < KP) s_lack[threadIdx.x] = 0;
     __syncthreads();
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    cudaGridDependencySynchronize();                     // the totals of k_prepass (and the work-area reset before it)
     if (s < pb.P) {
         const int key = pb.pod_key[s];
         for (int e = pb.pod_sptr[s]; e < pb.pod_sptr[s + 1]; ++e) {
@@ -199,7 +202,7 @@ void launch_prepass(const DevProblem& pb, cudaStream_t st) {
 }
 
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st) {
-    if (pb.P > 0) k_tracker_init<<<(pb.P + 255) / 256, 256, 0, st>>>(pb);
+    if (pb.P > 0) launch_pdl(k_tracker_init, dim3((pb.P + 255) / 256), dim3(256), 0, st, pb);
 }
 
 }  // namespace nsp

@@ -674,8 +674,8 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     __shared__ int s_choff[RUN_CACHE];
     __shared__ unsigned long long s_masks[KP + 1];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
-    if (!fast_applicable(pb, lack0, lane)) return;
+    cudaTriggerProgrammaticLaunchCompletion();
+    // prologue on uploaded data only; the results of k_prepass / k_tracker_init are read after the dependency wait
     load_tables(pb, tb, tid, blockDim.x);
     PodCache pc;
     pc.cpu = nullptr; pc.mem = nullptr; pc.eph = nullptr; pc.key = nullptr; pc.flag = nullptr;
@@ -683,6 +683,9 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
     __syncthreads();
     build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
+    cudaGridDependencySynchronize();
+    const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
+    if (!fast_applicable(pb, lack0, lane)) return;
 
     WarpScratch& ws = ws_all[warp];
     int lack = lack0 > 0 ? SATURATED : 0;
@@ -739,6 +742,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     unsigned* s_removed = reinterpret_cast<unsigned*>(pc.flag + RUN_CACHE);      // [(n_keys+31)/32]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    cudaGridDependencySynchronize();
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
     const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0));
 
@@ -892,8 +896,7 @@ cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st) {
     if (!pb.fast_eligible || pb.N == 0 || pb.P == 0 || pb.node_hi <= pb.node_lo) return cudaSuccess;
     int blocks = (pb.node_hi - pb.node_lo + 3) / 4;
     if (blocks > g_par_blocks) blocks = g_par_blocks;
-    k_plan_parallel<<<blocks, 128, 0, st>>>(pb);
-    return cudaGetLastError();
+    return launch_pdl(k_plan_parallel, dim3(blocks), dim3(128), 0, st, pb);
 }
 
 // Node-sharded Plan(): every rank ran the node-parallel pass on its own node range and all-gathered its
@@ -922,8 +925,7 @@ void launch_shard_combine(const DevProblem& pb, const void* gathered, int world,
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st) {
     const size_t dyn = sweep_dyn_smem(pb);
     if (dyn > SWEEP_DYN_MAX) return cudaErrorInvalidValue;
-    k_plan_sweep<<<1, 256, dyn, st>>>(pb, cand_idx);
-    return cudaGetLastError();
+    return launch_pdl(k_plan_sweep, dim3(1), dim3(256), dyn, st, pb, cand_idx);
 }
 
 }  // namespace nsp
