@@ -309,6 +309,43 @@ typedef struct nosplan_victim_query {
 int nosplan_quota_victims(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_victim_query* query,
                           uint8_t* victim /* [n_pods] out: 1 = potential victim */, nosplan_stats* stats);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Snapshot packer: the status annotations of N nodes -> the per-GPU arrays of nosplan_snapshot.
+ * Replaces: gpu.ParseNodeAnnotations (pkg/gpu/annotation.go:29-104), StatusAnnotationList.GroupByGpuIndex (:186-196) and
+ * the GPU construction of mig.NewNode / slicing.NewNode (pkg/gpu/mig/node.go:65-100, pkg/gpu/slicing/node.go:48-105).
+ * The caller flattens the node.Annotations maps into byte buffers (every annotation of every node, related or not; the
+ * engine applies the reference's own acceptance rules: prefix, strings.Split(key, "-") part count, strconv.Atoi of value
+ * and GPU index, case-insensitive status word) and supplies the profile dictionary in the id order of the snapshot it is
+ * building.  GPUs come out in ascending annotated index (the canonical resolution of the reference's map iteration),
+ * followed by the GPUs the nvidia.com/gpu.count label adds (index = position). */
+typedef struct nosplan_annotations {
+    int32_t n_nodes;                   /* N */
+    const int32_t* node_ptr;           /* [N+1] CSR over the annotations of each node */
+    const int32_t* key_off;            /* [A+1] byte offsets into key_bytes (A = node_ptr[N]) */
+    const char* key_bytes;
+    const int32_t* val_off;            /* [A+1] */
+    const char* val_bytes;
+    const int32_t* gpu_count;          /* [N] gpu.GetCount: label nvidia.com/gpu.count (pkg/gpu/util.go:43-56) */
+    int32_t n_profiles;                /* K */
+    const int32_t* profile_off;        /* [K+1] */
+    const char* profile_bytes;         /* profile names, id order */
+    int32_t gpus_per_node;             /* G: row stride of the outputs */
+} nosplan_annotations;
+
+typedef struct nosplan_parsed_gpus {   /* every pointer may be NULL = not wanted; layouts as in nosplan_snapshot */
+    uint8_t* gpu_used;                 /* [N*G][16] */
+    uint8_t* gpu_free;                 /* [N*G][16] */
+    uint16_t* gpu_used_mask;           /* [N*G] */
+    uint16_t* gpu_free_mask;           /* [N*G] */
+    int32_t* gpu_index;                /* [N*G] */
+    int32_t* node_gpu_count;           /* [N] */
+    int32_t* errors;                   /* [4] annotations naming a profile outside the dictionary; device counts outside [0,255];
+                                          nodes with more than G GPUs; GPU indices beyond 32 bits.  Any non-zero entry also
+                                          fails the call (NOSPLAN_E_INVALID / NOSPLAN_E_LIMIT). */
+} nosplan_parsed_gpus;
+
+int nosplan_parse_annotations(nosplan_t* h, const nosplan_annotations* in, nosplan_parsed_gpus* out, nosplan_stats* stats);
+
 #ifdef __cplusplus
 }
 #endif

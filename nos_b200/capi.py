@@ -24,7 +24,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
-    "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced",
+    "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -184,6 +184,41 @@ def pinned_partitioning(s: PackedSnapshot):
 _KEEP_PINNED = []
 
 
+class CAnnotations(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("node_ptr", C.c_void_p), ("key_off", C.c_void_p), ("key_bytes", C.c_void_p),
+                ("val_off", C.c_void_p), ("val_bytes", C.c_void_p), ("gpu_count", C.c_void_p), ("n_profiles", C.c_int32),
+                ("profile_off", C.c_void_p), ("profile_bytes", C.c_void_p), ("gpus_per_node", C.c_int32)]
+
+
+class CParsedGpus(C.Structure):
+    _fields_ = [("gpu_used", C.c_void_p), ("gpu_free", C.c_void_p), ("gpu_used_mask", C.c_void_p), ("gpu_free_mask", C.c_void_p),
+                ("gpu_index", C.c_void_p), ("node_gpu_count", C.c_void_p), ("errors", C.c_void_p)]
+
+
+def flatten_annotations(v1_nodes, profiles):
+    """[{annotations: {k: v}, labels: {...}}] -> the flat buffers of nosplan_annotations (numpy arrays kept by the caller).
+    gpu_count comes from the nvidia.com/gpu.count label (0 when absent or not an integer: NewNode would have failed)."""
+    import re
+    keys, vals, ptr, cnt = [], [], [0], []
+    for n in v1_nodes:
+        for k, v in n.get("annotations", {}).items():
+            keys.append(k.encode()); vals.append(str(v).encode())
+        ptr.append(len(keys))
+        c = n.get("labels", {}).get("nvidia.com/gpu.count", "0")
+        cnt.append(int(c) if re.fullmatch(r"[+-]?\d+", str(c)) else 0)
+
+    def pack(strs):
+        off = np.zeros(len(strs) + 1, np.int32)
+        if strs:
+            off[1:] = np.cumsum([len(x) for x in strs])
+        return off, np.frombuffer(b"".join(strs) or b"\0", np.uint8).copy()
+
+    ko, kb = pack(keys); vo, vb = pack(vals); po, pb = pack([p.encode() for p in profiles])
+    return {"node_ptr": np.array(ptr, np.int32), "key_off": ko, "key_bytes": kb, "val_off": vo, "val_bytes": vb,
+            "gpu_count": np.array(cnt, np.int32).reshape(len(v1_nodes)), "profile_off": po, "profile_bytes": pb,
+            "n_nodes": len(v1_nodes), "n_profiles": len(profiles)}
+
+
 class NosplanError(RuntimeError):
     pass
 
@@ -243,6 +278,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_slice_mid.restype = C.c_int
     lib.nosplan_run_sliced.argtypes = [C.c_void_p]
     lib.nosplan_run_sliced.restype = C.c_int
+    lib.nosplan_parse_annotations.argtypes = [C.c_void_p, C.POINTER(CAnnotations), C.POINTER(CParsedGpus), C.POINTER(CStats)]
+    lib.nosplan_parse_annotations.restype = C.c_int
     from . import victim_packing as vp
     lib.nosplan_quota_victims.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(vp.CVictimQuery), C.c_void_p, C.POINTER(CStats)]
     lib.nosplan_quota_victims.restype = C.c_int
@@ -326,6 +363,27 @@ class Engine:
             raise SlicedNotApplicable("the node-parallel pass does not apply: plan this problem unsharded")
         self._check(rc, "nosplan_download")
         return cnt, msk, st.as_dict()
+
+    def parse_annotations(self, flat: dict, gpus_per_node: int):
+        """nosplan_parse_annotations on the buffers of flatten_annotations -> (dict of per-GPU arrays, stats dict)."""
+        N, G = flat["n_nodes"], gpus_per_node
+        n = max(1, N * G)
+        out = {"gpu_used": np.zeros((n, 16), np.uint8), "gpu_free": np.zeros((n, 16), np.uint8), "gpu_used_mask": np.zeros(n, np.uint16),
+               "gpu_free_mask": np.zeros(n, np.uint16), "gpu_index": np.zeros(n, np.int32), "node_gpu_count": np.zeros(max(1, N), np.int32),
+               "errors": np.zeros(4, np.int32)}
+        ptr = lambda a: a.ctypes.data
+        ca = CAnnotations(N, ptr(flat["node_ptr"]), ptr(flat["key_off"]), ptr(flat["key_bytes"]), ptr(flat["val_off"]), ptr(flat["val_bytes"]),
+                          ptr(flat["gpu_count"]) if N else None, flat["n_profiles"], ptr(flat["profile_off"]), ptr(flat["profile_bytes"]), G)
+        co = CParsedGpus(*[ptr(out[k]) for k in ("gpu_used", "gpu_free", "gpu_used_mask", "gpu_free_mask", "gpu_index", "node_gpu_count", "errors")])
+        st = CStats()
+        rc = self.lib.nosplan_parse_annotations(self.h, C.byref(ca), C.byref(co), C.byref(st))
+        out["node_gpu_count"] = out["node_gpu_count"][:N]
+        if rc != 0:
+            msg = self.lib.nosplan_last_error(self.h)
+            e = NosplanError(f"nosplan_parse_annotations failed ({rc}): {msg.decode() if msg else ''}")
+            e.errors = out["errors"].copy()
+            raise e
+        return out, st.as_dict()
 
     def slice_begin(self, d_totals: int):
         self._check(self.lib.nosplan_slice_begin(self.h, d_totals), "nosplan_slice_begin")

@@ -40,6 +40,10 @@ extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_q
                                           const nosplan_quotas* qs, const nosplan_victim_query* vq, uint8_t* victim,
                                           float* ms_k, int* launches);
 
+extern "C" int nosplan_parse_annotations_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                              const nosplan_annotations* in, nosplan_parsed_gpus* out, float* ms_h2d, float* ms_k,
+                                              float* ms_d2h, long long* h2d_bytes, long long* d2h_bytes);
+
 #include "handle.cuh"
 
 extern "C" void nosplan_shard_ctx_free(nosplan_shard_ctx* c);
@@ -826,6 +830,19 @@ int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const no
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
+        stats->h2d_bytes = hb; stats->d2h_bytes = db;
+    }
+    return rc;
+}
+
+int nosplan_parse_annotations(nosplan_t* h, const nosplan_annotations* in, nosplan_parsed_gpus* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    float a = 0, b = 0, c = 0; long long hb = 0, db = 0;
+    const int rc = nosplan_parse_annotations_impl(h->device, h->stream, h->qctx, &h->err, in, out, &a, &b, &c, &hb, &db);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = 2;
         stats->h2d_bytes = hb; stats->d2h_bytes = db;
     }
     return rc;

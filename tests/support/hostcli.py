@@ -12,9 +12,9 @@ def _rl(d):
     return ",".join(f"{k}={v}" for k, v in d.items()) or "-"
 
 
-def logical_to_v1(kind_name, nodes):
+def logical_to_v1(kind_name, nodes, strict=True):
     """Logical node (gpus with used/free maps) -> v1.Node labels + status annotations; None when the node cannot be
-    expressed that way (GPUs of different models, or GPU indices that NewNode would renumber)."""
+    expressed that way (GPUs of different models, or -- strict only -- GPU indices that NewNode would renumber)."""
     out = []
     for n in nodes:
         models = {g["model"] for g in n["gpus"]}
@@ -27,7 +27,7 @@ def logical_to_v1(kind_name, nodes):
             labels[pk.LABEL_MEMORY] = str(mem * 1000)
         ann = {}
         annotated = [bool(g["used"] or g["free"]) for g in n["gpus"]]
-        if any(annotated[i] and not all(annotated[:i]) for i in range(len(annotated))):
+        if strict and any(annotated[i] and not all(annotated[:i]) for i in range(len(annotated))):
             return None                      # un-annotated GPUs are appended after the annotated ones
         for g in n["gpus"]:
             for st in ("used", "free"):
