@@ -285,7 +285,7 @@ def run_ours(args):
                    "regime": "saturating", "filter": "resources_fit",
                    "parallelism": "single GPU" if world == 1 else f"node-sliced x{world}: each GPU holds {n_full} nodes; two NCCL all-gathers "
                                   f"per Plan() (256 B of cluster totals, then {eng.shard_exchange_bytes()} B of counters + placed-key bitmap per rank); "
-                                  f"plan rows stay on their rank",
+                                  f"plan rows stay on their rank; transport: {eng.shard_transport()}",
                    "l2": "flushed between iterations (256 MiB device write)", "candidates_per_plan": cands,
                    "visited_nodes": int(st["visited_nodes"]), "placements": int(st["placements"])},
         "plan_p50_ms": float(np.median(step_ms)), "plan_p95_ms": float(np.percentile(step_ms, 95)),

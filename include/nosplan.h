@@ -201,6 +201,11 @@ int nosplan_download_sharded(nosplan_t* h, nosplan_partitioning* out, nosplan_st
 int nosplan_slice_begin(nosplan_t* h, void* d_totals);
 int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes);
 int nosplan_run_sliced(nosplan_t* h);
+/* 1: nosplan_run_sliced moves its two blocks over peer memory -- every rank stores its block straight into a mailbox in each
+ * peer's HBM (CUDA IPC mapping, NVLink) and raises a flag there; the consuming kernel waits on the flags of its own mailbox,
+ * so no collective is launched on the path.  0: NCCL all-gathers (no peer access between the GPUs, more than 8 ranks,
+ * NOSPLAN_NO_PEER set, or an exchange block above 64 KiB).  Decided once, unanimously, in nosplan_shard_init. */
+int nosplan_shard_transport(nosplan_t* h);
 
 /* No counterpart in the reference.  The tracker initialisation of Plan() -- lacking[p] summed over the pods, and the
  * number of distinct pod keys that lack any slice -- for callers that may not allocate device memory: processes

@@ -24,7 +24,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
-    "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations",
+    "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -278,6 +278,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_slice_mid.restype = C.c_int
     lib.nosplan_run_sliced.argtypes = [C.c_void_p]
     lib.nosplan_run_sliced.restype = C.c_int
+    lib.nosplan_shard_transport.argtypes = [C.c_void_p]
+    lib.nosplan_shard_transport.restype = C.c_int
     lib.nosplan_parse_annotations.argtypes = [C.c_void_p, C.POINTER(CAnnotations), C.POINTER(CParsedGpus), C.POINTER(CStats)]
     lib.nosplan_parse_annotations.restype = C.c_int
     from . import victim_packing as vp
@@ -390,6 +392,9 @@ class Engine:
 
     def slice_mid(self, rank: int, world: int, d_totals_gathered: int, d_exchange: int, nbytes: int):
         self._check(self.lib.nosplan_slice_mid(self.h, rank, world, d_totals_gathered, d_exchange, nbytes), "nosplan_slice_mid")
+
+    def shard_transport(self) -> str:
+        return "peer-memory" if self.lib.nosplan_shard_transport(self.h) else "nccl"
 
     def run_sliced(self):
         self._check(self.lib.nosplan_run_sliced(self.h), "nosplan_run_sliced")

@@ -20,9 +20,11 @@ void launch_prepass(const DevProblem& pb, cudaStream_t st);
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
 cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st);
-void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, cudaStream_t st);
+void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, const PeerWait& wait, cudaStream_t st);
 void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st);
-void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, cudaStream_t st);
+void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, const PeerWait& wait, cudaStream_t st);
+void launch_push_totals(const DevProblem& pb, const PeerBox& box, unsigned epoch, cudaStream_t st);
+void launch_push_exchange(const void* src, size_t bytes, const PeerBox& box, unsigned epoch, cudaStream_t st);
 cudaError_t sweep_prepare_device();
 int sweep_max_keys();
 }  // namespace nsp
@@ -701,28 +703,33 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
 }
 
 // ---- slice mode: every rank uploaded ONLY its own slice of the name-ordered node list -------------------------------
-int nosplan_slice_begin(nosplan_t* h, void* d_totals) {
+}  // extern "C"
+
+// box != nullptr: the totals block is pushed into every rank's mailbox (peer memory) instead of being packed for a collective
+int nosplan_slice_begin_ex(nosplan* h, void* d_totals, const PeerBox* box, unsigned epoch) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_slice_begin before nosplan_upload");
-    if (!d_totals) return fail(h, NOSPLAN_E_INVALID, "null totals buffer");
+    if (!d_totals && !box) return fail(h, NOSPLAN_E_INVALID, "null totals buffer");
     CU(h, cudaSetDevice(h->device));
     h->pb.slice_mode = 1;
     int rc = run_pre(h, false);                             // cluster totals of the slice
     if (rc != NOSPLAN_OK) return rc;
-    launch_slice_pack_totals(h->pb, d_totals, h->stream);
+    if (box) launch_push_totals(h->pb, *box, epoch, h->stream);
+    else launch_slice_pack_totals(h->pb, d_totals, h->stream);
     CU(h, cudaGetLastError());
     h->launches = (h->pb.N > 0) + 1;
     return NOSPLAN_OK;
 }
 
-int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes) {
+int nosplan_slice_mid_ex(nosplan* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes,
+                         const PeerWait& wait) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->uploaded || !h->pb.slice_mode) return fail(h, NOSPLAN_E_INVALID, "nosplan_slice_mid before nosplan_slice_begin");
     if (world < 1 || rank < 0 || rank >= world) return fail(h, NOSPLAN_E_INVALID, "rank %d of %d", rank, world);
     const int64_t need = nosplan_shard_exchange_bytes(h);
     if (!d_totals_gathered || !d_exchange || exchange_bytes < need) return fail(h, NOSPLAN_E_INVALID, "exchange buffer smaller than %lld bytes", (long long)need);
     CU(h, cudaSetDevice(h->device));
-    launch_slice_combine_totals(h->pb, d_totals_gathered, world, h->stream);   // cluster-wide totals on every rank
+    launch_slice_combine_totals(h->pb, d_totals_gathered, world, wait, h->stream);   // cluster-wide totals on every rank
     CU(h, cudaMemsetAsync(d_exchange, 0, (size_t)need, h->stream));
     launch_tracker_init(h->pb, h->stream);
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[7], h->stream));
@@ -737,12 +744,12 @@ int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_t
     return NOSPLAN_OK;
 }
 
-int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world) {
+int nosplan_shard_end_ex(nosplan* h, const void* d_gathered, int32_t world, size_t stride, const PeerWait& wait) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_shard_end before nosplan_upload");
     if (!d_gathered || world < 1) return fail(h, NOSPLAN_E_INVALID, "null gathered buffer");
     CU(h, cudaSetDevice(h->device));
-    launch_shard_combine(h->pb, d_gathered, world, (size_t)nosplan_shard_exchange_bytes(h), h->stream);
+    launch_shard_combine(h->pb, d_gathered, world, stride, wait, h->stream);
     DevProblem verify = h->pb;
     verify.whole_snapshot = 0;                               // final lacking vector comes from the OR-ed bitmap
     CU(h, launch_sweep(verify, h->d_cand_idx, h->stream));
@@ -750,6 +757,18 @@ int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world) {
     h->launches += 2;
     h->ran = true;
     return NOSPLAN_OK;
+}
+
+extern "C" {
+
+int nosplan_slice_begin(nosplan_t* h, void* d_totals) { return nosplan_slice_begin_ex(h, d_totals, nullptr, 0); }
+
+int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes) {
+    return nosplan_slice_mid_ex(h, rank, world, d_totals_gathered, d_exchange, exchange_bytes, PeerWait{nullptr, 0, 0});
+}
+
+int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world) {
+    return nosplan_shard_end_ex(h, d_gathered, world, h && h->uploaded ? (size_t)nosplan_shard_exchange_bytes(h) : 0, PeerWait{nullptr, 0, 0});
 }
 
 int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count, void** d_gpu_mask) {
@@ -803,6 +822,7 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
     }
     if (h->pb.slice_mode) {
         DevStats ds; std::memcpy(&ds, O + o_stats, sizeof ds);
+        if (ds.pad == 2) return fail(h, NOSPLAN_E_CUDA, "peer exchange timed out: a rank of the sliced job did not deliver its block");
         if (ds.pad) return NOSPLAN_SLICED_NOT_APPLICABLE;
     }
     return NOSPLAN_OK;

@@ -84,6 +84,7 @@ struct DevProblem {
     int32_t* maxfree;                // [KP] max free count of a profile on any GPU at t0 (work area)
     int32_t* gflags;                 // [4]  [0] some node's Allocatable/Requested disagree with its GPUs' used/free
                                      //      [1] largest GPU memory GB of any GPU (MPS: bounds the devices one GPU can hold)
+                                     //      [3] a peer exchange timed out on this rank (never exchanged)
     unsigned* placed;                // [(n_keys+31)/32] tracker keys placed by the node-parallel pass
     unsigned long long* acc;         // [4]  placements, geometry evals, visited, candidate nodes of the node-parallel pass
     int32_t* lack_dec;               // [KP] lacking quantities removed by the node-parallel pass (single-rank runs)
@@ -108,6 +109,33 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+// ---- exchange over peer memory (slice mode on NVLink-connected GPUs, one process per GPU) ------------------------------
+// Every rank owns one mailbox in its own HBM, mapped into the other ranks through CUDA IPC.  A rank PUSHES its block into
+// every mailbox (remote stores over NVLink), fences, and raises its flag there; the consumer kernel on each rank spins on
+// the W flags of its own mailbox (local loads) and reads W blocks from local memory.  Flags carry the Plan() epoch and
+// slots alternate by epoch parity, so nothing is ever reset and a rank at most one step ahead never overwrites unread data.
+constexpr int PEER_MAX = 8;
+struct PeerBox { unsigned char* base[PEER_MAX]; int world, rank; unsigned long long xb_max; };
+struct PeerWait { const unsigned* flags; int world; unsigned epoch; };      // flags == nullptr: nothing to wait for
+__host__ __device__ inline size_t box_flags(int which, int parity) { return (size_t)(which - 1) * 64 + (size_t)parity * 32; }
+__host__ __device__ inline size_t box_tot(int parity, int r) { return 256 + ((size_t)parity * PEER_MAX + r) * 256; }
+__host__ __device__ inline size_t box_x(int parity, int r, size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + ((size_t)parity * PEER_MAX + r) * xb_max; }
+inline size_t box_bytes(size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + 2 * PEER_MAX * xb_max; }
+
+// all threads of the block call it; false = a peer did not show up within several seconds (the caller records the failure
+// instead of hanging the GPU)
+__device__ __forceinline__ bool peer_wait(const PeerWait& w) {
+    bool ok = true;
+    if (w.flags && (int)threadIdx.x < w.world) {
+        const volatile unsigned* f = w.flags + threadIdx.x;
+        unsigned spins = 0;
+        while ((int)(*f - w.epoch) < 0) { __nanosleep(500); if (++spins > (1u << 24)) { ok = false; break; } }
+    }
+    ok = __syncthreads_and(ok) != 0;
+    __threadfence_system();
+    return ok;
 }
 
 __device__ __forceinline__ unsigned byte_of(const uint4& v, int p) {

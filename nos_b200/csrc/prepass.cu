@@ -166,7 +166,8 @@ __global__ void k_slice_pack_totals(DevProblem pb, unsigned char* block) {
     if (t < 4) reinterpret_cast<int32_t*>(block + 192)[t] = pb.gflags[t];
 }
 
-__global__ void k_slice_combine_totals(DevProblem pb, const unsigned char* gathered, int world) {
+__global__ void k_slice_combine_totals(DevProblem pb, const unsigned char* gathered, int world, PeerWait wait) {
+    if (!peer_wait(wait) && threadIdx.x == 0) pb.gflags[3] = 1;
     const int t = threadIdx.x;
     if (t < KP) {
         long long s = 0; int m = 0;
@@ -176,7 +177,7 @@ __global__ void k_slice_combine_totals(DevProblem pb, const unsigned char* gathe
         }
         pb.tot[t] = s; pb.maxfree[t] = m;
     }
-    if (t < 4) {
+    if (t < 3) {
         int f = 0;
         for (int r = 0; r < world; ++r) {
             const int v = reinterpret_cast<const int32_t*>(gathered + (size_t)r * 256 + 192)[t];
@@ -186,11 +187,49 @@ __global__ void k_slice_combine_totals(DevProblem pb, const unsigned char* gathe
     }
 }
 
+// pack + push: the 256-byte totals block goes straight into every rank's mailbox, then this rank's flag is raised there
+__global__ void k_push_totals(DevProblem pb, PeerBox box, unsigned epoch) {
+    __shared__ __align__(16) unsigned char s_block[256];
+    const int t = threadIdx.x, par = epoch & 1;
+    if (t < 64) reinterpret_cast<int32_t*>(s_block)[t] = 0;
+    __syncthreads();
+    if (t < KP) reinterpret_cast<long long*>(s_block)[t] = pb.tot[t];
+    if (t < KP) reinterpret_cast<int32_t*>(s_block + 128)[t] = pb.maxfree[t];
+    if (t < 3) reinterpret_cast<int32_t*>(s_block + 192)[t] = pb.gflags[t];
+    __syncthreads();
+    for (int x = t; x < box.world * 16; x += blockDim.x) {
+        const int r = x >> 4, q = x & 15;
+        reinterpret_cast<uint4*>(box.base[r] + box_tot(par, box.rank))[q] = reinterpret_cast<const uint4*>(s_block)[q];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (t < box.world) *reinterpret_cast<volatile unsigned*>(box.base[t] + box_flags(1, par) + 4 * box.rank) = epoch;
+}
+
+// the exchange block of the node-parallel pass (counters + placed-key bitmap, 8-byte granular) into every mailbox
+__global__ void __launch_bounds__(256) k_push_exchange(const unsigned char* src, unsigned long long bytes, PeerBox box, unsigned epoch) {
+    const int t = threadIdx.x, par = epoch & 1;
+    const unsigned long long n8 = bytes >> 3;
+    for (int r = 0; r < box.world; ++r) {
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(box.base[r] + box_x(par, box.rank, box.xb_max));
+        for (unsigned long long i = t; i < n8; i += blockDim.x) dst[i] = reinterpret_cast<const unsigned long long*>(src)[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (t < box.world) *reinterpret_cast<volatile unsigned*>(box.base[t] + box_flags(2, par) + 4 * box.rank) = epoch;
+}
+
 void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st) {
     k_slice_pack_totals<<<1, 32, 0, st>>>(pb, static_cast<unsigned char*>(block));
 }
-void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, cudaStream_t st) {
-    k_slice_combine_totals<<<1, 32, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world);
+void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, const PeerWait& wait, cudaStream_t st) {
+    k_slice_combine_totals<<<1, 32, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world, wait);
+}
+void launch_push_totals(const DevProblem& pb, const PeerBox& box, unsigned epoch, cudaStream_t st) {
+    k_push_totals<<<1, 128, 0, st>>>(pb, box, epoch);
+}
+void launch_push_exchange(const void* src, size_t bytes, const PeerBox& box, unsigned epoch, cudaStream_t st) {
+    k_push_exchange<<<1, 256, 0, st>>>(static_cast<const unsigned char*>(src), (unsigned long long)bytes, box, epoch);
 }
 
 void launch_prepass(const DevProblem& pb, cudaStream_t st) {

@@ -7,7 +7,9 @@
 
 #include <algorithm>
 #include <cstring>
+#include <cstdlib>
 #include <mutex>
+#include <vector>
 
 #include "handle.cuh"
 
@@ -27,6 +29,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -45,6 +48,7 @@ NcclApi& nccl() {
         api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
         api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
         api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+        api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
         api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
         api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
         api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
@@ -57,9 +61,21 @@ inline size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
 
 }  // namespace
 
+namespace nsp {
+void launch_push_totals(const DevProblem& pb, const PeerBox& box, unsigned epoch, cudaStream_t st);
+void launch_push_exchange(const void* src, size_t bytes, const PeerBox& box, unsigned epoch, cudaStream_t st);
+}
+
+constexpr size_t PEER_XB_MAX = 64 << 10;                  // exchange blocks up to 64 KiB (524 032 tracker keys) go over peer memory
+
 struct nosplan_shard_ctx {
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
+    // peer-memory mailboxes (slice mode): this rank's box and the IPC mappings of the others; peer_ok == false: NCCL only
+    bool peer_ok = false;
+    nsp::PeerBox box{};
+    unsigned char* box_local = nullptr;
+    unsigned epoch = 0;
     unsigned char* d = nullptr; size_t cap = 0;
     size_t o_local_x = 0, o_gather_x = 0, o_local_cnt = 0, o_local_msk = 0, o_cnt_all = 0, o_msk_all = 0;
     size_t xb = 0, chunk_rows = 0;
@@ -73,6 +89,9 @@ struct nosplan_shard_ctx {
 
 extern "C" void nosplan_shard_ctx_free(nosplan_shard_ctx* c) {
     if (!c) return;
+    for (int r = 0; r < c->world && r < nsp::PEER_MAX; ++r)
+        if (r != c->rank && c->box.base[r]) cudaIpcCloseMemHandle(c->box.base[r]);
+    if (c->box_local) cudaFree(c->box_local);
     if (c->comm && nccl().ok) nccl().CommDestroy(c->comm);
     if (c->d) cudaFree(c->d);
     delete c;
@@ -100,8 +119,49 @@ extern "C" int nosplan_shard_init(nosplan_t* h, int32_t rank, int32_t world, con
     ncclResult_t r = nccl().CommInitRank(&c->comm, world, id, rank);
     if (r != ncclSuccess) { delete c; return nosplan_fail(h, NOSPLAN_E_CUDA, "ncclCommInitRank: %s", nccl().GetErrorString(r)); }
     h->sctx = c;
+    // Mailboxes over peer memory for the two small exchanges of slice mode.  Every step below is allowed to fail (no P2P,
+    // more than PEER_MAX ranks, NOSPLAN_NO_PEER set): the ranks then agree, through one all-reduce, to stay on NCCL.
+    int ok = world <= nsp::PEER_MAX && world > 1 && getenv("NOSPLAN_NO_PEER") == nullptr && nccl().AllReduce != nullptr;
+    const size_t bb = nsp::box_bytes(PEER_XB_MAX);
+    unsigned char* tmp = nullptr;                           // [world] IPC handles + one int
+    const size_t hb = sizeof(cudaIpcMemHandle_t);
+    SCU(h, cudaMalloc(&tmp, hb * (world + 1) + 256));
+    cudaIpcMemHandle_t mine; std::memset(&mine, 0, sizeof mine);
+    if (ok && (cudaMalloc(&c->box_local, bb) != cudaSuccess || cudaMemset(c->box_local, 0, bb) != cudaSuccess ||
+               cudaIpcGetMemHandle(&mine, c->box_local) != cudaSuccess)) ok = 0;
+    (void)cudaGetLastError();
+    std::vector<cudaIpcMemHandle_t> all(world);
+    int* d_ok = reinterpret_cast<int*>(tmp + hb * (world + 1));
+    bool comm_fine = cudaMemcpyAsync(tmp + hb * world, &mine, hb, cudaMemcpyHostToDevice, h->stream) == cudaSuccess &&
+                     nccl().AllGather(tmp + hb * world, tmp, hb, ncclUint8, c->comm, h->stream) == ncclSuccess &&
+                     cudaMemcpyAsync(all.data(), tmp, hb * world, cudaMemcpyDeviceToHost, h->stream) == cudaSuccess &&
+                     cudaStreamSynchronize(h->stream) == cudaSuccess;
+    if (!comm_fine) ok = 0;
+    for (int q = 0; q < world && q < nsp::PEER_MAX; ++q) c->box.base[q] = nullptr;
+    if (ok) {
+        for (int q = 0; q < world; ++q) {
+            if (q == rank) { c->box.base[q] = c->box_local; continue; }
+            void* p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, all[q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; (void)cudaGetLastError(); break; }
+            c->box.base[q] = static_cast<unsigned char*>(p);
+        }
+    }
+    if (comm_fine && nccl().AllReduce) {                    // unanimous or not at all
+        comm_fine = cudaMemcpyAsync(d_ok, &ok, sizeof ok, cudaMemcpyHostToDevice, h->stream) == cudaSuccess &&
+                    nccl().AllReduce(d_ok, d_ok, 1, ncclInt32, ncclMin, c->comm, h->stream) == ncclSuccess &&
+                    cudaMemcpyAsync(&ok, d_ok, sizeof ok, cudaMemcpyDeviceToHost, h->stream) == cudaSuccess &&
+                    cudaStreamSynchronize(h->stream) == cudaSuccess;
+        if (!comm_fine) ok = 0;
+    } else ok = 0;
+    cudaFree(tmp);
+    (void)cudaGetLastError();
+    c->box.world = world; c->box.rank = rank; c->box.xb_max = PEER_XB_MAX;
+    c->peer_ok = ok != 0;
     return NOSPLAN_OK;
 }
+
+// 1 when the two exchanges of slice mode travel over peer memory (NVLink stores + flags), 0 when they use NCCL
+extern "C" int nosplan_shard_transport(nosplan_t* h) { return h && h->sctx && h->sctx->peer_ok ? 1 : 0; }
 
 extern "C" int nosplan_run_sharded(nosplan_t* h, int32_t gather_plan) {
     if (!h) return NOSPLAN_E_INVALID;
@@ -174,6 +234,24 @@ extern "C" int nosplan_run_sliced(nosplan_t* h) {
         c->d = nullptr; c->cap = 0;
         SCU(h, cudaMalloc(&c->d, o + o / 4 + (1 << 20)));
         c->cap = o + o / 4 + (1 << 20);
+    }
+    if (c->peer_ok && xb <= PEER_XB_MAX) {
+        // peer-memory transport: each producer kernel is followed by a push into every rank's mailbox, each consumer kernel
+        // starts by waiting for the W flags of its own mailbox -- no collective launch on the path
+        const unsigned epoch = ++c->epoch;
+        const int par = epoch & 1;
+        unsigned char* me = c->box.base[c->rank];
+        int rc = nosplan_slice_begin_ex(h, nullptr, &c->box, epoch);
+        if (rc != NOSPLAN_OK) return rc;
+        rc = nosplan_slice_mid_ex(h, c->rank, W, me + nsp::box_tot(par, 0), c->d + c->o_local_x, (int64_t)xb,
+                                  nsp::PeerWait{reinterpret_cast<const unsigned*>(me + nsp::box_flags(1, par)), W, epoch});
+        if (rc != NOSPLAN_OK) return rc;
+        nsp::launch_push_exchange(c->d + c->o_local_x, xb, c->box, epoch, h->stream);
+        SCU(h, cudaGetLastError());
+        rc = nosplan_shard_end_ex(h, me + nsp::box_x(par, 0, PEER_XB_MAX), W, PEER_XB_MAX,
+                                  nsp::PeerWait{reinterpret_cast<const unsigned*>(me + nsp::box_flags(2, par)), W, epoch});
+        if (rc == NOSPLAN_OK) h->launches += 2;                  // the two push kernels
+        return rc;
     }
     int rc = nosplan_slice_begin(h, c->d + o_t);
     if (rc != NOSPLAN_OK) return rc;

@@ -743,6 +743,10 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     cudaGridDependencySynchronize();
+    if (pb.gflags[3]) {                  // a peer never delivered its block: nothing below would be meaningful
+        if (tid == 0) { pb.stats->path = 0; pb.stats->pad = 2; }
+        return;
+    }
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
     const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0));
 
@@ -901,7 +905,8 @@ cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st) {
 
 // Node-sharded Plan(): every rank ran the node-parallel pass on its own node range and all-gathered its
 // [acc (4 x u64) | placed bitmap] block; OR the bitmaps and sum the counters into this rank's work area.
-__global__ void __launch_bounds__(256) k_shard_combine(DevProblem pb, const unsigned char* gathered, int world, size_t stride) {
+__global__ void __launch_bounds__(256) k_shard_combine(DevProblem pb, const unsigned char* gathered, int world, size_t stride, PeerWait wait) {
+    if (!peer_wait(wait) && threadIdx.x == 0) pb.gflags[3] = 1;
     const int words = (pb.n_keys + 31) / 32;
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x < words) {
@@ -916,10 +921,10 @@ __global__ void __launch_bounds__(256) k_shard_combine(DevProblem pb, const unsi
     }
 }
 
-void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, cudaStream_t st) {
+void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, const PeerWait& wait, cudaStream_t st) {
     const int words = (pb.n_keys + 31) / 32;
     const int n = words > 4 ? words : 4;
-    k_shard_combine<<<(n + 255) / 256, 256, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world, stride);
+    k_shard_combine<<<(n + 255) / 256, 256, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world, stride, wait);
 }
 
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st) {

@@ -70,7 +70,7 @@ def main():
                 same_c &= st["path"] == 0 and ost["lacking_at_start"] > 0   # the sequential sweep is needed: same verdict on every rank
         ok &= same_a and same_b and same_c
         print(f"rank {rank}/{world} {shape} {regime}: path={st['path']}/{st2['path']} torch-collectives={'OK' if same_a else 'MISMATCH'} "
-              f"library-collectives={'OK' if same_b else 'MISMATCH'} sliced={'OK' if same_c else 'MISMATCH'}", flush=True)
+              f"library-collectives={'OK' if same_b else 'MISMATCH'} sliced[{eng.shard_transport()}]={'OK' if same_c else 'MISMATCH'}", flush=True)
     eng.close()
     dist.barrier()
     dist.destroy_process_group()
