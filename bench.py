@@ -199,10 +199,10 @@ def run_ours(args):
             torch.cuda.synchronize()
 
     def one_step(timed):
-        with torch.cuda.stream(ext):
-            flush.zero_()
-        if sharded_run:                      # ranks enter the step together: a late peer would otherwise be timed as NCCL wait
+        if sharded_run:                      # ranks enter the step together: a late peer would otherwise be timed as waiting
             sync_all()
+        with torch.cuda.stream(ext):         # L2 flush; the Plan()'s launches queue up behind it exactly as on one GPU
+            flush.zero_()
         s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
         s.record(ext)
         if sharded_run:

@@ -23,8 +23,7 @@ cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st);
 void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, const PeerWait& wait, cudaStream_t st);
 void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st);
 void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, const PeerWait& wait, cudaStream_t st);
-void launch_push_totals(const DevProblem& pb, const PeerBox& box, unsigned epoch, cudaStream_t st);
-void launch_push_exchange(const void* src, size_t bytes, const PeerBox& box, unsigned epoch, cudaStream_t st);
+
 cudaError_t sweep_prepare_device();
 int sweep_max_keys();
 }  // namespace nsp
@@ -705,17 +704,15 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
 // ---- slice mode: every rank uploaded ONLY its own slice of the name-ordered node list -------------------------------
 }  // extern "C"
 
-// box != nullptr: the totals block is pushed into every rank's mailbox (peer memory) instead of being packed for a collective
-int nosplan_slice_begin_ex(nosplan* h, void* d_totals, const PeerBox* box, unsigned epoch) {
+int nosplan_slice_begin_ex(nosplan* h, void* d_totals) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_slice_begin before nosplan_upload");
-    if (!d_totals && !box) return fail(h, NOSPLAN_E_INVALID, "null totals buffer");
+    if (!d_totals) return fail(h, NOSPLAN_E_INVALID, "null totals buffer");
     CU(h, cudaSetDevice(h->device));
     h->pb.slice_mode = 1;
     int rc = run_pre(h, false);                             // cluster totals of the slice
     if (rc != NOSPLAN_OK) return rc;
-    if (box) launch_push_totals(h->pb, *box, epoch, h->stream);
-    else launch_slice_pack_totals(h->pb, d_totals, h->stream);
+    launch_slice_pack_totals(h->pb, d_totals, h->stream);
     CU(h, cudaGetLastError());
     h->launches = (h->pb.N > 0) + 1;
     return NOSPLAN_OK;
@@ -759,9 +756,41 @@ int nosplan_shard_end_ex(nosplan* h, const void* d_gathered, int32_t world, size
     return NOSPLAN_OK;
 }
 
+// Slice mode with both exchanges fused into the planning kernels (peer-memory transport, DevProblem::xf_*).
+int nosplan_run_sliced_fused(nosplan* h, const PeerBox& box, unsigned epoch, unsigned char* d_exchange, size_t xb) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_run_sliced before nosplan_upload");
+    CU(h, cudaSetDevice(h->device));
+    DevProblem& pb = h->pb;
+    pb.slice_mode = 1;
+    pb.xf_on = 1; pb.xf_epoch = epoch; pb.xf_box = box; pb.xf_exchange = d_exchange; pb.xf_xb = xb;
+    int rc = run_pre(h, false);                             // reset, k_prepass (+ push of the slice's totals)
+    if (rc == NOSPLAN_OK) {
+        launch_tracker_init(pb, h->stream);                 // wait + fold the totals, clear the exchange block, tracker
+        if (h->kernel_events) cudaEventRecord(h->ev[7], h->stream);
+        DevProblem shard = pb;                              // the whole local snapshot IS this rank's slice
+        shard.whole_snapshot = 0;
+        shard.acc = reinterpret_cast<unsigned long long*>(d_exchange);
+        shard.placed = reinterpret_cast<unsigned*>(d_exchange + 32);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = launch_parallel(shard, h->stream);       // node-parallel pass (+ push of the exchange block)
+        if (h->kernel_events) cudaEventRecord(h->ev[8], h->stream);
+        DevProblem verify = pb;
+        verify.whole_snapshot = 0;
+        if (e == cudaSuccess) e = launch_sweep(verify, h->d_cand_idx, h->stream);   // wait + fold the blocks, verification
+        if (e == cudaSuccess) e = cudaEventRecord(h->ev[3], h->stream);
+        if (e != cudaSuccess) rc = fail(h, NOSPLAN_E_CUDA, "sliced Plan(): %s", cudaGetErrorString(e));
+    }
+    pb.xf_on = 0;                                           // the other drivers of this handle never see the fused fields
+    if (rc != NOSPLAN_OK) return rc;
+    h->launches = 4;
+    h->ran = true;
+    return NOSPLAN_OK;
+}
+
 extern "C" {
 
-int nosplan_slice_begin(nosplan_t* h, void* d_totals) { return nosplan_slice_begin_ex(h, d_totals, nullptr, 0); }
+int nosplan_slice_begin(nosplan_t* h, void* d_totals) { return nosplan_slice_begin_ex(h, d_totals); }
 
 int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes) {
     return nosplan_slice_mid_ex(h, rank, world, d_totals_gathered, d_exchange, exchange_bytes, PeerWait{nullptr, 0, 0});

@@ -43,7 +43,7 @@ struct nosplan {
 
 int nosplan_fail(nosplan* h, int code, const char* fmt, ...);
 void nosplan_phase_times(nosplan* h, nosplan_stats* stats);
-int nosplan_slice_begin_ex(nosplan* h, void* d_totals, const nsp::PeerBox* box, unsigned epoch);
+int nosplan_slice_begin_ex(nosplan* h, void* d_totals);
 int nosplan_slice_mid_ex(nosplan* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes,
                          const nsp::PeerWait& wait);
 int nosplan_shard_end_ex(nosplan* h, const void* d_gathered, int32_t world, size_t stride, const nsp::PeerWait& wait);

@@ -35,6 +35,33 @@ struct DevStats {
     int path, pad;             // 1: node-parallel pass stood, 0: sequential sweep
 };
 
+// ---- exchange over peer memory (slice mode on NVLink-connected GPUs, one process per GPU) ------------------------------
+// Every rank owns one mailbox in its own HBM, mapped into the other ranks through CUDA IPC.  A rank PUSHES its block into
+// every mailbox (remote stores over NVLink), fences, and raises its flag there; the consumer kernel on each rank spins on
+// the W flags of its own mailbox (local loads) and reads W blocks from local memory.  Flags carry the Plan() epoch and
+// slots alternate by epoch parity, so nothing is ever reset and a rank at most one step ahead never overwrites unread data.
+constexpr int PEER_MAX = 8;
+struct PeerBox { unsigned char* base[PEER_MAX]; int world, rank; unsigned long long xb_max; };
+struct PeerWait { const unsigned* flags; int world; unsigned epoch; };      // flags == nullptr: nothing to wait for
+__host__ __device__ inline size_t box_flags(int which, int parity) { return (size_t)(which - 1) * 64 + (size_t)parity * 32; }
+__host__ __device__ inline size_t box_tot(int parity, int r) { return 256 + ((size_t)parity * PEER_MAX + r) * 256; }
+__host__ __device__ inline size_t box_x(int parity, int r, size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + ((size_t)parity * PEER_MAX + r) * xb_max; }
+inline size_t box_bytes(size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + 2 * PEER_MAX * xb_max; }
+
+// all threads of the block call it; false = a peer did not show up within several seconds (the caller records the failure
+// instead of hanging the GPU)
+__device__ __forceinline__ bool peer_wait(const PeerWait& w) {
+    bool ok = true;
+    if (w.flags && (int)threadIdx.x < w.world) {
+        const volatile unsigned* f = w.flags + threadIdx.x;
+        unsigned spins = 0;
+        while ((int)(*f - w.epoch) < 0) { __nanosleep(500); if (++spins > (1u << 24)) { ok = false; break; } }
+    }
+    ok = __syncthreads_and(ok) != 0;
+    __threadfence_system();
+    return ok;
+}
+
 struct DevProblem {
     int kind, K, R, n_other;
     int N, G, P, n_keys, n_runs, filter_mode;
@@ -76,6 +103,12 @@ struct DevProblem {
     int fast_eligible;               // every pod class requests at most one slice profile
     int32_t sat_m[KP];               // MIG: M_p, most devices of profile p one GPU can hold (allowed-geometry rows); MPS: from gflags[1]
     int slice_mode;                  // this rank holds only its own slice of the node list: no sequential sweep is possible here
+    // slice mode with the two exchanges fused into the kernels (peer-memory transport): k_prepass's last CTA pushes the totals,
+    // k_tracker_init waits for and folds them, k_plan_parallel's last CTA pushes the exchange block, k_plan_sweep waits and folds
+    int xf_on; unsigned xf_epoch;
+    PeerBox xf_box;
+    unsigned char* xf_exchange;      // this rank's exchange block [4 x u64 counters | placed-key bitmap]
+    unsigned long long xf_xb;        // its size in bytes (8-byte granular)
     // work area (zeroed before each run)
     long long* tot;                  // [KP] sum over nodes of (alloc - requested) per slice column
     int32_t* lack;                   // [KP] SliceTracker.lackingSlices
@@ -88,7 +121,7 @@ struct DevProblem {
     unsigned* placed;                // [(n_keys+31)/32] tracker keys placed by the node-parallel pass
     unsigned long long* acc;         // [4]  placements, geometry evals, visited, candidate nodes of the node-parallel pass
     int32_t* lack_dec;               // [KP] lacking quantities removed by the node-parallel pass (single-rank runs)
-    int32_t* next_node;              // [1]  work counter of the node-parallel pass
+    int32_t* next_node;              // [4]  [0] work counter of the node-parallel pass, [1] / [2] CTAs of k_prepass / k_plan_parallel done
     int whole_snapshot;              // the node-parallel pass covers every node on this rank (no exchange needed)
     // outputs
     uint4* out_count;                // [N*G]
@@ -111,31 +144,30 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
-// ---- exchange over peer memory (slice mode on NVLink-connected GPUs, one process per GPU) ------------------------------
-// Every rank owns one mailbox in its own HBM, mapped into the other ranks through CUDA IPC.  A rank PUSHES its block into
-// every mailbox (remote stores over NVLink), fences, and raises its flag there; the consumer kernel on each rank spins on
-// the W flags of its own mailbox (local loads) and reads W blocks from local memory.  Flags carry the Plan() epoch and
-// slots alternate by epoch parity, so nothing is ever reset and a rank at most one step ahead never overwrites unread data.
-constexpr int PEER_MAX = 8;
-struct PeerBox { unsigned char* base[PEER_MAX]; int world, rank; unsigned long long xb_max; };
-struct PeerWait { const unsigned* flags; int world; unsigned epoch; };      // flags == nullptr: nothing to wait for
-__host__ __device__ inline size_t box_flags(int which, int parity) { return (size_t)(which - 1) * 64 + (size_t)parity * 32; }
-__host__ __device__ inline size_t box_tot(int parity, int r) { return 256 + ((size_t)parity * PEER_MAX + r) * 256; }
-__host__ __device__ inline size_t box_x(int parity, int r, size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + ((size_t)parity * PEER_MAX + r) * xb_max; }
-inline size_t box_bytes(size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + 2 * PEER_MAX * xb_max; }
+// last-CTA-done: true in exactly one CTA of the grid, after every other CTA's global writes and atomics are visible to it
+__device__ __forceinline__ bool last_block_done(int32_t* counter) {
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(counter, 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (s_last) __threadfence();
+    return s_last != 0;
+}
 
-// all threads of the block call it; false = a peer did not show up within several seconds (the caller records the failure
-// instead of hanging the GPU)
-__device__ __forceinline__ bool peer_wait(const PeerWait& w) {
-    bool ok = true;
-    if (w.flags && (int)threadIdx.x < w.world) {
-        const volatile unsigned* f = w.flags + threadIdx.x;
-        unsigned spins = 0;
-        while ((int)(*f - w.epoch) < 0) { __nanosleep(500); if (++spins > (1u << 24)) { ok = false; break; } }
+// one CTA stores `bytes` (8-byte granular, read through L2) into slot `which` of every rank's mailbox and raises its flag
+__device__ __forceinline__ void peer_push(const PeerBox& box, int which, unsigned epoch, const unsigned char* src, unsigned long long bytes) {
+    const int par = epoch & 1;
+    const unsigned long long n8 = bytes >> 3;
+    for (int r = 0; r < box.world; ++r) {
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(
+            box.base[r] + (which == 1 ? box_tot(par, box.rank) : box_x(par, box.rank, box.xb_max)));
+        for (unsigned long long i = threadIdx.x; i < n8; i += blockDim.x) dst[i] = __ldcg(reinterpret_cast<const unsigned long long*>(src) + i);
     }
-    ok = __syncthreads_and(ok) != 0;
     __threadfence_system();
-    return ok;
+    __syncthreads();
+    if ((int)threadIdx.x < box.world)
+        *reinterpret_cast<volatile unsigned*>(box.base[threadIdx.x] + box_flags(which, par) + 4 * box.rank) = epoch;
 }
 
 __device__ __forceinline__ unsigned byte_of(const uint4& v, int p) {

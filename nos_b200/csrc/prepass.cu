@@ -128,22 +128,70 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) mf = max(mf, s_maxfree[w][lane]);
         if (mf > 0) atomicMax(&pb.maxfree[lane], mf);
     }
+    // slice mode, fused exchange 1: the CTA that finishes last pushes this rank's totals into every rank's mailbox
+    if (pb.xf_on && last_block_done(&pb.next_node[1])) {
+        __shared__ __align__(16) unsigned char s_blk[256];
+        const int par = pb.xf_epoch & 1;
+        if (tid < 64) reinterpret_cast<int32_t*>(s_blk)[tid] = 0;
+        __syncthreads();
+        if (tid < KP) reinterpret_cast<long long*>(s_blk)[tid] = __ldcg(&pb.tot[tid]);
+        if (tid < KP) reinterpret_cast<int32_t*>(s_blk + 128)[tid] = __ldcg(&pb.maxfree[tid]);
+        if (tid < 3) reinterpret_cast<int32_t*>(s_blk + 192)[tid] = __ldcg(&pb.gflags[tid]);
+        __syncthreads();
+        for (int x = tid; x < pb.xf_box.world * 16; x += blockDim.x) {
+            const int r = x >> 4, q = x & 15;
+            reinterpret_cast<uint4*>(pb.xf_box.base[r] + box_tot(par, pb.xf_box.rank))[q] = reinterpret_cast<const uint4*>(s_blk)[q];
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (tid < pb.xf_box.world)
+            *reinterpret_cast<volatile unsigned*>(pb.xf_box.base[tid] + box_flags(1, par) + 4 * pb.xf_box.rank) = pb.xf_epoch;
+    }
 }
 
 __global__ void __launch_bounds__(256) k_tracker_init(DevProblem pb) {
     __shared__ int s_lack[KP];
+    __shared__ long long s_tot[KP];
     cudaTriggerProgrammaticLaunchCompletion();
     if (threadIdx.x < KP) s_lack[threadIdx.x] = 0;
-    __syncthreads();
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     cudaGridDependencySynchronize();                     // the totals of k_prepass (and the work-area reset before it)
+    if (pb.xf_on) {
+        // slice mode, fused exchange 1: wait for every rank's totals in this rank's mailbox and fold them (each CTA for itself;
+        // CTA 0 also publishes them for the kernels that follow), and clear this rank's exchange block for the pass to come
+        const int par = pb.xf_epoch & 1, W = pb.xf_box.world;
+        const unsigned char* me = pb.xf_box.base[pb.xf_box.rank];
+        const bool ok = peer_wait(PeerWait{reinterpret_cast<const unsigned*>(me + box_flags(1, par)), W, pb.xf_epoch});
+        const int t = threadIdx.x;
+        if (t < KP) {
+            long long sum = 0; int m = 0;
+            for (int r = 0; r < W; ++r) {
+                sum += __ldcg(reinterpret_cast<const long long*>(me + box_tot(par, r)) + t);
+                m = max(m, __ldcg(reinterpret_cast<const int32_t*>(me + box_tot(par, r) + 128) + t));
+            }
+            s_tot[t] = sum;
+            if (blockIdx.x == 0) { pb.tot[t] = sum; pb.maxfree[t] = m; }
+        }
+        if (blockIdx.x == 0 && t < 3) {
+            int f = 0;
+            for (int r = 0; r < W; ++r) {
+                const int v = __ldcg(reinterpret_cast<const int32_t*>(me + box_tot(par, r) + 192) + t);
+                f = t == 0 ? (f | v) : max(f, v);
+            }
+            pb.gflags[t] = f;
+        }
+        if (blockIdx.x == 0 && t == 0 && !ok) pb.gflags[3] = 1;
+        unsigned long long* ex = reinterpret_cast<unsigned long long*>(pb.xf_exchange);
+        for (unsigned long long i = s; i < (pb.xf_xb >> 3); i += (unsigned long long)gridDim.x * blockDim.x) ex[i] = 0;
+    } else if (threadIdx.x < KP) s_tot[threadIdx.x] = pb.tot[threadIdx.x];
+    __syncthreads();
     if (s < pb.P) {
         const int key = pb.pod_key[s];
         for (int e = pb.pod_sptr[s]; e < pb.pod_sptr[s + 1]; ++e) {
             const int col = pb.pod_scol[e];
             if (col >= 3 + pb.K) break;              // columns ascend: slice columns come first
             const int p = col - 3;
-            long long avail = pb.tot[p];
+            long long avail = s_tot[p];
             if (avail < 0) avail = 0;                 // SubtractNonNegative (pkg/resource/resource.go:76-88)
             const long long diff = avail - pb.pod_sqty[e];
             if (diff < 0) {
@@ -187,61 +235,23 @@ __global__ void k_slice_combine_totals(DevProblem pb, const unsigned char* gathe
     }
 }
 
-// pack + push: the 256-byte totals block goes straight into every rank's mailbox, then this rank's flag is raised there
-__global__ void k_push_totals(DevProblem pb, PeerBox box, unsigned epoch) {
-    __shared__ __align__(16) unsigned char s_block[256];
-    const int t = threadIdx.x, par = epoch & 1;
-    if (t < 64) reinterpret_cast<int32_t*>(s_block)[t] = 0;
-    __syncthreads();
-    if (t < KP) reinterpret_cast<long long*>(s_block)[t] = pb.tot[t];
-    if (t < KP) reinterpret_cast<int32_t*>(s_block + 128)[t] = pb.maxfree[t];
-    if (t < 3) reinterpret_cast<int32_t*>(s_block + 192)[t] = pb.gflags[t];
-    __syncthreads();
-    for (int x = t; x < box.world * 16; x += blockDim.x) {
-        const int r = x >> 4, q = x & 15;
-        reinterpret_cast<uint4*>(box.base[r] + box_tot(par, box.rank))[q] = reinterpret_cast<const uint4*>(s_block)[q];
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (t < box.world) *reinterpret_cast<volatile unsigned*>(box.base[t] + box_flags(1, par) + 4 * box.rank) = epoch;
-}
-
-// the exchange block of the node-parallel pass (counters + placed-key bitmap, 8-byte granular) into every mailbox
-__global__ void __launch_bounds__(256) k_push_exchange(const unsigned char* src, unsigned long long bytes, PeerBox box, unsigned epoch) {
-    const int t = threadIdx.x, par = epoch & 1;
-    const unsigned long long n8 = bytes >> 3;
-    for (int r = 0; r < box.world; ++r) {
-        unsigned long long* dst = reinterpret_cast<unsigned long long*>(box.base[r] + box_x(par, box.rank, box.xb_max));
-        for (unsigned long long i = t; i < n8; i += blockDim.x) dst[i] = reinterpret_cast<const unsigned long long*>(src)[i];
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (t < box.world) *reinterpret_cast<volatile unsigned*>(box.base[t] + box_flags(2, par) + 4 * box.rank) = epoch;
-}
-
 void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st) {
     k_slice_pack_totals<<<1, 32, 0, st>>>(pb, static_cast<unsigned char*>(block));
 }
 void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, const PeerWait& wait, cudaStream_t st) {
     k_slice_combine_totals<<<1, 32, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world, wait);
 }
-void launch_push_totals(const DevProblem& pb, const PeerBox& box, unsigned epoch, cudaStream_t st) {
-    k_push_totals<<<1, 128, 0, st>>>(pb, box, epoch);
-}
-void launch_push_exchange(const void* src, size_t bytes, const PeerBox& box, unsigned epoch, cudaStream_t st) {
-    k_push_exchange<<<1, 256, 0, st>>>(static_cast<const unsigned char*>(src), (unsigned long long)bytes, box, epoch);
-}
-
 void launch_prepass(const DevProblem& pb, cudaStream_t st) {
     if (pb.N > 0) {
         int blocks = (pb.N + PRE_NODES - 1) / PRE_NODES;      // one tile of 32 nodes per block, grid-stride beyond 8 waves
         if (blocks > 148 * 8) blocks = 148 * 8;
         k_prepass<<<blocks, 256, 0, st>>>(pb);
-    }
+    } else if (pb.xf_on) k_prepass<<<1, 256, 0, st>>>(pb);      // fused slice mode: an empty slice still pushes its (zero) totals
 }
 
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st) {
-    if (pb.P > 0) launch_pdl(k_tracker_init, dim3((pb.P + 255) / 256), dim3(256), 0, st, pb);
+    // fused slice mode: the kernel also folds the exchanged totals, so it runs even without pods
+    if (pb.P > 0 || pb.xf_on) launch_pdl(k_tracker_init, dim3(pb.P > 0 ? (pb.P + 255) / 256 : 1), dim3(256), 0, st, pb);
 }
 
 }  // namespace nsp

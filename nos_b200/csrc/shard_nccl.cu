@@ -20,6 +20,7 @@ int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world);
 int nosplan_slice_begin(nosplan_t* h, void* d_totals);
 int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes);
 }
+int nosplan_run_sliced_fused(nosplan* h, const nsp::PeerBox& box, unsigned epoch, unsigned char* d_exchange, size_t xb);
 
 namespace {
 
@@ -60,11 +61,6 @@ NcclApi& nccl() {
 inline size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
 
 }  // namespace
-
-namespace nsp {
-void launch_push_totals(const DevProblem& pb, const PeerBox& box, unsigned epoch, cudaStream_t st);
-void launch_push_exchange(const void* src, size_t bytes, const PeerBox& box, unsigned epoch, cudaStream_t st);
-}
 
 constexpr size_t PEER_XB_MAX = 64 << 10;                  // exchange blocks up to 64 KiB (524 032 tracker keys) go over peer memory
 
@@ -236,21 +232,10 @@ extern "C" int nosplan_run_sliced(nosplan_t* h) {
         c->cap = o + o / 4 + (1 << 20);
     }
     if (c->peer_ok && xb <= PEER_XB_MAX) {
-        // peer-memory transport: each producer kernel is followed by a push into every rank's mailbox, each consumer kernel
-        // starts by waiting for the W flags of its own mailbox -- no collective launch on the path
-        const unsigned epoch = ++c->epoch;
-        const int par = epoch & 1;
-        unsigned char* me = c->box.base[c->rank];
-        int rc = nosplan_slice_begin_ex(h, nullptr, &c->box, epoch);
-        if (rc != NOSPLAN_OK) return rc;
-        rc = nosplan_slice_mid_ex(h, c->rank, W, me + nsp::box_tot(par, 0), c->d + c->o_local_x, (int64_t)xb,
-                                  nsp::PeerWait{reinterpret_cast<const unsigned*>(me + nsp::box_flags(1, par)), W, epoch});
-        if (rc != NOSPLAN_OK) return rc;
-        nsp::launch_push_exchange(c->d + c->o_local_x, xb, c->box, epoch, h->stream);
-        SCU(h, cudaGetLastError());
-        rc = nosplan_shard_end_ex(h, me + nsp::box_x(par, 0, PEER_XB_MAX), W, PEER_XB_MAX,
-                                  nsp::PeerWait{reinterpret_cast<const unsigned*>(me + nsp::box_flags(2, par)), W, epoch});
-        if (rc == NOSPLAN_OK) h->launches += 2;                  // the two push kernels
+        // peer-memory transport, fused: the last CTA of each producer kernel pushes the rank's block into every mailbox and
+        // the consumer kernel starts by waiting for the W flags of its own mailbox -- five stream operations per Plan(), the
+        // same as on one GPU, and no collective launch on the path
+        const int rc = nosplan_run_sliced_fused(h, c->box, ++c->epoch, c->d + c->o_local_x, xb);
         return rc;
     }
     int rc = nosplan_slice_begin(h, c->d + o_t);

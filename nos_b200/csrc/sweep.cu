@@ -685,7 +685,8 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
     cudaGridDependencySynchronize();
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
-    if (!fast_applicable(pb, lack0, lane)) return;
+    const bool applicable = fast_applicable(pb, lack0, lane);
+    if (!applicable && !pb.xf_on) return;
 
     WarpScratch& ws = ws_all[warp];
     int lack = lack0 > 0 ? SATURATED : 0;
@@ -694,7 +695,7 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     // dynamic distribution: nodes differ a lot in cost (how many runs are feasible), so warps pull the next node.  Pulling
     // ahead of need (to hide the counter's round trip or to prefetch rows) was measured slower: with ~3 nodes per warp the
     // reserved nodes wait behind a busy warp while other warps idle.
-    for (;;) {
+    while (applicable) {
         int i = 0;
         if (lane == 0) i = pb.node_lo + atomicAdd(pb.next_node, 1);
         i = __shfl_sync(FULL, i, 0);
@@ -712,6 +713,9 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
         atomicAdd(&pb.acc[1], (unsigned long long)st_evals);
         atomicAdd(&pb.acc[2], (unsigned long long)visited);
     }
+    // slice mode, fused exchange 2: the CTA that finishes last pushes this rank's counters and placed-key bitmap (pb.acc and
+    // pb.placed point into the exchange block) into every rank's mailbox -- also when the pass did not apply (all zero)
+    if (pb.xf_on && last_block_done(&pb.next_node[2])) peer_push(pb.xf_box, 2, pb.xf_epoch, pb.xf_exchange, pb.xf_xb);
 }
 
 // verification of the node-parallel pass, or the sequential sweep
@@ -743,6 +747,25 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     cudaGridDependencySynchronize();
+    if (pb.xf_on) {
+        // slice mode, fused exchange 2: wait for every rank's block in this rank's mailbox; OR the bitmaps, sum the counters
+        const int par = pb.xf_epoch & 1, W = pb.xf_box.world;
+        const unsigned char* me = pb.xf_box.base[pb.xf_box.rank];
+        if (!peer_wait(PeerWait{reinterpret_cast<const unsigned*>(me + box_flags(2, par)), W, pb.xf_epoch}) && tid == 0) pb.gflags[3] = 1;
+        const int words = (pb.n_keys + 31) / 32;
+        for (int x = tid; x < words; x += blockDim.x) {
+            unsigned w = 0;
+            for (int r = 0; r < W; ++r) w |= __ldcg(reinterpret_cast<const unsigned*>(me + box_x(par, r, pb.xf_box.xb_max) + 32) + x);
+            pb.placed[x] = w;
+        }
+        if (tid < 4) {
+            unsigned long long a = 0;
+            for (int r = 0; r < W; ++r) a += __ldcg(reinterpret_cast<const unsigned long long*>(me + box_x(par, r, pb.xf_box.xb_max)) + tid);
+            pb.acc[tid] = a;
+        }
+        __threadfence_block();
+        __syncthreads();
+    }
     if (pb.gflags[3]) {                  // a peer never delivered its block: nothing below would be meaningful
         if (tid == 0) { pb.stats->path = 0; pb.stats->pad = 2; }
         return;
@@ -897,8 +920,9 @@ cudaError_t sweep_prepare_device() {
 }
 
 cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st) {
-    if (!pb.fast_eligible || pb.N == 0 || pb.P == 0 || pb.node_hi <= pb.node_lo) return cudaSuccess;
-    int blocks = (pb.node_hi - pb.node_lo + 3) / 4;
+    const bool work = pb.fast_eligible && pb.N > 0 && pb.P > 0 && pb.node_hi > pb.node_lo;
+    if (!work && !pb.xf_on) return cudaSuccess;            // fused slice mode: the kernel still pushes this rank's (empty) block
+    int blocks = work ? (pb.node_hi - pb.node_lo + 3) / 4 : 1;
     if (blocks > g_par_blocks) blocks = g_par_blocks;
     return launch_pdl(k_plan_parallel, dim3(blocks), dim3(128), 0, st, pb);
 }
