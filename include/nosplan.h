@@ -118,7 +118,7 @@ typedef struct nosplan_stats {
     int32_t lacking_at_end;
     float   ms_h2d, ms_kernels, ms_d2h;/* CUDA-event times of the last call (ms_kernels = whole run()) */
     float   ms_prepass, ms_tracker, ms_parallel, ms_sweep; /* per-kernel CUDA-event times inside ms_kernels */
-    float   pad0;
+    int32_t waves;                     /* path 0 only: > 0 = the sweep ran as that many parallel waves (exact lacking vector) */
     int32_t kernel_launches;
     int32_t path;                      /* 1: node-parallel pass (saturated lacking vector), 0: sequential sweep */
     int64_t h2d_bytes, d2h_bytes;      /* bytes copied by upload() / download() */

@@ -77,7 +77,7 @@ class CStats(C.Structure):
         ("lacking_at_start", C.c_int32), ("lacking_at_end", C.c_int32),
         ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float),
         ("ms_prepass", C.c_float), ("ms_tracker", C.c_float), ("ms_parallel", C.c_float), ("ms_sweep", C.c_float),
-        ("pad0", C.c_float),
+        ("waves", C.c_int32),
         ("kernel_launches", C.c_int32), ("path", C.c_int32),
         ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
     ]

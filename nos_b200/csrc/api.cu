@@ -20,6 +20,7 @@ void launch_prepass(const DevProblem& pb, cudaStream_t st);
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
 cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st);
+cudaError_t launch_waves(const DevProblem& pb, cudaStream_t st);
 void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, const PeerWait& wait, cudaStream_t st);
 void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st);
 void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, const PeerWait& wait, cudaStream_t st);
@@ -112,7 +113,7 @@ struct GoStable {
 struct Layout {            // byte offsets into the arena / staging buffer
     size_t model_off, geom, node_gpu_count, gpu_model, gpu_mem, gpu_used, gpu_free, gpu_umask, gpu_fmask,
         node_alloc, node_req, node_allowed, node_npods, nodes_end,
-        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, work_end, cand_flag, cand_idx, out_count, out_mask, out_end,
+        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, wave, work_end, cand_flag, cand_idx, out_count, out_mask, out_end,
         pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
         cmin_cpu, cmin_mem, cmin_eph, upload_end, placed, entry_lack, total;
 };
@@ -401,7 +402,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     put(L.node_allowed, 4 * (size_t)N); put(L.node_npods, 4 * (size_t)N);
     L.nodes_end = o;
     put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats));
-    put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.lack_dec, 4 * KP); put(L.next_node, 16);
+    put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.lack_dec, 4 * KP); put(L.next_node, 16); put(L.wave, 32);
     put(L.placed, 4 * (((size_t)P + 31) / 32));             // tracker tables: sized for P keys (keys <= P), reset with the rest
     put(L.entry_lack, 4 * (size_t)P * KP);
     L.work_end = o;
@@ -486,6 +487,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     pb.maxfree = (int32_t*)(A + L.maxfree); pb.gflags = (int32_t*)(A + L.gflags);
     pb.acc = (unsigned long long*)(A + L.acc);
     pb.lack_dec = (int32_t*)(A + L.lack_dec); pb.next_node = (int32_t*)(A + L.next_node); pb.whole_snapshot = 1;
+    pb.wave = (int32_t*)(A + L.wave);
     pb.tot = (long long*)(A + L.tot); pb.lack = (int32_t*)(A + L.lack); pb.stats = (DevStats*)(A + L.stats);
     pb.cand_flag = (uint8_t*)(A + L.cand_flag);
     pb.out_count = (uint4*)(A + L.out_count); pb.out_mask = (uint16_t*)(A + L.out_mask);
@@ -652,8 +654,9 @@ static int run_post(nosplan* h) {
     CU(h, launch_parallel(h->pb, h->stream));
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
     CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
+    CU(h, launch_waves(h->pb, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
-    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
+    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + 2 * (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     h->ran = true;
     return NOSPLAN_OK;
 }
@@ -750,6 +753,7 @@ int nosplan_shard_end_ex(nosplan* h, const void* d_gathered, int32_t world, size
     DevProblem verify = h->pb;
     verify.whole_snapshot = 0;                               // final lacking vector comes from the OR-ed bitmap
     CU(h, launch_sweep(verify, h->d_cand_idx, h->stream));
+    if (!verify.slice_mode) CU(h, launch_waves(verify, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
     h->launches += 2;
     h->ran = true;
@@ -845,6 +849,7 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         nosplan_phase_times(h, stats);
         cudaEventElapsedTime(&stats->ms_d2h, h->ev[4], h->ev[5]);
         stats->path = ds.path;
+        stats->waves = h->pb.slice_mode ? 0 : ds.pad;
         stats->kernel_launches = h->launches;
         stats->h2d_bytes = (int64_t)h->h2d_bytes;
         stats->d2h_bytes = (int64_t)(h->out_count_bytes + h->out_mask_bytes + sizeof(DevStats));

@@ -122,6 +122,8 @@ struct DevProblem {
     unsigned long long* acc;         // [4]  placements, geometry evals, visited, candidate nodes of the node-parallel pass
     int32_t* lack_dec;               // [KP] lacking quantities removed by the node-parallel pass (single-rank runs)
     int32_t* next_node;              // [4]  [0] work counter of the node-parallel pass, [1] / [2] CTAs of k_prepass / k_plan_parallel done
+    int32_t* wave;                   // [8]  [0] k_plan_sweep hands the plan to k_plan_waves  [1],[2] first node of the wave that changes
+                                     //      the lacking vector (by wave parity)  [3] candidate nodes  [4] waves run
     int whole_snapshot;              // the node-parallel pass covers every node on this rank (no exchange needed)
     // outputs
     uint4* out_count;                // [N*G]

@@ -31,6 +31,8 @@
 //                    in registers / shared memory, prefetching the next node while the current one is processed.
 #include <climits>
 
+#include <cooperative_groups.h>
+
 #include "nosplan_dev.cuh"
 
 namespace nsp {
@@ -300,8 +302,24 @@ __device__ __forceinline__ bool mps_gpu_update(SNode& nd, int g, int required, i
 // SliceTracker.Remove (core/tracker.go:67-88).
 //   sequential driver: `removed` is a shared-memory bitmap of emptied entries; lanes = profiles subtract the entry.
 //   parallel driver:   only the global "placed" bitmap is set; the lacking vector is rebuilt from it afterwards.
-template <bool PAR>
-__device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, unsigned* removed, int& lack, int lane) {
+// MODE: how one node is processed
+//   M_SEQ     sequential sweep: exact lacking vector, gate, shared-memory removed-set
+//   M_PAR     node-parallel pass: saturated view, geometry of all GPUs at once, global placed bitmap
+//   M_SPEC    wave, speculative: exact view, nothing written; reports whether the node would change the lacking vector
+//   M_COMMIT  wave, the one node of a wave that does change it: exact view, updates the global removed-set and vector
+constexpr int M_SEQ = 0, M_PAR = 1, M_SPEC = 2, M_COMMIT = 3;
+
+template <int MODE>
+__device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, unsigned* removed, int& lack, int lane, int& dirty) {
+    constexpr bool PAR = MODE == M_PAR;
+    if (MODE == M_SPEC) {
+        // would this placement change the lacking vector?  (the entry's one and only removal, tracker.go:78-86)
+        const unsigned w = __ldcg(&removed[key >> 5]);       // written by other SMs in earlier waves: read at L2
+        if (w >> (key & 31) & 1) return;
+        const int e = (lane < KP) ? pb.entry_lack[(size_t)key * KP + lane] : 0;
+        if (__ballot_sync(FULL, e > 0)) dirty = 1;
+        return;
+    }
     if (PAR) {
         if (lane == 0) {
             const unsigned bit = 1u << (key & 31);
@@ -313,7 +331,7 @@ __device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, un
         }
         return;
     }
-    const unsigned w = removed[key >> 5];
+    const unsigned w = MODE == M_COMMIT ? __ldcg(&removed[key >> 5]) : removed[key >> 5];
     if (w >> (key & 31) & 1) return;
     __syncwarp();
     if (lane == 0) removed[key >> 5] = w | (1u << (key & 31));
@@ -327,10 +345,12 @@ __device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, un
 // One candidate node, start to finish.  `ws.nd` holds the node.  Returns the number of pods added.
 //   lack      lane p: SliceTracker.lackingSlices[p] (PAR: SATURATED on the lacking profiles, never modified)
 //   D         lane p: cluster-wide sum(Allocatable - Requested) of slice column p (unused when PAR)
-template <bool PAR>
+template <int MODE>
 __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& ws, const Tables& tb, const PodCache* pc,
                                             unsigned* removed, int& lack, long long& D, bool& committed,
-                                            long long& st_evals, long long& st_place, int lane) {
+                                            long long& st_evals, long long& st_place, int lane, int& dirty, bool& upd_out) {
+    constexpr bool PAR = MODE == M_PAR;        // saturated view: geometry of all GPUs at once, global placed bitmap
+    constexpr bool GATE = MODE == M_SEQ;       // the cluster-wide gate (core/snapshot.go:132-165); vacuous in the other modes
     SNode& nd = ws.nd;
     const bool mig = pb.kind == NOSPLAN_KIND_MIG;
     const int K = pb.K, fm = pb.filter_mode;
@@ -367,7 +387,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     if (lane < K)
         for (int g = 0; g < ng; ++g) newA += (long long)bytes(nd.used[g])[lane] + bytes(nd.free_[g])[lane];
     const long long allocF = upd ? newA : oldA;                // Allocatable of the forked entry the pods are added to
-    if (lane < KP) { ws.allocF[lane] = allocF; ws.reqF[lane] = oldR; ws.Dg[lane] = PAR ? 0 : D - oldA + allocF; }
+    if (lane < KP) { ws.allocF[lane] = allocF; ws.reqF[lane] = oldR; ws.Dg[lane] = GATE ? D - oldA + allocF : 0; }
     long long remc = nd.alloc[0] - nd.req[0], remm = nd.alloc[1] - nd.req[1], reme = nd.alloc[2] - nd.req[2];
     const bool podcount_ok = nd.npods + 1 <= nd.allowed;
     // no pod requests ephemeral storage and the node is not over-committed on it: every `0 <= reme` test holds
@@ -402,7 +422,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
         // class-level tests; all of them only get tighter while this node is processed
         bool ok_l = true;
         if (q_l > 0) {
-            if (!PAR) ok_l = ws.Dg[lane] >= q_l;                                            // gate, snapshot.go:132-165
+            if (GATE) ok_l = ws.Dg[lane] >= q_l;                                            // gate, snapshot.go:132-165
             if (fit) ok_l = ok_l && (q_l <= ws.allocF[lane] - ws.reqF[lane]);
         }
         if (!__all_sync(FULL, ok_l)) continue;
@@ -417,7 +437,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                 const int fr0 = (lane < ng) ? (int)bytes(nd.free_[lane])[p] : 0;
                 const int cg = q == 1 ? fr0 : fr0 / q;                                        // GPU.AddPod feasibility
                 cap = warp_sum_int(cg);
-                if (!PAR) cap = min(cap, ws.Dg[p] / q);
+                if (GATE) cap = min(cap, ws.Dg[p] / q);
                 if (fit) cap = min(cap, (ws.allocF[p] - ws.reqF[p]) / q);
             }
             if (cap <= 0) continue;
@@ -515,7 +535,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                                 while (todo) {
                                     const int l = __ffs(todo) - 1;
                                     todo &= todo - 1;
-                                    tracker_remove<PAR>(pb, __shfl_sync(FULL, key, l), removed, lack, lane);
+                                    tracker_remove<MODE>(pb, __shfl_sync(FULL, key, l), removed, lack, lane, dirty);
                                 }
                             }
                             added += n; st_place += n;
@@ -554,7 +574,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                                     if (lane == 0) { ws.reqF[p] += q; ws.Dg[p] -= q; }
                                     cap -= 1;
                                 }
-                                tracker_remove<PAR>(pb, pkey, removed, lack, lane);
+                                tracker_remove<MODE>(pb, pkey, removed, lack, lane, dirty);
                                 ++added; ++st_place;
                                 __syncwarp();
                             }
@@ -572,7 +592,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                 const long long cpu = pb.pod_cpu[s], mem = pb.pod_mem[s], eph = pb.pod_eph[s];
                 bool okc = true;                                   // gate + class-level fit again (state moves inside the run)
                 if (q_l > 0) {
-                    if (!PAR) okc = ws.Dg[lane] >= q_l;
+                    if (GATE) okc = ws.Dg[lane] >= q_l;
                     if (fit) okc = okc && (q_l <= ws.allocF[lane] - ws.reqF[lane]);
                 }
                 if (!__all_sync(FULL, okc)) break;                 // every later pod of the run fails the same way
@@ -589,7 +609,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                     }
                 }
                 if (!ok) continue;
-                bool placed = false, dirty = false;                // Node.AddPod: GPUs in order, profiles ascending
+                bool placed = false, moved = false;                // Node.AddPod: GPUs in order, profiles ascending
                 for (int g = 0; g < ng && !placed; ++g) {
                     const int fr = (lane < KP) ? (int)bytes(nd.free_[g])[lane] : 0;
                     const unsigned bad = __ballot_sync(FULL, q_l > 0 && fr < q_l);
@@ -599,11 +619,11 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                         bytes(nd.free_[g])[lane] -= (uint8_t)q_l; bytes(nd.used[g])[lane] += (uint8_t)q_l;
                     }
                     if (lane == 0 && mv) nd.umask[g] |= (uint16_t)mv;
-                    dirty |= mv != 0;
+                    moved |= mv != 0;
                     placed = bad == 0;
                     __syncwarp();
                 }
-                if (!placed) { if (!dirty) break; else continue; }   // a clean failure repeats for the rest of the run
+                if (!placed) { if (!moved) break; else continue; }   // a clean failure repeats for the rest of the run
                 remc -= cpu; remm -= mem; reme -= eph;
                 if (q_l > 0) { ws.reqF[lane] += q_l; ws.Dg[lane] -= q_l; }
                 if (lane == 0 && (fl & PF_HAS_OTHER))
@@ -611,7 +631,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                         const int col = pb.pod_scol[e];
                         if (col >= 3 + K) nd.req[col] += pb.pod_sqty[e];
                     }
-                tracker_remove<PAR>(pb, pb.pod_key[s], removed, lack, lane);
+                tracker_remove<MODE>(pb, pb.pod_key[s], removed, lack, lane, dirty);
                 ++added; ++st_place;
                 __syncwarp();
             }
@@ -620,16 +640,17 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
 
     // ---- 3. Commit / Revert (planner.go:144-149) with the object-graph aliasing rules
     if (added > 0) {
-        if (!PAR && lane < KP) D = ws.Dg[lane];
+        if (GATE && lane < KP) D = ws.Dg[lane];
         committed = true;
-        if (upd && lane < ng) {                                // partitioningState[n] = GetPartitioning(n) (planner.go:138)
+        if (MODE != M_SPEC && upd && lane < ng) {                                // partitioningState[n] = GetPartitioning(n) (planner.go:138)
             const int x = node_i * pb.G + lane;
             pb.out_count[x] = add_bytes(nd.used[lane], nd.free_[lane]);
             pb.out_mask[x] = nd.umask[lane] | nd.fmask[lane];
         }
-    } else if (!PAR && !committed) {
+    } else if (GATE && !committed) {
         D += newA - oldA;                                      // the mutated original is still what the snapshot holds
     }
+    upd_out = upd;
     __syncwarp();
     return added;
 }
@@ -691,7 +712,8 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     WarpScratch& ws = ws_all[warp];
     int lack = lack0 > 0 ? SATURATED : 0;
     long long D = 0, st_evals = 0, st_place = 0, visited = 0;
-    bool committed = true;
+    bool committed = true, upd_unused = false;
+    int dirty_unused = 0;
     // dynamic distribution: nodes differ a lot in cost (how many runs are feasible), so warps pull the next node.  Pulling
     // ahead of need (to hide the counter's round trip or to prefetch rows) was measured slower: with ~3 nodes per warp the
     // reserved nodes wait behind a busy warp while other warps idle.
@@ -706,7 +728,7 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
         store_node(ws.nd, nr, i, lane);
         __syncwarp();
         ++visited;
-        process_node<true>(pb, ws, tb, &pc, pb.placed, lack, D, committed, st_evals, st_place, lane);
+        process_node<M_PAR>(pb, ws, tb, &pc, pb.placed, lack, D, committed, st_evals, st_place, lane, dirty_unused, upd_unused);
     }
     if (lane == 0 && visited) {
         atomicAdd(&pb.acc[0], (unsigned long long)st_place);
@@ -817,6 +839,20 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
         __syncthreads();
     }
 
+    // The sweep must follow the EXACT lacking vector.  It changes only when a node places a pod key nobody placed before
+    // (at most sum(lack) times), and between two changes the nodes are independent of each other: k_plan_waves processes
+    // them in parallel waves.  That needs what the node-parallel pass needs except saturation -- single-profile classes and
+    // consistent node accounts, which make the gate vacuous -- and pays off when few changes are possible.
+    if (!pb.slice_mode && pb.fast_eligible && pb.gflags[0] == 0 && pb.N > 0 && lack_start > 0) {
+        long long total = 0;
+        for (int p = 0; p < KP; ++p) total += max(0, __shfl_sync(FULL, lack0, p));
+        if (total * 45 < (long long)pb.N * 17) {            // ~45 us per change against ~17 us per node of the chain below
+            for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x) pb.placed[w] = 0;
+            if (tid < 4) pb.acc[tid] = 0;
+            if (tid == 0) { pb.stats->lacking_at_start = lack_start; pb.wave[0] = 1; }
+            return;
+        }
+    }
     if (pb.slice_mode) {
         // this rank holds only its slice of the node list: the sequential chain cannot run here.  Report it (path 0, no
         // visits); the caller plans this problem unsharded (nosplan_download_sliced returns NOSPLAN_SLICED_NOT_APPLICABLE).
@@ -868,7 +904,8 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     const int n_cand = s_ncand;
     int lack = lack0;                                              // lane p: lackingSlices[p]
     long long D = (lane < KP) ? pb.tot[lane] : 0;                  // lane p: sum(alloc - requested) of slice column p
-    bool committed = false;
+    bool committed = false, upd_unused = false;
+    int dirty_unused = 0;
     long long st_visited = 0, st_evals = 0, st_place = 0;
 
     NodeRegs nr;
@@ -883,7 +920,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
         int next_i = 0;
         if (have_next) { next_i = cand_idx[c + 1]; load_node(pb, next_i, lane, nr); }   // prefetch, consumed below
         ++st_visited;
-        process_node<false>(pb, ws2[c & 1], tb, &pc, s_removed, lack, D, committed, st_evals, st_place, lane);
+        process_node<M_SEQ>(pb, ws2[c & 1], tb, &pc, s_removed, lack, D, committed, st_evals, st_place, lane, dirty_unused, upd_unused);
         if (have_next) store_node(ws2[(c + 1) & 1].nd, nr, next_i, lane);
         __syncwarp();
     }
@@ -904,18 +941,133 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
 constexpr size_t SWEEP_DYN_MAX = 160 * 1024;
 constexpr size_t SWEEP_CHUNK_BYTES = (size_t)RUN_CACHE * 32 * (8 + 8 + 8 + 4 + 4);
 
+// ------------------------------------------------------------------------------------------------------------
+// The sweep as parallel waves (cooperative launch, one warp per node, grid = one resident wave of CTAs).
+//   wave over nodes [a, a + warps):  phase 1  every warp processes its node against the exact lacking vector without
+//                                             writing anything (M_SPEC) and reports whether the node would change the vector;
+//                                    grid sync
+//                                    phase 2  f = first such node.  Nodes a..f saw the vector they would have seen in the
+//                                             sequential sweep: the clean ones write their rows, node f is processed again
+//                                             on the real state (M_COMMIT: removed-set and vector updated); nodes > f are
+//                                             dropped and start the next wave.
+//                                    grid sync
+// Exact by construction: a node's decisions depend on earlier nodes only through the lacking vector (the gate is vacuous
+// for consistent node accounts, see fast_applicable), and the reference's loop exit (planner.go:94-97) is the wave loop's.
+__global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_waves(DevProblem pb) {
+    __shared__ Tables tb;
+    __shared__ WarpScratch ws_all[4];
+    __shared__ RunRec s_runs[RUN_CACHE];
+    __shared__ int s_choff[RUN_CACHE];
+    __shared__ unsigned long long s_masks[KP + 1];
+    __shared__ int s_cnt[4];
+    if (__ldcg(&pb.wave[0]) == 0) return;                     // k_plan_sweep kept the plan (same verdict in every CTA)
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    load_tables(pb, tb, tid, blockDim.x);
+    PodCache pc;
+    pc.cpu = nullptr; pc.mem = nullptr; pc.eph = nullptr; pc.key = nullptr; pc.flag = nullptr;
+    pc.runs = s_runs; pc.chunk_off = s_choff; pc.n_cached = min(pb.n_runs, RUN_CACHE); pc.prof_runs = s_masks;
+    for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
+    __syncthreads();
+    build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
+    {   // len(GetCandidateNodes()) for the stats; first-change slots start at "none"
+        int c = 0;
+        for (int i = blockIdx.x * blockDim.x + tid; i < pb.N; i += gridDim.x * blockDim.x) c += pb.cand_flag[i] != 0;
+        c = __reduce_add_sync(FULL, c);
+        if (lane == 0) s_cnt[warp] = c;
+        __syncthreads();
+        if (tid == 0) {
+            atomicAdd(&pb.wave[3], s_cnt[0] + s_cnt[1] + s_cnt[2] + s_cnt[3]);
+            if (blockIdx.x == 0) { pb.wave[1] = INT_MAX; pb.wave[2] = INT_MAX; }
+        }
+    }
+    grid.sync();
+
+    WarpScratch& ws = ws_all[warp];
+    const int total_warps = gridDim.x * (blockDim.x >> 5), gw = blockIdx.x * (blockDim.x >> 5) + warp;
+    long long st_evals = 0, st_place = 0, st_visited = 0, D = 0;
+    bool committed = true;
+    int a = 0, n_waves = 0;
+    for (;;) {
+        const int lack = (lane < KP) ? __ldcg(&pb.lack[lane]) : 0;
+        if (a >= pb.N || __ballot_sync(FULL, lack > 0) == 0) break;          // planner.go:94-97
+        int32_t* first_change = &pb.wave[1 + (n_waves & 1)];
+        // ---- phase 1
+        const int i = a + gw;
+        const bool have = i < pb.N && pb.cand_flag[i];
+        int dirty = 0, added = 0, lk = lack;
+        bool upd = false;
+        long long ev = 0, pl = 0;
+        NodeRegs nr;
+        if (have) {
+            load_node(pb, i, lane, nr);
+            store_node(ws.nd, nr, i, lane);
+            __syncwarp();
+            added = process_node<M_SPEC>(pb, ws, tb, &pc, pb.placed, lk, D, committed, ev, pl, lane, dirty, upd);
+            if (dirty && lane == 0) atomicMin(first_change, i);
+        }
+        grid.sync();
+        // ---- phase 2
+        const int f = __ldcg(first_change);
+        const int last_valid = min(f, a + total_warps - 1);
+        if (have && i <= last_valid) {
+            if (i == f) {
+                store_node(ws.nd, nr, i, lane);                              // phase 1 moved devices around in the copy
+                __syncwarp();
+                ev = 0; pl = 0; lk = lack;
+                int d2 = 0;
+                process_node<M_COMMIT>(pb, ws, tb, &pc, pb.placed, lk, D, committed, ev, pl, lane, d2, upd);
+                if (lane < KP) pb.lack[lane] = lk;
+            } else if (added > 0 && upd && lane < ws.nd.ng) {                // partitioningState[n] = GetPartitioning(n) (planner.go:138)
+                const int x = i * pb.G + lane;
+                pb.out_count[x] = add_bytes(ws.nd.used[lane], ws.nd.free_[lane]);
+                pb.out_mask[x] = ws.nd.umask[lane] | ws.nd.fmask[lane];
+            }
+            ++st_visited; st_evals += ev; st_place += pl;
+        }
+        if (gw == 0 && lane == 0) pb.wave[1 + ((n_waves + 1) & 1)] = INT_MAX; // the other slot, last read one wave ago
+        a = last_valid + 1;
+        ++n_waves;
+        grid.sync();
+    }
+    if (lane == 0 && st_visited) {
+        atomicAdd(&pb.acc[0], (unsigned long long)st_place);
+        atomicAdd(&pb.acc[1], (unsigned long long)st_evals);
+        atomicAdd(&pb.acc[2], (unsigned long long)st_visited);
+    }
+    grid.sync();
+    if (gw == 0) {
+        const int le = (lane < KP) ? __ldcg(&pb.lack[lane]) : 0;
+        const int lack_end = __popc(__ballot_sync(FULL, le > 0));
+        if (lane == 0) {
+            DevStats* st = pb.stats;
+            st->visited_nodes = (long long)__ldcg(&pb.acc[2]);
+            st->candidates = st->visited_nodes * pb.P;
+            st->geometry_evals = (long long)__ldcg(&pb.acc[1]);
+            st->placements = (long long)__ldcg(&pb.acc[0]);
+            st->candidate_nodes = __ldcg(&pb.wave[3]);
+            st->lacking_at_end = lack_end;
+            st->path = 0;
+            st->pad = n_waves;
+        }
+    }
+}
+
 size_t sweep_dyn_smem(const DevProblem& pb) { return SWEEP_CHUNK_BYTES + (size_t)((pb.n_keys + 31) / 32) * 4 + 16; }
 
 // largest number of tracker keys (distinct namespace/name of pending pods) the shared-memory bitmap can hold
 int sweep_max_keys() { return (int)((SWEEP_DYN_MAX - SWEEP_CHUNK_BYTES - 16) / 4) * 32; }
 
-static int g_par_blocks = 148 * 4;
+static int g_par_blocks = 148 * 4, g_wave_blocks = 148 * 4;
 
 cudaError_t sweep_prepare_device() {
     int dev = 0, sms = 148, per_sm = 4;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_plan_parallel, 128, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
     g_par_blocks = sms * per_sm;                               // one resident wave, grid-stride over the nodes
+    int per_sm_w = 4;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_w, k_plan_waves, 128, 0) != cudaSuccess || per_sm_w < 1) per_sm_w = 2;
+    g_wave_blocks = sms * per_sm_w;                            // cooperative launch: every CTA must be resident
     return cudaFuncSetAttribute(k_plan_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SWEEP_DYN_MAX);
 }
 
@@ -949,6 +1101,16 @@ void launch_shard_combine(const DevProblem& pb, const void* gathered, int world,
     const int words = (pb.n_keys + 31) / 32;
     const int n = words > 4 ? words : 4;
     k_shard_combine<<<(n + 255) / 256, 256, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world, stride, wait);
+}
+
+// always queued behind k_plan_sweep for problems the waves can take; returns at once unless k_plan_sweep handed over
+cudaError_t launch_waves(const DevProblem& pb, cudaStream_t st) {
+    if (!pb.fast_eligible || pb.N == 0 || pb.P == 0 || pb.slice_mode) return cudaSuccess;
+    int blocks = (pb.N + 3) / 4;
+    if (blocks > g_wave_blocks) blocks = g_wave_blocks;
+    DevProblem arg = pb;
+    void* args[] = {&arg};
+    return cudaLaunchCooperativeKernel((const void*)k_plan_waves, dim3(blocks), dim3(128), args, 0, st);
 }
 
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st) {

