@@ -651,12 +651,21 @@ static int run_post(nosplan* h) {
     launch_tracker_init(h->pb, h->stream);
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[7], h->stream));
     CU(h, cudaGetLastError());
-    CU(h, launch_parallel(h->pb, h->stream));
-    if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
-    CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
-    CU(h, launch_waves(h->pb, h->stream));
+    // single GPU: where the node-parallel pass can run at all, its last CTA verifies it and k_plan_waves (which returns at
+    // once when the pass stands) holds both fallbacks; other problems go straight to k_plan_sweep
+    const bool work = h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0;
+    if (work) {
+        DevProblem p2 = h->pb;
+        p2.verify_inline = 1;
+        CU(h, launch_parallel(p2, h->stream));
+        if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
+        CU(h, launch_waves(p2, h->stream));
+    } else {
+        if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
+        CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
+    }
     CU(h, cudaEventRecord(h->ev[3], h->stream));
-    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + 2 * (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
+    h->launches = (h->pb.N > 0) + (h->pb.P > 0) + 1 + (work ? 1 : 0);
     h->ran = true;
     return NOSPLAN_OK;
 }

@@ -125,6 +125,7 @@ struct DevProblem {
     int32_t* wave;                   // [8]  [0] k_plan_sweep hands the plan to k_plan_waves  [1],[2] first node of the wave that changes
                                      //      the lacking vector (by wave parity)  [3] candidate nodes  [4] waves run
     int whole_snapshot;              // the node-parallel pass covers every node on this rank (no exchange needed)
+    int verify_inline;               // single GPU: the last CTA of k_plan_parallel verifies the pass itself (else k_plan_sweep does)
     // outputs
     uint4* out_count;                // [N*G]
     uint16_t* out_mask;              // [N*G]

@@ -707,7 +707,10 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     cudaGridDependencySynchronize();
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
     const bool applicable = fast_applicable(pb, lack0, lane);
-    if (!applicable && !pb.xf_on) return;
+    if (!applicable) {
+        if (pb.verify_inline && blockIdx.x == 0 && tid == 0) pb.wave[0] = 2;     // k_plan_waves takes the plan from here
+        if (!pb.xf_on) return;
+    }
 
     WarpScratch& ws = ws_all[warp];
     int lack = lack0 > 0 ? SATURATED : 0;
@@ -734,6 +737,27 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
         atomicAdd(&pb.acc[0], (unsigned long long)st_place);
         atomicAdd(&pb.acc[1], (unsigned long long)st_evals);
         atomicAdd(&pb.acc[2], (unsigned long long)visited);
+    }
+    // single GPU: the CTA that finishes last verifies the saturation hypothesis on the final lacking vector (what
+    // k_plan_sweep does for the sharded drivers) and either publishes the counters or hands the plan to k_plan_waves
+    if (pb.verify_inline && applicable && last_block_done(&pb.next_node[2]) && warp == 0) {
+        const int le = lack0 - ((lane < KP) ? __ldcg(&pb.lack_dec[lane]) : 0);
+        const bool ok = fast_applicable(pb, lack0 > 0 ? le : 0, lane) && __all_sync(FULL, !(lane < KP && lack0 > 0) || le > 0);
+        const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0)), lack_end = __popc(__ballot_sync(FULL, le > 0));
+        if (lane == 0) {
+            if (ok) {
+                DevStats* st = pb.stats;
+                const long long vis = (long long)__ldcg(&pb.acc[2]);
+                st->visited_nodes = vis;
+                st->candidates = vis * pb.P;
+                st->geometry_evals = (long long)__ldcg(&pb.acc[1]);
+                st->placements = (long long)__ldcg(&pb.acc[0]);
+                st->candidate_nodes = vis;
+                st->lacking_at_start = lack_start;
+                st->lacking_at_end = lack_end;
+                st->path = 1;
+            } else pb.wave[0] = 2;
+        }
     }
     // slice mode, fused exchange 2: the CTA that finishes last pushes this rank's counters and placed-key bitmap (pb.acc and
     // pb.placed point into the exchange block) into every rank's mailbox -- also when the pass did not apply (all zero)
@@ -960,7 +984,8 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_waves(DevProblem p
     __shared__ int s_choff[RUN_CACHE];
     __shared__ unsigned long long s_masks[KP + 1];
     __shared__ int s_cnt[4];
-    if (__ldcg(&pb.wave[0]) == 0) return;                     // k_plan_sweep kept the plan (same verdict in every CTA)
+    const int mode = __ldcg(&pb.wave[0]);
+    if (mode == 0) return;                                    // the node-parallel pass stands (same verdict in every CTA)
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     load_tables(pb, tb, tid, blockDim.x);
@@ -970,6 +995,26 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_waves(DevProblem p
     for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
     __syncthreads();
     build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
+    const int lack0 = (lane < KP) ? pb.lack[lane] : 0;        // the vector at t0: nothing on this path has touched it yet
+    const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0));
+    bool as_waves = true;
+    if (mode == 2) {
+        // the node-parallel pass was rejected or did not apply (single-GPU driver): drop whatever it wrote, then choose
+        // between waves and the single-warp chain exactly as k_plan_sweep does for the sharded drivers
+        const int gtid = blockIdx.x * blockDim.x + tid, gthreads = gridDim.x * blockDim.x;
+        for (int x = gtid; x < pb.N * pb.G; x += gthreads) {
+            const int i = x / pb.G, j = x - i * pb.G;
+            if (j < pb.node_gpu_count[i]) {
+                pb.out_count[x] = add_bytes(pb.gpu_used[x], pb.gpu_free[x]);
+                pb.out_mask[x] = pb.gpu_umask[x] | pb.gpu_fmask[x];
+            }
+        }
+        for (int w = gtid; w < (pb.n_keys + 31) / 32; w += gthreads) pb.placed[w] = 0;
+        if (gtid < 4) pb.acc[gtid] = 0;
+        long long total = 0;
+        for (int p = 0; p < KP; ++p) total += max(0, __shfl_sync(FULL, lack0, p));
+        as_waves = pb.gflags[0] == 0 && lack_start > 0 && total * 45 < (long long)pb.N * 17;
+    }
     {   // len(GetCandidateNodes()) for the stats; first-change slots start at "none"
         int c = 0;
         for (int i = blockIdx.x * blockDim.x + tid; i < pb.N; i += gridDim.x * blockDim.x) c += pb.cand_flag[i] != 0;
@@ -978,10 +1023,38 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_waves(DevProblem p
         __syncthreads();
         if (tid == 0) {
             atomicAdd(&pb.wave[3], s_cnt[0] + s_cnt[1] + s_cnt[2] + s_cnt[3]);
-            if (blockIdx.x == 0) { pb.wave[1] = INT_MAX; pb.wave[2] = INT_MAX; }
+            if (blockIdx.x == 0) { pb.wave[1] = INT_MAX; pb.wave[2] = INT_MAX; pb.stats->lacking_at_start = lack_start; }
         }
     }
     grid.sync();
+
+    if (!as_waves) {
+        // ---- the chain: one warp, nodes in name order, exact lacking vector, gate and removed-set as in k_plan_sweep (the
+        //      removed-set lives in global memory here)
+        if (blockIdx.x != 0 || warp != 0) return;
+        WarpScratch& cw = ws_all[0];
+        int lack = lack0, dirty_unused = 0;
+        long long D = (lane < KP) ? pb.tot[lane] : 0, vis = 0, ev = 0, pl = 0;
+        bool committed = false, upd_unused = false;
+        for (int i = 0; i < pb.N && lack_start > 0; ++i) {
+            if (!pb.cand_flag[i]) continue;
+            if (__ballot_sync(FULL, lack > 0) == 0) break;         // planner.go:94-97
+            NodeRegs nr;
+            load_node(pb, i, lane, nr);
+            store_node(cw.nd, nr, i, lane);
+            __syncwarp();
+            ++vis;
+            process_node<M_SEQ>(pb, cw, tb, &pc, pb.placed, lack, D, committed, ev, pl, lane, dirty_unused, upd_unused);
+        }
+        const int lack_end = __popc(__ballot_sync(FULL, lack > 0));
+        if (lane == 0) {
+            DevStats* st = pb.stats;
+            st->visited_nodes = vis; st->candidates = vis * pb.P; st->geometry_evals = ev; st->placements = pl;
+            st->candidate_nodes = lack_start > 0 ? __ldcg(&pb.wave[3]) : 0;   // not reached on the early return (planner.go:80-83)
+            st->lacking_at_start = lack_start; st->lacking_at_end = lack_end; st->path = 0;
+        }
+        return;
+    }
 
     WarpScratch& ws = ws_all[warp];
     const int total_warps = gridDim.x * (blockDim.x >> 5), gw = blockIdx.x * (blockDim.x >> 5) + warp;
