@@ -21,7 +21,7 @@ def main(rep, so, kernel, cubin_key, top=40):
         m = re.match(r"\s*/\*([0-9a-f]{4,})\*/", l)
         if m:
             off2line[int(m.group(1), 16)] = cur
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kernel], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     hdr = rows[1]
     ie, ss = hdr.index("Instructions Executed"), hdr.index("# Samples")
