@@ -44,6 +44,9 @@ struct DevQuota {
     long long* guaranteed; uint8_t* prefilter; uint8_t* over_quota; long long* operator_used; int32_t* ambiguous;
     // labelling work
     unsigned long long *key_a, *key_b; int32_t *val_a, *val_b; int32_t* seg_count; int32_t* seg_off;
+    int32_t* chunk_off;        // [E+1] first 256-pod chunk of each quota's segment
+    long long* chunk_sum;      // [chunks][QR] column sums of a chunk, then (in place) the running sum before the chunk
+    int n_chunk_bound;
 };
 
 __device__ __forceinline__ long long go_int64(double x) {       // int64(f) as compiled for amd64 (CVTTSD2SQ)
@@ -199,6 +202,7 @@ __global__ void __launch_bounds__(256) k_label_rekey(DevQuota q, const int32_t* 
         if (e >= 0) atomicAdd(&q.seg_count[e], 1); else q.over_quota[i] = 0;
     }
 }
+constexpr int LABEL_CHUNK = 256;                               // pods per chunk of the labelling scan == its block size
 __global__ void k_label_offsets(DevQuota q) {                  // exclusive scan of the per-quota counts (single thread block)
     __shared__ int s_carry;
     if (threadIdx.x == 0) s_carry = 0;
@@ -221,6 +225,28 @@ __global__ void k_label_offsets(DevQuota q) {                  // exclusive scan
         __syncthreads();
     }
     if (threadIdx.x == 0) q.seg_off[q.E] = s_carry;
+    __syncthreads();
+    // the same again for the number of 256-pod chunks of each segment
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < q.E; base += blockDim.x) {
+        const int e = base + threadIdx.x;
+        const int cnt = e < q.E ? (q.seg_count[e] + LABEL_CHUNK - 1) / LABEL_CHUNK : 0;
+        __shared__ int s2[256];
+        s2[threadIdx.x] = cnt;
+        __syncthreads();
+        for (int o = 1; o < (int)blockDim.x; o <<= 1) {
+            const int v = threadIdx.x >= o ? s2[threadIdx.x - o] : 0;
+            __syncthreads();
+            s2[threadIdx.x] += v;
+            __syncthreads();
+        }
+        if (e < q.E) q.chunk_off[e] = s_carry + s2[threadIdx.x] - cnt;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) s_carry += s2[threadIdx.x];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) q.chunk_off[q.E] = s_carry;
 }
 
 __device__ __forceinline__ long long quota_req_scalar(const DevQuota& q, int i, int c) {   // one column, thread-serial
@@ -263,18 +289,24 @@ __global__ void __launch_bounds__(256) k_label_ties(DevQuota q, int32_t* order) 
         for (int j = i + 1; j < end; ++j) { bool t = false; tie_less(q, order[i], order[j], &t); amb |= t; }
     if (amb) *q.ambiguous = 1;
 }
-// one block per quota: running sum of the requests in order, in-quota iff used <= min on every key of Min
-__global__ void __launch_bounds__(256) k_label_scan(DevQuota q, const int32_t* order) {
-    __shared__ long long s_warp[8][QR];
-    __shared__ long long s_carry[QR];
-    const int e = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int beg = q.seg_off[e], end = q.seg_off[e + 1];
-    const unsigned mm = q.min_mask[e];
-    if (tid < QR) s_carry[tid] = 0;
-    __syncthreads();
-    for (int base = beg; base < end; base += blockDim.x) {
-        const int x = base + tid;
-        const int i = x < end ? order[x] : -1;
+// The running sum of the requests of one quota's pods in order, in-quota iff used <= min on every key of Min
+// (elasticquota.go:44-60), as a chunked scan so that a quota with tens of thousands of pods does not serialise on one CTA:
+//   k_label_chunks(apply = 0)  one CTA per 256-pod chunk of a quota's segment: column sums of the chunk
+//   k_label_chunk_prefix       one warp per quota (lane = column): running sum before each of its chunks; final sum = status.used
+//   k_label_chunks(apply = 1)  the same CTAs again: scan inside the chunk on top of that prefix, compare with Min, write the label
+__device__ __forceinline__ int label_chunk_quota(const DevQuota& q, int chunk) {   // largest e with chunk_off[e] <= chunk
+    int lo = 0, hi = q.E;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (q.chunk_off[mid] <= chunk) lo = mid; else hi = mid; }
+    return lo;
+}
+__global__ void __launch_bounds__(LABEL_CHUNK) k_label_chunks(DevQuota q, const int32_t* order, int apply) {
+    __shared__ long long s_warp[LABEL_CHUNK / 32][QR];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int chunk = blockIdx.x; chunk < q.chunk_off[q.E]; chunk += gridDim.x) {
+        const int e = label_chunk_quota(q, chunk);
+        const int x = q.seg_off[e] + (chunk - q.chunk_off[e]) * LABEL_CHUNK + tid;
+        const int i = x < q.seg_off[e + 1] ? order[x] : -1;
+        const unsigned mm = q.min_mask[e];
         long long v[QR];
 #pragma unroll
         for (int c = 0; c < QR; ++c) v[c] = (i >= 0 && c < q.R) ? quota_req_scalar(q, i, c) : 0;
@@ -289,23 +321,36 @@ __global__ void __launch_bounds__(256) k_label_scan(DevQuota q, const int32_t* o
             if (lane == 31) s_warp[warp][c] = v[c];
         }
         __syncthreads();
-        bool in_quota = true;
+        if (!apply) {
+            if (tid < q.R) {
+                long long t = 0;
+                for (int w = 0; w < LABEL_CHUNK / 32; ++w) t += s_warp[w][tid];
+                q.chunk_sum[(size_t)chunk * QR + tid] = t;
+            }
+        } else {
+            bool in_quota = true;
 #pragma unroll
-        for (int c = 0; c < QR; ++c) {
-            long long pre = s_carry[c];
-            for (int w = 0; w < warp; ++w) pre += s_warp[w][c];
-            v[c] += pre;
-            if (c < q.R && (mm >> c & 1) && v[c] > q.qmin[(size_t)e * q.R + c]) in_quota = false;
-        }
-        if (i >= 0) q.over_quota[i] = in_quota ? 0 : 1;
-        __syncthreads();
-        if (tid == blockDim.x - 1) {
-#pragma unroll
-            for (int c = 0; c < QR; ++c) s_carry[c] = v[c];
+            for (int c = 0; c < QR; ++c) {
+                if (c >= q.R) break;
+                long long pre = q.chunk_sum[(size_t)chunk * QR + c];
+                for (int w = 0; w < warp; ++w) pre += s_warp[w][c];
+                if ((mm >> c & 1) && v[c] + pre > q.qmin[(size_t)e * q.R + c]) in_quota = false;
+            }
+            if (i >= 0) q.over_quota[i] = in_quota ? 0 : 1;
         }
         __syncthreads();
     }
-    if (tid < q.R) q.operator_used[(size_t)e * q.R + tid] = (mm >> tid & 1) ? s_carry[tid] : 0;
+}
+__global__ void __launch_bounds__(256) k_label_chunk_prefix(DevQuota q) {
+    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), c = threadIdx.x & 31;
+    if (e >= q.E || c >= q.R) return;
+    long long run = 0;
+    for (int chunk = q.chunk_off[e]; chunk < q.chunk_off[e + 1]; ++chunk) {
+        const long long t = q.chunk_sum[(size_t)chunk * QR + c];
+        q.chunk_sum[(size_t)chunk * QR + c] = run;
+        run += t;
+    }
+    q.operator_used[(size_t)e * q.R + c] = (q.min_mask[e] >> c & 1) ? run : 0;
 }
 
 }  // namespace nsp
@@ -350,7 +395,9 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
                  o_amb = put(16);
     const size_t out_end = o;
     const size_t o_keya = put(8 * (size_t)Pr), o_keyb = put(8 * (size_t)Pr), o_vala = put(4 * (size_t)Pr), o_valb = put(4 * (size_t)Pr),
-                 o_segc = put(4 * ((size_t)E + 1)), o_sego = put(4 * ((size_t)E + 2));
+                 o_segc = put(4 * ((size_t)E + 1)), o_sego = put(4 * ((size_t)E + 2)), o_choff = put(4 * ((size_t)E + 2));
+    const int n_chunk_bound = Pr / 256 + E + 1;                 // every quota's last chunk may be partial
+    const size_t o_chsum = put(8 * (size_t)n_chunk_bound * QR);
     size_t cub_bytes = 0;
     if (want_label) {
         cub::DoubleBuffer<unsigned long long> dk(nullptr, nullptr); cub::DoubleBuffer<int32_t> dv(nullptr, nullptr);
@@ -397,6 +444,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     q.key_a = (unsigned long long*)(A + o_keya); q.key_b = (unsigned long long*)(A + o_keyb);
     q.val_a = (int32_t*)(A + o_vala); q.val_b = (int32_t*)(A + o_valb);
     q.seg_count = (int32_t*)(A + o_segc); q.seg_off = (int32_t*)(A + o_sego);
+    q.chunk_off = (int32_t*)(A + o_choff); q.chunk_sum = (long long*)(A + o_chsum); q.n_chunk_bound = n_chunk_bound;
 
     int n_launch = 0;
     // Used starts from used_init (scalar key set from used_mask)
@@ -428,8 +476,11 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, ebits, st));
         k_label_offsets<<<1, 256, 0, st>>>(q);
         k_label_ties<<<gb, 256, 0, st>>>(q, dv.Current());
-        k_label_scan<<<E, 256, 0, st>>>(q, dv.Current());
-        n_launch += 9;
+        const int cgrid = std::min(n_chunk_bound, 148 * 8);
+        k_label_chunks<<<cgrid, LABEL_CHUNK, 0, st>>>(q, dv.Current(), 0);
+        k_label_chunk_prefix<<<(E + 7) / 8, 256, 0, st>>>(q);
+        k_label_chunks<<<cgrid, LABEL_CHUNK, 0, st>>>(q, dv.Current(), 1);
+        n_launch += 11;
     }
     QCU(cudaGetLastError());
     QCU(cudaEventRecord(ev[2], st));
