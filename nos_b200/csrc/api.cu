@@ -297,6 +297,7 @@ void nosplan_destroy(nosplan_t* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : h->dbg_ev) if (e) cudaEventDestroy(e);
     if (h->d_arena) cudaFree(h->d_arena);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->h_out) cudaFreeHost(h->h_out);

@@ -50,6 +50,15 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int node0 = tile * PRE_NODES;
         const int rows = PRE_NODES * G;
+        // the int64 account columns of phase 2 do not depend on phase 1: issue their loads now, both round trips overlap
+        long long pa[PRE_NODES * KP / 256], pr_[PRE_NODES * KP / 256];
+#pragma unroll
+        for (int u = 0; u < PRE_NODES * KP / 256; ++u) {
+            const int i = node0 + (tid + u * 256) / KP;
+            const bool on = i < pb.N && my_p < K;
+            pa[u] = on ? pb.node_alloc[(size_t)i * pb.R + 3 + my_p] : 0;
+            pr_[u] = on ? pb.node_req[(size_t)i * pb.R + 3 + my_p] : 0;
+        }
         // ---- phase 1: one thread per GPU row, consecutive threads read consecutive rows (128-bit loads)
         for (int r = tid; r < rows; r += blockDim.x) {
             const int nl = r / G, j = r - nl * G, i = node0 + nl;
@@ -93,11 +102,12 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
             pb.cand_flag[node0 + tid] = any;
         }
         // ---- phase 2b: (node, profile) pairs: totals, largest free count, node accounts vs GPU maps
-        for (int pr = tid; pr < PRE_NODES * KP; pr += blockDim.x) {
+#pragma unroll
+        for (int u = 0; u < PRE_NODES * KP / 256; ++u) {
+            const int pr = tid + u * 256;
             const int nl = pr / KP, i = node0 + nl;          // pr % KP == my_p
             if (i >= pb.N || my_p >= K) continue;
-            const size_t o = (size_t)i * pb.R + 3 + my_p;
-            const long long a = pb.node_alloc[o], r = pb.node_req[o];
+            const long long a = pa[u], r = pr_[u];
             acc += a - r;
             int sum_free = 0, sum_used = 0;
             const uint8_t* fb = reinterpret_cast<const uint8_t*>(s_free + nl * G) + my_p;
@@ -155,6 +165,13 @@ __global__ void __launch_bounds__(256) k_tracker_init(DevProblem pb) {
     cudaTriggerProgrammaticLaunchCompletion();
     if (threadIdx.x < KP) s_lack[threadIdx.x] = 0;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    // the pod's own data was uploaded, not computed: fetch it while k_prepass is still finishing
+    int key = 0, e0 = 0, e1 = 0, col0 = 0;
+    long long qty0 = 0;
+    if (s < pb.P) {
+        key = pb.pod_key[s]; e0 = pb.pod_sptr[s]; e1 = pb.pod_sptr[s + 1];
+        if (e0 < e1) { col0 = pb.pod_scol[e0]; qty0 = pb.pod_sqty[e0]; }
+    }
     cudaGridDependencySynchronize();                     // the totals of k_prepass (and the work-area reset before it)
     if (pb.xf_on) {
         // slice mode, fused exchange 1: wait for every rank's totals in this rank's mailbox and fold them (each CTA for itself;
@@ -186,14 +203,13 @@ __global__ void __launch_bounds__(256) k_tracker_init(DevProblem pb) {
     } else if (threadIdx.x < KP) s_tot[threadIdx.x] = pb.tot[threadIdx.x];
     __syncthreads();
     if (s < pb.P) {
-        const int key = pb.pod_key[s];
-        for (int e = pb.pod_sptr[s]; e < pb.pod_sptr[s + 1]; ++e) {
-            const int col = pb.pod_scol[e];
+        for (int e = e0; e < e1; ++e) {
+            const int col = e == e0 ? col0 : pb.pod_scol[e];
             if (col >= 3 + pb.K) break;              // columns ascend: slice columns come first
             const int p = col - 3;
             long long avail = s_tot[p];
             if (avail < 0) avail = 0;                 // SubtractNonNegative (pkg/resource/resource.go:76-88)
-            const long long diff = avail - pb.pod_sqty[e];
+            const long long diff = avail - (e == e0 ? qty0 : pb.pod_sqty[e]);
             if (diff < 0) {
                 const int l = (int)(-diff);
                 atomicAdd(&pb.entry_lack[(size_t)key * KP + p], l);

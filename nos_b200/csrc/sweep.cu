@@ -977,7 +977,7 @@ constexpr size_t SWEEP_CHUNK_BYTES = (size_t)RUN_CACHE * 32 * (8 + 8 + 8 + 4 + 4
 //                                    grid sync
 // Exact by construction: a node's decisions depend on earlier nodes only through the lacking vector (the gate is vacuous
 // for consistent node accounts, see fast_applicable), and the reference's loop exit (planner.go:94-97) is the wave loop's.
-__global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_waves(DevProblem pb) {
+__global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
     __shared__ Tables tb;
     __shared__ WarpScratch ws_all[4];
     __shared__ RunRec s_runs[RUN_CACHE];
