@@ -11,6 +11,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "nosplan_dev.cuh"
@@ -334,7 +335,17 @@ int nosplan_host_pod_order(const nosplan_snapshot* s, const nosplan_pods* pods, 
 // is queued, so they run while the host is still ordering the pods.
 static int run_pre(nosplan* h, bool split) {
     CU(h, cudaEventRecord(h->ev[2], h->stream));
-    CU(h, cudaMemsetAsync(h->d_work, 0, h->work_bytes, h->stream));
+    {   // this run's copy of the small state; k_prepass clears the other copy and the tracker tables
+        DevProblem& pb = h->pb;
+        const unsigned use = h->run_parity ^= 1u;
+        const ptrdiff_t to_use = (ptrdiff_t)(use ? h->small_bytes : 0) - (ptrdiff_t)(h->bound_copy ? h->small_bytes : 0);
+        auto move = [&](auto*& p) { p = reinterpret_cast<std::remove_reference_t<decltype(p)>>(reinterpret_cast<unsigned char*>(p) + to_use); };
+        move(pb.tot); move(pb.lack); move(pb.stats); move(pb.maxfree); move(pb.gflags); move(pb.acc); move(pb.lack_dec);
+        move(pb.next_node); move(pb.wave);
+        h->bound_copy = use;
+        pb.zero_next = reinterpret_cast<unsigned long long*>(h->d_work + (use ? 0 : h->small_bytes));
+        pb.zero_next_n8 = (int)(h->small_bytes >> 3);
+    }
     launch_prepass(h->pb, h->stream);
     if (split || h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
     CU(h, cudaGetLastError());
@@ -402,8 +413,12 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     put(L.node_alloc, 8 * (size_t)N * R); put(L.node_req, 8 * (size_t)N * R);
     put(L.node_allowed, 4 * (size_t)N); put(L.node_npods, 4 * (size_t)N);
     L.nodes_end = o;
+    // small per-run state, twice: run k works in copy k & 1 while its k_prepass clears the other one for run k + 1, so no
+    // reset is queued in front of a run (the large tracker tables below are cleared by k_prepass for its own run)
     put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats));
     put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.lack_dec, 4 * KP); put(L.next_node, 16); put(L.wave, 32);
+    const size_t small_bytes = o - L.tot;
+    o += small_bytes;                                        // the second copy
     put(L.placed, 4 * (((size_t)P + 31) / 32));             // tracker tables: sized for P keys (keys <= P), reset with the rest
     put(L.entry_lack, 4 * (size_t)P * KP);
     L.work_end = o;
@@ -467,7 +482,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         if (L.nodes_end > from) CU(h, cudaMemcpyAsync(A + from, S + from, L.nodes_end - from, cudaMemcpyHostToDevice, h->stream));
     }
     h->direct_h2d = any_direct;
-    CU(h, cudaMemsetAsync(A + L.out_count, 0, L.out_end - L.out_count, h->stream));
+    CU(h, cudaMemsetAsync(A + L.tot, 0, L.out_end - L.tot, h->stream));       // per-run state (both copies) ... plan rows
     CU(h, cudaEventRecord(h->ev[1], h->stream));
 
     // ---- device problem description, node side
@@ -493,7 +508,8 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     pb.cand_flag = (uint8_t*)(A + L.cand_flag);
     pb.out_count = (uint4*)(A + L.out_count); pb.out_mask = (uint16_t*)(A + L.out_mask);
     h->d_cand_idx = (int32_t*)(A + L.cand_idx);
-    h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot;
+    h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot; h->small_bytes = small_bytes;
+    h->run_parity = 1; h->bound_copy = 0;                    // pb points at copy 0; the first run flips to it
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
     if (h->in_plan) { rc = run_pre(h, true); if (rc != NOSPLAN_OK) return rc; }
     lap("nodes queued");

@@ -23,6 +23,7 @@ struct nosplan {
     nsp::DevProblem pb{};
     int32_t* d_cand_idx = nullptr;
     unsigned char* d_work = nullptr; size_t work_bytes = 0;      // totals, lacking vector, counters, tracker tables: reset before k_prepass
+    size_t small_bytes = 0; unsigned run_parity = 1, bound_copy = 0;   // which copy of the small per-run state pb points at
     bool pre_done = false, split_run = false;                    // nosplan_plan queued the node-only kernels from inside upload()
     // host scratch reused across calls
     std::vector<int> v_first_prof, v_order;

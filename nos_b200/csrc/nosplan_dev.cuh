@@ -109,7 +109,9 @@ struct DevProblem {
     PeerBox xf_box;
     unsigned char* xf_exchange;      // this rank's exchange block [4 x u64 counters | placed-key bitmap]
     unsigned long long xf_xb;        // its size in bytes (8-byte granular)
-    // work area (zeroed before each run)
+    // work area.  The small fields exist twice; k_prepass of run k clears the copy of run k + 1 (zero_next) and, for its own
+    // run, the tracker tables (placed, entry_lack), which nothing touches before k_tracker_init
+    unsigned long long* zero_next; int zero_next_n8;
     long long* tot;                  // [KP] sum over nodes of (alloc - requested) per slice column
     int32_t* lack;                   // [KP] SliceTracker.lackingSlices
     int32_t* entry_lack;             // [n_keys][KP] lackingSlicesLookup

@@ -41,6 +41,13 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
     }
     __syncthreads();
 
+    {   // resets (see DevProblem::zero_next): the next run's small state by CTA 0, this run's tracker tables by everybody
+        if (blockIdx.x == 0) for (int x = tid; x < pb.zero_next_n8; x += blockDim.x) pb.zero_next[x] = 0;
+        const size_t gt = (size_t)blockIdx.x * blockDim.x + tid, gn = (size_t)gridDim.x * blockDim.x;
+        uint4* el = reinterpret_cast<uint4*>(pb.entry_lack);
+        for (size_t x = gt; x < (size_t)pb.n_keys * (KP / 4); x += gn) el[x] = make_uint4(0, 0, 0, 0);
+        for (size_t x = gt; x < (size_t)(pb.n_keys + 31) / 32; x += gn) pb.placed[x] = 0;
+    }
     // this thread's profile in phase 2 never changes: (node-in-tile, profile) pairs are laid out 16 profiles per node
     const int my_p = tid & (KP - 1);
     long long acc = 0;
@@ -262,7 +269,7 @@ void launch_prepass(const DevProblem& pb, cudaStream_t st) {
         int blocks = (pb.N + PRE_NODES - 1) / PRE_NODES;      // one tile of 32 nodes per block, grid-stride beyond 8 waves
         if (blocks > 148 * 8) blocks = 148 * 8;
         k_prepass<<<blocks, 256, 0, st>>>(pb);
-    } else if (pb.xf_on) k_prepass<<<1, 256, 0, st>>>(pb);      // fused slice mode: an empty slice still pushes its (zero) totals
+    } else k_prepass<<<1, 256, 0, st>>>(pb);     // no nodes: the resets (and, in fused slice mode, the push of zero totals) still happen
 }
 
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st) {
