@@ -184,3 +184,38 @@ def test_sweep_as_parallel_waves(eng, kind):
             waves_seen += st["waves"] > 0
             assert st["path"] == 1 or st["waves"] > 0 or st["visited_nodes"] * 45 >= 0
     assert waves_seen >= 4
+
+
+def test_compiled_in_limits(eng):
+    """At the limits of include/nosplan.h: 16 profiles, 16 GPUs per node, 32 allowed geometries of one model, 12 non-slice
+    scalar resources -- the wide code paths (4 words of byte-SIMD scoring, 32 geometry lanes per GPU) in every regime."""
+    import random
+    rng = random.Random(7)
+    profiles = [f"{i}g.{2 * i}gb" for i in range(1, 17)]
+    geoms = [{p: rng.randint(1, 7) for p in rng.sample(profiles, rng.randint(1, 4))} for _ in range(32)]
+    geoms[0] = {profiles[-1]: 1}
+    known = {"TEST-GPU": geoms}
+    paths = set()
+    for n_pods, seed in ((3000, 5), (40, 6), (300, 7)):
+        snap, pods = synth.mig_cluster(200, 16, n_pods, seed=seed, model="TEST-GPU", known=known, regime="saturating",
+                                       demand=profiles, demand_probs=[1 / 16] * 16)
+        assert snap.n_profiles == 16 and snap.gpus_per_node == 16 and snap.geom_counts.shape == (32, 16)
+        for fm in (pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT):
+            st = check(eng, snap, pods, None, fm, f"limits {n_pods} fm={fm}")
+            paths.add((st["path"], st["waves"] > 0))
+        # the same with 12 other scalar resources on nodes and on a third of the pods (exact per-pod path)
+        other = [f"example.com/res-{k:02d}" for k in range(12)]
+        snap.other_resources = other
+        N = snap.n_nodes
+        extra_a = np.full((N, 12), 50, np.int64); extra_r = np.zeros((N, 12), np.int64)
+        snap.node_alloc = np.concatenate([snap.node_alloc, extra_a], 1); snap.node_requested = np.concatenate([snap.node_requested, extra_r], 1)
+        K = snap.n_profiles
+        ptr, col, qty = [0], [], []
+        for i in range(pods.n_pods):
+            col.append(int(pods.scalar_col[i])); qty.append(1)
+            if i % 3 == 0:
+                col.append(3 + K + (i % 12)); qty.append(1 + i % 4)
+            ptr.append(len(col))
+        pods.scalar_ptr = np.array(ptr, np.int32); pods.scalar_col = np.array(col, np.int32); pods.scalar_qty = np.array(qty, np.int64)
+        check(eng, snap, pods, None, pk.FILTER_RESOURCES_FIT, f"limits+other {n_pods}")
+    assert (1, False) in paths
