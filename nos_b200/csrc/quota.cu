@@ -47,6 +47,7 @@ struct DevQuota {
     int32_t* chunk_off;        // [E+1] first 256-pod chunk of each quota's segment
     long long* chunk_sum;      // [chunks][QR] column sums of a chunk, then (in place) the running sum before the chunk
     int n_chunk_bound;
+    long long fuse_ts_min, fuse_prio_min; int fuse_tbits, fuse_pbits;   // single-sort labelling (k_label_keys pass 1)
 };
 
 __device__ __forceinline__ long long go_int64(double x) {       // int64(f) as compiled for amd64 (CVTTSD2SQ)
@@ -109,8 +110,9 @@ __global__ void __launch_bounds__(256) k_quota_used(DevQuota q, int use_smem) {
     }
 }
 
-__global__ void __launch_bounds__(256) k_quota_aggregate(DevQuota q) {
-    __shared__ long long s_min[16][QR], s_used[16][QR], s_over[16][QR];
+constexpr int AGG_THREADS = 1024, AGG_ROWS = AGG_THREADS / 16;   // 64 namespaces in flight: the loop is a chain of dependent loads
+__global__ void __launch_bounds__(AGG_THREADS) k_quota_aggregate(DevQuota q) {
+    __shared__ long long s_min[AGG_ROWS][QR], s_used[AGG_ROWS][QR], s_over[AGG_ROWS][QR];
     __shared__ unsigned s_m[3];
     __shared__ long long a_min[QR], a_used[QR], a_over[QR];
     const int tid = threadIdx.x, c = tid & 15, j = tid >> 4;
@@ -118,7 +120,7 @@ __global__ void __launch_bounds__(256) k_quota_aggregate(DevQuota q) {
     __syncthreads();
     long long mn = 0, us = 0, ov = 0;
     unsigned mm = 0, um = 0, om = 0;
-    for (int ns = j; ns < q.NS; ns += 16) {
+    for (int ns = j; ns < q.NS; ns += AGG_ROWS) {
         const int e = q.ns_quota[ns];
         if (e < 0) continue;
         const bool has_min = (q.min_mask[e] & NOSPLAN_QUOTA_NONNIL) != 0;
@@ -137,7 +139,7 @@ __global__ void __launch_bounds__(256) k_quota_aggregate(DevQuota q) {
     __syncthreads();
     if (tid < QR) {
         long long a = 0, b = 0, d = 0;
-        for (int k = 0; k < 16; ++k) { a += s_min[k][tid]; b += s_used[k][tid]; d += s_over[k][tid]; }
+        for (int k = 0; k < AGG_ROWS; ++k) { a += s_min[k][tid]; b += s_used[k][tid]; d += s_over[k][tid]; }
         a_min[tid] = a; a_used[tid] = b; a_over[tid] = d;
         if (tid < q.R) { q.agg_min[tid] = a; q.agg_used[tid] = b; q.agg_over[tid] = d; }
     }
@@ -188,6 +190,16 @@ __global__ void __launch_bounds__(256) k_label_keys(DevQuota q, int pass) {
     if (pass == 0) {                                       // least significant key: priority (biased to unsigned)
         q.key_a[i] = (unsigned long long)((long long)q.r_prio[i] - (long long)INT_MIN);
         q.val_a[i] = i;
+    } else {
+        // all three keys in one word -- quota row | creationTimestamp - min | priority - min -- when their ranges fit 64 bits
+        const int ns = q.r_ns[i];
+        const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+        const unsigned long long ek = e < 0 ? (unsigned long long)q.E : (unsigned long long)e;
+        q.key_a[i] = (ek << (q.fuse_tbits + q.fuse_pbits)) |
+                     ((unsigned long long)(q.r_ts[i] - q.fuse_ts_min) << q.fuse_pbits) |
+                     (unsigned long long)((long long)q.r_prio[i] - q.fuse_prio_min);
+        q.val_a[i] = i;
+        if (e >= 0) atomicAdd(&q.seg_count[e], 1); else q.over_quota[i] = 0;
     }
 }
 __global__ void __launch_bounds__(256) k_label_rekey(DevQuota q, const int32_t* vals, unsigned long long* keys, int pass) {
@@ -459,21 +471,39 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         k_quota_used<<<blocks, 256, use_smem ? tab : 0, st>>>(q, use_smem);
         ++n_launch;
     }
-    k_quota_aggregate<<<1, 256, 0, st>>>(q);
+    k_quota_aggregate<<<1, AGG_THREADS, 0, st>>>(q);
     ++n_launch;
     if (Pp) { k_quota_prefilter<<<(Pp + 15) / 16, 256, 0, st>>>(q); ++n_launch; }
     if (want_label) {
         // stable LSD radix sort: priority, then creationTimestamp, then quota row
         const int gb = (Pr + 255) / 256;
-        k_label_keys<<<gb, 256, 0, st>>>(q, 0);
         cub::DoubleBuffer<unsigned long long> dk(q.key_a, q.key_b); cub::DoubleBuffer<int32_t> dv(q.val_a, q.val_b);
         size_t tb = cub_bytes;
-        QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, 32, st));
-        k_label_rekey<<<gb, 256, 0, st>>>(q, dv.Current(), dk.Current(), 1);
-        QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, 64, st));
-        k_label_rekey<<<gb, 256, 0, st>>>(q, dv.Current(), dk.Current(), 2);
         int ebits = 1; while ((1ll << ebits) <= E) ++ebits;
-        QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, ebits, st));
+        // ranges of the two inner keys (host scan of the caller's arrays): if quota | timestamp | priority fit one 64-bit word
+        // a single radix sort over exactly the bits in use replaces the three stable passes
+        long long tmin = LLONG_MAX, tmax = LLONG_MIN, pmin = LLONG_MAX, pmax = LLONG_MIN;
+        const bool have_keys = running->creation_ts && running->priority;
+        for (int i = 0; have_keys && i < Pr; ++i) {
+            const long long t = running->creation_ts[i], pr = running->priority[i];
+            tmin = std::min(tmin, t); tmax = std::max(tmax, t); pmin = std::min(pmin, pr); pmax = std::max(pmax, pr);
+        }
+        auto bits_of = [](unsigned long long range) { int b = 1; while (b < 64 && (range >> b)) ++b; return b; };
+        const bool ts_ok = have_keys && (unsigned long long)tmax - (unsigned long long)tmin < (1ull << 62);
+        const int tbits = ts_ok ? bits_of((unsigned long long)(tmax - tmin)) : 64, pbits = bits_of((unsigned long long)(pmax - pmin));
+        if (ts_ok && ebits + tbits + pbits <= 64) {
+            q.fuse_ts_min = tmin; q.fuse_prio_min = pmin; q.fuse_tbits = tbits; q.fuse_pbits = pbits;
+            k_label_keys<<<gb, 256, 0, st>>>(q, 1);
+            QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, ebits + tbits + pbits, st));
+            n_launch -= 4;
+        } else {
+            k_label_keys<<<gb, 256, 0, st>>>(q, 0);
+            QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, 32, st));
+            k_label_rekey<<<gb, 256, 0, st>>>(q, dv.Current(), dk.Current(), 1);
+            QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, 64, st));
+            k_label_rekey<<<gb, 256, 0, st>>>(q, dv.Current(), dk.Current(), 2);
+            QCU(cub::DeviceRadixSort::SortPairs(A + o_cub, tb, dk, dv, Pr, 0, ebits, st));
+        }
         k_label_offsets<<<1, 256, 0, st>>>(q);
         k_label_ties<<<gb, 256, 0, st>>>(q, dv.Current());
         const int cgrid = std::min(n_chunk_bound, 148 * 8);

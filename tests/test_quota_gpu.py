@@ -96,3 +96,15 @@ def test_zero_sizes(eng):
     pq, (run,) = qp.pack_quotas({}, [[{"namespace": "a", "name": "p", "request": {"cpu": 1}}]], 16)
     got, _ = eng.quota_recompute(pq, run)
     compare(got, ol.quota(pq, run), "no quotas")
+
+
+def test_labelling_with_key_ranges_beyond_one_word(eng):
+    """creationTimestamps and priorities spanning (almost) their whole types: quota | timestamp | priority no longer fit one
+    64-bit sort key, so the three stable radix passes run instead of the fused one -- same labels either way."""
+    for seed in (3, 11, 42):
+        pq, run, pend = synth.quota_state(40, 3000, 50, seed=seed)
+        i = np.arange(run.n_pods)
+        run.creation_ts = np.where(i % 2 == 0, run.creation_ts - (1 << 61), run.creation_ts + (1 << 61)).astype(np.int64)
+        run.priority = np.where(i % 3 == 0, np.int64(-2**31), np.where(i % 3 == 1, np.int64(2**31 - 1), run.priority)).astype(np.int32)
+        got, _ = eng.quota_recompute(pq, run, pend)
+        compare(got, ol.quota(pq, run, pend), f"wide keys seed {seed}")
