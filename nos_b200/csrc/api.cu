@@ -386,16 +386,6 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         const int c = s->model_geom_offset[m + 1] - s->model_geom_offset[m];
         if (c < 0 || c > NOSPLAN_MAX_GEOMS) return fail(h, NOSPLAN_E_LIMIT, "model %d has %d geometries > NOSPLAN_MAX_GEOMS", m, c);
     }
-    for (int i = 0; i < N; ++i) {
-        const int ng = s->node_gpu_count[i];
-        if (ng < 0 || ng > G) return fail(h, NOSPLAN_E_INVALID, "node %d: gpu count out of range", i);
-        if (mig) {
-            const int32_t* gm = s->gpu_model + (size_t)i * G;
-            unsigned bad = 0;
-            for (int j = 0; j < ng; ++j) bad |= (unsigned)gm[j] >= (unsigned)n_models;
-            if (bad) return fail(h, NOSPLAN_E_INVALID, "node %d: GPU model id out of range", i);
-        }
-    }
     const int nnz = P > 0 ? pods->scalar_ptr[P] : 0;
     if (nnz < 0) return fail(h, NOSPLAN_E_INVALID, "negative scalar entry count");
     lap("validate");
@@ -472,10 +462,16 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
             cudaEventRecord(h->dbg_ev[h->dbg_n], h->stream);
             h->dbg_bytes[h->dbg_n] = bytes; h->dbg_direct[h->dbg_n] = direct; h->dbg_n++;
         };
+        // cudaStreamQuery after each copy pushes it to the copy engine at once (the driver otherwise holds queued copies back for
+        // a while): measured in one session, end to end 0.60 ms without, 0.55 ms with; an event record per copy and alternating
+        // the copies between two streams were both measured slower.  NOSPLAN_COPY_MODE=0 switches the push off.
+        const char* cm = getenv("NOSPLAN_COPY_MODE");
+        const int copy_mode = cm ? atoi(cm) : 1;
         for (const Seg& g : segs) {
             if (!g.direct) continue;
             if (g.off > from) { CU(h, cudaMemcpyAsync(A + from, S + from, g.off - from, cudaMemcpyHostToDevice, h->stream)); mark(g.off - from, false); }
             CU(h, cudaMemcpyAsync(A + g.off, g.src, g.bytes, cudaMemcpyHostToDevice, h->stream));
+            if (copy_mode == 1) (void)cudaStreamQuery(h->stream);
             mark(g.bytes, true);
             from = al(g.off + g.bytes);
         }
@@ -513,6 +509,24 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
     if (h->in_plan) { rc = run_pre(h, true); if (rc != NOSPLAN_OK) return rc; }
     lap("nodes queued");
+    // per-node validation, while the copy engine works (k_prepass, the only kernel that can already be queued, clamps what it
+    // reads; every other kernel is launched after this call has succeeded)
+    for (int i = 0; i < N; ++i) {
+        const int ng = s->node_gpu_count[i];
+        bool bad = ng < 0 || ng > G;
+        if (!bad && mig) {
+            const int32_t* gm = s->gpu_model + (size_t)i * G;
+            unsigned b = 0;
+            for (int j = 0; j < ng; ++j) b |= (unsigned)gm[j] >= (unsigned)n_models;
+            bad = b != 0;
+        }
+        if (bad) {
+            cudaStreamSynchronize(h->stream);                    // nothing of the caller's may be in flight when we return
+            const bool cnt = ng < 0 || ng > G;
+            return fail(h, NOSPLAN_E_INVALID, cnt ? "node %d: gpu count out of range" : "node %d: GPU model id out of range", i);
+        }
+    }
+    lap("validate nodes");
 
     // ---- pods, pass 1 (original order): validation, flags, first requested profile, class key of the slice request
     //      (equal keys <=> identical slice requests; CLS_MULTI = compare the entries)

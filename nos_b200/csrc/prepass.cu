@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
             const int nl = r / G, j = r - nl * G, i = node0 + nl;
             uint4 used = make_uint4(0, 0, 0, 0), fre = used;
             bool has_free = false;
-            if (i < pb.N && j < pb.node_gpu_count[i]) {
+            if (i < pb.N && j < min(pb.node_gpu_count[i], G)) {     // clamped: this kernel may run before the host has validated
                 const int x = i * G + j;
                 used = pb.gpu_used[x]; fre = pb.gpu_free[x];
                 const uint16_t um = pb.gpu_umask[x], fm = pb.gpu_fmask[x];
@@ -82,9 +82,9 @@ __global__ void __launch_bounds__(256) k_prepass(DevProblem pb) {
                 if (mig) {
                     has_free = fm != 0;
                     if (!has_free) {                     // AllowsGeometry(GetGeometry()) (mig/gpu.go:215-222)
-                        const int m = pb.gpu_model[x];
+                        const int m = min(max(pb.gpu_model[x], 0), max(pb.n_models - 1, 0));
                         bool allowed = false;
-                        for (int q = s_off[m]; q < s_off[m + 1]; ++q) {
+                        for (int q = s_off[m]; pb.n_models > 0 && q < s_off[m + 1]; ++q) {
                             const uint4 row = s_geom[q];
                             allowed |= (s_gmask[q] == gm) && row.x == cnt.x && row.y == cnt.y && row.z == cnt.z && row.w == cnt.w;
                         }
