@@ -77,6 +77,20 @@ bool matches_mig_resource(const std::string& r) {
     }
     return false;
 }
+// regexp `\d+g\.\d+gb` (pkg/constant/constants.go:51), unanchored: mig.ProfileName.isValid (pkg/gpu/mig/profile.go:57-59)
+bool matches_mig_profile(const std::string& p) {
+    for (size_t i = 0; i < p.size(); ++i) {
+        size_t d = digits_at(p, i);
+        if (!d) continue;
+        size_t j = i + d;
+        if (p.compare(j, 2, "g.") == 0) {
+            size_t d2 = digits_at(p, j + 2);
+            if (d2 && p.compare(j + 2 + d2, 2, "gb") == 0) return true;
+        }
+        i = j - 1;                       // a shorter suffix of the same digit run ends at the same place: same verdict
+    }
+    return false;
+}
 // regexp `nvidia\.com/gpu-\d+gb` (pkg/gpu/slicing/profile.go:30-31)
 bool matches_mps_resource(const std::string& r) {
     for (size_t at = r.find(kMpsPrefix); at != std::string::npos; at = r.find(kMpsPrefix, at + 1)) {
@@ -255,10 +269,13 @@ const KnownGeometries& DefaultKnownGeometries() {
     return t;
 }
 void SetKnownGeometries(const KnownGeometries& g) {
-    for (auto& [model, list] : g) {                                          // ValidateConfigs (known_configs.go:159-181)
-        if (list.empty()) throw Error("no allowed geometries for model " + model);
-        for (auto& geom : list) for (auto& [p, q] : geom) if (q < 1) throw Error("invalid quantity for profile " + p + " of model " + model);
-    }
+    if (g.empty()) throw Error("no known configs provided");                 // ValidateConfigs (known_configs.go:159-181)
+    for (auto& [model, list] : g)
+        for (auto& geom : list)
+            for (auto& [p, q] : geom) {
+                if (!matches_mig_profile(p)) throw Error("invalid profile " + p);
+                if (q < 1) throw Error("invalid quantity " + std::to_string(q) + " for profile " + p);
+            }
     g_known = g; g_known_set = true;
 }
 const KnownGeometries& GetKnownGeometries() { return g_known_set ? g_known : DefaultKnownGeometries(); }

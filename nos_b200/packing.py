@@ -82,6 +82,22 @@ def mps_size(profile: str) -> int:  # slicing.ProfileName.GetMemorySizeGB (profi
     return int(t) if re.fullmatch(r"[+-]?\d+", t) else 0
 
 
+_RE_MIG_PROFILE = re.compile(r"\d+g\.\d+gb")      # pkg/constant/constants.go:51, mig.ProfileName.isValid (profile.go:57-59)
+
+
+def validate_known_geometries(configs: Dict[str, List[Dict[str, int]]]) -> None:
+    """mig.ValidateConfigs (pkg/gpu/mig/known_configs.go:159-181): raises PackError where the reference returns an error."""
+    if len(configs) == 0:
+        raise PackError("no known configs provided")
+    for geometries in configs.values():
+        for geometry in geometries:
+            for profile, quantity in geometry.items():
+                if _RE_MIG_PROFILE.search(profile) is None:
+                    raise PackError(f"invalid profile {profile}")
+                if quantity < 1:
+                    raise PackError(f"invalid quantity {quantity} for profile {profile}")
+
+
 def compute_pod_request(pod: dict) -> Dict[str, int]:
     """resource.ComputePodRequest (pkg/resource/resource.go:127-146); the overhead sum is discarded there."""
     if "request" in pod:

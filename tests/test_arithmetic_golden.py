@@ -37,3 +37,29 @@ def test_required_gpu_memory():
     for c in G["required_gpu_memory_gb"]:
         pod = m.Pod("ns", "p", containers=[dict(c["request"])])
         assert qm.quota_pod_request(pod, c["nvidia_gpu_memory_gb"])[m.RESOURCE_GPU_MEMORY] == c["expected"], c["name"]
+
+
+def test_mig_resource_name_functions():
+    for c in G["is_nvidia_mig_device"]:
+        assert m.is_mig_resource(c["resource"]) == c["expected"], c["name"]
+        assert (pk.slice_profile_of(pk.KIND_MIG, c["resource"]) is not None) == c["expected"], c["name"]
+    for c in G["extract_memory_gb_from_mig_format"]:
+        # the model folds the error into 0, which is how every caller on the path uses it (pkg/gpu/util/resource.go:76-82)
+        assert m.mig_memory_gb_from_resource(c["resource"]) == (0 if c["error"] else c["expected"]), c["name"]
+
+
+def test_validate_configs():
+    from support import hostcli as hc
+    import __graft_entry__ as g
+    g.build()
+    node = {"name": "n", "labels": {pk.LABEL_PARTITIONING: "mig", pk.LABEL_PRODUCT: "NVIDIA-A30", pk.LABEL_COUNT: "1"}}
+    for c in G["validate_configs"]:
+        configs = m.DEFAULT_KNOWN_GEOMETRIES if c["configs"] == "default" else c["configs"]
+        if c["error"]:
+            with pytest.raises(pk.PackError):
+                pk.validate_known_geometries(configs)
+        else:
+            pk.validate_known_geometries(configs)
+        if configs:                                   # the text driver cannot state an empty table (it falls back to the default)
+            code, out = hc.run(hc.to_text("mig", [node], [], "state", geometries=configs))
+            assert (code == 1 and out.startswith("error ")) == c["error"], (c["name"], out)
