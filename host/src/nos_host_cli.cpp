@@ -7,7 +7,8 @@
 //   node <name> | nilnode <key>          label <k> <v>   annotation <k> <v>   allocatable <res> <n>   requested <res> <n>
 //   numpods <n>
 //   pod <namespace> <name> <priority|->  container <res>=<n>,...|-   init <res>=<n>,...|-
-//   run plan | run pack | run state | run diff
+//   sa|sb <node> [<gpu index> <res>=<n>,...]   (two partitioning states for `run equal`)
+//   run plan | run pack | run state | run diff | run equal
 // stdout: `run plan`  -> "node <name>" / "gpu <index> <res>=<n>,..." lines, then "stats ..." ;
 //         `run pack`  -> one "<array> v v v" line per packed buffer;  `run state` -> the snapshot's current state;
 //         `run diff`  -> plan, then "apply <node>" per node Actuator.Apply would partition and "changed <node>".
@@ -64,6 +65,7 @@ int main() {
     framework::NodeInfo* cur = nullptr;
     std::vector<v1::Pod> pods;
     mig::KnownGeometries custom;
+    state::PartitioningState stA, stB;
     std::string line, mode;
     try {
         while (std::getline(std::cin, line)) {
@@ -85,9 +87,19 @@ int main() {
             else if (cmd == "pod") { v1::Pod p; p.ns = a; p.name = b; if (c != "-" && !c.empty()) p.priority = std::stoi(c); pods.push_back(p); }
             else if (cmd == "container") pods.back().containers.push_back({parse_list(a)});
             else if (cmd == "init") pods.back().initContainers.push_back({parse_list(a)});
+            else if (cmd == "sa" || cmd == "sb") {          // sa|sb <node> [<gpu index> <res>=<n>,...|-]: one GPU of one of two states
+                state::PartitioningState& st = cmd == "sa" ? stA : stB;
+                state::NodePartitioning& np = st[a];
+                if (!b.empty()) {
+                    state::GPUPartitioning g; g.GPUIndex = std::stoi(b);
+                    for (auto& [r, q] : parse_list(c.empty() ? "-" : c)) g.Resources[r] = (int)q;
+                    np.GPUs.push_back(g);
+                }
+            }
             else if (cmd == "run") { mode = a; break; }
             else throw Error("unknown directive " + cmd);
         }
+        if (mode == "equal") { std::cout << "equal " << (stA.Equal(stB) ? "true" : "false") << '\n'; return 0; }
         if (!custom.empty()) mig::SetKnownGeometries(custom);
         core::Snapshot snap = core::TakeSnapshot(kind, cluster);
         if (mode == "state") { print_state(snap.GetPartitioningState()); return 0; }

@@ -155,3 +155,17 @@ def test_random_cases_through_cpp_planner_vs_oracle():
         assert changed == ([] if same else [k for k in sorted(st) if canon(cur[k]) != canon(st[k])])
         n += 1
     assert n > 60
+
+
+def test_partitioning_state_equal_golden():
+    """internal/partitioning/state/partitioning_test.go:27-260 through nos::state::PartitioningState::Equal."""
+    cases = json.load(open(os.path.join(HERE, "golden", "partitioning_state.json")))["cases"]
+    for c in cases:
+        lines = []
+        for tag, st in (("sa", c["a"]), ("sb", c["b"])):
+            for node, gpus in st.items():
+                lines.append(f"{tag} {node}")
+                for g in gpus:
+                    lines.append(f"{tag} {node} {g['gpu_index']} " + (",".join(f"{k}={v}" for k, v in g["resources"].items()) or "-"))
+        code, out = hc.run("\n".join(lines + ["run equal"]) + "\n")
+        assert code == 0 and out.strip() == ("equal true" if c["expected"] else "equal false"), (c["name"], out)
