@@ -314,6 +314,43 @@ typedef struct nosplan_victim_query {
 int nosplan_quota_victims(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_victim_query* query,
                           uint8_t* victim /* [n_pods] out: 1 = potential victim */, nosplan_stats* stats);
 
+/* The WHOLE of preemptor.SelectVictimsOnNode (capacity_scheduling.go:468-675) for ONE preemptor over MANY nodes (SURVEY.md
+ * section 8f row 2): the first pass above, then "no victims" (:598-602), the Filter with the potential victims gone
+ * (:610-612), max quota / aggregated min quota with the pod's request (:617-624), the PodDisruptionBudget split
+ * (filterPodsWithPDBViolation :850-895) and the two reprieve loops (:636-673).  Nodes are independent (one clone of the
+ * quota snapshot and one NodeInfo each); the pods of a node are sequential.
+ * The Filter is NodeResourcesFit on the node account given here (k8s.io/kubernetes v1.25.4, not part of the reference tree;
+ * no nominated pods on the node).  Quota columns double as node resource columns: 0 cpu milli, 1 memory, 2 ephemeral
+ * storage, 3 pods (node_alloc = allowed pod number, node_requested = len(Pods)), >= 4 scalars; the gpu-memory column is
+ * ignored on the node side.  The PDB match (namespace, selector, DisruptedPods: :856-877) is string work done by the caller,
+ * who passes per pod the ids of the budgets that would be decremented. */
+#define NOSPLAN_VICTIMS_OK 0           /* framework.Success: victim[] / num_violating are valid for the node */
+#define NOSPLAN_VICTIMS_NONE 1         /* UnschedulableAndUnresolvable "No victims found on node" (:598-602) */
+#define NOSPLAN_VICTIMS_FILTER 2       /* the Filter still rejects the pod with every potential victim gone (:610-612) */
+#define NOSPLAN_VICTIMS_MAX_QUOTA 3    /* Unschedulable "max quota exceeded" (:618-620) */
+#define NOSPLAN_VICTIMS_MIN_QUOTA 4    /* Unschedulable "total min quota exceeded" (:621-623) */
+#define NOSPLAN_VICTIMS_ERROR 5        /* framework.AsStatus(err): removePod of a pod that already left the node (:653-655) */
+#define NOSPLAN_PREEMPT_MAX_PDBS 64    /* PodDisruptionBudgets per query */
+
+typedef struct nosplan_preempt_query {
+    nosplan_victim_query v;            /* preemptor, nominated_in_eq and the pods grouped by node, as for nosplan_quota_victims */
+    const int64_t* pod_req;            /* [Rq] PreFilterState.podReq: the preemptor's quota request (gpu-memory filled) */
+    const int64_t* nominated;          /* [Rq] PreFilterState.nominatedPodsReqWithPodReq */
+    const int64_t* fit_request;        /* [Rq] the preemptor's request as NodeResourcesFit computes it (column 3 unused) */
+    uint32_t fit_mask;                 /* scalar columns present in fit_request */
+    int32_t n_pdbs;                    /* <= NOSPLAN_PREEMPT_MAX_PDBS */
+    const int64_t* node_alloc;         /* [n_nodes][Rq] NodeInfo.Allocatable */
+    const int64_t* node_requested;     /* [n_nodes][Rq] NodeInfo.Requested */
+    const int32_t* pdb_allowed;        /* [n_pdbs] pdb.Status.DisruptionsAllowed */
+    const int32_t* pod_pdb_ptr;        /* [n_pods+1] CSR */
+    const int32_t* pod_pdb;            /* budgets matching each pod and not listing it in DisruptedPods, ascending id */
+} nosplan_preempt_query;
+
+int nosplan_preempt_dryrun(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_preempt_query* query,
+                           uint8_t* victim /* [n_pods] out: 1 = victim (meaningful where node_status is OK) */,
+                           int32_t* node_status /* [n_nodes] out: NOSPLAN_VICTIMS_* */,
+                           int32_t* num_violating /* [n_nodes] out: numViolatingVictim */, nosplan_stats* stats);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Snapshot packer: the status annotations of N nodes -> the per-GPU arrays of nosplan_snapshot.
  * Replaces: gpu.ParseNodeAnnotations (pkg/gpu/annotation.go:29-104), StatusAnnotationList.GroupByGpuIndex (:186-196) and

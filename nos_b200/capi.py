@@ -25,6 +25,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
+    "nosplan_preempt_dryrun",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -285,6 +286,10 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     from . import victim_packing as vp
     lib.nosplan_quota_victims.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(vp.CVictimQuery), C.c_void_p, C.POINTER(CStats)]
     lib.nosplan_quota_victims.restype = C.c_int
+    from . import preempt_packing as pp
+    lib.nosplan_preempt_dryrun.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(pp.CPreemptQuery), C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.POINTER(CStats)]
+    lib.nosplan_preempt_dryrun.restype = C.c_int
     return lib
 
 
@@ -455,6 +460,22 @@ class Engine:
         self._check(rc, "nosplan_quota_victims")
         del k1, k2
         return victim[:query.n_pods], st.as_dict()
+
+    def preempt_dryrun(self, pq, query):
+        """nosplan_preempt_dryrun -> (victim [n_pods] uint8, node_status [n_nodes] int32, num_violating [n_nodes] int32, stats dict)."""
+        from . import quota_packing as qp
+        cq, k1 = qp.c_quotas(pq)
+        cv, k2 = query.c_struct()
+        n_pods, n_nodes = query.v.n_pods, len(query.v.node_ptr) - 1
+        victim = np.zeros(max(1, n_pods), np.uint8)
+        status = np.zeros(max(1, n_nodes), np.int32)
+        nviol = np.zeros(max(1, n_nodes), np.int32)
+        st = CStats()
+        rc = self.lib.nosplan_preempt_dryrun(self.h, C.byref(cq), C.byref(cv), victim.ctypes.data, status.ctypes.data, nviol.ctypes.data,
+                                             C.byref(st))
+        self._check(rc, "nosplan_preempt_dryrun")
+        del k1, k2
+        return victim[:n_pods], status[:n_nodes], nviol[:n_nodes], st.as_dict()
 
     def quota_recompute(self, pq, running=None, pending=None):
         """nosplan_quota_recompute -> (dict of arrays as QuotaResult.trimmed(), stats dict)"""

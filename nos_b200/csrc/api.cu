@@ -43,6 +43,11 @@ extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_q
                                           const nosplan_quotas* qs, const nosplan_victim_query* vq, uint8_t* victim,
                                           float* ms_k, int* launches);
 
+extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                           const nosplan_quotas* qs, const nosplan_preempt_query* pq, uint8_t* victim,
+                                           int32_t* node_status, int32_t* num_violating, float* ms_h2d, float* ms_k, float* ms_d2h,
+                                           int* launches, long long* h2d_bytes, long long* d2h_bytes);
+
 extern "C" int nosplan_parse_annotations_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                               const nosplan_annotations* in, nosplan_parsed_gpus* out, float* ms_h2d, float* ms_k,
                                               float* ms_d2h, long long* h2d_bytes, long long* d2h_bytes);
@@ -951,6 +956,21 @@ int nosplan_quota_victims(nosplan_t* h, const nosplan_quotas* quotas, const nosp
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         stats->ms_kernels = ms; stats->kernel_launches = launches;
+    }
+    return rc;
+}
+
+int nosplan_preempt_dryrun(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_preempt_query* query, uint8_t* victim,
+                           int32_t* node_status, int32_t* num_violating, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
+    const int rc = nosplan_preempt_dryrun_impl(h->device, h->stream, h->qctx, &h->err, quotas, query, victim, node_status, num_violating,
+                                               &a, &b, &c, &launches, &hb, &db);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
+        stats->h2d_bytes = hb; stats->d2h_bytes = db;
     }
     return rc;
 }

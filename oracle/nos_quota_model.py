@@ -319,3 +319,143 @@ def select_potential_victims(infos: ElasticQuotaInfos, preemptor: Pod, nominated
             if pod_priority(pv) < prio:
                 victims[i] = True
     return victims
+
+
+# ------------------------------------------------------------------------------------------------------------
+# preemption dry run, the whole of preemptor.SelectVictimsOnNode (capacity_scheduling.go:468-675) for one node:
+# first pass as above, Filter with the potential victims gone, quota checks, the PDB split, and the reprieve loops.
+# Third-party pieces restated from k8s.io/kubernetes v1.25.4 (not in /root/reference; parity unpinned by the reference, whose
+# TestDryRunPreemption only counts candidates): NodeInfo.RemovePod / AddPodInfo (Requested and len(Pods) bookkeeping, an
+# error when the pod is not on the node), NodeResourcesFit as the only Filter, no nominated pods on the node.
+# ------------------------------------------------------------------------------------------------------------
+VICTIMS_OK, VICTIMS_NONE, VICTIMS_FILTER, VICTIMS_MAX_QUOTA, VICTIMS_MIN_QUOTA, VICTIMS_ERROR = 0, 1, 2, 3, 4, 5
+
+
+@dataclass
+class PreemptionNode:
+    allocatable: Resource
+    requested: Resource            # of every pod in `pods`
+    pods: List[Pod]                # least important first (the order sort.Slice with !MoreImportantPod leaves, :516)
+    pdbs_of_pod: List[List[int]]   # per pod: ids of the PDBs that match it and do not list it in DisruptedPods (:864-883)
+
+
+def select_victims_on_node(infos: ElasticQuotaInfos, preemptor: Pod, pod_req: Resource, nominated_in_eq: Resource, nominated: Resource,
+                           node: PreemptionNode, pdb_allowed: List[int], nvidia_gpu_memory_gb: int):
+    """-> (status, victims as indices into node.pods in the order the reference appends them, numViolatingVictim)"""
+    from nos_model import NodeInfo, node_resources_fit
+    snap = clone_infos(infos)
+    prio = pod_priority(preemptor)
+    pre_eq = snap.get(preemptor.namespace)
+    ni = NodeInfo(node.allocatable.clone(), node.requested.clone(), len(node.pods))
+    on_node = set(range(len(node.pods)))
+    fit_req = resource_from_list(compute_pod_request(preemptor))
+
+    def node_req(pv: Pod) -> Resource:
+        return resource_from_list(compute_pod_request(pv))
+
+    def quota_req(pv: Pod) -> Resource:
+        return resource_from_list(quota_pod_request(pv, nvidia_gpu_memory_gb))
+
+    def remove_pod(i: int) -> bool:                      # removePod closure (:492-501); False = NodeInfo.RemovePod error
+        if i not in on_node:
+            return False
+        on_node.discard(i)
+        r = node_req(node.pods[i])
+        ni.requested.milli_cpu -= r.milli_cpu; ni.requested.memory -= r.memory; ni.requested.ephemeral -= r.ephemeral
+        for k, v in r.scalars.items():
+            ni.requested.scalars[k] = ni.requested.scalars.get(k, 0) - v
+        ni.num_pods -= 1
+        e = snap.get(node.pods[i].namespace)
+        if e is not None:
+            e.delete_pod_if_present(("pod", i), quota_req(node.pods[i]))
+        return True
+
+    def add_pod(i: int) -> None:                         # addPod closure (:502-509)
+        on_node.add(i)
+        ni.add_pod(node.pods[i])
+        e = snap.get(node.pods[i].namespace)
+        if e is not None:
+            e.add_pod_if_not_present(("pod", i), quota_req(node.pods[i]))
+
+    for i, pv in enumerate(node.pods):                   # every pod of the node is accounted in its quota (Reserve / informer)
+        e = snap.get(pv.namespace)
+        if e is not None:
+            e.pods.add(("pod", i))
+
+    potential: List[int] = []
+    if pre_eq is not None:
+        more_than_min = pre_eq.used_over_min_with(nominated_in_eq)
+        for i, pv in enumerate(node.pods):
+            pv_eq = snap.get(pv.namespace)
+            if pv_eq is None:
+                continue
+            if more_than_min:
+                if pv.namespace == preemptor.namespace:
+                    if pod_priority(pv) < prio:
+                        potential.append(i); remove_pod(i)
+                    continue
+                if not over_quota_label(pv):
+                    continue
+                g = snap.guaranteed_overquotas(preemptor.namespace)
+                if pre_eq.used_lte_with(res_sum(g, pre_eq.min), nominated_in_eq):
+                    pg = snap.guaranteed_overquotas(pv.namespace)
+                    if pv_eq.used_over(res_sum(pg, pv_eq.min)):
+                        potential.append(i); remove_pod(i)
+            else:
+                if pv.namespace != preemptor.namespace and pv_eq.used_over_min() and over_quota_label(pv):
+                    potential.append(i); remove_pod(i)
+    else:
+        for i, pv in enumerate(node.pods):
+            if pv.namespace in snap:
+                continue
+            if pod_priority(pv) < prio:
+                potential.append(i); remove_pod(i)
+
+    if not potential:                                    # :598-602
+        return VICTIMS_NONE, [], 0
+    if not node_resources_fit(fit_req, ni):              # :610-612
+        return VICTIMS_FILTER, [], 0
+    if pre_eq is not None:                               # :617-624
+        if pre_eq.used_over_max_with(pod_req):
+            return VICTIMS_MAX_QUOTA, [], 0
+        if snap.aggregated_used_over_min_with(pod_req):
+            return VICTIMS_MIN_QUOTA, [], 0
+
+    potential = list(reversed(potential))                # sort by MoreImportantPod (:628-630): most important first
+    allowed = list(pdb_allowed)                          # filterPodsWithPDBViolation (:850-895)
+    violating, non_violating = [], []
+    for i in potential:
+        bad = False
+        for b in node.pdbs_of_pod[i]:
+            allowed[b] -= 1
+            if allowed[b] < 0:
+                bad = True
+        (violating if bad else non_violating).append(i)
+
+    victims: List[int] = []
+
+    def reprieve(i: int):                                # :636-660 -> (fits, ok)
+        add_pod(i)
+        fits = node_resources_fit(fit_req, ni)
+        if not fits:
+            if not remove_pod(i):
+                return fits, False
+            victims.append(i)
+        if pre_eq is not None and (pre_eq.used_over_max_with(nominated_in_eq) or snap.aggregated_used_over_min_with(nominated)):
+            if not remove_pod(i):                        # the pod is already gone when it did not fit: RemovePod errors (:653-655)
+                return fits, False
+            victims.append(i)
+        return fits, True
+
+    num_violating = 0
+    for i in violating:
+        fits, ok = reprieve(i)
+        if not ok:
+            return VICTIMS_ERROR, [], 0
+        if not fits:
+            num_violating += 1
+    for i in non_violating:
+        _, ok = reprieve(i)
+        if not ok:
+            return VICTIMS_ERROR, [], 0
+    return VICTIMS_OK, victims, num_violating

@@ -17,7 +17,7 @@ def lib():
     global _lib
     if _lib is None:
         path = os.path.join(ORACLE_DIR, "libnosoracle.so")
-        srcs = [os.path.join(ORACLE_DIR, f) for f in ("nos_oracle.cpp", "nos_quota_oracle.cpp", "nos_victims_oracle.cpp")] + \
+        srcs = [os.path.join(ORACLE_DIR, f) for f in ("nos_oracle.cpp", "nos_quota_oracle.cpp", "nos_victims_oracle.cpp", "nos_preempt_oracle.cpp")] + \
                [os.path.join(ROOT, "include", "nosplan.h")]
         if not os.path.exists(path) or any(os.path.getmtime(s) > os.path.getmtime(path) for s in srcs if os.path.exists(s)):
             subprocess.check_call(["make", "-C", ORACLE_DIR, "-s"])
@@ -76,3 +76,21 @@ def quota(pq, running=None, pending=None):
     d = res.trimmed()
     d["seconds"] = sec.value
     return d
+
+
+def preempt_dryrun(pq, query):
+    """CPU oracle of the whole SelectVictimsOnNode on packed structs -> (victim [P] u8, node_status [N] i32, num_violating [N] i32)."""
+    from nos_b200 import preempt_packing as pp, quota_packing as qp
+    L = lib()
+    L.nos_oracle_preempt_dryrun.argtypes = [C.POINTER(qp.CQuotas), C.POINTER(pp.CPreemptQuery), C.c_void_p, C.c_void_p, C.c_void_p]
+    L.nos_oracle_preempt_dryrun.restype = C.c_int
+    cq, k1 = qp.c_quotas(pq)
+    cv, k2 = query.c_struct()
+    n_nodes = len(query.v.node_ptr) - 1
+    victim = np.zeros(max(1, query.v.n_pods), np.uint8)
+    status = np.zeros(max(1, n_nodes), np.int32)
+    nviol = np.zeros(max(1, n_nodes), np.int32)
+    rc = L.nos_oracle_preempt_dryrun(C.byref(cq), C.byref(cv), victim.ctypes.data, status.ctypes.data, nviol.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"nos_oracle_preempt_dryrun -> {rc}")
+    return victim[:query.v.n_pods], status[:n_nodes], nviol[:n_nodes]
