@@ -139,14 +139,14 @@ __global__ void __launch_bounds__(256) k_preempt_dryrun(DevPreempt v) {
             rq = r;
         };
         // reserve (sign -1) / un-reserve (sign +1) pod i in the clone of its namespace; NodeInfo bookkeeping with it
-        auto move_pod = [&](int i, int sign) {
+        bool lte_known = false, lte_cached = false;        // usedLteWith(guaranteed + min) of the preemptor's quota: changes only with a move
+        auto move_pod = [&](int i, int sign, int pns, int ev) {
             long long rq, rn; unsigned rm;
             pod_rows(i, rq, rn, rm);
             requested -= sign * rn;                        // RemovePod: Requested -= r (sign +1), AddPodInfo: += r
             if (c == 3) requested -= sign;
-            const int pns = v.ns[i];
-            const int ev = (pns >= 0 && pns < v.NS) ? v.ns_quota[pns] : -1;
             if (ev < 0) return;
+            lte_known = false;
             unsigned hit = __ballot_sync(P_FULL, lane < n_touch && tns[lane] == pns);
             int slot;
             if (hit) slot = __ffs(hit) - 1;
@@ -188,35 +188,52 @@ __global__ void __launch_bounds__(256) k_preempt_dryrun(DevPreempt v) {
             const long long up = used_of(v.pn, ep);
             more_than_min = __ballot_sync(P_FULL, col && p_cmp_col(c, mm_p) && nom + up > min_p) != 0;   // usedOverMinWith, once (:522)
         }
+        // pods are taken 32 at a time: lane k fetches the scalars of pod b + k (coalesced), the warp then walks them in order
         int n_potential = 0;
-        for (int i = p0; i < p1 && !overflow; ++i) {
-            const int pns = v.ns[i];
-            const int ev = (pns >= 0 && pns < v.NS) ? v.ns_quota[pns] : -1;
-            bool is_victim = false;
-            if (ep < 0) is_victim = ev < 0 && v.prio[i] < v.pprio;                                  // :582-596
-            else if (ev >= 0) {
-                if (more_than_min) {
-                    if (pns == v.pn) is_victim = v.prio[i] < v.pprio;                               // :527-535
-                    else if (v.over[i]) {                                                           // :541-559
-                        const unsigned ymask = omask | (mm_p & P_SCALAR_BITS);
-                        const long long up = used_of(v.pn, ep);
-                        const long long y = guaranteed(ep) + min_p;
-                        const bool lte = __ballot_sync(P_FULL, col && p_cmp_col(c, ymask) && nom + up > y) == 0;
-                        if (lte) {
-                            const unsigned vmask = omask | (v.min_mask[ev] & P_SCALAR_BITS);
-                            const long long uv = used_of(pns, ev);
-                            const long long yv = guaranteed(ev) + (col ? v.qmin[(size_t)ev * v.R + c] : 0);
-                            is_victim = __ballot_sync(P_FULL, col && p_cmp_col(c, vmask) && uv > yv) != 0;
+        for (int b = p0; b < p1 && !overflow; b += 32) {
+            const int il = b + lane;
+            const bool inr = il < p1;
+            const int l_ns = inr ? v.ns[il] : -1, l_prio = inr ? v.prio[il] : 0, l_over = inr ? v.over[il] : 0;
+            const int l_ev = (l_ns >= 0 && l_ns < v.NS) ? v.ns_quota[l_ns] : -1;
+            int l_state = 0;
+            const int nb = min(32, p1 - b);
+            for (int k = 0; k < nb && !overflow; ++k) {
+                const int i = b + k;
+                const int pns = __shfl_sync(P_FULL, l_ns, k), ev = __shfl_sync(P_FULL, l_ev, k);
+                const int prio = __shfl_sync(P_FULL, l_prio, k), over = __shfl_sync(P_FULL, l_over, k);
+                bool is_victim = false;
+                if (ep < 0) is_victim = ev < 0 && prio < v.pprio;                                   // :582-596
+                else if (ev >= 0) {
+                    if (more_than_min) {
+                        if (pns == v.pn) is_victim = prio < v.pprio;                                // :527-535
+                        else if (over) {                                                            // :541-559
+                            if (!lte_known) {
+                                const unsigned ymask = omask | (mm_p & P_SCALAR_BITS);
+                                const long long up = used_of(v.pn, ep);
+                                const long long y = guaranteed(ep) + min_p;
+                                lte_cached = __ballot_sync(P_FULL, col && p_cmp_col(c, ymask) && nom + up > y) == 0;
+                                lte_known = true;
+                            }
+                            if (lte_cached) {
+                                const unsigned vmask = omask | (v.min_mask[ev] & P_SCALAR_BITS);
+                                const long long uv = used_of(pns, ev);
+                                const long long yv = guaranteed(ev) + (col ? v.qmin[(size_t)ev * v.R + c] : 0);
+                                is_victim = __ballot_sync(P_FULL, col && p_cmp_col(c, vmask) && uv > yv) != 0;
+                            }
                         }
+                    } else if (pns != v.pn && over) {                                               // :569-577
+                        const long long uv = used_of(pns, ev);
+                        is_victim = __ballot_sync(P_FULL, col && p_cmp_col(c, v.min_mask[ev]) &&
+                                                              uv > v.qmin[(size_t)ev * v.R + c]) != 0;
                     }
-                } else if (pns != v.pn && v.over[i]) {                                              // :569-577
-                    const long long uv = used_of(pns, ev);
-                    is_victim = __ballot_sync(P_FULL, col && p_cmp_col(c, v.min_mask[ev]) &&
-                                                          uv > v.qmin[(size_t)ev * v.R + c]) != 0;
+                }
+                if (is_victim) {
+                    if (lane == k) l_state = S_POTENTIAL | S_OFF;
+                    ++n_potential;
+                    move_pod(i, +1, pns, ev);
                 }
             }
-            if (lane == 0) v.state[i] = is_victim ? (S_POTENTIAL | S_OFF) : 0;
-            if (is_victim) { ++n_potential; move_pod(i, +1); }
+            if (inr) v.state[il] = (uint8_t)l_state;
         }
         __syncwarp();
         // ---- the checks between the passes (:598-624)
@@ -230,35 +247,52 @@ __global__ void __launch_bounds__(256) k_preempt_dryrun(DevPreempt v) {
         }
         int n_viol = 0;
         if (status == NOSPLAN_VICTIMS_OK) {
+            const int last_chunk = p0 + ((p1 - p0 - 1) & ~31);
             // ---- pass 2: PodDisruptionBudget split, most important victim first (:628-635, :850-895)
             for (int k = lane; k < v.n_pdbs; k += 32) pdb[k] = v.pdb_allowed[k];
             __syncwarp();
-            for (int i = p1 - 1; i >= p0; --i) {
-                if (!(v.state[i] & S_POTENTIAL)) continue;
-                bool bad = false;
-                if (lane == 0) {
-                    for (int k = v.pod_pdb_ptr[i]; k < v.pod_pdb_ptr[i + 1]; ++k)
-                        if (--pdb[v.pod_pdb[k]] < 0) bad = true;
-                    if (bad) v.state[i] |= S_VIOLATING;
+            for (int b = last_chunk; b >= p0; b -= 32) {
+                const int il = b + lane;
+                const bool mine = il < p1 && (v.state[il] & S_POTENTIAL);
+                // lane k walks the budgets of pod b + k; the lanes take turns from the most important pod down
+                unsigned todo = __ballot_sync(P_FULL, mine);
+                while (todo) {
+                    const int k = 31 - __clz(todo);
+                    todo &= ~(1u << k);
+                    if (lane == k) {
+                        bool bad = false;
+                        for (int x = v.pod_pdb_ptr[il]; x < v.pod_pdb_ptr[il + 1]; ++x)
+                            if (--pdb[v.pod_pdb[x]] < 0) bad = true;
+                        if (bad) v.state[il] |= S_VIOLATING;
+                    }
+                    __syncwarp();
                 }
-                __syncwarp();
             }
             // ---- pass 3: reprieve the violating victims, then the others (:636-673)
             for (int round = 0; round < 2 && status == NOSPLAN_VICTIMS_OK; ++round) {
-                for (int i = p1 - 1; i >= p0 && status == NOSPLAN_VICTIMS_OK; --i) {
-                    const uint8_t st = v.state[i];
-                    if (!(st & S_POTENTIAL) || ((st & S_VIOLATING) != 0) != (round == 0)) continue;
-                    move_pod(i, -1);                                     // addPod
-                    bool off = false, victim = false;
-                    const bool fit = fits();
-                    if (!fit) { move_pod(i, +1); off = true; victim = true; }
-                    if (ep >= 0 && (over_max_with(nom) || agg_over_min_with(nominated))) {
-                        if (off) { status = NOSPLAN_VICTIMS_ERROR; break; }  // RemovePod of a pod that is not on the node
-                        move_pod(i, +1); off = true; victim = true;
+                for (int b = last_chunk; b >= p0 && status == NOSPLAN_VICTIMS_OK; b -= 32) {
+                    const int il = b + lane;
+                    int l_state = il < p1 ? v.state[il] : 0;
+                    const int l_ns = (l_state & S_POTENTIAL) ? v.ns[il] : -1;
+                    const int l_ev = (l_ns >= 0 && l_ns < v.NS) ? v.ns_quota[l_ns] : -1;
+                    unsigned todo = __ballot_sync(P_FULL, (l_state & S_POTENTIAL) && ((l_state & S_VIOLATING) != 0) == (round == 0));
+                    while (todo) {
+                        const int k = 31 - __clz(todo);
+                        todo &= ~(1u << k);
+                        const int i = b + k;
+                        const int pns = __shfl_sync(P_FULL, l_ns, k), ev = __shfl_sync(P_FULL, l_ev, k);
+                        move_pod(i, -1, pns, ev);                                // addPod
+                        bool off = false, victim = false;
+                        const bool fit = fits();
+                        if (!fit) { move_pod(i, +1, pns, ev); off = true; victim = true; }
+                        if (ep >= 0 && (over_max_with(nom) || agg_over_min_with(nominated))) {
+                            if (off) { status = NOSPLAN_VICTIMS_ERROR; break; }  // RemovePod of a pod that is not on the node
+                            move_pod(i, +1, pns, ev); off = true; victim = true;
+                        }
+                        if (!fit && round == 0) ++n_viol;
+                        if (lane == k) l_state = (l_state & ~(S_OFF | S_VICTIM)) | (off ? S_OFF : 0) | (victim ? S_VICTIM : 0);
                     }
-                    if (!fit && round == 0) ++n_viol;
-                    if (lane == 0) v.state[i] = (uint8_t)((st & ~(S_OFF | S_VICTIM)) | (off ? S_OFF : 0) | (victim ? S_VICTIM : 0));
-                    __syncwarp();
+                    if (il < p1) v.state[il] = (uint8_t)l_state;
                 }
             }
         }
@@ -355,9 +389,8 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
     PCU(cudaEventRecord(ev[1], st));
     k_preempt_aggregate<<<1, 256, 0, st>>>(v);
     if (Nn > 0) {
-        int blocks = (Nn + 7) / 8;
-        if (blocks > 148 * 4) blocks = 148 * 4;
-        k_preempt_dryrun<<<blocks, 256, 0, st>>>(v);
+        // one node per warp: nodes differ widely in work (victims found or not, reprieve loops), so the block scheduler balances them
+        k_preempt_dryrun<<<(Nn + 7) / 8, 256, 0, st>>>(v);
     }
     PCU(cudaGetLastError());
     PCU(cudaEventRecord(ev[2], st));

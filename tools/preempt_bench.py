@@ -1,0 +1,39 @@
+"""Preemption dry-run timing at BASELINE config #4 scale (run on a GPU box): 500 ElasticQuotas, 100 000 running pods on
+10 000 nodes, one preemptor per call; nosplan_preempt_dryrun (host buffers in and out) against the CPU oracle on the same
+inputs.  Quota state: the recipe's, Min scaled so that cluster-wide Used is 98 % of the aggregated Min."""
+import json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, ROOT + "/tests", ROOT + "/oracle"]
+import numpy as np
+from nos_b200 import capi, preempt_packing as pp, victim_packing as vp
+from support import oracle_lib as ol
+from test_preempt_gpu import c4_query
+
+eng = capi.Engine(0)
+pq, run, r, order, ptr, req, node_req, alloc, pdb_allowed, pdb_ptr, pod_pdb = c4_query(eng, fill=0.98)
+popular = int(np.bincount(run.ns).argmax())
+nom = np.zeros(pq.n_res, np.int64)
+nom[0], nom[1], nom[5] = 4000, 8 << 30, 1
+nom[pq.gpu_memory_col] = 32
+fit = nom.copy(); fit[pq.gpu_memory_col] = 0
+nominated = nom.copy(); nominated[0] += 12000
+v = vp.PackedVictimQuery(popular, 1000, nom, ptr, run.ns[order], run.priority[order], r["over_quota"][order], req, run.request_mask[order])
+q = pp.PackedPreemptQuery(v, nom.copy(), nominated, fit, 1 << 5, alloc, node_req, pdb_allowed, pdb_ptr, pod_pdb)
+for _ in range(3):
+    gv, gs, gn, st = eng.preempt_dryrun(pq, q)
+ts, ks = [], []
+for _ in range(20):
+    t0 = time.perf_counter(); gv, gs, gn, st = eng.preempt_dryrun(pq, q); ts.append(time.perf_counter() - t0); ks.append(st["ms_kernels"])
+cpu = []
+for _ in range(5):
+    t0 = time.perf_counter(); ev, es, en = ol.preempt_dryrun(pq, q); cpu.append(time.perf_counter() - t0)
+same = bool(np.array_equal(gv, ev) and np.array_equal(gs, es) and np.array_equal(gn, en))
+P, N, R = run.n_pods, len(ptr) - 1, pq.n_res
+b_alg = P * (4 + 4 + 1 + 8 * R + 4 + 4 + 1) + len(pod_pdb) * 4 + N * (16 * R + 4 + 8)
+print(json.dumps({"config": "C4 scale: 500 quotas, %d running pods on %d nodes, %d resource columns, %d PodDisruptionBudgets" % (P, N, R, len(pdb_allowed)),
+                  "gpu": {"ms_call_p50": 1e3 * float(np.median(ts)), "ms_h2d": st["ms_h2d"], "ms_kernels_p50": float(np.median(ks)), "ms_d2h": st["ms_d2h"],
+                          "kernel_launches": st["kernel_launches"], "h2d_bytes": st["h2d_bytes"], "d2h_bytes": st["d2h_bytes"],
+                          "nodes_per_s_kernels": N / (float(np.median(ks)) / 1e3), "algorithmic_bytes": int(b_alg),
+                          "achieved_GBps_kernels": b_alg / (float(np.median(ks)) / 1e3) / 1e9},
+                  "outcome": {"status_counts": {str(k): int((gs == k).sum()) for k in range(6)}, "victims": int(gv.sum()), "violating": int(gn.sum())},
+                  "cpu_oracle_ms_p50": 1e3 * float(np.median(cpu)), "cpu_cores": 1, "identical_to_oracle": same}))
