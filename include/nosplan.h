@@ -289,6 +289,29 @@ typedef struct nosplan_quota_out {     /* every pointer may be NULL = not wanted
 int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
                             const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats);
 
+/* The operator pass returning only what has to be patched.  The reference walks the pods of a
+ * quota in the order of sortPodListForFindingOverQuotaPods and calls patchCapacityInfoIfDifferent on each
+ * (internal/controllers/elasticquota/elasticquota.go:44-60, :120-149): a pod is patched iff its label
+ * nos.nebuly.com/capacity differs from the desired value.  Here every quota is reconciled in one call and the pods to patch
+ * come back as one list: by quota row, and inside a quota in the reference's patch order.  Pods of namespaces without a
+ * quota are never reconciled and never listed. */
+#define NOSPLAN_LABEL_OTHER 0          /* label absent, or any value but the two below */
+#define NOSPLAN_LABEL_IN_QUOTA 1       /* constant.CapacityInfoInQuota   "in-quota"   */
+#define NOSPLAN_LABEL_OVER_QUOTA 2     /* constant.CapacityInfoOverQuota "over-quota" */
+typedef struct nosplan_label_changes {
+    const uint8_t* current;            /* [P_running] in: NOSPLAN_LABEL_* now on the pod */
+    int32_t capacity;                  /* in: entries available in pod / desired */
+    int32_t* pod;                      /* [capacity] out: index of the running pod to patch */
+    uint8_t* desired;                  /* [capacity] out: NOSPLAN_LABEL_IN_QUOTA / NOSPLAN_LABEL_OVER_QUOTA */
+    int32_t* n_changes;                /* [1] out: how many pods need a patch; when it exceeds capacity the first `capacity`
+                                          are returned and the call reports NOSPLAN_E_LIMIT */
+} nosplan_label_changes;
+
+/* `out` may be NULL or carry any of the nosplan_quota_out outputs computed from the running pods on the way
+ * (operator_used = the status.used each reconcile would write, over_quota, ambiguous_order, used ...). */
+int nosplan_quota_label_changes(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
+                                const nosplan_label_changes* changes, nosplan_quota_out* out, nosplan_stats* stats);
+
 /* First pass of preemptor.SelectVictimsOnNode (capacity_scheduling.go:511-596) for ONE preemptor over MANY nodes: which
  * pods of each node become potential victims under the quota predicates.  Upstream fans SelectVictimsOnNode out per
  * node, each on its own clone of the quota snapshot; removing a victim un-reserves its request in that clone

@@ -25,7 +25,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
-    "nosplan_preempt_dryrun",
+    "nosplan_preempt_dryrun", "nosplan_quota_label_changes",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -220,6 +220,13 @@ def flatten_annotations(v1_nodes, profiles):
             "n_nodes": len(v1_nodes), "n_profiles": len(profiles)}
 
 
+class CLabelChanges(C.Structure):
+    _fields_ = [("current", C.c_void_p), ("capacity", C.c_int32), ("pod", C.c_void_p), ("desired", C.c_void_p), ("n_changes", C.c_void_p)]
+
+
+LABEL_OTHER, LABEL_IN_QUOTA, LABEL_OVER_QUOTA = 0, 1, 2
+
+
 class NosplanError(RuntimeError):
     pass
 
@@ -290,6 +297,9 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_preempt_dryrun.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(pp.CPreemptQuery), C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.POINTER(CStats)]
     lib.nosplan_preempt_dryrun.restype = C.c_int
+    lib.nosplan_quota_label_changes.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(qp.CQuotaPods), C.POINTER(CLabelChanges),
+                                                C.POINTER(qp.CQuotaOut), C.POINTER(CStats)]
+    lib.nosplan_quota_label_changes.restype = C.c_int
     return lib
 
 
@@ -460,6 +470,32 @@ class Engine:
         self._check(rc, "nosplan_quota_victims")
         del k1, k2
         return victim[:query.n_pods], st.as_dict()
+
+    def quota_label_changes(self, pq, running, current, capacity=None, with_outputs=False):
+        """nosplan_quota_label_changes -> (pod indices to patch int32, desired labels uint8, n_changes, outputs dict or None, stats).
+        A capacity smaller than the number of changes raises NosplanError after filling what fits (read `.partial`)."""
+        from . import quota_packing as qp
+        cq, k1 = qp.c_quotas(pq)
+        cr, k2 = qp.c_quota_pods(running)
+        cur = np.ascontiguousarray(current, dtype=np.uint8)
+        cap = running.n_pods if capacity is None else int(capacity)
+        pod = np.zeros(max(1, cap), np.int32)
+        desired = np.zeros(max(1, cap), np.uint8)
+        n = np.zeros(1, np.int32)
+        lc = CLabelChanges(cur.ctypes.data if cur.size else None, cap, pod.ctypes.data, desired.ctypes.data, n.ctypes.data)
+        res = qp.QuotaResult(pq, running.n_pods, 0) if with_outputs else None
+        out = res.c_struct() if with_outputs else None
+        st = CStats()
+        rc = self.lib.nosplan_quota_label_changes(self.h, C.byref(cq), C.byref(cr), C.byref(lc), C.byref(out) if with_outputs else None,
+                                                  C.byref(st))
+        take = min(int(n[0]), cap)
+        if rc != 0:
+            msg = self.lib.nosplan_last_error(self.h)
+            e = NosplanError(f"nosplan_quota_label_changes failed ({rc}): {msg.decode() if msg else ''}")
+            e.partial = (pod[:take].copy(), desired[:take].copy(), int(n[0]))
+            raise e
+        del k1, k2
+        return pod[:take], desired[:take], int(n[0]), (res.trimmed() if with_outputs else None), st.as_dict()
 
     def preempt_dryrun(self, pq, query):
         """nosplan_preempt_dryrun -> (victim [n_pods] uint8, node_status [n_nodes] int32, num_violating [n_nodes] int32, stats dict)."""

@@ -36,7 +36,8 @@ struct nosplan_quota_ctx;
 extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                             const nosplan_quotas* qs, const nosplan_quota_pods* running,
                                             const nosplan_quota_pods* pending, nosplan_quota_out* out, float* ms_h2d, float* ms_k,
-                                            float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes);
+                                            float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes,
+                                            const nosplan_label_changes* lc);
 extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx);
 extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new();
 extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
@@ -925,7 +926,23 @@ int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const no
     if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
     float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
     const int rc = nosplan_quota_recompute_impl(h->device, h->stream, h->qctx, &h->err, quotas, running, pending, out, &a, &b, &c,
-                                                &launches, &hb, &db);
+                                                &launches, &hb, &db, nullptr);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
+        stats->h2d_bytes = hb; stats->d2h_bytes = db;
+    }
+    return rc;
+}
+
+int nosplan_quota_label_changes(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
+                                const nosplan_label_changes* changes, nosplan_quota_out* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!changes) { h->err = "null changes"; return NOSPLAN_E_INVALID; }
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
+    const int rc = nosplan_quota_recompute_impl(h->device, h->stream, h->qctx, &h->err, quotas, running, nullptr, out, &a, &b, &c,
+                                                &launches, &hb, &db, changes);
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;

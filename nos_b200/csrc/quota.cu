@@ -18,6 +18,7 @@
 #include <string>
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
 
 #include "nosplan_dev.cuh"
 
@@ -48,6 +49,8 @@ struct DevQuota {
     long long* chunk_sum;      // [chunks][QR] column sums of a chunk, then (in place) the running sum before the chunk
     int n_chunk_bound;
     long long fuse_ts_min, fuse_prio_min; int fuse_tbits, fuse_pbits;   // single-sort labelling (k_label_keys pass 1)
+    // label changes (patchCapacityInfoIfDifferent): per sorted position, pod index << 1 | over-quota and "differs from the label on the pod"
+    const uint8_t* cur_label; int32_t* chg_packed; uint8_t* chg_flag;
 };
 
 __device__ __forceinline__ long long go_int64(double x) {       // int64(f) as compiled for amd64 (CVTTSD2SQ)
@@ -348,7 +351,13 @@ __global__ void __launch_bounds__(LABEL_CHUNK) k_label_chunks(DevQuota q, const 
                 for (int w = 0; w < warp; ++w) pre += s_warp[w][c];
                 if ((mm >> c & 1) && v[c] + pre > q.qmin[(size_t)e * q.R + c]) in_quota = false;
             }
-            if (i >= 0) q.over_quota[i] = in_quota ? 0 : 1;
+            if (i >= 0) {
+                q.over_quota[i] = in_quota ? 0 : 1;
+                if (q.cur_label) {
+                    q.chg_packed[x] = (i << 1) | (in_quota ? 0 : 1);
+                    q.chg_flag[x] = q.cur_label[i] != (in_quota ? NOSPLAN_LABEL_IN_QUOTA : NOSPLAN_LABEL_OVER_QUOTA);
+                }
+            }
         }
         __syncthreads();
     }
@@ -375,17 +384,25 @@ using namespace nsp;
 extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                             const nosplan_quotas* qs, const nosplan_quota_pods* running,
                                             const nosplan_quota_pods* pending, nosplan_quota_out* out, float* ms_h2d, float* ms_k,
-                                            float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes) {
+                                            float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes,
+                                            const nosplan_label_changes* lc) {
     auto fail = [&](int code, const char* msg, const char* detail = "") { if (err) *err = std::string(msg) + detail; return code; };
 #define QCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(NOSPLAN_E_CUDA, #call ": ", cudaGetErrorString(e_)); } while (0)
+    nosplan_quota_out no_out;
+    if (lc && !out) { std::memset(&no_out, 0, sizeof no_out); out = &no_out; }
     if (!qs || !out) return fail(NOSPLAN_E_INVALID, "null quotas or out");
+    if (lc && (!lc->n_changes || lc->capacity < 0 || (lc->capacity > 0 && (!lc->pod || !lc->desired))))
+        return fail(NOSPLAN_E_INVALID, "label changes: n_changes, and pod / desired for a non-zero capacity, are required");
     const int E = qs->n_quotas, R = qs->n_res, NS = qs->n_namespaces;
     const int Pr = running ? running->n_pods : 0, Pp = pending ? pending->n_pods : 0;
     if (R < 4 || R > QR) return fail(NOSPLAN_E_LIMIT, "n_res must be in [4, NOSPLAN_QUOTA_MAX_RES]");
     if (E < 0 || NS < 0 || Pr < 0 || Pp < 0) return fail(NOSPLAN_E_INVALID, "negative size");
     if (qs->gpu_memory_col >= R || (qs->gpu_memory_col >= 0 && qs->gpu_memory_col < 4)) return fail(NOSPLAN_E_INVALID, "gpu_memory_col out of range");
     for (int ns = 0; ns < NS; ++ns) if (qs->ns_quota[ns] >= E) return fail(NOSPLAN_E_INVALID, "ns_quota out of range");
-    const bool want_label = (out->over_quota || out->operator_used || out->ambiguous_order) && Pr > 0 && E > 0;
+    if (lc && Pr > 0 && !lc->current) return fail(NOSPLAN_E_INVALID, "label changes: current labels of the running pods are required");
+    if (lc && Pr >= (1 << 30)) return fail(NOSPLAN_E_LIMIT, "label changes: at most 2^30 - 1 running pods");
+    const bool want_label = (out->over_quota || out->operator_used || out->ambiguous_order || lc) && Pr > 0 && E > 0;
+    const bool want_changes = lc && want_label;
     if (want_label && (!running->priority || !running->creation_ts || !running->name_rank))
         return fail(NOSPLAN_E_INVALID, "operator labelling needs priority, creation_ts and name_rank of the running pods");
     QCU(cudaSetDevice(device));
@@ -399,13 +416,16 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
                  o_mm = put(4 * (size_t)E), o_xm = put(4 * (size_t)E), o_um = put(4 * (size_t)E), o_enf = put((size_t)E),
                  o_rns = put(4 * (size_t)Pr), o_rreq = put(8 * (size_t)Pr * R), o_rmask = put(4 * (size_t)Pr),
                  o_rprio = put(4 * (size_t)Pr), o_rts = put(8 * (size_t)Pr), o_rrank = put(4 * (size_t)Pr),
-                 o_pns = put(4 * (size_t)Pp), o_preq = put(8 * (size_t)Pp * R), o_pmask = put(4 * (size_t)Pp);
+                 o_pns = put(4 * (size_t)Pp), o_preq = put(8 * (size_t)Pp * R), o_pmask = put(4 * (size_t)Pp),
+                 o_cur = put(want_changes ? (size_t)Pr : 0);
     const size_t upload_end = o;
     // outputs (contiguous, one D2H)
     const size_t o_used = put(8 * ER), o_umask = put(4 * (size_t)E), o_amin = put(8 * QR), o_aused = put(8 * QR), o_aover = put(8 * QR),
                  o_amask = put(16), o_guar = put(8 * ER), o_pref = put((size_t)Pp), o_over = put((size_t)Pr), o_opused = put(8 * ER),
-                 o_amb = put(16);
+                 o_amb = put(16), o_nsel = put(16);
     const size_t out_end = o;
+    const size_t o_sel = put(want_changes ? 4 * (size_t)Pr : 0);   // fetched by a second copy of exactly n_changes entries
+    const size_t o_packed = put(want_changes ? 4 * (size_t)Pr : 0), o_flag = put(want_changes ? (size_t)Pr : 0);
     const size_t o_keya = put(8 * (size_t)Pr), o_keyb = put(8 * (size_t)Pr), o_vala = put(4 * (size_t)Pr), o_valb = put(4 * (size_t)Pr),
                  o_segc = put(4 * ((size_t)E + 1)), o_sego = put(4 * ((size_t)E + 2)), o_choff = put(4 * ((size_t)E + 2));
     const int n_chunk_bound = Pr / 256 + E + 1;                 // every quota's last chunk may be partial
@@ -415,9 +435,15 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         cub::DoubleBuffer<unsigned long long> dk(nullptr, nullptr); cub::DoubleBuffer<int32_t> dv(nullptr, nullptr);
         QCU(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, dk, dv, Pr, 0, 64, st));
     }
+    if (want_changes) {
+        size_t sel_bytes = 0;
+        QCU(cub::DeviceSelect::Flagged(nullptr, sel_bytes, (const int32_t*)nullptr, (const uint8_t*)nullptr, (int32_t*)nullptr,
+                                       (int32_t*)nullptr, Pr, st));
+        cub_bytes = std::max(cub_bytes, sel_bytes);
+    }
     const size_t o_cub = put(cub_bytes + 256);
     const size_t total = o;
-    QCU(quota_ctx_ensure(ctx, total, std::max(upload_end, out_end - upload_end)));
+    QCU(quota_ctx_ensure(ctx, total, std::max(upload_end, out_end - upload_end + (want_changes ? 4 * (size_t)Pr + 256 : 0))));
     unsigned char* S = ctx->hs; unsigned char* A = ctx->d;
     auto cp = [&](size_t at, const void* src, size_t bytes) { if (bytes) { if (src) std::memcpy(S + at, src, bytes); else std::memset(S + at, 0, bytes); } };
     cp(o_nsq, qs->ns_quota, 4 * (size_t)NS); cp(o_min, qs->min, 8 * ER); cp(o_max, qs->max, 8 * ER); cp(o_uin, qs->used_init, 8 * ER);
@@ -429,6 +455,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         cp(o_rmask, running->request_mask, 4 * (size_t)Pr); cp(o_rprio, running->priority, 4 * (size_t)Pr);
         cp(o_rts, running->creation_ts, 8 * (size_t)Pr); cp(o_rrank, running->name_rank, 4 * (size_t)Pr);
     }
+    if (want_changes) cp(o_cur, lc->current, (size_t)Pr);
     if (Pp) { cp(o_pns, pending->ns, 4 * (size_t)Pp); cp(o_preq, pending->request, 8 * (size_t)Pp * R); cp(o_pmask, pending->request_mask, 4 * (size_t)Pp); }
 
     cudaEvent_t ev[4];
@@ -457,6 +484,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     q.val_a = (int32_t*)(A + o_vala); q.val_b = (int32_t*)(A + o_valb);
     q.seg_count = (int32_t*)(A + o_segc); q.seg_off = (int32_t*)(A + o_sego);
     q.chunk_off = (int32_t*)(A + o_choff); q.chunk_sum = (long long*)(A + o_chsum); q.n_chunk_bound = n_chunk_bound;
+    if (want_changes) { q.cur_label = A + o_cur; q.chg_packed = (int32_t*)(A + o_packed); q.chg_flag = A + o_flag; }
 
     int n_launch = 0;
     // Used starts from used_init (scalar key set from used_mask)
@@ -511,10 +539,25 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         k_label_chunk_prefix<<<(E + 7) / 8, 256, 0, st>>>(q);
         k_label_chunks<<<cgrid, LABEL_CHUNK, 0, st>>>(q, dv.Current(), 1);
         n_launch += 11;
+        if (want_changes) {                                    // sorted positions whose label differs, compacted in order
+            size_t sb = cub_bytes;
+            QCU(cub::DeviceSelect::Flagged(A + o_cub, sb, (const int32_t*)q.chg_packed, (const uint8_t*)q.chg_flag, (int32_t*)(A + o_sel),
+                                           (int32_t*)(A + o_nsel), Pr, st));
+            n_launch += 2;
+        }
     }
     QCU(cudaGetLastError());
     QCU(cudaEventRecord(ev[2], st));
-    QCU(cudaMemcpyAsync(S, A + upload_end, out_end - upload_end, cudaMemcpyDeviceToHost, st));
+    // one D2H over the span of the outputs the caller asked for (all of them for nosplan_quota_recompute; for the label
+    // changes alone that is the 16-byte counter, and the list follows in a second copy of exactly n_changes entries)
+    size_t d_lo = out_end, d_hi = upload_end;
+    auto span = [&](const void* wanted, size_t at, size_t bytes) { if (wanted && bytes) { d_lo = std::min(d_lo, at); d_hi = std::max(d_hi, at + bytes); } };
+    span(out->used, o_used, 8 * ER); span(out->used_mask, o_umask, 4 * (size_t)E); span(out->agg_min, o_amin, 8 * QR);
+    span(out->agg_used, o_aused, 8 * QR); span(out->agg_overquota, o_aover, 8 * QR); span(out->agg_masks, o_amask, 16);
+    span(out->guaranteed, o_guar, 8 * ER); span(out->prefilter, o_pref, (size_t)Pp);
+    if (want_label) { span(out->over_quota, o_over, (size_t)Pr); span(out->operator_used, o_opused, 8 * ER); span(out->ambiguous_order, o_amb, 16); }
+    if (want_changes) span(lc, o_nsel, 16);
+    if (d_hi > d_lo) QCU(cudaMemcpyAsync(S + (d_lo - upload_end), A + d_lo, d_hi - d_lo, cudaMemcpyDeviceToHost, st));
     QCU(cudaEventRecord(ev[3], st));
     QCU(cudaStreamSynchronize(st));
     auto back = [&](void* dst, size_t at, size_t bytes) { if (dst && bytes) std::memcpy(dst, S + (at - upload_end), bytes); };
@@ -527,14 +570,34 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         if (out->operator_used && ER) std::memset(out->operator_used, 0, 8 * ER);
         if (out->ambiguous_order) *out->ambiguous_order = 0;
     }
+    long long d2h_extra = 0;
+    int rc_changes = NOSPLAN_OK;
+    if (lc) {
+        int32_t n = 0;
+        if (want_changes) std::memcpy(&n, S + (o_nsel - upload_end), 4);
+        *lc->n_changes = n;
+        const int take = std::min(n, lc->capacity);
+        if (take > 0) {
+            unsigned char* L = S + (out_end - upload_end);     // behind the first copy's landing area
+            QCU(cudaMemcpyAsync(L, A + o_sel, 4 * (size_t)take, cudaMemcpyDeviceToHost, st));
+            QCU(cudaStreamSynchronize(st));
+            const int32_t* packed = (const int32_t*)L;
+            for (int k = 0; k < take; ++k) {
+                lc->pod[k] = packed[k] >> 1;
+                lc->desired[k] = (packed[k] & 1) ? NOSPLAN_LABEL_OVER_QUOTA : NOSPLAN_LABEL_IN_QUOTA;
+            }
+            d2h_extra = 4 * (long long)take;
+        }
+        if (n > lc->capacity) rc_changes = fail(NOSPLAN_E_LIMIT, "label changes: more pods to patch than `capacity` (n_changes holds the number)");
+    }
     if (ms_h2d) cudaEventElapsedTime(ms_h2d, ev[0], ev[1]);
     if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
     if (ms_d2h) cudaEventElapsedTime(ms_d2h, ev[2], ev[3]);
     for (auto& e : ev) cudaEventDestroy(e);
     if (launches) *launches = n_launch;
     if (h2d_bytes) *h2d_bytes = (long long)upload_end;
-    if (d2h_bytes) *d2h_bytes = (long long)(out_end - upload_end);
-    return NOSPLAN_OK;
+    if (d2h_bytes) *d2h_bytes = (long long)(d_hi > d_lo ? d_hi - d_lo : 0) + d2h_extra;
+    return rc_changes;
 #undef QCU
 }
 

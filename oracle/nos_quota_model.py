@@ -260,6 +260,20 @@ def patch_pods_and_compute_used(pods: List[Pod], quota_min: Dict[str, int], quot
 # there (RemovePod extension :311-321 -> deletePodIfPresent), so later pods of the same node see the updated Used.
 # `node_pods` must already be in the order the reference's sort gives (least important first, :516).
 # ------------------------------------------------------------------------------------------------------------
+def capacity_info_patches(pods: List[Pod], quota_min: Dict[str, int], quota_max: Dict[str, int],
+                          nvidia_gpu_memory_gb: int) -> List[Tuple[str, str]]:
+    """The Patch calls one PatchPodsAndComputeUsedQuota issues (patchCapacityInfoIfDifferent :120-149): (pod key, desired
+    label) for every pod whose nos.nebuly.com/capacity label differs from the desired value, in the order they are patched."""
+    _, labels = patch_pods_and_compute_used(pods, quota_min, quota_max, nvidia_gpu_memory_gb)
+    by_key = {p.key(): p for p in pods}
+    out = []
+    for key, over in labels:
+        want = "over-quota" if over else "in-quota"
+        if (by_key[key].labels or {}).get("nos.nebuly.com/capacity", "") != want:
+            out.append((key, want))
+    return out
+
+
 def clone_infos(infos: ElasticQuotaInfos) -> ElasticQuotaInfos:
     # elasticquotainfo.go:37-43 clones every map entry separately, so the namespaces of a composite quota become
     # DISTINCT objects in the snapshot: un-reserving a victim only touches the copy of the victim's own namespace.

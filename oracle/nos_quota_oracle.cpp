@@ -63,8 +63,37 @@ bool sum_greater_than(int R, const int64_t* x1, const int64_t* x2, const int64_t
 
 }  // namespace
 
+static int oracle_quota(const nosplan_quotas* q, const nosplan_quota_pods* running, const nosplan_quota_pods* pending,
+                        nosplan_quota_out* out, double* seconds, std::vector<int>* patch_order);
+
 extern "C" int nos_oracle_quota(const nosplan_quotas* q, const nosplan_quota_pods* running, const nosplan_quota_pods* pending,
                                 nosplan_quota_out* out, double* seconds) {
+    return oracle_quota(q, running, pending, out, seconds, nullptr);
+}
+
+// patchCapacityInfoIfDifferent over every quota (elasticquota.go:44-60, :120-149): the pods whose label differs from the
+// desired one, by quota row and inside a quota in the order of the reference's sort
+extern "C" int nos_oracle_label_changes(const nosplan_quotas* q, const nosplan_quota_pods* running, const uint8_t* current,
+                                        int32_t* pod, uint8_t* desired, int32_t* n_changes) {
+    if (!q || !running || !current || !pod || !desired || !n_changes) return NOSPLAN_E_INVALID;
+    std::vector<uint8_t> over((size_t)std::max(1, running->n_pods));
+    nosplan_quota_out out;
+    std::memset(&out, 0, sizeof out);
+    out.over_quota = over.data();
+    std::vector<int> order;
+    const int rc = oracle_quota(q, running, nullptr, &out, nullptr, &order);
+    if (rc != NOSPLAN_OK) return rc;
+    int n = 0;
+    for (int i : order) {
+        const uint8_t want = over[i] ? NOSPLAN_LABEL_OVER_QUOTA : NOSPLAN_LABEL_IN_QUOTA;
+        if (current[i] != want) { pod[n] = i; desired[n] = want; ++n; }
+    }
+    *n_changes = n;
+    return NOSPLAN_OK;
+}
+
+static int oracle_quota(const nosplan_quotas* q, const nosplan_quota_pods* running, const nosplan_quota_pods* pending,
+                        nosplan_quota_out* out, double* seconds, std::vector<int>* patch_order) {
     if (!q || !out) return NOSPLAN_E_INVALID;
     if (q->n_res < 4 || q->n_res > QR) return NOSPLAN_E_LIMIT;
     auto t0 = std::chrono::steady_clock::now();
@@ -195,6 +224,7 @@ extern "C" int nos_oracle_quota(const nosplan_quotas* q, const nosplan_quota_pod
                     if ((mm >> c & 1) && used[c] > q->min[(size_t)e * R + c]) in_quota = false;
                 }
                 if (out->over_quota) out->over_quota[i] = in_quota ? 0 : 1;
+                if (patch_order) patch_order->push_back(i);
             }
             if (out->operator_used)
                 for (int c = 0; c < R; ++c) out->operator_used[(size_t)e * R + c] = (mm >> c & 1) ? used[c] : 0;

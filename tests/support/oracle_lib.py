@@ -94,3 +94,23 @@ def preempt_dryrun(pq, query):
     if rc != 0:
         raise RuntimeError(f"nos_oracle_preempt_dryrun -> {rc}")
     return victim[:query.v.n_pods], status[:n_nodes], nviol[:n_nodes]
+
+
+def label_changes(pq, running, current):
+    """CPU oracle of patchCapacityInfoIfDifferent over every quota -> (pod indices int32, desired labels uint8), in patch order."""
+    from nos_b200 import quota_packing as qp
+    L = lib()
+    L.nos_oracle_label_changes.argtypes = [C.POINTER(qp.CQuotas), C.POINTER(qp.CQuotaPods), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.nos_oracle_label_changes.restype = C.c_int
+    cq, k1 = qp.c_quotas(pq)
+    cr, k2 = qp.c_quota_pods(running)
+    cur = np.ascontiguousarray(current, dtype=np.uint8)
+    if cur.size == 0:
+        cur = np.zeros(1, np.uint8)
+    pod = np.zeros(max(1, running.n_pods), np.int32)
+    desired = np.zeros(max(1, running.n_pods), np.uint8)
+    n = np.zeros(1, np.int32)
+    rc = L.nos_oracle_label_changes(C.byref(cq), C.byref(cr), cur.ctypes.data, pod.ctypes.data, desired.ctypes.data, n.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"nos_oracle_label_changes -> {rc}")
+    return pod[:n[0]].copy(), desired[:n[0]].copy()
