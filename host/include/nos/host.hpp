@@ -119,6 +119,28 @@ struct PartitioningState : std::map<std::string, NodePartitioning> {   // :40-56
 using ClusterState = std::map<std::string, framework::NodeInfo>;       // state.ClusterState.GetNodes()
 }  // namespace state
 
+namespace mig {
+// getGPUSpecAnnotationList (internal/partitioning/mig/partitioner.go:77-94); GPUs in the order given, resources of a GPU in
+// name order (the reference iterates a Go map; the annotations end up in a map, so the order is not observable).
+std::vector<gpu::SpecAnnotation> GetGPUSpecAnnotationList(const state::NodePartitioning& p);
+std::string SpecAnnotationKey(const gpu::SpecAnnotation& a);   // SpecAnnotation.String (pkg/gpu/annotation.go:152-154)
+}  // namespace mig
+
+namespace mps {
+struct MPSResource {                                           // nvidiav1.MPSResource as ToPluginConfig fills it
+    std::string Name, Rename;
+    int MemoryGB = 0;
+    std::vector<std::string> Devices;
+    int Replicas = 0;
+};
+struct PluginConfig {                                          // nvidiav1.Config, the fields ToPluginConfig sets
+    std::string MigStrategy = "none";
+    bool FailRequestsGreaterThanOne = true;
+    std::vector<MPSResource> Resources;
+};
+PluginConfig ToPluginConfig(const state::NodePartitioning& p); // internal/partitioning/mps/partitioner.go:123-157
+}  // namespace mps
+
 namespace core {
 
 enum class Kind { MIG = NOSPLAN_KIND_MIG, MPS = NOSPLAN_KIND_MPS };
@@ -191,6 +213,21 @@ private:
     nosplan_t* h_ = nullptr;
     nosplan_stats stats_{};
 };
+
+// What Actuator.Apply (core/actuator.go:39-66) writes, as data: per node of the desired state, in map order, the node
+// annotations after mig Partitioner.ApplyPartitioning (internal/partitioning/mig/partitioner.go:43-74: old
+// nos.nebuly.com/spec-gpu* keys dropped, one spec annotation per (GPU, profile), the plan id) or, for MPS, the device-plugin
+// ConfigMap entry and node label of mps Partitioner.ApplyPartitioning (internal/partitioning/mps/partitioner.go:60-112).
+// Throws Error where the reference returns one: a node of the plan that is not in the cluster ("failed to get node"), a
+// resource that is not a slice of the kind.
+struct NodePatch {
+    std::string node;
+    std::map<std::string, std::string> annotations;            // MIG: the node's full annotation map after the patch
+    std::string configKey;                                     // MPS: "<node>-<plan id>" (DevicePluginConfigKeyFormat, :38)
+    mps::PluginConfig config;                                  // MPS: ToPluginConfig(partitioning)
+};
+struct ApplyResult { bool applied = false; std::vector<NodePatch> patches; };
+ApplyResult Apply(Kind kind, const state::ClusterState& cluster, const Snapshot& snapshot, const PartitioningPlan& plan);
 
 // Actuator.Apply's decision (core/actuator.go:39-66): false when the desired state equals the current one or is empty;
 // otherwise the node names that Apply would hand to the Partitioner.  changedOnly = skip nodes whose partitioning

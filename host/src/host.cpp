@@ -323,6 +323,41 @@ bool PartitioningState::Equal(const PartitioningState& other) const {
 }  // namespace state
 
 // ---------------------------------------------------------------------------------------------------------------
+namespace mig {
+std::vector<gpu::SpecAnnotation> GetGPUSpecAnnotationList(const state::NodePartitioning& p) {
+    std::vector<gpu::SpecAnnotation> res;
+    for (auto& g : p.GPUs)
+        for (auto& [r, q] : g.Resources) {
+            auto profile = slice_profile_of(core::Kind::MIG, r);
+            if (!profile) throw Error("invalid input string, required format is nvidia\\.com\\/mig-\\d+g\\.\\d+gb");
+            res.push_back(gpu::SpecAnnotation{*profile, g.GPUIndex, q});
+        }
+    return res;
+}
+std::string SpecAnnotationKey(const gpu::SpecAnnotation& a) {
+    return std::string(kSpecPrefix) + "-" + std::to_string(a.Index) + "-" + a.ProfileName;
+}
+}  // namespace mig
+
+namespace mps {
+PluginConfig ToPluginConfig(const state::NodePartitioning& p) {
+    PluginConfig cfg;
+    for (auto& g : p.GPUs)
+        for (auto& [r, q] : g.Resources) {
+            auto profile = slice_profile_of(core::Kind::MPS, r);
+            if (!profile) throw Error("invalid input string, required format is nvidia\\.com/gpu-\\d+gb");
+            MPSResource m;
+            m.Name = "nvidia.com/gpu";
+            m.Rename = starts_with(r, "nvidia.com/") ? r.substr(11) : r;       // strings.TrimPrefix(r, constant.NvidiaResourcePrefix)
+            m.MemoryGB = mps_size_gb(*profile);
+            m.Devices = {std::to_string(g.GPUIndex)};
+            m.Replicas = q;
+            cfg.Resources.push_back(std::move(m));
+        }
+    return cfg;
+}
+}  // namespace mps
+
 namespace core {
 
 const Node* Snapshot::GetNode(const std::string& name) const {
@@ -583,6 +618,34 @@ std::vector<std::string> NodesToPartition(const Snapshot& snapshot, const Partit
         out.push_back(name);
     }
     return out;
+}
+
+ApplyResult Apply(Kind kind, const state::ClusterState& cluster, const Snapshot& snapshot, const PartitioningPlan& plan) {
+    ApplyResult res;
+    if (snapshot.GetPartitioningState().Equal(plan.DesiredState) || plan.DesiredState.IsEmpty()) return res;
+    for (auto& [name, np] : plan.DesiredState) {
+        auto it = cluster.find(name);
+        if (it == cluster.end() || !it->second.node) throw Error("failed to get node " + name + ": not found");
+        NodePatch patch;
+        patch.node = name;
+        try {
+            if (kind == Kind::MIG) {
+                auto list = mig::GetGPUSpecAnnotationList(np);
+                for (auto& [k, v] : it->second.node->annotations)
+                    if (!starts_with(k, kSpecPrefix)) patch.annotations[k] = v;
+                for (auto& a : list) patch.annotations[mig::SpecAnnotationKey(a)] = std::to_string(a.Quantity);
+                patch.annotations["nos.nebuly.com/spec-partitioning-plan"] = plan.GetId();
+            } else {
+                patch.config = mps::ToPluginConfig(np);
+                patch.configKey = name + "-" + plan.GetId();
+            }
+        } catch (const Error& e) {
+            throw Error("error partitioning node " + name + ": " + e.what());
+        }
+        res.patches.push_back(std::move(patch));
+    }
+    res.applied = true;
+    return res;
 }
 
 }  // namespace core

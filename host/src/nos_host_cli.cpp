@@ -8,10 +8,15 @@
 //   numpods <n>
 //   pod <namespace> <name> <priority|->  container <res>=<n>,...|-   init <res>=<n>,...|-
 //   sa|sb <node> [<gpu index> <res>=<n>,...]   (two partitioning states for `run equal`)
-//   run plan | run pack | run state | run diff | run equal
+//   planid <id>             (plan id for `run apply`; default "plan")
+//   run plan | run pack | run state | run diff | run equal | run apply | run pluginconfig
 // stdout: `run plan`  -> "node <name>" / "gpu <index> <res>=<n>,..." lines, then "stats ..." ;
 //         `run pack`  -> one "<array> v v v" line per packed buffer;  `run state` -> the snapshot's current state;
 //         `run diff`  -> plan, then "apply <node>" per node Actuator.Apply would partition and "changed <node>".
+//         `run apply` -> Actuator.Apply of the desired state `sa` on the cluster: "applied true|false", then per patched node
+//                        "node <name>" and "annotation <k> <v>" lines (MIG) or "configkey <k>" and
+//                        "resource <name> <rename> <memoryGB> <device> <replicas>" lines (MPS);
+//         `run pluginconfig` -> mps.ToPluginConfig of node "n" of `sa`: "resources <count>" and the resource lines.
 // Any nos::Error ends the run with "error <message>" and exit status 1.
 #include <cstdio>
 #include <iostream>
@@ -66,7 +71,7 @@ int main() {
     std::vector<v1::Pod> pods;
     mig::KnownGeometries custom;
     state::PartitioningState stA, stB;
-    std::string line, mode;
+    std::string line, mode, planId = "plan";
     try {
         while (std::getline(std::cin, line)) {
             std::stringstream ss(line);
@@ -96,13 +101,36 @@ int main() {
                     np.GPUs.push_back(g);
                 }
             }
+            else if (cmd == "planid") planId = a;
             else if (cmd == "run") { mode = a; break; }
             else throw Error("unknown directive " + cmd);
         }
         if (mode == "equal") { std::cout << "equal " << (stA.Equal(stB) ? "true" : "false") << '\n'; return 0; }
+        auto print_resources = [](const mps::PluginConfig& cfg) {
+            for (auto& r : cfg.Resources)
+                std::cout << "resource " << r.Name << ' ' << r.Rename << ' ' << r.MemoryGB << ' ' << r.Devices[0] << ' ' << r.Replicas << '\n';
+        };
+        if (mode == "pluginconfig") {
+            mps::PluginConfig cfg = mps::ToPluginConfig(stA["n"]);
+            std::cout << "resources " << cfg.Resources.size() << " migstrategy " << cfg.MigStrategy << " failgt1 " << cfg.FailRequestsGreaterThanOne << '\n';
+            print_resources(cfg);
+            return 0;
+        }
         if (!custom.empty()) mig::SetKnownGeometries(custom);
         core::Snapshot snap = core::TakeSnapshot(kind, cluster);
         if (mode == "state") { print_state(snap.GetPartitioningState()); return 0; }
+        if (mode == "apply") {
+            core::PartitioningPlan plan = core::NewPartitioningPlan(stA);
+            plan.id = planId;
+            core::ApplyResult r = core::Apply(kind, cluster, snap, plan);
+            std::cout << "applied " << (r.applied ? "true" : "false") << '\n';
+            for (auto& p : r.patches) {
+                std::cout << "node " << p.node << '\n';
+                for (auto& [k, v] : p.annotations) std::cout << "annotation " << k << ' ' << v << '\n';
+                if (kind == core::Kind::MPS) { std::cout << "configkey " << p.configKey << '\n'; print_resources(p.config); }
+            }
+            return 0;
+        }
         if (mode == "pack") {
             core::Packed pk = core::Pack(snap, pods);
             dump("profiles", pk.profiles); dump("models", pk.models); dump("others", pk.others); dump("node_names", pk.nodeNames);

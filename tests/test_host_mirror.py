@@ -169,3 +169,51 @@ def test_partitioning_state_equal_golden():
                     lines.append(f"{tag} {node} {g['gpu_index']} " + (",".join(f"{k}={v}" for k, v in g["resources"].items()) or "-"))
         code, out = hc.run("\n".join(lines + ["run equal"]) + "\n")
         assert code == 0 and out.strip() == ("equal true" if c["expected"] else "equal false"), (c["name"], out)
+
+
+def test_actuator_apply_golden():
+    """internal/partitioning/mig/partitioner_test.go:39-262 (TestActuator__Apply) through nos::core::Apply: which nodes are
+    patched and the annotations each ends up with (the plan-id annotation is excluded, as in the reference's test)."""
+    cases = json.load(open(os.path.join(HERE, "golden", "actuator_apply.json")))["apply_cases"]
+    for c in cases:
+        lines = ["kind mig", "planid 1700000000"]
+        for name, n in c["nodes"].items():
+            lines.append(f"node {name}")
+            lines += [f"label {k} {v}" for k, v in n["labels"].items()] + [f"annotation {k} {v}" for k, v in n["annotations"].items()]
+        for node, gpus in c["desired"].items():
+            lines.append(f"sa {node}")
+            lines += [f"sa {node} {g['gpu_index']} " + (",".join(f"{k}={v}" for k, v in g["resources"].items()) or "-") for g in gpus]
+        code, out = hc.run("\n".join(lines + ["run apply"]) + "\n")
+        if c["expected_err"]:
+            assert code == 1 and out.startswith("error failed to get node"), (c["name"], out)
+            continue
+        assert code == 0, (c["name"], out)
+        rows = out.strip().splitlines()
+        assert rows[0] == ("applied true" if c["expected_applied"] else "applied false"), (c["name"], out)
+        got, cur = {name: dict(n["annotations"]) for name, n in c["nodes"].items()}, None      # un-patched nodes keep theirs
+        for r in rows[1:]:
+            t = r.split(" ")
+            if t[0] == "node":
+                cur = got[t[1]] = {}
+            elif t[0] == "annotation":
+                cur[t[1]] = t[2]
+        for node, exp in c["expected_annotations"].items():
+            plan_id = got[node].pop("nos.nebuly.com/spec-partitioning-plan", None)
+            assert got[node] == exp, (c["name"], node, got[node])
+            assert plan_id == ("1700000000" if c["expected_applied"] else None)
+
+
+def test_to_plugin_config_golden():
+    """internal/partitioning/mps/partitioner_test.go:36-82 (TestToPluginConfig) through nos::mps::ToPluginConfig."""
+    cases = json.load(open(os.path.join(HERE, "golden", "actuator_apply.json")))["plugin_config_cases"]
+    for c in cases:
+        lines = ["kind mps", "sa n"] + [f"sa n {g['gpu_index']} " + ",".join(f"{k}={v}" for k, v in g["resources"].items()) for g in c["gpus"]]
+        code, out = hc.run("\n".join(lines + ["run pluginconfig"]) + "\n")
+        if c["expected_err"]:
+            assert code == 1 and out.startswith("error invalid input string"), (c["name"], out)
+            continue
+        rows = out.strip().splitlines()
+        assert code == 0 and rows[0] == f"resources {c['expected_len']} migstrategy none failgt1 1", (c["name"], out)
+        if "derived_resources" in c:
+            got = sorted(tuple(r.split(" ")[1:]) for r in rows[1:])
+            assert got == sorted(tuple(str(x) for x in r) for r in c["derived_resources"])
