@@ -403,7 +403,9 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     put(L.model_off, sizeof(int32_t) * (n_models + 1));
     put(L.geom, 16 * (size_t)n_rows);
     put(L.node_gpu_count, 4 * (size_t)N);
-    put(L.gpu_model, 4 * NG); put(L.gpu_mem, 4 * NG);
+    // only the array of the snapshot's kind travels (model ids: MIG, memory sizes: MPS); the other pointer aliases it, its
+    // values are read into registers by shared code and never used
+    if (mig) { put(L.gpu_model, 4 * NG); L.gpu_mem = L.gpu_model; } else { put(L.gpu_mem, 4 * NG); L.gpu_model = L.gpu_mem; }
     put(L.gpu_used, 16 * NG); put(L.gpu_free, 16 * NG);
     put(L.gpu_umask, 2 * NG); put(L.gpu_fmask, 2 * NG);
     put(L.node_alloc, 8 * (size_t)N * R); put(L.node_req, 8 * (size_t)N * R);
@@ -442,8 +444,8 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     if (n_rows) std::memcpy(S + L.geom, s->geom_counts, 16 * (size_t)n_rows);
     struct Seg { size_t off; const void* src; size_t bytes; bool direct; };
     Seg segs[11] = {
-        {L.node_gpu_count, s->node_gpu_count, 4 * (size_t)N, false}, {L.gpu_model, s->gpu_model, 4 * NG, false},
-        {L.gpu_mem, s->gpu_memory_gb, 4 * NG, false}, {L.gpu_used, s->gpu_used, 16 * NG, false}, {L.gpu_free, s->gpu_free, 16 * NG, false},
+        {L.node_gpu_count, s->node_gpu_count, 4 * (size_t)N, false}, {L.gpu_model, s->gpu_model, mig ? 4 * NG : 0, false},
+        {L.gpu_mem, s->gpu_memory_gb, mig ? 0 : 4 * NG, false}, {L.gpu_used, s->gpu_used, 16 * NG, false}, {L.gpu_free, s->gpu_free, 16 * NG, false},
         {L.gpu_umask, s->gpu_used_mask, 2 * NG, false}, {L.gpu_fmask, s->gpu_free_mask, 2 * NG, false},
         {L.node_alloc, s->node_alloc, 8 * (size_t)N * R, false}, {L.node_req, s->node_requested, 8 * (size_t)N * R, false},
         {L.node_allowed, s->node_allowed_pods, 4 * (size_t)N, false}, {L.node_npods, s->node_num_pods, 4 * (size_t)N, false}};
@@ -454,7 +456,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
             cudaPointerAttributes at;
             g.direct = g.bytes >= (128u << 10) && cudaPointerGetAttributes(&at, g.src) == cudaSuccess && at.type == cudaMemoryTypeHost;
             if (g.direct) any_direct = true;
-            else std::memcpy(S + g.off, g.src, g.bytes);
+            else if (g.bytes) std::memcpy(S + g.off, g.src, g.bytes);
         }
         (void)cudaGetLastError();
     }

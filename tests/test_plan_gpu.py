@@ -146,6 +146,26 @@ def test_errors_are_reported_not_crashes(eng):
     eng.plan(s, p, None, 0)                               # the handle stays usable
 
 
+def test_errors_while_the_node_dma_is_in_flight(eng):
+    """On a snapshot large enough for its node arrays to be in flight while the host validates: an error found in a node, an
+    error found in a pod, and both at once come back as codes, and the handle keeps working -- with results identical to
+    the oracle's."""
+    s, p = synth.mig_cluster(2500, 8, 3000, seed=21)
+    good_model, good_qty = int(s.gpu_model[8 * 1700]), int(p.scalar_qty[5])
+    s.gpu_model[8 * 1700] = 99
+    with pytest.raises(capi.NosplanError, match="node 1700: GPU model id out of range"):
+        eng.plan(s, p, None, pk.FILTER_RESOURCES_FIT)
+    p.scalar_qty[5] = 0                                   # a pod error as well: whichever is reported, it is an error
+    with pytest.raises(capi.NosplanError):
+        eng.plan(s, p, None, pk.FILTER_RESOURCES_FIT)
+    s.gpu_model[8 * 1700] = good_model
+    with pytest.raises(capi.NosplanError, match="pod 5"):
+        eng.plan(s, p, None, pk.FILTER_RESOURCES_FIT)
+    p.scalar_qty[5] = good_qty
+    for _ in range(3):
+        check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "after errors")
+
+
 def test_paths_taken(eng):
     """The node-parallel pass must be the one that produced the saturating plans, the sequential sweep the others."""
     s, p = synth.mig_cluster(200, 8, 1000, seed=5)
