@@ -303,6 +303,8 @@ def run_ours(args):
         "gpu_launches": int(st["kernel_launches"]) * args.steps,
         "clocks": clocks,
     }
+    if world == 1 and args.batch > 1:
+        line["batched"] = batched_plans(torch, capi, eng, ext, flush, args, local)
     if world == 1 and not args.no_cpu_baseline:
         from support import oracle_lib as ol
         n = min(n_full, 450)
@@ -322,6 +324,52 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def batched_plans(torch, capi, eng0, ext0, flush, args, local):
+    """B independent Plan() problems in flight at once on ONE GPU -- what the reference's two controllers
+    (MIG and MPS planners, cmd/gpupartitioner/gpupartitioner.go:215-250) or several pending-pod batches give.  Every problem
+    is a snapshot of the bench workload's recipe under its own seed on its own handle and stream, resident in HBM; all streams
+    are released by one event behind the L2 flush and the step lasts until the last one finishes.  Reported next to the
+    single-problem figure, never instead of it."""
+    B = args.batch
+    engs, exts, cands = [eng0], [ext0], 0
+    dev = torch.device("cuda", local)
+    for b in range(1, B):
+        snap_b, pods_b = make_workload(args.workload, seed_offset=b)
+        e = capi.Engine(local)
+        e.upload(snap_b, pods_b, None, FILTER_RESOURCES_FIT)
+        engs.append(e); exts.append(torch.cuda.ExternalStream(e.stream(), device=dev))
+    for e in engs:
+        e.set_kernel_events(False)
+
+    def step():
+        with torch.cuda.stream(ext0):
+            flush.zero_()
+        go = torch.cuda.Event(enable_timing=True)
+        go.record(ext0)
+        for x in exts[1:]:
+            x.wait_event(go)
+        for e in engs:
+            e.run()
+        ends = []
+        for x in exts:
+            ev = torch.cuda.Event(enable_timing=True); ev.record(x); ends.append(ev)
+        sts = [e.download()[2] for e in engs]                 # synchronises every stream
+        return max(go.elapsed_time(ev) for ev in ends), sum(int(st["candidates"]) for st in sts)
+
+    for _ in range(3):
+        step()
+    ms = []
+    for _ in range(args.steps):
+        t, cands = step()
+        ms.append(t)
+    for e in engs[1:]:
+        e.close()
+    eng0.set_kernel_events(True)
+    return {"problems": B, "value": cands * len(ms) / (sum(ms) / 1e3), "unit": "candidates/s", "ms_per_step": float(np.mean(ms)),
+            "ms_p50": float(np.median(ms)), "candidates_per_step": cands,
+            "note": f"{B} independent snapshots of the same recipe (different seeds), one handle and stream each, all resident"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -330,6 +378,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="mig-10k", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--batch", type=int, default=4, help="N=1 only: also time this many independent Plan() problems in flight at once (0/1 = skip)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
