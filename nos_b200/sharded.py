@@ -163,3 +163,88 @@ class SlicedPlanner:
             self.engine.slice_mid(self.rank, self.world, self.tot_all.data_ptr(), self.local.data_ptr(), self.nbytes)
             self._all_gather(self.gathered, self.local)
             self.engine.shard_end(self.gathered.data_ptr(), self.world)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Quota accounting over several GPUs (collective 4): pods are split between the ranks, every rank
+# reserves its own pods into a zero-based Used on its GPU (nosplan_quota_recompute), the partial Used rows are summed and the
+# key masks OR-ed across ranks -- int64 sums and bit-ORs, so any reduction order gives the single-GPU result bit for bit --
+# and every rank then derives the aggregates, the guaranteed over-quotas and the PreFilter verdicts of ITS pending pods from
+# the reduced rows.  The operator's per-quota running sum needs all pods of a quota in one place: `assign_quotas` gives every
+# quota one owner rank (balanced by pod count) and `split_pods_by_owner` routes a pod list accordingly; with that split the
+# labels and the label changes are rank-local, and the reduction of Used still holds (non-owners contribute zero rows).
+# ------------------------------------------------------------------------------------------------------------
+def assign_quotas(pq, pod_ns: np.ndarray, world: int) -> np.ndarray:
+    """-> owner rank of every quota row [E]: largest quota first onto the least loaded rank (ties: lowest rank, lowest row)."""
+    E = len(pq.names)
+    e_of = pq.ns_quota[np.asarray(pod_ns)] if len(pod_ns) else np.zeros(0, np.int32)
+    counts = np.bincount(e_of[e_of >= 0], minlength=E) if E else np.zeros(0, np.int64)
+    owner = np.zeros(E, np.int32)
+    load = np.zeros(world, np.int64)
+    for e in sorted(range(E), key=lambda e: (-int(counts[e]), e)):
+        r = int(np.argmin(load))
+        owner[e] = r
+        load[r] += int(counts[e])
+    return owner
+
+
+def take_pods(pods, idx: np.ndarray):
+    """The sub-list `idx` of a PackedQuotaPods (order kept)."""
+    from . import quota_packing as qp
+    idx = np.asarray(idx, np.int64)
+    return qp.PackedQuotaPods([pods.keys[i] for i in idx] if pods.keys else [], pods.ns[idx], pods.request[idx], pods.request_mask[idx],
+                              pods.priority[idx], pods.creation_ts[idx], pods.name_rank[idx])
+
+
+def split_pods_by_owner(pq, pods, owner: np.ndarray, rank: int, world: int) -> np.ndarray:
+    """Indices of the pods rank `rank` holds: those of the quotas it owns; pods of namespaces without a quota go round-robin."""
+    e_of = pq.ns_quota[pods.ns] if pods.n_pods else np.zeros(0, np.int32)
+    who = np.where(e_of >= 0, owner[np.maximum(e_of, 0)] if len(owner) else 0, np.arange(pods.n_pods) % world)
+    return np.flatnonzero(who == rank)
+
+
+class ShardedQuota:
+    """One rank of the sharded quota recomputation.  `all_reduce(array, op)` reduces a host int64 / uint32 array over the ranks
+    in place, op in {"sum", "or"}; default: torch.distributed on `device` (NCCL on a GPU, gloo on the CPU)."""
+
+    def __init__(self, engine, rank: int, world: int, device=None, group=None, all_reduce: Optional[Callable] = None):
+        self.engine, self.rank, self.world, self.device, self.group = engine, rank, world, device, group
+        self.all_reduce = all_reduce or self._dist_all_reduce
+
+    def _dist_all_reduce(self, a: np.ndarray, op: str):
+        import torch
+        import torch.distributed as dist
+        t = torch.from_numpy(a.view(np.int64) if a.dtype == np.int64 else a.astype(np.int64))
+        if self.device is not None and str(self.device) != "cpu":
+            t = t.to(self.device)
+        if op == "sum":
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        else:                                                  # NCCL has no bitwise OR: gather the (tiny) masks and fold them here
+            parts = [torch.empty_like(t) for _ in range(self.world)]
+            dist.all_gather(parts, t, group=self.group)
+            for other in parts:
+                t = t | other
+        a[...] = t.cpu().numpy().astype(a.dtype)
+
+    def recompute(self, pq, running_mine, pending_mine, label: bool = False):
+        """running_mine / pending_mine: this rank's share of the pods.  -> dict as Engine.quota_recompute, with `prefilter`
+        (and, with label=True and an owner split, `over_quota`) for this rank's pods only; Used, aggregates, guaranteed rows
+        and operator_used are the cluster-wide values on every rank."""
+        import dataclasses
+        E, R = len(pq.names), pq.n_res
+        zero = dataclasses.replace(pq, used_init=np.zeros((E, R), np.int64), used_mask=np.zeros(E, np.uint32))
+        part, _ = self.engine.quota_recompute(zero, running_mine if (running_mine is not None and running_mine.n_pods) else None, None)
+        used = np.ascontiguousarray(part["used"], dtype=np.int64).copy()
+        mask = np.ascontiguousarray(part["used_mask"], dtype=np.uint32).copy()
+        op_used = np.ascontiguousarray(part["operator_used"], dtype=np.int64).copy() if label else None
+        self.all_reduce(used, "sum")
+        self.all_reduce(mask, "or")
+        full = dataclasses.replace(pq, used_init=pq.used_init + used, used_mask=(pq.used_mask | mask).astype(np.uint32))
+        res, st = self.engine.quota_recompute(full, None, pending_mine if (pending_mine is not None and pending_mine.n_pods) else None)
+        res = dict(res)
+        if label:
+            self.all_reduce(op_used, "sum")                    # a quota's row is non-zero on its owner only
+            amb = np.array([int(part["ambiguous_order"])], np.int64)
+            self.all_reduce(amb, "or")
+            res["over_quota"], res["operator_used"], res["ambiguous_order"] = part["over_quota"], op_used, int(amb[0])
+        return res, st

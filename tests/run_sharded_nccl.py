@@ -71,6 +71,18 @@ def main():
         ok &= same_a and same_b and same_c
         print(f"rank {rank}/{world} {shape} {regime}: path={st['path']}/{st2['path']} torch-collectives={'OK' if same_a else 'MISMATCH'} "
               f"library-collectives={'OK' if same_b else 'MISMATCH'} sliced[{eng.shard_transport()}]={'OK' if same_c else 'MISMATCH'}", flush=True)
+    # quota accounting with the pods split between the ranks: Used summed / masks OR-ed over NCCL, everything else rank-local
+    pq, run, pend = synth.quota_state(300, 40_000, 4_000, seed=0xC4)
+    exp = ol.quota(pq, run, pend)
+    owner = sharded.assign_quotas(pq, run.ns, world)
+    mine = sharded.split_pods_by_owner(pq, run, owner, rank, world)
+    pmine = np.arange(rank, pend.n_pods, world)
+    sq = sharded.ShardedQuota(eng, rank, world, dev)
+    got, _ = sq.recompute(pq, sharded.take_pods(run, mine), sharded.take_pods(pend, pmine), label=True)
+    same_q = all(np.array_equal(got[k], exp[k]) for k in ("used", "agg_min", "agg_used", "agg_overquota", "guaranteed", "operator_used"))
+    same_q &= np.array_equal(got["prefilter"], exp["prefilter"][pmine]) and np.array_equal(got["over_quota"], exp["over_quota"][mine])
+    ok &= bool(same_q)
+    print(f"rank {rank}/{world} quota 300 quotas / 40000 running ({len(mine)} here) / 4000 pending: sharded-quota={'OK' if same_q else 'MISMATCH'}", flush=True)
     eng.close()
     dist.barrier()
     dist.destroy_process_group()

@@ -75,3 +75,69 @@ def test_gloo_world2_all_gather_and_combine():
         assert acc[:3] == [21, 41, 61]                               # sums of the two ranks' counters
         got = {32 * w + b for w, v in enumerate(placed) for b in range(32) if v >> b & 1}
         assert got == union                                          # OR of the bitmaps
+
+
+# ---- quota accounting split over the ranks (nos_b200/sharded.py:ShardedQuota) ----------------------------------------
+class OracleQuotaEngine:
+    """Stands in for capi.Engine.quota_recompute on CPU (the CUDA path is covered by tests/test_sharded_gpu.py)."""
+
+    def quota_recompute(self, pq, running=None, pending=None):
+        from support import oracle_lib as ol
+        return ol.quota(pq, running, pending), {}
+
+
+def _quota_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from nos_b200 import synth
+    pq, run, pend = synth.quota_state(60, 4000, 600, seed=17)
+    pq.used_init[:] = (np.arange(pq.used_init.size).reshape(pq.used_init.shape) % 5) * 1000
+    owner = sharded.assign_quotas(pq, run.ns, world)
+    mine = sharded.split_pods_by_owner(pq, run, owner, rank, world)
+    pmine = np.arange(rank, pend.n_pods, world)
+    sq = sharded.ShardedQuota(OracleQuotaEngine(), rank, world, torch.device("cpu"))
+    got, _ = sq.recompute(pq, sharded.take_pods(run, mine), sharded.take_pods(pend, pmine), label=True)
+    q.put((rank, mine, pmine, {k: np.asarray(v) for k, v in got.items()}))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_sharded_quota():
+    from nos_b200 import synth
+    from support import oracle_lib as ol
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_quota_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    pq, run, pend = synth.quota_state(60, 4000, 600, seed=17)
+    pq.used_init[:] = (np.arange(pq.used_init.size).reshape(pq.used_init.shape) % 5) * 1000
+    exp = ol.quota(pq, run, pend)
+    seen = np.zeros(run.n_pods, int)
+    for rank, mine, pmine, got in res:
+        for k in ("used", "agg_min", "agg_used", "agg_overquota", "guaranteed", "operator_used"):
+            assert np.array_equal(got[k], exp[k]), (rank, k)
+        assert np.array_equal(got["prefilter"], exp["prefilter"][pmine]) and np.array_equal(got["over_quota"], exp["over_quota"][mine])
+        seen[mine] += 1
+    assert (seen == 1).all()                                         # every running pod on exactly one rank
+
+
+def test_assign_quotas_balances_and_keeps_a_quota_whole():
+    from nos_b200 import synth
+    pq, run, _ = synth.quota_state(200, 20_000, 0, seed=3)
+    for world in (2, 4, 8):
+        owner = sharded.assign_quotas(pq, run.ns, world)
+        sizes = []
+        for r in range(world):
+            idx = sharded.split_pods_by_owner(pq, run, owner, r, world)
+            e = pq.ns_quota[run.ns[idx]]
+            assert (owner[e[e >= 0]] == r).all()
+            sizes.append(len(idx))
+        biggest = np.bincount(pq.ns_quota[run.ns][pq.ns_quota[run.ns] >= 0]).max()
+        assert sum(sizes) == run.n_pods and max(sizes) <= max(biggest, run.n_pods // world + biggest // 2 + 1)

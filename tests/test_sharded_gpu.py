@@ -134,3 +134,61 @@ def test_sliced_reports_when_the_sequential_sweep_is_needed(world):
     snap, pods = synth.mig_cluster(60, 8, 2, seed=3, regime="saturating")      # two pods: lacking but far from saturated
     seen.add(check_sliced(snap, pods, pk.FILTER_NONE, world))
     assert "needs-full" in seen
+
+
+# ---- quota accounting split over the ranks: one Engine and one thread per emulated rank, the reductions through a barrier ----
+class ThreadReduce:
+    def __init__(self, world):
+        import threading
+        self.world, self.slots, self.bar = world, [None] * world, threading.Barrier(world)
+
+    def for_rank(self, rank):
+        def all_reduce(a, op):
+            self.slots[rank] = a.copy()
+            self.bar.wait()
+            tot = self.slots[0].copy()
+            for other in self.slots[1:]:
+                tot = tot + other if op == "sum" else tot | other
+            self.bar.wait()                                   # everyone has read the slots before the next reduction reuses them
+            a[...] = tot
+        return all_reduce
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_quota_equals_single(world):
+    """C4 recipe, pods split by quota owner: Used / aggregates / guaranteed / operator_used identical on every rank to the
+    single-GPU engine and the oracle; PreFilter verdicts and labels identical for the rank's own pods."""
+    import threading
+    pq, run, pend = synth.quota_state(500, 100_000, 10_000, seed=0xC4)
+    exp = ol.quota(pq, run, pend)
+    owner = sharded.assign_quotas(pq, run.ns, world)
+    red = ThreadReduce(world)
+    engines = [capi.Engine(0) for _ in range(world)]
+    out, errs = [None] * world, []
+
+    def work(r):
+        try:
+            mine = sharded.split_pods_by_owner(pq, run, owner, r, world)
+            pmine = np.arange(r, pend.n_pods, world)
+            sq = sharded.ShardedQuota(engines[r], r, world, all_reduce=red.for_rank(r))
+            got, _ = sq.recompute(pq, sharded.take_pods(run, mine), sharded.take_pods(pend, pmine), label=True)
+            out[r] = (mine, pmine, got)
+        except Exception as e:                                # a dead thread would leave the others at the barrier
+            errs.append(e)
+            red.bar.abort()
+
+    ts = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=120)
+    for e in engines:
+        e.close()
+    assert not errs, errs
+    seen = np.zeros(run.n_pods, int)
+    for mine, pmine, got in out:
+        for k in ("used", "agg_min", "agg_used", "agg_overquota", "guaranteed", "operator_used"):
+            assert np.array_equal(got[k], exp[k]), k
+        assert np.array_equal(got["prefilter"], exp["prefilter"][pmine]) and np.array_equal(got["over_quota"], exp["over_quota"][mine])
+        seen[mine] += 1
+    assert (seen == 1).all()
