@@ -200,6 +200,15 @@ int nosplan_download_sharded(nosplan_t* h, nosplan_partitioning* out, nosplan_st
 #define NOSPLAN_SLICED_NOT_APPLICABLE 1
 int nosplan_slice_begin(nosplan_t* h, void* d_totals);
 int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes);
+
+/* Slice mode, problems the node-parallel pass does not cover (nosplan_download reported NOSPLAN_SLICED_NOT_APPLICABLE, the
+ * same verdict on every rank): the reference's sequential sweep (core/planner.go:86-141) run rank after rank in name order.
+ * Rank 0 calls with d_state_in = NULL; every other rank calls once its predecessor's d_state_out block has reached it (any
+ * transport; nosplan_slice_chain_bytes bytes of device memory: lacking vector, running totals, counters, removed tracker
+ * keys).  Every rank must take its turn, also after the lacking vector has emptied (its turn then costs one launch).
+ * Afterwards nosplan_download gives this rank's rows; its stats are cumulative up to this rank, i.e. final on the last one. */
+int64_t nosplan_slice_chain_bytes(nosplan_t* h);
+int nosplan_slice_chain(nosplan_t* h, const void* d_state_in, void* d_state_out);
 int nosplan_run_sliced(nosplan_t* h);
 /* 1: nosplan_run_sliced moves its two blocks over peer memory -- every rank stores its block straight into a mailbox in each
  * peer's HBM (CUDA IPC mapping, NVLink) and raises a flag there; the consuming kernel waits on the flags of its own mailbox,

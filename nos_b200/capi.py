@@ -25,7 +25,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
-    "nosplan_preempt_dryrun", "nosplan_quota_label_changes",
+    "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -407,6 +407,16 @@ class Engine:
 
     def slice_mid(self, rank: int, world: int, d_totals_gathered: int, d_exchange: int, nbytes: int):
         self._check(self.lib.nosplan_slice_mid(self.h, rank, world, d_totals_gathered, d_exchange, nbytes), "nosplan_slice_mid")
+
+    def slice_chain_bytes(self) -> int:
+        self.lib.nosplan_slice_chain_bytes.argtypes = [C.c_void_p]
+        self.lib.nosplan_slice_chain_bytes.restype = C.c_int64
+        return int(self.lib.nosplan_slice_chain_bytes(self.h))
+
+    def slice_chain(self, d_state_in: int, d_state_out: int):
+        self.lib.nosplan_slice_chain.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.nosplan_slice_chain.restype = C.c_int
+        self._check(self.lib.nosplan_slice_chain(self.h, d_state_in or None, d_state_out), "nosplan_slice_chain")
 
     def shard_transport(self) -> str:
         return "peer-memory" if self.lib.nosplan_shard_transport(self.h) else "nccl"

@@ -204,8 +204,8 @@ extern "C" int nosplan_parse_annotations_impl(int device, cudaStream_t st, nospl
     if (A > 0) { cp(o_koff, in->key_off, 4 * ((size_t)A + 1)); cp(o_keys, in->key_bytes, kb); cp(o_voff, in->val_off, 4 * ((size_t)A + 1)); cp(o_vals, in->val_bytes, vb); }
     cp(o_cnt, in->gpu_count, 4 * (size_t)N);
     if (K > 0) { cp(o_poff, in->profile_off, 4 * ((size_t)K + 1)); cp(o_prof, in->profile_bytes, pb); }
-    cudaEvent_t ev[4];
-    for (auto& e : ev) ACU(cudaEventCreate(&e));
+    cudaEvent_t* ev = nullptr;
+    ACU(quota_ctx_events(ctx, &ev));
     ACU(cudaEventRecord(ev[0], st));
     ACU(cudaMemcpyAsync(D, S, upload_end, cudaMemcpyHostToDevice, st));
     ACU(cudaMemsetAsync(D + upload_end, 0, out_end - upload_end, st));
@@ -232,7 +232,6 @@ extern "C" int nosplan_parse_annotations_impl(int device, cudaStream_t st, nospl
     if (ms_h2d) cudaEventElapsedTime(ms_h2d, ev[0], ev[1]);
     if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
     if (ms_d2h) cudaEventElapsedTime(ms_d2h, ev[2], ev[3]);
-    for (auto& e : ev) cudaEventDestroy(e);
     if (h2d_bytes) *h2d_bytes = (long long)upload_end;
     if (d2h_bytes) *d2h_bytes = (long long)(out_end - upload_end);
     auto back = [&](void* dst, size_t at, size_t bytes) { if (dst && bytes) std::memcpy(dst, S + (at - upload_end), bytes); };

@@ -852,6 +852,27 @@ int nosplan_shard_end(nosplan_t* h, const void* d_gathered, int32_t world) {
     return nosplan_shard_end_ex(h, d_gathered, world, h && h->uploaded ? (size_t)nosplan_shard_exchange_bytes(h) : 0, PeerWait{nullptr, 0, 0});
 }
 
+int64_t nosplan_slice_chain_bytes(nosplan_t* h) {
+    if (!h || !h->uploaded) return 0;
+    return (int64_t)(sizeof(ChainHead) + 4 * (((size_t)h->pb.n_keys + 31) / 32));
+}
+
+int nosplan_slice_chain(nosplan_t* h, const void* d_state_in, void* d_state_out) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded || !h->ran || !h->pb.slice_mode) return fail(h, NOSPLAN_E_INVALID, "nosplan_slice_chain before a sliced run of this problem");
+    if (!d_state_out) return fail(h, NOSPLAN_E_INVALID, "null state buffer");
+    CU(h, cudaSetDevice(h->device));
+    DevProblem chain = h->pb;
+    chain.chain_mode = 1;
+    chain.chain_in = static_cast<const unsigned char*>(d_state_in);
+    chain.chain_out = static_cast<unsigned char*>(d_state_out);
+    chain.xf_on = 0;
+    CU(h, launch_sweep(chain, h->d_cand_idx, h->stream));
+    CU(h, cudaEventRecord(h->ev[3], h->stream));
+    h->launches += 1;
+    return NOSPLAN_OK;
+}
+
 int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count, void** d_gpu_mask) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_device_outputs before nosplan_upload");

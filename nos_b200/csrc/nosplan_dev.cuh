@@ -29,6 +29,16 @@ struct __align__(16) RunRec {
 };
 static_assert(sizeof(RunRec) == 48, "RunRec layout");
 
+// State handed from rank to rank by the chained sweep: lackingSlices, the running sum(alloc - requested) per slice column,
+// counters (visited nodes, geometry evaluations, placements, candidate nodes), committed flag, lacking profiles at the start,
+// then the bitmap of tracker keys removed so far.
+struct ChainHead {
+    int32_t lack[16];
+    long long D[16];
+    long long counters[4];
+    int32_t committed, lack_start, pad[2];
+};
+
 struct DevStats {
     long long candidates, visited_nodes, geometry_evals, placements, candidate_nodes;
     int lacking_at_start, lacking_at_end;
@@ -103,6 +113,9 @@ struct DevProblem {
     int fast_eligible;               // every pod class requests at most one slice profile
     int32_t sat_m[KP];               // MIG: M_p, most devices of profile p one GPU can hold (allowed-geometry rows); MPS: from gflags[1]
     int slice_mode;                  // this rank holds only its own slice of the node list: no sequential sweep is possible here
+    // slice mode, the sequential sweep rank after rank (nosplan_slice_chain): k_plan_sweep runs the chain over this rank's
+    // slice, starting from the state its predecessor left (chain_in; NULL = the first rank) and leaving its own in chain_out
+    int chain_mode; const unsigned char* chain_in; unsigned char* chain_out;
     // slice mode with the two exchanges fused into the kernels (peer-memory transport): k_prepass's last CTA pushes the totals,
     // k_tracker_init waits for and folds them, k_plan_parallel's last CTA pushes the exchange block, k_plan_sweep waits and folds
     int xf_on; unsigned xf_epoch;

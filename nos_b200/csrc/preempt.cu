@@ -320,6 +320,8 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
     const int E = qs->n_quotas, R = qs->n_res, NS = qs->n_namespaces, P = vq->n_pods, Nn = vq->n_nodes, B = pq->n_pdbs;
     if (R < 4 || R > PQR) return fail(NOSPLAN_E_LIMIT, "n_res must be in [4, NOSPLAN_QUOTA_MAX_RES]");
     if (E < 0 || NS < 0 || P < 0 || Nn < 0 || B < 0) return fail(NOSPLAN_E_INVALID, "negative size");
+    if (qs->gpu_memory_col >= R || (qs->gpu_memory_col >= 0 && qs->gpu_memory_col < 4)) return fail(NOSPLAN_E_INVALID, "gpu_memory_col out of range");
+    for (int ns = 0; ns < NS; ++ns) if (qs->ns_quota[ns] >= E) return fail(NOSPLAN_E_INVALID, "ns_quota out of range");
     if (B > P_PDBS) return fail(NOSPLAN_E_LIMIT, "n_pdbs exceeds NOSPLAN_PREEMPT_MAX_PDBS");
     if (Nn > 0 && (vq->node_ptr[0] != 0 || vq->node_ptr[Nn] != P)) return fail(NOSPLAN_E_INVALID, "node_ptr must span [0, n_pods]");
     if (!vq->nominated_in_eq || !pq->pod_req || !pq->nominated || !pq->fit_request) return fail(NOSPLAN_E_INVALID, "nominated_in_eq, pod_req, nominated and fit_request are required");
@@ -360,8 +362,8 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
     cp(o_over, vq->over_quota, (size_t)P); cp(o_req, vq->request, 8 * (size_t)P * R); cp(o_rmask, vq->request_mask, 4 * (size_t)P);
     cp(o_alloc, pq->node_alloc, 8 * NR); cp(o_nreq, pq->node_requested, 8 * NR); cp(o_pdba, pq->pdb_allowed, 4 * (size_t)B);
     cp(o_pptr, pq->pod_pdb_ptr, 4 * ((size_t)P + 1)); cp(o_ppdb, pq->pod_pdb, 4 * (size_t)M);
-    cudaEvent_t ev[4];
-    for (auto& e : ev) PCU(cudaEventCreate(&e));
+    cudaEvent_t* ev = nullptr;
+    PCU(quota_ctx_events(ctx, &ev));
     PCU(cudaEventRecord(ev[0], st));
     PCU(cudaMemcpyAsync(A, S, upload_end, cudaMemcpyHostToDevice, st));
     PCU(cudaMemsetAsync(A + upload_end, 0, total - upload_end, st));
@@ -400,7 +402,6 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
     if (ms_h2d) cudaEventElapsedTime(ms_h2d, ev[0], ev[1]);
     if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
     if (ms_d2h) cudaEventElapsedTime(ms_d2h, ev[2], ev[3]);
-    for (auto& e : ev) cudaEventDestroy(e);
     if (launches) *launches = 1 + (Nn > 0);
     if (h2d_bytes) *h2d_bytes = (long long)upload_end;
     if (d2h_bytes) *d2h_bytes = (long long)(out_end - upload_end);

@@ -458,8 +458,8 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     if (want_changes) cp(o_cur, lc->current, (size_t)Pr);
     if (Pp) { cp(o_pns, pending->ns, 4 * (size_t)Pp); cp(o_preq, pending->request, 8 * (size_t)Pp * R); cp(o_pmask, pending->request_mask, 4 * (size_t)Pp); }
 
-    cudaEvent_t ev[4];
-    for (auto& e : ev) QCU(cudaEventCreate(&e));
+    cudaEvent_t* ev = nullptr;
+    QCU(quota_ctx_events(ctx, &ev));
     QCU(cudaEventRecord(ev[0], st));
     QCU(cudaMemcpyAsync(A, S, upload_end, cudaMemcpyHostToDevice, st));
     QCU(cudaMemsetAsync(A + upload_end, 0, total - upload_end, st));
@@ -593,7 +593,6 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     if (ms_h2d) cudaEventElapsedTime(ms_h2d, ev[0], ev[1]);
     if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
     if (ms_d2h) cudaEventElapsedTime(ms_d2h, ev[2], ev[3]);
-    for (auto& e : ev) cudaEventDestroy(e);
     if (launches) *launches = n_launch;
     if (h2d_bytes) *h2d_bytes = (long long)upload_end;
     if (d2h_bytes) *d2h_bytes = (long long)(d_hi > d_lo ? d_hi - d_lo : 0) + d2h_extra;
@@ -605,6 +604,7 @@ extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx) {
     if (!ctx) return;
     if (ctx->d) cudaFree(ctx->d);
     if (ctx->hs) cudaFreeHost(ctx->hs);
+    for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     delete ctx;
 }
 extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new() { return new nosplan_quota_ctx(); }

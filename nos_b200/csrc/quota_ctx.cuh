@@ -6,7 +6,16 @@
 struct nosplan_quota_ctx {
     unsigned char* d = nullptr; size_t d_cap = 0;
     unsigned char* hs = nullptr; size_t hs_cap = 0;
+    cudaEvent_t ev[4] = {};            // phase timing of the entry points, created on first use and kept with the handle
 };
+
+// the context's four timing events (created once; an error path of a call has nothing to give back)
+inline cudaError_t quota_ctx_events(nosplan_quota_ctx* ctx, cudaEvent_t** out) {
+    for (auto& e : ctx->ev)
+        if (!e) { cudaError_t r = cudaEventCreate(&e); if (r != cudaSuccess) return r; }
+    *out = ctx->ev;
+    return cudaSuccess;
+}
 
 // returns cudaSuccess or the failing call's error; buffers are only ever grown
 inline cudaError_t quota_ctx_ensure(nosplan_quota_ctx* ctx, size_t dev_bytes, size_t host_bytes) {

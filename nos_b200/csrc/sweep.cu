@@ -816,11 +816,12 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
         if (tid == 0) { pb.stats->path = 0; pb.stats->pad = 2; }
         return;
     }
-    const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
-    const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0));
+    const ChainHead* cin = pb.chain_mode ? reinterpret_cast<const ChainHead*>(pb.chain_in) : nullptr;
+    const int lack0 = (lane < KP) ? (cin ? cin->lack[lane] : pb.lack[lane]) : 0;
+    const int lack_start = cin ? cin->lack_start : __popc(__ballot_sync(FULL, lack0 > 0));
 
     // ---------------- did the node-parallel pass run, and did its hypothesis hold to the end?
-    if (fast_applicable(pb, lack0, lane)) {
+    if (!pb.chain_mode && fast_applicable(pb, lack0, lane)) {
         if (tid < KP) s_lackend[tid] = pb.lack[tid] - (pb.whole_snapshot ? pb.lack_dec[tid] : 0);
         __syncthreads();
         for (int k = tid; !pb.whole_snapshot && k < pb.n_keys; k += blockDim.x)
@@ -877,7 +878,7 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
             return;
         }
     }
-    if (pb.slice_mode) {
+    if (pb.slice_mode && !pb.chain_mode) {
         // this rank holds only its slice of the node list: the sequential chain cannot run here.  Report it (path 0, no
         // visits); the caller plans this problem unsharded (nosplan_download_sliced returns NOSPLAN_SLICED_NOT_APPLICABLE).
         if (tid == 0) {
@@ -890,7 +891,8 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     }
     // ---------------- sequential sweep.  prologue (whole CTA): tables, run cache, candidate compaction in name order
     load_tables(pb, tb, tid, blockDim.x);
-    for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x) s_removed[w] = 0;
+    for (int w = tid; w < (pb.n_keys + 31) / 32; w += blockDim.x)
+        s_removed[w] = cin ? reinterpret_cast<const unsigned*>(pb.chain_in + sizeof(ChainHead))[w] : 0u;
     for (int r = tid; r < pc.n_cached; r += blockDim.x) { s_runs[r] = pb.runs[r]; s_choff[r] = pb.run_chunk_off[r]; }
     __syncthreads();
     build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
@@ -927,10 +929,11 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
     // ---------------- the chain (warp 0)
     const int n_cand = s_ncand;
     int lack = lack0;                                              // lane p: lackingSlices[p]
-    long long D = (lane < KP) ? pb.tot[lane] : 0;                  // lane p: sum(alloc - requested) of slice column p
-    bool committed = false, upd_unused = false;
+    long long D = (lane < KP) ? (cin ? cin->D[lane] : pb.tot[lane]) : 0;   // lane p: sum(alloc - requested) of slice column p
+    bool committed = cin ? cin->committed != 0 : false, upd_unused = false;
     int dirty_unused = 0;
-    long long st_visited = 0, st_evals = 0, st_place = 0;
+    long long st_visited = cin ? cin->counters[0] : 0, st_evals = cin ? cin->counters[1] : 0, st_place = cin ? cin->counters[2] : 0;
+    const long long cand_before = cin ? cin->counters[3] : 0;
 
     NodeRegs nr;
     if (n_cand > 0 && lack_start > 0) {
@@ -955,10 +958,23 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
         st->candidates = st_visited * pb.P;
         st->geometry_evals = st_evals;
         st->placements = st_place;
-        st->candidate_nodes = lack_start > 0 ? n_cand : 0;   // GetCandidateNodes is not reached on the early return (planner.go:80-83)
+        st->candidate_nodes = cand_before + (lack_start > 0 ? n_cand : 0);   // GetCandidateNodes is not reached on the early return (planner.go:80-83)
         st->lacking_at_start = lack_start;
         st->lacking_at_end = lack_end;
         st->path = 0;
+        if (pb.chain_mode) st->pad = 0;
+    }
+    if (pb.chain_mode && pb.chain_out) {                              // what the next rank starts from
+        ChainHead* co = reinterpret_cast<ChainHead*>(pb.chain_out);
+        if (lane < 16) { co->lack[lane] = lane < KP ? lack : 0; co->D[lane] = lane < KP ? D : 0; }
+        if (lane == 0) {
+            co->counters[0] = st_visited; co->counters[1] = st_evals; co->counters[2] = st_place;
+            co->counters[3] = cand_before + (lack_start > 0 ? n_cand : 0);
+            co->committed = committed ? 1 : 0; co->lack_start = lack_start; co->pad[0] = co->pad[1] = 0;
+        }
+        __syncwarp();
+        unsigned* ro = reinterpret_cast<unsigned*>(pb.chain_out + sizeof(ChainHead));
+        for (int w = lane; w < (pb.n_keys + 31) / 32; w += 32) ro[w] = s_removed[w];
     }
 }
 

@@ -179,6 +179,8 @@ extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_q
     const int E = qs->n_quotas, R = qs->n_res, NS = qs->n_namespaces, P = vq->n_pods, Nn = vq->n_nodes;
     if (R < 4 || R > VQR) return fail(NOSPLAN_E_LIMIT, "n_res must be in [4, NOSPLAN_QUOTA_MAX_RES]");
     if (E < 0 || NS < 0 || P < 0 || Nn < 0) return fail(NOSPLAN_E_INVALID, "negative size");
+    if (qs->gpu_memory_col >= R || (qs->gpu_memory_col >= 0 && qs->gpu_memory_col < 4)) return fail(NOSPLAN_E_INVALID, "gpu_memory_col out of range");
+    for (int ns = 0; ns < NS; ++ns) if (qs->ns_quota[ns] >= E) return fail(NOSPLAN_E_INVALID, "ns_quota out of range");
     if (Nn > 0 && (vq->node_ptr[0] != 0 || vq->node_ptr[Nn] != P)) return fail(NOSPLAN_E_INVALID, "node_ptr must span [0, n_pods]");
     if (!vq->nominated_in_eq) return fail(NOSPLAN_E_INVALID, "nominated_in_eq is required");
     VCU(cudaSetDevice(device));
@@ -201,8 +203,8 @@ extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_q
     cp(o_mm, qs->min_mask, 4 * (size_t)E); cp(o_um, qs->used_mask, 4 * (size_t)E);
     cp(o_ptr, vq->node_ptr, 4 * ((size_t)Nn + 1)); cp(o_ns, vq->ns, 4 * (size_t)P); cp(o_prio, vq->priority, 4 * (size_t)P);
     cp(o_over, vq->over_quota, (size_t)P); cp(o_req, vq->request, 8 * (size_t)P * R); cp(o_rmask, vq->request_mask, 4 * (size_t)P);
-    cudaEvent_t ev[2];
-    for (auto& e : ev) VCU(cudaEventCreate(&e));
+    cudaEvent_t* ev = nullptr;
+    VCU(quota_ctx_events(ctx, &ev));
     VCU(cudaMemcpyAsync(A, S, upload_end, cudaMemcpyHostToDevice, st));
     VCU(cudaMemsetAsync(A + upload_end, 0, total - upload_end, st));
     DevVictims v; std::memset(&v, 0, sizeof v);
@@ -229,7 +231,6 @@ extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_q
     VCU(cudaMemcpyAsync(S, A + upload_end, out_end - upload_end, cudaMemcpyDeviceToHost, st));
     VCU(cudaStreamSynchronize(st));
     if (ms_k) cudaEventElapsedTime(ms_k, ev[0], ev[1]);
-    for (auto& e : ev) cudaEventDestroy(e);
     if (launches) *launches = 1 + (Nn > 0);
     int32_t overflow; std::memcpy(&overflow, S + (o_ovf - upload_end), 4);
     if (overflow) return fail(NOSPLAN_E_LIMIT, "a node's victims come from more than 32 namespaces");

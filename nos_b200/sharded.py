@@ -164,6 +164,37 @@ class SlicedPlanner:
             self._all_gather(self.gathered, self.local)
             self.engine.shard_end(self.gathered.data_ptr(), self.world)
 
+    def chain(self, send: Optional[Callable] = None, recv: Optional[Callable] = None):
+        """For problems the node-parallel pass does not cover (download() raised SlicedNotApplicable on every rank): the
+        sequential sweep rank after rank.  Every rank waits for its predecessor's state block, runs the chain over its slice
+        and hands its own block on; send(tensor, dst) / recv(tensor, src) default to torch.distributed point-to-point.
+        -> this rank's state block (final on the last rank; see chain_counters)."""
+        t = self.torch
+        import torch.distributed as dist
+        n = self.engine.slice_chain_bytes()
+        state_in = t.zeros(n, dtype=t.uint8, device=self.device)
+        state_out = t.zeros(n, dtype=t.uint8, device=self.device)
+        send = send or (lambda x, dst: dist.send(x, dst, group=self.group))
+        recv = recv or (lambda x, src: dist.recv(x, src, group=self.group))
+        stream = t.cuda.ExternalStream(self.engine.stream(), device=self.device)
+        with t.cuda.stream(stream):
+            if self.rank > 0:
+                recv(state_in, self.rank - 1)
+            self.engine.slice_chain(state_in.data_ptr() if self.rank > 0 else 0, state_out.data_ptr())
+            if self.rank + 1 < self.world:
+                send(state_out, self.rank + 1)
+        stream.synchronize()
+        return state_out
+
+
+def chain_counters(state) -> dict:
+    """Counters of a chain state block (ChainHead in nos_b200/csrc/nosplan_dev.cuh) as download()'s stats name them."""
+    raw = state.cpu().numpy() if hasattr(state, "cpu") else np.asarray(state)
+    lack = raw[:64].view(np.int32)
+    c = raw[64 + 128:64 + 128 + 32].view(np.int64)
+    return {"visited_nodes": int(c[0]), "geometry_evals": int(c[1]), "placements": int(c[2]), "candidate_nodes": int(c[3]),
+            "lacking_at_end": int((lack > 0).sum()), "lacking_at_start": int(raw[64 + 128 + 32 + 4:64 + 128 + 32 + 8].view(np.int32)[0])}
+
 
 # ------------------------------------------------------------------------------------------------------------
 # Quota accounting over several GPUs (SURVEY.md section 8e, collective 4): pods are split between the ranks, every rank

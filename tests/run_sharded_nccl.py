@@ -29,8 +29,11 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     eng.shard_init(rank, world, uid[0])
     ok = True
-    for shape, regime in (((4000, 8, 3000), "saturating"), ((1001, 8, 2000), "saturating"), ((500, 8, 900), "satisfiable")):
-        snap, pods = synth.mig_cluster(*shape, seed=31, regime=regime)
+    for shape, regime in (((4000, 8, 3000), "saturating"), ((1001, 8, 2000), "saturating"), ((500, 8, 900), "satisfiable"), ((60, 8, 2), "saturating"), ((150, 8, 700), "satisfiable-7")):
+        seed = 31
+        if "-" in regime:
+            regime, seed = regime.split("-")[0], int(regime.split("-")[1])
+        snap, pods = synth.mig_cluster(*shape, seed=seed, regime=regime)
         ocnt, omsk, ost, _ = ol.plan(snap, pods, None, pk.FILTER_RESOURCES_FIT, ol.INCREMENTAL)
         # (a) collectives through torch.distributed
         eng.upload(snap, pods, None, pk.FILTER_RESOURCES_FIT)
@@ -50,7 +53,7 @@ def main():
         lo, hi = sharded.shard_range(snap.n_nodes, rank, world)
         sl = sharded.slice_snapshot(snap, lo, hi, pad_to=chunk)
         G = snap.gpus_per_node
-        same_c = True
+        same_c, chained = True, False
         for driver in ("torch", "library"):
             eng.upload(sl, pods, None, pk.FILTER_RESOURCES_FIT)
             if driver == "torch":
@@ -68,9 +71,19 @@ def main():
                     same_c &= ost["lacking_at_start"] == 0
             except capi.SlicedNotApplicable:
                 same_c &= st["path"] == 0 and ost["lacking_at_start"] > 0   # the sequential sweep is needed: same verdict on every rank
+                # ... and runs rank after rank, the state block travelling over NCCL point-to-point
+                chainer = sharded.SlicedPlanner(eng, rank, world, dev)
+                state = chainer.chain()
+                cnt, msk, st4 = eng.download()
+                n = (hi - lo) * G
+                same_c &= np.array_equal(cnt[:n], ocnt[lo * G:hi * G]) and np.array_equal(msk[:n], omsk[lo * G:hi * G])
+                dist.broadcast(state, src=world - 1)
+                fin = sharded.chain_counters(state)
+                same_c &= all(fin[k] == ost[k] for k in ("visited_nodes", "placements", "geometry_evals", "candidate_nodes", "lacking_at_end"))
+                chained = True
         ok &= same_a and same_b and same_c
         print(f"rank {rank}/{world} {shape} {regime}: path={st['path']}/{st2['path']} torch-collectives={'OK' if same_a else 'MISMATCH'} "
-              f"library-collectives={'OK' if same_b else 'MISMATCH'} sliced[{eng.shard_transport()}]={'OK' if same_c else 'MISMATCH'}", flush=True)
+              f"library-collectives={'OK' if same_b else 'MISMATCH'} sliced[{eng.shard_transport()}]={'OK' if same_c else 'MISMATCH'}{' (chained sweep)' if chained else ''}", flush=True)
     # quota accounting with the pods split between the ranks: Used summed / masks OR-ed over NCCL, everything else rank-local
     pq, run, pend = synth.quota_state(300, 40_000, 4_000, seed=0xC4)
     exp = ol.quota(pq, run, pend)

@@ -29,4 +29,4 @@ def test_sharded_protocols_on_two_gpus(transport):
                        capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MISMATCH" not in r.stdout and f"sliced[{transport}]=OK" in r.stdout
-    assert r.stdout.count("sharded-quota=OK") == 2
+    assert r.stdout.count("sharded-quota=OK") == 2 and "(chained sweep)" in r.stdout

@@ -88,22 +88,41 @@ def run_sliced_emulated(snap, pods, fm, world):
             out.append((cnt, msk, st))
         except capi.SlicedNotApplicable:
             out.append(None)
+    chained = None
+    if all(o is None for o in out):
+        # the sequential sweep rank after rank: each rank starts from the state block its predecessor left
+        n = engines[0].slice_chain_bytes()
+        states = [torch.zeros(n, dtype=torch.uint8, device=dev) for _ in range(world)]
+        chained = []
+        for r, e in enumerate(engines):
+            e.slice_chain(states[r - 1].data_ptr() if r else 0, states[r].data_ptr())
+            cnt, msk, st = e.download()                      # synchronises: the next rank reads a finished block
+            chained.append((cnt, msk, st))
+        chained = (chained, sharded.chain_counters(states[-1]))
     for e in engines:
         e.close()
-    return out, slices
+    return out, slices, chained
 
 
 def check_sliced(snap, pods, fm, world):
     """Slice mode against the oracle: same counters and this rank's rows where the node-parallel pass stands (or nothing is
-    lacking), the NOT_APPLICABLE verdict on every rank where the single-GPU engine needs its sequential sweep."""
+    lacking); where the single-GPU engine needs its sequential sweep, the NOT_APPLICABLE verdict on every rank and then the
+    chained sweep (nosplan_slice_chain), rank after rank, with the oracle's rows and counters."""
     ocnt, omsk, ost, _ = ol.plan(snap, pods, None, fm, ol.INCREMENTAL)
     e = capi.Engine(0)
     single_path = e.plan(snap, pods, None, fm)[2]["path"]
     e.close()
-    out, slices = run_sliced_emulated(snap, pods, fm, world)
+    out, slices, chained = run_sliced_emulated(snap, pods, fm, world)
     G = snap.gpus_per_node
     if single_path == 0 and ost["lacking_at_start"] > 0:
-        assert all(o is None for o in out)
+        assert all(o is None for o in out) and chained is not None
+        rows, final = chained
+        for k in ("visited_nodes", "placements", "geometry_evals", "candidate_nodes", "lacking_at_start", "lacking_at_end"):
+            assert final[k] == ost[k], (world, k, final[k], ost[k])
+        assert rows[-1][2]["candidates"] == ost["candidates"] and rows[-1][2]["path"] == 0
+        for (cnt, msk, st), (lo, hi) in zip(rows, slices):
+            n = (hi - lo) * G
+            assert np.array_equal(cnt[:n], ocnt[lo * G:hi * G]) and np.array_equal(msk[:n], omsk[lo * G:hi * G])
         return "needs-full"
     for (cnt, msk, st), (lo, hi) in zip(out, slices):
         assert st["path"] == single_path
@@ -126,7 +145,7 @@ def test_sliced_equals_single(world, kind):
 
 
 @pytest.mark.parametrize("world", [2, 4])
-def test_sliced_reports_when_the_sequential_sweep_is_needed(world):
+def test_sliced_chains_the_sequential_sweep_when_it_is_needed(world):
     seen = set()
     for seed in range(5, 11):           # satisfiable demand: unsaturated lacking vector, or nothing lacking at all (planner.go:80-83)
         snap, pods = synth.mig_cluster(150, 8, 700, seed=seed, regime="satisfiable")
@@ -134,6 +153,71 @@ def test_sliced_reports_when_the_sequential_sweep_is_needed(world):
     snap, pods = synth.mig_cluster(60, 8, 2, seed=3, regime="saturating")      # two pods: lacking but far from saturated
     seen.add(check_sliced(snap, pods, pk.FILTER_NONE, world))
     assert "needs-full" in seen
+
+
+def test_sliced_random_small_cases_through_the_chain():
+    """Random small clusters (multi-profile pods, inconsistent node accounts, zero-valued free keys, a PreFilter vector ...):
+    whatever route slice mode takes on two or three ranks -- node-parallel pass, nothing lacking, chained sweep -- rows and
+    counters are the oracle's."""
+    import nos_model as m
+    from support import randcases as rc
+    from test_plan_gpu import _has_zero_qty_slice
+    import torch
+    dev = torch.device("cuda", 0)
+    routes = {"parallel": 0, "nothing": 0, "chained": 0}
+    for seed in range(0, 240):
+        kind_name, nodes, pods, pre, fmode = rc.rand_case(seed, max_nodes=7)
+        kind = pk.KIND_BY_NAME[kind_name]
+        if _has_zero_qty_slice(kind, pods) or len(nodes) < 2:
+            continue
+        snap, pp = pk.pack(kind, nodes, pods, m.DEFAULT_KNOWN_GEOMETRIES)
+        ocnt, omsk, ost, _ = ol.plan(snap, pp, pre, fmode, ol.INCREMENTAL)
+        world = 2 + seed % 2
+        G = snap.gpus_per_node
+        chunk = (snap.n_nodes + world - 1) // world
+        engines, planners, slices = [], [], []
+        for r in range(world):
+            lo, hi = sharded.shard_range(snap.n_nodes, r, world)
+            e = capi.Engine(0)
+            e.upload(sharded.slice_snapshot(snap, lo, hi, pad_to=chunk), pp, pre, fmode)
+            p = sharded.SlicedPlanner(e, r, world, dev, all_gather=lambda dst, src: None)
+            p.prepare()
+            engines.append(e); planners.append(p); slices.append((lo, hi))
+        for e, p in zip(engines, planners):
+            e.slice_begin(p.tot_local.data_ptr())
+        torch.cuda.synchronize()
+        tot_all = torch.cat([p.tot_local for p in planners])
+        for r, (e, p) in enumerate(zip(engines, planners)):
+            e.slice_mid(r, world, tot_all.data_ptr(), p.local.data_ptr(), p.nbytes)
+        torch.cuda.synchronize()
+        gathered = torch.cat([p.local for p in planners])
+        rows, need_chain = [], 0
+        for e in engines:
+            e.shard_end(gathered.data_ptr(), world)
+            try:
+                rows.append(e.download())
+            except capi.SlicedNotApplicable:
+                need_chain += 1
+        assert need_chain in (0, world), f"seed {seed}: the ranks disagree"
+        if need_chain:
+            n = engines[0].slice_chain_bytes()
+            states = [torch.zeros(n, dtype=torch.uint8, device=dev) for _ in range(world)]
+            for r, e in enumerate(engines):
+                e.slice_chain(states[r - 1].data_ptr() if r else 0, states[r].data_ptr())
+                rows.append(e.download())
+            final = sharded.chain_counters(states[-1])
+            routes["chained"] += 1
+        else:
+            final = rows[-1][2]
+            routes["parallel" if final["path"] == 1 else "nothing"] += 1
+        for e in engines:
+            e.close()
+        for k in ("visited_nodes", "placements", "geometry_evals", "lacking_at_start", "lacking_at_end"):
+            assert final[k] == ost[k], (seed, k, final[k], ost[k])
+        for (cnt, msk, st), (lo, hi) in zip(rows, slices):
+            nrow = (hi - lo) * G
+            assert np.array_equal(cnt[:nrow], ocnt[lo * G:hi * G]) and np.array_equal(msk[:nrow], omsk[lo * G:hi * G]), f"seed {seed} rows of rank slice {lo}:{hi}"
+    assert routes["chained"] > 40, routes
 
 
 # ---- quota accounting split over the ranks: one Engine and one thread per emulated rank, the reductions through a barrier ----
