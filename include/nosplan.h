@@ -138,6 +138,17 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
                  const uint8_t* prefilter_ok, int32_t filter_mode,
                  nosplan_partitioning* out, nosplan_stats* stats);
 
+/* Plan() against a snapshot that STAYS in HBM between calls -- the device-side twin of state.ClusterState, the cache the
+ * reference's informers keep current and every TakeSnapshot reads (internal/partitioning/state/cluster_state.go,
+ * internal/partitioning/mig/snapshot_taker.go:31-53).  nosplan_plan_resident plans new pending pods against the node arrays
+ * of the last nosplan_plan / nosplan_upload on this handle without copying them again (Plan() never modifies the snapshot
+ * it is given: partitioner_controller.go:185 plans on a clone).  nosplan_update_nodes overwrites nodes
+ * [first, first + rows->n_nodes) of the resident snapshot from a snapshot struct that holds just those rows (same kind,
+ * profiles, gpus_per_node and n_other; its tables are ignored); the snapshot's shape is fixed by the full upload. */
+int nosplan_plan_resident(nosplan_t* h, const nosplan_pods* pods, const uint8_t* prefilter_ok, int32_t filter_mode,
+                          nosplan_partitioning* out, nosplan_stats* stats);
+int nosplan_update_nodes(nosplan_t* h, int32_t first, const nosplan_snapshot* rows);
+
 /* Host-only: the pod order the engine derives before uploading.  Replaces: NewPodSorter(...).Sort (core/util.go:34-73):
  * stable by priority descending, then by SmallerThan of the first requested profile.  order_out[k] = index of the k-th pod.
  * Where that comparator is a strict weak order on the pods present, a counting sort is used (every stable sort agrees);

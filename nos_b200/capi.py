@@ -26,6 +26,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
+    "nosplan_plan_resident", "nosplan_update_nodes",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -358,8 +359,31 @@ class Engine:
         pre, k3 = self._pre(prefilter_ok, pods.n_pods)
         rc = self.lib.nosplan_plan(self.h, C.byref(cs), C.byref(cp), pre, filter_mode, C.byref(out), C.byref(st))
         self._check(rc, "nosplan_plan")
+        self._snap = snap
         del k1, k2, k3
         return cnt, msk, st.as_dict()
+
+    def plan_resident(self, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0, out=None):
+        """nosplan_plan_resident: new pods against the snapshot the last plan() / upload() left in HBM."""
+        snap = self._snap
+        cp, k2 = c_pods(pods)
+        out, cnt, msk = alloc_partitioning(snap, out)
+        st = CStats()
+        pre, k3 = self._pre(prefilter_ok, pods.n_pods)
+        self.lib.nosplan_plan_resident.argtypes = [C.c_void_p, C.POINTER(CPods), C.c_void_p, C.c_int32, C.POINTER(CPartitioning), C.POINTER(CStats)]
+        self.lib.nosplan_plan_resident.restype = C.c_int
+        rc = self.lib.nosplan_plan_resident(self.h, C.byref(cp), pre, filter_mode, C.byref(out), C.byref(st))
+        self._check(rc, "nosplan_plan_resident")
+        del k2, k3
+        return cnt, msk, st.as_dict()
+
+    def update_nodes(self, first: int, rows: PackedSnapshot):
+        """nosplan_update_nodes: overwrite nodes [first, first + rows.n_nodes) of the resident snapshot."""
+        cs, k1 = c_snapshot(rows)
+        self.lib.nosplan_update_nodes.argtypes = [C.c_void_p, C.c_int32, C.POINTER(CSnapshot)]
+        self.lib.nosplan_update_nodes.restype = C.c_int
+        self._check(self.lib.nosplan_update_nodes(self.h, first, C.byref(cs)), "nosplan_update_nodes")
+        del k1
 
     def upload(self, snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0):
         cs, k1 = c_snapshot(snap)

@@ -125,12 +125,20 @@ struct Layout {            // byte offsets into the arena / staging buffer
         cmin_cpu, cmin_mem, cmin_eph, upload_end, placed, entry_lack, total;
 };
 
-int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes) {
+int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes, size_t keep_bytes = 0) {
     if (dev_bytes > h->d_cap) {
-        if (h->d_arena) CU(h, cudaFree(h->d_arena));
-        h->d_arena = nullptr; h->d_cap = 0;
+        unsigned char* old = h->d_arena;
         size_t cap = dev_bytes + dev_bytes / 4 + (1 << 20);
-        CU(h, cudaMalloc(&h->d_arena, cap));
+        unsigned char* fresh = nullptr;
+        if (old && !keep_bytes) { CU(h, cudaFree(old)); old = nullptr; h->d_arena = nullptr; h->d_cap = 0; }
+        CU(h, cudaMalloc(&fresh, cap));
+        if (old) {                                           // a resident snapshot moves with the arena
+            cudaError_t e = cudaMemcpyAsync(fresh, old, keep_bytes, cudaMemcpyDeviceToDevice, h->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+            if (e != cudaSuccess) { cudaFree(fresh); return fail(h, NOSPLAN_E_CUDA, "moving the resident snapshot: %s", cudaGetErrorString(e)); }
+            CU(h, cudaFree(old));
+        }
+        h->d_arena = fresh;
         h->d_cap = cap;
     }
     if (stage_bytes > h->h_cap) {
@@ -360,10 +368,14 @@ static int run_pre(nosplan* h, bool split) {
     return NOSPLAN_OK;
 }
 
-int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
-                   int32_t filter_mode) {
+}  // extern "C"
+
+// keep: the node arrays of the last full upload are still in the arena and are planned against again (s = &h->res_snap)
+static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
+                       int32_t filter_mode, bool keep) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!s || !pods) return fail(h, NOSPLAN_E_INVALID, "null snapshot or pods");
+    if (!keep) h->nodes_resident = false;
     h->uploaded = h->ran = h->pre_done = false;
     // NOSPLAN_TRACE=1: per-phase host microseconds of this call on stderr
     const bool trace = getenv("NOSPLAN_TRACE") != nullptr;
@@ -431,7 +443,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     const size_t bound = part1_end + al(sizeof(RunRec) * (size_t)P) + al(4 * ((size_t)P + 1)) + 3 * al(8 * (size_t)P) + 4096;
     CU(h, cudaSetDevice(h->device));
     const size_t out_bytes = al(16 * NG) + al(2 * NG) + al(sizeof(DevStats));
-    int rc = ensure(h, bound, bound, out_bytes);
+    int rc = ensure(h, bound, bound, out_bytes, keep ? h->res_nodes_end : 0);
     if (rc != NOSPLAN_OK) return rc;
     lap("layout+alloc");
 
@@ -439,9 +451,11 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     //      (cudaHostAlloc / cudaHostRegister) the copy engine reads them where they are; otherwise they pass through staging.
     unsigned char* S = h->h_stage;
     unsigned char* A = h->d_arena;
+    if (!keep) {
     if (n_models > 0) std::memcpy(S + L.model_off, s->model_geom_offset, sizeof(int32_t) * (n_models + 1));
     else std::memset(S + L.model_off, 0, sizeof(int32_t));
     if (n_rows) std::memcpy(S + L.geom, s->geom_counts, 16 * (size_t)n_rows);
+    }
     struct Seg { size_t off; const void* src; size_t bytes; bool direct; };
     Seg segs[11] = {
         {L.node_gpu_count, s->node_gpu_count, 4 * (size_t)N, false}, {L.gpu_model, s->gpu_model, mig ? 4 * NG : 0, false},
@@ -450,7 +464,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         {L.node_alloc, s->node_alloc, 8 * (size_t)N * R, false}, {L.node_req, s->node_requested, 8 * (size_t)N * R, false},
         {L.node_allowed, s->node_allowed_pods, 4 * (size_t)N, false}, {L.node_npods, s->node_num_pods, 4 * (size_t)N, false}};
     bool any_direct = false;
-    if (N) {
+    if (N && !keep) {
         for (Seg& g : segs) {
             // small arrays are cheaper to memcpy into staging than to give a DMA descriptor of their own
             cudaPointerAttributes at;
@@ -461,9 +475,9 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
         (void)cudaGetLastError();
     }
     CU(h, cudaEventRecord(h->ev[0], h->stream));
-    {
+    h->dbg_n = 0;
+    if (!keep) {
         size_t from = 0;
-        h->dbg_n = 0;
         auto mark = [&](size_t bytes, bool direct) {          // NOSPLAN_TRACE: one event per copy
             if (!trace || h->dbg_n >= 32) return;
             if (!h->dbg_ev[h->dbg_n]) cudaEventCreate(&h->dbg_ev[h->dbg_n]);
@@ -519,7 +533,7 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     lap("nodes queued");
     // per-node validation, while the copy engine works (k_prepass, the only kernel that can already be queued, clamps what it
     // reads; every other kernel is launched after this call has succeeded)
-    for (int i = 0; i < N; ++i) {
+    for (int i = 0; i < N && !keep; ++i) {
         const int ng = s->node_gpu_count[i];
         bool bad = ng < 0 || ng > G;
         if (!bad && mig) {
@@ -678,10 +692,34 @@ int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* 
     pb.placed = (unsigned*)(A + L.placed);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
     lap("pods queued");
-    h->h2d_bytes = L.nodes_end + (L.upload_end - L.pod_cpu);
+    h->h2d_bytes = (keep ? 0 : L.nodes_end) + (L.upload_end - L.pod_cpu);
     h->uploaded = true;
+    if (!keep) {                                             // what a later nosplan_plan_resident / nosplan_update_nodes needs
+        h->res_snap = *s;
+        h->res_pmem.assign(s->profile_mem_gb, s->profile_mem_gb + K); h->res_pgi.assign(s->profile_gi, s->profile_gi + K);
+        h->res_model_off.assign(n_models > 0 ? s->model_geom_offset : nullptr, n_models > 0 ? s->model_geom_offset + n_models + 1 : nullptr);
+        h->res_geom.assign(n_rows ? s->geom_counts : nullptr, n_rows ? s->geom_counts + 16 * (size_t)n_rows : nullptr);
+        nosplan_snapshot& r = h->res_snap;
+        r.profile_mem_gb = h->res_pmem.data(); r.profile_gi = h->res_pgi.data();
+        r.model_geom_offset = h->res_model_off.data(); r.geom_counts = h->res_geom.data();
+        r.node_gpu_count = r.gpu_model = r.gpu_index = r.gpu_memory_gb = nullptr; r.gpu_used = r.gpu_free = nullptr;
+        r.gpu_used_mask = r.gpu_free_mask = nullptr; r.node_alloc = r.node_requested = nullptr;
+        r.node_allowed_pods = r.node_num_pods = nullptr;
+        const size_t offs[11] = {L.node_gpu_count, L.gpu_model, L.gpu_mem, L.gpu_used, L.gpu_free, L.gpu_umask, L.gpu_fmask,
+                                 L.node_alloc, L.node_req, L.node_allowed, L.node_npods};
+        std::memcpy(h->res_off, offs, sizeof offs);
+        h->res_nodes_end = L.nodes_end;
+        h->nodes_resident = true;
+    }
     if (any_direct && !h->in_plan) CU(h, cudaStreamSynchronize(h->stream));   // nothing of the caller's is read after return
     return NOSPLAN_OK;
+}
+
+extern "C" {
+
+int nosplan_upload(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
+                   int32_t filter_mode) {
+    return upload_impl(h, s, pods, prefilter_ok, filter_mode, false);
 }
 
 // Kernels that need the pods: tracker tables reset, k_tracker_init, node-parallel pass, verification / sequential sweep.
@@ -941,6 +979,52 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
     rc = h->pre_done ? run_post(h) : nosplan_run(h);       // upload() already queued the node-only kernels
     if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); return rc; }
     return nosplan_download(h, out, stats);
+}
+
+int nosplan_plan_resident(nosplan_t* h, const nosplan_pods* pods, const uint8_t* prefilter_ok, int32_t filter_mode,
+                          nosplan_partitioning* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->nodes_resident) return fail(h, NOSPLAN_E_INVALID, "nosplan_plan_resident: no snapshot resident on this handle (call nosplan_plan or nosplan_upload first)");
+    h->in_plan = true;
+    int rc = upload_impl(h, &h->res_snap, pods, prefilter_ok, filter_mode, true);
+    h->in_plan = false;
+    if (rc != NOSPLAN_OK) return rc;
+    rc = h->pre_done ? run_post(h) : nosplan_run(h);
+    if (rc != NOSPLAN_OK) return rc;
+    return nosplan_download(h, out, stats);
+}
+
+int nosplan_update_nodes(nosplan_t* h, int32_t first, const nosplan_snapshot* rows) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->nodes_resident) return fail(h, NOSPLAN_E_INVALID, "nosplan_update_nodes: no snapshot resident on this handle");
+    if (!rows) return fail(h, NOSPLAN_E_INVALID, "null rows");
+    const nosplan_snapshot& r = h->res_snap;
+    const int N = r.n_nodes, G = r.gpus_per_node, R = 3 + r.n_profiles + r.n_other, n = rows->n_nodes;
+    if (rows->kind != r.kind || rows->gpus_per_node != G || rows->n_profiles != r.n_profiles || rows->n_other != r.n_other)
+        return fail(h, NOSPLAN_E_INVALID, "nosplan_update_nodes: rows of another shape (kind, gpus_per_node, n_profiles, n_other) than the resident snapshot");
+    if (first < 0 || n < 0 || (long long)first + n > N) return fail(h, NOSPLAN_E_INVALID, "nosplan_update_nodes: nodes [%d, %d) outside the resident snapshot of %d", first, first + n, N);
+    if (n == 0) return NOSPLAN_OK;
+    const bool mig = r.kind == NOSPLAN_KIND_MIG;
+    for (int i = 0; i < n; ++i) {                            // the checks nosplan_upload makes per node
+        const int ng = rows->node_gpu_count[i];
+        if (ng < 0 || ng > G) return fail(h, NOSPLAN_E_INVALID, "node %d: gpu count out of range", first + i);
+        for (int j = 0; mig && j < ng; ++j)
+            if ((unsigned)rows->gpu_model[(size_t)i * G + j] >= (unsigned)r.n_models) return fail(h, NOSPLAN_E_INVALID, "node %d: GPU model id out of range", first + i);
+    }
+    CU(h, cudaSetDevice(h->device));
+    unsigned char* A = h->d_arena;
+    const void* src[11] = {rows->node_gpu_count, mig ? (const void*)rows->gpu_model : nullptr, mig ? nullptr : (const void*)rows->gpu_memory_gb,
+                           rows->gpu_used, rows->gpu_free, rows->gpu_used_mask, rows->gpu_free_mask, rows->node_alloc, rows->node_requested,
+                           rows->node_allowed_pods, rows->node_num_pods};
+    const size_t stride[11] = {4, 4 * (size_t)G, 4 * (size_t)G, 16 * (size_t)G, 16 * (size_t)G, 2 * (size_t)G, 2 * (size_t)G,
+                               8 * (size_t)R, 8 * (size_t)R, 4, 4};
+    for (int k = 0; k < 11; ++k) {
+        if (!src[k]) continue;
+        CU(h, cudaMemcpyAsync(A + h->res_off[k] + stride[k] * (size_t)first, src[k], stride[k] * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+    }
+    CU(h, cudaStreamSynchronize(h->stream));                 // nothing of the caller's is read after return
+    h->ran = false;                                          // the plan of the previous call is stale
+    return NOSPLAN_OK;
 }
 
 int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,

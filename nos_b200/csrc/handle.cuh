@@ -38,6 +38,13 @@ struct nosplan {
     nosplan_quota_ctx* qctx = nullptr;
     nosplan_shard_ctx* sctx = nullptr;
     std::string err;
+    // snapshot kept resident between calls (nosplan_plan_resident / nosplan_update_nodes): shape and small tables of the last
+    // full upload (node arrays of res_snap are not kept: they live in the arena), byte offsets of the node sections
+    bool nodes_resident = false;
+    nosplan_snapshot res_snap{};
+    std::vector<int32_t> res_pmem, res_pgi, res_model_off;
+    std::vector<uint8_t> res_geom;
+    size_t res_off[11] = {}; size_t res_nodes_end = 0;
     // NOSPLAN_TRACE=1 only: one event per H2D copy of the node arrays
     cudaEvent_t dbg_ev[32] = {}; size_t dbg_bytes[32] = {}; bool dbg_direct[32] = {}; int dbg_n = 0;
 };
