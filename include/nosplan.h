@@ -149,6 +149,14 @@ int nosplan_plan_resident(nosplan_t* h, const nosplan_pods* pods, const uint8_t*
                           nosplan_partitioning* out, nosplan_stats* stats);
 int nosplan_update_nodes(nosplan_t* h, int32_t first, const nosplan_snapshot* rows);
 
+/* Change detection for the actuator.  Actuator.Apply (core/actuator.go:39-66) compares the
+ * desired state with the current one as a whole (PartitioningState.Equal, state/partitioning.go:33-56) and then patches EVERY
+ * node of the plan; this call names the nodes whose desired partitioning differs from the snapshot's current one -- compared
+ * as NodePartitioning.Equal compares them, zero-count keys included -- so that only those are patched.  After a Plan() on this
+ * handle (any of nosplan_plan / plan_resident / run); indices ascending (name order), of the handle's own nodes in slice
+ * mode.  More than `capacity` changes: the first `capacity` are returned with NOSPLAN_E_LIMIT, *n_changed holds the number. */
+int nosplan_changed_nodes(nosplan_t* h, int32_t* node_idx, int32_t capacity, int32_t* n_changed);
+
 /* Host-only: the pod order the engine derives before uploading.  Replaces: NewPodSorter(...).Sort (core/util.go:34-73):
  * stable by priority descending, then by SmallerThan of the first requested profile.  order_out[k] = index of the k-th pod.
  * Where that comparator is a strict weak order on the pods present, a counting sort is used (every stable sort agrees);

@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
-    "nosplan_plan_resident", "nosplan_update_nodes",
+    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -376,6 +376,21 @@ class Engine:
         self._check(rc, "nosplan_plan_resident")
         del k2, k3
         return cnt, msk, st.as_dict()
+
+    def changed_nodes(self, capacity=None):
+        """nosplan_changed_nodes -> indices (int32, ascending) of the nodes whose desired partitioning differs from the current one."""
+        cap = self._snap.n_nodes if capacity is None else int(capacity)
+        idx = np.zeros(max(1, cap), np.int32)
+        n = np.zeros(1, np.int32)
+        self.lib.nosplan_changed_nodes.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+        self.lib.nosplan_changed_nodes.restype = C.c_int
+        rc = self.lib.nosplan_changed_nodes(self.h, idx.ctypes.data, cap, n.ctypes.data)
+        if rc != 0:
+            msg = self.lib.nosplan_last_error(self.h)
+            e = NosplanError(f"nosplan_changed_nodes failed ({rc}): {msg.decode() if msg else ''}")
+            e.partial = (idx[:min(int(n[0]), cap)].copy(), int(n[0]))
+            raise e
+        return idx[:int(n[0])]
 
     def update_nodes(self, first: int, rows: PackedSnapshot):
         """nosplan_update_nodes: overwrite nodes [first, first + rows.n_nodes) of the resident snapshot."""
