@@ -50,14 +50,15 @@ __device__ __forceinline__ double p_approx(int c, long long v) { return c == 0 ?
 __device__ __forceinline__ bool p_cmp_col(int c, unsigned ymask) { return c == 0 || c == 1 || (c >= 4 && (ymask >> c & 1)); }
 
 // aggregates over the namespace -> quota map (a composite quota counts once per namespace)
-__global__ void __launch_bounds__(256) k_preempt_aggregate(DevPreempt v) {
-    __shared__ long long s_min[16][PQR], s_over[16][PQR], s_used[16][PQR];
+constexpr int P_AGG_THREADS = 1024, P_AGG_ROWS = P_AGG_THREADS / 16;   // 64 namespaces in flight: each step is a chain of dependent loads
+__global__ void __launch_bounds__(P_AGG_THREADS) k_preempt_aggregate(DevPreempt v) {
+    __shared__ long long s_min[P_AGG_ROWS][PQR], s_over[P_AGG_ROWS][PQR], s_used[P_AGG_ROWS][PQR];
     __shared__ unsigned s_om, s_am;
     const int tid = threadIdx.x, c = tid & 15, j = tid >> 4;
     if (tid == 0) { s_om = 0; s_am = 0; }
     __syncthreads();
     long long mn = 0, ov = 0, us = 0; unsigned om = 0, am = 0;
-    for (int ns = j; ns < v.NS; ns += 16) {
+    for (int ns = j; ns < v.NS; ns += P_AGG_ROWS) {
         const int e = v.ns_quota[ns];
         if (e < 0) continue;
         if (c < v.R) {
@@ -69,10 +70,12 @@ __global__ void __launch_bounds__(256) k_preempt_aggregate(DevPreempt v) {
     s_min[j][c] = mn; s_over[j][c] = ov; s_used[j][c] = us;
     if (c == 0) { if (om) atomicOr(&s_om, om); if (am) atomicOr(&s_am, am); }
     __syncthreads();
-    if (tid < PQR) {
-        long long a = 0, b = 0, d = 0;
-        for (int k = 0; k < 16; ++k) { a += s_min[k][tid]; b += s_over[k][tid]; d += s_used[k][tid]; }
-        v.agg[tid] = a; v.agg[PQR + tid] = b; v.agg[2 * PQR + tid] = d;
+    if (tid < 3 * PQR) {                                       // one thread per (vector, column)
+        const int which = tid / PQR, col = tid % PQR;
+        long long (*src)[PQR] = which == 0 ? s_min : which == 1 ? s_over : s_used;
+        long long a = 0;
+        for (int k = 0; k < P_AGG_ROWS; ++k) a += src[k][col];
+        v.agg[which * PQR + col] = a;
     }
     if (tid == 0) { v.masks[0] = s_om; v.masks[1] = s_am; }
 }
@@ -389,7 +392,7 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
     v.agg = (long long*)(A + o_agg); v.masks = (unsigned*)(A + o_masks); v.state = (uint8_t*)(A + o_state);
     v.status = (int32_t*)(A + o_status); v.nviol = (int32_t*)(A + o_nviol); v.overflow = (int32_t*)(A + o_ovf);
     PCU(cudaEventRecord(ev[1], st));
-    k_preempt_aggregate<<<1, 256, 0, st>>>(v);
+    k_preempt_aggregate<<<1, P_AGG_THREADS, 0, st>>>(v);
     if (Nn > 0) {
         // one node per warp: nodes differ widely in work (victims found or not, reprieve loops), so the block scheduler balances them
         k_preempt_dryrun<<<(Nn + 7) / 8, 256, 0, st>>>(v);

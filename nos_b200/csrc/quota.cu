@@ -187,35 +187,73 @@ __global__ void __launch_bounds__(256) k_quota_prefilter(DevQuota q) {
 }
 
 // ---------------------------------------------------------------- operator labelling
+// pods per quota: block-private histogram in shared memory (a popular quota would otherwise serialise thousands of atomics on
+// one word), flushed with one global atomic per quota the block saw; quota tables too large for it count with
+// warp-aggregated atomics
+constexpr int SEG_HIST = 1024;      // larger quota tables: zeroing and flushing the histogram per block would cost more than it saves
+__device__ __forceinline__ void seg_hist_begin(const DevQuota& q, int* s_hist) {
+    if (q.E <= SEG_HIST) { for (int k = threadIdx.x; k < q.E; k += blockDim.x) s_hist[k] = 0; }
+    __syncthreads();
+}
+__device__ __forceinline__ void seg_hist_add(const DevQuota& q, int* s_hist, int e, bool valid) {
+    if (q.E <= SEG_HIST) { if (valid && e >= 0) atomicAdd(&s_hist[e], 1); return; }
+    const unsigned act = __ballot_sync(0xffffffffu, valid && e >= 0);
+    if (valid && e >= 0) {
+        const unsigned peers = __match_any_sync(act, e);
+        if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&q.seg_count[e], __popc(peers));
+    }
+}
+__device__ __forceinline__ void seg_hist_end(const DevQuota& q, int* s_hist) {
+    __syncthreads();
+    if (q.E <= SEG_HIST)
+        for (int k = threadIdx.x; k < q.E; k += blockDim.x) { const int n = s_hist[k]; if (n) atomicAdd(&q.seg_count[k], n); }
+}
+
 __global__ void __launch_bounds__(256) k_label_keys(DevQuota q, int pass) {
+    __shared__ int s_hist[SEG_HIST];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pass != 0) {
+        seg_hist_begin(q, s_hist);
+        int e = -1;
+        if (i < q.Pr) {
+            // all three keys in one word -- quota row | creationTimestamp - min | priority - min -- when their ranges fit 64 bits
+            const int ns = q.r_ns[i];
+            e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+            const unsigned long long ek = e < 0 ? (unsigned long long)q.E : (unsigned long long)e;
+            q.key_a[i] = (ek << (q.fuse_tbits + q.fuse_pbits)) |
+                         ((unsigned long long)(q.r_ts[i] - q.fuse_ts_min) << q.fuse_pbits) |
+                         (unsigned long long)((long long)q.r_prio[i] - q.fuse_prio_min);
+            q.val_a[i] = i;
+            if (e < 0) q.over_quota[i] = 0;
+        }
+        seg_hist_add(q, s_hist, e, i < q.Pr);
+        seg_hist_end(q, s_hist);
+        return;
+    }
     if (i >= q.Pr) return;
     if (pass == 0) {                                       // least significant key: priority (biased to unsigned)
         q.key_a[i] = (unsigned long long)((long long)q.r_prio[i] - (long long)INT_MIN);
         q.val_a[i] = i;
-    } else {
-        // all three keys in one word -- quota row | creationTimestamp - min | priority - min -- when their ranges fit 64 bits
-        const int ns = q.r_ns[i];
-        const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
-        const unsigned long long ek = e < 0 ? (unsigned long long)q.E : (unsigned long long)e;
-        q.key_a[i] = (ek << (q.fuse_tbits + q.fuse_pbits)) |
-                     ((unsigned long long)(q.r_ts[i] - q.fuse_ts_min) << q.fuse_pbits) |
-                     (unsigned long long)((long long)q.r_prio[i] - q.fuse_prio_min);
-        q.val_a[i] = i;
-        if (e >= 0) atomicAdd(&q.seg_count[e], 1); else q.over_quota[i] = 0;
     }
 }
 __global__ void __launch_bounds__(256) k_label_rekey(DevQuota q, const int32_t* vals, unsigned long long* keys, int pass) {
+    __shared__ int s_hist[SEG_HIST];
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    if (x >= q.Pr) return;
-    const int i = vals[x];
-    if (pass == 1) keys[x] = (unsigned long long)q.r_ts[i] ^ 0x8000000000000000ull;      // creationTimestamp
-    else {                                                                                // quota row; no quota -> sorted last
-        const int ns = q.r_ns[i];
-        const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
-        keys[x] = e < 0 ? (unsigned long long)q.E : (unsigned long long)e;
-        if (e >= 0) atomicAdd(&q.seg_count[e], 1); else q.over_quota[i] = 0;
+    if (pass == 1) {
+        if (x < q.Pr) keys[x] = (unsigned long long)q.r_ts[vals[x]] ^ 0x8000000000000000ull;     // creationTimestamp
+        return;
     }
+    seg_hist_begin(q, s_hist);                                                            // quota row; no quota -> sorted last
+    int e = -1;
+    if (x < q.Pr) {
+        const int i = vals[x];
+        const int ns = q.r_ns[i];
+        e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+        keys[x] = e < 0 ? (unsigned long long)q.E : (unsigned long long)e;
+        if (e < 0) q.over_quota[i] = 0;
+    }
+    seg_hist_add(q, s_hist, e, x < q.Pr);
+    seg_hist_end(q, s_hist);
 }
 constexpr int LABEL_CHUNK = 256;                               // pods per chunk of the labelling scan == its block size
 __global__ void k_label_offsets(DevQuota q) {                  // exclusive scan of the per-quota counts (single thread block)
@@ -362,16 +400,37 @@ __global__ void __launch_bounds__(LABEL_CHUNK) k_label_chunks(DevQuota q, const 
         __syncthreads();
     }
 }
+// one warp per quota, lane = chunk (32 chunks per step, every column's loads in flight together), warp scan per column
 __global__ void __launch_bounds__(256) k_label_chunk_prefix(DevQuota q) {
-    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), c = threadIdx.x & 31;
-    if (e >= q.E || c >= q.R) return;
-    long long run = 0;
-    for (int chunk = q.chunk_off[e]; chunk < q.chunk_off[e + 1]; ++chunk) {
-        const long long t = q.chunk_sum[(size_t)chunk * QR + c];
-        q.chunk_sum[(size_t)chunk * QR + c] = run;
-        run += t;
+    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (e >= q.E) return;                                      // warp-uniform
+    const int c0 = q.chunk_off[e], c1 = q.chunk_off[e + 1];
+    long long carry[QR];
+#pragma unroll
+    for (int c = 0; c < QR; ++c) carry[c] = 0;
+    for (int base = c0; base < c1; base += 32) {
+        const int chunk = base + lane;
+        const bool in = chunk < c1;
+        long long t[QR];
+#pragma unroll
+        for (int c = 0; c < QR; ++c) t[c] = (in && c < q.R) ? q.chunk_sum[(size_t)chunk * QR + c] : 0;
+#pragma unroll
+        for (int c = 0; c < QR; ++c) {
+            if (c >= q.R) break;
+            long long v = t[c];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long u = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += u;
+            }
+            if (in) q.chunk_sum[(size_t)chunk * QR + c] = carry[c] + v - t[c];       // running sum BEFORE the chunk
+            carry[c] += __shfl_sync(0xffffffffu, v, 31);
+        }
     }
-    q.operator_used[(size_t)e * q.R + c] = (q.min_mask[e] >> c & 1) ? run : 0;
+    long long mine = 0;
+#pragma unroll
+    for (int c = 0; c < QR; ++c) if (c == lane) mine = carry[c];
+    if (lane < q.R) q.operator_used[(size_t)e * q.R + lane] = (q.min_mask[e] >> lane & 1) ? mine : 0;
 }
 
 }  // namespace nsp

@@ -38,14 +38,15 @@ __device__ __forceinline__ long long v_go_int64(double x) {
 __device__ __forceinline__ double v_approx(int c, long long v) { return c == 0 ? __dmul_rn((double)v, 1e-3) : (double)v; }
 __device__ __forceinline__ bool v_cmp_col(int c, unsigned ymask) { return c == 0 || c == 1 || (c >= 4 && (ymask >> c & 1)); }
 
-__global__ void __launch_bounds__(256) k_victims_aggregate(DevVictims v) {
-    __shared__ long long s_min[16][VQR], s_over[16][VQR];
+constexpr int V_AGG_THREADS = 1024, V_AGG_ROWS = V_AGG_THREADS / 16;   // 64 namespaces in flight: each step is a chain of dependent loads
+__global__ void __launch_bounds__(V_AGG_THREADS) k_victims_aggregate(DevVictims v) {
+    __shared__ long long s_min[V_AGG_ROWS][VQR], s_over[V_AGG_ROWS][VQR];
     __shared__ unsigned s_om;
     const int tid = threadIdx.x, c = tid & 15, j = tid >> 4;
     if (tid == 0) s_om = 0;
     __syncthreads();
     long long mn = 0, ov = 0; unsigned om = 0;
-    for (int ns = j; ns < v.NS; ns += 16) {
+    for (int ns = j; ns < v.NS; ns += V_AGG_ROWS) {
         const int e = v.ns_quota[ns];
         if (e < 0) continue;
         if (c < v.R) {
@@ -57,10 +58,11 @@ __global__ void __launch_bounds__(256) k_victims_aggregate(DevVictims v) {
     s_min[j][c] = mn; s_over[j][c] = ov;
     if (c == 0 && om) atomicOr(&s_om, om);
     __syncthreads();
-    if (tid < VQR) {
-        long long a = 0, b = 0;
-        for (int k = 0; k < 16; ++k) { a += s_min[k][tid]; b += s_over[k][tid]; }
-        v.agg[tid] = a; v.agg[VQR + tid] = b;
+    if (tid < 2 * VQR) {
+        const int which = tid / VQR, col = tid % VQR;
+        long long a = 0;
+        for (int k = 0; k < V_AGG_ROWS; ++k) a += (which ? s_over : s_min)[k][col];
+        v.agg[which * VQR + col] = a;
     }
     if (tid == 0) *v.omask = s_om;
 }
@@ -220,7 +222,7 @@ extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_q
     v.rmask = vq->request_mask ? (const uint32_t*)(A + o_rmask) : nullptr;
     v.agg = (long long*)(A + o_agg); v.omask = (unsigned*)(A + o_om); v.victim = (uint8_t*)(A + o_vic); v.overflow = (int32_t*)(A + o_ovf);
     VCU(cudaEventRecord(ev[0], st));
-    k_victims_aggregate<<<1, 256, 0, st>>>(v);
+    k_victims_aggregate<<<1, V_AGG_THREADS, 0, st>>>(v);
     if (Nn > 0) {
         int blocks = (Nn + 7) / 8;
         if (blocks > 148 * 4) blocks = 148 * 4;
