@@ -402,6 +402,13 @@ int nosplan_preempt_dryrun(nosplan_t* h, const nosplan_quotas* quotas, const nos
                            int32_t* node_status /* [n_nodes] out: NOSPLAN_VICTIMS_* */,
                            int32_t* num_violating /* [n_nodes] out: numViolatingVictim */, nosplan_stats* stats);
 
+/* The next preemptor against the SAME cluster state: quotas, nodes, pods and budgets of the last nosplan_preempt_dryrun on this
+ * handle stay in HBM (upstream's DryRunPreemption runs once per unschedulable pod of a scheduling cycle, each time over the
+ * same snapshot); only the preemptor's fields of `preemptor` are read -- v.preemptor_ns, v.preemptor_priority,
+ * v.nominated_in_eq, pod_req, nominated, fit_request, fit_mask -- and the outputs are sized as in that call. */
+int nosplan_preempt_dryrun_again(nosplan_t* h, const nosplan_preempt_query* preemptor, uint8_t* victim, int32_t* node_status,
+                                 int32_t* num_violating, nosplan_stats* stats);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Snapshot packer: the status annotations of N nodes -> the per-GPU arrays of nosplan_snapshot.
  * Replaces: gpu.ParseNodeAnnotations (pkg/gpu/annotation.go:29-104), StatusAnnotationList.GroupByGpuIndex (:186-196) and

@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
-    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes",
+    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -560,6 +560,21 @@ class Engine:
                                              C.byref(st))
         self._check(rc, "nosplan_preempt_dryrun")
         del k1, k2
+        return victim[:n_pods], status[:n_nodes], nviol[:n_nodes], st.as_dict()
+
+    def preempt_dryrun_again(self, query):
+        """nosplan_preempt_dryrun_again: `query`'s preemptor against the cluster state the last preempt_dryrun() uploaded."""
+        cv, k2 = query.c_struct()
+        n_pods, n_nodes = query.v.n_pods, len(query.v.node_ptr) - 1
+        victim = np.zeros(max(1, n_pods), np.uint8)
+        status = np.zeros(max(1, n_nodes), np.int32)
+        nviol = np.zeros(max(1, n_nodes), np.int32)
+        st = CStats()
+        self.lib.nosplan_preempt_dryrun_again.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(CStats)]
+        self.lib.nosplan_preempt_dryrun_again.restype = C.c_int
+        rc = self.lib.nosplan_preempt_dryrun_again(self.h, C.byref(cv), victim.ctypes.data, status.ctypes.data, nviol.ctypes.data, C.byref(st))
+        self._check(rc, "nosplan_preempt_dryrun_again")
+        del k2
         return victim[:n_pods], status[:n_nodes], nviol[:n_nodes], st.as_dict()
 
     def quota_recompute(self, pq, running=None, pending=None):

@@ -49,6 +49,10 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
                                            int32_t* node_status, int32_t* num_violating, float* ms_h2d, float* ms_k, float* ms_d2h,
                                            int* launches, long long* h2d_bytes, long long* d2h_bytes);
 
+extern "C" int nosplan_preempt_dryrun_again_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                                 const nosplan_preempt_query* pq, uint8_t* victim, int32_t* node_status,
+                                                 int32_t* num_violating, float* ms_k, float* ms_d2h, int* launches, long long* d2h_bytes);
+
 extern "C" int nosplan_parse_annotations_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                               const nosplan_annotations* in, nosplan_parsed_gpus* out, float* ms_h2d, float* ms_k,
                                               float* ms_d2h, long long* h2d_bytes, long long* d2h_bytes);
@@ -317,6 +321,7 @@ void nosplan_destroy(nosplan_t* h) {
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->qctx) nosplan_quota_ctx_free(h->qctx);
+    if (h->pctx) nosplan_quota_ctx_free(h->pctx);
     if (h->sctx) nosplan_shard_ctx_free(h->sctx);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -1087,14 +1092,28 @@ int nosplan_quota_victims(nosplan_t* h, const nosplan_quotas* quotas, const nosp
 int nosplan_preempt_dryrun(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_preempt_query* query, uint8_t* victim,
                            int32_t* node_status, int32_t* num_violating, nosplan_stats* stats) {
     if (!h) return NOSPLAN_E_INVALID;
-    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    if (!h->pctx) h->pctx = nosplan_quota_ctx_new();
     float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
-    const int rc = nosplan_preempt_dryrun_impl(h->device, h->stream, h->qctx, &h->err, quotas, query, victim, node_status, num_violating,
+    const int rc = nosplan_preempt_dryrun_impl(h->device, h->stream, h->pctx, &h->err, quotas, query, victim, node_status, num_violating,
                                                &a, &b, &c, &launches, &hb, &db);
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
         stats->h2d_bytes = hb; stats->d2h_bytes = db;
+    }
+    return rc;
+}
+
+int nosplan_preempt_dryrun_again(nosplan_t* h, const nosplan_preempt_query* preemptor, uint8_t* victim, int32_t* node_status,
+                                 int32_t* num_violating, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->pctx) { h->err = "nosplan_preempt_dryrun_again: no cluster state resident on this handle (call nosplan_preempt_dryrun first)"; return NOSPLAN_E_INVALID; }
+    float b = 0, c = 0; int launches = 0; long long db = 0;
+    const int rc = nosplan_preempt_dryrun_again_impl(h->device, h->stream, h->pctx, &h->err, preemptor, victim, node_status, num_violating,
+                                                     &b, &c, &launches, &db);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches; stats->d2h_bytes = db;
     }
     return rc;
 }

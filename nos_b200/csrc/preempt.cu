@@ -312,6 +312,75 @@ __global__ void __launch_bounds__(256) k_preempt_dryrun(DevPreempt v) {
 
 using namespace nsp;
 
+namespace {
+// what nosplan_preempt_dryrun_again needs of the last full call: the device problem and where its outputs lie
+struct PreemptResident {
+    bool valid = false;
+    DevPreempt v;
+    size_t upload_end = 0, out_end = 0, total = 0, o_state = 0, o_status = 0, o_nviol = 0, o_ovf = 0;
+    int P = 0, Nn = 0, R = 0;
+};
+void preempt_resident_free(void* p) { delete static_cast<PreemptResident*>(p); }
+
+// preemptor fields -> device problem, work area cleared, both kernels, outputs back to the caller
+int preempt_run(cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err, PreemptResident& rs, const nosplan_preempt_query* pq,
+                uint8_t* victim, int32_t* node_status, int32_t* num_violating, cudaEvent_t* ev, float* ms_k, float* ms_d2h,
+                int* launches, long long* d2h_bytes) {
+    auto fail = [&](int code, const char* msg, const char* detail = "") { if (err) *err = std::string(msg) + detail; return code; };
+#define RCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(NOSPLAN_E_CUDA, #call ": ", cudaGetErrorString(e_)); } while (0)
+    DevPreempt& v = rs.v;
+    unsigned char* S = ctx->hs; unsigned char* A = ctx->d;
+    v.pn = pq->v.preemptor_ns; v.pprio = pq->v.preemptor_priority; v.fit_mask = pq->fit_mask;
+    for (int c = 0; c < PQR; ++c) {
+        const bool in = c < rs.R;
+        v.nom[c] = in ? pq->v.nominated_in_eq[c] : 0;
+        v.pod_req[c] = in ? pq->pod_req[c] : 0;
+        v.nominated[c] = in ? pq->nominated[c] : 0;
+        v.fit[c] = in ? pq->fit_request[c] : 0;
+    }
+    RCU(cudaMemsetAsync(A + rs.upload_end, 0, rs.total - rs.upload_end, st));
+    RCU(cudaEventRecord(ev[1], st));
+    k_preempt_aggregate<<<1, P_AGG_THREADS, 0, st>>>(v);
+    if (rs.Nn > 0) {
+        // one node per warp: nodes differ widely in work (victims found or not, reprieve loops), so the block scheduler balances them
+        k_preempt_dryrun<<<(rs.Nn + 7) / 8, 256, 0, st>>>(v);
+    }
+    RCU(cudaGetLastError());
+    RCU(cudaEventRecord(ev[2], st));
+    RCU(cudaMemcpyAsync(S, A + rs.upload_end, rs.out_end - rs.upload_end, cudaMemcpyDeviceToHost, st));
+    RCU(cudaEventRecord(ev[3], st));
+    RCU(cudaStreamSynchronize(st));
+    if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
+    if (ms_d2h) cudaEventElapsedTime(ms_d2h, ev[2], ev[3]);
+    if (launches) *launches = 1 + (rs.Nn > 0);
+    if (d2h_bytes) *d2h_bytes = (long long)(rs.out_end - rs.upload_end);
+    int32_t overflow; std::memcpy(&overflow, S + (rs.o_ovf - rs.upload_end), 4);
+    if (overflow) return fail(NOSPLAN_E_LIMIT, "a node's victims come from more than 32 namespaces");
+    if (rs.P) std::memcpy(victim, S + (rs.o_state - rs.upload_end), (size_t)rs.P);
+    if (rs.Nn) {
+        std::memcpy(node_status, S + (rs.o_status - rs.upload_end), 4 * (size_t)rs.Nn);
+        std::memcpy(num_violating, S + (rs.o_nviol - rs.upload_end), 4 * (size_t)rs.Nn);
+    }
+    return NOSPLAN_OK;
+#undef RCU
+}
+}  // namespace
+
+// Another preemptor against the cluster state (quotas, nodes, pods, budgets) the last nosplan_preempt_dryrun left in HBM.
+extern "C" int nosplan_preempt_dryrun_again_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                                 const nosplan_preempt_query* pq, uint8_t* victim, int32_t* node_status,
+                                                 int32_t* num_violating, float* ms_k, float* ms_d2h, int* launches, long long* d2h_bytes) {
+    auto fail = [&](int code, const char* msg) { if (err) *err = msg; return code; };
+    PreemptResident* rs = ctx ? static_cast<PreemptResident*>(ctx->preempt_resident) : nullptr;
+    if (!rs || !rs->valid) return fail(NOSPLAN_E_INVALID, "nosplan_preempt_dryrun_again: no cluster state resident on this handle (call nosplan_preempt_dryrun first)");
+    if (!pq || !victim || !node_status || !num_violating) return fail(NOSPLAN_E_INVALID, "null argument");
+    if (!pq->v.nominated_in_eq || !pq->pod_req || !pq->nominated || !pq->fit_request) return fail(NOSPLAN_E_INVALID, "nominated_in_eq, pod_req, nominated and fit_request are required");
+    if (cudaSetDevice(device) != cudaSuccess) return fail(NOSPLAN_E_CUDA, "cudaSetDevice");
+    cudaEvent_t* ev = nullptr;
+    if (quota_ctx_events(ctx, &ev) != cudaSuccess) return fail(NOSPLAN_E_CUDA, "cudaEventCreate");
+    return preempt_run(st, ctx, err, *rs, pq, victim, node_status, num_violating, ev, ms_k, ms_d2h, launches, d2h_bytes);
+}
+
 extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                            const nosplan_quotas* qs, const nosplan_preempt_query* pq, uint8_t* victim,
                                            int32_t* node_status, int32_t* num_violating, float* ms_h2d, float* ms_k, float* ms_d2h,
@@ -341,6 +410,9 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
             if (pq->pod_pdb[k] < 0 || pq->pod_pdb[k] >= B) return fail(NOSPLAN_E_INVALID, "pod_pdb names a budget outside [0, n_pdbs)");
     }
     PCU(cudaSetDevice(device));
+    if (!ctx->preempt_resident) { ctx->preempt_resident = new PreemptResident(); ctx->preempt_resident_free = preempt_resident_free; }
+    PreemptResident& rs = *static_cast<PreemptResident*>(ctx->preempt_resident);
+    rs.valid = false;
     size_t o = 0;
     auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
     auto put = [&](size_t bytes) { size_t at = o; o = al(o + bytes); return at; };
@@ -369,8 +441,7 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
     PCU(quota_ctx_events(ctx, &ev));
     PCU(cudaEventRecord(ev[0], st));
     PCU(cudaMemcpyAsync(A, S, upload_end, cudaMemcpyHostToDevice, st));
-    PCU(cudaMemsetAsync(A + upload_end, 0, total - upload_end, st));
-    DevPreempt v; std::memset(&v, 0, sizeof v);
+    DevPreempt& v = rs.v; std::memset(&v, 0, sizeof v);
     v.E = E; v.R = R; v.NS = NS; v.gm = qs->gpu_memory_col; v.n_nodes = Nn; v.n_pods = P; v.pn = vq->preemptor_ns; v.pprio = vq->preemptor_priority;
     v.n_pdbs = B; v.fit_mask = pq->fit_mask;
     v.ns_quota = (const int32_t*)(A + o_nsq); v.qmin = (const long long*)(A + o_min); v.qmax = (const long long*)(A + o_max);
@@ -391,30 +462,13 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
     v.pdb_allowed = (const int32_t*)(A + o_pdba); v.pod_pdb_ptr = (const int32_t*)(A + o_pptr); v.pod_pdb = (const int32_t*)(A + o_ppdb);
     v.agg = (long long*)(A + o_agg); v.masks = (unsigned*)(A + o_masks); v.state = (uint8_t*)(A + o_state);
     v.status = (int32_t*)(A + o_status); v.nviol = (int32_t*)(A + o_nviol); v.overflow = (int32_t*)(A + o_ovf);
-    PCU(cudaEventRecord(ev[1], st));
-    k_preempt_aggregate<<<1, P_AGG_THREADS, 0, st>>>(v);
-    if (Nn > 0) {
-        // one node per warp: nodes differ widely in work (victims found or not, reprieve loops), so the block scheduler balances them
-        k_preempt_dryrun<<<(Nn + 7) / 8, 256, 0, st>>>(v);
-    }
-    PCU(cudaGetLastError());
-    PCU(cudaEventRecord(ev[2], st));
-    PCU(cudaMemcpyAsync(S, A + upload_end, out_end - upload_end, cudaMemcpyDeviceToHost, st));
-    PCU(cudaEventRecord(ev[3], st));
-    PCU(cudaStreamSynchronize(st));
+    rs.upload_end = upload_end; rs.out_end = out_end; rs.total = total;
+    rs.o_state = o_state; rs.o_status = o_status; rs.o_nviol = o_nviol; rs.o_ovf = o_ovf;
+    rs.P = P; rs.Nn = Nn; rs.R = R;
+    const int rc = preempt_run(st, ctx, err, rs, pq, victim, node_status, num_violating, ev, ms_k, ms_d2h, launches, d2h_bytes);
     if (ms_h2d) cudaEventElapsedTime(ms_h2d, ev[0], ev[1]);
-    if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
-    if (ms_d2h) cudaEventElapsedTime(ms_d2h, ev[2], ev[3]);
-    if (launches) *launches = 1 + (Nn > 0);
     if (h2d_bytes) *h2d_bytes = (long long)upload_end;
-    if (d2h_bytes) *d2h_bytes = (long long)(out_end - upload_end);
-    int32_t overflow; std::memcpy(&overflow, S + (o_ovf - upload_end), 4);
-    if (overflow) return fail(NOSPLAN_E_LIMIT, "a node's victims come from more than 32 namespaces");
-    if (P) std::memcpy(victim, S + (o_state - upload_end), (size_t)P);
-    if (Nn) {
-        std::memcpy(node_status, S + (o_status - upload_end), 4 * (size_t)Nn);
-        std::memcpy(num_violating, S + (o_nviol - upload_end), 4 * (size_t)Nn);
-    }
-    return NOSPLAN_OK;
+    rs.valid = rc == NOSPLAN_OK || rc == NOSPLAN_E_LIMIT;     // the uploaded state is intact either way
+    return rc;
 #undef PCU
 }

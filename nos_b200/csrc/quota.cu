@@ -664,6 +664,7 @@ extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx) {
     if (ctx->d) cudaFree(ctx->d);
     if (ctx->hs) cudaFreeHost(ctx->hs);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->preempt_resident && ctx->preempt_resident_free) ctx->preempt_resident_free(ctx->preempt_resident);
     delete ctx;
 }
 extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new() { return new nosplan_quota_ctx(); }

@@ -7,6 +7,10 @@ struct nosplan_quota_ctx {
     unsigned char* d = nullptr; size_t d_cap = 0;
     unsigned char* hs = nullptr; size_t hs_cap = 0;
     cudaEvent_t ev[4] = {};            // phase timing of the entry points, created on first use and kept with the handle
+    // nosplan_preempt_dryrun leaves its cluster state in `d` for nosplan_preempt_dryrun_again (the handle gives the preemption
+    // entry points a context of their own, so no other call overwrites it); owned by preempt.cu
+    void* preempt_resident = nullptr;
+    void (*preempt_resident_free)(void*) = nullptr;
 };
 
 // the context's four timing events (created once; an error path of a call has nothing to give back)

@@ -133,3 +133,48 @@ def test_empty_query(eng):
                               np.zeros(0, np.int32), np.zeros(1, np.int32), np.zeros(0, np.int32))
     gv, gs, gn, _ = eng.preempt_dryrun(pq, q)
     assert gv.size == 0 and gs.size == 0 and gn.size == 0
+
+
+def test_next_preemptors_against_the_resident_cluster_state(eng):
+    """nosplan_preempt_dryrun_again: several preemptors in a row against the quotas / nodes / pods one full call uploaded, other
+    entry points of the handle used in between; every answer is the oracle's for that preemptor on the full query."""
+    pq, run, r, order, ptr, req, node_req, alloc, pdb_allowed, pdb_ptr, pod_pdb = c4_query(eng, n_nodes=2000, fill=0.98)
+    popular = int(np.bincount(run.ns).argmax())
+
+    def query(pre_ns, pre_prio, cpu, extra):
+        nom = np.zeros(pq.n_res, np.int64)
+        nom[0], nom[1], nom[5] = cpu, 8 << 30, 1
+        nom[pq.gpu_memory_col] = 32
+        fit = nom.copy()
+        fit[pq.gpu_memory_col] = 0
+        nominated = nom.copy()
+        nominated[0] += extra
+        v = vp.PackedVictimQuery(pre_ns, pre_prio, nom, ptr, run.ns[order], run.priority[order], r["over_quota"][order],
+                                 req, run.request_mask[order])
+        return pp.PackedPreemptQuery(v, nom.copy(), nominated, fit, 1 << 5, alloc, node_req, pdb_allowed, pdb_ptr, pod_pdb)
+
+    first = query(popular, 1000, 4000, 12000)
+    gv, gs, gn, st0 = eng.preempt_dryrun(pq, first)
+    ev, es, en = ol.preempt_dryrun(pq, first)
+    assert np.array_equal(gv, ev) and np.array_equal(gs, es) and np.array_equal(gn, en)
+    seen = collections.Counter()
+    for k, (pre_ns, pre_prio, cpu, extra) in enumerate(((popular, 100, 500, 0), (int(run.ns[3]), 1000, 64000, 0),
+                                                         (len(pq.namespaces) - 1, 100, 4000, 10 ** 9), (popular, 1000, 4000, 12000))):
+        if k == 2:
+            eng.quota_recompute(pq, run)                     # another entry point of the handle must not disturb the resident state
+        q = query(pre_ns, pre_prio, cpu, extra)
+        gv, gs, gn, st = eng.preempt_dryrun_again(q)
+        ev, es, en = ol.preempt_dryrun(pq, q)
+        assert np.array_equal(gs, es) and np.array_equal(gv, ev) and np.array_equal(gn, en), k
+        assert st["h2d_bytes"] == 0 and st["kernel_launches"] == 2
+        seen.update(int(x) for x in gs)
+    assert seen[0] > 0 and seen[1] > 0
+
+
+def test_again_without_a_resident_state():
+    fresh = capi.Engine(0)
+    case = pc.rand_preempt_case(3)
+    pq, query = pc.packed_dryrun_query(*case, lambda pq_, run_: (ol.quota(pq_, run_)["used"], ol.quota(pq_, run_)["used_mask"]))
+    with pytest.raises(capi.NosplanError, match="no cluster state resident"):
+        fresh.preempt_dryrun_again(query)
+    fresh.close()

@@ -24,6 +24,13 @@ for _ in range(3):
 ts, ks = [], []
 for _ in range(20):
     t0 = time.perf_counter(); gv, gs, gn, st = eng.preempt_dryrun(pq, q); ts.append(time.perf_counter() - t0); ks.append(st["ms_kernels"])
+# the next preemptors against the cluster state that call left in HBM: nothing but the preemptor's vectors travels in
+for _ in range(3):
+    av, as_, an, ast = eng.preempt_dryrun_again(q)
+tsa = []
+for _ in range(20):
+    t0 = time.perf_counter(); av, as_, an, ast = eng.preempt_dryrun_again(q); tsa.append(time.perf_counter() - t0)
+same_again = bool(np.array_equal(av, gv) and np.array_equal(as_, gs) and np.array_equal(an, gn))
 cpu = []
 for _ in range(5):
     t0 = time.perf_counter(); ev, es, en = ol.preempt_dryrun(pq, q); cpu.append(time.perf_counter() - t0)
@@ -31,7 +38,7 @@ same = bool(np.array_equal(gv, ev) and np.array_equal(gs, es) and np.array_equal
 P, N, R = run.n_pods, len(ptr) - 1, pq.n_res
 b_alg = P * (4 + 4 + 1 + 8 * R + 4 + 4 + 1) + len(pod_pdb) * 4 + N * (16 * R + 4 + 8)
 print(json.dumps({"config": "C4 scale: 500 quotas, %d running pods on %d nodes, %d resource columns, %d PodDisruptionBudgets" % (P, N, R, len(pdb_allowed)),
-                  "gpu": {"ms_call_p50": 1e3 * float(np.median(ts)), "ms_h2d": st["ms_h2d"], "ms_kernels_p50": float(np.median(ks)), "ms_d2h": st["ms_d2h"],
+                  "gpu": {"ms_call_p50": 1e3 * float(np.median(ts)), "ms_call_p50_resident_state": 1e3 * float(np.median(tsa)), "resident_identical": same_again, "ms_h2d": st["ms_h2d"], "ms_kernels_p50": float(np.median(ks)), "ms_d2h": st["ms_d2h"],
                           "kernel_launches": st["kernel_launches"], "h2d_bytes": st["h2d_bytes"], "d2h_bytes": st["d2h_bytes"],
                           "nodes_per_s_kernels": N / (float(np.median(ks)) / 1e3), "algorithmic_bytes": int(b_alg),
                           "achieved_GBps_kernels": b_alg / (float(np.median(ks)) / 1e3) / 1e9},
