@@ -317,6 +317,29 @@ typedef struct nosplan_quota_out {     /* every pointer may be NULL = not wanted
 int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
                             const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats);
 
+/* Event-driven accounting on a quota state that stays in HBM -- the way the plugin itself keeps its ElasticQuotaInfos current:
+ * the pod informer handlers and Reserve / Unreserve call AddPodIfNotPresent / DeletePodIfPresent
+ * (pkg/scheduler/plugins/capacityscheduling/elasticquotainfo.go:276-310, capacity_scheduling.go:311-321,381-445), which
+ * reserve / unreserve the pod's request unless the pod is already / not accounted in its quota (the `pods` set).
+ * nosplan_quota_state_begin uploads the quota tables (Used = used_init, no pod accounted); nosplan_quota_state_apply applies
+ * one batch of events and returns what `out` asks for of used, used_mask, agg_*, guaranteed (NULL pointers = not wanted).
+ * pod_id: dense id the caller assigns to a pod UID, < pod_capacity.  The events of a batch are applied in no particular
+ * order, so a pod may occur at most once per batch (checked; two batches for an add and a delete of the same pod). */
+#define NOSPLAN_QUOTA_EVENT_ADD 0      /* AddPodIfNotPresent (:276-292) */
+#define NOSPLAN_QUOTA_EVENT_DELETE 1   /* DeletePodIfPresent (:294-310) */
+typedef struct nosplan_quota_events {
+    int32_t n_events;
+    const uint8_t* op;                 /* [n] NOSPLAN_QUOTA_EVENT_* */
+    const int32_t* pod_id;             /* [n] */
+    const int32_t* ns;                 /* [n] namespace id */
+    const int64_t* request;            /* [n][Rq] plain request at the time of the event (the engine adds gpu-memory) */
+    const uint32_t* request_mask;      /* [n] or NULL, as in nosplan_quota_pods */
+} nosplan_quota_events;
+
+int nosplan_quota_state_begin(nosplan_t* h, const nosplan_quotas* quotas, int32_t pod_capacity);
+int nosplan_quota_state_apply(nosplan_t* h, const nosplan_quota_events* events, nosplan_quota_out* out,
+                              int32_t* n_applied /* [1] out, may be NULL: events that changed the state */, nosplan_stats* stats);
+
 /* The operator pass returning only what has to be patched.  The reference walks the pods of a
  * quota in the order of sortPodListForFindingOverQuotaPods and calls patchCapacityInfoIfDifferent on each
  * (internal/controllers/elasticquota/elasticquota.go:44-60, :120-149): a pod is patched iff its label

@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
-    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again",
+    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -226,6 +226,14 @@ class CLabelChanges(C.Structure):
 
 
 LABEL_OTHER, LABEL_IN_QUOTA, LABEL_OVER_QUOTA = 0, 1, 2
+
+
+class CQuotaEvents(C.Structure):
+    _fields_ = [("n_events", C.c_int32), ("op", C.c_void_p), ("pod_id", C.c_void_p), ("ns", C.c_void_p), ("request", C.c_void_p),
+                ("request_mask", C.c_void_p)]
+
+
+EVENT_ADD, EVENT_DELETE = 0, 1
 
 
 class NosplanError(RuntimeError):
@@ -561,6 +569,43 @@ class Engine:
         self._check(rc, "nosplan_preempt_dryrun")
         del k1, k2
         return victim[:n_pods], status[:n_nodes], nviol[:n_nodes], st.as_dict()
+
+    def quota_state_begin(self, pq, pod_capacity: int):
+        """nosplan_quota_state_begin: quota tables into HBM, Used = used_init, no pod accounted."""
+        from . import quota_packing as qp
+        cq, k1 = qp.c_quotas(pq)
+        self.lib.nosplan_quota_state_begin.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.c_int32]
+        self.lib.nosplan_quota_state_begin.restype = C.c_int
+        self._check(self.lib.nosplan_quota_state_begin(self.h, C.byref(cq), int(pod_capacity)), "nosplan_quota_state_begin")
+        self._state_pq = pq
+        del k1
+
+    def quota_state_apply(self, op, pod_id, ns, request, request_mask=None, outputs=True):
+        """nosplan_quota_state_apply: one batch of AddPodIfNotPresent / DeletePodIfPresent events.
+        -> (dict with used, used_mask, agg_*, guaranteed -- or None --, number of events that changed the state, stats)"""
+        from . import quota_packing as qp
+        pq = self._state_pq
+        n = len(op)
+        keep = [np.ascontiguousarray(op, np.uint8), np.ascontiguousarray(pod_id, np.int32), np.ascontiguousarray(ns, np.int32),
+                np.ascontiguousarray(request, np.int64).reshape(n, pq.n_res) if n else np.zeros((1, pq.n_res), np.int64)]
+        mask = np.ascontiguousarray(request_mask, np.uint32) if request_mask is not None else None
+        p = lambda a: a.ctypes.data if a.size else None
+        ev = CQuotaEvents(n, p(keep[0]), p(keep[1]), p(keep[2]), keep[3].ctypes.data, mask.ctypes.data if mask is not None and n else None)
+        res = qp.QuotaResult(pq, 0, 0) if outputs else None
+        out = res.c_struct() if outputs else None
+        if outputs:
+            out.prefilter = None; out.over_quota = None; out.operator_used = None; out.ambiguous_order = None
+        applied = np.zeros(1, np.int32)
+        st = CStats()
+        self.lib.nosplan_quota_state_apply.argtypes = [C.c_void_p, C.POINTER(CQuotaEvents), C.POINTER(qp.CQuotaOut), C.c_void_p, C.POINTER(CStats)]
+        self.lib.nosplan_quota_state_apply.restype = C.c_int
+        rc = self.lib.nosplan_quota_state_apply(self.h, C.byref(ev), C.byref(out) if outputs else None, applied.ctypes.data, C.byref(st))
+        self._check(rc, "nosplan_quota_state_apply")
+        d = None
+        if outputs:
+            t = res.trimmed()
+            d = {k: t[k] for k in ("used", "used_mask", "agg_min", "agg_used", "agg_overquota", "agg_masks", "guaranteed")}
+        return d, int(applied[0]), st.as_dict()
 
     def preempt_dryrun_again(self, query):
         """nosplan_preempt_dryrun_again: `query`'s preemptor against the cluster state the last preempt_dryrun() uploaded."""

@@ -49,6 +49,11 @@ extern "C" int nosplan_preempt_dryrun_impl(int device, cudaStream_t st, nosplan_
                                            int32_t* node_status, int32_t* num_violating, float* ms_h2d, float* ms_k, float* ms_d2h,
                                            int* launches, long long* h2d_bytes, long long* d2h_bytes);
 
+extern "C" int nosplan_quota_state_begin_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                              const nosplan_quotas* qs, int32_t pod_capacity);
+extern "C" int nosplan_quota_state_apply_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, nosplan_quota_ctx* scratch, std::string* err,
+                                              const nosplan_quota_events* evs, nosplan_quota_out* out, int32_t* n_applied,
+                                              float* ms_k, long long* h2d_bytes, long long* d2h_bytes);
 extern "C" int nosplan_preempt_dryrun_again_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                                  const nosplan_preempt_query* pq, uint8_t* victim, int32_t* node_status,
                                                  int32_t* num_violating, float* ms_k, float* ms_d2h, int* launches, long long* d2h_bytes);
@@ -322,6 +327,7 @@ void nosplan_destroy(nosplan_t* h) {
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->qctx) nosplan_quota_ctx_free(h->qctx);
     if (h->pctx) nosplan_quota_ctx_free(h->pctx);
+    if (h->ectx) nosplan_quota_ctx_free(h->ectx);
     if (h->sctx) nosplan_shard_ctx_free(h->sctx);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -1043,6 +1049,26 @@ int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const no
         std::memset(stats, 0, sizeof *stats);
         stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
         stats->h2d_bytes = hb; stats->d2h_bytes = db;
+    }
+    return rc;
+}
+
+int nosplan_quota_state_begin(nosplan_t* h, const nosplan_quotas* quotas, int32_t pod_capacity) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->ectx) h->ectx = nosplan_quota_ctx_new();
+    return nosplan_quota_state_begin_impl(h->device, h->stream, h->ectx, &h->err, quotas, pod_capacity);
+}
+
+int nosplan_quota_state_apply(nosplan_t* h, const nosplan_quota_events* events, nosplan_quota_out* out, int32_t* n_applied,
+                              nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->ectx) { h->err = "nosplan_quota_state_apply: no quota state resident on this handle (call nosplan_quota_state_begin first)"; return NOSPLAN_E_INVALID; }
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    float k = 0; long long hb = 0, db = 0;
+    const int rc = nosplan_quota_state_apply_impl(h->device, h->stream, h->ectx, h->qctx, &h->err, events, out, n_applied, &k, &hb, &db);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_kernels = k; stats->h2d_bytes = hb; stats->d2h_bytes = db; stats->kernel_launches = 2;
     }
     return rc;
 }

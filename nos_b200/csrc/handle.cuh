@@ -36,6 +36,7 @@ struct nosplan {
     int launches = 0;
     size_t h2d_bytes = 0;
     nosplan_quota_ctx* qctx = nullptr;
+    nosplan_quota_ctx* ectx = nullptr;          // the resident quota state of nosplan_quota_state_begin / apply
     nosplan_quota_ctx* pctx = nullptr;          // the preemption entry points' own scratch: holds the resident cluster state
     nosplan_shard_ctx* sctx = nullptr;
     std::string err;

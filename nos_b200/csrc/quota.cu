@@ -16,6 +16,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
@@ -111,6 +112,42 @@ __global__ void __launch_bounds__(256) k_quota_used(DevQuota q, int use_smem) {
         for (int x = tid; x < q.E * q.R; x += blockDim.x)
             if (s_tab[x] != 0) atomicAdd((unsigned long long*)&q.used[x], (unsigned long long)s_tab[x]);
     }
+}
+
+// Event-driven accounting on a resident state: AddPodIfNotPresent / DeletePodIfPresent (elasticquotainfo.go:276-310) for a batch of
+// pod events.  Half a warp per event (lane = resource column); the first lane tests and flips the pod's bit in the set of
+// accounted pods (a pod occurs at most once per batch, checked on the host, so the events of a batch commute: int64 sums),
+// then reserveResource / unreserveResource (:194-208) on Memory, MilliCPU and the scalars the request names.
+struct DevEvents {
+    int n;
+    const uint8_t* op; const int32_t* pod_id; const int32_t* ns; const long long* req; const uint32_t* mask;
+    unsigned* present;         // [capacity / 32] accounted pods
+    int32_t* applied;          // [1] events that changed the state
+};
+__global__ void __launch_bounds__(256) k_quota_events(DevQuota q, DevEvents ev) {
+    const int tid = threadIdx.x, c = tid & 15, sub = (tid >> 4) & 1;
+    const unsigned segmask = 0xffffu << (16 * sub);
+    const int i = blockIdx.x * (blockDim.x / 16) + (tid >> 4);
+    if (i >= ev.n) return;                                   // whole 16-lane segment
+    const int ns = ev.ns[i];
+    const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+    uint32_t rmask;
+    const long long v = pod_request16(q, ev.req, ev.mask, i, c, segmask, rmask);
+    if (e < 0) return;                                       // namespace without quota: no ElasticQuotaInfo to account in
+    const bool add = ev.op[i] == NOSPLAN_QUOTA_EVENT_ADD;
+    int go = 0;
+    if (c == 0) {
+        const int id = ev.pod_id[i];
+        const unsigned bit = 1u << (id & 31);
+        const unsigned old = add ? atomicOr(&ev.present[id >> 5], bit) : atomicAnd(&ev.present[id >> 5], ~bit);
+        go = add ? !(old & bit) : (old & bit) != 0;
+        if (go) atomicAdd(ev.applied, 1);
+    }
+    go = __shfl_sync(segmask, go, 16 * sub);
+    if (!go) return;
+    const bool take = c < q.R && (c == 0 || c == 1 || (c >= 4 && (rmask >> c & 1)));
+    if (take && v != 0) atomicAdd((unsigned long long*)&q.used[(size_t)e * q.R + c], (unsigned long long)(add ? v : -v));
+    if (c == 0 && (rmask & ~q.used_mask[e])) atomicOr(&q.used_mask[e], rmask);
 }
 
 constexpr int AGG_THREADS = 1024, AGG_ROWS = AGG_THREADS / 16;   // 64 namespaces in flight: the loop is a chain of dependent loads
@@ -659,12 +696,164 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
 #undef QCU
 }
 
+namespace {
+struct QuotaResident {
+    bool valid = false;
+    DevQuota q;
+    int capacity = 0;
+    size_t o_used = 0, o_umask = 0, o_amin = 0, o_aused = 0, o_aover = 0, o_amask = 0, o_guar = 0, o_present = 0, o_applied = 0, total = 0;
+    std::vector<uint64_t> batch_seen;                        // host: pods of the batch being checked
+};
+void quota_resident_free(void* p) { delete static_cast<QuotaResident*>(p); }
+}  // namespace
+
+// ctx: the handle's context for the resident quota state; nothing else uses it
+extern "C" int nosplan_quota_state_begin_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                              const nosplan_quotas* qs, int32_t pod_capacity) {
+    auto fail = [&](int code, const char* msg, const char* detail = "") { if (err) *err = std::string(msg) + detail; return code; };
+#define SCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(NOSPLAN_E_CUDA, #call ": ", cudaGetErrorString(e_)); } while (0)
+    if (!qs) return fail(NOSPLAN_E_INVALID, "null quotas");
+    const int E = qs->n_quotas, R = qs->n_res, NS = qs->n_namespaces;
+    if (R < 4 || R > QR) return fail(NOSPLAN_E_LIMIT, "n_res must be in [4, NOSPLAN_QUOTA_MAX_RES]");
+    if (E < 0 || NS < 0 || pod_capacity < 0) return fail(NOSPLAN_E_INVALID, "negative size");
+    if (qs->gpu_memory_col >= R || (qs->gpu_memory_col >= 0 && qs->gpu_memory_col < 4)) return fail(NOSPLAN_E_INVALID, "gpu_memory_col out of range");
+    for (int ns = 0; ns < NS; ++ns) if (qs->ns_quota[ns] >= E) return fail(NOSPLAN_E_INVALID, "ns_quota out of range");
+    SCU(cudaSetDevice(device));
+    if (!ctx->quota_resident) { ctx->quota_resident = new QuotaResident(); ctx->quota_resident_free = quota_resident_free; }
+    QuotaResident& rs = *static_cast<QuotaResident*>(ctx->quota_resident);
+    rs.valid = false;
+    size_t o = 0;
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    auto put = [&](size_t bytes) { size_t at = o; o = al(o + bytes); return at; };
+    const size_t ER = (size_t)E * R, words = ((size_t)pod_capacity + 31) / 32;
+    const size_t o_nsq = put(4 * (size_t)NS), o_min = put(8 * ER), o_max = put(8 * ER), o_mm = put(4 * (size_t)E), o_xm = put(4 * (size_t)E),
+                 o_enf = put((size_t)E);
+    rs.o_used = put(8 * ER); rs.o_umask = put(4 * (size_t)E);
+    const size_t upload_end = o;
+    rs.o_amin = put(8 * QR); rs.o_aused = put(8 * QR); rs.o_aover = put(8 * QR); rs.o_amask = put(16); rs.o_guar = put(8 * ER);
+    rs.o_present = put(4 * words); rs.o_applied = put(16);
+    rs.total = o;
+    SCU(quota_ctx_ensure(ctx, rs.total, std::max(upload_end, rs.o_present)));
+    unsigned char* S = ctx->hs; unsigned char* A = ctx->d;
+    auto cp = [&](size_t at, const void* src, size_t bytes) { if (bytes) { if (src) std::memcpy(S + at, src, bytes); else std::memset(S + at, 0, bytes); } };
+    cp(o_nsq, qs->ns_quota, 4 * (size_t)NS); cp(o_min, qs->min, 8 * ER); cp(o_max, qs->max, 8 * ER);
+    cp(o_mm, qs->min_mask, 4 * (size_t)E); cp(o_xm, qs->max_mask, 4 * (size_t)E); cp(o_enf, qs->max_enforced, (size_t)E);
+    cp(rs.o_used, qs->used_init, 8 * ER); cp(rs.o_umask, qs->used_mask, 4 * (size_t)E);
+    for (int e = 0; e < E; ++e) reinterpret_cast<uint32_t*>(S + rs.o_umask)[e] &= SCALAR_BITS;
+    SCU(cudaMemcpyAsync(A, S, upload_end, cudaMemcpyHostToDevice, st));
+    SCU(cudaMemsetAsync(A + upload_end, 0, rs.total - upload_end, st));
+    DevQuota& q = rs.q; std::memset(&q, 0, sizeof q);
+    q.E = E; q.R = R; q.NS = NS; q.gm = qs->gpu_memory_col;
+    q.ns_quota = (const int32_t*)(A + o_nsq); q.qmin = (const long long*)(A + o_min); q.qmax = (const long long*)(A + o_max);
+    q.min_mask = (const uint32_t*)(A + o_mm); q.max_mask = (const uint32_t*)(A + o_xm); q.max_enforced = (const uint8_t*)(A + o_enf);
+    for (int c = 0; c < QR; ++c) q.coeff[c] = (c < R && qs->gpu_memory_coeff) ? qs->gpu_memory_coeff[c] : 0;
+    q.used = (long long*)(A + rs.o_used); q.used_mask = (uint32_t*)(A + rs.o_umask);
+    q.agg_min = (long long*)(A + rs.o_amin); q.agg_used = (long long*)(A + rs.o_aused); q.agg_over = (long long*)(A + rs.o_aover);
+    q.agg_masks = (uint32_t*)(A + rs.o_amask); q.guaranteed = (long long*)(A + rs.o_guar);
+    SCU(cudaStreamSynchronize(st));
+    rs.capacity = pod_capacity;
+    rs.batch_seen.assign(((size_t)pod_capacity + 63) / 64, 0);
+    rs.valid = true;
+    return NOSPLAN_OK;
+#undef SCU
+}
+
+// ctx: the resident state; scratch: the handle's ordinary quota context, used to carry the events in and the outputs back
+extern "C" int nosplan_quota_state_apply_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, nosplan_quota_ctx* scratch, std::string* err,
+                                              const nosplan_quota_events* evs, nosplan_quota_out* out, int32_t* n_applied,
+                                              float* ms_k, long long* h2d_bytes, long long* d2h_bytes) {
+    auto fail = [&](int code, const char* msg, const char* detail = "") { if (err) *err = std::string(msg) + detail; return code; };
+#define SCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(NOSPLAN_E_CUDA, #call ": ", cudaGetErrorString(e_)); } while (0)
+    QuotaResident* rp = ctx ? static_cast<QuotaResident*>(ctx->quota_resident) : nullptr;
+    if (!rp || !rp->valid) return fail(NOSPLAN_E_INVALID, "nosplan_quota_state_apply: no quota state resident on this handle (call nosplan_quota_state_begin first)");
+    QuotaResident& rs = *rp;
+    const int n = evs ? evs->n_events : 0;
+    if (n < 0) return fail(NOSPLAN_E_INVALID, "negative event count");
+    if (n > 0 && (!evs->op || !evs->pod_id || !evs->ns || !evs->request)) return fail(NOSPLAN_E_INVALID, "op, pod_id, ns and request are required");
+    const int E = rs.q.E, R = rs.q.R;
+    // a pod at most once per batch (the events of a batch are applied in no particular order), ids inside the capacity
+    int bad = -1; const char* why = "";
+    int checked = 0;
+    for (; checked < n; ++checked) {
+        const int id = evs->pod_id[checked];
+        if (id < 0 || id >= rs.capacity) { bad = checked; why = "pod_id outside [0, pod_capacity)"; break; }
+        if (evs->op[checked] > NOSPLAN_QUOTA_EVENT_DELETE) { bad = checked; why = "unknown op"; break; }
+        uint64_t& w = rs.batch_seen[(size_t)id >> 6];
+        const uint64_t bit = 1ull << (id & 63);
+        if (w & bit) { bad = checked; why = "the same pod twice in one batch"; break; }
+        w |= bit;
+    }
+    for (int i = 0; i < checked; ++i) rs.batch_seen[(size_t)evs->pod_id[i] >> 6] = 0;
+    if (bad >= 0) { if (err) *err = std::string("nosplan_quota_state_apply: event ") + std::to_string(bad) + ": " + why; return NOSPLAN_E_INVALID; }
+    SCU(cudaSetDevice(device));
+    cudaEvent_t* ev = nullptr;
+    SCU(quota_ctx_events(ctx, &ev));
+    size_t o = 0;
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    auto put = [&](size_t bytes) { size_t at = o; o = al(o + bytes); return at; };
+    const size_t o_op = put((size_t)n), o_id = put(4 * (size_t)n), o_ns = put(4 * (size_t)n), o_req = put(8 * (size_t)n * R), o_mask = put(4 * (size_t)n);
+    const size_t ev_bytes = o;
+    const size_t ER = (size_t)E * R;
+    SCU(quota_ctx_ensure(scratch, ev_bytes + 256, std::max(ev_bytes, rs.total) + 512));
+    unsigned char* S = scratch->hs; unsigned char* B = scratch->d; unsigned char* A = ctx->d;
+    if (n) {
+        std::memcpy(S + o_op, evs->op, (size_t)n); std::memcpy(S + o_id, evs->pod_id, 4 * (size_t)n); std::memcpy(S + o_ns, evs->ns, 4 * (size_t)n);
+        std::memcpy(S + o_req, evs->request, 8 * (size_t)n * R);
+        if (evs->request_mask) std::memcpy(S + o_mask, evs->request_mask, 4 * (size_t)n);
+        SCU(cudaMemcpyAsync(B, S, ev_bytes, cudaMemcpyHostToDevice, st));
+    }
+    SCU(cudaMemsetAsync(A + rs.o_applied, 0, 16, st));
+    SCU(cudaEventRecord(ev[1], st));
+    if (n) {
+        DevEvents de;
+        de.n = n; de.op = B + o_op; de.pod_id = (const int32_t*)(B + o_id); de.ns = (const int32_t*)(B + o_ns);
+        de.req = (const long long*)(B + o_req); de.mask = evs->request_mask ? (const uint32_t*)(B + o_mask) : nullptr;
+        de.present = (unsigned*)(A + rs.o_present); de.applied = (int32_t*)(A + rs.o_applied);
+        k_quota_events<<<(n + 15) / 16, 256, 0, st>>>(rs.q, de);
+    }
+    const bool want_agg = out && (out->agg_min || out->agg_used || out->agg_overquota || out->agg_masks || out->guaranteed);
+    if (want_agg) k_quota_aggregate<<<1, AGG_THREADS, 0, st>>>(rs.q);
+    SCU(cudaGetLastError());
+    SCU(cudaEventRecord(ev[2], st));
+    // outputs: the span asked for, plus the counter
+    size_t d_lo = rs.o_applied, d_hi = rs.o_applied + 16;
+    auto span = [&](const void* wanted, size_t at, size_t bytes) { if (wanted && bytes) { d_lo = std::min(d_lo, at); d_hi = std::max(d_hi, at + bytes); } };
+    if (out) {
+        span(out->used, rs.o_used, 8 * ER); span(out->used_mask, rs.o_umask, 4 * (size_t)E); span(out->agg_min, rs.o_amin, 8 * QR);
+        span(out->agg_used, rs.o_aused, 8 * QR); span(out->agg_overquota, rs.o_aover, 8 * QR); span(out->agg_masks, rs.o_amask, 16);
+        span(out->guaranteed, rs.o_guar, 8 * ER);
+    }
+    // the span may bridge the presence bitmap (it lies between the rows and the counter): fetch the counter on its own then
+    const bool split = d_lo < rs.o_present;
+    const size_t first_hi = split ? std::min(d_hi, rs.o_present) : d_hi;
+    if (split) {
+        SCU(cudaMemcpyAsync(S + d_lo, A + d_lo, first_hi - d_lo, cudaMemcpyDeviceToHost, st));
+        SCU(cudaMemcpyAsync(S + first_hi + 256, A + rs.o_applied, 16, cudaMemcpyDeviceToHost, st));
+    } else SCU(cudaMemcpyAsync(S + d_lo, A + d_lo, d_hi - d_lo, cudaMemcpyDeviceToHost, st));
+    SCU(cudaStreamSynchronize(st));
+    auto back = [&](void* dst, size_t at, size_t bytes) { if (dst && bytes) std::memcpy(dst, S + at, bytes); };
+    if (out) {
+        back(out->used, rs.o_used, 8 * ER); back(out->used_mask, rs.o_umask, 4 * (size_t)E); back(out->agg_min, rs.o_amin, 8 * (size_t)R);
+        back(out->agg_used, rs.o_aused, 8 * (size_t)R); back(out->agg_overquota, rs.o_aover, 8 * (size_t)R); back(out->agg_masks, rs.o_amask, 12);
+        back(out->guaranteed, rs.o_guar, 8 * ER);
+    }
+    int32_t applied = 0;
+    std::memcpy(&applied, S + (split ? first_hi + 256 : rs.o_applied), 4);
+    if (n_applied) *n_applied = applied;
+    if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
+    if (h2d_bytes) *h2d_bytes = (long long)(n ? ev_bytes : 0);
+    if (d2h_bytes) *d2h_bytes = (long long)((split ? first_hi - d_lo + 16 : d_hi - d_lo));
+    return NOSPLAN_OK;
+#undef SCU
+}
+
 extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx) {
     if (!ctx) return;
     if (ctx->d) cudaFree(ctx->d);
     if (ctx->hs) cudaFreeHost(ctx->hs);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->preempt_resident && ctx->preempt_resident_free) ctx->preempt_resident_free(ctx->preempt_resident);
+    if (ctx->quota_resident && ctx->quota_resident_free) ctx->quota_resident_free(ctx->quota_resident);
     delete ctx;
 }
 extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new() { return new nosplan_quota_ctx(); }

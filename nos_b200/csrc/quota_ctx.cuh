@@ -11,6 +11,10 @@ struct nosplan_quota_ctx {
     // entry points a context of their own, so no other call overwrites it); owned by preempt.cu
     void* preempt_resident = nullptr;
     void (*preempt_resident_free)(void*) = nullptr;
+    // nosplan_quota_state_begin keeps the quota tables, Used and the set of accounted pods in `d` for
+    // nosplan_quota_state_apply (again in a context of its own); owned by quota.cu
+    void* quota_resident = nullptr;
+    void (*quota_resident_free)(void*) = nullptr;
 };
 
 // the context's four timing events (created once; an error path of a call has nothing to give back)
