@@ -340,6 +340,10 @@ int nosplan_quota_state_begin(nosplan_t* h, const nosplan_quotas* quotas, int32_
 int nosplan_quota_state_apply(nosplan_t* h, const nosplan_quota_events* events, nosplan_quota_out* out,
                               int32_t* n_applied /* [1] out, may be NULL: events that changed the state */, nosplan_stats* stats);
 
+/* The quota part of CapacityScheduling.PreFilter (capacity_scheduling.go:190-278) for a batch of pending pods against the
+ * resident state as the events applied so far left it: verdict[i] = NOSPLAN_PREFILTER_*. */
+int nosplan_quota_state_prefilter(nosplan_t* h, const nosplan_quota_pods* pending, uint8_t* verdict /* [n_pods] */, nosplan_stats* stats);
+
 /* The operator pass returning only what has to be patched.  The reference walks the pods of a
  * quota in the order of sortPodListForFindingOverQuotaPods and calls patchCapacityInfoIfDifferent on each
  * (internal/controllers/elasticquota/elasticquota.go:44-60, :120-149): a pod is patched iff its label

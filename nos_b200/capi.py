@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
-    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply",
+    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply", "nosplan_quota_state_prefilter",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -606,6 +606,18 @@ class Engine:
             t = res.trimmed()
             d = {k: t[k] for k in ("used", "used_mask", "agg_min", "agg_used", "agg_overquota", "agg_masks", "guaranteed")}
         return d, int(applied[0]), st.as_dict()
+
+    def quota_state_prefilter(self, pending):
+        """nosplan_quota_state_prefilter -> verdict per pending pod (uint8) against the resident quota state."""
+        from . import quota_packing as qp
+        cp, k = qp.c_quota_pods(pending)
+        verdict = np.zeros(max(1, pending.n_pods), np.uint8)
+        st = CStats()
+        self.lib.nosplan_quota_state_prefilter.argtypes = [C.c_void_p, C.POINTER(qp.CQuotaPods), C.c_void_p, C.POINTER(CStats)]
+        self.lib.nosplan_quota_state_prefilter.restype = C.c_int
+        self._check(self.lib.nosplan_quota_state_prefilter(self.h, C.byref(cp), verdict.ctypes.data, C.byref(st)), "nosplan_quota_state_prefilter")
+        del k
+        return verdict[:pending.n_pods], st.as_dict()
 
     def preempt_dryrun_again(self, query):
         """nosplan_preempt_dryrun_again: `query`'s preemptor against the cluster state the last preempt_dryrun() uploaded."""

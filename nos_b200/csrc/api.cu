@@ -54,6 +54,8 @@ extern "C" int nosplan_quota_state_begin_impl(int device, cudaStream_t st, nospl
 extern "C" int nosplan_quota_state_apply_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, nosplan_quota_ctx* scratch, std::string* err,
                                               const nosplan_quota_events* evs, nosplan_quota_out* out, int32_t* n_applied,
                                               float* ms_k, long long* h2d_bytes, long long* d2h_bytes);
+extern "C" int nosplan_quota_state_prefilter_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, nosplan_quota_ctx* scratch, std::string* err,
+                                                  const nosplan_quota_pods* pending, uint8_t* verdict, float* ms_k);
 extern "C" int nosplan_preempt_dryrun_again_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
                                                  const nosplan_preempt_query* pq, uint8_t* victim, int32_t* node_status,
                                                  int32_t* num_violating, float* ms_k, float* ms_d2h, int* launches, long long* d2h_bytes);
@@ -1070,6 +1072,16 @@ int nosplan_quota_state_apply(nosplan_t* h, const nosplan_quota_events* events, 
         std::memset(stats, 0, sizeof *stats);
         stats->ms_kernels = k; stats->h2d_bytes = hb; stats->d2h_bytes = db; stats->kernel_launches = 2;
     }
+    return rc;
+}
+
+int nosplan_quota_state_prefilter(nosplan_t* h, const nosplan_quota_pods* pending, uint8_t* verdict, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->ectx) { h->err = "nosplan_quota_state_prefilter: no quota state resident on this handle (call nosplan_quota_state_begin first)"; return NOSPLAN_E_INVALID; }
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    float k = 0;
+    const int rc = nosplan_quota_state_prefilter_impl(h->device, h->stream, h->ectx, h->qctx, &h->err, pending, verdict, &k);
+    if (stats) { std::memset(stats, 0, sizeof *stats); stats->ms_kernels = k; stats->kernel_launches = 2; }
     return rc;
 }
 

@@ -847,6 +847,45 @@ extern "C" int nosplan_quota_state_apply_impl(int device, cudaStream_t st, nospl
 #undef SCU
 }
 
+// the quota part of PreFilter (capacity_scheduling.go:190-278) for a batch of pending pods against the resident state
+extern "C" int nosplan_quota_state_prefilter_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, nosplan_quota_ctx* scratch, std::string* err,
+                                                  const nosplan_quota_pods* pending, uint8_t* verdict, float* ms_k) {
+    auto fail = [&](int code, const char* msg, const char* detail = "") { if (err) *err = std::string(msg) + detail; return code; };
+#define SCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(NOSPLAN_E_CUDA, #call ": ", cudaGetErrorString(e_)); } while (0)
+    QuotaResident* rp = ctx ? static_cast<QuotaResident*>(ctx->quota_resident) : nullptr;
+    if (!rp || !rp->valid) return fail(NOSPLAN_E_INVALID, "nosplan_quota_state_prefilter: no quota state resident on this handle (call nosplan_quota_state_begin first)");
+    const int Pp = pending ? pending->n_pods : 0;
+    if (Pp < 0) return fail(NOSPLAN_E_INVALID, "negative size");
+    if (Pp == 0) return NOSPLAN_OK;
+    if (!verdict || !pending->ns || !pending->request) return fail(NOSPLAN_E_INVALID, "ns, request and verdict are required");
+    const int R = rp->q.R;
+    SCU(cudaSetDevice(device));
+    cudaEvent_t* ev = nullptr;
+    SCU(quota_ctx_events(ctx, &ev));
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t o_ns = 0, o_req = al(4 * (size_t)Pp), o_mask = o_req + al(8 * (size_t)Pp * R), o_out = o_mask + al(4 * (size_t)Pp), total = o_out + al((size_t)Pp);
+    SCU(quota_ctx_ensure(scratch, total, total));
+    unsigned char* S = scratch->hs; unsigned char* B = scratch->d;
+    std::memcpy(S + o_ns, pending->ns, 4 * (size_t)Pp); std::memcpy(S + o_req, pending->request, 8 * (size_t)Pp * R);
+    if (pending->request_mask) std::memcpy(S + o_mask, pending->request_mask, 4 * (size_t)Pp);
+    SCU(cudaMemcpyAsync(B, S, o_out, cudaMemcpyHostToDevice, st));
+    DevQuota q = rp->q;
+    q.Pp = Pp; q.p_ns = (const int32_t*)(B + o_ns); q.p_req = (const long long*)(B + o_req);
+    q.p_mask = pending->request_mask ? (const uint32_t*)(B + o_mask) : nullptr;
+    q.prefilter = B + o_out;
+    SCU(cudaEventRecord(ev[1], st));
+    k_quota_aggregate<<<1, AGG_THREADS, 0, st>>>(q);          // the aggregates of the state as it is now
+    k_quota_prefilter<<<(Pp + 15) / 16, 256, 0, st>>>(q);
+    SCU(cudaGetLastError());
+    SCU(cudaEventRecord(ev[2], st));
+    SCU(cudaMemcpyAsync(S + o_out, B + o_out, (size_t)Pp, cudaMemcpyDeviceToHost, st));
+    SCU(cudaStreamSynchronize(st));
+    std::memcpy(verdict, S + o_out, (size_t)Pp);
+    if (ms_k) cudaEventElapsedTime(ms_k, ev[1], ev[2]);
+    return NOSPLAN_OK;
+#undef SCU
+}
+
 extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx) {
     if (!ctx) return;
     if (ctx->d) cudaFree(ctx->d);

@@ -111,6 +111,23 @@ def test_c4_size_against_the_batch_engine(eng):
     assert applied == 0 and np.array_equal(got["used"], full["used"]) and np.array_equal(got["guaranteed"], full["guaranteed"])
 
 
+def test_prefilter_against_the_resident_state(eng):
+    """PreFilter verdicts read from the resident state = the batch engine's verdicts for the same accounted pods."""
+    pq, run, pend = synth.quota_state(300, 30_000, 5_000, seed=12)
+    eng.quota_state_begin(pq, run.n_pods)
+    ids = np.arange(run.n_pods, dtype=np.int32)
+    eng.quota_state_apply(np.zeros(run.n_pods, np.uint8), ids, run.ns, run.request, run.request_mask, outputs=False)
+    verdict, _ = eng.quota_state_prefilter(pend)
+    exp = ol.quota(pq, run, pend)["prefilter"]
+    assert np.array_equal(verdict, exp) and len(set(exp.tolist())) > 1
+    from nos_b200 import sharded
+    gone = np.flatnonzero(ids % 2 == 0).astype(np.int32)
+    eng.quota_state_apply(np.ones(len(gone), np.uint8), gone, run.ns[gone], run.request[gone], run.request_mask[gone], outputs=False)
+    verdict, _ = eng.quota_state_prefilter(pend)
+    exp2 = ol.quota(pq, sharded.take_pods(run, np.flatnonzero(ids % 2 == 1)), pend)["prefilter"]
+    assert np.array_equal(verdict, exp2) and not np.array_equal(exp, exp2)
+
+
 def test_errors(eng):
     fresh = capi.Engine(0)
     pq, run, _ = synth.quota_state(5, 20, 0, seed=2)
