@@ -148,6 +148,10 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
 int nosplan_plan_resident(nosplan_t* h, const nosplan_pods* pods, const uint8_t* prefilter_ok, int32_t filter_mode,
                           nosplan_partitioning* out, nosplan_stats* stats);
 int nosplan_update_nodes(nosplan_t* h, int32_t first, const nosplan_snapshot* rows);
+/* nosplan_upload for the pods alone, against the resident snapshot: what nosplan_plan_resident does before it runs the
+ * kernels, for the callers that drive the run themselves (nosplan_run, the sliced and sharded protocols: every rank keeps
+ * its slice of the nodes resident). */
+int nosplan_upload_pods(nosplan_t* h, const nosplan_pods* pods, const uint8_t* prefilter_ok, int32_t filter_mode);
 
 /* Change detection for the actuator.  Actuator.Apply (core/actuator.go:39-66) compares the
  * desired state with the current one as a whole (PartitioningState.Equal, state/partitioning.go:33-56) and then patches EVERY

@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_host_pod_order", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
-    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply", "nosplan_quota_state_prefilter",
+    "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_upload_pods", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply", "nosplan_quota_state_prefilter",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -399,6 +399,15 @@ class Engine:
             e.partial = (idx[:min(int(n[0]), cap)].copy(), int(n[0]))
             raise e
         return idx[:int(n[0])]
+
+    def upload_pods(self, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0):
+        """nosplan_upload_pods: new pods against the resident snapshot, kernels not run yet."""
+        cp, k2 = c_pods(pods)
+        pre, k3 = self._pre(prefilter_ok, pods.n_pods)
+        self.lib.nosplan_upload_pods.argtypes = [C.c_void_p, C.POINTER(CPods), C.c_void_p, C.c_int32]
+        self.lib.nosplan_upload_pods.restype = C.c_int
+        self._check(self.lib.nosplan_upload_pods(self.h, C.byref(cp), pre, filter_mode), "nosplan_upload_pods")
+        del k2, k3
 
     def update_nodes(self, first: int, rows: PackedSnapshot):
         """nosplan_update_nodes: overwrite nodes [first, first + rows.n_nodes) of the resident snapshot."""

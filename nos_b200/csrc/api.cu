@@ -1007,6 +1007,12 @@ int nosplan_plan_resident(nosplan_t* h, const nosplan_pods* pods, const uint8_t*
     return nosplan_download(h, out, stats);
 }
 
+int nosplan_upload_pods(nosplan_t* h, const nosplan_pods* pods, const uint8_t* prefilter_ok, int32_t filter_mode) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->nodes_resident) return fail(h, NOSPLAN_E_INVALID, "nosplan_upload_pods: no snapshot resident on this handle (call nosplan_plan or nosplan_upload first)");
+    return upload_impl(h, &h->res_snap, pods, prefilter_ok, filter_mode, true);
+}
+
 int nosplan_update_nodes(nosplan_t* h, int32_t first, const nosplan_snapshot* rows) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->nodes_resident) return fail(h, NOSPLAN_E_INVALID, "nosplan_update_nodes: no snapshot resident on this handle");

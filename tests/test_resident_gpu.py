@@ -71,6 +71,49 @@ def test_update_nodes(eng):
         same_as_oracle(eng.plan_resident(pods, None, pk.FILTER_RESOURCES_FIT), cur, pods, pk.FILTER_RESOURCES_FIT)
 
 
+def test_sliced_ranks_keep_their_slices_resident():
+    """Slice mode on two emulated ranks: the slices are uploaded once, then two more pod lists are planned with
+    nosplan_upload_pods + the sliced protocol; rows and counters are the oracle's each time."""
+    import torch
+    dev = torch.device("cuda", 0)
+    world = 2
+    snap, pods = synth.mig_cluster(400, 8, 900, seed=71, regime="saturating")
+    G = snap.gpus_per_node
+    engines, planners, slices = [], [], []
+    for r in range(world):
+        lo, hi = sharded.shard_range(snap.n_nodes, r, world)
+        e = capi.Engine(0)
+        e.upload(sharded.slice_snapshot(snap, lo, hi, pad_to=(snap.n_nodes + world - 1) // world), pods, None, pk.FILTER_RESOURCES_FIT)
+        engines.append(e); slices.append((lo, hi))
+    for step, seed in enumerate((71, 72, 73)):
+        _, pp = synth.mig_cluster(400, 8, 900 if step < 2 else 3000, seed=seed, regime="saturating")
+        ocnt, omsk, ost, _ = ol.plan(snap, pp, None, pk.FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+        planners = []
+        for r, e in enumerate(engines):
+            if step:
+                e.upload_pods(pp, None, pk.FILTER_RESOURCES_FIT)
+            p = sharded.SlicedPlanner(e, r, world, dev, all_gather=lambda dst, src: None)
+            p.prepare()
+            planners.append(p)
+        for e, p in zip(engines, planners):
+            e.slice_begin(p.tot_local.data_ptr())
+        torch.cuda.synchronize()
+        tot_all = torch.cat([p.tot_local for p in planners])
+        for r, (e, p) in enumerate(zip(engines, planners)):
+            e.slice_mid(r, world, tot_all.data_ptr(), p.local.data_ptr(), p.nbytes)
+        torch.cuda.synchronize()
+        gathered = torch.cat([p.local for p in planners])
+        for e, (lo, hi) in zip(engines, slices):
+            e.shard_end(gathered.data_ptr(), world)
+            cnt, msk, st = e.download()
+            n = (hi - lo) * G
+            assert np.array_equal(cnt[:n], ocnt[lo * G:hi * G]) and np.array_equal(msk[:n], omsk[lo * G:hi * G]), step
+            for k in ("candidates", "visited_nodes", "placements", "geometry_evals", "lacking_at_end"):
+                assert st[k] == ost[k], (step, k)
+    for e in engines:
+        e.close()
+
+
 def test_errors(eng):
     fresh = capi.Engine(0)
     snap, pods = synth.mig_cluster(20, 4, 30, seed=3)
