@@ -904,25 +904,33 @@ __global__ void __launch_bounds__(256, 1) k_plan_sweep(DevProblem pb, int32_t* c
             pc.key[r][l] = pb.pod_key[s]; pc.flag[r][l] = pb.pod_flags[s];
         }
     }
-    {   // ordered compaction of candidate flags -> cand_idx (GetCandidateNodes, core/snapshot.go:119-130)
+    // ordered compaction of candidate flags -> cand_idx (GetCandidateNodes, core/snapshot.go:119-130): 1024 nodes per step, four
+    // flag bytes per thread in one load, warp scan + eight warp totals.  Not reached on the reference's early return
+    // (nothing lacking, planner.go:80-83), where the list is never asked for.
+    if (lack_start > 0) {
         int base = 0;
-        for (int c0 = 0; c0 < pb.N; c0 += blockDim.x) {
-            const int i = c0 + tid;
-            const int f = (i < pb.N) ? pb.cand_flag[i] : 0;
-            s_scan[tid] = f;
+        int* s_wsum = s_scan;
+        for (int c0 = 0; c0 < pb.N; c0 += 4 * (int)blockDim.x) {
+            const int i0 = c0 + 4 * tid;
+            unsigned f4 = 0;
+            if (i0 + 3 < pb.N) f4 = *reinterpret_cast<const unsigned*>(pb.cand_flag + i0);
+            else for (int k = 0; k < 4; ++k) if (i0 + k < pb.N && pb.cand_flag[i0 + k]) f4 |= 1u << (8 * k);
+            const int cnt = ((f4 & 0xffu) != 0) + ((f4 & 0xff00u) != 0) + ((f4 & 0xff0000u) != 0) + ((f4 & 0xff000000u) != 0);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+            if (lane == 31) s_wsum[warp] = incl;
             __syncthreads();
-            for (int o = 1; o < (int)blockDim.x; o <<= 1) {
-                int v = (tid >= o) ? s_scan[tid - o] : 0;
-                __syncthreads();
-                s_scan[tid] += v;
-                __syncthreads();
-            }
-            if (f) cand_idx[base + s_scan[tid] - 1] = i;
-            base += s_scan[blockDim.x - 1];
+            int woff = 0, total = 0;
+            for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { const int t = s_wsum[w]; if (w < warp) woff += t; total += t; }
+            int pos = base + woff + incl - cnt;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (f4 >> (8 * k) & 0xffu) cand_idx[pos++] = i0 + k;
+            base += total;
             __syncthreads();
         }
         if (tid == 0) s_ncand = base;
-    }
+    } else if (tid == 0) s_ncand = 0;
     __syncthreads();
     if (warp != 0) return;
 
