@@ -1001,6 +1001,7 @@ constexpr size_t SWEEP_CHUNK_BYTES = (size_t)RUN_CACHE * 32 * (8 + 8 + 8 + 4 + 4
 //                                    grid sync
 // Exact by construction: a node's decisions depend on earlier nodes only through the lacking vector (the gate is vacuous
 // for consistent node accounts, see fast_applicable), and the reference's loop exit (planner.go:94-97) is the wave loop's.
+constexpr int WAVE_PRELUDE = 3;            // candidates the chain takes before the first wave
 __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
     __shared__ Tables tb;
     __shared__ WarpScratch ws_all[4];
@@ -1084,7 +1085,33 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
     const int total_warps = gridDim.x * (blockDim.x >> 5), gw = blockIdx.x * (blockDim.x >> 5) + warp;
     long long st_evals = 0, st_place = 0, st_visited = 0, D = 0;
     bool committed = true;
-    int a = 0, n_waves = 0;
+    // ---- a short chain first: a handful of pending pods is usually satisfied by the first candidate or two, and a node of the
+    //      chain costs less than a wave with its two grid barriers.  One warp takes the first WAVE_PRELUDE candidates in name
+    //      order exactly as the chain does (removed-set in global memory) and leaves the vector, the counters and the node to
+    //      go on from where the waves read them; if the vector is empty by then the wave loop ends before its first wave.
+    if (gw == 0) {
+        int lack = lack0, dirty_unused = 0, i = 0, seen = 0;
+        long long Dc = (lane < KP) ? pb.tot[lane] : 0, vis = 0, ev = 0, pl = 0;
+        bool comm = false, upd_unused = false;
+        for (; i < pb.N && seen < WAVE_PRELUDE; ++i) {
+            if (!pb.cand_flag[i]) continue;
+            if (__ballot_sync(FULL, lack > 0) == 0) break;         // planner.go:94-97
+            NodeRegs nr;
+            load_node(pb, i, lane, nr);
+            store_node(ws.nd, nr, i, lane);
+            __syncwarp();
+            ++vis; ++seen;
+            process_node<M_SEQ>(pb, ws, tb, &pc, pb.placed, lack, Dc, comm, ev, pl, lane, dirty_unused, upd_unused);
+        }
+        if (lane < KP) pb.lack[lane] = lack;
+        if (lane == 0) {
+            pb.acc[0] += (unsigned long long)pl; pb.acc[1] += (unsigned long long)ev; pb.acc[2] += (unsigned long long)vis;
+            pb.wave[4] = i;
+        }
+        __threadfence();
+    }
+    grid.sync();
+    int a = __ldcg(&pb.wave[4]), n_waves = 0;
     for (;;) {
         const int lack = (lane < KP) ? __ldcg(&pb.lack[lane]) : 0;
         if (a >= pb.N || __ballot_sync(FULL, lack > 0) == 0) break;          // planner.go:94-97
