@@ -9,6 +9,7 @@
 //   pod <namespace> <name> <priority|->  container <res>=<n>,...|-   init <res>=<n>,...|-
 //   sa|sb <node> [<gpu index> <res>=<n>,...]   (two partitioning states for `run equal`)
 //   planid <id>             (plan id for `run apply`; default "plan")
+//   clientdrop <node>       (`run apply`: the node is in the snapshot but the API client does not find it)
 //   run plan | run pack | run state | run diff | run equal | run apply | run pluginconfig
 // stdout: `run plan`  -> "node <name>" / "gpu <index> <res>=<n>,..." lines, then "stats ..." ;
 //         `run pack`  -> one "<array> v v v" line per packed buffer;  `run state` -> the snapshot's current state;
@@ -72,6 +73,7 @@ int main() {
     mig::KnownGeometries custom;
     state::PartitioningState stA, stB;
     std::string line, mode, planId = "plan";
+    std::vector<std::string> clientDrop;
     try {
         while (std::getline(std::cin, line)) {
             std::stringstream ss(line);
@@ -102,6 +104,7 @@ int main() {
                 }
             }
             else if (cmd == "planid") planId = a;
+            else if (cmd == "clientdrop") clientDrop.push_back(a);      // node the API client of `run apply` does not hold
             else if (cmd == "run") { mode = a; break; }
             else throw Error("unknown directive " + cmd);
         }
@@ -122,7 +125,9 @@ int main() {
         if (mode == "apply") {
             core::PartitioningPlan plan = core::NewPartitioningPlan(stA);
             plan.id = planId;
-            core::ApplyResult r = core::Apply(kind, cluster, snap, plan);
+            state::ClusterState client = cluster;                          // the snapshot was taken; the client may have lost nodes since
+            for (auto& n : clientDrop) client.erase(n);
+            core::ApplyResult r = core::Apply(kind, client, snap, plan);
             std::cout << "applied " << (r.applied ? "true" : "false") << '\n';
             for (auto& p : r.patches) {
                 std::cout << "node " << p.node << '\n';
