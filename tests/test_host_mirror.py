@@ -296,3 +296,31 @@ def test_actuator_decision_golden():
             assert code == 1 and out.startswith("error"), (c["name"], out)
         else:
             assert code == 0 and out.splitlines()[0] == ("applied true" if c["expected_res"] else "applied false"), (c["name"], out)
+
+
+def test_memory_label_and_partitioning_kind_golden():
+    """pkg/gpu/util_test.go:28-69 (GetMemoryGB) and pkg/gpu/partitioning_test.go:29-153 (which kind a node's label selects),
+    through the Python model and the C++ snapshot takers."""
+    import nos_model as m
+    g = _adapters()
+    base = {"nos.nebuly.com/gpu-partitioning": "mps", "nvidia.com/gpu.count": "1", "nvidia.com/gpu.product": "NVIDIA-A100-40GB-SXM4"}
+    for c in g["get_memory_gb"]:
+        node = {"name": "node-1", "labels": dict(base, **c["labels"]), "annotations": {}}
+        code, out = hc.run(hc.to_text("mps", [node], [], "pack"))
+        if c["expected_err"]:
+            assert code == 1 and out.startswith("error"), (c["name"], out)
+            with pytest.raises(Exception):
+                m.new_mps_node(node)
+        else:
+            assert code == 0 and int(hc.parse_pack(out)["gpu_memory_gb"][0]) == c["expected"], (c["name"], out)
+            assert m.gpu_memory_gb(node["labels"]) == c["expected"]
+    for c in g["partitioning_kind"]:
+        labels = {"nvidia.com/gpu.count": "1", "nvidia.com/gpu.product": "NVIDIA-A100-40GB-SXM4", "nvidia.com/gpu.memory": "40000"}
+        if c["label"] is not None:
+            labels["nos.nebuly.com/gpu-partitioning"] = c["label"]
+        node = {"name": "node-1", "labels": labels, "annotations": {}}
+        for kind in ("mig", "mps"):
+            code, out = hc.run(hc.to_text(kind, [node], [], "state"))
+            st, _, _ = hc.parse_state(out)
+            assert code == 0 and (("node-1" in st) == c[kind]), (c["name"], kind, out)
+            assert ("node-1" in m.take_snapshot(kind, [node]).get_nodes()) == c[kind]
