@@ -1,8 +1,10 @@
 // TEST INFRASTRUCTURE ONLY -- CPU restatement, on the packed structs of include/nosplan.h, of the whole of
 // preemptor.SelectVictimsOnNode (pkg/scheduler/plugins/capacityscheduling/capacity_scheduling.go:468-675).
-// Checked against oracle/nos_quota_model.py:select_victims_on_node on random cases.  The reference's own test of this path
-// (TestDryRunPreemption) only counts candidates, and NodeInfo / NodeResourcesFit come from k8s.io/kubernetes v1.25.4, which
-// is not in the reference tree: parity is pinned by the line-by-line restatement only ("parity unpinned").
+// Checked against oracle/nos_quota_model.py:select_victims_on_node on random cases and on the three fixtures of the reference's own
+// test of this path (TestDryRunPreemption, capacity_scheduling_test.go:249-535 -> tests/golden/dryrun_preemption.json): that test
+// asserts the candidate count only, which is what it pins here; the victims its `want` names are reproduced where they do not
+// depend on the order of equal-priority pods.  NodeInfo / NodeResourcesFit come from k8s.io/kubernetes v1.25.4, which is not in
+// the reference tree: restated.
 #include <algorithm>
 #include <cmath>
 #include <cstdint>

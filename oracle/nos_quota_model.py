@@ -338,8 +338,8 @@ def select_potential_victims(infos: ElasticQuotaInfos, preemptor: Pod, nominated
 # ------------------------------------------------------------------------------------------------------------
 # preemption dry run, the whole of preemptor.SelectVictimsOnNode (capacity_scheduling.go:468-675) for one node:
 # first pass as above, Filter with the potential victims gone, quota checks, the PDB split, and the reprieve loops.
-# Third-party pieces restated from k8s.io/kubernetes v1.25.4 (not in /root/reference; parity unpinned by the reference, whose
-# TestDryRunPreemption only counts candidates): NodeInfo.RemovePod / AddPodInfo (Requested and len(Pods) bookkeeping, an
+# Third-party pieces restated from k8s.io/kubernetes v1.25.4 (not in /root/reference; the reference's TestDryRunPreemption
+# asserts the candidate count only -- its three fixtures are tests/golden/dryrun_preemption.json): NodeInfo.RemovePod / AddPodInfo (Requested and len(Pods) bookkeeping, an
 # error when the pod is not on the node), NodeResourcesFit as the only Filter, no nominated pods on the node.
 # ------------------------------------------------------------------------------------------------------------
 VICTIMS_OK, VICTIMS_NONE, VICTIMS_FILTER, VICTIMS_MAX_QUOTA, VICTIMS_MIN_QUOTA, VICTIMS_ERROR = 0, 1, 2, 3, 4, 5

@@ -178,3 +178,18 @@ def test_again_without_a_resident_state():
     with pytest.raises(capi.NosplanError, match="no cluster state resident"):
         fresh.preempt_dryrun_again(query)
     fresh.close()
+
+
+def test_reference_dryrun_preemption_fixtures(eng):
+    """capacity_scheduling_test.go:249-535 (TestDryRunPreemption) through the C-ABI: the candidate count the reference asserts and
+    the victims its `want` names where they do not depend on the order of equal-priority pods."""
+    from support import dryrun_golden as dg
+    for c, quotas, running, nodes, preemptor, gb, pdb_allowed, extra in dg.cases():
+        pq, query = pc.packed_dryrun_query(quotas, running, nodes, preemptor, gb, pdb_allowed, extra, engine_used_fn(eng))
+        gv, gs, gn, _ = eng.preempt_dryrun(pq, query)
+        ev, es, en = ol.preempt_dryrun(pq, query)
+        assert np.array_equal(gv, ev) and np.array_equal(gs, es) and np.array_equal(gn, en), c["name"]
+        assert int((gs == pp.VICTIMS_OK).sum()) == c["expected_candidates"], (c["name"], gs)
+        if c["expected_victims"] is not None:
+            assert [p["name"] for p, v in zip(nodes[0]["pods"], gv) if v] == c["expected_victims"], c["name"]
+        assert int(gn.sum()) == 0

@@ -34,3 +34,18 @@ def test_every_status_occurs():
     if TOTAL["blocks"] < 4:
         pytest.skip("runs after the four blocks above, in one process")
     assert all(TOTAL[s] > 0 for s in range(6)) and TOTAL["violating"] > 0, TOTAL
+
+
+def test_reference_dryrun_preemption_fixtures():
+    """capacity_scheduling_test.go:249-535 (TestDryRunPreemption): the candidate count the reference asserts, and the victims its
+    `want` names where they do not depend on the order of equal-priority pods -- Python model and packed oracle."""
+    from support import dryrun_golden as dg
+    for c, quotas, running, nodes, preemptor, gb, pdb_allowed, extra in dg.cases():
+        ev, es, en = pc.model_dryrun(quotas, running, nodes, preemptor, gb, pdb_allowed, extra)
+        pq, query = pc.packed_dryrun_query(quotas, running, nodes, preemptor, gb, pdb_allowed, extra, oracle_used)
+        gv, gs, gn = ol.preempt_dryrun(pq, query)
+        assert np.array_equal(gv, ev) and np.array_equal(gs, es) and np.array_equal(gn, en), c["name"]
+        assert int((es == 0).sum()) == c["expected_candidates"], (c["name"], es)
+        if c["expected_victims"] is not None:
+            assert [p["name"] for p, v in zip(nodes[0]["pods"], ev) if v] == c["expected_victims"], c["name"]
+        assert int(en.sum()) == 0                                           # NumPDBViolations: 0 in every `want`
