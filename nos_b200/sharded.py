@@ -176,13 +176,19 @@ class SlicedPlanner:
         state_out = t.zeros(n, dtype=t.uint8, device=self.device)
         send = send or (lambda x, dst: dist.send(x, dst, group=self.group))
         recv = recv or (lambda x, src: dist.recv(x, src, group=self.group))
-        stream = t.cuda.ExternalStream(self.engine.stream(), device=self.device)
-        with t.cuda.stream(stream):
+        def turn():
             if self.rank > 0:
                 recv(state_in, self.rank - 1)
             self.engine.slice_chain(state_in.data_ptr() if self.rank > 0 else 0, state_out.data_ptr())
             if self.rank + 1 < self.world:
                 send(state_out, self.rank + 1)
+
+        if str(self.device) == "cpu":                          # host-side plumbing only (tests with a stand-in engine, gloo)
+            turn()
+            return state_out
+        stream = t.cuda.ExternalStream(self.engine.stream(), device=self.device)
+        with t.cuda.stream(stream):
+            turn()
         stream.synchronize()
         return state_out
 

@@ -141,3 +141,58 @@ def test_assign_quotas_balances_and_keeps_a_quota_whole():
             sizes.append(len(idx))
         biggest = np.bincount(pq.ns_quota[run.ns][pq.ns_quota[run.ns] >= 0]).max()
         assert sum(sizes) == run.n_pods and max(sizes) <= max(biggest, run.n_pods // world + biggest // 2 + 1)
+
+
+# ---- the chained sweep of slice mode: the state block travels rank after rank (SlicedPlanner.chain) ---------------------
+class FakeChainEngine:
+    """Stands in for capi.Engine on CPU: its slice_chain adds this rank's share to the counters of the incoming block the way
+    k_plan_sweep does in chain mode (tests/test_sharded_gpu.py covers the kernel itself)."""
+
+    def __init__(self, rank):
+        self.rank = rank
+
+    def slice_chain_bytes(self):
+        return 224 + 8
+
+    def stream(self):
+        return 0
+
+    def slice_chain(self, d_in, d_out):
+        import ctypes
+        n = self.slice_chain_bytes()
+        block = np.zeros(n, np.uint8) if not d_in else np.frombuffer((ctypes.c_uint8 * n).from_address(d_in), np.uint8).copy()
+        c = block[64 + 128:64 + 128 + 32].view(np.int64)
+        c[0] += 10 + self.rank            # visited nodes
+        c[2] += 100 * (self.rank + 1)     # placements
+        c[3] += 7                         # candidate nodes
+        block[:64].view(np.int32)[0] = 3 - self.rank          # lacking of profile 0 shrinks along the chain
+        block[224 + self.rank] = 0xff                         # removed keys of this rank
+        ctypes.memmove(d_out, block.ctypes.data, n)
+
+
+def _chain_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sp = sharded.SlicedPlanner(FakeChainEngine(rank), rank, world, torch.device("cpu"))
+    state = sp.chain()
+    dist.broadcast(state, src=world - 1)
+    q.put((rank, sharded.chain_counters(state), state.numpy()[224:].tolist()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_chained_sweep_hand_over():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_chain_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, fin, removed in res:                                   # the last rank's block, on every rank
+        assert fin["visited_nodes"] == 10 + 11 and fin["placements"] == 100 + 200 and fin["candidate_nodes"] == 14
+        assert fin["lacking_at_end"] == 1 and removed[:2] == [255, 255]
