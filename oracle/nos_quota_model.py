@@ -132,6 +132,24 @@ def _quantity_value(name: str, v: int) -> int:
 
 
 class ElasticQuotaInfos(dict):  # namespace -> *ElasticQuotaInfo (a composite quota sits under several keys) :31-174
+    def add(self, e: "ElasticQuotaInfo") -> None:  # :68-72
+        for ns in sorted(e.namespaces):
+            self[ns] = e
+
+    def update(self, old: "ElasticQuotaInfo", new: "ElasticQuotaInfo") -> None:  # :51-66 (dict.update is not used on this class)
+        for ns in sorted(new.namespaces):
+            cur = self.get(ns)
+            if cur is not None:
+                new.pods, new.used = cur.pods, cur.used
+            self[ns] = new
+        for ns in sorted(old.namespaces):
+            if ns not in new.namespaces:
+                self.pop(ns, None)
+
+    def delete(self, e: "ElasticQuotaInfo") -> None:  # :45-49
+        for ns in sorted(e.namespaces):
+            self.pop(ns, None)
+
     def aggregated_min(self) -> Resource:  # :154-163
         tot = Resource()
         for e in self.values():

@@ -124,3 +124,44 @@ def test_patch_pods_and_compute_used():
     used, labels = q.patch_pods_and_compute_used(pods, {"cpu": 2500, "nos.nebuly.com/gpu-memory": 48}, {}, 16)
     assert [o for _, o in labels] == [False, False, True, True]
     assert used == {"cpu": 4000, "nos.nebuly.com/gpu-memory": 64}
+
+
+def _info(name, ns_name, namespaces):
+    e = q.ElasticQuotaInfo(name=name, namespaces=list(namespaces))
+    e.resource_namespace = ns_name
+    return e
+
+
+def test_elastic_quota_infos_add_update_golden():
+    """capacity_scheduling_test.go:562-700 (TestElasticQuotaInfos_Add / _Update): which namespace keys point at which quota after
+    Add and Update -- the map the packer's ns_quota row encodes."""
+    from nos_b200 import quota_packing as qp
+    # Add
+    infos = q.ElasticQuotaInfos(); infos.add(q.ElasticQuotaInfo())
+    assert len(infos) == 0                                                          # "Empty ElasticQuotaInfos, empty ElasticQuotaInfo"
+    infos = q.ElasticQuotaInfos({"ns-1": q.ElasticQuotaInfo()}); infos.add(q.ElasticQuotaInfo())
+    assert list(infos) == ["ns-1"]                                                  # "Empty ElasticQuotaInfo"
+    infos = q.ElasticQuotaInfos({"ns-1": _info("test", "test", [])})
+    infos.add(_info("updated", "updated", ["ns-2", "ns-3", "ns-4"]))               # "ElasticQuotaInfo with some namespaces not present"
+    assert sorted(infos) == ["ns-1", "ns-2", "ns-3", "ns-4"] and infos["ns-1"].name == "test"
+    assert all(infos[k].name == "updated" and sorted(infos[k].namespaces) == ["ns-2", "ns-3", "ns-4"] for k in ("ns-2", "ns-3", "ns-4"))
+    assert infos["ns-2"] is infos["ns-3"] is infos["ns-4"]                          # one object under several keys
+    # Update
+    infos = q.ElasticQuotaInfos()
+    infos.update(q.ElasticQuotaInfo(), _info("new-name", "new-ns", ["ns-1", "ns-2"]))   # "Empty ElasticQuotaInfos"
+    assert sorted(infos) == ["ns-1", "ns-2"] and all(e.name == "new-name" and e.resource_namespace == "new-ns" for e in infos.values())
+    infos = q.ElasticQuotaInfos()
+    infos.update(_info("old-name", "old-ns", ["ns-1", "ns-2"]), _info("new-name", "new-ns", ["ns-2", "ns-3"]))
+    assert sorted(infos) == ["ns-2", "ns-3"] and all(sorted(e.namespaces) == ["ns-2", "ns-3"] for e in infos.values())
+    # Update carries Used and the accounted pods over (elasticquotainfo.go:54-57), Delete drops every key of the quota (:45-49)
+    old = _info("eq", "ns", ["ns-1"]); old.used = m.resource_from_list({"cpu": 500}); old.pods = {"uid-1"}
+    infos = q.ElasticQuotaInfos(); infos.add(old)
+    new = _info("eq", "ns", ["ns-1", "ns-9"]); new.used = m.Resource()
+    infos.update(old, new)
+    assert infos["ns-9"].used.milli_cpu == 500 and infos["ns-9"].pods == {"uid-1"}
+    infos.delete(new)
+    assert len(infos) == 0
+    # the packer's map: every namespace of a composite quota points at the quota's one row
+    pq, _ = qp.pack_quotas({"test": {"namespaces": ["ns-1"], "min": {"cpu": 1}}, "updated": {"namespaces": ["ns-2", "ns-3", "ns-4"], "min": {"cpu": 1}}}, [], 8)
+    row = {ns: int(pq.ns_quota[i]) for i, ns in enumerate(pq.namespaces)}
+    assert row["ns-1"] == pq.names.index("test") and row["ns-2"] == row["ns-3"] == row["ns-4"] == pq.names.index("updated")
