@@ -98,6 +98,17 @@ def validate_known_geometries(configs: Dict[str, List[Dict[str, int]]]) -> None:
                     raise PackError(f"invalid quantity {quantity} for profile {profile}")
 
 
+def group_by_model(allowed: Sequence[dict]) -> Dict[str, List[Dict[str, int]]]:
+    """AllowedMigGeometriesList.GroupByModel (pkg/gpu/mig/allowed_geometries.go): the configuration file's list of
+    {"models": [...], "allowedGeometries": [...]} entries -> model -> geometries, the shape `known_geometries` takes here and
+    mig.SetKnownGeometries takes in the reference (cmd/gpupartitioner/gpupartitioner.go loads it at start-up)."""
+    out: Dict[str, List[Dict[str, int]]] = {}
+    for entry in allowed:
+        for model in entry.get("models", []):
+            out[model] = [dict(g) for g in entry.get("allowedGeometries", [])]
+    return out
+
+
 def compute_pod_request(pod: dict) -> Dict[str, int]:
     """resource.ComputePodRequest (pkg/resource/resource.go:127-146); the overhead sum is discarded there."""
     if "request" in pod:

@@ -121,3 +121,14 @@ def test_golden_nodes_on_the_gpu_parser():
                 assert out["gpu_free"][0, 0] == 3 and out["gpu_index"][0] == 0 and out["gpu_used_mask"][0] == 0
     finally:
         eng.close()
+
+
+def test_allowed_geometries_group_by_model_golden():
+    """pkg/gpu/mig/allowed_geometries_test.go:133-203 (TestAllowedMigGeometriesList__GroupByModel)."""
+    from nos_b200 import packing as pk
+    assert pk.group_by_model([]) == {}
+    got = pk.group_by_model([{"models": ["m1", "m2"], "allowedGeometries": [{"p1": 1, "p2": 2}, {"p1": 3}]},
+                             {"models": ["m3"], "allowedGeometries": [{"p3": 2, "p2": 2}]}])
+    assert got == {"m1": [{"p1": 1, "p2": 2}, {"p1": 3}], "m2": [{"p1": 1, "p2": 2}, {"p1": 3}], "m3": [{"p3": 2, "p2": 2}]}
+    got["m1"][0]["p1"] = 9
+    assert got["m2"][0]["p1"] == 1                                    # the models of one entry do not share their lists
