@@ -141,6 +141,47 @@ struct PluginConfig {                                          // nvidiav1.Confi
 PluginConfig ToPluginConfig(const state::NodePartitioning& p); // internal/partitioning/mps/partitioner.go:123-157
 }  // namespace mps
 
+// The quota side of the C-ABI: what a cgo shim inside pkg/scheduler/plugins/capacityscheduling would build from its
+// ElasticQuotaInfos and pod lists before nosplan_quota_recompute / nosplan_quota_label_changes / nosplan_preempt_dryrun.
+namespace capacityscheduling {
+struct ElasticQuotaInfo {                         // elasticquotainfo.go:177-192, the fields the accounting reads
+    std::string ResourceName;
+    std::vector<std::string> Namespaces;          // one entry: ElasticQuota; several: CompositeElasticQuota
+    std::optional<ResourceList> Min, Max, Used;   // nil *framework.Resource == nullopt
+    bool MaxEnforced = false;
+};
+struct QuotaPod {                                 // a pod as the accounting sees it
+    std::string ns, name;
+    int32_t priority = 0;                         // *Spec.Priority, 0 when unset
+    int64_t creationTimestamp = 0;                // unix seconds
+    ResourceList request;                         // resource.ComputePodRequest, without nos.nebuly.com/gpu-memory
+};
+struct PackedQuotaPods {
+    std::vector<std::string> keys;                // namespace/name
+    std::vector<int32_t> ns, priority, nameRank;
+    std::vector<int64_t> request, creationTs;     // request: [P][Rq]
+    std::vector<uint32_t> requestMask;
+    nosplan_quota_pods c() const;
+};
+struct PackedQuotas {
+    std::vector<std::string> names, namespaces, columns;
+    int32_t gpuMemoryCol = -1;
+    std::vector<int32_t> nsQuota;
+    std::vector<int64_t> min, max, usedInit, gpuMemoryCoeff;
+    std::vector<uint32_t> minMask, maxMask, usedMask;
+    std::vector<uint8_t> maxEnforced;
+    std::vector<PackedQuotaPods> podSets;         // one per pod list given to PackQuotas, same order
+    int R() const { return (int)columns.size(); }
+    nosplan_quotas c() const;
+};
+// Interns namespaces (quotas first, in the order given, then the pods'), resource names (cpu, memory, ephemeral-storage, pods,
+// then every scalar seen, sorted, nos.nebuly.com/gpu-memory always among them) and quota rows; a namespace listed by two
+// quotas points at the later one, as ElasticQuotaInfos.Add overwrites (elasticquotainfo.go:68-72).  Throws nos::Error beyond
+// NOSPLAN_QUOTA_MAX_RES columns.
+PackedQuotas PackQuotas(const std::vector<ElasticQuotaInfo>& quotas, const std::vector<std::vector<QuotaPod>>& podSets,
+                        int nvidiaGpuMemoryGB);
+}  // namespace capacityscheduling
+
 namespace core {
 
 enum class Kind { MIG = NOSPLAN_KIND_MIG, MPS = NOSPLAN_KIND_MPS };

@@ -358,6 +358,125 @@ PluginConfig ToPluginConfig(const state::NodePartitioning& p) {
 }
 }  // namespace mps
 
+namespace capacityscheduling {
+namespace {
+// mig.ExtractMemoryGBFromMigFormat (pkg/gpu/mig/util.go:68-86): the resource must match the MIG pattern and hold exactly one
+// `\\d+gb`; 0 where the reference returns an error (pkg/gpu/util/resource.go:70-86 skips the resource then)
+int64_t mig_memory_gb_of_resource(const std::string& r) {
+    if (!matches_mig_resource(r)) return 0;
+    int n = 0; long long val = 0;
+    for (size_t i = 0; i < r.size();) {
+        const size_t d = digits_at(r, i);
+        if (!d) { ++i; continue; }
+        if (r.compare(i + d, 2, "gb") == 0) {
+            ++n;
+            val = 0;
+            for (size_t k = i; k < i + d; ++k) val = std::min<long long>(val * 10 + (r[k] - '0'), INT_MAX);
+            i += d + 2;
+        } else i += d;
+    }
+    return n == 1 ? val : 0;
+}
+}  // namespace
+
+nosplan_quota_pods PackedQuotaPods::c() const {
+    nosplan_quota_pods p{};
+    p.n_pods = (int32_t)ns.size(); p.ns = ns.data(); p.request = request.data(); p.request_mask = requestMask.data();
+    p.priority = priority.data(); p.creation_ts = creationTs.data(); p.name_rank = nameRank.data();
+    return p;
+}
+nosplan_quotas PackedQuotas::c() const {
+    nosplan_quotas q{};
+    q.n_quotas = (int32_t)names.size(); q.n_res = R(); q.n_namespaces = (int32_t)namespaces.size(); q.gpu_memory_col = gpuMemoryCol;
+    q.ns_quota = nsQuota.data(); q.min = min.data(); q.max = max.data(); q.used_init = usedInit.data();
+    q.min_mask = minMask.data(); q.max_mask = maxMask.data(); q.used_mask = usedMask.data(); q.max_enforced = maxEnforced.data();
+    q.gpu_memory_coeff = gpuMemoryCoeff.data();
+    return q;
+}
+
+PackedQuotas PackQuotas(const std::vector<ElasticQuotaInfo>& quotas, const std::vector<std::vector<QuotaPod>>& podSets, int nvidiaGpuMemoryGB) {
+    static const char* kGpuMemory = "nos.nebuly.com/gpu-memory";
+    static const char* kNvidiaGpu = "nvidia.com/gpu";
+    PackedQuotas pq;
+    auto fixed = [](const std::string& r) { return r == "cpu" ? 0 : r == "memory" ? 1 : r == "ephemeral-storage" ? 2 : r == "pods" ? 3 : -1; };
+    std::vector<std::string> scalars;
+    auto note = [&](const ResourceList& rl) {
+        for (auto& [r, v] : rl) { (void)v; if (fixed(r) < 0 && std::find(scalars.begin(), scalars.end(), r) == scalars.end()) scalars.push_back(r); }
+    };
+    for (auto& e : quotas) { if (e.Min) note(*e.Min); if (e.Max) note(*e.Max); if (e.Used) note(*e.Used); }
+    for (auto& pods : podSets) for (auto& p : pods) note(p.request);
+    if (std::find(scalars.begin(), scalars.end(), kGpuMemory) == scalars.end()) scalars.push_back(kGpuMemory);
+    std::sort(scalars.begin(), scalars.end());
+    pq.columns = {"cpu", "memory", "ephemeral-storage", "pods"};
+    pq.columns.insert(pq.columns.end(), scalars.begin(), scalars.end());
+    const int R = pq.R();
+    if (R > NOSPLAN_QUOTA_MAX_RES) throw Error(std::to_string(R) + " quota resource columns > NOSPLAN_QUOTA_MAX_RES");
+    std::map<std::string, int> col;
+    for (int c = 0; c < R; ++c) col[pq.columns[c]] = c;
+    pq.gpuMemoryCol = col[kGpuMemory];
+    pq.gpuMemoryCoeff.assign(R, 0);
+    for (auto& [r, c] : col) {
+        if (r == kNvidiaGpu) pq.gpuMemoryCoeff[c] = nvidiaGpuMemoryGB;
+        else if (matches_mig_resource(r)) pq.gpuMemoryCoeff[c] = mig_memory_gb_of_resource(r);
+    }
+    std::map<std::string, int> nsid;
+    auto intern = [&](const std::string& ns) {
+        auto it = nsid.find(ns);
+        if (it != nsid.end()) return it->second;
+        const int id = (int)pq.namespaces.size();
+        pq.namespaces.push_back(ns); nsid[ns] = id;
+        return id;
+    };
+    for (auto& e : quotas) for (auto& ns : e.Namespaces) intern(ns);
+    for (auto& pods : podSets) for (auto& p : pods) intern(p.ns);
+    const size_t E = quotas.size();
+    pq.nsQuota.assign(pq.namespaces.size(), -1);
+    pq.min.assign(E * R, 0); pq.max.assign(E * R, 0); pq.usedInit.assign(E * R, 0);
+    pq.minMask.assign(E, 0); pq.maxMask.assign(E, 0); pq.usedMask.assign(E, 0); pq.maxEnforced.assign(E, 0);
+    auto fill = [&](int64_t* row, const std::optional<ResourceList>& rl) -> uint32_t {
+        if (!rl) return 0;
+        uint32_t m = 0;
+        for (auto& [r, v] : *rl) { row[col[r]] += v; m |= 1u << col[r]; }
+        return m | NOSPLAN_QUOTA_NONNIL;
+    };
+    for (size_t i = 0; i < E; ++i) {
+        const ElasticQuotaInfo& e = quotas[i];
+        pq.names.push_back(e.ResourceName);
+        for (auto& ns : e.Namespaces) pq.nsQuota[nsid[ns]] = (int32_t)i;
+        pq.minMask[i] = fill(&pq.min[i * R], e.Min);
+        pq.maxMask[i] = fill(&pq.max[i * R], e.Max);
+        pq.usedMask[i] = fill(&pq.usedInit[i * R], e.Used);
+        pq.maxEnforced[i] = e.MaxEnforced ? 1 : 0;
+    }
+    for (auto& pods : podSets) {
+        PackedQuotaPods pp;
+        const size_t P = pods.size();
+        pp.request.assign(P * R, 0); pp.requestMask.assign(P, 0); pp.nameRank.assign(P, 0);
+        std::vector<size_t> order(P);
+        for (size_t i = 0; i < P; ++i) {
+            const QuotaPod& p = pods[i];
+            order[i] = i;
+            pp.keys.push_back(p.ns + "/" + p.name);
+            pp.ns.push_back(nsid[p.ns]); pp.priority.push_back(p.priority); pp.creationTs.push_back(p.creationTimestamp);
+            for (auto& [r, v] : p.request) {
+                if (r == kGpuMemory) continue;
+                const int c = col[r];
+                pp.request[i * R + c] += v;
+                if (c >= 4) pp.requestMask[i] |= 1u << c;
+            }
+        }
+        std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return pods[a].name < pods[b].name; });   // byte order
+        int rank = -1;
+        for (size_t k = 0; k < P; ++k) {
+            if (k == 0 || pods[order[k]].name != pods[order[k - 1]].name) ++rank;
+            pp.nameRank[order[k]] = rank;
+        }
+        pq.podSets.push_back(std::move(pp));
+    }
+    return pq;
+}
+}  // namespace capacityscheduling
+
 namespace core {
 
 const Node* Snapshot::GetNode(const std::string& name) const {

@@ -8,6 +8,8 @@
 //   numpods <n>
 //   pod <namespace> <name> <priority|->  container <res>=<n>,...|-   init <res>=<n>,...|-
 //   sa|sb <node> [<gpu index> <res>=<n>,...]   (two partitioning states for `run equal`)
+//   gpumem <GB>             quota <name> <maxEnforced 0|1>   qns <namespace>   qmin|qmax|qused <res>=<n>,...|nil
+//   qset                    qpod <namespace> <name> <priority> <creationTs> <res>=<n>,...|-     (`run quotapack`: the quota packer)
 //   planid <id>             (plan id for `run apply`; default "plan")
 //   clientdrop <node>       (`run apply`: the node is in the snapshot but the API client does not find it)
 //   run plan | run pack | run state | run diff | run equal | run apply | run pluginconfig
@@ -74,6 +76,9 @@ int main() {
     state::PartitioningState stA, stB;
     std::string line, mode, planId = "plan";
     std::vector<std::string> clientDrop;
+    std::vector<capacityscheduling::ElasticQuotaInfo> quotas;
+    std::vector<std::vector<capacityscheduling::QuotaPod>> podSets;
+    int gpuMem = 0;
     try {
         while (std::getline(std::cin, line)) {
             std::stringstream ss(line);
@@ -103,6 +108,20 @@ int main() {
                     np.GPUs.push_back(g);
                 }
             }
+            else if (cmd == "gpumem") gpuMem = std::stoi(a);
+            else if (cmd == "quota") { quotas.emplace_back(); quotas.back().ResourceName = a; quotas.back().MaxEnforced = b == "1"; }
+            else if (cmd == "qns") quotas.back().Namespaces.push_back(a);
+            else if (cmd == "qmin") { if (a != "nil") quotas.back().Min = parse_list(a); }
+            else if (cmd == "qmax") { if (a != "nil") quotas.back().Max = parse_list(a); }
+            else if (cmd == "qused") { if (a != "nil") quotas.back().Used = parse_list(a); }
+            else if (cmd == "qset") podSets.emplace_back();
+            else if (cmd == "qpod") {                       // qpod <namespace> <name> <priority> <creation ts> <res>=<n>,...|-
+                std::string d, e;
+                ss >> d >> e;
+                capacityscheduling::QuotaPod qp;
+                qp.ns = a; qp.name = b; qp.priority = std::stoi(c); qp.creationTimestamp = std::stoll(d); qp.request = parse_list(e.empty() ? "-" : e);
+                podSets.back().push_back(qp);
+            }
             else if (cmd == "planid") planId = a;
             else if (cmd == "clientdrop") clientDrop.push_back(a);      // node the API client of `run apply` does not hold
             else if (cmd == "run") { mode = a; break; }
@@ -113,6 +132,22 @@ int main() {
             for (auto& r : cfg.Resources)
                 std::cout << "resource " << r.Name << ' ' << r.Rename << ' ' << r.MemoryGB << ' ' << r.Devices[0] << ' ' << r.Replicas << '\n';
         };
+        if (mode == "quotapack") {
+            capacityscheduling::PackedQuotas pq = capacityscheduling::PackQuotas(quotas, podSets, gpuMem);
+            dump("names", pq.names); dump("namespaces", pq.namespaces); dump("columns", pq.columns);
+            dump("gpu_memory_col", std::vector<int>{pq.gpuMemoryCol}); dump("ns_quota", pq.nsQuota);
+            dump("min", pq.min); dump("max", pq.max); dump("used_init", pq.usedInit);
+            dump("min_mask", pq.minMask); dump("max_mask", pq.maxMask); dump("used_mask", pq.usedMask);
+            dump("max_enforced", pq.maxEnforced); dump("gpu_memory_coeff", pq.gpuMemoryCoeff);
+            for (size_t k = 0; k < pq.podSets.size(); ++k) {
+                const auto& pp = pq.podSets[k];
+                const std::string t = "set" + std::to_string(k) + "_";
+                dump((t + "keys").c_str(), pp.keys); dump((t + "ns").c_str(), pp.ns); dump((t + "request").c_str(), pp.request);
+                dump((t + "request_mask").c_str(), pp.requestMask); dump((t + "priority").c_str(), pp.priority);
+                dump((t + "creation_ts").c_str(), pp.creationTs); dump((t + "name_rank").c_str(), pp.nameRank);
+            }
+            return 0;
+        }
         if (mode == "pluginconfig") {
             mps::PluginConfig cfg = mps::ToPluginConfig(stA["n"]);
             std::cout << "resources " << cfg.Resources.size() << " migstrategy " << cfg.MigStrategy << " failgt1 " << cfg.FailRequestsGreaterThanOne << '\n';

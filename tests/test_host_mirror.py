@@ -324,3 +324,47 @@ def test_memory_label_and_partitioning_kind_golden():
             st, _, _ = hc.parse_state(out)
             assert code == 0 and (("node-1" in st) == c[kind]), (c["name"], kind, out)
             assert ("node-1" in m.take_snapshot(kind, [node]).get_nodes()) == c[kind]
+
+
+def _quota_text(quotas, pod_sets, gb):
+    rl = lambda d: ",".join(f"{k}={v}" for k, v in d.items()) or "-"
+    L = [f"gpumem {gb}"]
+    for name, e in quotas.items():
+        L.append(f"quota {name} {1 if e.get('max_enforced') else 0}")
+        L += [f"qns {ns}" for ns in e.get("namespaces", [])]
+        for key in ("min", "max", "used"):
+            v = e.get(key)
+            L.append(f"q{key} " + ("nil" if v is None else rl(v)))
+    for pods in pod_sets:
+        L.append("qset")
+        for p in pods:
+            L.append(f"qpod {p['namespace']} {p['name']} {p.get('priority') or 0} {p.get('creation_ts', 0)} {rl(p.get('request') or {})}")
+    return "\n".join(L + ["run quotapack"]) + "\n"
+
+
+def test_quota_packer_cpp_vs_python():
+    """nos::capacityscheduling::PackQuotas (the C++ twin of the shim's packQuotas) against nos_b200/quota_packing.pack_quotas on
+    random quota states: same interning of namespaces, columns and rows, same masks, same pod arrays."""
+    import numpy as np
+    from nos_b200 import quota_packing as qp
+    from support import quotacases as qc
+    for seed in range(60):
+        quotas, running, pending, gb = qc.rand_quota_case(seed)
+        pq, (run, pend) = qp.pack_quotas(quotas, [running, pending], gb)
+        code, out = hc.run(_quota_text(quotas, [running, pending], gb))
+        assert code == 0, out
+        got = {}
+        for line in out.strip().splitlines():
+            k, *v = line.split(" ")
+            got[k] = v
+        ints = lambda k: np.array([int(x) for x in got[k]], np.int64)
+        assert got["names"] == pq.names and got["namespaces"] == pq.namespaces and got["columns"] == pq.columns, seed
+        assert int(got["gpu_memory_col"][0]) == pq.gpu_memory_col
+        for k, ref in (("ns_quota", pq.ns_quota), ("min", pq.min), ("max", pq.max), ("used_init", pq.used_init), ("min_mask", pq.min_mask),
+                       ("max_mask", pq.max_mask), ("used_mask", pq.used_mask), ("max_enforced", pq.max_enforced), ("gpu_memory_coeff", pq.gpu_memory_coeff)):
+            assert np.array_equal(ints(k), np.asarray(ref).astype(np.int64).reshape(-1)), (seed, k)
+        for t, pods in (("set0_", run), ("set1_", pend)):
+            assert got[t + "keys"] == pods.keys
+            for k, ref in (("ns", pods.ns), ("request", pods.request), ("request_mask", pods.request_mask), ("priority", pods.priority),
+                           ("creation_ts", pods.creation_ts), ("name_rank", pods.name_rank)):
+                assert np.array_equal(ints(t + k), np.asarray(ref).astype(np.int64).reshape(-1)), (seed, t + k)
