@@ -148,6 +148,32 @@ int main() {
             }
             return 0;
         }
+        if (mode == "quota") {                                  // PackQuotas -> nosplan_quota_recompute (set 0 running, set 1 pending)
+            capacityscheduling::PackedQuotas pq = capacityscheduling::PackQuotas(quotas, podSets, gpuMem);
+            nosplan_t* h = nullptr;
+            if (nosplan_create(0, &h) != NOSPLAN_OK) throw Error("nosplan_create failed (no CUDA device: there is no CPU path)");
+            const size_t E = pq.names.size(), R = (size_t)pq.R();
+            const size_t Pr = pq.podSets.size() > 0 ? pq.podSets[0].ns.size() : 0, Pp = pq.podSets.size() > 1 ? pq.podSets[1].ns.size() : 0;
+            std::vector<int64_t> used(E * R + 1), aggMin(R), aggUsed(R), aggOver(R), guaranteed(E * R + 1), opUsed(E * R + 1);
+            std::vector<uint32_t> usedMask(E + 1), aggMasks(3);
+            std::vector<uint8_t> prefilter(Pp + 1), overQuota(Pr + 1);
+            int32_t ambiguous = 0;
+            nosplan_quota_out out{};
+            out.used = used.data(); out.used_mask = usedMask.data(); out.agg_min = aggMin.data(); out.agg_used = aggUsed.data();
+            out.agg_overquota = aggOver.data(); out.agg_masks = aggMasks.data(); out.guaranteed = guaranteed.data();
+            out.prefilter = prefilter.data(); out.over_quota = overQuota.data(); out.operator_used = opUsed.data(); out.ambiguous_order = &ambiguous;
+            nosplan_quotas cq = pq.c();
+            nosplan_quota_pods cr{}, cp{};
+            if (Pr) cr = pq.podSets[0].c();
+            if (Pp) cp = pq.podSets[1].c();
+            const int rc = nosplan_quota_recompute(h, &cq, Pr ? &cr : nullptr, Pp ? &cp : nullptr, &out, nullptr);
+            if (rc != NOSPLAN_OK) { std::string msg = nosplan_last_error(h); nosplan_destroy(h); throw Error("nosplan_quota_recompute: " + msg); }
+            nosplan_destroy(h);
+            used.resize(E * R); guaranteed.resize(E * R); opUsed.resize(E * R); prefilter.resize(Pp); overQuota.resize(Pr);
+            dump("used", used); dump("agg_min", aggMin); dump("agg_used", aggUsed); dump("agg_overquota", aggOver);
+            dump("guaranteed", guaranteed); dump("prefilter", prefilter); dump("over_quota", overQuota); dump("operator_used", opUsed);
+            return 0;
+        }
         if (mode == "pluginconfig") {
             mps::PluginConfig cfg = mps::ToPluginConfig(stA["n"]);
             std::cout << "resources " << cfg.Resources.size() << " migstrategy " << cfg.MigStrategy << " failgt1 " << cfg.FailRequestsGreaterThanOne << '\n';

@@ -368,3 +368,21 @@ def test_quota_packer_cpp_vs_python():
             for k, ref in (("ns", pods.ns), ("request", pods.request), ("request_mask", pods.request_mask), ("priority", pods.priority),
                            ("creation_ts", pods.creation_ts), ("name_rank", pods.name_rank)):
                 assert np.array_equal(ints(t + k), np.asarray(ref).astype(np.int64).reshape(-1)), (seed, t + k)
+
+
+@pytest.mark.gpu
+def test_quota_recompute_through_the_cpp_host_side():
+    """PackQuotas + nosplan_quota_recompute driven from C++ (nos_host_cli `run quota`) against the oracle on random quota states."""
+    import numpy as np
+    from nos_b200 import quota_packing as qp
+    from support import oracle_lib as ol
+    from support import quotacases as qc
+    for seed in range(100, 112):
+        quotas, running, pending, gb = qc.rand_quota_case(seed)
+        pq, (run, pend) = qp.pack_quotas(quotas, [running, pending], gb)
+        exp = ol.quota(pq, run, pend)
+        code, out = hc.run(_quota_text(quotas, [running, pending], gb).replace("run quotapack", "run quota"))
+        assert code == 0, out
+        got = {line.split(" ")[0]: np.array([int(x) for x in line.split(" ")[1:]], np.int64) for line in out.strip().splitlines()}
+        for k in ("used", "agg_min", "agg_used", "agg_overquota", "guaranteed", "prefilter", "over_quota", "operator_used"):
+            assert np.array_equal(got[k], np.asarray(exp[k]).astype(np.int64).reshape(-1)), (seed, k)
