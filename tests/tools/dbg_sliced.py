@@ -1,5 +1,5 @@
 import sys, os
-ROOT=os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT=os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0]=[ROOT,ROOT+'/tests',ROOT+'/oracle']
 import numpy as np, torch
 from nos_b200 import capi, packing as pk, sharded, synth

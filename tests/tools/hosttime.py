@@ -1,7 +1,7 @@
 """Where the end-to-end time of nosplan_plan goes on the host side (run on a GPU box)."""
 import sys, time
 import os
-ROOT=os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT=os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0]=[ROOT,ROOT+'/tests',ROOT+'/oracle']
 import numpy as np
 from nos_b200 import capi, synth

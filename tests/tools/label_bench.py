@@ -2,7 +2,7 @@
 nosplan_quota_label_changes (host buffers in and out) against the CPU oracle on the same inputs, for a settled cluster with
 1 % of the labels off and for a fresh cluster (every pod of a quota needs its first label)."""
 import json, os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [ROOT, ROOT + "/tests", ROOT + "/oracle"]
 import numpy as np
 from nos_b200 import capi

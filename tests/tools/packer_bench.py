@@ -1,7 +1,7 @@
 """Snapshot packer timing (run on a GPU box): status annotations of a 10 000-node x 8-GPU cluster -> per-GPU rows,
 on the GPU (nosplan_parse_annotations, host buffers in and out) and with the host packers beside it."""
 import json, os, subprocess, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [ROOT, ROOT + "/tests", ROOT + "/oracle"]
 import numpy as np
 import nos_model as m

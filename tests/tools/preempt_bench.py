@@ -2,7 +2,7 @@
 10 000 nodes, one preemptor per call; nosplan_preempt_dryrun (host buffers in and out) against the CPU oracle on the same
 inputs.  Quota state: the recipe's, Min scaled so that cluster-wide Used is 98 % of the aggregated Min."""
 import json, os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [ROOT, ROOT + "/tests", ROOT + "/oracle"]
 import numpy as np
 from nos_b200 import capi, preempt_packing as pp, victim_packing as vp

@@ -1,7 +1,7 @@
 """Quota engine timing at BASELINE config #4 (run on a GPU box): 500 ElasticQuotas, 100 000 running pods, 10 000 pending;
 nosplan_quota_recompute (host buffers in and out) and nosplan_quota_victims against the CPU oracle on the same inputs."""
 import json, os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [ROOT, ROOT + "/tests", ROOT + "/oracle"]
 import numpy as np
 from nos_b200 import capi, synth

@@ -2,9 +2,9 @@
 filter modes -- GPU Plan() (kernels with the snapshot resident; end to end with host buffers), the incremental CPU port at
 full size, and the faithful CPU port (the reference's own O(N^2 P) asymptotics) at N in {100, 250, 500, 1000} with the
 fitted a*N^2*P extrapolated to each config.  Every GPU plan is compared with the oracle before its time is printed.
-  python tools/results_table.py > profiles/rNN_results.md"""
+  python tests/tools/results_table.py > profiles/rNN_results.md"""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [ROOT, ROOT + "/tests", ROOT + "/oracle"]
 import numpy as np
 import torch

@@ -1,7 +1,7 @@
 """Timing of the sequential path (run on a GPU box): problems where the node-parallel pass does not apply -- nothing lacking
 (the reference's early return) and unsaturated demand -- at 10 000 and 100 000 nodes, snapshot resident."""
 import json, os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [ROOT, ROOT + "/tests", ROOT + "/oracle"]
 import numpy as np
 from nos_b200 import capi, packing as pk, synth
