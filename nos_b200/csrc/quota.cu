@@ -154,7 +154,7 @@ constexpr int AGG_THREADS = 1024, AGG_ROWS = AGG_THREADS / 16;   // 64 namespace
 __global__ void __launch_bounds__(AGG_THREADS) k_quota_aggregate(DevQuota q) {
     __shared__ long long s_min[AGG_ROWS][QR], s_used[AGG_ROWS][QR], s_over[AGG_ROWS][QR];
     __shared__ unsigned s_m[3];
-    __shared__ long long a_min[QR], a_used[QR], a_over[QR];
+    __shared__ long long a_min[QR], a_over[QR];
     const int tid = threadIdx.x, c = tid & 15, j = tid >> 4;
     if (tid < 3) s_m[tid] = 0;
     __syncthreads();
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(AGG_THREADS) k_quota_aggregate(DevQuota q) {
     if (tid < QR) {
         long long a = 0, b = 0, d = 0;
         for (int k = 0; k < AGG_ROWS; ++k) { a += s_min[k][tid]; b += s_used[k][tid]; d += s_over[k][tid]; }
-        a_min[tid] = a; a_used[tid] = b; a_over[tid] = d;
+        a_min[tid] = a; a_over[tid] = d;
         if (tid < q.R) { q.agg_min[tid] = a; q.agg_used[tid] = b; q.agg_over[tid] = d; }
     }
     if (tid < 3) q.agg_masks[tid] = s_m[tid];
