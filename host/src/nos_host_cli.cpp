@@ -12,7 +12,7 @@
 //   qset                    qpod <namespace> <name> <priority> <creationTs> <res>=<n>,...|-     (`run quotapack`: the quota packer)
 //   planid <id>             (plan id for `run apply`; default "plan")
 //   clientdrop <node>       (`run apply`: the node is in the snapshot but the API client does not find it)
-//   run plan | run pack | run state | run diff | run equal | run apply | run pluginconfig
+//   run plan | run pack | run state | run diff | run equal | run apply | run pluginconfig | run parsespec | run quotapack | run quota
 // stdout: `run plan`  -> "node <name>" / "gpu <index> <res>=<n>,..." lines, then "stats ..." ;
 //         `run pack`  -> one "<array> v v v" line per packed buffer;  `run state` -> the snapshot's current state;
 //         `run diff`  -> plan, then "apply <node>" per node Actuator.Apply would partition and "changed <node>".
@@ -172,6 +172,17 @@ int main() {
             used.resize(E * R); guaranteed.resize(E * R); opUsed.resize(E * R); prefilter.resize(Pp); overQuota.resize(Pr);
             dump("used", used); dump("agg_min", aggMin); dump("agg_used", aggUsed); dump("agg_overquota", aggOver);
             dump("guaranteed", guaranteed); dump("prefilter", prefilter); dump("over_quota", overQuota); dump("operator_used", opUsed);
+            return 0;
+        }
+        if (mode == "parsespec") {                              // gpu.ParseSpecAnnotation on every annotation of every node
+            for (auto& [name, ni] : cluster) {
+                if (!ni.node) continue;
+                for (auto& [k, v] : ni.node->annotations) {
+                    auto sa = gpu::ParseSpecAnnotation(k, v);
+                    if (sa) std::cout << "spec " << sa->Index << ' ' << sa->ProfileName << ' ' << sa->Quantity << '\n';
+                    else std::cout << "notspec " << k << '\n';
+                }
+            }
             return 0;
         }
         if (mode == "pluginconfig") {

@@ -132,3 +132,19 @@ def test_allowed_geometries_group_by_model_golden():
     assert got == {"m1": [{"p1": 1, "p2": 2}, {"p1": 3}], "m2": [{"p1": 1, "p2": 2}, {"p1": 3}], "m3": [{"p3": 2, "p2": 2}]}
     got["m1"][0]["p1"] = 9
     assert got["m2"][0]["p1"] == 1                                    # the models of one entry do not share their lists
+
+
+def test_parse_spec_annotation_golden():
+    """pkg/gpu/annotation_test.go:391-450 (TestParseSpecAnnotation) through the Python model and nos::gpu::ParseSpecAnnotation."""
+    import nos_model as m
+    from support import hostcli as hc
+    prefix = "nos.nebuly.com/spec-gpu"
+    cases = [("nos.nebuly.com/foo", "1", None), (prefix + "foo", "1", None), (f"{prefix}-0-1g.10gb", "foo", None),
+             (f"{prefix}-1-1g.10gb", "1", (1, "1g.10gb", 1))]
+    assert m.parse_spec_annotation("", "") is None                       # "Empty key and value" (the text driver cannot carry an empty key)
+    for key, value, exp in cases:
+        assert m.parse_spec_annotation(key, value) == exp, key
+        code, out = hc.run(f"kind mig\nnode n\nannotation {key} {value}\nrun parsespec\n")
+        assert code == 0, out
+        want = f"spec {exp[0]} {exp[1]} {exp[2]}" if exp else f"notspec {key}"
+        assert out.strip() == want, (key, out)
