@@ -155,6 +155,7 @@ struct QuotaPod {                                 // a pod as the accounting see
     int32_t priority = 0;                         // *Spec.Priority, 0 when unset
     int64_t creationTimestamp = 0;                // unix seconds
     ResourceList request;                         // resource.ComputePodRequest, without nos.nebuly.com/gpu-memory
+    bool overQuota = false;                       // label nos.nebuly.com/capacity == over-quota (pkg/util/pod/pod.go:31-36)
 };
 struct PackedQuotaPods {
     std::vector<std::string> keys;                // namespace/name
@@ -180,6 +181,24 @@ struct PackedQuotas {
 // NOSPLAN_QUOTA_MAX_RES columns.
 PackedQuotas PackQuotas(const std::vector<ElasticQuotaInfo>& quotas, const std::vector<std::vector<QuotaPod>>& podSets,
                         int nvidiaGpuMemoryGB);
+// nosplan_preempt_query for one preemptor over the candidate nodes (preemptor.SelectVictimsOnNode, capacity_scheduling.go:468-675).
+struct PreemptNode {
+    ResourceList allocatable;                     // NodeInfo.Allocatable, "pods" = allowed pod number
+    std::vector<QuotaPod> pods;                   // NodeInfo.Pods, least important first (the order of :516)
+    std::vector<std::vector<int32_t>> pdbsOfPod;  // per pod: budgets that match it and do not list it in DisruptedPods (:856-877)
+};
+struct PackedPreemptQuery {
+    int32_t preemptorNs = -1, preemptorPriority = 0;
+    uint32_t fitMask = 0;
+    std::vector<int64_t> nominatedInEQ, podReq, nominated, fitRequest, request, nodeAlloc, nodeRequested;
+    std::vector<int32_t> nodePtr, ns, priority, pdbAllowed, podPdbPtr, podPdb;
+    std::vector<uint8_t> overQuota;
+    std::vector<uint32_t> requestMask;
+    nosplan_preempt_query c() const;
+};
+PackedPreemptQuery PackPreemptQuery(const PackedQuotas& pq, const QuotaPod& preemptor, const ResourceList& nominatedInEQ,
+                                    const ResourceList& nominated, const std::vector<PreemptNode>& nodes,
+                                    const std::vector<int32_t>& pdbAllowed);
 }  // namespace capacityscheduling
 
 namespace core {

@@ -475,6 +475,73 @@ PackedQuotas PackQuotas(const std::vector<ElasticQuotaInfo>& quotas, const std::
     }
     return pq;
 }
+nosplan_preempt_query PackedPreemptQuery::c() const {
+    nosplan_preempt_query q{};
+    q.v.preemptor_ns = preemptorNs; q.v.preemptor_priority = preemptorPriority; q.v.nominated_in_eq = nominatedInEQ.data();
+    q.v.n_nodes = (int32_t)nodePtr.size() - 1; q.v.node_ptr = nodePtr.data(); q.v.n_pods = (int32_t)ns.size();
+    q.v.ns = ns.data(); q.v.priority = priority.data(); q.v.over_quota = overQuota.data(); q.v.request = request.data();
+    q.v.request_mask = requestMask.data();
+    q.pod_req = podReq.data(); q.nominated = nominated.data(); q.fit_request = fitRequest.data(); q.fit_mask = fitMask;
+    q.n_pdbs = (int32_t)pdbAllowed.size(); q.node_alloc = nodeAlloc.data(); q.node_requested = nodeRequested.data();
+    q.pdb_allowed = pdbAllowed.data(); q.pod_pdb_ptr = podPdbPtr.data(); q.pod_pdb = podPdb.data();
+    return q;
+}
+
+PackedPreemptQuery PackPreemptQuery(const PackedQuotas& pq, const QuotaPod& preemptor, const ResourceList& nominatedInEQ,
+                                    const ResourceList& nominated, const std::vector<PreemptNode>& nodes,
+                                    const std::vector<int32_t>& pdbAllowed) {
+    static const std::string kGpuMemory = "nos.nebuly.com/gpu-memory";
+    const int R = pq.R();
+    std::map<std::string, int> col, nsid;
+    for (int c = 0; c < R; ++c) col[pq.columns[c]] = c;
+    for (size_t i = 0; i < pq.namespaces.size(); ++i) nsid[pq.namespaces[i]] = (int)i;
+    auto column = [&](const std::string& r) {
+        auto it = col.find(r);
+        if (it == col.end()) throw Error("resource " + r + " has no column in the packed quotas");
+        return it->second;
+    };
+    auto ns_of = [&](const std::string& n) { auto it = nsid.find(n); return it == nsid.end() ? -1 : it->second; };
+    // dense row of a plain resource list, the gpu-memory key skipped; scalar key mask on the side
+    auto row = [&](const ResourceList& rl, int64_t* out, bool skipPods, uint32_t* mask) {
+        for (auto& [r, v] : rl) {
+            if (r == kGpuMemory || (skipPods && r == "pods")) continue;
+            const int c = column(r);
+            out[c] += v;
+            if (mask && c >= 4) *mask |= 1u << c;
+        }
+    };
+    PackedPreemptQuery q;
+    q.preemptorNs = ns_of(preemptor.ns); q.preemptorPriority = preemptor.priority;
+    q.nominatedInEQ.assign(R, 0); q.nominated.assign(R, 0); q.podReq.assign(R, 0); q.fitRequest.assign(R, 0);
+    for (auto& [r, v] : nominatedInEQ) q.nominatedInEQ[column(r)] += v;
+    for (auto& [r, v] : nominated) q.nominated[column(r)] += v;
+    row(preemptor.request, q.podReq.data(), false, nullptr);           // quota request: gpu-memory filled (pkg/gpu/util/resource.go:60-86)
+    int64_t g = 0;
+    for (int c = 0; c < R; ++c) g += pq.gpuMemoryCoeff[c] * q.podReq[c];
+    q.podReq[pq.gpuMemoryCol] = g;
+    row(preemptor.request, q.fitRequest.data(), true, &q.fitMask);     // NodeResourcesFit request
+    q.nodePtr.push_back(0); q.podPdbPtr.push_back(0);
+    q.nodeAlloc.assign(nodes.size() * R, 0); q.nodeRequested.assign(nodes.size() * R, 0);
+    q.pdbAllowed = pdbAllowed;
+    for (size_t k = 0; k < nodes.size(); ++k) {
+        const PreemptNode& n = nodes[k];
+        row(n.allocatable, &q.nodeAlloc[k * R], false, nullptr);
+        for (size_t i = 0; i < n.pods.size(); ++i) {
+            const QuotaPod& p = n.pods[i];
+            q.ns.push_back(ns_of(p.ns)); q.priority.push_back(p.priority); q.overQuota.push_back(p.overQuota ? 1 : 0);
+            q.request.resize(q.request.size() + R, 0);
+            uint32_t m = 0;
+            row(p.request, &q.request[q.request.size() - R], false, &m);
+            q.requestMask.push_back(m);
+            row(p.request, &q.nodeRequested[k * R], true, nullptr);
+            if (i < n.pdbsOfPod.size()) q.podPdb.insert(q.podPdb.end(), n.pdbsOfPod[i].begin(), n.pdbsOfPod[i].end());
+            q.podPdbPtr.push_back((int32_t)q.podPdb.size());
+        }
+        q.nodeRequested[k * R + 3] = (int64_t)n.pods.size();
+        q.nodePtr.push_back((int32_t)q.ns.size());
+    }
+    return q;
+}
 }  // namespace capacityscheduling
 
 namespace core {

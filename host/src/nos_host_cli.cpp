@@ -9,6 +9,8 @@
 //   pod <namespace> <name> <priority|->  container <res>=<n>,...|-   init <res>=<n>,...|-
 //   sa|sb <node> [<gpu index> <res>=<n>,...]   (two partitioning states for `run equal`)
 //   gpumem <GB>             quota <name> <maxEnforced 0|1>   qns <namespace>   qmin|qmax|qused <res>=<n>,...|nil
+//   pre <ns> <name> <priority> <res>=..   nomeq|nom <res>=..   pdb <allowed>   pnode <allocatable>   ppod <ns> <name> <prio> <over> <res>=.. <pdb ids|->
+//                           (`run preemptpack`: the preemption query packer)
 //   qset                    qpod <namespace> <name> <priority> <creationTs> <res>=<n>,...|-     (`run quotapack`: the quota packer)
 //   planid <id>             (plan id for `run apply`; default "plan")
 //   clientdrop <node>       (`run apply`: the node is in the snapshot but the API client does not find it)
@@ -79,6 +81,10 @@ int main() {
     std::vector<capacityscheduling::ElasticQuotaInfo> quotas;
     std::vector<std::vector<capacityscheduling::QuotaPod>> podSets;
     int gpuMem = 0;
+    capacityscheduling::QuotaPod preemptor;
+    ResourceList nomInEQ, nomAll;
+    std::vector<capacityscheduling::PreemptNode> pnodes;
+    std::vector<int32_t> pdbAllowed;
     try {
         while (std::getline(std::cin, line)) {
             std::stringstream ss(line);
@@ -121,6 +127,20 @@ int main() {
                 capacityscheduling::QuotaPod qp;
                 qp.ns = a; qp.name = b; qp.priority = std::stoi(c); qp.creationTimestamp = std::stoll(d); qp.request = parse_list(e.empty() ? "-" : e);
                 podSets.back().push_back(qp);
+            }
+            else if (cmd == "pre") { std::string d; ss >> d; preemptor.ns = a; preemptor.name = b; preemptor.priority = std::stoi(c); preemptor.request = parse_list(d.empty() ? "-" : d); }
+            else if (cmd == "nomeq") nomInEQ = parse_list(a);
+            else if (cmd == "nom") nomAll = parse_list(a);
+            else if (cmd == "pdb") pdbAllowed.push_back(std::stoi(a));
+            else if (cmd == "pnode") { pnodes.emplace_back(); pnodes.back().allocatable = parse_list(a); }
+            else if (cmd == "ppod") {                       // ppod <namespace> <name> <priority> <over 0|1> <res>=<n>,...|- <pdb id,...|->
+                std::string d, e, f;
+                ss >> d >> e >> f;
+                capacityscheduling::QuotaPod qp;
+                qp.ns = a; qp.name = b; qp.priority = std::stoi(c); qp.overQuota = d == "1"; qp.request = parse_list(e.empty() ? "-" : e);
+                std::vector<int32_t> ids;
+                if (!f.empty() && f != "-") { std::stringstream fs(f); std::string t; while (std::getline(fs, t, ',')) ids.push_back(std::stoi(t)); }
+                pnodes.back().pods.push_back(qp); pnodes.back().pdbsOfPod.push_back(ids);
             }
             else if (cmd == "planid") planId = a;
             else if (cmd == "clientdrop") clientDrop.push_back(a);      // node the API client of `run apply` does not hold
@@ -183,6 +203,18 @@ int main() {
                     else std::cout << "notspec " << k << '\n';
                 }
             }
+            return 0;
+        }
+        if (mode == "preemptpack") {                            // PackQuotas (the preemptor's resources get columns too), then PackPreemptQuery
+            auto sets = podSets;
+            sets.push_back({preemptor});
+            capacityscheduling::PackedQuotas pq = capacityscheduling::PackQuotas(quotas, sets, gpuMem);
+            capacityscheduling::PackedPreemptQuery q = capacityscheduling::PackPreemptQuery(pq, preemptor, nomInEQ, nomAll, pnodes, pdbAllowed);
+            dump("preemptor", std::vector<int>{q.preemptorNs, q.preemptorPriority, (int)q.fitMask});
+            dump("nominated_in_eq", q.nominatedInEQ); dump("pod_req", q.podReq); dump("nominated", q.nominated); dump("fit_request", q.fitRequest);
+            dump("node_ptr", q.nodePtr); dump("ns", q.ns); dump("priority", q.priority); dump("over_quota", q.overQuota);
+            dump("request", q.request); dump("request_mask", q.requestMask); dump("node_alloc", q.nodeAlloc); dump("node_requested", q.nodeRequested);
+            dump("pdb_allowed", q.pdbAllowed); dump("pod_pdb_ptr", q.podPdbPtr); dump("pod_pdb", q.podPdb);
             return 0;
         }
         if (mode == "pluginconfig") {

@@ -386,3 +386,38 @@ def test_quota_recompute_through_the_cpp_host_side():
         got = {line.split(" ")[0]: np.array([int(x) for x in line.split(" ")[1:]], np.int64) for line in out.strip().splitlines()}
         for k in ("used", "agg_min", "agg_used", "agg_overquota", "guaranteed", "prefilter", "over_quota", "operator_used"):
             assert np.array_equal(got[k], np.asarray(exp[k]).astype(np.int64).reshape(-1)), (seed, k)
+
+
+def test_preempt_query_packer_cpp_vs_python():
+    """nos::capacityscheduling::PackPreemptQuery against nos_b200/preempt_packing.pack_preempt_query on random preemption cases."""
+    import numpy as np
+    from nos_b200 import preempt_packing as pp, quota_packing as qp, victim_packing as vp
+    from support import preemptcases as pc
+    rl = lambda d: ",".join(f"{k}={v}" for k, v in d.items()) or "-"
+    for seed in range(40):
+        quotas, running, nodes, preemptor, gb, pdb_allowed, extra = pc.rand_preempt_case(seed)
+        pq, _ = qp.pack_quotas(quotas, [running, [preemptor]], gb)
+        nom_row = vp.quota_request_row(pq, preemptor["request"])
+        nom_in_eq = {c: int(v) for c, v in zip(pq.columns, nom_row)}
+        nominated = dict(nom_in_eq)
+        for r, v in extra.items():
+            nominated[r] = nominated.get(r, 0) + v
+        ref = pp.pack_preempt_query(pq, preemptor, nom_in_eq, nominated, nodes, pdb_allowed)
+        text = _quota_text(quotas, [running], gb).splitlines()[:-1]
+        text.append(f"pre {preemptor['namespace']} {preemptor['name']} {preemptor.get('priority') or 0} {rl(preemptor['request'])}")
+        text += [f"nomeq {rl(nom_in_eq)}", f"nom {rl(nominated)}"] + [f"pdb {a}" for a in pdb_allowed]
+        for n in nodes:
+            text.append(f"pnode {rl(n['allocatable'])}")
+            for p, ids in zip(n["pods"], n["pdbs_of_pod"]):
+                text.append(f"ppod {p['namespace']} {p['name']} {p.get('priority') or 0} {1 if p.get('over_quota') else 0} {rl(p['request'])} "
+                            + (",".join(str(i) for i in ids) or "-"))
+        code, out = hc.run("\n".join(text + ["run preemptpack"]) + "\n")
+        assert code == 0, out
+        got = {line.split(" ")[0]: np.array([int(x) for x in line.split(" ")[1:]], np.int64) for line in out.strip().splitlines()}
+        v = ref.v
+        assert got["preemptor"].tolist() == [v.preemptor_ns, v.preemptor_priority, int(ref.fit_mask)], seed
+        for k, a in (("nominated_in_eq", v.nominated_in_eq), ("pod_req", ref.pod_req), ("nominated", ref.nominated), ("fit_request", ref.fit_request),
+                     ("node_ptr", v.node_ptr), ("ns", v.ns), ("priority", v.priority), ("over_quota", v.over_quota), ("request", v.request),
+                     ("request_mask", v.request_mask), ("node_alloc", ref.node_alloc), ("node_requested", ref.node_requested),
+                     ("pdb_allowed", ref.pdb_allowed), ("pod_pdb_ptr", ref.pod_pdb_ptr), ("pod_pdb", ref.pod_pdb)):
+            assert np.array_equal(got[k], np.asarray(a).astype(np.int64).reshape(-1)), (seed, k)
