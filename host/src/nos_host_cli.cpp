@@ -14,7 +14,7 @@
 //   qset                    qpod <namespace> <name> <priority> <creationTs> <res>=<n>,...|-     (`run quotapack`: the quota packer)
 //   planid <id>             (plan id for `run apply`; default "plan")
 //   clientdrop <node>       (`run apply`: the node is in the snapshot but the API client does not find it)
-//   run plan | run pack | run state | run diff | run equal | run apply | run pluginconfig | run parsespec | run quotapack | run quota
+//   run plan | run pack | run state | run diff | run equal | run apply | run pluginconfig | run parsespec | run quotapack | run quota | run preemptpack | run preempt
 // stdout: `run plan`  -> "node <name>" / "gpu <index> <res>=<n>,..." lines, then "stats ..." ;
 //         `run pack`  -> one "<array> v v v" line per packed buffer;  `run state` -> the snapshot's current state;
 //         `run diff`  -> plan, then "apply <node>" per node Actuator.Apply would partition and "changed <node>".
@@ -205,11 +205,39 @@ int main() {
             }
             return 0;
         }
-        if (mode == "preemptpack") {                            // PackQuotas (the preemptor's resources get columns too), then PackPreemptQuery
+        if (mode == "preemptpack" || mode == "preempt") {       // PackQuotas (the preemptor's resources get columns too), then PackPreemptQuery
             auto sets = podSets;
             sets.push_back({preemptor});
             capacityscheduling::PackedQuotas pq = capacityscheduling::PackQuotas(quotas, sets, gpuMem);
             capacityscheduling::PackedPreemptQuery q = capacityscheduling::PackPreemptQuery(pq, preemptor, nomInEQ, nomAll, pnodes, pdbAllowed);
+            if (mode == "preempt") {
+                // the current Used of every quota comes from the running pods (set 0), then the dry run -- both on the GPU
+                nosplan_t* h = nullptr;
+                if (nosplan_create(0, &h) != NOSPLAN_OK) throw Error("nosplan_create failed (no CUDA device: there is no CPU path)");
+                const size_t E = pq.names.size(), R = (size_t)pq.R();
+                std::vector<int64_t> used(E * R + 1);
+                std::vector<uint32_t> usedMask(E + 1);
+                nosplan_quota_out out{};
+                out.used = used.data(); out.used_mask = usedMask.data();
+                nosplan_quotas cq = pq.c();
+                nosplan_quota_pods cr = pq.podSets[0].c();
+                int rc = nosplan_quota_recompute(h, &cq, pq.podSets[0].ns.empty() ? nullptr : &cr, nullptr, &out, nullptr);
+                if (rc == NOSPLAN_OK) {
+                    cq.used_init = used.data(); cq.used_mask = usedMask.data();
+                    nosplan_preempt_query cqy = q.c();
+                    std::vector<uint8_t> victim(q.ns.size() + 1);
+                    std::vector<int32_t> status(pnodes.size() + 1), viol(pnodes.size() + 1);
+                    rc = nosplan_preempt_dryrun(h, &cq, &cqy, victim.data(), status.data(), viol.data(), nullptr);
+                    if (rc == NOSPLAN_OK) {
+                        victim.resize(q.ns.size()); status.resize(pnodes.size()); viol.resize(pnodes.size());
+                        dump("victim", victim); dump("node_status", status); dump("num_violating", viol);
+                    }
+                }
+                std::string msg = rc == NOSPLAN_OK ? "" : nosplan_last_error(h);
+                nosplan_destroy(h);
+                if (rc != NOSPLAN_OK) throw Error("preemption dry run: " + msg);
+                return 0;
+            }
             dump("preemptor", std::vector<int>{q.preemptorNs, q.preemptorPriority, (int)q.fitMask});
             dump("nominated_in_eq", q.nominatedInEQ); dump("pod_req", q.podReq); dump("nominated", q.nominated); dump("fit_request", q.fitRequest);
             dump("node_ptr", q.nodePtr); dump("ns", q.ns); dump("priority", q.priority); dump("over_quota", q.overQuota);

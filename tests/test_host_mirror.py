@@ -421,3 +421,36 @@ def test_preempt_query_packer_cpp_vs_python():
                      ("request_mask", v.request_mask), ("node_alloc", ref.node_alloc), ("node_requested", ref.node_requested),
                      ("pdb_allowed", ref.pdb_allowed), ("pod_pdb_ptr", ref.pod_pdb_ptr), ("pod_pdb", ref.pod_pdb)):
             assert np.array_equal(got[k], np.asarray(a).astype(np.int64).reshape(-1)), (seed, k)
+
+
+@pytest.mark.gpu
+def test_preempt_dryrun_through_the_cpp_host_side():
+    """PackQuotas + PackPreemptQuery + nosplan_quota_recompute + nosplan_preempt_dryrun driven from C++ (nos_host_cli `run preempt`)
+    against the oracle on random preemption cases."""
+    import numpy as np
+    from support import oracle_lib as ol
+    from support import preemptcases as pc
+    from test_victims_packed import oracle_used
+    rl = lambda d: ",".join(f"{k}={v}" for k, v in d.items()) or "-"
+    n_ok = 0
+    for seed in range(200, 214):
+        case = pc.rand_preempt_case(seed)
+        quotas, running, nodes, preemptor, gb, pdb_allowed, extra = case
+        pq, query = pc.packed_dryrun_query(*case, oracle_used)
+        ev, es, en = ol.preempt_dryrun(pq, query)
+        nom_in_eq = {c: int(v) for c, v in zip(pq.columns, query.v.nominated_in_eq)}
+        nominated = {c: int(v) for c, v in zip(pq.columns, query.nominated)}
+        text = _quota_text(quotas, [running], gb).splitlines()[:-1]
+        text.append(f"pre {preemptor['namespace']} {preemptor['name']} {preemptor.get('priority') or 0} {rl(preemptor['request'])}")
+        text += [f"nomeq {rl(nom_in_eq)}", f"nom {rl(nominated)}"] + [f"pdb {a}" for a in pdb_allowed]
+        for n in nodes:
+            text.append(f"pnode {rl(n['allocatable'])}")
+            for p, ids in zip(n["pods"], n["pdbs_of_pod"]):
+                text.append(f"ppod {p['namespace']} {p['name']} {p.get('priority') or 0} {1 if p.get('over_quota') else 0} {rl(p['request'])} "
+                            + (",".join(str(i) for i in ids) or "-"))
+        code, out = hc.run("\n".join(text + ["run preempt"]) + "\n")
+        assert code == 0, out
+        got = {line.split(" ")[0]: np.array([int(x) for x in line.split(" ")[1:]], np.int64) for line in out.strip().splitlines()}
+        assert np.array_equal(got["node_status"], es) and np.array_equal(got["victim"], ev) and np.array_equal(got["num_violating"], en), seed
+        n_ok += int((es == 0).sum())
+    assert n_ok > 0
