@@ -248,7 +248,9 @@ int nosplan_shard_transport(nosplan_t* h);
  * device array of NOSPLAN_STATIC_MAX_KEYS rows (1 MiB per GPU, kept until the process exits): n_keys above that is
  * refused with NOSPLAN_E_LIMIT.  The table is shared by every call on that GPU -- overlapping calls race -- and is
  * cleared per call.  Work is enqueued on cuda_stream, no synchronisation, no allocation; the first call on a GPU
- * resolves the table's device address and should be made outside stream capture.  errbuf (optional) gets a message. */
+ * resolves the table's device address and should be made outside stream capture.  errbuf (optional) gets a message.
+ * The pods are device data the host cannot check: a pod whose tracker key lies outside [0, n_keys) or whose scalar
+ * column is below 3 is skipped on the GPU and *d_lacking_entries comes back negative (sign bit set; d_lack incomplete). */
 #define NOSPLAN_STATIC_MAX_KEYS 16384
 int nosplan_lacking_static(int cuda_device, void* cuda_stream, int32_t n_pods, int32_t n_keys, int32_t n_profiles,
                            const int32_t* d_tracker_key, const int32_t* d_scalar_ptr, const int32_t* d_scalar_col,

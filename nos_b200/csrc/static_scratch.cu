@@ -13,11 +13,15 @@
 //     two threads) race on it; serialise them.  It keeps the previous call's contents, so every call first clears the
 //     rows it is about to use, and clears the two outputs, on the caller's stream;
 //   * at most NOSPLAN_STATIC_MAX_KEYS distinct pod keys; more is refused with NOSPLAN_E_LIMIT, nothing is launched;
+//   * the pods are device data, so bad entries can only be caught on the GPU: a pod whose tracker key is outside
+//     [0, n_keys) or whose scalar column is below 3 is skipped, and *d_lacking_entries comes back NEGATIVE (sign bit
+//     set) to say that d_lack is incomplete;
 //   * the first call on a given GPU looks up the device address of the array (cudaGetSymbolAddress, with that GPU
 //     current).  Make that first call outside any stream capture;
 //   * nothing here calls cudaMalloc, cudaFree, cudaMallocHost or any library routine that allocates; the work is
 //     enqueued on `cuda_stream` and the call returns without synchronising: read the outputs after the stream has
 //     finished.  The calling thread's current device is left set to `cuda_device`.
+#include <climits>
 #include <cstdio>
 #include <mutex>
 
@@ -36,18 +40,24 @@ int32_t* g_scratch_addr[MAX_DEVICES] = {};      // device address of g_static_en
 
 // same arithmetic as k_tracker_init (prepass.cu): lacking = request - max(0, cluster free total), NewSliceTracker
 // (internal/partitioning/core/tracker.go:34-57); `entry` is the caller-invisible table in static device memory
-__global__ void __launch_bounds__(256) k_lacking_static(int32_t* entry, int n_pods, int K, const int32_t* pod_key,
+// The pods are DEVICE data the host cannot inspect, so the kernel itself refuses what nosplan_upload refuses on the host:
+// a tracker key outside [0, n_keys) would land in rows this call did not clear (or past the table), a column below 3 is
+// not a scalar column.  Such a pod is skipped and the sign bit of *bad_out (the entries counter) is raised.
+__global__ void __launch_bounds__(256) k_lacking_static(int32_t* entry, int n_pods, int n_keys, int K, const int32_t* pod_key,
                                                         const int32_t* sptr, const int32_t* scol, const long long* sqty,
-                                                        const long long* tot, int32_t* lack) {
+                                                        const long long* tot, int32_t* lack, int32_t* bad_out) {
     __shared__ int s_lack[nsp::KP];
     if (threadIdx.x < nsp::KP) s_lack[threadIdx.x] = 0;
     __syncthreads();
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s < n_pods) {
         const int key = pod_key[s];
-        for (int e = sptr[s]; e < sptr[s + 1]; ++e) {
+        const bool key_ok = (unsigned)key < (unsigned)n_keys;
+        if (!key_ok) atomicOr(bad_out, INT_MIN);
+        for (int e = sptr[s]; key_ok && e < sptr[s + 1]; ++e) {
             const int col = scol[e];
             if (col >= 3 + K) break;
+            if (col < 3) { atomicOr(bad_out, INT_MIN); break; }
             const int p = col - 3;
             long long avail = tot[p];
             if (avail < 0) avail = 0;
@@ -123,9 +133,9 @@ extern "C" int nosplan_lacking_static(int cuda_device, void* cuda_stream, int32_
     if (e == cudaSuccess) e = cudaMemsetAsync(d_lacking_entries, 0, sizeof(int32_t), st);
     if (e != cudaSuccess) return fail(errbuf, errbuf_len, NOSPLAN_E_CUDA, "cudaMemsetAsync(outputs): ", cudaGetErrorString(e));
     if (n_pods > 0)
-        k_lacking_static<<<(n_pods + 255) / 256, 256, 0, st>>>(scratch, n_pods, n_profiles, d_tracker_key, d_scalar_ptr, d_scalar_col,
+        k_lacking_static<<<(n_pods + 255) / 256, 256, 0, st>>>(scratch, n_pods, n_keys, n_profiles, d_tracker_key, d_scalar_ptr, d_scalar_col,
                                                               reinterpret_cast<const long long*>(d_scalar_qty),
-                                                              reinterpret_cast<const long long*>(d_totals), d_lack);
+                                                              reinterpret_cast<const long long*>(d_totals), d_lack, d_lacking_entries);
     if (n_keys > 0) k_count_lacking_entries<<<(n_keys + 255) / 256, 256, 0, st>>>(scratch, n_keys, d_lacking_entries);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(errbuf, errbuf_len, NOSPLAN_E_CUDA, "kernel launch: ", cudaGetErrorString(e));

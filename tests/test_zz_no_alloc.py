@@ -71,6 +71,26 @@ def test_static_scratch_matches_plan_twice_in_a_row():
     eng.close()
 
 
+def test_static_scratch_flags_bad_device_data_instead_of_writing_out_of_bounds():
+    """A tracker key outside [0, n_keys) sits in device memory where the host cannot see it: the kernel skips the pod and
+    returns a negative entries counter; the next (clean) call is unaffected."""
+    import torch
+    import __graft_entry__ as g
+    g.build()
+    lib = capi.load_library()
+    snap, pods = synth.mig_cluster(20, 4, 200, seed=23)
+    n_keys = int(pods.tracker_key.max()) + 1
+    good = pods.tracker_key.copy()
+    pods.tracker_key[7] = n_keys + 5                                      # beyond the rows this call clears
+    pods.tracker_key[11] = 1 << 20                                        # beyond the table
+    pods.tracker_key[13] = -3
+    _, n_ent, _, _ = run_static(lib, torch, snap, pods, n_keys)
+    assert n_ent < 0
+    pods.tracker_key[:] = good
+    lack, n_ent, lack_ref, ent_ref = run_static(lib, torch, snap, pods, n_keys)
+    assert n_ent == ent_ref and np.array_equal(lack.astype(np.int64), lack_ref)
+
+
 def test_static_scratch_rejects_oversize_without_launching():
     import __graft_entry__ as g
     g.build()
