@@ -284,7 +284,8 @@ def run_ours(args):
     b_plan = algorithmic_bytes(snap, pods)       # per GPU: its own node rows and the (replicated) pods
     sweep_avg_ms = float(np.mean(sweep_ms))
     # dominant kernel: the node-parallel pass when it produced the plan, else the sequential sweep
-    dom_name = "k_plan_parallel" if st["path"] == 1 else "k_plan_sweep"
+    fused = bool(st.get("fused"))
+    dom_name = "k_plan_fused" if fused else ("k_plan_parallel" if st["path"] == 1 else "k_plan_sweep")
     dom_ms = float(np.mean(par_ms)) if st["path"] == 1 else sweep_avg_ms
     achieved = b_plan / (dom_ms / 1e3) / 1e9
     line = {
@@ -301,7 +302,8 @@ def run_ours(args):
         "plan_p50_ms": float(np.median(step_ms)), "plan_p95_ms": float(np.percentile(step_ms, 95)),
         "kernel_ms": {"prepass": float(st["ms_prepass"]), "tracker_init" if world == 1 else "totals_exchange+tracker_init": float(st["ms_tracker"]),
                       "parallel": float(np.mean(par_ms)),
-                      "verify_or_sweep" if world == 1 else "exchange+verify": sweep_avg_ms, "path": "node-parallel" if st["path"] == 1 else "sequential"},
+                      "verify_or_sweep" if world == 1 else "exchange+verify": sweep_avg_ms,
+                      "path": "single launch (k_plan_fused)" if fused else ("node-parallel" if st["path"] == 1 else "sequential")},
         "roofline": {"bound": "hbm", "kernel": dom_name, "kernel_ms": dom_ms, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": recorded_traffic(dom_name) if (args.workload == "mig-10k" and world == 1) else None, "algorithmic_bytes": b_plan, "peak_source": peak_src},
         "e2e": {"value": e2e_value, "unit": "candidates/s", "h2d_bytes_per_step": int(est["h2d_bytes"]),

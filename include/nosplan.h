@@ -122,6 +122,8 @@ typedef struct nosplan_stats {
     int32_t kernel_launches;
     int32_t path;                      /* 1: node-parallel pass (saturated lacking vector), 0: sequential sweep */
     int64_t h2d_bytes, d2h_bytes;      /* bytes copied by upload() / download() */
+    int32_t fused;                     /* 1: the plan is the single-launch kernel's (path == 1), 0: the classic kernel sequence's */
+    int32_t fused_reject;              /* != 0: the single-launch kernel ran first and rejected its own hypothesis (reason bits) */
 } nosplan_stats;
 
 /* Create an engine bound to one CUDA device.  Replaces: mig.NewPlanner / mps.NewPlanner

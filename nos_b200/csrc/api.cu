@@ -28,6 +28,9 @@ void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int
 
 cudaError_t sweep_prepare_device();
 int sweep_max_keys();
+cudaError_t fused_prepare_device(int* blocks_per_sm);
+cudaError_t launch_fused(const DevProblem& pb, int max_blocks, cudaStream_t st);
+int fused_max_pad_pods();
 }  // namespace nsp
 
 using namespace nsp;
@@ -133,7 +136,7 @@ struct Layout {            // byte offsets into the arena / staging buffer
         node_alloc, node_req, node_allowed, node_npods, nodes_end,
         tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, wave, work_end, cand_flag, cand_idx, out_count, out_mask, out_end,
         pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
-        cmin_cpu, cmin_mem, cmin_eph, upload_end, placed, entry_lack, total;
+        cmin_cpu, cmin_mem, cmin_eph, fp_pod, fp_l1, fp_l2, fp_runs, upload_end, placed, entry_lack, total;
 };
 
 int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes, size_t keep_bytes = 0) {
@@ -289,7 +292,9 @@ void nosplan_phase_times(nosplan* h, nosplan_stats* stats) {
         cudaEventElapsedTime(&a, h->ev[2], h->ev[6]); cudaEventElapsedTime(&b, h->ev[11], h->ev[3]);
         stats->ms_kernels = a + b;
     } else cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
-    if (h->kernel_events) {
+    stats->ms_kernels += h->ms_rejected;              // a rejected single-launch attempt in front of the classic sequence
+    if (h->last_fused) stats->ms_parallel = stats->ms_kernels;
+    else if (h->kernel_events) {
         cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
         cudaEventElapsedTime(&stats->ms_tracker, h->ev[h->split_run ? 11 : 6], h->ev[7]);
         cudaEventElapsedTime(&stats->ms_parallel, h->ev[7], h->ev[8]);
@@ -307,11 +312,14 @@ int nosplan_create(int cuda_device, nosplan_t** out) {
     nosplan* h = new (std::nothrow) nosplan();
     if (!h) return NOSPLAN_E_NOMEM;
     h->device = cuda_device;
+    int sms = 148, per_sm = 4;
     if (cudaSetDevice(cuda_device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        sweep_prepare_device() != cudaSuccess) {
+        sweep_prepare_device() != cudaSuccess || fused_prepare_device(&per_sm) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cuda_device) != cudaSuccess) {
         delete h;
         return NOSPLAN_E_CUDA;
     }
+    h->fused_blocks = sms * per_sm;
     for (auto& e : h->ev)
         if (cudaEventCreate(&e) != cudaSuccess) { delete h; return NOSPLAN_E_CUDA; }
     *out = h;
@@ -360,9 +368,8 @@ int nosplan_host_pod_order(const nosplan_snapshot* s, const nosplan_pods* pods, 
 
 // Kernels that need only the node arrays: work-area reset + k_prepass.  nosplan_plan issues them as soon as the node DMA
 // is queued, so they run while the host is still ordering the pods.
-static int run_pre(nosplan* h, bool split) {
-    CU(h, cudaEventRecord(h->ev[2], h->stream));
-    {   // this run's copy of the small state; k_prepass clears the other copy and the tracker tables
+static void flip_small_state(nosplan* h) {
+    {   // this run's copy of the small state; the run's first kernel clears the other copy (and k_prepass the tracker tables)
         DevProblem& pb = h->pb;
         const unsigned use = h->run_parity ^= 1u;
         const ptrdiff_t to_use = (ptrdiff_t)(use ? h->small_bytes : 0) - (ptrdiff_t)(h->bound_copy ? h->small_bytes : 0);
@@ -373,6 +380,13 @@ static int run_pre(nosplan* h, bool split) {
         pb.zero_next = reinterpret_cast<unsigned long long*>(h->d_work + (use ? 0 : h->small_bytes));
         pb.zero_next_n8 = (int)(h->small_bytes >> 3);
     }
+}
+
+static int run_pre(nosplan* h, bool split) {
+    CU(h, cudaEventRecord(h->ev[2], h->stream));
+    flip_small_state(h);
+    h->fused_pending = false; h->last_fused = false; h->fused_reject = 0; h->ms_rejected = 0.f;
+    h->placed_dirty = true;                  // the classic kernels index `placed` by tracker key
     launch_prepass(h->pb, h->stream);
     if (split || h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
     CU(h, cudaGetLastError());
@@ -442,7 +456,10 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     put(L.maxfree, 4 * KP); put(L.gflags, 16); put(L.acc, 32); put(L.lack_dec, 4 * KP); put(L.next_node, 16); put(L.wave, 32);
     const size_t small_bytes = o - L.tot;
     o += small_bytes;                                        // the second copy
-    put(L.placed, 4 * (((size_t)P + 31) / 32));             // tracker tables: sized for P keys (keys <= P), reset with the rest
+    // tracker tables: sized for P keys (keys <= P), reset with the rest; the single-launch plan indexes `placed` by padded pod
+    // position instead (at most FRUN_MAX runs, each padded to a multiple of 64)
+    const size_t pad_pods_max = (size_t)P + 64 * (size_t)FRUN_MAX;
+    put(L.placed, 4 * ((pad_pods_max + 31) / 32));
     put(L.entry_lack, 4 * (size_t)P * KP);
     L.work_end = o;
     put(L.cand_flag, (size_t)N); put(L.cand_idx, 4 * (size_t)N);
@@ -453,7 +470,8 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     put(L.pod_sptr, 4 * ((size_t)P + 1)); put(L.pod_scol, 4 * (size_t)nnz); put(L.pod_sqty, 8 * (size_t)nnz);
     const size_t part1_end = o;
     // part 2 (runs, chunk minima) is laid out once the pods are ordered; the arena is sized from bounds: runs <= P, chunks <= P
-    const size_t bound = part1_end + al(sizeof(RunRec) * (size_t)P) + al(4 * ((size_t)P + 1)) + 3 * al(8 * (size_t)P) + 4096;
+    const size_t bound = part1_end + al(sizeof(RunRec) * (size_t)P) + al(4 * ((size_t)P + 1)) + 3 * al(8 * (size_t)P) + 4096 +
+                         al(8 * pad_pods_max) + al(pad_pods_max) + al(pad_pods_max / 8 + 8) + al(sizeof(FRun) * FRUN_MAX);
     CU(h, cudaSetDevice(h->device));
     const size_t out_bytes = al(16 * NG) + al(2 * NG) + al(sizeof(DevStats));
     int rc = ensure(h, bound, bound, out_bytes, keep ? h->res_nodes_end : 0);
@@ -542,7 +560,12 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot; h->small_bytes = small_bytes;
     h->run_parity = 1; h->bound_copy = 0;                    // pb points at copy 0; the first run flips to it
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
-    if (h->in_plan) { rc = run_pre(h, true); if (rc != NOSPLAN_OK) return rc; }
+    // Node-side conditions of the single-launch plan (fused.cu); the pod-side ones follow below.  Where it can still apply,
+    // k_prepass is not queued early: the fused kernel does that work itself once the pods are on the device.
+    bool fused_ok = mig && G <= 8 && N > 0 && P > 0 && !getenv("NOSPLAN_NO_FUSED");
+    for (int r = 0; r < n_rows && fused_ok; ++r)
+        for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p] > 31) { fused_ok = false; break; }
+    if (h->in_plan && !fused_ok) { rc = run_pre(h, true); if (rc != NOSPLAN_OK) return rc; }
     lap("nodes queued");
     // per-node validation, while the copy engine works (k_prepass, the only kernel that can already be queued, clamps what it
     // reads; every other kernel is launched after this call has succeeded)
@@ -570,6 +593,11 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     std::vector<uint32_t>& flags = h->v_flags; flags.resize(P);
     std::vector<unsigned long long>& cls = h->v_cls; cls.resize(P);
     int n_keys = 0;
+    std::vector<uint8_t>& key_seen = h->v_key_seen; key_seen.assign(P, 0);
+    bool keys_unique = true, any_other = false, any_zero = false;
+    long long max_q = 0;
+    unsigned long long or_cpu = 0, or_mem = 0;
+    long long max_cpu = 0, max_mem = 0;
     for (int i = 0; i < P; ++i) {
         const int a = pods->scalar_ptr[i], b = pods->scalar_ptr[i + 1];
         if (a > b || b > nnz) return fail(h, NOSPLAN_E_INVALID, "pod %d: bad scalar_ptr", i);
@@ -583,6 +611,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
                 const long long q = pods->scalar_qty[e];
                 if (q <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
                 if (first_prof[i] < 0) first_prof[i] = col - 3;
+                max_q = std::max(max_q, q);
                 ck = (++n_slice == 1 && q < (1ll << 40)) ? (((unsigned long long)(col - 2)) << 40 | (unsigned long long)q) : CLS_MULTI;
             } else other = true;
         }
@@ -591,11 +620,15 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         if ((bc | bm | be) < 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: negative cpu / memory / ephemeral-storage request", i);
         uint32_t f = 0;
         if (!prefilter_ok || prefilter_ok[i]) f |= PF_PRE_OK;
-        if (other) f |= PF_HAS_OTHER;
-        if (a == b && (bc | bm | be) == 0) f |= PF_ZERO_REQ;
+        if (other) { f |= PF_HAS_OTHER; any_other = true; }
+        if (a == b && (bc | bm | be) == 0) { f |= PF_ZERO_REQ; any_zero = true; }
         flags[i] = f;
+        or_cpu |= (unsigned long long)bc; or_mem |= (unsigned long long)bm;
+        max_cpu = std::max(max_cpu, bc); max_mem = std::max(max_mem, bm);
         const int k = pods->tracker_key[i];
         if (k < 0 || k >= P) return fail(h, NOSPLAN_E_INVALID, "pod %d: tracker_key out of range", i);
+        if (key_seen[k]) keys_unique = false;
+        key_seen[k] = 1;
         n_keys = std::max(n_keys, k + 1);
     }
     if (n_keys > sweep_max_keys()) return fail(h, NOSPLAN_E_LIMIT, "%d tracker keys > %d", n_keys, sweep_max_keys());
@@ -673,6 +706,21 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     put(L.runs, sizeof(RunRec) * (size_t)n_runs);
     put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
     put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
+    // ---- single-launch plan (fused.cu), pod-side conditions: single-profile classes in at most FRUN_MAX runs, one tracker
+    //      entry per pod, only cpu / memory / slice requests, and requests that fit the compact int32 units
+    int cpu_shift = 0, mem_shift = 0, pad_pods = 0;
+    unsigned rset = 0;
+    fused_ok = fused_ok && single_profile_classes && n_runs <= FRUN_MAX && keys_unique && any_eph == 0 && !any_zero &&
+               !(any_other && filter_mode == NOSPLAN_FILTER_RESOURCES_FIT) && max_q < (1 << 15);
+    if (fused_ok) {
+        cpu_shift = or_cpu ? __builtin_ctzll(or_cpu) : 0; mem_shift = or_mem ? __builtin_ctzll(or_mem) : 0;
+        fused_ok = (max_cpu >> cpu_shift) < F_COST_LIMIT && (max_mem >> mem_shift) < F_COST_LIMIT;
+        for (const RunRec& r : runs) { pad_pods += (r.len + 63) & ~63; if (r.n_ent) rset |= 1u << r.p_single; }
+        fused_ok = fused_ok && pad_pods <= fused_max_pad_pods() && rset != 0;
+    }
+    if (fused_ok) {
+        put(L.fp_pod, 8 * (size_t)pad_pods); put(L.fp_l1, (size_t)pad_pods); put(L.fp_l2, (size_t)pad_pods / 8); put(L.fp_runs, sizeof(FRun) * (size_t)n_runs);
+    } else L.fp_pod = L.fp_l1 = L.fp_l2 = L.fp_runs = o;
     L.upload_end = o;
     L.total = o;
     if (L.total > bound) return fail(h, NOSPLAN_E_NOMEM, "internal: arena bound exceeded");
@@ -681,6 +729,36 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     {
         long long* c0 = (long long*)(S + L.cmin_cpu); long long* c1 = (long long*)(S + L.cmin_mem); long long* c2 = (long long*)(S + L.cmin_eph);
         for (int c = 0; c < n_chunks; ++c) { c0[c] = cmin[3 * (size_t)c]; c1[c] = cmin[3 * (size_t)c + 1]; c2[c] = cmin[3 * (size_t)c + 2]; }
+    }
+    if (fused_ok) {
+        // padded position space: run r occupies [pos0, pos0 + 64 * nblk); a pod that can never be placed (PreFilter verdict
+        // false) and every padding slot cost F_NONE; minima per 8 and per 64 positions and per run
+        int32_t* fpod = (int32_t*)(S + L.fp_pod); int32_t* l1 = (int32_t*)(S + L.fp_l1); int32_t* l2 = (int32_t*)(S + L.fp_l2);
+        FRun* fr = (FRun*)(S + L.fp_runs);
+        const long long* cpu = (const long long*)(S + L.pod_cpu); const long long* mem = (const long long*)(S + L.pod_mem);
+        const uint32_t* fl = (const uint32_t*)(S + L.pod_flags);
+        std::fill(fpod, fpod + 2 * (size_t)pad_pods, (int32_t)F_NONE);
+        std::fill(l1, l1 + (size_t)pad_pods / 4, (int32_t)F_NONE);
+        std::fill(l2, l2 + (size_t)pad_pods / 32, (int32_t)F_NONE);
+        int pos = 0;
+        for (int r = 0; r < n_runs; ++r) {
+            const RunRec& rr = runs[r];
+            FRun f; std::memset(&f, 0, sizeof f);
+            f.pos0 = pos; f.nblk = (rr.len + 63) >> 6; f.n_real = rr.len;
+            f.p = rr.n_ent ? (int)rr.p_single : -1; f.q = rr.n_ent ? (int)rr.q[rr.p_single] : 0;
+            f.min_c = f.min_m = F_NONE;
+            for (int k = 0; k < rr.len; ++k) {
+                const int si = rr.start + k, x = pos + k;
+                if (!(fl[si] & PF_PRE_OK)) continue;
+                const int32_t c = (int32_t)(cpu[si] >> cpu_shift), m = (int32_t)(mem[si] >> mem_shift);
+                fpod[2 * (size_t)x] = c; fpod[2 * (size_t)x + 1] = m;
+                int32_t* a = l1 + 2 * (size_t)(x >> 3); int32_t* b = l2 + 2 * (size_t)(x >> 6);
+                a[0] = std::min(a[0], c); a[1] = std::min(a[1], m); b[0] = std::min(b[0], c); b[1] = std::min(b[1], m);
+                f.min_c = std::min(f.min_c, c); f.min_m = std::min(f.min_m, m);
+            }
+            fr[r] = f;
+            pos += f.nblk * 64;
+        }
     }
     CU(h, cudaEventRecord(h->ev[9], h->stream));
     CU(h, cudaMemcpyAsync(A + L.pod_cpu, S + L.pod_cpu, L.upload_end - L.pod_cpu, cudaMemcpyHostToDevice, h->stream));
@@ -704,6 +782,10 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     }
     pb.placed = (unsigned*)(A + L.placed);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
+    pb.fp_pod = (const uint2*)(A + L.fp_pod); pb.fp_l1 = (const uint2*)(A + L.fp_l1); pb.fp_l2 = (const uint2*)(A + L.fp_l2);
+    pb.fp_runs = (const FRun*)(A + L.fp_runs);
+    pb.fp_n_runs = fused_ok ? n_runs : 0; pb.fp_pad_pods = pad_pods; pb.fp_cpu_shift = cpu_shift; pb.fp_mem_shift = mem_shift; pb.fp_rset = rset;
+    h->fused_ok = fused_ok; h->fused_pending = false; h->placed_dirty = false;
     lap("pods queued");
     h->h2d_bytes = (keep ? 0 : L.nodes_end) + (L.upload_end - L.pod_cpu);
     h->uploaded = true;
@@ -760,14 +842,36 @@ static int run_post(nosplan* h) {
     return NOSPLAN_OK;
 }
 
-int nosplan_run(nosplan_t* h) {
-    if (!h) return NOSPLAN_E_INVALID;
-    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_run before nosplan_upload");
-    CU(h, cudaSetDevice(h->device));
+// The whole Plan() as one kernel (fused.cu).  Its verdict is read back by nosplan_resolve.
+static int run_fused(nosplan* h) {
+    if (h->placed_dirty) {                                   // a classic run indexed `placed` by tracker key
+        CU(h, cudaMemsetAsync(h->pb.placed, 0, 4 * (size_t)(h->pb.fp_pad_pods >> 5), h->stream));
+        h->placed_dirty = false;
+    }
+    CU(h, cudaEventRecord(h->ev[2], h->stream));
+    flip_small_state(h);
+    h->pb.slice_mode = 0; h->pb.node_lo = 0; h->pb.node_hi = h->pb.N; h->pb.whole_snapshot = 1;
+    CU(h, launch_fused(h->pb, h->fused_blocks, h->stream));
+    CU(h, cudaEventRecord(h->ev[3], h->stream));
+    h->pre_done = false; h->split_run = false;
+    h->launches = 1;
+    h->fused_pending = true; h->last_fused = true; h->fused_reject = 0; h->ms_rejected = 0.f;
+    h->ran = true;
+    return NOSPLAN_OK;
+}
+
+static int run_classic(nosplan* h) {
     h->pb.slice_mode = 0;
     int rc = run_pre(h, false);
     if (rc != NOSPLAN_OK) return rc;
     return run_post(h);
+}
+
+int nosplan_run(nosplan_t* h) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_run before nosplan_upload");
+    CU(h, cudaSetDevice(h->device));
+    return h->fused_ok ? run_fused(h) : run_classic(h);
 }
 
 // ---- node-sharded Plan() over `world` ranks (one handle per rank, the same snapshot uploaded on each) --------------
@@ -927,10 +1031,35 @@ int nosplan_slice_chain(nosplan_t* h, const void* d_state_in, void* d_state_out)
 int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count, void** d_gpu_mask) {
     if (!h) return NOSPLAN_E_INVALID;
     if (!h->uploaded) return fail(h, NOSPLAN_E_INVALID, "nosplan_device_outputs before nosplan_upload");
+    { const int rc = nosplan_resolve(h); if (rc != NOSPLAN_OK) return rc; }
     if (d_gpu_count) *d_gpu_count = h->pb.out_count;
     if (d_gpu_mask) *d_gpu_mask = h->pb.out_mask;
     return NOSPLAN_OK;
 }
+
+}  // extern "C"
+
+static int nosplan_reject_to_classic(nosplan* h, int reasons) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, h->ev[2], h->ev[3]);
+    const int rc = run_classic(h);
+    h->fused_reject = reasons; h->ms_rejected = t;
+    h->launches += 1;
+    return rc;
+}
+
+int nosplan_resolve(nosplan* h) {
+    if (!h || !h->fused_pending) return NOSPLAN_OK;
+    CU(h, cudaSetDevice(h->device));
+    DevStats* ds = reinterpret_cast<DevStats*>(h->h_out + al(h->out_count_bytes) + al(h->out_mask_bytes));
+    CU(h, cudaMemcpyAsync(ds, h->pb.stats, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->fused_pending = false;
+    if (ds->path != 2) return NOSPLAN_OK;
+    return nosplan_reject_to_classic(h, ds->pad);
+}
+
+extern "C" {
 
 int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* stats) {
     if (!h) return NOSPLAN_E_INVALID;
@@ -948,14 +1077,23 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
                  cudaPointerGetAttributes(&a2, out->gpu_mask) == cudaSuccess && a2.type == cudaMemoryTypeHost;
         (void)cudaGetLastError();
     }
-    CU(h, cudaEventRecord(h->ev[4], h->stream));
-    if (h->out_count_bytes) {
-        CU(h, cudaMemcpyAsync(direct ? (void*)out->gpu_count : (void*)O, h->pb.out_count, h->out_count_bytes, cudaMemcpyDeviceToHost, h->stream));
-        CU(h, cudaMemcpyAsync(direct ? (void*)out->gpu_mask : (void*)(O + o_mask), h->pb.out_mask, h->out_mask_bytes, cudaMemcpyDeviceToHost, h->stream));
+    for (;;) {
+        CU(h, cudaEventRecord(h->ev[4], h->stream));
+        if (h->out_count_bytes) {
+            CU(h, cudaMemcpyAsync(direct ? (void*)out->gpu_count : (void*)O, h->pb.out_count, h->out_count_bytes, cudaMemcpyDeviceToHost, h->stream));
+            CU(h, cudaMemcpyAsync(direct ? (void*)out->gpu_mask : (void*)(O + o_mask), h->pb.out_mask, h->out_mask_bytes, cudaMemcpyDeviceToHost, h->stream));
+        }
+        CU(h, cudaMemcpyAsync(O + o_stats, h->pb.stats, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
+        CU(h, cudaEventRecord(h->ev[5], h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));
+        if (!h->fused_pending) break;
+        // single-launch plan: the kernel verified its own hypothesis; rejected -> the classic sequence on the same inputs
+        h->fused_pending = false;
+        DevStats ds; std::memcpy(&ds, O + o_stats, sizeof ds);
+        if (ds.path != 2) break;
+        const int rc2 = nosplan_reject_to_classic(h, ds.pad);
+        if (rc2 != NOSPLAN_OK) return rc2;
     }
-    CU(h, cudaMemcpyAsync(O + o_stats, h->pb.stats, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
-    CU(h, cudaEventRecord(h->ev[5], h->stream));
-    CU(h, cudaStreamSynchronize(h->stream));
     if (want && !direct) {
         std::memcpy(out->gpu_count, O, h->out_count_bytes);
         std::memcpy(out->gpu_mask, O + o_mask, h->out_mask_bytes);
@@ -969,8 +1107,10 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         nosplan_phase_times(h, stats);
         cudaEventElapsedTime(&stats->ms_d2h, h->ev[4], h->ev[5]);
         stats->path = ds.path;
-        stats->waves = h->pb.slice_mode ? 0 : ds.pad;
+        stats->waves = (h->pb.slice_mode || h->last_fused) ? 0 : ds.pad;
         stats->kernel_launches = h->launches;
+        stats->fused = h->last_fused ? 1 : 0;
+        stats->fused_reject = h->fused_reject;
         stats->h2d_bytes = (int64_t)h->h2d_bytes;
         stats->d2h_bytes = (int64_t)(h->out_count_bytes + h->out_mask_bytes + sizeof(DevStats));
     }

@@ -43,6 +43,7 @@ extern "C" int nosplan_changed_nodes(nosplan_t* h, int32_t* node_idx, int32_t ca
     if (!n_changed || capacity < 0 || (capacity > 0 && !node_idx)) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_changed_nodes: null output");
 #define DCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return nosplan_fail(h, NOSPLAN_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
     DCU(cudaSetDevice(h->device));
+    { const int rc = nosplan_resolve(h); if (rc != NOSPLAN_OK) return rc; }   // a single-launch plan whose verdict is still on the device
     const int N = h->pb.N;
     *n_changed = 0;
     if (N == 0) return NOSPLAN_OK;

@@ -32,6 +32,13 @@ struct nosplan {
     std::vector<nsp::RunRec> v_runs;
     std::vector<int32_t> v_chunk_off;
     std::vector<long long> v_cmin;
+    std::vector<uint8_t> v_key_seen;
+    // single-launch plan (fused.cu): applicable to the uploaded problem; its verdict has not been read back yet (the host
+    // runs the classic kernel sequence if the kernel rejected its own hypothesis); the classic sequence left key-indexed
+    // bits in `placed`; grid size of one resident wave on this handle's device
+    bool fused_ok = false, fused_pending = false, placed_dirty = false;
+    bool last_fused = false; int fused_reject = 0; float ms_rejected = 0.f;   // what the last run was; why / how long a rejected attempt took
+    int fused_blocks = 148 * 4;
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
     size_t h2d_bytes = 0;
@@ -52,6 +59,7 @@ struct nosplan {
 };
 
 int nosplan_fail(nosplan* h, int code, const char* fmt, ...);
+int nosplan_resolve(nosplan* h);      // waits for a pending single-launch plan and re-plans on the classic path if it was rejected
 void nosplan_phase_times(nosplan* h, nosplan_stats* stats);
 int nosplan_slice_begin_ex(nosplan* h, void* d_totals);
 int nosplan_slice_mid_ex(nosplan* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes,

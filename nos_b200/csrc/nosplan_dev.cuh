@@ -29,6 +29,32 @@ struct __align__(16) RunRec {
 };
 static_assert(sizeof(RunRec) == 48, "RunRec layout");
 
+// ---- single-launch Plan() (fused.cu) ---------------------------------------------------------------------------------
+// Pods of the fused path live in a PADDED position space: every run starts at a multiple of 64 and is padded to a multiple
+// of 64 with ineligible dummies, so that the 8-ary tree of minima over the positions (8 pods, 64 pods) never straddles a
+// run.  A pod is its two NodeResourcesFit costs as non-negative int32 in common power-of-two units (cpu milli >> cpu_shift,
+// memory bytes >> mem_shift; exact because every pod request is a multiple of the unit); F_NONE marks a pod that can never be
+// placed (PreFilter verdict false, or padding) and, in the minima, a group without an eligible pod.
+constexpr int FRUN_MAX = 64;                 // runs the fused kernel keeps in shared memory
+constexpr int F_NONE = 0x7fffffff;
+constexpr int F_REM_MAX = 0x7ffffffe;        // largest remaining capacity representable; larger node values reject the fused plan
+constexpr int F_COST_LIMIT = 1 << 28;        // pod costs stay below this so that eight of them sum without overflow
+struct __align__(16) FRun {
+    int32_t pos0;                            // first padded position (multiple of 64)
+    int32_t nblk;                            // 64-pod blocks
+    int32_t n_real;                          // pods of the run, eligible or not (SliceTracker counts them all)
+    int32_t p;                               // requested profile id, -1: no slice request
+    int32_t q;                               // requested quantity
+    int32_t min_c, min_m;                    // minima over the run's eligible pods
+    int32_t pad;
+};
+static_assert(sizeof(FRun) == 32, "FRun layout");
+// reasons the fused plan is rejected (DevProblem::wave[5]); the host then runs the classic kernel sequence
+constexpr int FREJ_COUNTS = 1;               // a used / free count above 31: the byte-wise sums over a node's GPUs could wrap
+constexpr int FREJ_REM = 2;                  // a node's remaining cpu / memory does not fit the int32 units
+constexpr int FREJ_HYPOTHESIS = 4;           // lacking set != requested profiles, or not saturated to the end
+constexpr int FREJ_ACCOUNTS = 8;             // a node's Allocatable / Requested disagree with its GPUs
+
 // State handed from rank to rank by the chained sweep: lackingSlices, the running sum(alloc - requested) per slice column,
 // counters (visited nodes, geometry evaluations, placements, candidate nodes), committed flag, lacking profiles at the start,
 // then the bitmap of tracker keys removed so far.
@@ -139,6 +165,10 @@ struct DevProblem {
     int32_t* next_node;              // [4]  [0] work counter of the node-parallel pass, [1] / [2] CTAs of k_prepass / k_plan_parallel done
     int32_t* wave;                   // [8]  [0] k_plan_sweep hands the plan to k_plan_waves  [1],[2] first node of the wave that changes
                                      //      the lacking vector (by wave parity)  [3] candidate nodes  [4] waves run
+    // single-launch Plan() (fused.cu): padded pod costs, their minima per 8 and per 64 positions, runs, units
+    const uint2* fp_pod; const uint2* fp_l1; const uint2* fp_l2; const FRun* fp_runs;
+    int fp_n_runs, fp_pad_pods, fp_cpu_shift, fp_mem_shift;
+    unsigned fp_rset;                // profiles some pod requests: the lacking set the fused kernel speculates on
     int whole_snapshot;              // the node-parallel pass covers every node on this rank (no exchange needed)
     int verify_inline;               // single GPU: the last CTA of k_plan_parallel verifies the pass itself (else k_plan_sweep does)
     // outputs
