@@ -28,8 +28,8 @@ void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int
 
 cudaError_t sweep_prepare_device();
 int sweep_max_keys();
-cudaError_t fused_prepare_device(int* blocks_per_sm);
-cudaError_t launch_fused(const DevProblem& pb, int max_blocks, cudaStream_t st);
+cudaError_t fused_prepare_device();
+cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st);
 int fused_max_pad_pods();
 }  // namespace nsp
 
@@ -136,7 +136,7 @@ struct Layout {            // byte offsets into the arena / staging buffer
         node_alloc, node_req, node_allowed, node_npods, nodes_end,
         tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, wave, work_end, cand_flag, cand_idx, out_count, out_mask, out_end,
         pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
-        cmin_cpu, cmin_mem, cmin_eph, fp_pod, fp_l1, fp_l2, fp_runs, upload_end, placed, entry_lack, total;
+        cmin_cpu, cmin_mem, cmin_eph, fp_blob, upload_end, placed, entry_lack, total;
 };
 
 int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes, size_t keep_bytes = 0) {
@@ -312,14 +312,14 @@ int nosplan_create(int cuda_device, nosplan_t** out) {
     nosplan* h = new (std::nothrow) nosplan();
     if (!h) return NOSPLAN_E_NOMEM;
     h->device = cuda_device;
-    int sms = 148, per_sm = 4;
+    int sms = 148;
     if (cudaSetDevice(cuda_device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        sweep_prepare_device() != cudaSuccess || fused_prepare_device(&per_sm) != cudaSuccess ||
+        sweep_prepare_device() != cudaSuccess || fused_prepare_device() != cudaSuccess ||
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cuda_device) != cudaSuccess) {
         delete h;
         return NOSPLAN_E_CUDA;
     }
-    h->fused_blocks = sms * per_sm;
+    h->sms = sms;
     for (auto& e : h->ev)
         if (cudaEventCreate(&e) != cudaSuccess) { delete h; return NOSPLAN_E_CUDA; }
     *out = h;
@@ -471,7 +471,8 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     const size_t part1_end = o;
     // part 2 (runs, chunk minima) is laid out once the pods are ordered; the arena is sized from bounds: runs <= P, chunks <= P
     const size_t bound = part1_end + al(sizeof(RunRec) * (size_t)P) + al(4 * ((size_t)P + 1)) + 3 * al(8 * (size_t)P) + 4096 +
-                         al(8 * pad_pods_max) + al(pad_pods_max) + al(pad_pods_max / 8 + 8) + al(sizeof(FRun) * FRUN_MAX);
+                         al(8 * (pad_pods_max + pad_pods_max / 8 + pad_pods_max / 64 + pad_pods_max / 512 + 8)) + al(sizeof(FRun) * FRUN_MAX) +
+                         al(18 * (size_t)MAX_ROWS) + al(4 * (MAX_MODELS + 1)) + 4096;
     CU(h, cudaSetDevice(h->device));
     const size_t out_bytes = al(16 * NG) + al(2 * NG) + al(sizeof(DevStats));
     int rc = ensure(h, bound, bound, out_bytes, keep ? h->res_nodes_end : 0);
@@ -711,16 +712,30 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     int cpu_shift = 0, mem_shift = 0, pad_pods = 0;
     unsigned rset = 0;
     fused_ok = fused_ok && single_profile_classes && n_runs <= FRUN_MAX && keys_unique && any_eph == 0 && !any_zero &&
-               !(any_other && filter_mode == NOSPLAN_FILTER_RESOURCES_FIT) && max_q < (1 << 15);
+               !(any_other && filter_mode == NOSPLAN_FILTER_RESOURCES_FIT) && max_q <= 1;
     if (fused_ok) {
         cpu_shift = or_cpu ? __builtin_ctzll(or_cpu) : 0; mem_shift = or_mem ? __builtin_ctzll(or_mem) : 0;
         fused_ok = (max_cpu >> cpu_shift) < F_COST_LIMIT && (max_mem >> mem_shift) < F_COST_LIMIT;
         for (const RunRec& r : runs) { pad_pods += (r.len + 63) & ~63; if (r.n_ent) rset |= 1u << r.p_single; }
         fused_ok = fused_ok && pad_pods <= fused_max_pad_pods() && rset != 0;
     }
-    if (fused_ok) {
-        put(L.fp_pod, 8 * (size_t)pad_pods); put(L.fp_l1, (size_t)pad_pods); put(L.fp_l2, (size_t)pad_pods / 8); put(L.fp_runs, sizeof(FRun) * (size_t)n_runs);
-    } else L.fp_pod = L.fp_l1 = L.fp_l2 = L.fp_runs = o;
+    // the blob: header [geometry rows | key masks | model ranges | runs | runs per profile], then (cpu, memory) pairs
+    // [minima per 512 | per 64 | per 8 | pods]; every section starts on a 16-byte boundary
+    int fp_off[9] = {0};
+    {
+        auto a16 = [](size_t x) { return (int)((x + 15) & ~(size_t)15); };
+        const int n3 = (pad_pods + 511) / 512, n2 = pad_pods / 64, n1 = pad_pods / 8;
+        fp_off[0] = a16(16 * (size_t)n_rows);
+        fp_off[1] = fp_off[0] + a16(2 * (size_t)n_rows);
+        fp_off[2] = fp_off[1] + a16(4 * ((size_t)n_models + 1));
+        fp_off[3] = fp_off[2] + a16(sizeof(FRun) * (size_t)n_runs);
+        fp_off[4] = fp_off[3] + a16(8 * (KP + 1));
+        fp_off[5] = fp_off[4] + a16(8 * (size_t)n3);
+        fp_off[6] = fp_off[5] + a16(8 * (size_t)n2);
+        fp_off[7] = fp_off[6] + a16(8 * (size_t)n1);
+        fp_off[8] = fp_off[7] + a16(8 * (size_t)pad_pods);
+    }
+    if (fused_ok) put(L.fp_blob, (size_t)fp_off[8]); else L.fp_blob = o;
     L.upload_end = o;
     L.total = o;
     if (L.total > bound) return fail(h, NOSPLAN_E_NOMEM, "internal: arena bound exceeded");
@@ -733,13 +748,22 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     if (fused_ok) {
         // padded position space: run r occupies [pos0, pos0 + 64 * nblk); a pod that can never be placed (PreFilter verdict
         // false) and every padding slot cost F_NONE; minima per 8 and per 64 positions and per run
-        int32_t* fpod = (int32_t*)(S + L.fp_pod); int32_t* l1 = (int32_t*)(S + L.fp_l1); int32_t* l2 = (int32_t*)(S + L.fp_l2);
-        FRun* fr = (FRun*)(S + L.fp_runs);
+        unsigned char* B = S + L.fp_blob;
+        int32_t* l3 = (int32_t*)(B + fp_off[4]); int32_t* l2 = (int32_t*)(B + fp_off[5]); int32_t* l1 = (int32_t*)(B + fp_off[6]);
+        int32_t* fpod = (int32_t*)(B + fp_off[7]);
+        FRun* fr = (FRun*)(B + fp_off[2]);
+        unsigned long long* prof_runs = (unsigned long long*)(B + fp_off[3]);
+        std::memset(B, 0, (size_t)fp_off[4]);
+        if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
+        for (int r = 0; r < n_rows; ++r) {
+            uint16_t m = 0;
+            for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p]) m |= (uint16_t)(1u << p);
+            ((uint16_t*)(B + fp_off[0]))[r] = m;
+        }
+        if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
         const long long* cpu = (const long long*)(S + L.pod_cpu); const long long* mem = (const long long*)(S + L.pod_mem);
         const uint32_t* fl = (const uint32_t*)(S + L.pod_flags);
-        std::fill(fpod, fpod + 2 * (size_t)pad_pods, (int32_t)F_NONE);
-        std::fill(l1, l1 + (size_t)pad_pods / 4, (int32_t)F_NONE);
-        std::fill(l2, l2 + (size_t)pad_pods / 32, (int32_t)F_NONE);
+        std::fill(l3, (int32_t*)(B + fp_off[8]), (int32_t)F_NONE);
         int pos = 0;
         for (int r = 0; r < n_runs; ++r) {
             const RunRec& rr = runs[r];
@@ -752,11 +776,13 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
                 if (!(fl[si] & PF_PRE_OK)) continue;
                 const int32_t c = (int32_t)(cpu[si] >> cpu_shift), m = (int32_t)(mem[si] >> mem_shift);
                 fpod[2 * (size_t)x] = c; fpod[2 * (size_t)x + 1] = m;
-                int32_t* a = l1 + 2 * (size_t)(x >> 3); int32_t* b = l2 + 2 * (size_t)(x >> 6);
+                int32_t* a = l1 + 2 * (size_t)(x >> 3); int32_t* b = l2 + 2 * (size_t)(x >> 6); int32_t* d = l3 + 2 * (size_t)(x >> 9);
                 a[0] = std::min(a[0], c); a[1] = std::min(a[1], m); b[0] = std::min(b[0], c); b[1] = std::min(b[1], m);
+                d[0] = std::min(d[0], c); d[1] = std::min(d[1], m);
                 f.min_c = std::min(f.min_c, c); f.min_m = std::min(f.min_m, m);
             }
             fr[r] = f;
+            prof_runs[f.p >= 0 ? f.p : KP] |= 1ull << r;
             pos += f.nblk * 64;
         }
     }
@@ -782,8 +808,8 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     }
     pb.placed = (unsigned*)(A + L.placed);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
-    pb.fp_pod = (const uint2*)(A + L.fp_pod); pb.fp_l1 = (const uint2*)(A + L.fp_l1); pb.fp_l2 = (const uint2*)(A + L.fp_l2);
-    pb.fp_runs = (const FRun*)(A + L.fp_runs);
+    pb.fp_blob = A + L.fp_blob;
+    for (int k = 0; k < 9; ++k) pb.fp_off[k] = fp_off[k];
     pb.fp_n_runs = fused_ok ? n_runs : 0; pb.fp_pad_pods = pad_pods; pb.fp_cpu_shift = cpu_shift; pb.fp_mem_shift = mem_shift; pb.fp_rset = rset;
     h->fused_ok = fused_ok; h->fused_pending = false; h->placed_dirty = false;
     lap("pods queued");
@@ -851,7 +877,7 @@ static int run_fused(nosplan* h) {
     CU(h, cudaEventRecord(h->ev[2], h->stream));
     flip_small_state(h);
     h->pb.slice_mode = 0; h->pb.node_lo = 0; h->pb.node_hi = h->pb.N; h->pb.whole_snapshot = 1;
-    CU(h, launch_fused(h->pb, h->fused_blocks, h->stream));
+    CU(h, launch_fused(h->pb, h->sms, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
     h->pre_done = false; h->split_run = false;
     h->launches = 1;

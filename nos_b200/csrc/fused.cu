@@ -12,18 +12,24 @@
 // compact units below) the kernel reports it and the host runs the classic sequence k_prepass -> k_tracker_init ->
 // k_plan_parallel -> ... on the untouched inputs; nothing the fused kernel wrote survives that.
 //
-// Mapping.  8 lanes per node (lane = GPU of the node), 4 nodes per warp, 16 per CTA; all group-level votes and reductions
-// use the 8-lane mask.  reference -> here:
-//   mig.GPU.UpdateGeometryFor (pkg/gpu/mig/gpu.go:158-212)   each lane walks the allowed geometries of ITS GPU: SWAR
-//        "row >= used" on 4 profiles per word, score = dp4a(row - used, lacking mask); strict > in table order
-//   mig.Node.AddPod / GPU.AddPod (mig/node.go:201-210, gpu.go:233-247)   capacity per run = sum over lanes of free[p] / q,
-//        first-fit over the GPUs by an 8-lane exclusive prefix, once per run
-//   tryAddPod over all pods (planner.go:116-141) + NodeResourcesFit   runs of identical slice requests in NewPodSorter order;
-//        pods are (cpu, memory) int32 pairs in a padded position space with minima per 8 and per 64 pods, so that a group
-//        descends only into blocks that can still hold a fitting pod; 8 pods per step, sequential first-fit reproduced with
-//        an 8-lane prefix sum when the step's candidates do not all fit together
-//   SliceTracker.Remove (core/tracker.go:67-88)   one bit per pod POSITION (tracker keys are unique on this path), OR-ed in
-//        shared memory and flushed once per CTA; the final lacking vector is rebuilt from the bitmap by the last CTA
+// A CTA takes tiles of `tile_nodes` nodes through three phases:
+//   phase 1  8 lanes per node, lane = GPU (all lanes of a warp converged, 8-lane shuffles):
+//            mig.GPU.UpdateGeometryFor (pkg/gpu/mig/gpu.go:158-212) -- each lane walks the allowed geometries of ITS GPU: SWAR
+//            "row >= used" on 4 profiles per word, score = dp4a(row - used, lacking mask), strict > in table order;
+//            k_prepass's duties (HasFreeCapacity, totals, largest free count, accounts against GPU maps); the node's free
+//            devices per profile after the update (byte-wise sum over its GPUs) go to shared memory for phase 2
+//   phase 2  ONE THREAD PER NODE: tryAddPod over all pods (planner.go:116-141) with NodeResourcesFit.  The pods are
+//            (cpu, memory) int32 pairs in a padded position space, runs of identical slice requests in NewPodSorter order,
+//            with minima per 8 / 64 / 512 positions; the whole structure is brought into shared memory once per CTA by an
+//            asynchronous bulk copy (cp.async.bulk + mbarrier) that runs under phase 1.  A thread walks its node's runs,
+//            skips what the minima rule out and tests eight pods per step in registers; there is no cross-lane
+//            communication in this phase, so the warp's 32 nodes advance together with no vote / shuffle on the chain.
+//            Every request on this path is for ONE device, so GPU.AddPod (mig/gpu.go:233-247) is "a free device of the
+//            profile exists on the node" and the first-fit GPU choice (mig/node.go:201-210) cannot change the result:
+//            used + free per GPU is invariant under AddPod.
+//   phase 3  8 lanes per node again: partitioningState[n] (planner.go:138) for the nodes that added a pod after an update.
+// SliceTracker.Remove (core/tracker.go:67-88) is one bit per pod POSITION (tracker keys are unique on this path), OR-ed in
+// shared memory and flushed once per CTA; the final lacking vector is rebuilt from the bitmap by the last CTA.
 #include <climits>
 
 #include "nosplan_dev.cuh"
@@ -32,28 +38,328 @@ namespace nsp {
 
 namespace {
 
-constexpr int FUSED_THREADS = 128;
-constexpr int FUSED_NODES = FUSED_THREADS / 8;       // nodes per CTA step
+constexpr int FT = 640;                               // threads per CTA: one CTA per SM, 80 nodes per phase-1 step
+constexpr unsigned FULL = 0xffffffffu;
 constexpr unsigned HI = 0x80808080u;
 constexpr int CAP_NONE = 1 << 30;                     // capacity of a run without slice request
+
+struct __align__(16) NodeS {                          // phase 1 -> phase 2 -> phase 3, one per node of the tile
+    int remc, remm;                                   // remaining cpu / memory in the pods' units (-1: nothing fits)
+    int flags;                                        // 1 candidate, 2 geometry updated, 4 every pod fails the filter, 8 a pod was added
+    int pad;
+    unsigned cap[4];                                  // free devices per profile over the node's GPUs after the update, one byte each
+};
+static_assert(sizeof(NodeS) == 32, "NodeS layout");
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// global (this GPU's own memory) -> shared memory of this CTA, completion counted in bytes on the mbarrier; no multicast
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
 
 __device__ __forceinline__ unsigned byte_at(unsigned lo, unsigned hi, int p) {   // byte p (< 8) of the pair
     return ((p < 4 ? lo : hi) >> ((p & 3) * 8)) & 0xffu;
 }
 
-template <bool WIDE>       // WIDE: profiles 8..15 in use (words z, w)
-__device__ __forceinline__ void plan_nodes(const DevProblem& pb, const uint4* s_geom, const uint16_t* s_gmask, const int* s_off,
-                                           const FRun* s_runs, const unsigned long long* s_prof_runs, unsigned* s_bits,
-                                           unsigned long long* s_D, int* s_maxfree, unsigned long long* s_cnt, int* s_flags) {
-    const int tid = threadIdx.x, lane = tid & 31, grp = lane >> 3, j = lane & 7;
-    const unsigned gmask = 0xffu << (grp * 8);
-    const int gsh = grp * 8;
+struct Acc {                                          // what a thread accumulates over all its tiles
+    long long D0 = 0, D1 = 0;                         // sum(alloc - requested) of slice columns j and j + 8
+    uint4 mf = make_uint4(0, 0, 0, 0);                // byte-wise max of the free counts seen
+    unsigned flags = 0;
+    long long place = 0, evals = 0;
+    int visited = 0;
+};
+
+// ---- phase 1 for one node: lane j of the 8-lane group = GPU j.  Executed by whole warps (converged).
+template <bool WIDE>
+__device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool node_on, int j, int gsh, const uint4* s_geom,
+                                            const uint16_t* s_gmask, const int* s_off, const unsigned (&Lw)[4], int n_req,
+                                            NodeS* ns, unsigned* gs, Acc& a, unsigned long long* hdr_bar) {
     const int G = pb.G, K = pb.K, R = pb.R;
     const bool fit = pb.filter_mode == NOSPLAN_FILTER_RESOURCES_FIT;
-    const bool reject_all = pb.filter_mode == NOSPLAN_FILTER_REJECT_ALL;
+    int ng = 0;
+    uint4 used = make_uint4(0, 0, 0, 0), fre = used;
+    unsigned um = 0, fm = 0;
+    int model = 0;
+    long long a0 = 0, r0 = 0, a1 = 0, r1 = 0;
+    long long ac = 0, am = 0, ae = 0, rc = 0, rm = 0, re = 0;
+    int allowed_pods = 0, npods = 0;
+    if (node_on) {
+        const int ng_raw = pb.node_gpu_count[i];
+        const long long* al = pb.node_alloc + (size_t)i * R;
+        const long long* rq = pb.node_req + (size_t)i * R;
+        if (j == 0) {
+            ac = al[0]; am = al[1]; ae = al[2]; rc = rq[0]; rm = rq[1]; re = rq[2];
+            allowed_pods = pb.node_allowed_pods[i]; npods = pb.node_num_pods[i];
+        }
+        if (j < K) { a0 = al[3 + j]; r0 = rq[3 + j]; }
+        if (WIDE && j + 8 < K) { a1 = al[3 + 8 + j]; r1 = rq[3 + 8 + j]; }
+        if (j < G) {                                   // the row exists whatever the node's GPU count: one round trip, masked below
+            const int x = i * G + j;
+            used = pb.gpu_used[x]; fre = pb.gpu_free[x];
+            um = pb.gpu_umask[x]; fm = pb.gpu_fmask[x];
+            model = pb.gpu_model[x];
+        }
+        ng = min(max(ng_raw, 0), G);
+        if (j >= ng) { used = make_uint4(0, 0, 0, 0); fre = used; um = fm = 0; }
+        model = min(max(model, 0), max(pb.n_models - 1, 0));
+    }
+    const bool has = j < ng;
+    // ---- k_prepass duties: totals, largest free count, node accounts against the GPU maps
+    a.D0 += a0 - r0; a.D1 += a1 - r1;
+    if (((used.x | used.y | fre.x | fre.y | (WIDE ? (used.z | used.w | fre.z | fre.w) : 0u)) & 0xe0e0e0e0u) != 0) a.flags |= FREJ_COUNTS;
+    // a count without its key would make the plan's key mask depend on which GPU takes a pod: left to the classic kernels
+    {
+        unsigned nzu = nz_nibble(used.x) | (nz_nibble(used.y) << 4), nzf = nz_nibble(fre.x) | (nz_nibble(fre.y) << 4);
+        if (WIDE) { nzu |= (nz_nibble(used.z) << 8) | (nz_nibble(used.w) << 12); nzf |= (nz_nibble(fre.z) << 8) | (nz_nibble(fre.w) << 12); }
+        if ((nzu & ~um) | (nzf & ~fm)) a.flags |= FREJ_COUNTS;
+    }
+    a.mf.x = __vmaxu4(a.mf.x, fre.x); a.mf.y = __vmaxu4(a.mf.y, fre.y);
+    if (WIDE) { a.mf.z = __vmaxu4(a.mf.z, fre.z); a.mf.w = __vmaxu4(a.mf.w, fre.w); }
+    {
+        unsigned fx = fre.x, fy = fre.y, ux = used.x, uy = used.y, fz = fre.z, fw = fre.w, uz = used.z, uw = used.w;
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {              // byte-wise sums over the node's GPUs (counts <= 31: no carry)
+            fx += __shfl_xor_sync(FULL, fx, o); fy += __shfl_xor_sync(FULL, fy, o);
+            ux += __shfl_xor_sync(FULL, ux, o); uy += __shfl_xor_sync(FULL, uy, o);
+            if (WIDE) {
+                fz += __shfl_xor_sync(FULL, fz, o); fw += __shfl_xor_sync(FULL, fw, o);
+                uz += __shfl_xor_sync(FULL, uz, o); uw += __shfl_xor_sync(FULL, uw, o);
+            }
+        }
+        bool bad = false;
+        if (j < K) { const long long sf = byte_at(fx, fy, j), su = byte_at(ux, uy, j); bad = (a0 - r0 < sf) || (r0 > su); }
+        if (WIDE && j + 8 < K) { const long long sf = byte_at(fz, fw, j), su = byte_at(uz, uw, j); bad |= (a1 - r1 < sf) || (r1 > su); }
+        if (bad) a.flags |= FREJ_ACCOUNTS;
+    }
+    // ---- mig.GPU.UpdateGeometryFor for this lane's GPU + AllowsGeometry(current) for HasFreeCapacity
+    if (hdr_bar) mbar_wait(hdr_bar, 0);               // the tables arrive by bulk copy, under the loads above
+    const uint4 cnt0 = make_uint4(used.x + fre.x, used.y + fre.y, used.z + fre.z, used.w + fre.w);
+    const unsigned gm0 = um | fm;
+    unsigned best = 0;
+    bool allowed = false;
+    int nrows = 0, row0 = 0;
+    if (has && pb.n_models > 0) { row0 = s_off[model]; nrows = s_off[model + 1] - row0; }
+    for (int r = 0; r < nrows; ++r) {
+        const uint4 row = s_geom[row0 + r];
+        const unsigned tx = (row.x | HI) - used.x, ty = (row.y | HI) - used.y;   // bit 7 of a byte: row >= used
+        unsigned ok = tx & ty;
+        unsigned sc = __dp4a(tx & ~HI, Lw[0], 0u);
+        sc = __dp4a(ty & ~HI, Lw[1], sc);
+        bool same = row.x == cnt0.x && row.y == cnt0.y;
+        if (WIDE) {
+            const unsigned tz = (row.z | HI) - used.z, tw = (row.w | HI) - used.w;
+            ok &= tz & tw;
+            sc = __dp4a(tz & ~HI, Lw[2], sc);
+            sc = __dp4a(tw & ~HI, Lw[3], sc);
+            same = same && row.z == cnt0.z && row.w == cnt0.w;
+        }
+        if ((ok & HI) == HI && sc) best = max(best, (sc << 5) | (unsigned)(31 - r));   // strict > in table order
+        allowed |= same && s_gmask[row0 + r] == gm0;
+    }
+    const bool has_free = has && (fm != 0 || !allowed);
+    const bool candidate = (__ballot_sync(FULL, has_free) >> gsh & 0xffu) != 0;
+    int br = 0xffff;
+    if (candidate && best) {
+        br = row0 + 31 - (int)(best & 31u);
+        const uint4 row = s_geom[br];
+        fre = make_uint4(row.x - used.x, row.y - used.y, WIDE ? row.z - used.z : 0u, WIDE ? row.w - used.w : 0u);   // zero kept (:141)
+    }
+    const bool upd = (__ballot_sync(FULL, br != 0xffff) >> gsh & 0xffu) != 0;
+    // free devices per profile on the node after the update
+    unsigned cx = has ? fre.x : 0u, cy = has ? fre.y : 0u, cz = (WIDE && has) ? fre.z : 0u, cw = (WIDE && has) ? fre.w : 0u;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        cx += __shfl_xor_sync(FULL, cx, o); cy += __shfl_xor_sync(FULL, cy, o);
+        if (WIDE) { cz += __shfl_xor_sync(FULL, cz, o); cw += __shfl_xor_sync(FULL, cw, o); }
+    }
+    if (candidate && has) a.evals += (long long)nrows * n_req;
+    if (node_on) {
+        // partitioningState[n] as it was (planner.go:72); phase 3 overwrites the rows of nodes that add a pod after an update
+        if (has) {
+            const int x = i * G + j;
+            pb.out_count[x] = cnt0;
+            pb.out_mask[x] = (uint16_t)gm0;
+        }
+        *gs = (unsigned)br | (um << 16);
+        if (j == 0) {
+            NodeS s;
+            s.remc = s.remm = F_REM_MAX;
+            bool all_fail = pb.filter_mode == NOSPLAN_FILTER_REJECT_ALL;
+            if (fit) {
+                const long long dc = ac - rc, dm = am - rm;
+                const long long qc = dc >> pb.fp_cpu_shift, qm = dm >> pb.fp_mem_shift;
+                if (candidate && (qc > F_REM_MAX || qm > F_REM_MAX)) a.flags |= FREJ_REM;
+                s.remc = dc < 0 ? -1 : (int)min(qc, (long long)F_REM_MAX);
+                s.remm = dm < 0 ? -1 : (int)min(qm, (long long)F_REM_MAX);
+                if (ae - re < 0) s.remc = -1;               // no pod requests ephemeral storage: 0 <= negative fails for every pod
+                all_fail = all_fail || !(npods + 1 <= allowed_pods);
+            }
+            s.flags = (candidate ? 1 : 0) | (upd ? 2 : 0) | (all_fail ? 4 : 0);
+            s.pad = 0;
+            s.cap[0] = cx; s.cap[1] = cy; s.cap[2] = cz; s.cap[3] = cw;
+            *ns = s;
+            if (candidate) ++a.visited;
+        }
+    }
+}
+
+// ---- phase 2: lane = node; the warp's 32 nodes take the runs in lockstep (the run record is warp-uniform), each lane walks
+//      its own way through the run.  Returns the number of pods added on this lane's node.
+// loads of the pod structure: shared-memory instructions when the whole blob is staged; otherwise generic loads (the upper
+// levels may sit in shared memory while the lower ones are read from global memory through L1)
+template <bool SMEM>
+__device__ __forceinline__ uint2 ld_pair(const uint2* p) {
+    if (SMEM) {
+        uint2 v;
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_u32(p)));
+        return v;
+    }
+    return *p;
+}
+template <bool SMEM>
+__device__ __forceinline__ uint4 ld_quad(const uint4* p) {
+    if (SMEM) {
+        uint4 v;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+        return v;
+    }
+    return *p;
+}
+
+template <bool WIDE, bool FIT, bool SMEM>
+__device__ __forceinline__ int warp_phase2(const NodeS& s, bool on, const FRun* s_runs,
+                                           const unsigned long long* s_prof_runs, const uint2* L3, const uint2* L2, const uint2* L1,
+                                           const uint2* PODS, unsigned* s_bits) {
+    const bool active = on && (s.flags & 5) == 1;
+    int remc = -1, remm = -1;
+    unsigned cv0 = 0, cv1 = 0, cv2 = 0, cv3 = 0;
+    unsigned long long live = 0;
+    if (active) {
+        remc = s.remc; remm = s.remm;
+        cv0 = s.cap[0]; cv1 = s.cap[1]; cv2 = s.cap[2]; cv3 = s.cap[3];
+        unsigned feas = nz_nibble(cv0) | (nz_nibble(cv1) << 4);
+        if (WIDE) feas |= (nz_nibble(cv2) << 8) | (nz_nibble(cv3) << 12);
+        live = s_prof_runs[KP];
+        for (unsigned f = feas; f; f &= f - 1) live |= s_prof_runs[__ffs(f) - 1];
+    }
+    // runs some node of the warp can still use, in NewPodSorter order
+    unsigned long long todo = ((unsigned long long)__reduce_or_sync(FULL, (unsigned)(live >> 32)) << 32) | __reduce_or_sync(FULL, (unsigned)live);
+    int added = 0;
+    while (todo) {
+        const int ri = __ffsll((long long)todo) - 1;
+        todo &= todo - 1;
+        const FRun fr = s_runs[ri];                                        // the same record for every lane
+        const int p = fr.p;
+        int cap = 0;
+        if ((live >> ri & 1) && fr.min_c <= remc && fr.min_m <= remm) {    // else: no pod of the run can pass on this node (any more)
+            if (p >= 0) {                                                  // GPU.AddPod feasibility: a free device of the profile (q == 1)
+                const unsigned w = p < 8 ? (p < 4 ? cv0 : cv1) : (p < 12 ? cv2 : cv3);
+                cap = (int)((w >> ((p & 3) * 8)) & 0xffu);
+            } else cap = CAP_NONE;
+        }
+        if (!__any_sync(FULL, cap > 0)) continue;
+        const int cap0 = cap;
+        int cur = fr.pos0 >> 3;
+        const int end = cur + fr.nblk * 8;
+        for (;;) {
+            // next group of eight pods this node has to look at: skip what the minima rule out
+            int sub = -1;
+            while (cap > 0 && cur < end) {
+                if ((cur & 63) == 0) {
+                    const uint2 m = ld_pair<SMEM>(L3 + (cur >> 6));
+                    if ((int)m.x > remc || (int)m.y > remm) { cur += 64; continue; }
+                }
+                if ((cur & 7) == 0) {
+                    const uint2 m = ld_pair<SMEM>(L2 + (cur >> 3));
+                    if ((int)m.x > remc || (int)m.y > remm) { cur += 8; continue; }
+                }
+                const uint2 m = ld_pair<SMEM>(L1 + cur);
+                if ((int)m.x > remc || (int)m.y > remm) { ++cur; continue; }
+                sub = cur++;
+                break;
+            }
+            if (!__any_sync(FULL, sub >= 0)) break;
+            if (sub >= 0) {
+                // eight pods in order; a pod that does not fit now never fits later on this node: the state only gets tighter
+                const uint4* pp = reinterpret_cast<const uint4*>(PODS + (size_t)sub * 8);
+                const uint4 q0 = ld_quad<SMEM>(pp), q1 = ld_quad<SMEM>(pp + 1), q2 = ld_quad<SMEM>(pp + 2), q3 = ld_quad<SMEM>(pp + 3);
+                unsigned bits = 0;
+#define NOS_TRY(C, M, B)                                                              \
+    if (cap > 0 && (int)(C) <= remc && (int)(M) <= remm) {                             \
+        if (FIT) { remc -= (int)(C); remm -= (int)(M); }                               \
+        --cap; bits |= 1u << (B);                                                      \
+    }
+                NOS_TRY(q0.x, q0.y, 0) NOS_TRY(q0.z, q0.w, 1) NOS_TRY(q1.x, q1.y, 2) NOS_TRY(q1.z, q1.w, 3)
+                NOS_TRY(q2.x, q2.y, 4) NOS_TRY(q2.z, q2.w, 5) NOS_TRY(q3.x, q3.y, 6) NOS_TRY(q3.z, q3.w, 7)
+#undef NOS_TRY
+                if (bits) atomicOr(&s_bits[sub >> 2], bits << ((sub & 3) * 8));            // tracker.Remove
+            }
+        }
+        const int n = cap0 - cap;                                          // devices of the run's profile taken on this node
+        if (n > 0) {
+            added += n;
+            if (p >= 0) {
+                const unsigned d = (unsigned)n << ((p & 3) * 8);
+                if (p < 4) cv0 -= d; else if (p < 8) cv1 -= d; else if (p < 12) cv2 -= d; else cv3 -= d;
+            }
+        }
+    }
+    return added;
+}
+
+}  // namespace
+
+struct FusedLaunch { int tile_nodes, stage_bytes; };
+
+template <bool WIDE>
+__device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaunch fl, unsigned char* s_dyn, unsigned long long (*s_wD)[KP],
+                                           unsigned (*s_wmf)[4], unsigned long long (*s_wcnt)[4], int* s_flags, unsigned long long* s_bar) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, j = lane & 7, gsh = (lane >> 3) * 8;
+    const int n_words = pb.fp_pad_pods >> 5;
+    // dynamic shared memory: [placed bitmap][staged prefix of the blob: tables, runs, minima, pods][per-node state][per-GPU state]
+    unsigned* s_bits = reinterpret_cast<unsigned*>(s_dyn);
+    const size_t o_blob = ((size_t)n_words * 4 + 15) & ~(size_t)15;
+    const unsigned char* s_blob = s_dyn + o_blob;
+    NodeS* s_node = reinterpret_cast<NodeS*>(s_dyn + o_blob + (size_t)fl.stage_bytes);
+    unsigned* s_gpu = reinterpret_cast<unsigned*>(s_node + fl.tile_nodes);
+    const uint4* s_geom = reinterpret_cast<const uint4*>(s_blob);
+    const uint16_t* s_gmask = reinterpret_cast<const uint16_t*>(s_blob + pb.fp_off[0]);
+    const int* s_off = reinterpret_cast<const int*>(s_blob + pb.fp_off[1]);
+    const FRun* s_runs = reinterpret_cast<const FRun*>(s_blob + pb.fp_off[2]);
+    const unsigned long long* s_prof_runs = reinterpret_cast<const unsigned long long*>(s_blob + pb.fp_off[3]);
+    // levels of the pod structure: from shared memory where staged, else from global memory (L1-cached)
+    auto level = [&](int k) {
+        const unsigned char* base = pb.fp_off[k + 1] <= fl.stage_bytes ? s_blob : pb.fp_blob;
+        return reinterpret_cast<const uint2*>(base + pb.fp_off[k]);
+    };
+    const uint2* L3 = level(4); const uint2* L2 = level(5); const uint2* L1 = level(6); const uint2* PODS = level(7);
+    const bool smem_all = pb.fp_off[8] <= fl.stage_bytes, fit = pb.filter_mode == NOSPLAN_FILTER_RESOURCES_FIT;
+
     const int n_req = __popc(pb.fp_rset);
-    // lacking profiles as a 0/1 byte per profile (the dp4a weights)
-    unsigned Lw[4];
+    unsigned Lw[4];                                   // lacking profiles as a 0/1 byte per profile (the dp4a weights)
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
         unsigned v = 0;
@@ -61,300 +367,138 @@ __device__ __forceinline__ void plan_nodes(const DevProblem& pb, const uint4* s_
         for (int b = 0; b < 4; ++b) v |= ((pb.fp_rset >> (w * 4 + b)) & 1u) << (8 * b);
         Lw[w] = v;
     }
-    long long accD0 = 0, accD1 = 0;                   // sum(alloc - requested) of slice columns j and j + 8
-    uint4 mf = make_uint4(0, 0, 0, 0);                // byte-wise max of the free counts this lane has seen
-    unsigned flags = 0;
-    long long st_place = 0, st_evals = 0;
-    int st_visited = 0;
-
-    const int n_tiles = (pb.node_hi - pb.node_lo + FUSED_NODES - 1) / FUSED_NODES;
+    Acc a;
+    const int n_nodes = pb.node_hi - pb.node_lo;
+    const int n_tiles = (n_nodes + fl.tile_nodes - 1) / fl.tile_nodes;
+    bool hdr_ready = false, staged_ready = fl.stage_bytes <= pb.fp_off[4];
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int i = pb.node_lo + tile * FUSED_NODES + (tid >> 3);
-        const bool node_on = i < pb.node_hi;
-        // ---- the node's rows: every load is issued before the first use
-        int ng = 0, allowed_pods = 0, npods = 0;
-        uint4 used = make_uint4(0, 0, 0, 0), fre = used;
-        unsigned um = 0, fm = 0;
-        int model = 0;
-        long long ac = 0, am = 0, ae = 0, rc = 0, rm = 0, re = 0, a0 = 0, r0 = 0, a1 = 0, r1 = 0;
-        if (node_on) {
-            ng = min(max(pb.node_gpu_count[i], 0), G);
-            allowed_pods = pb.node_allowed_pods[i]; npods = pb.node_num_pods[i];
-            const long long* al = pb.node_alloc + (size_t)i * R;
-            const long long* rq = pb.node_req + (size_t)i * R;
-            ac = al[0]; am = al[1]; ae = al[2]; rc = rq[0]; rm = rq[1]; re = rq[2];
-            if (j < K) { a0 = al[3 + j]; r0 = rq[3 + j]; }
-            if (WIDE && j + 8 < K) { a1 = al[3 + 8 + j]; r1 = rq[3 + 8 + j]; }
-            if (j < ng) {
-                const int x = i * G + j;
-                used = pb.gpu_used[x]; fre = pb.gpu_free[x];
-                um = pb.gpu_umask[x]; fm = pb.gpu_fmask[x];
-                model = min(max(pb.gpu_model[x], 0), max(pb.n_models - 1, 0));
-            }
+        const int base = pb.node_lo + tile * fl.tile_nodes;
+        const int count = min(fl.tile_nodes, pb.node_hi - base);
+        // ---- phase 1
+        for (int g0 = 0; g0 < count * 8; g0 += FT) {
+            const int g = g0 + tid, nl = g >> 3;
+            const bool on = nl < count;
+            node_phase1<WIDE>(pb, base + nl, on, j, gsh, s_geom, s_gmask, s_off, Lw, n_req, &s_node[on ? nl : 0], &s_gpu[on ? g : 0], a,
+                              hdr_ready ? nullptr : &s_bar[0]);
+            hdr_ready = true;
         }
-        const bool has = j < ng;
-        // ---- k_prepass duties: totals, largest free count, node accounts against the GPU maps
-        accD0 += a0 - r0; accD1 += a1 - r1;
-        if (((used.x | used.y | fre.x | fre.y | (WIDE ? (used.z | used.w | fre.z | fre.w) : 0u)) & 0xe0e0e0e0u) != 0) flags |= FREJ_COUNTS;
-        mf.x = __vmaxu4(mf.x, fre.x); mf.y = __vmaxu4(mf.y, fre.y);
-        if (WIDE) { mf.z = __vmaxu4(mf.z, fre.z); mf.w = __vmaxu4(mf.w, fre.w); }
+        __syncthreads();
+        if (!staged_ready) { mbar_wait(&s_bar[1], 0); staged_ready = true; }
+        // ---- phase 2: node nl on lane nl / NW of warp nl % NW -- a small tile spreads over all warps, a few lanes each, so
+        //      that a warp's chain is the longest of a few nodes, not of 32
         {
-            unsigned fx = fre.x, fy = fre.y, ux = used.x, uy = used.y, fz = fre.z, fw = fre.w, uz = used.z, uw = used.w;
-#pragma unroll
-            for (int o = 1; o < 8; o <<= 1) {          // byte-wise sums over the node's GPUs (counts <= 31: no carry)
-                fx += __shfl_xor_sync(gmask, fx, o); fy += __shfl_xor_sync(gmask, fy, o);
-                ux += __shfl_xor_sync(gmask, ux, o); uy += __shfl_xor_sync(gmask, uy, o);
-                if (WIDE) {
-                    fz += __shfl_xor_sync(gmask, fz, o); fw += __shfl_xor_sync(gmask, fw, o);
-                    uz += __shfl_xor_sync(gmask, uz, o); uw += __shfl_xor_sync(gmask, uw, o);
-                }
-            }
-            bool bad = false;
-            if (j < K) { const long long sf = byte_at(fx, fy, j), su = byte_at(ux, uy, j); bad = (a0 - r0 < sf) || (r0 > su); }
-            if (WIDE && j + 8 < K) { const long long sf = byte_at(fz, fw, j), su = byte_at(uz, uw, j); bad |= (a1 - r1 < sf) || (r1 > su); }
-            if (bad) flags |= FREJ_ACCOUNTS;
-        }
-        // ---- mig.GPU.UpdateGeometryFor for this lane's GPU + AllowsGeometry(current) for HasFreeCapacity
-        const uint4 cnt0 = make_uint4(used.x + fre.x, used.y + fre.y, used.z + fre.z, used.w + fre.w);
-        const unsigned gm0 = um | fm;
-        unsigned best = 0;
-        bool allowed = false;
-        int nrows = 0, row0 = 0;
-        if (has && pb.n_models > 0) { row0 = s_off[model]; nrows = s_off[model + 1] - row0; }
-        for (int r = 0; r < nrows; ++r) {
-            const uint4 row = s_geom[row0 + r];
-            const unsigned tx = (row.x | HI) - used.x, ty = (row.y | HI) - used.y;   // bit 7 of a byte: row >= used
-            unsigned ok = tx & ty;
-            unsigned sc = __dp4a(tx & ~HI, Lw[0], 0u);
-            sc = __dp4a(ty & ~HI, Lw[1], sc);
-            bool same = row.x == cnt0.x && row.y == cnt0.y;
-            if (WIDE) {
-                const unsigned tz = (row.z | HI) - used.z, tw = (row.w | HI) - used.w;
-                ok &= tz & tw;
-                sc = __dp4a(tz & ~HI, Lw[2], sc);
-                sc = __dp4a(tw & ~HI, Lw[3], sc);
-                same = same && row.z == cnt0.z && row.w == cnt0.w;
-            }
-            if ((ok & HI) == HI && sc) best = max(best, (sc << 5) | (unsigned)(31 - r));   // strict > in table order
-            allowed |= same && s_gmask[row0 + r] == gm0;
-        }
-        const bool has_free = has && (fm != 0 || !allowed);
-        const bool candidate = (__ballot_sync(gmask, has_free) >> gsh & 0xffu) != 0;
-        bool upd_g = false;
-        if (candidate && best) {
-            const int br = row0 + 31 - (int)(best & 31u);
-            const uint4 row = s_geom[br];
-            fre = make_uint4(row.x - used.x, row.y - used.y, WIDE ? row.z - used.z : 0u, WIDE ? row.w - used.w : 0u);   // zero kept (:141)
-            fm = s_gmask[br];
-            upd_g = true;
-        }
-        const bool upd = (__ballot_sync(gmask, upd_g) >> gsh & 0xffu) != 0;
-        int added = 0;
-        if (candidate) {
-            if (j == 0) ++st_visited;
-            if (has) st_evals += (long long)nrows * n_req;
-            // ---- NodeResourcesFit state in the pods' units
-            int remc = F_REM_MAX, remm = F_REM_MAX;
-            bool all_fail = reject_all;
-            if (fit) {
-                const long long dc = ac - rc, dm = am - rm;
-                const long long qc = dc >> pb.fp_cpu_shift, qm = dm >> pb.fp_mem_shift;
-                if (qc > F_REM_MAX || qm > F_REM_MAX) flags |= FREJ_REM;
-                remc = dc < 0 ? -1 : (int)min(qc, (long long)F_REM_MAX);
-                remm = dm < 0 ? -1 : (int)min(qm, (long long)F_REM_MAX);
-                if (ae - re < 0) remc = -1;                 // no pod requests ephemeral storage: 0 <= negative fails for every pod
-                all_fail = all_fail || !(npods + 1 <= allowed_pods);
-            }
-            // profiles with a free device somewhere on the node
-            unsigned nzm = nz_nibble(fre.x) | (nz_nibble(fre.y) << 4);
-            if (WIDE) nzm |= (nz_nibble(fre.z) << 8) | (nz_nibble(fre.w) << 12);
-            const unsigned feas = __reduce_or_sync(gmask, has ? nzm : 0u);
-            unsigned long long live = 0;
-            if (!all_fail) {
-                live = s_prof_runs[KP];
-                for (unsigned f = feas; f; f &= f - 1) live |= s_prof_runs[__ffs(f) - 1];
-            }
-            // ---- the pod loop, run by run
-            while (live) {
-                const int ri = __ffsll((long long)live) - 1;
-                live &= live - 1;
-                const FRun fr = s_runs[ri];
-                if (fr.min_c > remc || fr.min_m > remm) continue;          // no pod of the run can pass any more
-                const int p = fr.p, q = fr.q;
-                int cg = 0, cap = CAP_NONE;
-                if (p >= 0) {
-                    const unsigned w = p < 8 ? (p < 4 ? fre.x : fre.y) : (p < 12 ? fre.z : fre.w);
-                    const int f0 = (int)((w >> ((p & 3) * 8)) & 0xffu);
-                    cg = has ? (q == 1 ? f0 : f0 / q) : 0;                 // GPU.AddPod feasibility
-                    cap = (int)__reduce_add_sync(gmask, (unsigned)cg);
-                    if (cap <= 0) continue;
-                }
-                const int cap0 = cap;
-                const int blk0 = fr.pos0 >> 6;
-                for (int b0 = 0; b0 < fr.nblk && cap > 0; b0 += 8) {
-                    uint2 l2 = make_uint2(F_NONE, F_NONE);
-                    if (b0 + j < fr.nblk) l2 = __ldg(&pb.fp_l2[blk0 + b0 + j]);
-                    unsigned m2 = __ballot_sync(gmask, (int)l2.x <= remc && (int)l2.y <= remm) >> gsh & 0xffu;
-                    while (m2 && cap > 0) {
-                        const int blk = blk0 + b0 + __ffs(m2) - 1;
-                        m2 &= m2 - 1;
-                        const uint2 l1 = __ldg(&pb.fp_l1[blk * 8 + j]);
-                        unsigned m1 = __ballot_sync(gmask, (int)l1.x <= remc && (int)l1.y <= remm) >> gsh & 0xffu;
-                        while (m1 && cap > 0) {
-                            const int sub = blk * 8 + __ffs(m1) - 1;
-                            m1 &= m1 - 1;
-                            const uint2 pod = __ldg(&pb.fp_pod[sub * 8 + j]);
-                            const int c = (int)pod.x, m = (int)pod.y;
-                            unsigned acc_bits = 0;
-                            int from = 0;
-                            for (;;) {
-                                // a pod that does not fit now never fits later on this node: the state only gets tighter
-                                const bool valid = j >= from && c <= remc && m <= remm;
-                                const unsigned vm = __ballot_sync(gmask, valid) >> gsh & 0xffu;
-                                if (!vm) break;
-                                const bool cand = valid && __popc(vm & ((1u << j) - 1)) < cap;
-                                unsigned accm = __ballot_sync(gmask, cand) >> gsh & 0xffu;
-                                int next_from = 8;
-                                if (fit) {
-                                    int sc = (int)__reduce_add_sync(gmask, cand ? (unsigned)c : 0u);
-                                    int sm = (int)__reduce_add_sync(gmask, cand ? (unsigned)m : 0u);
-                                    if (sc > remc || sm > remm) {
-                                        // the candidates do not all fit together: sequential first-fit by prefix sums; the first
-                                        // pod that fails under "all earlier candidates placed" splits the step
-                                        int ec = cand ? c : 0, em = cand ? m : 0;
-#pragma unroll
-                                        for (int o = 1; o < 8; o <<= 1) {
-                                            const int tc = __shfl_up_sync(gmask, ec, o, 8), tm = __shfl_up_sync(gmask, em, o, 8);
-                                            if (j >= o) { ec += tc; em += tm; }
-                                        }
-                                        ec -= cand ? c : 0; em -= cand ? m : 0;
-                                        const unsigned failm = __ballot_sync(gmask, cand && (c > remc - ec || m > remm - em)) >> gsh & 0xffu;
-                                        const int ff = __ffs(failm) - 1;                 // exists: the totals did not fit
-                                        sc = __shfl_sync(gmask, ec, ff, 8); sm = __shfl_sync(gmask, em, ff, 8);
-                                        accm &= (1u << ff) - 1;
-                                        next_from = ff + 1;
-                                    }
-                                    if (accm) { remc -= sc; remm -= sm; }
-                                }
-                                cap -= __popc(accm);
-                                acc_bits |= accm;
-                                if (next_from >= 8 || cap <= 0) break;
-                                from = next_from;
-                            }
-                            if (acc_bits && j == 0) atomicOr(&s_bits[sub >> 2], acc_bits << ((sub & 3) * 8));   // tracker.Remove
-                        }
-                    }
-                }
-                const int n = cap0 - cap;
-                if (n > 0) {
-                    added += n;
-                    if (p >= 0) {                                          // first fit over the GPUs in order (mig/node.go:201-210)
-                        int ex = cg;
-#pragma unroll
-                        for (int o = 1; o < 8; o <<= 1) { const int t = __shfl_up_sync(gmask, ex, o, 8); if (j >= o) ex += t; }
-                        ex -= cg;
-                        const int take = max(0, min(cg, n - ex));
-                        if (take > 0) {
-                            const unsigned d = (unsigned)(take * q) << ((p & 3) * 8);
-                            if (p < 4) { fre.x -= d; used.x += d; } else if (p < 8) { fre.y -= d; used.y += d; }
-                            else if (p < 12) { fre.z -= d; used.z += d; } else { fre.w -= d; used.w += d; }
-                            um |= 1u << p;
-                        }
-                    }
-                }
-            }
-            if (j == 0) st_place += added;
-        }
-        // ---- partitioningState[n] (planner.go:72,138): the node's geometry after the update if a pod was added, else as it was
-        if (has) {
-            const int x = i * G + j;
-            if (added > 0 && upd) {
-                pb.out_count[x] = make_uint4(used.x + fre.x, used.y + fre.y, WIDE ? used.z + fre.z : 0u, WIDE ? used.w + fre.w : 0u);
-                pb.out_mask[x] = (uint16_t)(um | fm);
-            } else {
-                pb.out_count[x] = cnt0;
-                pb.out_mask[x] = (uint16_t)gm0;
+            constexpr int NW = FT / 32;
+            const int nl = lane * NW + warp;
+            const bool on = nl < count;
+            if (__any_sync(FULL, on)) {
+                const NodeS& ns = s_node[on ? nl : 0];
+                int added;
+                if (fit) added = smem_all ? warp_phase2<WIDE, true, true>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits)
+                                          : warp_phase2<WIDE, true, false>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits);
+                else added = smem_all ? warp_phase2<WIDE, false, true>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits)
+                                      : warp_phase2<WIDE, false, false>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits);
+                if (on && added > 0) { s_node[nl].flags |= 8; a.place += added; }
             }
         }
+        __syncthreads();
+        // ---- phase 3: the geometry after the update, for nodes that added a pod (planner.go:138)
+        for (int g = tid; g < count * 8; g += FT) {
+            const int nl = g >> 3, jj = g & 7;
+            if ((s_node[nl].flags & 10) != 10) continue;
+            const unsigned v = s_gpu[g];
+            const int br = (int)(v & 0xffffu);
+            if (br == 0xffff) continue;
+            const int x = (base + nl) * pb.G + jj;
+            pb.out_count[x] = s_geom[br];
+            pb.out_mask[x] = (uint16_t)((v >> 16) | s_gmask[br]);
+        }
+        __syncthreads();
     }
+    if (!hdr_ready) mbar_wait(&s_bar[0], 0);          // a CTA without tiles still has to see its copies land before it exits
+    if (!staged_ready) mbar_wait(&s_bar[1], 0);
 
-    // ---- CTA-level reduction of what the lanes accumulated
-    if (flags) atomicOr(&s_flags[0], (int)flags);
+    // ---- reduction of what the threads accumulated: warp shuffles, one shared-memory slot per warp
+    if (__any_sync(FULL, a.flags != 0)) { const unsigned f = __reduce_or_sync(FULL, a.flags); if (lane == 0) atomicOr(&s_flags[0], (int)f); }
 #pragma unroll
     for (int o = 8; o < 32; o <<= 1) {                 // lanes with the same j across the warp's four groups
-        accD0 += __shfl_xor_sync(0xffffffffu, accD0, o); accD1 += __shfl_xor_sync(0xffffffffu, accD1, o);
+        a.D0 += __shfl_xor_sync(FULL, a.D0, o); a.D1 += __shfl_xor_sync(FULL, a.D1, o);
     }
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        mf.x = __vmaxu4(mf.x, __shfl_xor_sync(0xffffffffu, mf.x, o)); mf.y = __vmaxu4(mf.y, __shfl_xor_sync(0xffffffffu, mf.y, o));
-        if (WIDE) { mf.z = __vmaxu4(mf.z, __shfl_xor_sync(0xffffffffu, mf.z, o)); mf.w = __vmaxu4(mf.w, __shfl_xor_sync(0xffffffffu, mf.w, o)); }
-        st_place += __shfl_xor_sync(0xffffffffu, st_place, o); st_evals += __shfl_xor_sync(0xffffffffu, st_evals, o);
-        st_visited += __shfl_xor_sync(0xffffffffu, st_visited, o);
+        a.mf.x = __vmaxu4(a.mf.x, __shfl_xor_sync(FULL, a.mf.x, o)); a.mf.y = __vmaxu4(a.mf.y, __shfl_xor_sync(FULL, a.mf.y, o));
+        if (WIDE) { a.mf.z = __vmaxu4(a.mf.z, __shfl_xor_sync(FULL, a.mf.z, o)); a.mf.w = __vmaxu4(a.mf.w, __shfl_xor_sync(FULL, a.mf.w, o)); }
+        a.place += __shfl_xor_sync(FULL, a.place, o); a.evals += __shfl_xor_sync(FULL, a.evals, o);
+        a.visited += __shfl_xor_sync(FULL, a.visited, o);
     }
-    if (lane < 8) {
-        if (accD0) atomicAdd(&s_D[lane], (unsigned long long)accD0);
-        if (WIDE && accD1) atomicAdd(&s_D[8 + lane], (unsigned long long)accD1);
-    }
-    if (lane < KP) { const int v = (int)byte_of(mf, lane); if (v) atomicMax(&s_maxfree[lane], v); }
+    if (lane < 8) { s_wD[warp][lane] = (unsigned long long)a.D0; s_wD[warp][8 + lane] = (unsigned long long)a.D1; }
     if (lane == 0) {
-        atomicAdd(&s_cnt[0], (unsigned long long)st_place); atomicAdd(&s_cnt[1], (unsigned long long)st_evals);
-        atomicAdd(&s_cnt[2], (unsigned long long)st_visited);
+        s_wmf[warp][0] = a.mf.x; s_wmf[warp][1] = a.mf.y; s_wmf[warp][2] = a.mf.z; s_wmf[warp][3] = a.mf.w;
+        s_wcnt[warp][0] = (unsigned long long)a.place; s_wcnt[warp][1] = (unsigned long long)a.evals; s_wcnt[warp][2] = (unsigned long long)a.visited;
+    }
+    __syncthreads();
+    // ---- this CTA's contribution to the grid-wide state
+    constexpr int NW = FT / 32;
+    if (tid < KP) {
+        unsigned long long d = 0;
+        int mfree = 0;
+        for (int w = 0; w < NW; ++w) {
+            d += s_wD[w][tid];
+            mfree = max(mfree, (int)((s_wmf[w][tid >> 2] >> ((tid & 3) * 8)) & 0xffu));
+        }
+        if (d) atomicAdd(reinterpret_cast<unsigned long long*>(&pb.tot[tid]), d);
+        if (mfree) atomicMax(&pb.maxfree[tid], mfree);
+    } else if (tid >= 32 && tid < 35) {
+        unsigned long long c = 0;
+        for (int w = 0; w < NW; ++w) c += s_wcnt[w][tid - 32];
+        if (c) atomicAdd(&pb.acc[tid - 32], c);
+    } else if (tid == 64 && s_flags[0]) atomicOr(&pb.wave[5], s_flags[0]);
+    for (int w = tid; w < n_words; w += FT) {
+        const unsigned b = s_bits[w];
+        if (b) atomicOr(&pb.placed[w], b);
     }
 }
 
-}  // namespace
-
-__global__ void __launch_bounds__(FUSED_THREADS, 6) k_plan_fused(DevProblem pb) {
-    extern __shared__ __align__(16) unsigned s_bits[];              // one bit per padded pod position: placed by this CTA
-    __shared__ uint4 s_geom[MAX_ROWS];
-    __shared__ uint16_t s_gmask[MAX_ROWS];
-    __shared__ int s_off[MAX_MODELS + 1];
-    __shared__ FRun s_runs[FRUN_MAX];
-    __shared__ unsigned long long s_prof_runs[KP + 1];
-    __shared__ unsigned long long s_D[KP];
-    __shared__ int s_maxfree[KP];
-    __shared__ unsigned long long s_cnt[4];
+__global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch fl) {
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    __shared__ unsigned long long s_wD[FT / 32][KP];
+    __shared__ unsigned s_wmf[FT / 32][4];
+    __shared__ unsigned long long s_wcnt[FT / 32][4];
     __shared__ int s_flags[1];
     __shared__ long long s_l0[KP], s_dec[KP];
     __shared__ long long s_e[FRUN_MAX];
+    __shared__ __align__(8) unsigned long long s_bar[2];
     const int tid = threadIdx.x;
     const int n_words = pb.fp_pad_pods >> 5;
 
-    for (int r = tid; r < pb.n_rows; r += FUSED_THREADS) { const uint4 row = pb.geom[r]; s_geom[r] = row; s_gmask[r] = nz_mask(row); }
-    for (int m = tid; m <= pb.n_models; m += FUSED_THREADS) s_off[m] = pb.model_off[m];
-    for (int r = tid; r < pb.fp_n_runs; r += FUSED_THREADS) s_runs[r] = pb.fp_runs[r];
-    for (int w = tid; w < n_words; w += FUSED_THREADS) s_bits[w] = 0;
-    if (tid <= KP) s_prof_runs[tid] = 0;
-    if (tid < KP) { s_D[tid] = 0; s_maxfree[tid] = 0; }
-    if (tid < 4) s_cnt[tid] = 0;
+    // tables, runs and the pod structure (this GPU's own memory) on their way into shared memory: the header lands first
+    // and is waited for in front of the geometry loop, the rest in front of the pod phase
+    if (tid == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        unsigned char* dst = s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15);
+        const unsigned hdr = (unsigned)min(fl.stage_bytes, pb.fp_off[4]), all = (unsigned)fl.stage_bytes;
+        mbar_expect_tx(&s_bar[0], hdr);
+        bulk_g2s(dst, pb.fp_blob, hdr, &s_bar[0]);
+        if (all > hdr) {
+            mbar_expect_tx(&s_bar[1], all - hdr);
+            for (unsigned o = hdr; o < all; o += 32768u) bulk_g2s(dst + o, pb.fp_blob + o, min(32768u, all - o), &s_bar[1]);
+        }
+    }
+    for (int w = tid; w < n_words; w += FT) reinterpret_cast<unsigned*>(s_dyn)[w] = 0;
     if (tid == 0) s_flags[0] = 0;
     // the next run's copy of the small per-run state (see DevProblem::zero_next)
-    if (blockIdx.x == 0) for (int x = tid; x < pb.zero_next_n8; x += FUSED_THREADS) pb.zero_next[x] = 0;
-    __syncthreads();
-    for (int r = tid; r < pb.fp_n_runs; r += FUSED_THREADS) atomicOr(&s_prof_runs[s_runs[r].p >= 0 ? s_runs[r].p : KP], 1ull << r);
+    if (blockIdx.x == 0) for (int x = tid; x < pb.zero_next_n8; x += FT) pb.zero_next[x] = 0;
     __syncthreads();
 
-    if (pb.K > 8) plan_nodes<true>(pb, s_geom, s_gmask, s_off, s_runs, s_prof_runs, s_bits, s_D, s_maxfree, s_cnt, s_flags);
-    else plan_nodes<false>(pb, s_geom, s_gmask, s_off, s_runs, s_prof_runs, s_bits, s_D, s_maxfree, s_cnt, s_flags);
-    __syncthreads();
-
-    // ---- this CTA's contribution to the grid-wide state
-    if (tid < KP) {
-        if (s_D[tid]) atomicAdd(reinterpret_cast<unsigned long long*>(&pb.tot[tid]), s_D[tid]);
-        if (s_maxfree[tid]) atomicMax(&pb.maxfree[tid], s_maxfree[tid]);
-    }
-    if (tid < 3 && s_cnt[tid]) atomicAdd(&pb.acc[tid], s_cnt[tid]);
-    if (tid == 0 && s_flags[0]) atomicOr(&pb.wave[5], s_flags[0]);
-    for (int w = tid; w < n_words; w += FUSED_THREADS) {
-        const unsigned b = s_bits[w];
-        if (b && (b & ~__ldcg(&pb.placed[w]))) atomicOr(&pb.placed[w], b);
-    }
+    if (pb.K > 8) fused_body<true>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_bar);
+    else fused_body<false>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_bar);
 
     // ---- the CTA that finishes last verifies the hypothesis on the final state (what k_plan_sweep does for the classic path)
     if (!last_block_done(&pb.next_node[2])) return;
+    const FRun* s_runs = reinterpret_cast<const FRun*>(s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15) + pb.fp_off[2]);
     if (tid < KP) { s_l0[tid] = 0; s_dec[tid] = 0; }
     __syncthreads();
-    for (int r = tid; r < pb.fp_n_runs; r += FUSED_THREADS) {
+    for (int r = tid; r < pb.fp_n_runs; r += FT) {
         const FRun fr = s_runs[r];
         long long e = 0;
         if (fr.p >= 0) {                                              // NewSliceTracker (core/tracker.go:34-57): lacking = request - available
@@ -365,10 +509,10 @@ __global__ void __launch_bounds__(FUSED_THREADS, 6) k_plan_fused(DevProblem pb) 
         s_e[r] = e;
     }
     __syncthreads();
-    for (int w = tid; w < n_words; w += FUSED_THREADS) {              // a 32-position word lies inside one run (runs are 64-aligned)
+    for (int w = tid; w < n_words; w += FT) {                         // a 32-position word lies inside one run (runs are 64-aligned)
         const int c = __popc(__ldcg(&pb.placed[w]));
-        pb.placed[w] = 0;                                             // clean for the next fused run of this problem
         if (!c) continue;
+        pb.placed[w] = 0;                                             // clean for the next fused run of this problem
         int r = 0;
         while (r + 1 < pb.fp_n_runs && s_runs[r + 1].pos0 <= (w << 5)) ++r;
         if (s_runs[r].p >= 0 && s_e[r]) atomicAdd(reinterpret_cast<unsigned long long*>(&s_dec[s_runs[r].p]), (unsigned long long)(c * s_e[r]));
@@ -388,9 +532,9 @@ __global__ void __launch_bounds__(FUSED_THREADS, 6) k_plan_fused(DevProblem pb) 
             }
         }
         int rej = __ldcg(&pb.wave[5]);
-        if (!__all_sync(0xffffffffu, ok)) rej |= FREJ_HYPOTHESIS;
-        const int lack_start = __popc(__ballot_sync(0xffffffffu, lane < KP && l0 > 0));
-        const int lack_end = __popc(__ballot_sync(0xffffffffu, lane < KP && le > 0));
+        if (!__all_sync(FULL, ok)) rej |= FREJ_HYPOTHESIS;
+        const int lack_start = __popc(__ballot_sync(FULL, lane < KP && l0 > 0));
+        const int lack_end = __popc(__ballot_sync(FULL, lane < KP && le > 0));
         if (lane == 0) {
             DevStats* st = pb.stats;
             const long long vis = (long long)__ldcg(&pb.acc[2]);
@@ -407,24 +551,33 @@ __global__ void __launch_bounds__(FUSED_THREADS, 6) k_plan_fused(DevProblem pb) 
     }
 }
 
-size_t fused_dyn_smem(const DevProblem& pb) { return (size_t)(pb.fp_pad_pods >> 5) * 4 + 16; }
-constexpr size_t FUSED_DYN_MAX = 32 * 1024;
-int fused_max_pad_pods() { return (int)((FUSED_DYN_MAX - 16) / 4) * 32; }
+// ---- launch geometry: how much of the blob is staged, how many nodes a CTA takes at a time
+constexpr size_t FUSED_SMEM = 200 * 1024;            // dynamic shared memory of the one CTA per SM
+int fused_max_pad_pods() { return 1 << 20; }
 
-cudaError_t fused_prepare_device(int* blocks_per_sm) {
-    cudaError_t e = cudaFuncSetAttribute(k_plan_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FUSED_DYN_MAX);
-    if (e != cudaSuccess) return e;
-    int per_sm = 4;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_plan_fused, FUSED_THREADS, 4096) != cudaSuccess || per_sm < 1) per_sm = 4;
-    *blocks_per_sm = per_sm;
-    return cudaSuccess;
+cudaError_t fused_prepare_device() {
+    return cudaFuncSetAttribute(k_plan_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FUSED_SMEM);
 }
 
-cudaError_t launch_fused(const DevProblem& pb, int max_blocks, cudaStream_t st) {
-    int blocks = (pb.node_hi - pb.node_lo + FUSED_NODES - 1) / FUSED_NODES;
-    if (blocks > max_blocks) blocks = max_blocks;
+cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st) {
+    const int n_nodes = pb.node_hi - pb.node_lo;
+    const size_t bits = (((size_t)(pb.fp_pad_pods >> 5) * 4) + 15) & ~(size_t)15;
+    auto need = [&](int stage_bytes, int tile_nodes) { return bits + (size_t)stage_bytes + (size_t)tile_nodes * (sizeof(NodeS) + 32); };
+    // one resident wave when the nodes allow it: the smallest tile (multiple of 8, at least 64 nodes) that covers them
+    FusedLaunch fl;
+    int tile = (n_nodes + sms - 1) / sms;
+    tile = (tile + 7) & ~7;
+    if (tile < 64) tile = 64;
+    if (tile > FT) tile = FT;
+    fl.tile_nodes = tile;
+    // the header (tables, runs) always; then whole levels of the pod structure, top down, while they fit
+    fl.stage_bytes = pb.fp_off[4];
+    for (int l = 5; l <= 8; ++l) if (need(pb.fp_off[l], tile) <= FUSED_SMEM) fl.stage_bytes = pb.fp_off[l];
+    if (need(fl.stage_bytes, tile) > FUSED_SMEM) return cudaErrorInvalidValue;
+    int blocks = (n_nodes + tile - 1) / tile;
+    if (blocks > sms) blocks = sms;
     if (blocks < 1) blocks = 1;
-    k_plan_fused<<<blocks, FUSED_THREADS, fused_dyn_smem(pb), st>>>(pb);
+    k_plan_fused<<<blocks, FT, need(fl.stage_bytes, tile), st>>>(pb, fl);
     return cudaGetLastError();
 }
 

@@ -35,10 +35,10 @@ struct nosplan {
     std::vector<uint8_t> v_key_seen;
     // single-launch plan (fused.cu): applicable to the uploaded problem; its verdict has not been read back yet (the host
     // runs the classic kernel sequence if the kernel rejected its own hypothesis); the classic sequence left key-indexed
-    // bits in `placed`; grid size of one resident wave on this handle's device
+    // bits in `placed`; SM count of this handle's device
     bool fused_ok = false, fused_pending = false, placed_dirty = false;
     bool last_fused = false; int fused_reject = 0; float ms_rejected = 0.f;   // what the last run was; why / how long a rejected attempt took
-    int fused_blocks = 148 * 4;
+    int sms = 148;
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
     size_t h2d_bytes = 0;

@@ -31,8 +31,11 @@ static_assert(sizeof(RunRec) == 48, "RunRec layout");
 
 // ---- single-launch Plan() (fused.cu) ---------------------------------------------------------------------------------
 // Pods of the fused path live in a PADDED position space: every run starts at a multiple of 64 and is padded to a multiple
-// of 64 with ineligible dummies, so that the 8-ary tree of minima over the positions (8 pods, 64 pods) never straddles a
-// run.  A pod is its two NodeResourcesFit costs as non-negative int32 in common power-of-two units (cpu milli >> cpu_shift,
+// of 64 with ineligible dummies, so that the minima over 8 and over 64 positions never straddle a run (the ones over 512
+// positions may: a minimum over more pods only skips less).  Everything the fused kernel reads besides the node rows is ONE
+// blob -- [geometry rows | their key masks | row range per model | run records | runs per profile] as a header, then
+// (cpu, memory) int32 pairs [minima per 512 | minima per 64 | minima per 8 | pods], every section a multiple of 16 bytes --
+// so that a prefix of it is copied into shared memory in one piece.  A pod is its two NodeResourcesFit costs as non-negative int32 in common power-of-two units (cpu milli >> cpu_shift,
 // memory bytes >> mem_shift; exact because every pod request is a multiple of the unit); F_NONE marks a pod that can never be
 // placed (PreFilter verdict false, or padding) and, in the minima, a group without an eligible pod.
 constexpr int FRUN_MAX = 64;                 // runs the fused kernel keeps in shared memory
@@ -166,7 +169,9 @@ struct DevProblem {
     int32_t* wave;                   // [8]  [0] k_plan_sweep hands the plan to k_plan_waves  [1],[2] first node of the wave that changes
                                      //      the lacking vector (by wave parity)  [3] candidate nodes  [4] waves run
     // single-launch Plan() (fused.cu): padded pod costs, their minima per 8 and per 64 positions, runs, units
-    const uint2* fp_pod; const uint2* fp_l1; const uint2* fp_l2; const FRun* fp_runs;
+    const unsigned char* fp_blob;
+    int fp_off[9];                   // byte offsets in the blob: key masks, model ranges, runs, runs per profile (geometry rows
+                                     // at 0), minima per 512 / 64 / 8, pods, total
     int fp_n_runs, fp_pad_pods, fp_cpu_shift, fp_mem_shift;
     unsigned fp_rset;                // profiles some pod requests: the lacking set the fused kernel speculates on
     int whole_snapshot;              // the node-parallel pass covers every node on this rank (no exchange needed)

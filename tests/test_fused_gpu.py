@@ -72,6 +72,7 @@ def test_fused_with_prefilter_vector_quantities_and_slice_less_pods(eng):
         _, _, st = check(eng, s, p, pre, fm, f"quantities + slice-less fm={fm}")
         assert st["fused"] == 1 or st["fused_reject"] == 0
     # tight nodes: little cpu and memory left, pod counts at the limit on some
+    p.scalar_qty[:] = 1
     s.node_requested[:, 0] = rng.integers(0, 64001, s.n_nodes)
     s.node_requested[:, 1] = rng.integers(0, 513, s.n_nodes) << 30
     s.node_num_pods[:] = rng.integers(100, 112, s.n_nodes)
@@ -164,6 +165,15 @@ def test_fused_at_the_compiled_in_profile_limit(eng):
     assert snap.n_profiles == 16
     for fm in (pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT):
         _, _, st = check(eng, snap, pods, None, fm, f"wide fm={fm}")
+        assert st["fused"] == 1
+
+
+def test_fused_with_a_pod_list_larger_than_shared_memory(eng):
+    """40 000 pods: the pod pairs (320 KB) stay in global memory, only the minima are staged in shared memory; 150 000 pods:
+    the per-8 minima stay in global memory too."""
+    for n_pods in (40000, 150000):
+        s, p = synth.mig_cluster(300, 8, n_pods, seed=91)
+        _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, f"{n_pods} pods")
         assert st["fused"] == 1
 
 
