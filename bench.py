@@ -3,15 +3,17 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
 
-A "step" is one Plan() over the packed snapshot: prepass + tracker-init + sweep kernels (nosplan_run).
-`value` is measured with the snapshot already resident in HBM (CUDA events on the engine's stream, L2 flushed
-between iterations); `e2e` is the same Plan() through nosplan_plan with HOST buffers, i.e. including the H2D
-copy of the snapshot and the D2H copy of the plan, by wall clock.  One JSON line is printed by rank 0.
+A "step" is one Plan() over the packed snapshot (nosplan_run: one kernel, k_plan_fused, where the single-launch plan
+applies).  `value` is measured with the snapshot already resident in HBM (CUDA events on the engine's stream, L2 flushed
+between iterations; median step, slowest rank per step); `e2e` is the same Plan() through nosplan_plan with HOST
+buffers, i.e. including the H2D copy of the snapshot and the D2H copy of the plan, by wall clock.  After the timed loops
+every rank compares its rows and the job-wide counters with the oracle's plan of the full snapshot: the line carries
+"parity" and the exit code is 1 on a mismatch.  One JSON line is printed by rank 0.
 
---impl reference times the reference's own algorithm on the host cores: the reference is Go and there is no Go
-toolchain on the box, so it is the faithful C++ port (oracle/nos_oracle.cpp, NOS_ORACLE_FAITHFUL: re-sums every
-node per gate check and clones every node per fork, like core/snapshot.go) on a bounded sub-snapshot of the
-same recipe.  Plan() is single-goroutine in the reference, so it runs on one core.
+--impl reference times the reference's own algorithm on the host cores on the SAME workload: the reference is Go and
+there is no Go toolchain on the box, so it is the C++ port (oracle/nos_oracle.cpp) -- the incremental mode at full size
+(same plan bit for bit; one core, Plan() is single-goroutine), with the faithful O(N^2 P) mode on a sub-snapshot and 8
+independent problems on 8 threads beside it.
 """
 import argparse
 import json
@@ -118,39 +120,108 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def core_config(args, world):
+    """The keys both arms share: they name the workload, nothing else."""
+    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
+    nodes = n_full * world if args.scaling == "weak" else n_full
+    return {"workload": args.workload, "kind": kind, "nodes": nodes, "gpus_per_node": gg, "pods": p_full,
+            "regime": "saturating", "filter": "resources_fit", "scaling": args.scaling}
+
+
+def job_workload(args, world):
+    """The snapshot and pods of the whole job: weak scaling keeps the workload's node count PER GPU, strong scaling in total."""
+    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
+    return make_workload(args.workload, nodes=n_full * world if args.scaling == "weak" else n_full)
+
+
+def cpu_reference(snap, pods, steps, budget_s, threads=1):
+    """The reference's Plan() on the host: the incremental port (oracle/nos_oracle.cpp: running totals instead of the
+    reference's re-summing and cloning -- the same plan, bit for bit, at a cost one core can pay at full size).
+    -> (times [s], stats of the last run).  threads > 1: that many INDEPENDENT problems at once (Plan() has no exact parallel
+    form: core/planner.go:92-150 is one goroutine), each thread times its own."""
+    from support import oracle_lib as ol
+    times, st = [], None
+    t_end = time.perf_counter() + budget_s
+    if threads == 1:
+        for _ in range(steps):
+            _, _, st, sec = ol.plan(snap, pods, None, FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+            times.append(sec)
+            if time.perf_counter() > t_end:
+                break
+        return times, st
+    import threading
+    out = [None] * threads
+
+    def work(k):
+        out[k] = ol.plan(snap, pods, None, FILTER_RESOURCES_FIT, ol.INCREMENTAL)      # ctypes releases the GIL
+
+    t0 = time.perf_counter()
+    ths = [threading.Thread(target=work, args=(k,)) for k in range(threads)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    return [time.perf_counter() - t0], out[0][2]
+
+
+def faithful_sample(args, reps):
+    """The reference's own asymptotics (re-sum every node per gate, clone every node per fork: O(N^2 P)) cannot run the full
+    workload (hours); a 450-node sub-snapshot of the same recipe, and the N^2 P extrapolation, are reported beside the
+    full-size figure."""
+    from support import oracle_lib as ol
+    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
+    n = min(n_full, 450)
+    p = max(10, int(round(n * p_full / n_full)))
+    snap, pods = make_workload(args.workload, nodes=n, pods=p)
+    secs, st = [], None
+    for _ in range(reps):
+        _, _, st, sec = ol.plan(snap, pods, None, FILTER_RESOURCES_FIT, ol.FAITHFUL)
+        secs.append(sec)
+    p50 = float(np.median(secs))
+    per = p50 / (float(n) * n * p)
+    return {"nodes": n, "pods": p, "repetitions": reps, "seconds_p50": p50, "candidates_per_s": st["candidates"] / p50,
+            "fitted_seconds_per_N2P": per, "extrapolated_seconds_full_size": per * float(n_full) ** 2 * p_full,
+            "note": "faithful C++ port of core.Planner.Plan (same asymptotics as the Go planner) on a sub-snapshot of the same recipe; "
+                    "cost per candidate grows linearly with N"}
+
+
 def run_reference(args):
-    """The reference algorithm (faithful port) on the host: bounded sub-snapshot of the same recipe."""
+    """The reference arm: the reference's algorithm on the host cores, on the SAME workload as our arm (at N GPUs: the
+    N-times-larger snapshot of the weak-scaling job).  The reference is Go and there is no Go toolchain on the box, so this is
+    the C++ port (oracle/): `value` is the incremental port at full size on one core (Plan() is single-goroutine); the
+    faithful O(N^2 P) port on a sub-snapshot and 8 independent problems on 8 threads are extra keys."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import __graft_entry__ as g
     if not os.path.exists(os.path.join(ROOT, "oracle", "libnosoracle.so")):
         g.build()
-    from support import oracle_lib as ol
-    kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
-    budget = 90.0 / max(1, args.steps + args.warmup)
-    n = int(max(100, min(1000, (budget / 1.0e-7) ** (1.0 / 3.0))))       # faithful cost ~ 2e-8 s * N^2 * P, P = N * p_full/n_full
-    n = min(n, n_full)
-    p = max(10, int(round(n * p_full / n_full)))
-    snap, pods = make_workload(args.workload, nodes=n, pods=p)
-    times, cands = [], 0
-    for i in range(args.warmup + args.steps):
-        _, _, st, sec = ol.plan(snap, pods, None, FILTER_RESOURCES_FIT, ol.FAITHFUL)
-        if i >= args.warmup:
-            times.append(sec)
-            cands = st["candidates"]
-    total = sum(times)
-    value = cands * len(times) / total if total > 0 else 0.0
-    sample = (f"faithful C++ port of core.Planner.Plan (O(N^2 P): re-sum all nodes per gate, clone all nodes per fork) on a "
-              f"{n}-node x {gg}-GPU, {p}-pod sub-snapshot of the {args.workload} recipe; single thread (Plan() is single-goroutine; "
-              f"Go toolchain absent so the Go planner itself cannot run)")
+    world = max(1, args.gpus)
+    snap, pods = job_workload(args, world)
+    steps = max(1, args.steps)
+    for _ in range(min(1, args.warmup)):
+        cpu_reference(snap, pods, 1, 1e9)
+    times, st = cpu_reference(snap, pods, steps, budget_s=150.0)
+    cands = int(st["candidates"])
+    p50 = float(np.median(times))
+    value = cands / p50
+    cores = os.cpu_count() or 1
+    nthreads = min(8, cores)
+    tt, _ = cpu_reference(snap, pods, 1, 1e9, threads=nthreads)
+    sample = (f"incremental C++ port of core.Planner.Plan (same plan as the reference, bit for bit; running totals instead of re-summing "
+              f"and cloning) on the FULL workload, {len(times)} of {steps} requested repetitions (wall-time cap 150 s), one thread "
+              f"(Plan() is single-goroutine; the Go planner itself cannot run: no Go toolchain on the box)")
     line = {
         "impl": "reference", "metric": "planner_candidates_per_sec", "value": value, "unit": "candidates/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / max(1, len(times)),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": {"workload": args.workload, "nodes": n_full, "gpus_per_node": gg, "pods": p_full, "regime": "saturating",
-                   "filter": "resources_fit", "sample_nodes": n, "sample_pods": p},
-        "cpu_baseline": {"value": value, "unit": "candidates/s", "cores": 1, "kind": "port", "sample": sample},
+        "n_gpus": args.gpus, "steps": len(times), "warmup": min(1, args.warmup), "ms_per_step": 1e3 * p50,
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": core_config(args, world),
+        "plan_p50_ms": 1e3 * p50, "plan_mean_ms": 1e3 * float(np.mean(times)), "repetitions": len(times),
+        "cpu_baseline": {"value": value, "unit": "candidates/s", "cores": 1, "kind": "port", "sample": sample,
+                         "host_cores": cores,
+                         "independent_problems_on_threads": {"threads": nthreads, "value": nthreads * cands / tt[0], "seconds": tt[0],
+                                                             "note": "the same problem planned by every thread at once, labelled replicas: Plan() has no exact parallel form"},
+                         "faithful_sub_snapshot": faithful_sample(args, 5)},
         "e2e": {"value": value, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -172,22 +243,24 @@ def run_ours(args):
     if not os.path.exists(g.LIB):
         g.build()
 
-    # N > 1: ONE Plan() over a snapshot of world x nodes (per-GPU node count fixed: weak scaling) in slice mode: every rank
-    # holds ONLY its own slice of the name-ordered node list (H2D, k_prepass, node-parallel pass and plan rows are per-rank
-    # work); two NCCL all-gathers per Plan(): 256 B of cluster totals per rank, then counters + placed-key bitmap.
+    # N > 1: ONE Plan() over the job's snapshot in slice mode -- every rank holds ONLY its own slice of the name-ordered node list
+    # (H2D, the planning kernel and the plan rows are per-rank work); one merged exchange per Plan() (see nosplan_run_sliced).
     kind, n_full, gg, p_full, _ = WORKLOADS[args.workload]
-    snap, pods = make_workload(args.workload, nodes=n_full * world)
+    full_snap, pods = job_workload(args, world)
+    snap = full_snap
+    lo, hi = 0, full_snap.n_nodes
     if world > 1:
         from nos_b200 import sharded
-        full_snap = snap
-        snap = sharded.slice_snapshot(full_snap, rank * n_full, (rank + 1) * n_full, pad_to=n_full)
+        chunk = (full_snap.n_nodes + world - 1) // world
+        lo, hi = sharded.shard_range(full_snap.n_nodes, rank, world)
+        snap = sharded.slice_snapshot(full_snap, lo, hi, pad_to=chunk)
     eng = capi.Engine(local)
     eng.upload(snap, pods, None, FILTER_RESOURCES_FIT)
     dev = torch.device("cuda", local)
     ext = torch.cuda.ExternalStream(eng.stream(), device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
     sharded_run = world > 1
-    if sharded_run:                          # collectives are issued by the library itself (one grouped NCCL launch per Plan)
+    if sharded_run:                          # the exchange is issued by the library itself (peer-memory mailboxes, or one NCCL all-gather)
         uid = [eng.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         eng.shard_init(rank, world, uid[0])
@@ -210,8 +283,8 @@ def run_ours(args):
         else:
             eng.run()
         e.record(ext)
-        _, _, st = eng.download()            # synchronises; outside the timed pair of events
-        return s.elapsed_time(e), st
+        cnt, msk, st = eng.download()        # synchronises; outside the timed pair of events
+        return s.elapsed_time(e), st, cnt, msk
 
     for _ in range(max(3, args.warmup)):
         one_step(False)
@@ -223,16 +296,16 @@ def run_ours(args):
     step_ms, sweep_ms, par_ms, st = [], [], [], None
     eng.set_kernel_events(False)             # the timed steps run without the library's per-kernel events ...
     for _ in range(args.steps):
-        ms, st = one_step(True)
+        ms, st, cnt, msk = one_step(True)
         step_ms.append(ms)
     sync_all()
     eng.set_kernel_events(True)              # ... which are then taken on the same steps again, for the roofline line
     for _ in range(max(5, args.steps // 2)):
-        _, kst = one_step(True)
+        _, kst, _, _ = one_step(True)
         sweep_ms.append(kst["ms_sweep"]); par_ms.append(kst["ms_parallel"])
     st = dict(st, ms_prepass=kst["ms_prepass"], ms_tracker=kst["ms_tracker"])
     sync_all()
-    # ---- end to end: host buffers in, host buffers out, wall clock (H2D + kernels [+ collectives] + D2H inside)
+    # ---- end to end: host buffers in, host buffers out, wall clock (H2D + kernels [+ exchange] + D2H inside)
     hsnap = capi.pin_snapshot(snap)      # the caller's snapshot arrays and plan buffers sit in page-locked host memory
     hout = capi.pinned_partitioning(snap)
 
@@ -248,6 +321,8 @@ def run_ours(args):
     sync_all()
     e2e_s = []
     for _ in range(args.steps):
+        if sharded_run:
+            sync_all()
         t0 = time.perf_counter()
         est = e2e_once()
         e2e_s.append(time.perf_counter() - t0)
@@ -264,42 +339,60 @@ def run_ours(args):
         sync_all()
     clocks = sampler.stop() if sampler else None
 
-    total_ms = float(sum(step_ms))
-    e2e_total = float(sum(e2e_s))
-    cands = int(st["candidates"])
-    if world > 1:
-        t = torch.tensor([total_ms, e2e_total], dtype=torch.float64, device=f"cuda:{local}")
+    # ---- parity, outside every timed region: this rank's rows and the job-wide counters against the oracle's plan of the
+    #      FULL snapshot (the name-order sweep of core/planner.go:92-150 that the slices must reproduce)
+    from support import oracle_lib as ol
+    t0 = time.perf_counter()
+    ocnt, omsk, ost, osec = ol.plan(full_snap, pods, None, FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+    n_rows = (hi - lo) * gg
+    same = bool(np.array_equal(cnt[:n_rows], ocnt[lo * gg:hi * gg]) and np.array_equal(msk[:n_rows], omsk[lo * gg:hi * gg]))
+    same = same and all(int(st[k]) == int(ost[k]) for k in ("candidates", "visited_nodes", "placements", "geometry_evals", "lacking_at_end"))
+    step = np.asarray(step_ms, np.float64)
+    e2e = np.asarray(e2e_s, np.float64)
+    if world > 1:                          # per step: the slowest rank; parity: every rank
+        t = torch.tensor(np.concatenate([step, e2e, [0.0 if same else 1.0]]), dtype=torch.float64, device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, e2e_total = float(t[0]), float(t[1])
-    cands_all = cands                      # visited nodes (all ranks) x pods: already the whole job
+        t = t.cpu().numpy()
+        step, e2e, same = t[:len(step)], t[len(step):len(step) + len(e2e)], t[-1] == 0.0
+    cands = int(st["candidates"])          # visited nodes (all ranks) x pods: already the whole job
     if rank != 0:
         eng.close()
         if world > 1:
             dist.destroy_process_group()
-        return
+        sys.exit(0 if same else 1)
 
-    value = cands_all * args.steps / (total_ms / 1e3)
-    e2e_value = cands_all * args.steps / e2e_total
+    p50_ms, mean_ms = float(np.median(step)), float(np.mean(step))
+    value = cands / (p50_ms / 1e3)
+    e2e_p50 = float(np.median(e2e))
+    e2e_value = cands / e2e_p50
     peak, peak_src = measured_peak()
     b_plan = algorithmic_bytes(snap, pods)       # per GPU: its own node rows and the (replicated) pods
     sweep_avg_ms = float(np.mean(sweep_ms))
-    # dominant kernel: the node-parallel pass when it produced the plan, else the sequential sweep
+    # dominant kernel: the single-launch plan, else the node-parallel pass when it produced the plan, else the sequential sweep
     fused = bool(st.get("fused"))
     dom_name = "k_plan_fused" if fused else ("k_plan_parallel" if st["path"] == 1 else "k_plan_sweep")
     dom_ms = float(np.mean(par_ms)) if st["path"] == 1 else sweep_avg_ms
     achieved = b_plan / (dom_ms / 1e3) / 1e9
+    if world == 1:
+        par = "single GPU"
+    else:
+        par = (f"node-sliced x{world}: each GPU holds {hi - lo} nodes of the name-ordered list, pods replicated; "
+               + ("ONE exchange per Plan(): the last CTA of k_plan_fused stores the rank's block (totals, counters, placed bitmap) into every "
+                  "rank's mailbox and k_fused_verify folds them" if fused else "two exchanges per Plan() (cluster totals, then counters + placed-key bitmap)")
+               + f"; plan rows stay on their rank; transport: {eng.shard_transport()}")
     line = {
         "metric": "planner_candidates_per_sec", "value": value, "unit": "candidates/s",
-        "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-        "config": {"workload": args.workload, "kind": kind, "nodes": n_full * world, "gpus_per_node": gg, "pods": p_full,
-                   "regime": "saturating", "filter": "resources_fit",
-                   "parallelism": "single GPU" if world == 1 else f"node-sliced x{world}: each GPU holds {n_full} nodes; two NCCL all-gathers "
-                                  f"per Plan() (256 B of cluster totals, then {eng.shard_exchange_bytes()} B of counters + placed-key bitmap per rank); "
-                                  f"plan rows stay on their rank; transport: {eng.shard_transport()}",
-                   "l2": "flushed between iterations (256 MiB device write)", "candidates_per_plan": cands,
-                   "visited_nodes": int(st["visited_nodes"]), "placements": int(st["placements"])},
-        "plan_p50_ms": float(np.median(step_ms)), "plan_p95_ms": float(np.percentile(step_ms, 95)),
+        "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": p50_ms,
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": core_config(args, world),
+        "parity": "identical" if same else "MISMATCH",
+        "parity_note": "rows of this rank's nodes and the job-wide counters against the oracle's plan of the full snapshot, every rank, after the timed loops",
+        "timing": {"value_from": "median step (p50), device time, max over ranks per step", "plan_p50_ms": p50_ms, "plan_mean_ms": mean_ms,
+                   "plan_p95_ms": float(np.percentile(step, 95)), "plan_max_ms": float(np.max(step)),
+                   "l2": "flushed between iterations (256 MiB device write)"},
+        "details": {"parallelism": par, "candidates_per_plan": cands, "visited_nodes": int(st["visited_nodes"]), "placements": int(st["placements"]),
+                    "nodes_per_gpu": hi - lo},
+        "plan_p50_ms": p50_ms, "plan_p95_ms": float(np.percentile(step, 95)),
         "kernel_ms": {"prepass": float(st["ms_prepass"]), "tracker_init" if world == 1 else "totals_exchange+tracker_init": float(st["ms_tracker"]),
                       "parallel": float(np.mean(par_ms)),
                       "verify_or_sweep" if world == 1 else "exchange+verify": sweep_avg_ms,
@@ -307,39 +400,36 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "kernel": dom_name, "kernel_ms": dom_ms, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": recorded_traffic(dom_name) if (args.workload == "mig-10k" and world == 1) else None, "algorithmic_bytes": b_plan, "peak_source": peak_src},
         "e2e": {"value": e2e_value, "unit": "candidates/s", "h2d_bytes_per_step": int(est["h2d_bytes"]),
-                "d2h_bytes_per_step": int(est["d2h_bytes"]), "ms_per_step": 1e3 * e2e_total / args.steps,
+                "d2h_bytes_per_step": int(est["d2h_bytes"]), "ms_per_step": 1e3 * e2e_p50, "ms_mean": 1e3 * float(np.mean(e2e)),
                 "ms_h2d": float(est["ms_h2d"]), "ms_kernels": float(est["ms_kernels"]), "ms_d2h": float(est["ms_d2h"]),
                 "host_buffers": "caller's node arrays and plan buffers page-locked and DMA'd in place; pod arrays (pageable) re-ordered by "
-                                "NewPodSorter into pinned staging while the node DMA and k_prepass run"
+                                "NewPodSorter into pinned staging while the node DMA runs"
                                 if world == 1 else "per rank: its slice's node arrays and plan rows page-locked and DMA'd in place"},
         "gpu_launches": int(st["kernel_launches"]) * args.steps,
         "clocks": clocks,
     }
     if res_s:
         line["e2e_resident_snapshot"] = {
-            "value": cands_all * len(res_s) / float(sum(res_s)), "unit": "candidates/s", "ms_per_step": 1e3 * float(np.mean(res_s)),
+            "value": cands / float(np.median(res_s)), "unit": "candidates/s", "ms_per_step": 1e3 * float(np.median(res_s)),
             "h2d_bytes_per_step": int(rst["h2d_bytes"]), "d2h_bytes_per_step": int(rst["d2h_bytes"]),
             "note": "nosplan_plan_resident: node arrays kept in HBM from the previous call (the device-side twin of the reference's "
                     "ClusterState cache), pods in and plan out through host buffers; reported next to e2e, not instead of it"}
     if world == 1 and args.batch > 1:
         line["batched"] = batched_plans(torch, capi, eng, ext, flush, args, local)
     if world == 1 and not args.no_cpu_baseline:
-        from support import oracle_lib as ol
-        n = min(n_full, 450)
-        p = max(10, int(round(n * p_full / n_full)))
-        ssnap, spods = make_workload(args.workload, nodes=n, pods=p)
-        _, _, ost, sec = ol.plan(ssnap, spods, None, FILTER_RESOURCES_FIT, ol.FAITHFUL)
-        _, _, ist, isec = ol.plan(snap, pods, None, FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+        times, ist = cpu_reference(snap, pods, 5, budget_s=20.0)
+        ip50 = float(np.median(times))
         line["cpu_baseline"] = {
-            "value": ost["candidates"] / sec, "unit": "candidates/s", "cores": 1, "kind": "port",
-            "sample": f"faithful C++ port of the reference algorithm (O(N^2 P)) on a {n}-node x {gg}-GPU, {p}-pod sub-snapshot "
-                      f"of the same recipe, {sec:.1f} s on one core; cost per candidate grows linearly with N",
-            "incremental_full_size": {"value": ist["candidates"] / isec, "seconds": isec,
-                                      "note": "same plan via running totals (oracle incremental mode), full workload, one core"}}
+            "value": ist["candidates"] / ip50, "unit": "candidates/s", "cores": 1, "kind": "port",
+            "sample": f"incremental C++ port of the reference algorithm (same plan, bit for bit) on the full workload, p50 of {len(times)} "
+                      f"repetitions, {ip50:.2f} s each, one core (Plan() is single-goroutine)",
+            "seconds_p50": ip50, "faithful_sub_snapshot": faithful_sample(args, 5)}
     print(json.dumps(line), flush=True)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+    if not same:
+        sys.exit(1)
 
 
 def batched_plans(torch, capi, eng0, ext0, flush, args, local):
@@ -396,6 +486,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="mig-10k", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = the workload's node count per GPU (default, what the driver's scaling run uses), strong = in total")
     ap.add_argument("--batch", type=int, default=4, help="N=1 only: also time this many independent Plan() problems in flight at once (0/1 = skip)")
     args = ap.parse_args()
     if args.impl == "reference":

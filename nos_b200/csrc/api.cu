@@ -30,6 +30,8 @@ cudaError_t sweep_prepare_device();
 int sweep_max_keys();
 cudaError_t fused_prepare_device();
 cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st);
+cudaError_t launch_fused_verify(const DevProblem& pb, const void* blocks, size_t stride, int world, const PeerWait& wait, cudaStream_t st);
+size_t fused_exchange_bytes(const DevProblem& pb);
 int fused_max_pad_pods();
 }  // namespace nsp
 
@@ -563,7 +565,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
     // Node-side conditions of the single-launch plan (fused.cu); the pod-side ones follow below.  Where it can still apply,
     // k_prepass is not queued early: the fused kernel does that work itself once the pods are on the device.
-    bool fused_ok = mig && G <= 8 && N > 0 && P > 0 && !getenv("NOSPLAN_NO_FUSED");
+    bool fused_ok = mig && G <= 8 && P > 0 && !getenv("NOSPLAN_NO_FUSED");
     for (int r = 0; r < n_rows && fused_ok; ++r)
         for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p] > 31) { fused_ok = false; break; }
     if (h->in_plan && !fused_ok) { rc = run_pre(h, true); if (rc != NOSPLAN_OK) return rc; }
@@ -868,6 +870,8 @@ static int run_post(nosplan* h) {
     return NOSPLAN_OK;
 }
 
+static int run_classic(nosplan* h);
+
 // The whole Plan() as one kernel (fused.cu).  Its verdict is read back by nosplan_resolve.
 static int run_fused(nosplan* h) {
     if (h->placed_dirty) {                                   // a classic run indexed `placed` by tracker key
@@ -882,6 +886,7 @@ static int run_fused(nosplan* h) {
     h->pre_done = false; h->split_run = false;
     h->launches = 1;
     h->fused_pending = true; h->last_fused = true; h->fused_reject = 0; h->ms_rejected = 0.f;
+    h->rerun = run_classic;
     h->ran = true;
     return NOSPLAN_OK;
 }
@@ -1021,6 +1026,41 @@ int nosplan_run_sliced_fused(nosplan* h, const PeerBox& box, unsigned epoch, uns
     return NOSPLAN_OK;
 }
 
+// Slice mode as ONE kernel per rank plus one merged exchange (fused.cu): every rank plans its slice speculatively and ships
+// [totals | largest free counts | reject bits | counters | placed bitmap] once; k_fused_verify folds the W blocks and
+// verifies.  box == nullptr: the block is only assembled in d_exchange and the caller moves it (an NCCL all-gather).
+int nosplan_run_sliced_fused_begin(nosplan* h, const PeerBox* box, unsigned epoch, unsigned char* d_exchange, size_t xb) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->uploaded || !h->fused_ok) return fail(h, NOSPLAN_E_INVALID, "single-launch sliced Plan() is not applicable to the uploaded problem");
+    if (xb < fused_exchange_bytes(h->pb)) return fail(h, NOSPLAN_E_INVALID, "exchange block smaller than %zu bytes", fused_exchange_bytes(h->pb));
+    CU(h, cudaSetDevice(h->device));
+    if (h->placed_dirty) {
+        CU(h, cudaMemsetAsync(h->pb.placed, 0, 4 * (size_t)(h->pb.fp_pad_pods >> 5), h->stream));
+        h->placed_dirty = false;
+    }
+    CU(h, cudaEventRecord(h->ev[2], h->stream));
+    flip_small_state(h);
+    DevProblem pb = h->pb;
+    pb.slice_mode = 1; pb.node_lo = 0; pb.node_hi = pb.N; pb.whole_snapshot = 0;
+    pb.xf_on = 1; pb.xf_epoch = epoch; pb.xf_exchange = d_exchange; pb.xf_xb = xb;
+    if (box) pb.xf_box = *box; else { std::memset(&pb.xf_box, 0, sizeof pb.xf_box); }
+    CU(h, launch_fused(pb, h->sms, h->stream));
+    h->pb.slice_mode = 1;
+    h->pre_done = false; h->split_run = false;
+    h->launches = 1;
+    return NOSPLAN_OK;
+}
+
+int nosplan_run_sliced_fused_end(nosplan* h, const void* blocks, size_t stride, int world, const PeerWait& wait, int (*rerun)(nosplan*)) {
+    CU(h, launch_fused_verify(h->pb, blocks, stride, world, wait, h->stream));
+    CU(h, cudaEventRecord(h->ev[3], h->stream));
+    h->launches += 1;
+    h->fused_pending = true; h->last_fused = true; h->fused_reject = 0; h->ms_rejected = 0.f;
+    h->rerun = rerun;
+    h->ran = true;
+    return NOSPLAN_OK;
+}
+
 extern "C" {
 
 int nosplan_slice_begin(nosplan_t* h, void* d_totals) { return nosplan_slice_begin_ex(h, d_totals); }
@@ -1068,7 +1108,7 @@ int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count, void** d_gpu_mask) 
 static int nosplan_reject_to_classic(nosplan* h, int reasons) {
     float t = 0.f;
     cudaEventElapsedTime(&t, h->ev[2], h->ev[3]);
-    const int rc = run_classic(h);
+    const int rc = h->rerun ? h->rerun(h) : run_classic(h);
     h->fused_reject = reasons; h->ms_rejected = t;
     h->launches += 1;
     return rc;

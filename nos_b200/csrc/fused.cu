@@ -332,6 +332,73 @@ __device__ __forceinline__ int warp_phase2(const NodeS& s, bool on, const FRun* 
 
 }  // namespace
 
+constexpr int FUSED_XHDR = 240;                       // bytes in front of the bitmap in a rank's exchange block
+
+// Was the hypothesis right?  `tot`, `maxfree`, `rej`, `acc` are the grid-wide (single GPU) or job-wide (slice mode, folded)
+// values; the placed bitmap is the OR of `world` bitmaps `stride` bytes apart.  Writes the statistics and the verdict
+// (path 1: the plan stands, path 2: rejected, reason bits in pad).  Whole CTA; s_l0 / s_dec / s_e are shared scratch.
+__device__ __forceinline__ void fused_verify(const DevProblem& pb, const FRun* runs, const long long* tot, const int* maxfree, int rej,
+                                             const unsigned long long* acc, const unsigned char* bitmap, size_t stride, int world,
+                                             bool clear_bitmap, long long* s_l0, long long* s_dec, long long* s_e) {
+    const int tid = threadIdx.x, nthreads = blockDim.x;
+    const int n_words = pb.fp_pad_pods >> 5;
+    if (tid < KP) { s_l0[tid] = 0; s_dec[tid] = 0; }
+    __syncthreads();
+    for (int r = tid; r < pb.fp_n_runs; r += nthreads) {
+        const FRun fr = runs[r];
+        long long e = 0;
+        if (fr.p >= 0) {                                              // NewSliceTracker (core/tracker.go:34-57): lacking = request - available
+            const long long avail = max(0ll, *reinterpret_cast<const volatile long long*>(&tot[fr.p]));   // SubtractNonNegative (pkg/resource/resource.go:76-88)
+            e = max(0ll, (long long)fr.q - avail);
+            if (e) atomicAdd(reinterpret_cast<unsigned long long*>(&s_l0[fr.p]), (unsigned long long)(e * fr.n_real));
+        }
+        s_e[r] = e;
+    }
+    __syncthreads();
+    for (int w = tid; w < n_words; w += nthreads) {                   // a 32-position word lies inside one run (runs are 64-aligned)
+        unsigned v = 0;
+        for (int k = 0; k < world; ++k) v |= __ldcg(reinterpret_cast<const unsigned*>(bitmap + k * stride) + w);
+        if (!v) continue;
+        if (clear_bitmap) const_cast<unsigned*>(reinterpret_cast<const unsigned*>(bitmap))[w] = 0;   // clean for the next fused run of this problem
+        const int c = __popc(v);
+        int r = 0;
+        while (r + 1 < pb.fp_n_runs && runs[r + 1].pos0 <= (w << 5)) ++r;
+        if (runs[r].p >= 0 && s_e[r]) atomicAdd(reinterpret_cast<unsigned long long*>(&s_dec[runs[r].p]), (unsigned long long)(c * s_e[r]));
+    }
+    __syncthreads();
+    if (tid < 32) {
+        const int lane = tid;
+        bool ok = true;
+        long long l0 = 0, le = 0;
+        if (lane < KP) {
+            l0 = s_l0[lane]; le = l0 - s_dec[lane];
+            const bool requested = (pb.fp_rset >> lane & 1u) != 0;
+            ok = requested == (l0 > 0);
+            if (requested) {                                          // saturation at the start and at the end (fast_applicable of sweep.cu)
+                const long long m = max(pb.sat_m[lane], *reinterpret_cast<const volatile int*>(&maxfree[lane]));
+                ok = ok && le > 0 && le > (long long)(pb.G + 2) * m && l0 < (1ll << 30);
+            }
+        }
+        if (!__all_sync(FULL, ok)) rej |= FREJ_HYPOTHESIS;
+        const int lack_start = __popc(__ballot_sync(FULL, lane < KP && l0 > 0));
+        const int lack_end = __popc(__ballot_sync(FULL, lane < KP && le > 0));
+        if (lane == 0) {
+            DevStats* st = pb.stats;
+            const volatile unsigned long long* va = acc;
+            const long long vis = (long long)va[2];
+            st->visited_nodes = vis;
+            st->candidates = vis * pb.P;
+            st->geometry_evals = (long long)va[1];
+            st->placements = (long long)va[0];
+            st->candidate_nodes = vis;
+            st->lacking_at_start = lack_start;
+            st->lacking_at_end = lack_end;
+            st->path = rej ? 2 : 1;
+            st->pad = rej;
+        }
+    }
+}
+
 struct FusedLaunch { int tile_nodes, stage_bytes; };
 
 template <bool WIDE>
@@ -493,62 +560,70 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
     if (pb.K > 8) fused_body<true>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_bar);
     else fused_body<false>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_bar);
 
-    // ---- the CTA that finishes last verifies the hypothesis on the final state (what k_plan_sweep does for the classic path)
+    // ---- the CTA that finishes last either verifies the hypothesis on the final state (single GPU: what k_plan_sweep does for
+    //      the classic path) or, in slice mode, ships this rank's part of that state to every rank in ONE block
     if (!last_block_done(&pb.next_node[2])) return;
     const FRun* s_runs = reinterpret_cast<const FRun*>(s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15) + pb.fp_off[2]);
-    if (tid < KP) { s_l0[tid] = 0; s_dec[tid] = 0; }
-    __syncthreads();
-    for (int r = tid; r < pb.fp_n_runs; r += FT) {
-        const FRun fr = s_runs[r];
-        long long e = 0;
-        if (fr.p >= 0) {                                              // NewSliceTracker (core/tracker.go:34-57): lacking = request - available
-            const long long avail = max(0ll, __ldcg(&pb.tot[fr.p]));  // SubtractNonNegative (pkg/resource/resource.go:76-88)
-            e = max(0ll, (long long)fr.q - avail);
-            if (e) atomicAdd(reinterpret_cast<unsigned long long*>(&s_l0[fr.p]), (unsigned long long)(e * fr.n_real));
+    if (pb.xf_on) {
+        // [tot int64 x16 | maxfree int32 x16 | reject bits, pad x3 | counters u64 x4 | placed bitmap]: sums, maxima and ORs are
+        // order-independent, so every rank folds the W blocks into the same state and reaches the same verdict
+        unsigned char* blk = pb.xf_exchange;
+        if (tid < KP) {
+            reinterpret_cast<long long*>(blk)[tid] = __ldcg(&pb.tot[tid]);
+            reinterpret_cast<int32_t*>(blk + 128)[tid] = __ldcg(&pb.maxfree[tid]);
         }
-        s_e[r] = e;
+        if (tid < 4) {
+            reinterpret_cast<int32_t*>(blk + 192)[tid] = tid == 0 ? __ldcg(&pb.wave[5]) : 0;
+            reinterpret_cast<unsigned long long*>(blk + 208)[tid] = __ldcg(&pb.acc[tid]);
+        }
+        for (int w = tid; w < n_words + (n_words & 1); w += FT) {
+            reinterpret_cast<unsigned*>(blk + FUSED_XHDR)[w] = w < n_words ? __ldcg(&pb.placed[w]) : 0u;
+            if (w < n_words) pb.placed[w] = 0;                        // clean for the next fused run of this problem
+        }
+        __threadfence();
+        __syncthreads();
+        peer_push(pb.xf_box, 2, pb.xf_epoch, blk, pb.xf_xb);
+        return;
+    }
+    fused_verify(pb, s_runs, pb.tot, pb.maxfree, __ldcg(&pb.wave[5]), pb.acc, reinterpret_cast<const unsigned char*>(pb.placed), 0, 1, true,
+                 s_l0, s_dec, s_e);
+}
+
+// slice mode: wait for every rank's block (peer mailbox flags, or an all-gather that is already complete), fold, verify
+__global__ void __launch_bounds__(256) k_fused_verify(DevProblem pb, const unsigned char* blocks, size_t stride, int world, PeerWait wait) {
+    __shared__ long long s_tot[KP];
+    __shared__ int s_maxfree[KP];
+    __shared__ unsigned long long s_acc[4];
+    __shared__ int s_rej;
+    __shared__ long long s_l0[KP], s_dec[KP];
+    __shared__ long long s_e[FRUN_MAX];
+    const int tid = threadIdx.x;
+    cudaGridDependencySynchronize();
+    if (!peer_wait(wait)) {                                            // a peer never delivered its block: nothing below would be meaningful
+        if (tid == 0) { pb.gflags[3] = 1; pb.stats->path = 0; pb.stats->pad = 2; }
+        return;
+    }
+    if (tid < KP) {
+        long long t = 0; int m = 0;
+        for (int r = 0; r < world; ++r) {
+            t += __ldcg(reinterpret_cast<const long long*>(blocks + r * stride) + tid);
+            m = max(m, __ldcg(reinterpret_cast<const int32_t*>(blocks + r * stride + 128) + tid));
+        }
+        s_tot[tid] = t; s_maxfree[tid] = m;
+    }
+    if (tid >= 32 && tid < 36) {
+        unsigned long long a = 0;
+        for (int r = 0; r < world; ++r) a += __ldcg(reinterpret_cast<const unsigned long long*>(blocks + r * stride + 208) + (tid - 32));
+        s_acc[tid - 32] = a;
+    }
+    if (tid == 64) {
+        int f = 0;
+        for (int r = 0; r < world; ++r) f |= __ldcg(reinterpret_cast<const int32_t*>(blocks + r * stride + 192));
+        s_rej = f;
     }
     __syncthreads();
-    for (int w = tid; w < n_words; w += FT) {                         // a 32-position word lies inside one run (runs are 64-aligned)
-        const int c = __popc(__ldcg(&pb.placed[w]));
-        if (!c) continue;
-        pb.placed[w] = 0;                                             // clean for the next fused run of this problem
-        int r = 0;
-        while (r + 1 < pb.fp_n_runs && s_runs[r + 1].pos0 <= (w << 5)) ++r;
-        if (s_runs[r].p >= 0 && s_e[r]) atomicAdd(reinterpret_cast<unsigned long long*>(&s_dec[s_runs[r].p]), (unsigned long long)(c * s_e[r]));
-    }
-    __syncthreads();
-    if (tid < 32) {
-        const int lane = tid;
-        bool ok = true;
-        long long l0 = 0, le = 0;
-        if (lane < KP) {
-            l0 = s_l0[lane]; le = l0 - s_dec[lane];
-            const bool requested = (pb.fp_rset >> lane & 1u) != 0;
-            ok = requested == (l0 > 0);
-            if (requested) {                                          // saturation at the start and at the end (fast_applicable of sweep.cu)
-                const long long m = max(pb.sat_m[lane], __ldcg(&pb.maxfree[lane]));
-                ok = ok && le > 0 && le > (long long)(pb.G + 2) * m && l0 < (1ll << 30);
-            }
-        }
-        int rej = __ldcg(&pb.wave[5]);
-        if (!__all_sync(FULL, ok)) rej |= FREJ_HYPOTHESIS;
-        const int lack_start = __popc(__ballot_sync(FULL, lane < KP && l0 > 0));
-        const int lack_end = __popc(__ballot_sync(FULL, lane < KP && le > 0));
-        if (lane == 0) {
-            DevStats* st = pb.stats;
-            const long long vis = (long long)__ldcg(&pb.acc[2]);
-            st->visited_nodes = vis;
-            st->candidates = vis * pb.P;
-            st->geometry_evals = (long long)__ldcg(&pb.acc[1]);
-            st->placements = (long long)__ldcg(&pb.acc[0]);
-            st->candidate_nodes = vis;
-            st->lacking_at_start = lack_start;
-            st->lacking_at_end = lack_end;
-            st->path = rej ? 2 : 1;
-            st->pad = rej;
-        }
-    }
+    const FRun* runs = reinterpret_cast<const FRun*>(pb.fp_blob + pb.fp_off[2]);
+    fused_verify(pb, runs, s_tot, s_maxfree, s_rej, s_acc, blocks + FUSED_XHDR, stride, world, false, s_l0, s_dec, s_e);
 }
 
 // ---- launch geometry: how much of the blob is staged, how many nodes a CTA takes at a time
@@ -579,6 +654,13 @@ cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st) {
     if (blocks < 1) blocks = 1;
     k_plan_fused<<<blocks, FT, need(fl.stage_bytes, tile), st>>>(pb, fl);
     return cudaGetLastError();
+}
+
+// slice mode: bytes of a rank's exchange block
+size_t fused_exchange_bytes(const DevProblem& pb) { const size_t w = (size_t)(pb.fp_pad_pods >> 5); return FUSED_XHDR + 4 * (w + (w & 1)); }
+
+cudaError_t launch_fused_verify(const DevProblem& pb, const void* blocks, size_t stride, int world, const PeerWait& wait, cudaStream_t st) {
+    return launch_pdl(k_fused_verify, dim3(1), dim3(256), 0, st, pb, static_cast<const unsigned char*>(blocks), stride, world, wait);
 }
 
 }  // namespace nsp

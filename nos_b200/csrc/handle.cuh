@@ -38,6 +38,7 @@ struct nosplan {
     // bits in `placed`; SM count of this handle's device
     bool fused_ok = false, fused_pending = false, placed_dirty = false;
     bool last_fused = false; int fused_reject = 0; float ms_rejected = 0.f;   // what the last run was; why / how long a rejected attempt took
+    int (*rerun)(nosplan*) = nullptr;           // the classic form of the last run: what a rejected single-launch plan is replaced by
     int sms = 148;
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
@@ -64,4 +65,6 @@ void nosplan_phase_times(nosplan* h, nosplan_stats* stats);
 int nosplan_slice_begin_ex(nosplan* h, void* d_totals);
 int nosplan_slice_mid_ex(nosplan* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes,
                          const nsp::PeerWait& wait);
+int nosplan_run_sliced_fused_begin(nosplan* h, const nsp::PeerBox* box, unsigned epoch, unsigned char* d_exchange, size_t xb);
+int nosplan_run_sliced_fused_end(nosplan* h, const void* blocks, size_t stride, int world, const nsp::PeerWait& wait, int (*rerun)(nosplan*));
 int nosplan_shard_end_ex(nosplan* h, const void* d_gathered, int32_t world, size_t stride, const nsp::PeerWait& wait);

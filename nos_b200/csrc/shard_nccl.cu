@@ -21,6 +21,7 @@ int nosplan_slice_begin(nosplan_t* h, void* d_totals);
 int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes);
 }
 int nosplan_run_sliced_fused(nosplan* h, const nsp::PeerBox& box, unsigned epoch, unsigned char* d_exchange, size_t xb);
+namespace nsp { size_t fused_exchange_bytes(const DevProblem& pb); }
 
 namespace {
 
@@ -210,13 +211,58 @@ extern "C" int nosplan_run_sharded(nosplan_t* h, int32_t gather_plan) {
     return rc;
 }
 
-// Slice mode with the library's own collectives: two small all-gathers per Plan() -- the 256-byte totals block between
-// k_prepass and k_tracker_init, and the exchange block after the node-parallel pass.  The plan rows stay on their rank.
+static int ensure_shard_buffer(nosplan* h, nosplan_shard_ctx* c, size_t bytes) {
+    if (bytes > c->cap) {
+        if (c->d) SCU(h, cudaFree(c->d));
+        c->d = nullptr; c->cap = 0;
+        SCU(h, cudaMalloc(&c->d, bytes + bytes / 4 + (1 << 20)));
+        c->cap = bytes + bytes / 4 + (1 << 20);
+    }
+    return NOSPLAN_OK;
+}
+
+static int run_sliced_classic(nosplan* h);
+
+// Slice mode.  Where the single-launch plan applies (fused.cu) a Plan() is ONE kernel per rank and ONE exchange: the last CTA
+// of k_plan_fused stores the rank's block into every rank's mailbox over NVLink and raises its flag there (or the block
+// travels in one NCCL all-gather), and k_fused_verify folds the W blocks and verifies the hypothesis -- every rank reaches the
+// same verdict, and a rejected plan is replaced by the classic two-exchange sequence below on every rank alike.
 extern "C" int nosplan_run_sliced(nosplan_t* h) {
     if (!h) return NOSPLAN_E_INVALID;
     nosplan_shard_ctx* c = h->sctx;
     if (!c) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sliced before nosplan_shard_init");
     if (!h->uploaded) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sliced before nosplan_upload");
+    if (!h->fused_ok) return run_sliced_classic(h);
+    SCU(h, cudaSetDevice(h->device));
+    const int W = c->world;
+    const size_t xb = nsp::fused_exchange_bytes(h->pb);
+    size_t o = 0;
+    auto put = [&](size_t bytes) { size_t at = o; o = al(o + bytes); return at; };
+    c->xb = xb; c->chunk_rows = 0; c->gathered = false;
+    c->o_local_x = put(xb); c->o_gather_x = put(xb * W);
+    int rc = ensure_shard_buffer(h, c, o);
+    if (rc != NOSPLAN_OK) return rc;
+    if (c->peer_ok && xb <= PEER_XB_MAX) {
+        const unsigned epoch = ++c->epoch;
+        rc = nosplan_run_sliced_fused_begin(h, &c->box, epoch, c->d + c->o_local_x, xb);
+        if (rc != NOSPLAN_OK) return rc;
+        const int par = epoch & 1;
+        const unsigned char* me = c->box.base[c->rank];
+        return nosplan_run_sliced_fused_end(h, me + nsp::box_x(par, 0, c->box.xb_max), (size_t)c->box.xb_max, W,
+                                            nsp::PeerWait{reinterpret_cast<const unsigned*>(me + nsp::box_flags(2, par)), W, epoch}, run_sliced_classic);
+    }
+    rc = nosplan_run_sliced_fused_begin(h, nullptr, 0, c->d + c->o_local_x, xb);
+    if (rc != NOSPLAN_OK) return rc;
+    SNC(h, nccl().AllGather(c->d + c->o_local_x, c->d + c->o_gather_x, xb, ncclUint8, c->comm, h->stream));
+    rc = nosplan_run_sliced_fused_end(h, c->d + c->o_gather_x, xb, W, nsp::PeerWait{nullptr, 0, 0}, run_sliced_classic);
+    if (rc == NOSPLAN_OK) h->launches += 1;                      // the NCCL kernel
+    return rc;
+}
+
+// The classic form: two small exchanges per Plan() -- the 256-byte totals block between k_prepass and k_tracker_init, and the
+// exchange block after the node-parallel pass.  The plan rows stay on their rank.
+static int run_sliced_classic(nosplan* h) {
+    nosplan_shard_ctx* c = h->sctx;
     SCU(h, cudaSetDevice(h->device));
     const int W = c->world;
     const size_t xb = (size_t)nosplan_shard_exchange_bytes(h), tb = NOSPLAN_SLICE_TOTALS_BYTES;

@@ -29,6 +29,7 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     eng.shard_init(rank, world, uid[0])
     ok = True
+    fused_seen = 0
     for shape, regime in (((4000, 8, 3000), "saturating"), ((1001, 8, 2000), "saturating"), ((500, 8, 900), "satisfiable"), ((60, 8, 2), "saturating"), ((150, 8, 700), "satisfiable-7")):
         seed = 31
         if "-" in regime:
@@ -64,6 +65,7 @@ def main():
                 eng.run_sliced()
             try:
                 cnt, msk, st3 = eng.download()
+                fused_seen += int(driver == "library" and st3["fused"] == 1)
                 n = (hi - lo) * G
                 same_c &= st3["path"] == st["path"] and all(st3[k] == ost[k] for k in KEYS)
                 same_c &= np.array_equal(cnt[:n], ocnt[lo * G:hi * G]) and np.array_equal(msk[:n], omsk[lo * G:hi * G])
@@ -84,6 +86,8 @@ def main():
         ok &= same_a and same_b and same_c
         print(f"rank {rank}/{world} {shape} {regime}: path={st['path']}/{st2['path']} torch-collectives={'OK' if same_a else 'MISMATCH'} "
               f"library-collectives={'OK' if same_b else 'MISMATCH'} sliced[{eng.shard_transport()}]={'OK' if same_c else 'MISMATCH'}{' (chained sweep)' if chained else ''}", flush=True)
+    ok &= fused_seen >= 2            # the saturating cases must have gone through the single-launch sliced plan
+    print(f"rank {rank}/{world} single-launch sliced plans: {fused_seen}", flush=True)
     # quota accounting with the pods split between the ranks: Used summed / masks OR-ed over NCCL, everything else rank-local
     pq, run, pend = synth.quota_state(300, 40_000, 4_000, seed=0xC4)
     exp = ol.quota(pq, run, pend)

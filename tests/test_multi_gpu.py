@@ -15,6 +15,22 @@ def _gpus():
     return torch.cuda.device_count()
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sliced_plan_identical_on_every_rank(world):
+    """bench.py --gpus N compares, after its timed loops, every rank's rows and the job-wide counters with the oracle's plan
+    of the full snapshot and exits non-zero on a mismatch: the same check the driver's scaling run carries in its line."""
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+                        "--master-port", str(29550 + world), os.path.join(ROOT, "bench.py"), "--gpus", str(world), "--steps", "5", "--warmup", "3",
+                        "--workload", "mig-c2"],
+                       capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    import json
+    line = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["parity"] == "identical" and line["n_gpus"] == world
+
+
 @pytest.mark.parametrize("transport", ["peer-memory", "nccl"])
 def test_sharded_protocols_on_two_gpus(transport):
     if _gpus() < 2:
