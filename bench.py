@@ -271,11 +271,17 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    tok = torch.zeros(1, dtype=torch.int32, device=dev)
+
     def one_step(timed):
         if sharded_run:                      # ranks enter the step together: a late peer would otherwise be timed as waiting
             sync_all()
         with torch.cuda.stream(ext):         # L2 flush; the Plan()'s launches queue up behind it exactly as on one GPU
             flush.zero_()
+            if sharded_run:
+                # the 256 MiB flush does not take the same time on every GPU: a one-element all-reduce on the engine's stream
+                # brings the ranks' device timelines back together in front of the timed region (it is not part of it)
+                dist.all_reduce(tok)
         s = torch.cuda.Event(enable_timing=True); e = torch.cuda.Event(enable_timing=True)
         s.record(ext)
         if sharded_run:

@@ -1052,9 +1052,11 @@ int nosplan_run_sliced_fused_begin(nosplan* h, const PeerBox* box, unsigned epoc
 }
 
 int nosplan_run_sliced_fused_end(nosplan* h, const void* blocks, size_t stride, int world, const PeerWait& wait, int (*rerun)(nosplan*)) {
-    CU(h, launch_fused_verify(h->pb, blocks, stride, world, wait, h->stream));
+    if (blocks) {                                            // NCCL transport: the gathered blocks are folded and verified by a kernel of its own
+        CU(h, launch_fused_verify(h->pb, blocks, stride, world, wait, h->stream));
+        h->launches += 1;
+    }
     CU(h, cudaEventRecord(h->ev[3], h->stream));
-    h->launches += 1;
     h->fused_pending = true; h->last_fused = true; h->fused_reject = 0; h->ms_rejected = 0.f;
     h->rerun = rerun;
     h->ran = true;

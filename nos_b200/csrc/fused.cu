@@ -332,7 +332,8 @@ __device__ __forceinline__ int warp_phase2(const NodeS& s, bool on, const FRun* 
 
 }  // namespace
 
-constexpr int FUSED_XHDR = 240;                       // bytes in front of the bitmap in a rank's exchange block
+constexpr int FUSED_XHDR = 240;                       // bytes in front of the bitmap in a rank's exchange block (NCCL transport)
+constexpr int FUSED_LL_HDR = 58;                      // 32-bit words in front of the bitmap in the flag-in-word form (peer transport)
 
 // Was the hypothesis right?  `tot`, `maxfree`, `rej`, `acc` are the grid-wide (single GPU) or job-wide (slice mode, folded)
 // values; the placed bitmap is the OR of `world` bitmaps `stride` bytes apart.  Writes the statistics and the verdict
@@ -357,7 +358,7 @@ __device__ __forceinline__ void fused_verify(const DevProblem& pb, const FRun* r
     __syncthreads();
     for (int w = tid; w < n_words; w += nthreads) {                   // a 32-position word lies inside one run (runs are 64-aligned)
         unsigned v = 0;
-        for (int k = 0; k < world; ++k) v |= __ldcg(reinterpret_cast<const unsigned*>(bitmap + k * stride) + w);
+        for (int k = 0; k < world; ++k) v |= *(reinterpret_cast<const volatile unsigned*>(bitmap + k * stride) + w);
         if (!v) continue;
         if (clear_bitmap) const_cast<unsigned*>(reinterpret_cast<const unsigned*>(bitmap))[w] = 0;   // clean for the next fused run of this problem
         const int c = __popc(v);
@@ -564,9 +565,83 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
     //      the classic path) or, in slice mode, ships this rank's part of that state to every rank in ONE block
     if (!last_block_done(&pb.next_node[2])) return;
     const FRun* s_runs = reinterpret_cast<const FRun*>(s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15) + pb.fp_off[2]);
+    if (pb.xf_on && pb.xf_box.world > 0) {
+        // ---- peer-memory transport, flag-in-word: the rank's state travels as 8-byte words {value, epoch}, stored straight into
+        //      every rank's mailbox over NVLink (an 8-byte store lands whole), so there is no fence and no separate flag: a
+        //      consumer polls each word until it carries this Plan()'s epoch.  Words: 0..31 sum(alloc - requested) per slice
+        //      column (lo, hi), 32..47 largest free count per profile, 48 reject bits, 49..56 counters (lo, hi), 58.. placed
+        //      bitmap.  This CTA is producer and consumer: the sliced Plan() stays ONE kernel per rank.  Every rank's kernel
+        //      reaches its stores independently of any other rank, so the wait cannot deadlock; it is bounded, and a peer
+        //      that never shows up is reported.
+        const int par = pb.xf_epoch & 1, W = pb.xf_box.world, D = FUSED_LL_HDR + n_words;
+        const unsigned epoch = pb.xf_epoch;
+        for (int i = tid; i < D; i += FT) {
+            unsigned v = 0;
+            if (i < 32) v = __ldcg(reinterpret_cast<const unsigned*>(pb.tot) + i);
+            else if (i < 48) v = (unsigned)__ldcg(&pb.maxfree[i - 32]);
+            else if (i == 48) v = (unsigned)__ldcg(&pb.wave[5]);
+            else if (i < 57) v = __ldcg(reinterpret_cast<const unsigned*>(pb.acc) + (i - 49));
+            else if (i >= FUSED_LL_HDR) { v = __ldcg(&pb.placed[i - FUSED_LL_HDR]); if (v) pb.placed[i - FUSED_LL_HDR] = 0; }   // clean for the next run
+            for (int r = 0; r < W; ++r)
+                reinterpret_cast<uint2*>(pb.xf_box.base[r] + box_ll(par, pb.xf_box.rank, pb.xf_box.xb_max))[i] = make_uint2(v, epoch);
+        }
+        // consume: W words per index from this rank's own mailbox (local memory)
+        const unsigned char* me = pb.xf_box.base[pb.xf_box.rank];
+        unsigned* s_hdr = reinterpret_cast<unsigned*>(s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15) + pb.fp_off[4]);   // staged minima: no longer needed
+        unsigned* s_or = reinterpret_cast<unsigned*>(s_dyn);                                                              // this CTA's placed bits: flushed long ago
+        bool ok = true;
+        for (int i = tid; i < D; i += FT) {
+            unsigned acc_or = 0;
+            for (int r = 0; r < W; ++r) {
+                const volatile uint2* src = reinterpret_cast<const volatile uint2*>(me + box_ll(par, r, pb.xf_box.xb_max)) + i;
+                unsigned vx, vy, spins = 0;
+                for (;;) {
+                    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(vx), "=r"(vy) : "l"(src) : "memory");
+                    if (vy == epoch) break;
+                    if (++spins > (1u << 22)) { ok = false; vx = 0; break; }
+                    if (spins > 64) __nanosleep(200);
+                }
+                if (i < FUSED_LL_HDR) s_hdr[r * FUSED_LL_HDR + i] = vx; else acc_or |= vx;
+            }
+            if (i >= FUSED_LL_HDR) s_or[i - FUSED_LL_HDR] = acc_or;
+        }
+        if (!__syncthreads_and(ok)) {
+            if (tid == 0) { pb.gflags[3] = 1; pb.stats->path = 0; pb.stats->pad = 2; }
+            return;
+        }
+        long long* f_tot = reinterpret_cast<long long*>(&s_wD[0][0]);
+        int* f_maxfree = reinterpret_cast<int*>(&s_wD[1][0]);
+        unsigned long long* f_acc = &s_wcnt[0][0];
+        if (tid < KP) {
+            long long t = 0; int m = 0;
+            for (int r = 0; r < W; ++r) {
+                const unsigned* hr = s_hdr + r * FUSED_LL_HDR;
+                t += (long long)(((unsigned long long)hr[2 * tid + 1] << 32) | hr[2 * tid]);
+                m = max(m, (int)hr[32 + tid]);
+            }
+            f_tot[tid] = t; f_maxfree[tid] = m;
+        }
+        if (tid >= 32 && tid < 36) {
+            unsigned long long a = 0;
+            for (int r = 0; r < W; ++r) {
+                const unsigned* hr = s_hdr + r * FUSED_LL_HDR + 49 + 2 * (tid - 32);
+                a += ((unsigned long long)hr[1] << 32) | hr[0];
+            }
+            f_acc[tid - 32] = a;
+        }
+        if (tid == 64) {
+            int f = 0;
+            for (int r = 0; r < W; ++r) f |= (int)s_hdr[r * FUSED_LL_HDR + 48];
+            s_flags[0] = f;
+        }
+        __syncthreads();
+        fused_verify(pb, s_runs, f_tot, f_maxfree, s_flags[0], f_acc, reinterpret_cast<const unsigned char*>(s_or), 0, 1, false, s_l0, s_dec, s_e);
+        return;
+    }
     if (pb.xf_on) {
-        // [tot int64 x16 | maxfree int32 x16 | reject bits, pad x3 | counters u64 x4 | placed bitmap]: sums, maxima and ORs are
-        // order-independent, so every rank folds the W blocks into the same state and reaches the same verdict
+        // ---- the block travels by NCCL: [tot int64 x16 | maxfree int32 x16 | reject bits, pad x3 | counters u64 x4 | placed
+        //      bitmap] is assembled here and k_fused_verify follows the all-gather on the stream.  Sums, maxima and ORs are
+        //      order-independent, so every rank folds the W blocks into the same state and reaches the same verdict.
         unsigned char* blk = pb.xf_exchange;
         if (tid < KP) {
             reinterpret_cast<long long*>(blk)[tid] = __ldcg(&pb.tot[tid]);
@@ -580,9 +655,6 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
             reinterpret_cast<unsigned*>(blk + FUSED_XHDR)[w] = w < n_words ? __ldcg(&pb.placed[w]) : 0u;
             if (w < n_words) pb.placed[w] = 0;                        // clean for the next fused run of this problem
         }
-        __threadfence();
-        __syncthreads();
-        peer_push(pb.xf_box, 2, pb.xf_epoch, blk, pb.xf_xb);
         return;
     }
     fused_verify(pb, s_runs, pb.tot, pb.maxfree, __ldcg(&pb.wave[5]), pb.acc, reinterpret_cast<const unsigned char*>(pb.placed), 0, 1, true,
@@ -656,7 +728,8 @@ cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-// slice mode: bytes of a rank's exchange block
+// slice mode: bytes of a rank's exchange block in the flag-in-word form / as assembled for NCCL
+size_t fused_exchange_bytes_ll(const DevProblem& pb) { return 8 * ((size_t)FUSED_LL_HDR + (size_t)(pb.fp_pad_pods >> 5)); }
 size_t fused_exchange_bytes(const DevProblem& pb) { const size_t w = (size_t)(pb.fp_pad_pods >> 5); return FUSED_XHDR + 4 * (w + (w & 1)); }
 
 cudaError_t launch_fused_verify(const DevProblem& pb, const void* blocks, size_t stride, int world, const PeerWait& wait, cudaStream_t st) {

@@ -85,7 +85,10 @@ struct PeerWait { const unsigned* flags; int world; unsigned epoch; };      // f
 __host__ __device__ inline size_t box_flags(int which, int parity) { return (size_t)(which - 1) * 64 + (size_t)parity * 32; }
 __host__ __device__ inline size_t box_tot(int parity, int r) { return 256 + ((size_t)parity * PEER_MAX + r) * 256; }
 __host__ __device__ inline size_t box_x(int parity, int r, size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + ((size_t)parity * PEER_MAX + r) * xb_max; }
-inline size_t box_bytes(size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + 2 * PEER_MAX * xb_max; }
+// a second set of slots for blocks in flag-in-word form (fused.cu): kept apart from the plain blocks so that a stale plain word
+// can never be taken for a word of the current epoch
+__host__ __device__ inline size_t box_ll(int parity, int r, size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + 2 * PEER_MAX * xb_max + ((size_t)parity * PEER_MAX + r) * xb_max; }
+inline size_t box_bytes(size_t xb_max) { return 256 + 2 * PEER_MAX * 256 + 4 * PEER_MAX * xb_max; }
 
 // all threads of the block call it; false = a peer did not show up within several seconds (the caller records the failure
 // instead of hanging the GPU)

@@ -21,7 +21,7 @@ int nosplan_slice_begin(nosplan_t* h, void* d_totals);
 int nosplan_slice_mid(nosplan_t* h, int32_t rank, int32_t world, const void* d_totals_gathered, void* d_exchange, int64_t exchange_bytes);
 }
 int nosplan_run_sliced_fused(nosplan* h, const nsp::PeerBox& box, unsigned epoch, unsigned char* d_exchange, size_t xb);
-namespace nsp { size_t fused_exchange_bytes(const DevProblem& pb); }
+namespace nsp { size_t fused_exchange_bytes(const DevProblem& pb); size_t fused_exchange_bytes_ll(const DevProblem& pb); }
 
 namespace {
 
@@ -242,14 +242,12 @@ extern "C" int nosplan_run_sliced(nosplan_t* h) {
     c->o_local_x = put(xb); c->o_gather_x = put(xb * W);
     int rc = ensure_shard_buffer(h, c, o);
     if (rc != NOSPLAN_OK) return rc;
-    if (c->peer_ok && xb <= PEER_XB_MAX) {
+    if (c->peer_ok && nsp::fused_exchange_bytes_ll(h->pb) <= PEER_XB_MAX) {
         const unsigned epoch = ++c->epoch;
         rc = nosplan_run_sliced_fused_begin(h, &c->box, epoch, c->d + c->o_local_x, xb);
         if (rc != NOSPLAN_OK) return rc;
-        const int par = epoch & 1;
-        const unsigned char* me = c->box.base[c->rank];
-        return nosplan_run_sliced_fused_end(h, me + nsp::box_x(par, 0, c->box.xb_max), (size_t)c->box.xb_max, W,
-                                            nsp::PeerWait{reinterpret_cast<const unsigned*>(me + nsp::box_flags(2, par)), W, epoch}, run_sliced_classic);
+        // the kernel's last CTA pushed, waited for the other ranks' blocks, folded and verified: nothing else to launch
+        return nosplan_run_sliced_fused_end(h, nullptr, 0, W, nsp::PeerWait{nullptr, 0, 0}, run_sliced_classic);
     }
     rc = nosplan_run_sliced_fused_begin(h, nullptr, 0, c->d + c->o_local_x, xb);
     if (rc != NOSPLAN_OK) return rc;
