@@ -133,13 +133,6 @@ struct GoStable {
     }
 };
 
-struct Layout {            // byte offsets into the arena / staging buffer
-    size_t model_off, geom, node_gpu_count, gpu_model, gpu_mem, gpu_used, gpu_free, gpu_umask, gpu_fmask,
-        node_alloc, node_req, node_allowed, node_npods, nodes_end,
-        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, wave, work_end, cand_flag, cand_idx, out_count, out_mask, out_end,
-        pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
-        cmin_cpu, cmin_mem, cmin_eph, fp_blob, upload_end, placed, entry_lack, total;
-};
 
 int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes, size_t keep_bytes = 0) {
     if (dev_bytes > h->d_cap) {
@@ -399,6 +392,45 @@ static int run_pre(nosplan* h, bool split) {
 
 }  // extern "C"
 
+// The classic kernels' view of the pods, in NewPodSorter order (h->v_order): request columns, tracker keys, flags, CSR of the
+// scalar entries, the run records and per-chunk (32 pods, run-relative) minima of the requests of the PreFilter-ok pods -- the
+// kernels skip chunks in which no pod can pass NodeResourcesFit.  An all-zero request passes regardless (fit.go short-circuit):
+// its minimum is LLONG_MIN.  Written into the staging buffer at the offsets of h->lay.
+static void stage_classic_pods(nosplan* h, const nosplan_pods* pods, int K) {
+    (void)K;
+    const Layout& L = h->lay;
+    unsigned char* S = h->h_stage;
+    const int P = pods->n_pods;
+    const std::vector<int>& order = h->v_order;
+    const std::vector<uint32_t>& flags = h->v_flags;
+    const std::vector<RunRec>& runs = h->v_runs;
+    const int n_runs = (int)runs.size();
+    long long* cpu = (long long*)(S + L.pod_cpu); long long* mem = (long long*)(S + L.pod_mem); long long* eph = (long long*)(S + L.pod_eph);
+    int32_t* key = (int32_t*)(S + L.pod_key); uint32_t* fl = (uint32_t*)(S + L.pod_flags);
+    int32_t* sptr = (int32_t*)(S + L.pod_sptr); int32_t* scol = (int32_t*)(S + L.pod_scol); long long* sqty = (long long*)(S + L.pod_sqty);
+    long long* c0 = (long long*)(S + L.cmin_cpu); long long* c1 = (long long*)(S + L.cmin_mem); long long* c2 = (long long*)(S + L.cmin_eph);
+    int w = 0, chunk = -1;
+    for (int r = 0; r < n_runs; ++r)
+        for (int k = 0; k < runs[r].len; ++k) {
+            const int si = runs[r].start + k, oi = order[si];
+            if ((k & 31) == 0) { ++chunk; c0[chunk] = c1[chunk] = c2[chunk] = LLONG_MAX; }
+            const long long bc = pods->base[3 * (size_t)oi], bm = pods->base[3 * (size_t)oi + 1], be = pods->base[3 * (size_t)oi + 2];
+            const uint32_t f = flags[oi];
+            if (f & PF_PRE_OK) {
+                const bool z = (f & PF_ZERO_REQ) != 0;
+                c0[chunk] = std::min(c0[chunk], z ? LLONG_MIN : bc); c1[chunk] = std::min(c1[chunk], z ? LLONG_MIN : bm);
+                c2[chunk] = std::min(c2[chunk], z ? LLONG_MIN : be);
+            }
+            cpu[si] = bc; mem[si] = bm; eph[si] = be;
+            key[si] = pods->tracker_key[oi]; fl[si] = f;
+            sptr[si] = w;
+            for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1]; ++e) { scol[w] = pods->scalar_col[e]; sqty[w] = pods->scalar_qty[e]; ++w; }
+        }
+    sptr[P] = w;
+    if (n_runs) std::memcpy(S + L.runs, runs.data(), sizeof(RunRec) * (size_t)n_runs);
+    std::memcpy(S + L.run_chunk_off, h->v_chunk_off.data(), 4 * ((size_t)n_runs + 1));
+}
+
 // keep: the node arrays of the last full upload are still in the arena and are planned against again (s = &h->res_snap)
 static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
                        int32_t filter_mode, bool keep) {
@@ -589,87 +621,267 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     }
     lap("validate nodes");
 
-    // ---- pods, pass 1 (original order): validation, flags, first requested profile, class key of the slice request
-    //      (equal keys <=> identical slice requests; CLS_MULTI = compare the entries)
-    constexpr unsigned long long CLS_MULTI = ~0ull;
-    std::vector<int>& first_prof = h->v_first_prof; first_prof.assign(P, -1);
-    std::vector<uint32_t>& flags = h->v_flags; flags.resize(P);
-    std::vector<unsigned long long>& cls = h->v_cls; cls.resize(P);
-    int n_keys = 0;
-    std::vector<uint8_t>& key_seen = h->v_key_seen; key_seen.assign(P, 0);
-    bool keys_unique = true, any_other = false, any_zero = false;
-    long long max_q = 0;
-    unsigned long long or_cpu = 0, or_mem = 0;
-    long long max_cpu = 0, max_mem = 0;
-    for (int i = 0; i < P; ++i) {
-        const int a = pods->scalar_ptr[i], b = pods->scalar_ptr[i + 1];
-        if (a > b || b > nnz) return fail(h, NOSPLAN_E_INVALID, "pod %d: bad scalar_ptr", i);
-        bool other = false; int prev = 2, n_slice = 0;
-        unsigned long long ck = 0;
-        for (int e = a; e < b; ++e) {
-            const int col = pods->scalar_col[e];
-            if (col < 3 || col >= R || col <= prev) return fail(h, NOSPLAN_E_INVALID, "pod %d: scalar columns must be in [3,R) and ascending", i);
-            prev = col;
-            if (col < 3 + K) {
-                const long long q = pods->scalar_qty[e];
-                if (q <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
-                if (first_prof[i] < 0) first_prof[i] = col - 3;
-                max_q = std::max(max_q, q);
-                ck = (++n_slice == 1 && q < (1ll << 40)) ? (((unsigned long long)(col - 2)) << 40 | (unsigned long long)q) : CLS_MULTI;
-            } else other = true;
-        }
-        cls[i] = ck;
-        const long long bc = pods->base[3 * (size_t)i], bm = pods->base[3 * (size_t)i + 1], be = pods->base[3 * (size_t)i + 2];
-        if ((bc | bm | be) < 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: negative cpu / memory / ephemeral-storage request", i);
-        uint32_t f = 0;
-        if (!prefilter_ok || prefilter_ok[i]) f |= PF_PRE_OK;
-        if (other) { f |= PF_HAS_OTHER; any_other = true; }
-        if (a == b && (bc | bm | be) == 0) { f |= PF_ZERO_REQ; any_zero = true; }
-        flags[i] = f;
-        or_cpu |= (unsigned long long)bc; or_mem |= (unsigned long long)bm;
-        max_cpu = std::max(max_cpu, bc); max_mem = std::max(max_mem, bm);
-        const int k = pods->tracker_key[i];
-        if (k < 0 || k >= P) return fail(h, NOSPLAN_E_INVALID, "pod %d: tracker_key out of range", i);
-        if (key_seen[k]) keys_unique = false;
-        key_seen[k] = 1;
-        n_keys = std::max(n_keys, k + 1);
-    }
-    if (n_keys > sweep_max_keys()) return fail(h, NOSPLAN_E_LIMIT, "%d tracker keys > %d", n_keys, sweep_max_keys());
-    lap("pod keys");
-
-    // ---- NewPodSorter (core/util.go:34-73)
-    std::vector<int>& order = h->v_order;
-    pod_order(s, pods, first_prof.data(), order);
-    lap("sort");
-
-    // ---- pass 2 (sorted order), fused: pods into staging, runs of identical slice requests, and per-chunk (32 pods,
-    //      run-relative) minima of the requests of the PreFilter-ok pods -- the kernels skip chunks in which no pod can pass
-    //      NodeResourcesFit.  An all-zero request passes regardless (fit.go short-circuit): its minimum is LLONG_MIN.
-    std::vector<RunRec>& runs = h->v_runs; runs.clear();
-    std::vector<int32_t>& run_chunk_off = h->v_chunk_off; run_chunk_off.clear();
-    std::vector<long long>& cmin = h->v_cmin; cmin.clear();                  // [chunk][3]
-    auto same_entries = [&](int x, int y) {
-        int ex = pods->scalar_ptr[x], ey = pods->scalar_ptr[y];
-        const int bx = pods->scalar_ptr[x + 1], by = pods->scalar_ptr[y + 1];
-        for (;;) {
-            const bool sx = ex < bx && pods->scalar_col[ex] < 3 + K, sy = ey < by && pods->scalar_col[ey] < 3 + K;
-            if (!sx || !sy) return sx == sy;
-            if (pods->scalar_col[ex] != pods->scalar_col[ey] || pods->scalar_qty[ex] != pods->scalar_qty[ey]) return false;
-            ++ex; ++ey;
-        }
-    };
-    bool single_profile_classes = true;
+    // ---- results of the pod side (either path below)
+    int n_keys = 0, n_runs = 0, n_chunks = 0, cpu_shift = 0, mem_shift = 0, pad_pods = 0;
+    bool single_profile_classes = true, lazy = false;
     long long any_eph = 0;
-    {
-        long long* cpu = (long long*)(S + L.pod_cpu); long long* mem = (long long*)(S + L.pod_mem); long long* eph = (long long*)(S + L.pod_eph);
-        int32_t* key = (int32_t*)(S + L.pod_key); uint32_t* fl = (uint32_t*)(S + L.pod_flags);
-        int32_t* sptr = (int32_t*)(S + L.pod_sptr); int32_t* scol = (int32_t*)(S + L.pod_scol); long long* sqty = (long long*)(S + L.pod_sqty);
-        int w = 0, prev_oi = -1, in_run = 0;
-        long long* cm = nullptr;
-        for (int si = 0; si < P; ++si) {
+    unsigned rset = 0;
+    int fp_off[9] = {0};
+    size_t up_from = 0;
+    fused_ok = fused_ok && !h->force_classic;
+
+    // ---- fast path of one nosplan_plan / nosplan_plan_resident call that can use the single-launch kernel: TWO passes over
+    //      the pods in their original order.  Pass A validates, finds every pod's (priority level, requested profile) bucket
+    //      and counts; where NewPodSorter's comparator is a strict weak order on what is present, every stable sort gives
+    //      "buckets in (priority desc, profile rank) order, original order inside" (core/util.go:34-73, see pod_order), so pass
+    //      B writes each pod's (cpu, memory) pair straight to its position of the padded space.  Anything this does not cover
+    //      -- an invalid pod, several scalar entries, quantities above one, shared tracker keys, priority levels that mix
+    //      slice-less and sliced pods -- leaves it to the general path below, which also reports the errors.
+    bool fast_done = false;
+    if (fused_ok && h->in_plan && P > 0 && !getenv("NOSPLAN_NO_FAST_PODS")) fast_done = [&]() -> bool {
+        constexpr int LV_MAX = 64, NB = KP + 1;
+        struct Level { int32_t prio; int cnt[NB]; };
+        Level levels_store[LV_MAX];
+        struct { Level* d; size_t n; size_t size() const { return n; } Level& operator[](size_t k) { return d[k]; }
+                 const Level& operator[](size_t k) const { return d[k]; } void push_back(const Level& l) { d[n++] = l; }
+                 Level* begin() { return d; } Level* end() { return d + n; } } levels{levels_store, 0};
+        std::vector<uint16_t>& bk = h->v_bucket; bk.resize(P);
+        std::vector<uint8_t>& key_seen = h->v_key_seen; key_seen.assign(P, 0);
+        unsigned long long or_cpu = 0, or_mem = 0;
+        long long max_cpu = 0, max_mem = 0;
+        int max_key = -1;
+        size_t last = 0;
+        int32_t lv_prio[LV_MAX]; int n_lv_seen = 0;
+        for (int i = 0; i < P; ++i) {
+            const int a = pods->scalar_ptr[i], n = pods->scalar_ptr[i + 1] - a;
+            int pr = -1;
+            if (n == 1) {
+                const int col = pods->scalar_col[a];
+                if (a < 0 || a >= nnz || col < 3 || col >= 3 + K || pods->scalar_qty[a] != 1) return false;
+                pr = col - 3;
+            } else if (n != 0) return false;
+            const long long bc = pods->base[3 * (size_t)i], bm = pods->base[3 * (size_t)i + 1], be = pods->base[3 * (size_t)i + 2];
+            if ((bc | bm) < 0 || be != 0 || (n == 0 && (bc | bm) == 0)) return false;
+            const int k = pods->tracker_key[i];
+            if (k < 0 || k >= P || key_seen[k]) return false;
+            key_seen[k] = 1;
+            max_key = std::max(max_key, k);
+            const int32_t prio = pods->priority[i];
+            {   // few distinct priorities: compare with all of them, no data-dependent branch (the priorities arrive in random order)
+                int hit = -1;
+                for (int q = 0; q < n_lv_seen; ++q) hit = lv_prio[q] == prio ? q : hit;
+                if (hit < 0) {
+                    if (n_lv_seen >= LV_MAX) return false;
+                    Level l; l.prio = prio; std::memset(l.cnt, 0, sizeof l.cnt);
+                    levels.push_back(l);
+                    lv_prio[n_lv_seen] = prio;
+                    hit = n_lv_seen++;
+                }
+                last = (size_t)hit;
+            }
+            levels[last].cnt[pr + 1]++;
+            bk[i] = (uint16_t)(last * NB + pr + 1);
+            or_cpu |= (unsigned long long)bc; or_mem |= (unsigned long long)bm;
+            max_cpu = std::max(max_cpu, bc); max_mem = std::max(max_mem, bm);
+        }
+        // profiles present: the comparator must be a strict weak order on them, and no two of them may share a rank
+        const int32_t* pmem = s->profile_mem_gb; const int32_t* pgi = s->profile_gi;
+        auto smaller = [=](int x, int y) { if (pmem[x] < pmem[y]) return true; return mig && pgi[x] < pgi[y]; };
+        bool present[KP] = {false};
+        for (const Level& l : levels) {
+            bool sliced = false;
+            for (int pr = 0; pr < K; ++pr) if (l.cnt[pr + 1]) { present[pr] = true; sliced = true; }
+            if (l.cnt[0] && sliced) return false;                         // slice-less pods are incomparable to everything
+        }
+        int rank_of[KP] = {0};
+        unsigned ranks_used = 0;
+        for (int x = 0; x < K; ++x) {
+            if (!present[x]) continue;
+            for (int y = 0; y < K; ++y) {
+                if (!present[y]) continue;
+                if (smaller(x, y) && smaller(y, x)) return false;
+                if (smaller(y, x)) ++rank_of[x];
+                for (int z = 0; z < K; ++z) {
+                    if (!present[z]) continue;
+                    if (smaller(x, y) && smaller(y, z) && !smaller(x, z)) return false;
+                    const bool ixy = !smaller(x, y) && !smaller(y, x), iyz = !smaller(y, z) && !smaller(z, y), ixz = !smaller(x, z) && !smaller(z, x);
+                    if (ixy && iyz && !ixz) return false;
+                }
+            }
+            if (ranks_used >> rank_of[x] & 1u) return false;
+            ranks_used |= 1u << rank_of[x];
+        }
+        int prof_by_rank[KP], n_present = 0;
+        for (int r = 0; r < KP; ++r) for (int x = 0; x < K; ++x) if (present[x] && rank_of[x] == r) prof_by_rank[n_present++] = x;
+        // runs = non-empty buckets, priority descending, then profile rank
+        int lv_order[LV_MAX];
+        const int n_lv = (int)levels.size();
+        for (int q = 0; q < n_lv; ++q) lv_order[q] = q;
+        std::sort(lv_order, lv_order + n_lv, [&](int x, int y) { return levels[x].prio > levels[y].prio; });
+        FRun fr[FRUN_MAX];
+        int run_of[LV_MAX * NB];
+        int nr = 0, pos = 0, chunks = 0;
+        unsigned rs = 0;
+        for (int q = 0; q < n_lv; ++q) {
+            const Level& l = levels[lv_order[q]];
+            for (int c = -1; c < n_present; ++c) {
+                const int pr = c < 0 ? -1 : prof_by_rank[c], cnt = l.cnt[pr + 1];
+                if (!cnt) continue;
+                if (nr >= FRUN_MAX) return false;
+                FRun f; std::memset(&f, 0, sizeof f);
+                f.pos0 = pos; f.nblk = (cnt + 63) >> 6; f.n_real = cnt; f.p = pr; f.q = pr >= 0 ? 1 : 0; f.min_c = f.min_m = F_NONE;
+                run_of[lv_order[q] * NB + pr + 1] = nr;
+                fr[nr++] = f;
+                pos += f.nblk * 64; chunks += (cnt + 31) >> 5;
+                if (pr >= 0) rs |= 1u << pr;
+            }
+        }
+        const int cs = or_cpu ? __builtin_ctzll(or_cpu) : 0, ms = or_mem ? __builtin_ctzll(or_mem) : 0;
+        if ((max_cpu >> cs) >= F_COST_LIMIT || (max_mem >> ms) >= F_COST_LIMIT || pos > fused_max_pad_pods() || rs == 0) return false;
+        // layout, part 2 (the classic sections keep their room: a rejected plan stages them later), then the blob
+        n_keys = max_key + 1; n_runs = nr; n_chunks = chunks; cpu_shift = cs; mem_shift = ms; pad_pods = pos; rset = rs;
+        single_profile_classes = true; any_eph = 0;
+        o = part1_end;
+        put(L.runs, sizeof(RunRec) * (size_t)n_runs);
+        put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
+        put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
+        {
+            auto a16 = [](size_t x) { return (int)((x + 15) & ~(size_t)15); };
+            const int n3 = (pad_pods + 511) / 512, n2 = pad_pods / 64, n1 = pad_pods / 8;
+            fp_off[0] = a16(16 * (size_t)n_rows);
+            fp_off[1] = fp_off[0] + a16(2 * (size_t)n_rows);
+            fp_off[2] = fp_off[1] + a16(4 * ((size_t)n_models + 1));
+            fp_off[3] = fp_off[2] + a16(sizeof(FRun) * (size_t)n_runs);
+            fp_off[4] = fp_off[3] + a16(8 * (KP + 1));
+            fp_off[5] = fp_off[4] + a16(8 * (size_t)n3);
+            fp_off[6] = fp_off[5] + a16(8 * (size_t)n2);
+            fp_off[7] = fp_off[6] + a16(8 * (size_t)n1);
+            fp_off[8] = fp_off[7] + a16(8 * (size_t)pad_pods);
+        }
+        put(L.fp_blob, (size_t)fp_off[8]);
+        L.upload_end = o; L.total = o;
+        if (L.total > bound) return false;
+        h->lay = L;
+        unsigned char* B = S + L.fp_blob;
+        int32_t* l3 = (int32_t*)(B + fp_off[4]); int32_t* l2 = (int32_t*)(B + fp_off[5]); int32_t* l1 = (int32_t*)(B + fp_off[6]);
+        int32_t* fpod = (int32_t*)(B + fp_off[7]);
+        unsigned long long* prof_runs = (unsigned long long*)(B + fp_off[3]);
+        std::memset(B, 0, (size_t)fp_off[4]);
+        if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
+        for (int r = 0; r < n_rows; ++r) {
+            uint16_t m = 0;
+            for (int pp = 0; pp < 16; ++pp) if (s->geom_counts[16 * (size_t)r + pp]) m |= (uint16_t)(1u << pp);
+            ((uint16_t*)(B + fp_off[0]))[r] = m;
+        }
+        if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
+        std::fill(l3, (int32_t*)(B + fp_off[8]), (int32_t)F_NONE);
+        int cur[FRUN_MAX];
+        for (int r = 0; r < nr; ++r) cur[r] = fr[r].pos0;
+        for (int i = 0; i < P; ++i) {                                     // pass B: original order == order inside a bucket
+            const int x = cur[run_of[bk[i]]]++;
+            if (prefilter_ok && !prefilter_ok[i]) continue;
+            const int32_t c = (int32_t)(pods->base[3 * (size_t)i] >> cs), m = (int32_t)(pods->base[3 * (size_t)i + 1] >> ms);
+            fpod[2 * (size_t)x] = c; fpod[2 * (size_t)x + 1] = m;
+            int32_t* a1 = l1 + 2 * (size_t)(x >> 3);
+            a1[0] = std::min(a1[0], c); a1[1] = std::min(a1[1], m);
+        }
+        for (int r = 0; r < nr; ++r) {
+            FRun& f = fr[r];
+            for (int x8 = f.pos0 >> 3; x8 < (f.pos0 >> 3) + f.nblk * 8; ++x8) {
+                const int32_t c = l1[2 * (size_t)x8], m = l1[2 * (size_t)x8 + 1];
+                int32_t* b2 = l2 + 2 * (size_t)(x8 >> 3); int32_t* d3 = l3 + 2 * (size_t)(x8 >> 6);
+                b2[0] = std::min(b2[0], c); b2[1] = std::min(b2[1], m); d3[0] = std::min(d3[0], c); d3[1] = std::min(d3[1], m);
+                f.min_c = std::min(f.min_c, c); f.min_m = std::min(f.min_m, m);
+            }
+            prof_runs[f.p >= 0 ? f.p : KP] |= 1ull << r;
+        }
+        std::memcpy(B + fp_off[2], fr, sizeof(FRun) * (size_t)nr);
+        lazy = true; up_from = L.fp_blob;
+        h->classic_staged = false;
+        h->lazy_valid = true; h->lazy_pods = *pods; h->lazy_pre = prefilter_ok; h->lazy_filter = filter_mode;
+        return true;
+    }();
+    if (fast_done) {
+        CU(h, cudaEventRecord(h->ev[9], h->stream));
+        CU(h, cudaMemcpyAsync(A + up_from, S + up_from, L.upload_end - up_from, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaEventRecord(h->ev[10], h->stream));
+    }
+    lap("pods fast");
+    if (!fast_done) {
+        // ---- pods, pass 1 (original order): validation, flags, first requested profile, class key of the slice request
+        //      (equal keys <=> identical slice requests; CLS_MULTI = compare the entries)
+        constexpr unsigned long long CLS_MULTI = ~0ull;
+        std::vector<int>& first_prof = h->v_first_prof; first_prof.assign(P, -1);
+        std::vector<uint32_t>& flags = h->v_flags; flags.resize(P);
+        std::vector<unsigned long long>& cls = h->v_cls; cls.resize(P);
+        n_keys = 0;
+        std::vector<uint8_t>& key_seen = h->v_key_seen; key_seen.assign(P, 0);
+        bool keys_unique = true, any_other = false, any_zero = false;
+        long long max_q = 0;
+        unsigned long long or_cpu = 0, or_mem = 0;
+        long long max_cpu = 0, max_mem = 0;
+        any_eph = 0;
+        for (int i = 0; i < P; ++i) {
+            const int a = pods->scalar_ptr[i], b = pods->scalar_ptr[i + 1];
+            if (a > b || b > nnz) return fail(h, NOSPLAN_E_INVALID, "pod %d: bad scalar_ptr", i);
+            bool other = false; int prev = 2, n_slice = 0;
+            unsigned long long ck = 0;
+            for (int e = a; e < b; ++e) {
+                const int col = pods->scalar_col[e];
+                if (col < 3 || col >= R || col <= prev) return fail(h, NOSPLAN_E_INVALID, "pod %d: scalar columns must be in [3,R) and ascending", i);
+                prev = col;
+                if (col < 3 + K) {
+                    const long long q = pods->scalar_qty[e];
+                    if (q <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
+                    if (first_prof[i] < 0) first_prof[i] = col - 3;
+                    max_q = std::max(max_q, q);
+                    ck = (++n_slice == 1 && q < (1ll << 40)) ? (((unsigned long long)(col - 2)) << 40 | (unsigned long long)q) : CLS_MULTI;
+                } else other = true;
+            }
+            cls[i] = ck;
+            const long long bc = pods->base[3 * (size_t)i], bm = pods->base[3 * (size_t)i + 1], be = pods->base[3 * (size_t)i + 2];
+            if ((bc | bm | be) < 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: negative cpu / memory / ephemeral-storage request", i);
+            uint32_t f = 0;
+            if (!prefilter_ok || prefilter_ok[i]) f |= PF_PRE_OK;
+            if (other) { f |= PF_HAS_OTHER; any_other = true; }
+            if (a == b && (bc | bm | be) == 0) { f |= PF_ZERO_REQ; any_zero = true; }
+            flags[i] = f;
+            or_cpu |= (unsigned long long)bc; or_mem |= (unsigned long long)bm; any_eph |= be;
+            max_cpu = std::max(max_cpu, bc); max_mem = std::max(max_mem, bm);
+            const int k = pods->tracker_key[i];
+            if (k < 0 || k >= P) return fail(h, NOSPLAN_E_INVALID, "pod %d: tracker_key out of range", i);
+            if (key_seen[k]) keys_unique = false;
+            key_seen[k] = 1;
+            n_keys = std::max(n_keys, k + 1);
+        }
+        if (n_keys > sweep_max_keys()) return fail(h, NOSPLAN_E_LIMIT, "%d tracker keys > %d", n_keys, sweep_max_keys());
+        lap("pod keys");
+
+        // ---- NewPodSorter (core/util.go:34-73)
+        std::vector<int>& order = h->v_order;
+        pod_order(s, pods, first_prof.data(), order);
+        lap("sort");
+
+        // ---- pass 2a (sorted order): runs of identical slice requests; 32-pod chunks are run-relative
+        std::vector<RunRec>& runs = h->v_runs; runs.clear();
+        std::vector<int32_t>& run_chunk_off = h->v_chunk_off; run_chunk_off.clear();
+        auto same_entries = [&](int x, int y) {
+            int ex = pods->scalar_ptr[x], ey = pods->scalar_ptr[y];
+            const int bx = pods->scalar_ptr[x + 1], by = pods->scalar_ptr[y + 1];
+            for (;;) {
+                const bool sx = ex < bx && pods->scalar_col[ex] < 3 + K, sy = ey < by && pods->scalar_col[ey] < 3 + K;
+                if (!sx || !sy) return sx == sy;
+                if (pods->scalar_col[ex] != pods->scalar_col[ey] || pods->scalar_qty[ex] != pods->scalar_qty[ey]) return false;
+                ++ex; ++ey;
+            }
+        };
+        single_profile_classes = true;
+        n_chunks = 0;
+        for (int si = 0, prev_oi = -1; si < P; ++si) {
             const int oi = order[si];
             const bool same = si > 0 && cls[oi] == cls[prev_oi] && (cls[oi] != CLS_MULTI || same_entries(prev_oi, oi));
             if (!same) {
+                if (!runs.empty()) n_chunks += (runs.back().len + 31) >> 5;
                 RunRec r; std::memset(&r, 0, sizeof r);
                 r.start = si;
                 for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1] && pods->scalar_col[e] < 3 + K; ++e) {
@@ -680,117 +892,109 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
                 }
                 if (r.n_ent > 1) single_profile_classes = false;
                 runs.push_back(r);
-                run_chunk_off.push_back((int32_t)(cmin.size() / 3));
-                in_run = 0;
+                run_chunk_off.push_back(n_chunks);
             }
-            if ((in_run & 31) == 0) { cmin.insert(cmin.end(), 3, LLONG_MAX); cm = cmin.data() + cmin.size() - 3; }
-            ++in_run; runs.back().len = in_run;
+            runs.back().len++;
             prev_oi = oi;
-            const long long bc = pods->base[3 * (size_t)oi], bm = pods->base[3 * (size_t)oi + 1], be = pods->base[3 * (size_t)oi + 2];
-            const uint32_t f = flags[oi];
-            if (f & PF_PRE_OK) {
-                const bool z = (f & PF_ZERO_REQ) != 0;
-                cm[0] = std::min(cm[0], z ? LLONG_MIN : bc); cm[1] = std::min(cm[1], z ? LLONG_MIN : bm); cm[2] = std::min(cm[2], z ? LLONG_MIN : be);
-            }
-            cpu[si] = bc; mem[si] = bm; eph[si] = be; any_eph |= be;
-            key[si] = pods->tracker_key[oi]; fl[si] = f;
-            sptr[si] = w;
-            for (int e = pods->scalar_ptr[oi]; e < pods->scalar_ptr[oi + 1]; ++e) { scol[w] = pods->scalar_col[e]; sqty[w] = pods->scalar_qty[e]; ++w; }
         }
-        sptr[P] = w;
-    }
-    const int n_runs = (int)runs.size();
-    const int n_chunks = (int)(cmin.size() / 3);
-    run_chunk_off.push_back(n_chunks);
-    lap("runs+stage");
+        if (!runs.empty()) n_chunks += (runs.back().len + 31) >> 5;
+        n_runs = (int)runs.size();
+        run_chunk_off.push_back(n_chunks);
+        lap("runs");
 
-    // ---- layout, part 2
-    o = part1_end;
-    put(L.runs, sizeof(RunRec) * (size_t)n_runs);
-    put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
-    put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
-    // ---- single-launch plan (fused.cu), pod-side conditions: single-profile classes in at most FRUN_MAX runs, one tracker
-    //      entry per pod, only cpu / memory / slice requests, and requests that fit the compact int32 units
-    int cpu_shift = 0, mem_shift = 0, pad_pods = 0;
-    unsigned rset = 0;
-    fused_ok = fused_ok && single_profile_classes && n_runs <= FRUN_MAX && keys_unique && any_eph == 0 && !any_zero &&
-               !(any_other && filter_mode == NOSPLAN_FILTER_RESOURCES_FIT) && max_q <= 1;
-    if (fused_ok) {
-        cpu_shift = or_cpu ? __builtin_ctzll(or_cpu) : 0; mem_shift = or_mem ? __builtin_ctzll(or_mem) : 0;
-        fused_ok = (max_cpu >> cpu_shift) < F_COST_LIMIT && (max_mem >> mem_shift) < F_COST_LIMIT;
-        for (const RunRec& r : runs) { pad_pods += (r.len + 63) & ~63; if (r.n_ent) rset |= 1u << r.p_single; }
-        fused_ok = fused_ok && pad_pods <= fused_max_pad_pods() && rset != 0;
-    }
-    // the blob: header [geometry rows | key masks | model ranges | runs | runs per profile], then (cpu, memory) pairs
-    // [minima per 512 | per 64 | per 8 | pods]; every section starts on a 16-byte boundary
-    int fp_off[9] = {0};
-    {
-        auto a16 = [](size_t x) { return (int)((x + 15) & ~(size_t)15); };
-        const int n3 = (pad_pods + 511) / 512, n2 = pad_pods / 64, n1 = pad_pods / 8;
-        fp_off[0] = a16(16 * (size_t)n_rows);
-        fp_off[1] = fp_off[0] + a16(2 * (size_t)n_rows);
-        fp_off[2] = fp_off[1] + a16(4 * ((size_t)n_models + 1));
-        fp_off[3] = fp_off[2] + a16(sizeof(FRun) * (size_t)n_runs);
-        fp_off[4] = fp_off[3] + a16(8 * (KP + 1));
-        fp_off[5] = fp_off[4] + a16(8 * (size_t)n3);
-        fp_off[6] = fp_off[5] + a16(8 * (size_t)n2);
-        fp_off[7] = fp_off[6] + a16(8 * (size_t)n1);
-        fp_off[8] = fp_off[7] + a16(8 * (size_t)pad_pods);
-    }
-    if (fused_ok) put(L.fp_blob, (size_t)fp_off[8]); else L.fp_blob = o;
-    L.upload_end = o;
-    L.total = o;
-    if (L.total > bound) return fail(h, NOSPLAN_E_NOMEM, "internal: arena bound exceeded");
-    if (n_runs) std::memcpy(S + L.runs, runs.data(), sizeof(RunRec) * (size_t)n_runs);
-    std::memcpy(S + L.run_chunk_off, run_chunk_off.data(), 4 * ((size_t)n_runs + 1));
-    {
-        long long* c0 = (long long*)(S + L.cmin_cpu); long long* c1 = (long long*)(S + L.cmin_mem); long long* c2 = (long long*)(S + L.cmin_eph);
-        for (int c = 0; c < n_chunks; ++c) { c0[c] = cmin[3 * (size_t)c]; c1[c] = cmin[3 * (size_t)c + 1]; c2[c] = cmin[3 * (size_t)c + 2]; }
-    }
-    if (fused_ok) {
-        // padded position space: run r occupies [pos0, pos0 + 64 * nblk); a pod that can never be placed (PreFilter verdict
-        // false) and every padding slot cost F_NONE; minima per 8 and per 64 positions and per run
-        unsigned char* B = S + L.fp_blob;
-        int32_t* l3 = (int32_t*)(B + fp_off[4]); int32_t* l2 = (int32_t*)(B + fp_off[5]); int32_t* l1 = (int32_t*)(B + fp_off[6]);
-        int32_t* fpod = (int32_t*)(B + fp_off[7]);
-        FRun* fr = (FRun*)(B + fp_off[2]);
-        unsigned long long* prof_runs = (unsigned long long*)(B + fp_off[3]);
-        std::memset(B, 0, (size_t)fp_off[4]);
-        if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
-        for (int r = 0; r < n_rows; ++r) {
-            uint16_t m = 0;
-            for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p]) m |= (uint16_t)(1u << p);
-            ((uint16_t*)(B + fp_off[0]))[r] = m;
+        // ---- layout, part 2
+        o = part1_end;
+        put(L.runs, sizeof(RunRec) * (size_t)n_runs);
+        put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
+        put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
+        // ---- single-launch plan (fused.cu), pod-side conditions: single-profile classes in at most FRUN_MAX runs, one tracker
+        //      entry per pod, only cpu / memory / slice requests, and requests that fit the compact int32 units
+        fused_ok = fused_ok && single_profile_classes && n_runs <= FRUN_MAX && keys_unique && any_eph == 0 && !any_zero &&
+                   !(any_other && filter_mode == NOSPLAN_FILTER_RESOURCES_FIT) && max_q <= 1;
+        if (fused_ok) {
+            cpu_shift = or_cpu ? __builtin_ctzll(or_cpu) : 0; mem_shift = or_mem ? __builtin_ctzll(or_mem) : 0;
+            fused_ok = (max_cpu >> cpu_shift) < F_COST_LIMIT && (max_mem >> mem_shift) < F_COST_LIMIT;
+            for (const RunRec& r : runs) { pad_pods += (r.len + 63) & ~63; if (r.n_ent) rset |= 1u << r.p_single; }
+            fused_ok = fused_ok && pad_pods <= fused_max_pad_pods() && rset != 0;
         }
-        if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
-        const long long* cpu = (const long long*)(S + L.pod_cpu); const long long* mem = (const long long*)(S + L.pod_mem);
-        const uint32_t* fl = (const uint32_t*)(S + L.pod_flags);
-        std::fill(l3, (int32_t*)(B + fp_off[8]), (int32_t)F_NONE);
-        int pos = 0;
-        for (int r = 0; r < n_runs; ++r) {
-            const RunRec& rr = runs[r];
-            FRun f; std::memset(&f, 0, sizeof f);
-            f.pos0 = pos; f.nblk = (rr.len + 63) >> 6; f.n_real = rr.len;
-            f.p = rr.n_ent ? (int)rr.p_single : -1; f.q = rr.n_ent ? (int)rr.q[rr.p_single] : 0;
-            f.min_c = f.min_m = F_NONE;
-            for (int k = 0; k < rr.len; ++k) {
-                const int si = rr.start + k, x = pos + k;
-                if (!(fl[si] & PF_PRE_OK)) continue;
-                const int32_t c = (int32_t)(cpu[si] >> cpu_shift), m = (int32_t)(mem[si] >> mem_shift);
-                fpod[2 * (size_t)x] = c; fpod[2 * (size_t)x + 1] = m;
-                int32_t* a = l1 + 2 * (size_t)(x >> 3); int32_t* b = l2 + 2 * (size_t)(x >> 6); int32_t* d = l3 + 2 * (size_t)(x >> 9);
-                a[0] = std::min(a[0], c); a[1] = std::min(a[1], m); b[0] = std::min(b[0], c); b[1] = std::min(b[1], m);
-                d[0] = std::min(d[0], c); d[1] = std::min(d[1], m);
-                f.min_c = std::min(f.min_c, c); f.min_m = std::min(f.min_m, m);
+        // the blob: header [geometry rows | key masks | model ranges | runs | runs per profile], then (cpu, memory) pairs
+        // [minima per 512 | per 64 | per 8 | pods]; every section starts on a 16-byte boundary
+        {
+            auto a16 = [](size_t x) { return (int)((x + 15) & ~(size_t)15); };
+            const int n3 = (pad_pods + 511) / 512, n2 = pad_pods / 64, n1 = pad_pods / 8;
+            fp_off[0] = a16(16 * (size_t)n_rows);
+            fp_off[1] = fp_off[0] + a16(2 * (size_t)n_rows);
+            fp_off[2] = fp_off[1] + a16(4 * ((size_t)n_models + 1));
+            fp_off[3] = fp_off[2] + a16(sizeof(FRun) * (size_t)n_runs);
+            fp_off[4] = fp_off[3] + a16(8 * (KP + 1));
+            fp_off[5] = fp_off[4] + a16(8 * (size_t)n3);
+            fp_off[6] = fp_off[5] + a16(8 * (size_t)n2);
+            fp_off[7] = fp_off[6] + a16(8 * (size_t)n1);
+            fp_off[8] = fp_off[7] + a16(8 * (size_t)pad_pods);
+        }
+        if (fused_ok) put(L.fp_blob, (size_t)fp_off[8]); else L.fp_blob = o;
+        L.upload_end = o;
+        L.total = o;
+        if (L.total > bound) return fail(h, NOSPLAN_E_NOMEM, "internal: arena bound exceeded");
+        h->lay = L;
+        if (fused_ok) {
+            // padded position space: run r occupies [pos0, pos0 + 64 * nblk); a pod that can never be placed (PreFilter verdict
+            // false) and every padding slot cost F_NONE; minima per 8, 64 and 512 positions and per run
+            unsigned char* B = S + L.fp_blob;
+            int32_t* l3 = (int32_t*)(B + fp_off[4]); int32_t* l2 = (int32_t*)(B + fp_off[5]); int32_t* l1 = (int32_t*)(B + fp_off[6]);
+            int32_t* fpod = (int32_t*)(B + fp_off[7]);
+            FRun* fr = (FRun*)(B + fp_off[2]);
+            unsigned long long* prof_runs = (unsigned long long*)(B + fp_off[3]);
+            std::memset(B, 0, (size_t)fp_off[4]);
+            if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
+            for (int r = 0; r < n_rows; ++r) {
+                uint16_t m = 0;
+                for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p]) m |= (uint16_t)(1u << p);
+                ((uint16_t*)(B + fp_off[0]))[r] = m;
             }
-            fr[r] = f;
-            prof_runs[f.p >= 0 ? f.p : KP] |= 1ull << r;
-            pos += f.nblk * 64;
+            if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
+            std::fill(l3, (int32_t*)(B + fp_off[8]), (int32_t)F_NONE);
+            int pos = 0;
+            for (int r = 0; r < n_runs; ++r) {
+                const RunRec& rr = runs[r];
+                FRun f; std::memset(&f, 0, sizeof f);
+                f.pos0 = pos; f.nblk = (rr.len + 63) >> 6; f.n_real = rr.len;
+                f.p = rr.n_ent ? (int)rr.p_single : -1; f.q = rr.n_ent ? (int)rr.q[rr.p_single] : 0;
+                f.min_c = f.min_m = F_NONE;
+                for (int k = 0; k < rr.len; ++k) {
+                    const int oi = order[rr.start + k], x = pos + k;
+                    if (!(flags[oi] & PF_PRE_OK)) continue;
+                    const int32_t c = (int32_t)(pods->base[3 * (size_t)oi] >> cpu_shift), m = (int32_t)(pods->base[3 * (size_t)oi + 1] >> mem_shift);
+                    fpod[2 * (size_t)x] = c; fpod[2 * (size_t)x + 1] = m;
+                    int32_t* a = l1 + 2 * (size_t)(x >> 3);
+                    a[0] = std::min(a[0], c); a[1] = std::min(a[1], m);
+                }
+                // the coarser minima from the finer ones
+                for (int x8 = pos >> 3; x8 < (pos >> 3) + f.nblk * 8; ++x8) {
+                    const int32_t c = l1[2 * (size_t)x8], m = l1[2 * (size_t)x8 + 1];
+                    int32_t* b = l2 + 2 * (size_t)(x8 >> 3); int32_t* d = l3 + 2 * (size_t)(x8 >> 6);
+                    b[0] = std::min(b[0], c); b[1] = std::min(b[1], m); d[0] = std::min(d[0], c); d[1] = std::min(d[1], m);
+                    f.min_c = std::min(f.min_c, c); f.min_m = std::min(f.min_m, m);
+                }
+                fr[r] = f;
+                prof_runs[f.p >= 0 ? f.p : KP] |= 1ull << r;
+                pos += f.nblk * 64;
+            }
         }
+        lap("blob");
+        // ---- the classic kernels' pod arrays: now, unless this is one nosplan_plan / nosplan_plan_resident call planning with the
+        //      single-launch kernel (then only if that plan is rejected, see nosplan_reject_to_classic)
+        lazy = fused_ok && h->in_plan;
+        h->classic_staged = !lazy;
+        h->lazy_valid = lazy; h->lazy_pods = *pods; h->lazy_pre = prefilter_ok; h->lazy_filter = filter_mode;
+        if (!lazy) stage_classic_pods(h, pods, K);
+        lap("classic stage");
+        CU(h, cudaEventRecord(h->ev[9], h->stream));
+        up_from = lazy ? L.fp_blob : L.pod_cpu;
+        CU(h, cudaMemcpyAsync(A + up_from, S + up_from, L.upload_end - up_from, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaEventRecord(h->ev[10], h->stream));
+
     }
-    CU(h, cudaEventRecord(h->ev[9], h->stream));
-    CU(h, cudaMemcpyAsync(A + L.pod_cpu, S + L.pod_cpu, L.upload_end - L.pod_cpu, cudaMemcpyHostToDevice, h->stream));
-    CU(h, cudaEventRecord(h->ev[10], h->stream));
 
     // ---- device problem description, pod side
     pb.n_keys = n_keys; pb.n_runs = n_runs;
@@ -815,7 +1019,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     pb.fp_n_runs = fused_ok ? n_runs : 0; pb.fp_pad_pods = pad_pods; pb.fp_cpu_shift = cpu_shift; pb.fp_mem_shift = mem_shift; pb.fp_rset = rset;
     h->fused_ok = fused_ok; h->fused_pending = false; h->placed_dirty = false;
     lap("pods queued");
-    h->h2d_bytes = (keep ? 0 : L.nodes_end) + (L.upload_end - L.pod_cpu);
+    h->h2d_bytes = (keep ? 0 : L.nodes_end) + (L.upload_end - up_from);
     h->uploaded = true;
     if (!keep) {                                             // what a later nosplan_plan_resident / nosplan_update_nodes needs
         h->res_snap = *s;
@@ -1110,6 +1314,19 @@ int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count, void** d_gpu_mask) 
 static int nosplan_reject_to_classic(nosplan* h, int reasons) {
     float t = 0.f;
     cudaEventElapsedTime(&t, h->ev[2], h->ev[3]);
+    if (!h->classic_staged) {
+        // the call that uploaded this problem staged only what the single-launch kernel reads: the pods go through the general
+        // path now (the node arrays are still in the arena), and the classic sequence plans
+        if (!h->lazy_valid) return fail(h, NOSPLAN_E_INVALID, "the single-launch plan was rejected and the pods of that nosplan_plan call are gone: call nosplan_plan again");
+        const nosplan_pods pods = h->lazy_pods;
+        h->force_classic = true; h->in_plan = true;
+        int rc0 = upload_impl(h, &h->res_snap, &pods, h->lazy_pre, h->lazy_filter, true);
+        h->force_classic = false; h->in_plan = false;
+        if (rc0 == NOSPLAN_OK) rc0 = h->pre_done ? run_post(h) : run_classic(h);
+        h->fused_reject = reasons; h->ms_rejected = t;
+        h->launches += 1;
+        return rc0;
+    }
     const int rc = h->rerun ? h->rerun(h) : run_classic(h);
     h->fused_reject = reasons; h->ms_rejected = t;
     h->launches += 1;
@@ -1198,8 +1415,10 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
     h->in_plan = false;
     if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); return rc; }
     rc = h->pre_done ? run_post(h) : nosplan_run(h);       // upload() already queued the node-only kernels
-    if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); return rc; }
-    return nosplan_download(h, out, stats);
+    if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); h->lazy_valid = false; return rc; }
+    rc = nosplan_download(h, out, stats);            // a rejected single-launch plan is re-planned inside this call
+    h->lazy_valid = false;
+    return rc;
 }
 
 int nosplan_plan_resident(nosplan_t* h, const nosplan_pods* pods, const uint8_t* prefilter_ok, int32_t filter_mode,
@@ -1211,8 +1430,10 @@ int nosplan_plan_resident(nosplan_t* h, const nosplan_pods* pods, const uint8_t*
     h->in_plan = false;
     if (rc != NOSPLAN_OK) return rc;
     rc = h->pre_done ? run_post(h) : nosplan_run(h);
-    if (rc != NOSPLAN_OK) return rc;
-    return nosplan_download(h, out, stats);
+    if (rc != NOSPLAN_OK) { h->lazy_valid = false; return rc; }
+    rc = nosplan_download(h, out, stats);
+    h->lazy_valid = false;
+    return rc;
 }
 
 int nosplan_upload_pods(nosplan_t* h, const nosplan_pods* pods, const uint8_t* prefilter_ok, int32_t filter_mode) {

@@ -8,6 +8,16 @@
 struct nosplan_quota_ctx;
 struct nosplan_shard_ctx;          // in-library NCCL state of the node-sharded Plan() (shard_nccl.cu)
 
+namespace nsp {
+struct Layout {            // byte offsets into the arena / staging buffer
+    size_t model_off, geom, node_gpu_count, gpu_model, gpu_mem, gpu_used, gpu_free, gpu_umask, gpu_fmask,
+        node_alloc, node_req, node_allowed, node_npods, nodes_end,
+        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, wave, work_end, cand_flag, cand_idx, out_count, out_mask, out_end,
+        pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
+        cmin_cpu, cmin_mem, cmin_eph, fp_blob, upload_end, placed, entry_lack, total;
+};
+}  // namespace nsp
+
 struct nosplan {
     int device = -1;
     cudaStream_t stream = nullptr;
@@ -38,7 +48,14 @@ struct nosplan {
     // bits in `placed`; SM count of this handle's device
     bool fused_ok = false, fused_pending = false, placed_dirty = false;
     bool last_fused = false; int fused_reject = 0; float ms_rejected = 0.f;   // what the last run was; why / how long a rejected attempt took
-    int (*rerun)(nosplan*) = nullptr;           // the classic form of the last run: what a rejected single-launch plan is replaced by
+    int (*rerun)(nosplan*) = nullptr;
+    // nosplan_plan / nosplan_plan_resident stage only what the single-launch kernel reads; the classic kernels' pod arrays are
+    // staged (from the caller's arrays, still valid inside that call) only if the single-launch plan is rejected
+    nsp::Layout lay{};
+    bool classic_staged = true, lazy_valid = false;
+    nosplan_pods lazy_pods{}; const uint8_t* lazy_pre = nullptr; int lazy_filter = 0;
+    bool force_classic = false;                 // the general pod path and the classic kernels, whatever the problem looks like
+    std::vector<uint16_t> v_bucket;           // the classic form of the last run: what a rejected single-launch plan is replaced by
     int sms = 148;
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;

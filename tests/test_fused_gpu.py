@@ -177,6 +177,36 @@ def test_fused_with_a_pod_list_larger_than_shared_memory(eng):
         assert st["fused"] == 1
 
 
+def test_fast_and_general_pod_paths_agree(eng):
+    """nosplan_plan stages the pods for the single-launch kernel in two passes when it can; NOSPLAN_NO_FAST_PODS sends them
+    through the general path (NewPodSorter as a sort, runs, blob).  Same plan, same counters, whatever the pods look like;
+    and a plan rejected after the fast path is re-planned through the general path inside the same call."""
+    rng = np.random.default_rng(17)
+    for seed, n_pods in ((1, 3000), (2, 1200), (3, 9000)):
+        s, p = synth.mig_cluster(250, 8, n_pods, seed=100 + seed)
+        p.priority[:] = rng.choice([-5, 0, 7, 100, 1000, 2_000_000_000], n_pods)
+        pre = (rng.random(n_pods) < 0.8).astype(np.uint8)
+        cnt, msk, st = check(eng, s, p, pre, pk.FILTER_RESOURCES_FIT, f"fast path seed {seed}")
+        assert st["fused"] == 1
+        os.environ["NOSPLAN_NO_FAST_PODS"] = "1"
+        try:
+            gcnt, gmsk, gst = eng.plan(s, p, pre, pk.FILTER_RESOURCES_FIT)
+        finally:
+            del os.environ["NOSPLAN_NO_FAST_PODS"]
+        assert gst["fused"] == 1 and np.array_equal(cnt, gcnt) and np.array_equal(msk, gmsk)
+        for k in COUNTERS:
+            assert st[k] == gst[k]
+        assert st["h2d_bytes"] <= gst["h2d_bytes"]
+    # rejected after the fast path: satisfiable demand, and resident calls on top of it
+    s, p = synth.mig_cluster(200, 8, 1000, seed=5, regime="satisfiable")
+    _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "satisfiable after fast path")
+    assert st["fused"] == 0 and st["fused_reject"] & REJ_HYPOTHESIS
+    p2 = synth.mig_cluster(200, 8, 700, seed=6, regime="satisfiable")[1]
+    rcnt, rmsk, rst = eng.plan_resident(p2, None, pk.FILTER_RESOURCES_FIT)
+    o = ol.plan(s, p2, None, pk.FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+    assert np.array_equal(rcnt, o[0]) and np.array_equal(rmsk, o[1]) and rst["placements"] == o[2]["placements"]
+
+
 def test_fused_north_star_size(eng):
     s, p = synth.mig_cluster(10000, 8, 10000, seed=0xC5)
     _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "10k x 10k")
