@@ -183,7 +183,8 @@ int nosplan_set_kernel_events(nosplan_t* h, int32_t on);
 
 /* Node-sharded Plan() over `world` ranks -- one handle per rank (one process per GPU), the SAME snapshot uploaded on
  * every rank (the reference's Plan() is single-process, core/planner.go:67-153, so there is no
- * counterpart call).  Each rank runs the node-parallel pass on its slice [rank*N/world, (rank+1)*N/world) of the
+ * counterpart call).  Each rank runs the node-parallel pass on its slice [lo, hi), chunk = ceil(N/world), lo = min(N, rank*chunk),
+ * hi = min(N, lo+chunk) (equal-sized chunks, the last possibly short or empty, so that the rows all-gather), of the
  * name-ordered node list.  The only data-path exchange is one all-gather of nosplan_shard_exchange_bytes() per rank:
  * 4 counters and the bitmap of tracker keys its nodes placed.
  *   begin(): cluster totals and tracker initialisation (replicated: cheaper than a collective), node-parallel pass on

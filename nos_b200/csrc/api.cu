@@ -20,13 +20,13 @@ namespace nsp {
 void launch_prepass(const DevProblem& pb, cudaStream_t st);
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
-cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st);
-cudaError_t launch_waves(const DevProblem& pb, cudaStream_t st);
+cudaError_t launch_parallel(const DevProblem& pb, int max_blocks, cudaStream_t st);
+cudaError_t launch_waves(const DevProblem& pb, int max_blocks, cudaStream_t st);
 void launch_shard_combine(const DevProblem& pb, const void* gathered, int world, size_t stride, const PeerWait& wait, cudaStream_t st);
 void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st);
 void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, const PeerWait& wait, cudaStream_t st);
 
-cudaError_t sweep_prepare_device();
+cudaError_t sweep_prepare_device(int* par_blocks, int* wave_blocks);
 int sweep_max_keys();
 cudaError_t fused_prepare_device();
 cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st);
@@ -289,6 +289,7 @@ void nosplan_phase_times(nosplan* h, nosplan_stats* stats) {
     } else cudaEventElapsedTime(&stats->ms_kernels, h->ev[2], h->ev[3]);
     stats->ms_kernels += h->ms_rejected;              // a rejected single-launch attempt in front of the classic sequence
     if (h->last_fused) stats->ms_parallel = stats->ms_kernels;
+    else if (h->prepass_only) stats->ms_prepass = stats->ms_kernels;
     else if (h->kernel_events) {
         cudaEventElapsedTime(&stats->ms_prepass, h->ev[2], h->ev[6]);
         cudaEventElapsedTime(&stats->ms_tracker, h->ev[h->split_run ? 11 : 6], h->ev[7]);
@@ -309,7 +310,7 @@ int nosplan_create(int cuda_device, nosplan_t** out) {
     h->device = cuda_device;
     int sms = 148;
     if (cudaSetDevice(cuda_device) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        sweep_prepare_device() != cudaSuccess || fused_prepare_device() != cudaSuccess ||
+        sweep_prepare_device(&h->par_blocks, &h->wave_blocks) != cudaSuccess || fused_prepare_device() != cudaSuccess ||
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cuda_device) != cudaSuccess) {
         delete h;
         return NOSPLAN_E_CUDA;
@@ -380,7 +381,7 @@ static void flip_small_state(nosplan* h) {
 static int run_pre(nosplan* h, bool split) {
     CU(h, cudaEventRecord(h->ev[2], h->stream));
     flip_small_state(h);
-    h->fused_pending = false; h->last_fused = false; h->fused_reject = 0; h->ms_rejected = 0.f;
+    h->fused_pending = false; h->last_fused = false; h->fused_reject = 0; h->ms_rejected = 0.f; h->prepass_only = false;
     h->placed_dirty = true;                  // the classic kernels index `placed` by tracker key
     launch_prepass(h->pb, h->stream);
     if (split || h->kernel_events) CU(h, cudaEventRecord(h->ev[6], h->stream));
@@ -566,6 +567,9 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         if (L.nodes_end > from) CU(h, cudaMemcpyAsync(A + from, S + from, L.nodes_end - from, cudaMemcpyHostToDevice, h->stream));
     }
     h->direct_h2d = any_direct;
+    // nothing of the caller's may be in flight when this call returns, with an error as well: outside nosplan_plan (which
+    // synchronises itself) every return below waits for the copies queued above
+    struct InFlight { cudaStream_t st; bool armed; ~InFlight() { if (armed) cudaStreamSynchronize(st); } } in_flight{h->stream, any_direct && !h->in_plan};
     CU(h, cudaMemsetAsync(A + L.tot, 0, L.out_end - L.tot, h->stream));       // per-run state (both copies) ... plan rows
     CU(h, cudaEventRecord(h->ev[1], h->stream));
 
@@ -817,7 +821,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         n_keys = 0;
         std::vector<uint8_t>& key_seen = h->v_key_seen; key_seen.assign(P, 0);
         bool keys_unique = true, any_other = false, any_zero = false;
-        long long max_q = 0;
+        long long max_q = 0, sum_q[KP] = {0};
         unsigned long long or_cpu = 0, or_mem = 0;
         long long max_cpu = 0, max_mem = 0;
         any_eph = 0;
@@ -833,6 +837,9 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
                 if (col < 3 + K) {
                     const long long q = pods->scalar_qty[e];
                     if (q <= 0) return fail(h, NOSPLAN_E_INVALID, "pod %d: slice request quantity must be >= 1", i);
+                    // the kernels keep lacking quantities in int32 (the reference in Go's 64-bit int): refuse what could wrap
+                    if (q >= (1ll << 31) || (sum_q[col - 3] += q) >= (1ll << 31))
+                        return fail(h, NOSPLAN_E_LIMIT, "pod %d: requested quantities of slice column %d reach 2^31", i, col);
                     if (first_prof[i] < 0) first_prof[i] = col - 3;
                     max_q = std::max(max_q, q);
                     ck = (++n_slice == 1 && q < (1ll << 40)) ? (((unsigned long long)(col - 2)) << 40 | (unsigned long long)q) : CLS_MULTI;
@@ -1038,7 +1045,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         h->res_nodes_end = L.nodes_end;
         h->nodes_resident = true;
     }
-    if (any_direct && !h->in_plan) CU(h, cudaStreamSynchronize(h->stream));   // nothing of the caller's is read after return
+    if (in_flight.armed) { in_flight.armed = false; CU(h, cudaStreamSynchronize(h->stream)); }   // nothing of the caller's is read after return
     return NOSPLAN_OK;
 }
 
@@ -1061,9 +1068,9 @@ static int run_post(nosplan* h) {
     if (work) {
         DevProblem p2 = h->pb;
         p2.verify_inline = 1;
-        CU(h, launch_parallel(p2, h->stream));
+        CU(h, launch_parallel(p2, h->par_blocks, h->stream));
         if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
-        CU(h, launch_waves(p2, h->stream));
+        CU(h, launch_waves(p2, h->wave_blocks, h->stream));
     } else {
         if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
         CU(h, launch_sweep(h->pb, h->d_cand_idx, h->stream));
@@ -1136,7 +1143,7 @@ int nosplan_shard_begin(nosplan_t* h, int32_t rank, int32_t world, void* d_excha
     shard.acc = static_cast<unsigned long long*>(d_exchange);
     shard.placed = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(d_exchange) + 32);
     CU(h, cudaGetLastError());
-    CU(h, launch_parallel(shard, h->stream));
+    CU(h, launch_parallel(shard, h->par_blocks, h->stream));
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
     h->launches = (h->pb.N > 0) + (h->pb.P > 0) + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     return NOSPLAN_OK;
@@ -1176,7 +1183,7 @@ int nosplan_slice_mid_ex(nosplan* h, int32_t rank, int32_t world, const void* d_
     shard.acc = static_cast<unsigned long long*>(d_exchange);
     shard.placed = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(d_exchange) + 32);
     CU(h, cudaGetLastError());
-    CU(h, launch_parallel(shard, h->stream));
+    CU(h, launch_parallel(shard, h->par_blocks, h->stream));
     if (h->kernel_events) CU(h, cudaEventRecord(h->ev[8], h->stream));
     h->launches += 1 + (h->pb.P > 0) + (h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0);
     return NOSPLAN_OK;
@@ -1191,7 +1198,7 @@ int nosplan_shard_end_ex(nosplan* h, const void* d_gathered, int32_t world, size
     DevProblem verify = h->pb;
     verify.whole_snapshot = 0;                               // final lacking vector comes from the OR-ed bitmap
     CU(h, launch_sweep(verify, h->d_cand_idx, h->stream));
-    if (!verify.slice_mode) CU(h, launch_waves(verify, h->stream));
+    if (!verify.slice_mode) CU(h, launch_waves(verify, h->wave_blocks, h->stream));
     CU(h, cudaEventRecord(h->ev[3], h->stream));
     h->launches += 2;
     h->ran = true;
@@ -1215,7 +1222,7 @@ int nosplan_run_sliced_fused(nosplan* h, const PeerBox& box, unsigned epoch, uns
         shard.acc = reinterpret_cast<unsigned long long*>(d_exchange);
         shard.placed = reinterpret_cast<unsigned*>(d_exchange + 32);
         cudaError_t e = cudaGetLastError();
-        if (e == cudaSuccess) e = launch_parallel(shard, h->stream);       // node-parallel pass (+ push of the exchange block)
+        if (e == cudaSuccess) e = launch_parallel(shard, h->par_blocks, h->stream);       // node-parallel pass (+ push of the exchange block)
         if (h->kernel_events) cudaEventRecord(h->ev[8], h->stream);
         DevProblem verify = pb;
         verify.whole_snapshot = 0;
@@ -1311,9 +1318,21 @@ int nosplan_device_outputs(nosplan_t* h, void** d_gpu_count, void** d_gpu_mask) 
 
 }  // extern "C"
 
-static int nosplan_reject_to_classic(nosplan* h, int reasons) {
+static int nosplan_reject_to_classic(nosplan* h, int reasons, int lacking_at_start) {
     float t = 0.f;
     cudaEventElapsedTime(&t, h->ev[2], h->ev[3]);
+    if (reasons == FREJ_HYPOTHESIS && lacking_at_start == 0 && !h->pb.slice_mode) {
+        // nothing is lacking at t0: Plan() returns the state as it is (planner.go:80-83) -- k_prepass alone writes exactly that
+        // (GetPartitioningState), and every counter is zero; no pod has to be staged for the classic kernels
+        const int rc = run_pre(h, false);
+        if (rc != NOSPLAN_OK) return rc;
+        CU(h, cudaMemsetAsync(h->pb.stats, 0, sizeof(DevStats), h->stream));
+        CU(h, cudaEventRecord(h->ev[3], h->stream));
+        h->launches += 1;
+        h->fused_reject = reasons; h->ms_rejected = t; h->prepass_only = true;
+        h->ran = true;
+        return NOSPLAN_OK;
+    }
     if (!h->classic_staged) {
         // the call that uploaded this problem staged only what the single-launch kernel reads: the pods go through the general
         // path now (the node arrays are still in the arena), and the classic sequence plans
@@ -1341,7 +1360,7 @@ int nosplan_resolve(nosplan* h) {
     CU(h, cudaStreamSynchronize(h->stream));
     h->fused_pending = false;
     if (ds->path != 2) return NOSPLAN_OK;
-    return nosplan_reject_to_classic(h, ds->pad);
+    return nosplan_reject_to_classic(h, ds->pad, ds->lacking_at_start);
 }
 
 extern "C" {
@@ -1376,7 +1395,7 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         h->fused_pending = false;
         DevStats ds; std::memcpy(&ds, O + o_stats, sizeof ds);
         if (ds.path != 2) break;
-        const int rc2 = nosplan_reject_to_classic(h, ds.pad);
+        const int rc2 = nosplan_reject_to_classic(h, ds.pad, ds.lacking_at_start);
         if (rc2 != NOSPLAN_OK) return rc2;
     }
     if (want && !direct) {

@@ -54,9 +54,10 @@ struct nosplan {
     nsp::Layout lay{};
     bool classic_staged = true, lazy_valid = false;
     nosplan_pods lazy_pods{}; const uint8_t* lazy_pre = nullptr; int lazy_filter = 0;
+    bool prepass_only = false;                  // the last run was k_prepass alone (nothing lacking after a rejected single-launch plan)
     bool force_classic = false;                 // the general pod path and the classic kernels, whatever the problem looks like
     std::vector<uint16_t> v_bucket;           // the classic form of the last run: what a rejected single-launch plan is replaced by
-    int sms = 148;
+    int sms = 148, par_blocks = 148 * 4, wave_blocks = 148 * 4;   // SM count and resident-wave grid sizes of this handle's device
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
     size_t h2d_bytes = 0;

@@ -1182,24 +1182,24 @@ size_t sweep_dyn_smem(const DevProblem& pb) { return SWEEP_CHUNK_BYTES + (size_t
 // largest number of tracker keys (distinct namespace/name of pending pods) the shared-memory bitmap can hold
 int sweep_max_keys() { return (int)((SWEEP_DYN_MAX - SWEEP_CHUNK_BYTES - 16) / 4) * 32; }
 
-static int g_par_blocks = 148 * 4, g_wave_blocks = 148 * 4;
-
-cudaError_t sweep_prepare_device() {
+// grid sizes of one resident wave on the CURRENT device (the handle's): kept in the handle, so that handles on GPUs with
+// different SM counts, or under an SM-limited context, never share them
+cudaError_t sweep_prepare_device(int* par_blocks, int* wave_blocks) {
     int dev = 0, sms = 148, per_sm = 4;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_plan_parallel, 128, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
-    g_par_blocks = sms * per_sm;                               // one resident wave, grid-stride over the nodes
+    *par_blocks = sms * per_sm;                                // one resident wave, grid-stride over the nodes
     int per_sm_w = 4;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_w, k_plan_waves, 128, 0) != cudaSuccess || per_sm_w < 1) per_sm_w = 2;
-    g_wave_blocks = sms * per_sm_w;                            // cooperative launch: every CTA must be resident
+    *wave_blocks = sms * per_sm_w;                             // cooperative launch: every CTA must be resident
     return cudaFuncSetAttribute(k_plan_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SWEEP_DYN_MAX);
 }
 
-cudaError_t launch_parallel(const DevProblem& pb, cudaStream_t st) {
+cudaError_t launch_parallel(const DevProblem& pb, int max_blocks, cudaStream_t st) {
     const bool work = pb.fast_eligible && pb.N > 0 && pb.P > 0 && pb.node_hi > pb.node_lo;
     if (!work && !pb.xf_on) return cudaSuccess;            // fused slice mode: the kernel still pushes this rank's (empty) block
     int blocks = work ? (pb.node_hi - pb.node_lo + 3) / 4 : 1;
-    if (blocks > g_par_blocks) blocks = g_par_blocks;
+    if (blocks > max_blocks) blocks = max_blocks;
     return launch_pdl(k_plan_parallel, dim3(blocks), dim3(128), 0, st, pb);
 }
 
@@ -1228,10 +1228,10 @@ void launch_shard_combine(const DevProblem& pb, const void* gathered, int world,
 }
 
 // always queued behind k_plan_sweep for problems the waves can take; returns at once unless k_plan_sweep handed over
-cudaError_t launch_waves(const DevProblem& pb, cudaStream_t st) {
+cudaError_t launch_waves(const DevProblem& pb, int max_blocks, cudaStream_t st) {
     if (!pb.fast_eligible || pb.N == 0 || pb.P == 0 || pb.slice_mode) return cudaSuccess;
     int blocks = (pb.N + 3) / 4;
-    if (blocks > g_wave_blocks) blocks = g_wave_blocks;
+    if (blocks > max_blocks) blocks = max_blocks;
     DevProblem arg = pb;
     void* args[] = {&arg};
     return cudaLaunchCooperativeKernel((const void*)k_plan_waves, dim3(blocks), dim3(128), args, 0, st);

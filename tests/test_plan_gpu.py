@@ -93,6 +93,55 @@ def test_helm_table_order(eng):
     check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "helm table")
 
 
+def c1_snapshot():
+    """BASELINE config #1 exactly as SURVEY.md section 8d specifies it: 1 node, 1 x NVIDIA-A100-40GB-SXM4 (the 12 allowed
+    geometries of pkg/gpu/mig/known_configs.go:41-90), free {7g.40gb: 1}, allocatable cpu 64 000 m / memory 512 GiB / pods 110;
+    10 pods, priority 0, alternating 1g.5gb:1 / 2g.10gb:1, cpu 100 m.  No RNG."""
+    from nos_b200.geometries import A100_40
+    s, p = synth.mig_cluster(1, 1, 10, seed=0, model=A100_40, regime="satisfiable", p_full_free=0.0, p_used=0.0)
+    prof = {n: i for i, n in enumerate(s.profiles)}
+    K = s.n_profiles
+    s.gpu_used[:] = 0; s.gpu_free[:] = 0; s.gpu_used_mask[:] = 0
+    s.gpu_free[0, prof["7g.40gb"]] = 1; s.gpu_free_mask[0] = 1 << prof["7g.40gb"]
+    s.node_alloc[:] = 0; s.node_requested[:] = 0
+    s.node_alloc[0, 0] = 64000; s.node_alloc[0, 1] = 512 << 30; s.node_alloc[0, 3 + prof["7g.40gb"]] = 1
+    s.node_allowed_pods[:] = 110; s.node_num_pods[:] = 0
+    p.priority[:] = 0
+    p.base[:] = 0; p.base[:, 0] = 100
+    p.scalar_col[:] = [3 + prof["1g.5gb" if i % 2 == 0 else "2g.10gb"] for i in range(10)]
+    p.scalar_qty[:] = 1
+    return s, p, prof, K
+
+
+def test_config_c1_exact(eng):
+    s, p, prof, K = c1_snapshot()
+    assert s.geom_counts.shape[0] == 12
+    for fm in (pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT):
+        cnt, msk, st = eng.plan(s, p, None, fm)
+        ocnt, omsk, ost, _ = ol.plan(s, p, None, fm, ol.INCREMENTAL)
+        assert np.array_equal(cnt, ocnt) and np.array_equal(msk, omsk)
+        for k in COUNTERS:
+            assert st[k] == ost[k], k
+        # the one GPU is re-partitioned away from {7g.40gb: 1}; both requested profiles appear and pods are placed on it
+        assert cnt[0, prof["7g.40gb"]] == 0 and cnt[0, prof["1g.5gb"]] > 0 and cnt[0, prof["2g.10gb"]] > 0
+        assert st["visited_nodes"] == 1 and st["candidates"] == 10 and st["placements"] > 0
+    # the faithful mode of the oracle (the reference's own asymptotics) agrees as well
+    fcnt, fmsk, fst, _ = ol.plan(s, p, None, pk.FILTER_RESOURCES_FIT, ol.FAITHFUL)
+    assert np.array_equal(cnt, fcnt) and np.array_equal(msk, fmsk)
+
+
+def test_config_c5_mixed_mig_and_mps(eng):
+    """BASELINE config #5 at its lower end in miniature and in full: a snapshot that is half MIG nodes (C2 recipe) and half
+    MPS nodes (C3 recipe), 50/50 requests, planned per kind as the reference's two planners do
+    (cmd/gpupartitioner/gpupartitioner.go:215-250: one controller per partitioning kind over the nodes of that kind)."""
+    for n, pods in ((200, 400), (10000, 10000)):
+        smig, pmig = synth.mig_cluster(n // 2, 8, pods // 2, seed=0xC5)
+        smps, pmps = synth.mps_cluster(n // 2, 8, pods // 2, seed=0xC5 + 1)
+        a = check(eng, smig, pmig, None, pk.FILTER_RESOURCES_FIT, f"C5 mig half {n}")
+        b = check(eng, smps, pmps, None, pk.FILTER_RESOURCES_FIT, f"C5 mps half {n}")
+        assert a["candidates"] == a["visited_nodes"] * (pods // 2) and b["candidates"] == b["visited_nodes"] * (pods // 2)
+
+
 def test_config_c2_full_size(eng):
     """BASELINE config #2: 1,000 nodes x 8 A100-80GB, 5,000 pending pods."""
     s, p = synth.mig_cluster(1000, 8, 5000, seed=0xC2)
@@ -139,6 +188,9 @@ def test_errors_are_reported_not_crashes(eng):
     s, p = synth.mig_cluster(4, 2, 8, seed=1)
     p.scalar_qty[0] = 0
     with pytest.raises(capi.NosplanError):
+        eng.plan(s, p, None, 0)
+    p.scalar_qty[0] = 1 << 31                              # the lacking quantities would not fit the kernels' int32
+    with pytest.raises(capi.NosplanError, match="2\\^31"):
         eng.plan(s, p, None, 0)
     p.scalar_qty[0] = 1
     with pytest.raises(capi.NosplanError):
