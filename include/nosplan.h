@@ -326,6 +326,17 @@ typedef struct nosplan_quota_out {     /* every pointer may be NULL = not wanted
 int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
                             const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats);
 
+/* The same with the pods split between the ranks of a multi-GPU job (after nosplan_shard_init; SURVEY.md section 8e: "quota
+ * sums reduced the same way").  Every rank passes the SAME quota tables and ITS OWN share of the running and pending pods;
+ * each rank reserves its pods into a Used that starts from zero (used_init counts on rank 0 only), the [E][Rq] int64 rows are
+ * summed over the ranks with one NCCL all-reduce and the key masks OR-ed (all-gather + fold) inside the call, and aggregates,
+ * guaranteed over-quotas and the PreFilter verdicts of the rank's own pending pods follow from the reduced rows -- identical,
+ * bit for bit, to one nosplan_quota_recompute over all pods (int64 sums and ORs are order-independent).  No counterpart in
+ * the reference (its plugin is one process); the rows replaced are elasticquotainfo.go:194-208,74-174.  over_quota /
+ * operator_used are computed from the rank's own pods only: route every quota's pods to one rank if they are wanted. */
+int nosplan_quota_recompute_sharded(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
+                                    const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats);
+
 /* Event-driven accounting on a quota state that stays in HBM -- the way the plugin itself keeps its ElasticQuotaInfos current:
  * the pod informer handlers and Reserve / Unreserve call AddPodIfNotPresent / DeletePodIfPresent
  * (pkg/scheduler/plugins/capacityscheduling/elasticquotainfo.go:276-310, capacity_scheduling.go:311-321,381-445), which

@@ -27,6 +27,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
     "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_upload_pods", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply", "nosplan_quota_state_prefilter",
+    "nosplan_quota_recompute_sharded",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -274,6 +275,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.nosplan_quota_recompute.argtypes = [C.c_void_p, C.POINTER(qp.CQuotas), C.POINTER(qp.CQuotaPods), C.POINTER(qp.CQuotaPods),
                                             C.POINTER(qp.CQuotaOut), C.POINTER(CStats)]
     lib.nosplan_quota_recompute.restype = C.c_int
+    lib.nosplan_quota_recompute_sharded.argtypes = lib.nosplan_quota_recompute.argtypes
+    lib.nosplan_quota_recompute_sharded.restype = C.c_int
     lib.nosplan_shard_exchange_bytes.argtypes = [C.c_void_p]
     lib.nosplan_shard_exchange_bytes.restype = C.c_int64
     lib.nosplan_shard_begin.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64]
@@ -644,8 +647,9 @@ class Engine:
         del k2
         return victim[:n_pods], status[:n_nodes], nviol[:n_nodes], st.as_dict()
 
-    def quota_recompute(self, pq, running=None, pending=None):
-        """nosplan_quota_recompute -> (dict of arrays as QuotaResult.trimmed(), stats dict)"""
+    def quota_recompute(self, pq, running=None, pending=None, sharded=False):
+        """nosplan_quota_recompute (sharded: nosplan_quota_recompute_sharded, this rank's share of the pods, after shard_init)
+        -> (dict of arrays as QuotaResult.trimmed(), stats dict)"""
         from . import quota_packing as qp
         cq, k1 = qp.c_quotas(pq)
         cr, k2 = qp.c_quota_pods(running)
@@ -653,7 +657,8 @@ class Engine:
         res = qp.QuotaResult(pq, running.n_pods if running else 0, pending.n_pods if pending else 0)
         out = res.c_struct()
         st = CStats()
-        rc = self.lib.nosplan_quota_recompute(self.h, C.byref(cq), C.byref(cr), C.byref(cp), C.byref(out), C.byref(st))
-        self._check(rc, "nosplan_quota_recompute")
+        fn = self.lib.nosplan_quota_recompute_sharded if sharded else self.lib.nosplan_quota_recompute
+        rc = fn(self.h, C.byref(cq), C.byref(cr), C.byref(cp), C.byref(out), C.byref(st))
+        self._check(rc, "nosplan_quota_recompute_sharded" if sharded else "nosplan_quota_recompute")
         del k1, k2, k3
         return res.trimmed(), st.as_dict()

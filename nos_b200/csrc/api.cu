@@ -42,7 +42,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
                                             const nosplan_quotas* qs, const nosplan_quota_pods* running,
                                             const nosplan_quota_pods* pending, nosplan_quota_out* out, float* ms_h2d, float* ms_k,
                                             float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes,
-                                            const nosplan_label_changes* lc);
+                                            const nosplan_label_changes* lc, const struct nosplan_quota_reduce_hook* hook);
 extern "C" void nosplan_quota_ctx_free(nosplan_quota_ctx* ctx);
 extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new();
 extern "C" int nosplan_quota_victims_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
@@ -1500,7 +1500,7 @@ int nosplan_quota_recompute(nosplan_t* h, const nosplan_quotas* quotas, const no
     if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
     float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
     const int rc = nosplan_quota_recompute_impl(h->device, h->stream, h->qctx, &h->err, quotas, running, pending, out, &a, &b, &c,
-                                                &launches, &hb, &db, nullptr);
+                                                &launches, &hb, &db, nullptr, nullptr);
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
@@ -1546,7 +1546,7 @@ int nosplan_quota_label_changes(nosplan_t* h, const nosplan_quotas* quotas, cons
     if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
     float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
     const int rc = nosplan_quota_recompute_impl(h->device, h->stream, h->qctx, &h->err, quotas, running, nullptr, out, &a, &b, &c,
-                                                &launches, &hb, &db, changes);
+                                                &launches, &hb, &db, changes, nullptr);
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;

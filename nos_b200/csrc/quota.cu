@@ -150,17 +150,22 @@ __global__ void __launch_bounds__(256) k_quota_events(DevQuota q, DevEvents ev) 
     if (c == 0 && (rmask & ~q.used_mask[e])) atomicOr(&q.used_mask[e], rmask);
 }
 
-constexpr int AGG_THREADS = 1024, AGG_ROWS = AGG_THREADS / 16;   // 64 namespaces in flight: the loop is a chain of dependent loads
+constexpr int AGG_THREADS = 1024, AGG_ROWS = AGG_THREADS / 16;   // 64 namespaces per CTA, one (namespace, column) pair per thread
+// Column sums over the namespace -> quota map, many CTAs: every CTA takes 64 namespaces (all loads of a namespace's chain in
+// flight at once), reduces them in shared memory and adds its 3 x 16 partial sums to the global aggregates; the CTA that
+// finishes last (agg_masks[3] counts them) then derives GetGuaranteedOverquotas of every quota from the complete sums.  The
+// aggregates and the counter are zeroed by launch_quota_aggregate in front of the kernel.
 __global__ void __launch_bounds__(AGG_THREADS) k_quota_aggregate(DevQuota q) {
     __shared__ long long s_min[AGG_ROWS][QR], s_used[AGG_ROWS][QR], s_over[AGG_ROWS][QR];
     __shared__ unsigned s_m[3];
     __shared__ long long a_min[QR], a_over[QR];
+    __shared__ int s_last;
     const int tid = threadIdx.x, c = tid & 15, j = tid >> 4;
     if (tid < 3) s_m[tid] = 0;
     __syncthreads();
     long long mn = 0, us = 0, ov = 0;
     unsigned mm = 0, um = 0, om = 0;
-    for (int ns = j; ns < q.NS; ns += AGG_ROWS) {
+    for (int ns = blockIdx.x * AGG_ROWS + j; ns < q.NS; ns += gridDim.x * AGG_ROWS) {
         const int e = q.ns_quota[ns];
         if (e < 0) continue;
         const bool has_min = (q.min_mask[e] & NOSPLAN_QUOTA_NONNIL) != 0;
@@ -175,15 +180,24 @@ __global__ void __launch_bounds__(AGG_THREADS) k_quota_aggregate(DevQuota q) {
         }
     }
     s_min[j][c] = mn; s_used[j][c] = us; s_over[j][c] = ov;
-    if (c == 0) { atomicOr(&s_m[0], mm); atomicOr(&s_m[1], um); atomicOr(&s_m[2], om); }
+    if (c == 0 && (mm | um | om)) { atomicOr(&s_m[0], mm); atomicOr(&s_m[1], um); atomicOr(&s_m[2], om); }
     __syncthreads();
-    if (tid < QR) {
+    if (tid < q.R) {
         long long a = 0, b = 0, d = 0;
         for (int k = 0; k < AGG_ROWS; ++k) { a += s_min[k][tid]; b += s_used[k][tid]; d += s_over[k][tid]; }
-        a_min[tid] = a; a_over[tid] = d;
-        if (tid < q.R) { q.agg_min[tid] = a; q.agg_used[tid] = b; q.agg_over[tid] = d; }
+        if (a) atomicAdd((unsigned long long*)&q.agg_min[tid], (unsigned long long)a);
+        if (b) atomicAdd((unsigned long long*)&q.agg_used[tid], (unsigned long long)b);
+        if (d) atomicAdd((unsigned long long*)&q.agg_over[tid], (unsigned long long)d);
     }
-    if (tid < 3) q.agg_masks[tid] = s_m[tid];
+    if (tid < 3 && s_m[tid]) atomicOr(&q.agg_masks[tid], s_m[tid]);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(&q.agg_masks[3], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (tid < QR) { a_min[tid] = tid < q.R ? __ldcg(&q.agg_min[tid]) : 0; a_over[tid] = tid < q.R ? __ldcg(&q.agg_over[tid]) : 0; }
+    if (tid == 0) s_m[2] = __ldcg(&q.agg_masks[2]);
     __syncthreads();
     const unsigned omask = s_m[2];
     for (int x = tid; x < q.E * q.R; x += blockDim.x) {     // GetGuaranteedOverquotas of every quota (:81-119)
@@ -195,6 +209,19 @@ __global__ void __launch_bounds__(AGG_THREADS) k_quota_aggregate(DevQuota q) {
         const bool in_res = cc < 4 || (omask >> cc & 1);
         q.guaranteed[x] = in_res ? go_int64(floor(__dmul_rn((double)a_over[cc], pct))) : 0;
     }
+    if (tid == 0) q.agg_masks[3] = 0;
+}
+
+static cudaError_t launch_quota_aggregate(const DevQuota& q, cudaStream_t st) {
+    // agg_min | agg_used | agg_over | agg_masks (+ the CTA counter in its 4th word) are consecutive sections of the arena
+    const size_t bytes = (size_t)(reinterpret_cast<unsigned char*>(q.agg_masks) + 16 - reinterpret_cast<unsigned char*>(q.agg_min));
+    cudaError_t e = cudaMemsetAsync(q.agg_min, 0, bytes, st);
+    if (e != cudaSuccess) return e;
+    int blocks = (q.NS + AGG_ROWS - 1) / AGG_ROWS;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 148) blocks = 148;
+    k_quota_aggregate<<<blocks, AGG_THREADS, 0, st>>>(q);
+    return cudaGetLastError();
 }
 
 __global__ void __launch_bounds__(256) k_quota_prefilter(DevQuota q) {
@@ -481,7 +508,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
                                             const nosplan_quotas* qs, const nosplan_quota_pods* running,
                                             const nosplan_quota_pods* pending, nosplan_quota_out* out, float* ms_h2d, float* ms_k,
                                             float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes,
-                                            const nosplan_label_changes* lc) {
+                                            const nosplan_label_changes* lc, const nosplan_quota_reduce_hook* hook) {
     auto fail = [&](int code, const char* msg, const char* detail = "") { if (err) *err = std::string(msg) + detail; return code; };
 #define QCU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(NOSPLAN_E_CUDA, #call ": ", cudaGetErrorString(e_)); } while (0)
     nosplan_quota_out no_out;
@@ -584,8 +611,10 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
 
     int n_launch = 0;
     // Used starts from used_init (scalar key set from used_mask)
-    if (ER) QCU(cudaMemcpyAsync(q.used, q.used_init, 8 * ER, cudaMemcpyDeviceToDevice, st));
-    if (E) QCU(cudaMemcpyAsync(q.used_mask, q.used_mask_in, 4 * (size_t)E, cudaMemcpyDeviceToDevice, st));
+    // (pods split between ranks: used_init is counted on the first rank only, the others start from zero)
+    const bool take_init = !hook || hook->first_rank;
+    if (ER && take_init) QCU(cudaMemcpyAsync(q.used, q.used_init, 8 * ER, cudaMemcpyDeviceToDevice, st));
+    if (E && take_init) QCU(cudaMemcpyAsync(q.used_mask, q.used_mask_in, 4 * (size_t)E, cudaMemcpyDeviceToDevice, st));
     if (Pr && E) {
         const size_t tab = 8 * ER;
         const int use_smem = tab <= 96 * 1024;
@@ -595,7 +624,12 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         k_quota_used<<<blocks, 256, use_smem ? tab : 0, st>>>(q, use_smem);
         ++n_launch;
     }
-    k_quota_aggregate<<<1, AGG_THREADS, 0, st>>>(q);
+    if (hook && ER) {                                          // Used rows summed, key masks OR-ed over the ranks that share the pods
+        const int rc = hook->reduce(hook->ctx, q.used, ER, q.used_mask, (size_t)E, st);
+        if (rc != NOSPLAN_OK) return fail(rc, "quota reduction over the ranks failed");
+        n_launch += 3;
+    }
+    QCU(launch_quota_aggregate(q, st));
     ++n_launch;
     if (Pp) { k_quota_prefilter<<<(Pp + 15) / 16, 256, 0, st>>>(q); ++n_launch; }
     if (want_label) {
@@ -812,7 +846,7 @@ extern "C" int nosplan_quota_state_apply_impl(int device, cudaStream_t st, nospl
         k_quota_events<<<(n + 15) / 16, 256, 0, st>>>(rs.q, de);
     }
     const bool want_agg = out && (out->agg_min || out->agg_used || out->agg_overquota || out->agg_masks || out->guaranteed);
-    if (want_agg) k_quota_aggregate<<<1, AGG_THREADS, 0, st>>>(rs.q);
+    if (want_agg && launch_quota_aggregate(rs.q, st) != cudaSuccess) return fail(NOSPLAN_E_CUDA, "k_quota_aggregate");
     SCU(cudaGetLastError());
     SCU(cudaEventRecord(ev[2], st));
     // outputs: the span asked for, plus the counter
@@ -874,7 +908,7 @@ extern "C" int nosplan_quota_state_prefilter_impl(int device, cudaStream_t st, n
     q.p_mask = pending->request_mask ? (const uint32_t*)(B + o_mask) : nullptr;
     q.prefilter = B + o_out;
     SCU(cudaEventRecord(ev[1], st));
-    k_quota_aggregate<<<1, AGG_THREADS, 0, st>>>(q);          // the aggregates of the state as it is now
+    if (launch_quota_aggregate(q, st) != cudaSuccess) return fail(NOSPLAN_E_CUDA, "k_quota_aggregate");          // the aggregates of the state as it is now
     k_quota_prefilter<<<(Pp + 15) / 16, 256, 0, st>>>(q);
     SCU(cudaGetLastError());
     SCU(cudaEventRecord(ev[2], st));

@@ -44,3 +44,10 @@ inline cudaError_t quota_ctx_ensure(nosplan_quota_ctx* ctx, size_t dev_bytes, si
     }
     return cudaSuccess;
 }
+
+// nosplan_quota_recompute_sharded: called between "reserve this rank's pods into Used" and everything derived from Used
+struct nosplan_quota_reduce_hook {
+    int (*reduce)(void* ctx, long long* d_used, size_t n_used, uint32_t* d_mask, size_t n_quotas, cudaStream_t st);
+    void* ctx;
+    bool first_rank;
+};

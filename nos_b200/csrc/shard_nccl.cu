@@ -327,3 +327,63 @@ extern "C" int nosplan_download_sharded(nosplan_t* h, nosplan_partitioning* out,
     }
     return NOSPLAN_OK;
 }
+
+// ---- quota accounting with the pods split between the ranks (collective 4) -----------------------------
+#include "quota_ctx.cuh"
+extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan_quota_ctx* ctx, std::string* err,
+                                            const nosplan_quotas* qs, const nosplan_quota_pods* running,
+                                            const nosplan_quota_pods* pending, nosplan_quota_out* out, float* ms_h2d, float* ms_k,
+                                            float* ms_d2h, int* launches, long long* h2d_bytes, long long* d2h_bytes,
+                                            const nosplan_label_changes* lc, const nosplan_quota_reduce_hook* hook);
+extern "C" nosplan_quota_ctx* nosplan_quota_ctx_new();
+
+namespace {
+__global__ void k_or_fold(uint32_t* mask, const uint32_t* gathered, int n, int world) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    uint32_t m = 0;
+    for (int r = 0; r < world; ++r) m |= gathered[(size_t)r * n + e];
+    mask[e] = m;
+}
+struct ReduceCtx { nosplan* h; };
+int quota_reduce(void* vctx, long long* d_used, size_t n_used, uint32_t* d_mask, size_t E, cudaStream_t st) {
+    nosplan* h = static_cast<ReduceCtx*>(vctx)->h;
+    nosplan_shard_ctx* c = h->sctx;
+    const size_t need = al(4 * E) + al(4 * E * (size_t)c->world);
+    if (need > c->cap) {
+        if (c->d && cudaFree(c->d) != cudaSuccess) return NOSPLAN_E_CUDA;
+        c->d = nullptr; c->cap = 0;
+        if (cudaMalloc(&c->d, need + (1 << 20)) != cudaSuccess) return NOSPLAN_E_CUDA;
+        c->cap = need + (1 << 20);
+    }
+    // int64 sums are order-independent: the reduced rows are the single-GPU rows bit for bit.  NCCL has no bit-wise OR:
+    // the key masks are gathered and folded.
+    if (nccl().AllReduce(d_used, d_used, n_used, ncclInt64, ncclSum, c->comm, st) != ncclSuccess) return NOSPLAN_E_CUDA;
+    uint32_t* mine = reinterpret_cast<uint32_t*>(c->d);
+    uint32_t* all = reinterpret_cast<uint32_t*>(c->d + al(4 * E));
+    if (cudaMemcpyAsync(mine, d_mask, 4 * E, cudaMemcpyDeviceToDevice, st) != cudaSuccess) return NOSPLAN_E_CUDA;
+    if (nccl().AllGather(mine, all, 4 * E, ncclUint8, c->comm, st) != ncclSuccess) return NOSPLAN_E_CUDA;
+    k_or_fold<<<(unsigned)((E + 255) / 256), 256, 0, st>>>(d_mask, all, (int)E, c->world);
+    return cudaGetLastError() == cudaSuccess ? NOSPLAN_OK : NOSPLAN_E_CUDA;
+}
+}  // namespace
+
+extern "C" int nosplan_quota_recompute_sharded(nosplan_t* h, const nosplan_quotas* quotas, const nosplan_quota_pods* running,
+                                               const nosplan_quota_pods* pending, nosplan_quota_out* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!h->sctx) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_quota_recompute_sharded before nosplan_shard_init");
+    if (!nccl().AllReduce) return nosplan_fail(h, NOSPLAN_E_CUDA, "ncclAllReduce not found in libnccl");
+    if (!h->qctx) h->qctx = nosplan_quota_ctx_new();
+    ReduceCtx rc_ctx{h};
+    nosplan_quota_reduce_hook hook{quota_reduce, &rc_ctx, h->sctx->rank == 0};
+    float a = 0, b = 0, c = 0; int launches = 0; long long hb = 0, db = 0;
+    const int rc = nosplan_quota_recompute_impl(h->device, h->stream, h->qctx, &h->err, quotas, running, pending, out, &a, &b, &c,
+                                                &launches, &hb, &db, nullptr, &hook);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->ms_h2d = a; stats->ms_kernels = b; stats->ms_d2h = c; stats->kernel_launches = launches;
+        stats->h2d_bytes = hb; stats->d2h_bytes = db;
+    }
+    return rc;
+}
+

@@ -100,6 +100,13 @@ def main():
     same_q &= np.array_equal(got["prefilter"], exp["prefilter"][pmine]) and np.array_equal(got["over_quota"], exp["over_quota"][mine])
     ok &= bool(same_q)
     print(f"rank {rank}/{world} quota 300 quotas / 40000 running ({len(mine)} here) / 4000 pending: sharded-quota={'OK' if same_q else 'MISMATCH'}", flush=True)
+    # the same reduction inside the library (nosplan_quota_recompute_sharded): pods dealt round-robin, one NCCL all-reduce of Used
+    rmine = np.arange(rank, run.n_pods, world)
+    got2, st2q = eng.quota_recompute(pq, sharded.take_pods(run, rmine), sharded.take_pods(pend, pmine), sharded=True)
+    same_q2 = all(np.array_equal(got2[k], exp[k]) for k in ("used", "agg_min", "agg_used", "agg_overquota", "guaranteed"))
+    same_q2 &= np.array_equal(got2["prefilter"], exp["prefilter"][pmine])
+    ok &= bool(same_q2)
+    print(f"rank {rank}/{world} quota through nosplan_quota_recompute_sharded ({len(rmine)} running pods here): {'OK' if same_q2 else 'MISMATCH'}", flush=True)
     eng.close()
     dist.barrier()
     dist.destroy_process_group()

@@ -108,3 +108,25 @@ def test_labelling_with_key_ranges_beyond_one_word(eng):
         run.priority = np.where(i % 3 == 0, np.int64(-2**31), np.where(i % 3 == 1, np.int64(2**31 - 1), run.priority)).astype(np.int32)
         got, _ = eng.quota_recompute(pq, run, pend)
         compare(got, ol.quota(pq, run, pend), f"wide keys seed {seed}")
+
+
+def test_sharded_entry_point_with_one_rank():
+    """nosplan_quota_recompute_sharded with a one-rank communicator: the NCCL all-reduce / all-gather + fold of a single rank
+    must leave the rows as nosplan_quota_recompute computes them (the two-rank form runs in tests/run_sharded_nccl.py)."""
+    import __graft_entry__ as g
+    g.build()
+    from nos_b200 import capi, synth
+    from support import oracle_lib as ol
+    eng = capi.Engine(0)
+    try:
+        eng.shard_init(0, 1, eng.nccl_unique_id())
+    except capi.NosplanError as e:
+        eng.close()
+        pytest.skip(f"NCCL not available: {e}")
+    pq, run, pend = synth.quota_state(120, 20_000, 2_000, seed=0xC4)
+    exp = ol.quota(pq, run, pend)
+    got, st = eng.quota_recompute(pq, run, pend, sharded=True)
+    for k in ("used", "agg_min", "agg_used", "agg_overquota", "guaranteed", "prefilter", "over_quota", "operator_used"):
+        assert np.array_equal(np.asarray(got[k]), np.asarray(exp[k])), k
+    eng.close()
+
