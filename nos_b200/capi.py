@@ -159,6 +159,15 @@ def pin_snapshot(s: PackedSnapshot) -> PackedSnapshot:
     return out
 
 
+def refresh_pinned(pinned: PackedSnapshot, src: PackedSnapshot) -> None:
+    """Write the per-node arrays of `src` into the page-locked arrays of `pinned` again -- what a caller does when it packs a
+    fresh snapshot into the buffers it keeps (the Go shim's packer writes into its cudaHostAlloc'ed slices on every Plan())."""
+    for name in _PINNED_FIELDS:
+        a = getattr(pinned, name)
+        if a.size:
+            np.copyto(a, np.asarray(getattr(src, name)).reshape(a.shape))
+
+
 def alloc_partitioning(s: PackedSnapshot, out=None):
     n = max(1, s.n_nodes * s.gpus_per_node)
     if out is None:
