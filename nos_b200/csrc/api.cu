@@ -393,6 +393,68 @@ static int run_pre(nosplan* h, bool split) {
 
 }  // extern "C"
 
+// ---- the blob of the single-launch kernel (nosplan_dev.cuh): layout, header, and everything derived from the pod pairs
+static void blob_layout(int n_rows, int n_models, int n_runs, int pad_pods, int* fp_off) {
+    auto a16 = [](size_t x) { return (int)((x + 15) & ~(size_t)15); };
+    const int n3 = (pad_pods + 511) / 512, n2 = pad_pods / 64, n1 = pad_pods / 8;
+    fp_off[0] = a16(16 * (size_t)n_rows);
+    fp_off[1] = fp_off[0] + a16(2 * (size_t)n_rows);
+    fp_off[2] = fp_off[1] + a16(4 * ((size_t)n_models + 1));
+    fp_off[3] = fp_off[2] + a16(sizeof(FRun) * (size_t)n_runs);
+    fp_off[FP_L3] = fp_off[3] + a16(8 * (KP + 1));
+    fp_off[FP_L2] = fp_off[FP_L3] + a16(8 * (size_t)n3);
+    fp_off[FP_L1] = fp_off[FP_L2] + a16(8 * (size_t)n2);
+    fp_off[FP_SFX] = fp_off[FP_L1] + a16(8 * (size_t)n1);
+    fp_off[FP_CUM] = fp_off[FP_SFX] + a16(8 * (size_t)n1);
+    fp_off[FP_PODS] = fp_off[FP_CUM] + a16(16 * (size_t)n1);
+    fp_off[FP_END] = fp_off[FP_PODS] + a16(8 * (size_t)pad_pods);
+}
+// header tables; every pair of the minima and of the pods starts as F_NONE ("no eligible pod")
+static void blob_begin(unsigned char* B, const int* fp_off, const nosplan_snapshot* s, int n_rows, int n_models) {
+    std::memset(B, 0, (size_t)fp_off[FP_L3]);
+    if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
+    for (int r = 0; r < n_rows; ++r) {
+        uint16_t m = 0;
+        for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p]) m |= (uint16_t)(1u << p);
+        ((uint16_t*)(B + fp_off[0]))[r] = m;
+    }
+    if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
+    std::fill((int32_t*)(B + fp_off[FP_L3]), (int32_t*)(B + fp_off[FP_END]), (int32_t)F_NONE);
+}
+// the pod pairs are in place: minima per 8 / 64 / 512 positions, suffix minima and cumulative sums per run, run records
+static void blob_finish(unsigned char* B, const int* fp_off, FRun* fr, int nr) {
+    int32_t* l3 = (int32_t*)(B + fp_off[FP_L3]); int32_t* l2 = (int32_t*)(B + fp_off[FP_L2]); int32_t* l1 = (int32_t*)(B + fp_off[FP_L1]);
+    int32_t* sfx = (int32_t*)(B + fp_off[FP_SFX]); int32_t* cum = (int32_t*)(B + fp_off[FP_CUM]);
+    const int32_t* fpod = (const int32_t*)(B + fp_off[FP_PODS]);
+    unsigned long long* prof_runs = (unsigned long long*)(B + fp_off[3]);
+    for (int r = 0; r < nr; ++r) {
+        FRun& f = fr[r];
+        const int x0 = f.pos0 >> 3, x1 = x0 + f.nblk * 8;
+        long long sc = 0, sm = 0; int cnt = 0;
+        for (int x8 = x0; x8 < x1; ++x8) {
+            int32_t mc = F_NONE, mm = F_NONE; unsigned elig = 0;
+            for (int k = 0; k < 8; ++k) {
+                const int32_t c = fpod[2 * ((size_t)x8 * 8 + k)], m = fpod[2 * ((size_t)x8 * 8 + k) + 1];
+                if (c == F_NONE) continue;
+                mc = std::min(mc, c); mm = std::min(mm, m); elig |= 1u << k; sc += c; sm += m; ++cnt;
+            }
+            l1[2 * (size_t)x8] = mc; l1[2 * (size_t)x8 + 1] = mm;
+            int32_t* cu = cum + 4 * (size_t)x8;
+            cu[0] = (int32_t)std::min<long long>(sc, F_NONE); cu[1] = (int32_t)std::min<long long>(sm, F_NONE); cu[2] = cnt; cu[3] = (int32_t)elig;
+            int32_t* b2 = l2 + 2 * (size_t)(x8 >> 3); int32_t* d3 = l3 + 2 * (size_t)(x8 >> 6);
+            b2[0] = std::min(b2[0], mc); b2[1] = std::min(b2[1], mm); d3[0] = std::min(d3[0], mc); d3[1] = std::min(d3[1], mm);
+            f.min_c = std::min(f.min_c, mc); f.min_m = std::min(f.min_m, mm);
+        }
+        int32_t tc = F_NONE, tm = F_NONE;
+        for (int x8 = x1 - 1; x8 >= x0; --x8) {
+            tc = std::min(tc, l1[2 * (size_t)x8]); tm = std::min(tm, l1[2 * (size_t)x8 + 1]);
+            sfx[2 * (size_t)x8] = tc; sfx[2 * (size_t)x8 + 1] = tm;
+        }
+        prof_runs[f.p >= 0 ? f.p : KP] |= 1ull << r;
+    }
+    std::memcpy(B + fp_off[2], fr, sizeof(FRun) * (size_t)nr);
+}
+
 // The classic kernels' view of the pods, in NewPodSorter order (h->v_order): request columns, tracker keys, flags, CSR of the
 // scalar entries, the run records and per-chunk (32 pods, run-relative) minima of the requests of the PreFilter-ok pods -- the
 // kernels skip chunks in which no pod can pass NodeResourcesFit.  An all-zero request passes regardless (fit.go short-circuit):
@@ -506,7 +568,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     const size_t part1_end = o;
     // part 2 (runs, chunk minima) is laid out once the pods are ordered; the arena is sized from bounds: runs <= P, chunks <= P
     const size_t bound = part1_end + al(sizeof(RunRec) * (size_t)P) + al(4 * ((size_t)P + 1)) + 3 * al(8 * (size_t)P) + 4096 +
-                         al(8 * (pad_pods_max + pad_pods_max / 8 + pad_pods_max / 64 + pad_pods_max / 512 + 8)) + al(sizeof(FRun) * FRUN_MAX) +
+                         al(8 * (pad_pods_max + pad_pods_max / 8 + pad_pods_max / 64 + pad_pods_max / 512 + 8)) + al(3 * pad_pods_max + 64) + al(sizeof(FRun) * FRUN_MAX) +
                          al(18 * (size_t)MAX_ROWS) + al(4 * (MAX_MODELS + 1)) + 4096;
     CU(h, cudaSetDevice(h->device));
     const size_t out_bytes = al(16 * NG) + al(2 * NG) + al(sizeof(DevStats));
@@ -630,7 +692,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     bool single_profile_classes = true, lazy = false;
     long long any_eph = 0;
     unsigned rset = 0;
-    int fp_off[9] = {0};
+    int fp_off[FP_NOFF] = {0};
     size_t up_from = 0;
     fused_ok = fused_ok && !h->force_classic;
 
@@ -749,57 +811,23 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         put(L.runs, sizeof(RunRec) * (size_t)n_runs);
         put(L.run_chunk_off, 4 * ((size_t)n_runs + 1));
         put(L.cmin_cpu, 8 * (size_t)n_chunks); put(L.cmin_mem, 8 * (size_t)n_chunks); put(L.cmin_eph, 8 * (size_t)n_chunks);
-        {
-            auto a16 = [](size_t x) { return (int)((x + 15) & ~(size_t)15); };
-            const int n3 = (pad_pods + 511) / 512, n2 = pad_pods / 64, n1 = pad_pods / 8;
-            fp_off[0] = a16(16 * (size_t)n_rows);
-            fp_off[1] = fp_off[0] + a16(2 * (size_t)n_rows);
-            fp_off[2] = fp_off[1] + a16(4 * ((size_t)n_models + 1));
-            fp_off[3] = fp_off[2] + a16(sizeof(FRun) * (size_t)n_runs);
-            fp_off[4] = fp_off[3] + a16(8 * (KP + 1));
-            fp_off[5] = fp_off[4] + a16(8 * (size_t)n3);
-            fp_off[6] = fp_off[5] + a16(8 * (size_t)n2);
-            fp_off[7] = fp_off[6] + a16(8 * (size_t)n1);
-            fp_off[8] = fp_off[7] + a16(8 * (size_t)pad_pods);
-        }
-        put(L.fp_blob, (size_t)fp_off[8]);
+        blob_layout(n_rows, n_models, n_runs, pad_pods, fp_off);
+        put(L.fp_blob, (size_t)fp_off[FP_END]);
         L.upload_end = o; L.total = o;
         if (L.total > bound) return false;
         h->lay = L;
         unsigned char* B = S + L.fp_blob;
-        int32_t* l3 = (int32_t*)(B + fp_off[4]); int32_t* l2 = (int32_t*)(B + fp_off[5]); int32_t* l1 = (int32_t*)(B + fp_off[6]);
-        int32_t* fpod = (int32_t*)(B + fp_off[7]);
-        unsigned long long* prof_runs = (unsigned long long*)(B + fp_off[3]);
-        std::memset(B, 0, (size_t)fp_off[4]);
-        if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
-        for (int r = 0; r < n_rows; ++r) {
-            uint16_t m = 0;
-            for (int pp = 0; pp < 16; ++pp) if (s->geom_counts[16 * (size_t)r + pp]) m |= (uint16_t)(1u << pp);
-            ((uint16_t*)(B + fp_off[0]))[r] = m;
-        }
-        if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
-        std::fill(l3, (int32_t*)(B + fp_off[8]), (int32_t)F_NONE);
+        blob_begin(B, fp_off, s, n_rows, n_models);
+        int32_t* fpod = (int32_t*)(B + fp_off[FP_PODS]);
         int cur[FRUN_MAX];
         for (int r = 0; r < nr; ++r) cur[r] = fr[r].pos0;
         for (int i = 0; i < P; ++i) {                                     // pass B: original order == order inside a bucket
             const int x = cur[run_of[bk[i]]]++;
             if (prefilter_ok && !prefilter_ok[i]) continue;
-            const int32_t c = (int32_t)(pods->base[3 * (size_t)i] >> cs), m = (int32_t)(pods->base[3 * (size_t)i + 1] >> ms);
-            fpod[2 * (size_t)x] = c; fpod[2 * (size_t)x + 1] = m;
-            int32_t* a1 = l1 + 2 * (size_t)(x >> 3);
-            a1[0] = std::min(a1[0], c); a1[1] = std::min(a1[1], m);
+            fpod[2 * (size_t)x] = (int32_t)(pods->base[3 * (size_t)i] >> cs);
+            fpod[2 * (size_t)x + 1] = (int32_t)(pods->base[3 * (size_t)i + 1] >> ms);
         }
-        for (int r = 0; r < nr; ++r) {
-            FRun& f = fr[r];
-            for (int x8 = f.pos0 >> 3; x8 < (f.pos0 >> 3) + f.nblk * 8; ++x8) {
-                const int32_t c = l1[2 * (size_t)x8], m = l1[2 * (size_t)x8 + 1];
-                int32_t* b2 = l2 + 2 * (size_t)(x8 >> 3); int32_t* d3 = l3 + 2 * (size_t)(x8 >> 6);
-                b2[0] = std::min(b2[0], c); b2[1] = std::min(b2[1], m); d3[0] = std::min(d3[0], c); d3[1] = std::min(d3[1], m);
-                f.min_c = std::min(f.min_c, c); f.min_m = std::min(f.min_m, m);
-            }
-            prof_runs[f.p >= 0 ? f.p : KP] |= 1ull << r;
-        }
-        std::memcpy(B + fp_off[2], fr, sizeof(FRun) * (size_t)nr);
+        blob_finish(B, fp_off, fr, nr);
         lazy = true; up_from = L.fp_blob;
         h->classic_staged = false;
         h->lazy_valid = true; h->lazy_pods = *pods; h->lazy_pre = prefilter_ok; h->lazy_filter = filter_mode;
@@ -926,41 +954,19 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         }
         // the blob: header [geometry rows | key masks | model ranges | runs | runs per profile], then (cpu, memory) pairs
         // [minima per 512 | per 64 | per 8 | pods]; every section starts on a 16-byte boundary
-        {
-            auto a16 = [](size_t x) { return (int)((x + 15) & ~(size_t)15); };
-            const int n3 = (pad_pods + 511) / 512, n2 = pad_pods / 64, n1 = pad_pods / 8;
-            fp_off[0] = a16(16 * (size_t)n_rows);
-            fp_off[1] = fp_off[0] + a16(2 * (size_t)n_rows);
-            fp_off[2] = fp_off[1] + a16(4 * ((size_t)n_models + 1));
-            fp_off[3] = fp_off[2] + a16(sizeof(FRun) * (size_t)n_runs);
-            fp_off[4] = fp_off[3] + a16(8 * (KP + 1));
-            fp_off[5] = fp_off[4] + a16(8 * (size_t)n3);
-            fp_off[6] = fp_off[5] + a16(8 * (size_t)n2);
-            fp_off[7] = fp_off[6] + a16(8 * (size_t)n1);
-            fp_off[8] = fp_off[7] + a16(8 * (size_t)pad_pods);
-        }
-        if (fused_ok) put(L.fp_blob, (size_t)fp_off[8]); else L.fp_blob = o;
+        blob_layout(n_rows, n_models, n_runs, pad_pods, fp_off);
+        if (fused_ok) put(L.fp_blob, (size_t)fp_off[FP_END]); else L.fp_blob = o;
         L.upload_end = o;
         L.total = o;
         if (L.total > bound) return fail(h, NOSPLAN_E_NOMEM, "internal: arena bound exceeded");
         h->lay = L;
         if (fused_ok) {
             // padded position space: run r occupies [pos0, pos0 + 64 * nblk); a pod that can never be placed (PreFilter verdict
-            // false) and every padding slot cost F_NONE; minima per 8, 64 and 512 positions and per run
+            // false) and every padding slot cost F_NONE
             unsigned char* B = S + L.fp_blob;
-            int32_t* l3 = (int32_t*)(B + fp_off[4]); int32_t* l2 = (int32_t*)(B + fp_off[5]); int32_t* l1 = (int32_t*)(B + fp_off[6]);
-            int32_t* fpod = (int32_t*)(B + fp_off[7]);
-            FRun* fr = (FRun*)(B + fp_off[2]);
-            unsigned long long* prof_runs = (unsigned long long*)(B + fp_off[3]);
-            std::memset(B, 0, (size_t)fp_off[4]);
-            if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
-            for (int r = 0; r < n_rows; ++r) {
-                uint16_t m = 0;
-                for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p]) m |= (uint16_t)(1u << p);
-                ((uint16_t*)(B + fp_off[0]))[r] = m;
-            }
-            if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
-            std::fill(l3, (int32_t*)(B + fp_off[8]), (int32_t)F_NONE);
+            blob_begin(B, fp_off, s, n_rows, n_models);
+            int32_t* fpod = (int32_t*)(B + fp_off[FP_PODS]);
+            FRun fr[FRUN_MAX];
             int pos = 0;
             for (int r = 0; r < n_runs; ++r) {
                 const RunRec& rr = runs[r];
@@ -971,22 +977,13 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
                 for (int k = 0; k < rr.len; ++k) {
                     const int oi = order[rr.start + k], x = pos + k;
                     if (!(flags[oi] & PF_PRE_OK)) continue;
-                    const int32_t c = (int32_t)(pods->base[3 * (size_t)oi] >> cpu_shift), m = (int32_t)(pods->base[3 * (size_t)oi + 1] >> mem_shift);
-                    fpod[2 * (size_t)x] = c; fpod[2 * (size_t)x + 1] = m;
-                    int32_t* a = l1 + 2 * (size_t)(x >> 3);
-                    a[0] = std::min(a[0], c); a[1] = std::min(a[1], m);
-                }
-                // the coarser minima from the finer ones
-                for (int x8 = pos >> 3; x8 < (pos >> 3) + f.nblk * 8; ++x8) {
-                    const int32_t c = l1[2 * (size_t)x8], m = l1[2 * (size_t)x8 + 1];
-                    int32_t* b = l2 + 2 * (size_t)(x8 >> 3); int32_t* d = l3 + 2 * (size_t)(x8 >> 6);
-                    b[0] = std::min(b[0], c); b[1] = std::min(b[1], m); d[0] = std::min(d[0], c); d[1] = std::min(d[1], m);
-                    f.min_c = std::min(f.min_c, c); f.min_m = std::min(f.min_m, m);
+                    fpod[2 * (size_t)x] = (int32_t)(pods->base[3 * (size_t)oi] >> cpu_shift);
+                    fpod[2 * (size_t)x + 1] = (int32_t)(pods->base[3 * (size_t)oi + 1] >> mem_shift);
                 }
                 fr[r] = f;
-                prof_runs[f.p >= 0 ? f.p : KP] |= 1ull << r;
                 pos += f.nblk * 64;
             }
+            blob_finish(B, fp_off, fr, n_runs);
         }
         lap("blob");
         // ---- the classic kernels' pod arrays: now, unless this is one nosplan_plan / nosplan_plan_resident call planning with the
@@ -1022,7 +1019,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     pb.placed = (unsigned*)(A + L.placed);
     pb.entry_lack = (int32_t*)(A + L.entry_lack);
     pb.fp_blob = A + L.fp_blob;
-    for (int k = 0; k < 9; ++k) pb.fp_off[k] = fp_off[k];
+    for (int k = 0; k < FP_NOFF; ++k) pb.fp_off[k] = fp_off[k];
     pb.fp_n_runs = fused_ok ? n_runs : 0; pb.fp_pad_pods = pad_pods; pb.fp_cpu_shift = cpu_shift; pb.fp_mem_shift = mem_shift; pb.fp_rset = rset;
     h->fused_ok = fused_ok; h->fused_pending = false; h->placed_dirty = false;
     lap("pods queued");

@@ -168,16 +168,18 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
         unsigned ok = tx & ty;
         unsigned sc = __dp4a(tx & ~HI, Lw[0], 0u);
         sc = __dp4a(ty & ~HI, Lw[1], sc);
-        bool same = row.x == cnt0.x && row.y == cnt0.y;
         if (WIDE) {
             const unsigned tz = (row.z | HI) - used.z, tw = (row.w | HI) - used.w;
             ok &= tz & tw;
             sc = __dp4a(tz & ~HI, Lw[2], sc);
             sc = __dp4a(tw & ~HI, Lw[3], sc);
-            same = same && row.z == cnt0.z && row.w == cnt0.w;
         }
         if ((ok & HI) == HI && sc) best = max(best, (sc << 5) | (unsigned)(31 - r));   // strict > in table order
-        allowed |= same && s_gmask[row0 + r] == gm0;
+        if (fm == 0) {                                // AllowsGeometry(current) only decides HasFreeCapacity where no free key exists
+            bool same = row.x == cnt0.x && row.y == cnt0.y;
+            if (WIDE) same = same && row.z == cnt0.z && row.w == cnt0.w;
+            allowed |= same && s_gmask[row0 + r] == gm0;
+        }
     }
     const bool has_free = has && (fm != 0 || !allowed);
     const bool candidate = (__ballot_sync(FULL, has_free) >> gsh & 0xffu) != 0;
@@ -252,7 +254,7 @@ __device__ __forceinline__ uint4 ld_quad(const uint4* p) {
 template <bool WIDE, bool FIT, bool SMEM>
 __device__ __forceinline__ int warp_phase2(const NodeS& s, bool on, const FRun* s_runs,
                                            const unsigned long long* s_prof_runs, const uint2* L3, const uint2* L2, const uint2* L1,
-                                           const uint2* PODS, unsigned* s_bits) {
+                                           const uint2* SFX, const uint4* CUM, const uint2* PODS, unsigned* s_bits, int* s_pref) {
     const bool active = on && (s.flags & 5) == 1;
     int remc = -1, remm = -1;
     unsigned cv0 = 0, cv1 = 0, cv2 = 0, cv3 = 0;
@@ -284,10 +286,30 @@ __device__ __forceinline__ int warp_phase2(const NodeS& s, bool on, const FRun* 
         const int cap0 = cap;
         int cur = fr.pos0 >> 3;
         const int end = cur + fr.nblk * 8;
+        if (cap > 0) {
+            // the head of the run, whole groups of eight at a time: while the cumulative cost and count of the eligible pods
+            // through a group fit what the node has left, every one of them is placed (each prefix of a sum that fits, fits)
+            // and no pod has to be looked at.  The groups taken are recorded per run (s_pref) and turned into bits at the end.
+            int k = 0;
+            uint4 took = make_uint4(0, 0, 0, 0);
+            while (cur + k < end) {
+                const uint4 cu = ld_quad<SMEM>(CUM + cur + k);
+                if ((int)cu.z > cap || (FIT && ((int)cu.x > remc || (int)cu.y > remm))) break;
+                took = cu; ++k;
+            }
+            if (k > 0) {
+                if (FIT) { remc -= (int)took.x; remm -= (int)took.y; }
+                cap -= (int)took.z;
+                if (took.z) atomicMax(&s_pref[ri], k);
+                cur += k;
+            }
+        }
         for (;;) {
             // next group of eight pods this node has to look at: skip what the minima rule out
             int sub = -1;
             while (cap > 0 && cur < end) {
+                const uint2 sf = ld_pair<SMEM>(SFX + cur);
+                if ((int)sf.x > remc || (int)sf.y > remm) { cur = end; break; }      // nothing from here to the end of the run fits
                 if ((cur & 63) == 0) {
                     const uint2 m = ld_pair<SMEM>(L3 + (cur >> 6));
                     if ((int)m.x > remc || (int)m.y > remm) { cur += 64; continue; }
@@ -404,7 +426,7 @@ struct FusedLaunch { int tile_nodes, stage_bytes; };
 
 template <bool WIDE>
 __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaunch fl, unsigned char* s_dyn, unsigned long long (*s_wD)[KP],
-                                           unsigned (*s_wmf)[4], unsigned long long (*s_wcnt)[4], int* s_flags, unsigned long long* s_bar) {
+                                           unsigned (*s_wmf)[4], unsigned long long (*s_wcnt)[4], int* s_flags, int* s_pref, unsigned long long* s_bar) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, j = lane & 7, gsh = (lane >> 3) * 8;
     const int n_words = pb.fp_pad_pods >> 5;
     // dynamic shared memory: [placed bitmap][staged prefix of the blob: tables, runs, minima, pods][per-node state][per-GPU state]
@@ -423,8 +445,9 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
         const unsigned char* base = pb.fp_off[k + 1] <= fl.stage_bytes ? s_blob : pb.fp_blob;
         return reinterpret_cast<const uint2*>(base + pb.fp_off[k]);
     };
-    const uint2* L3 = level(4); const uint2* L2 = level(5); const uint2* L1 = level(6); const uint2* PODS = level(7);
-    const bool smem_all = pb.fp_off[8] <= fl.stage_bytes, fit = pb.filter_mode == NOSPLAN_FILTER_RESOURCES_FIT;
+    const uint2* L3 = level(FP_L3); const uint2* L2 = level(FP_L2); const uint2* L1 = level(FP_L1); const uint2* SFX = level(FP_SFX);
+    const uint4* CUM = reinterpret_cast<const uint4*>(level(FP_CUM)); const uint2* PODS = level(FP_PODS);
+    const bool smem_all = pb.fp_off[FP_END] <= fl.stage_bytes, fit = pb.filter_mode == NOSPLAN_FILTER_RESOURCES_FIT;
 
     const int n_req = __popc(pb.fp_rset);
     unsigned Lw[4];                                   // lacking profiles as a 0/1 byte per profile (the dp4a weights)
@@ -438,7 +461,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
     Acc a;
     const int n_nodes = pb.node_hi - pb.node_lo;
     const int n_tiles = (n_nodes + fl.tile_nodes - 1) / fl.tile_nodes;
-    bool hdr_ready = false, staged_ready = fl.stage_bytes <= pb.fp_off[4];
+    bool hdr_ready = false, staged_ready = fl.stage_bytes <= pb.fp_off[FP_L3];
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int base = pb.node_lo + tile * fl.tile_nodes;
         const int count = min(fl.tile_nodes, pb.node_hi - base);
@@ -461,10 +484,10 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
             if (__any_sync(FULL, on)) {
                 const NodeS& ns = s_node[on ? nl : 0];
                 int added;
-                if (fit) added = smem_all ? warp_phase2<WIDE, true, true>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits)
-                                          : warp_phase2<WIDE, true, false>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits);
-                else added = smem_all ? warp_phase2<WIDE, false, true>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits)
-                                      : warp_phase2<WIDE, false, false>(ns, on, s_runs, s_prof_runs, L3, L2, L1, PODS, s_bits);
+                if (fit) added = smem_all ? warp_phase2<WIDE, true, true>(ns, on, s_runs, s_prof_runs, L3, L2, L1, SFX, CUM, PODS, s_bits, s_pref)
+                                          : warp_phase2<WIDE, true, false>(ns, on, s_runs, s_prof_runs, L3, L2, L1, SFX, CUM, PODS, s_bits, s_pref);
+                else added = smem_all ? warp_phase2<WIDE, false, true>(ns, on, s_runs, s_prof_runs, L3, L2, L1, SFX, CUM, PODS, s_bits, s_pref)
+                                      : warp_phase2<WIDE, false, false>(ns, on, s_runs, s_prof_runs, L3, L2, L1, SFX, CUM, PODS, s_bits, s_pref);
                 if (on && added > 0) { s_node[nl].flags |= 8; a.place += added; }
             }
         }
@@ -485,23 +508,30 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
     if (!hdr_ready) mbar_wait(&s_bar[0], 0);          // a CTA without tiles still has to see its copies land before it exits
     if (!staged_ready) mbar_wait(&s_bar[1], 0);
 
-    // ---- reduction of what the threads accumulated: warp shuffles, one shared-memory slot per warp
+    // ---- reduction of what the threads accumulated: one shared-memory slot per warp
     if (__any_sync(FULL, a.flags != 0)) { const unsigned f = __reduce_or_sync(FULL, a.flags); if (lane == 0) atomicOr(&s_flags[0], (int)f); }
 #pragma unroll
     for (int o = 8; o < 32; o <<= 1) {                 // lanes with the same j across the warp's four groups
         a.D0 += __shfl_xor_sync(FULL, a.D0, o); a.D1 += __shfl_xor_sync(FULL, a.D1, o);
     }
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        a.mf.x = __vmaxu4(a.mf.x, __shfl_xor_sync(FULL, a.mf.x, o)); a.mf.y = __vmaxu4(a.mf.y, __shfl_xor_sync(FULL, a.mf.y, o));
-        if (WIDE) { a.mf.z = __vmaxu4(a.mf.z, __shfl_xor_sync(FULL, a.mf.z, o)); a.mf.w = __vmaxu4(a.mf.w, __shfl_xor_sync(FULL, a.mf.w, o)); }
-        a.place += __shfl_xor_sync(FULL, a.place, o); a.evals += __shfl_xor_sync(FULL, a.evals, o);
-        a.visited += __shfl_xor_sync(FULL, a.visited, o);
-    }
     if (lane < 8) { s_wD[warp][lane] = (unsigned long long)a.D0; s_wD[warp][8 + lane] = (unsigned long long)a.D1; }
-    if (lane == 0) {
-        s_wmf[warp][0] = a.mf.x; s_wmf[warp][1] = a.mf.y; s_wmf[warp][2] = a.mf.z; s_wmf[warp][3] = a.mf.w;
-        s_wcnt[warp][0] = (unsigned long long)a.place; s_wcnt[warp][1] = (unsigned long long)a.evals; s_wcnt[warp][2] = (unsigned long long)a.visited;
+    {   // largest free count per profile: byte-wise maximum over the warp, one redux per word half
+        unsigned mx = 0, my = 0, mz = 0, mw = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            mx |= __reduce_max_sync(FULL, (a.mf.x >> (8 * b)) & 0xffu) << (8 * b);
+            my |= __reduce_max_sync(FULL, (a.mf.y >> (8 * b)) & 0xffu) << (8 * b);
+            if (WIDE) {
+                mz |= __reduce_max_sync(FULL, (a.mf.z >> (8 * b)) & 0xffu) << (8 * b);
+                mw |= __reduce_max_sync(FULL, (a.mf.w >> (8 * b)) & 0xffu) << (8 * b);
+            }
+        }
+        if (lane == 0) { s_wmf[warp][0] = mx; s_wmf[warp][1] = my; s_wmf[warp][2] = mz; s_wmf[warp][3] = mw; }
+    }
+    {   // placements, geometry evaluations, visited nodes: a warp's share fits 32 bits (<= 32 nodes per tile, <= 2^20 tiles)
+        const unsigned pl = __reduce_add_sync(FULL, (unsigned)a.place), ev = __reduce_add_sync(FULL, (unsigned)a.evals);
+        const unsigned vi = __reduce_add_sync(FULL, (unsigned)a.visited);
+        if (lane == 0) { s_wcnt[warp][0] = pl; s_wcnt[warp][1] = ev; s_wcnt[warp][2] = vi; }
     }
     __syncthreads();
     // ---- this CTA's contribution to the grid-wide state
@@ -520,6 +550,15 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
         for (int w = 0; w < NW; ++w) c += s_wcnt[w][tid - 32];
         if (c) atomicAdd(&pb.acc[tid - 32], c);
     } else if (tid == 64 && s_flags[0]) atomicOr(&pb.wave[5], s_flags[0]);
+    // the heads taken whole: their eligible pods are placed pods (the cumulative record carries the group's eligibility mask)
+    for (int r = 0; r < pb.fp_n_runs; ++r) {
+        const int k = s_pref[r], x0 = s_runs[r].pos0 >> 3;
+        for (int x = tid; x < k; x += FT) {
+            const unsigned m = CUM[x0 + x].w;
+            if (m) atomicOr(&s_bits[(x0 + x) >> 2], m << (((x0 + x) & 3) * 8));
+        }
+    }
+    __syncthreads();
     for (int w = tid; w < n_words; w += FT) {
         const unsigned b = s_bits[w];
         if (b) atomicOr(&pb.placed[w], b);
@@ -532,6 +571,7 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
     __shared__ unsigned s_wmf[FT / 32][4];
     __shared__ unsigned long long s_wcnt[FT / 32][4];
     __shared__ int s_flags[1];
+    __shared__ int s_pref[FRUN_MAX];                               // per run: groups of eight taken whole from its head by some node of this CTA
     __shared__ long long s_l0[KP], s_dec[KP];
     __shared__ long long s_e[FRUN_MAX];
     __shared__ __align__(8) unsigned long long s_bar[2];
@@ -544,7 +584,7 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
         mbar_init(&s_bar[0], 1);
         mbar_init(&s_bar[1], 1);
         unsigned char* dst = s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15);
-        const unsigned hdr = (unsigned)min(fl.stage_bytes, pb.fp_off[4]), all = (unsigned)fl.stage_bytes;
+        const unsigned hdr = (unsigned)min(fl.stage_bytes, pb.fp_off[FP_L3]), all = (unsigned)fl.stage_bytes;
         mbar_expect_tx(&s_bar[0], hdr);
         bulk_g2s(dst, pb.fp_blob, hdr, &s_bar[0]);
         if (all > hdr) {
@@ -554,12 +594,13 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
     }
     for (int w = tid; w < n_words; w += FT) reinterpret_cast<unsigned*>(s_dyn)[w] = 0;
     if (tid == 0) s_flags[0] = 0;
+    if (tid < FRUN_MAX) s_pref[tid] = 0;
     // the next run's copy of the small per-run state (see DevProblem::zero_next)
     if (blockIdx.x == 0) for (int x = tid; x < pb.zero_next_n8; x += FT) pb.zero_next[x] = 0;
     __syncthreads();
 
-    if (pb.K > 8) fused_body<true>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_bar);
-    else fused_body<false>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_bar);
+    if (pb.K > 8) fused_body<true>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
+    else fused_body<false>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
 
     // ---- the CTA that finishes last either verifies the hypothesis on the final state (single GPU: what k_plan_sweep does for
     //      the classic path) or, in slice mode, ships this rank's part of that state to every rank in ONE block
@@ -587,7 +628,7 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
         }
         // consume: W words per index from this rank's own mailbox (local memory)
         const unsigned char* me = pb.xf_box.base[pb.xf_box.rank];
-        unsigned* s_hdr = reinterpret_cast<unsigned*>(s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15) + pb.fp_off[4]);   // staged minima: no longer needed
+        unsigned* s_hdr = reinterpret_cast<unsigned*>(s_dyn + (((size_t)n_words * 4 + 15) & ~(size_t)15) + pb.fp_off[FP_L3]);   // staged minima: no longer needed
         unsigned* s_or = reinterpret_cast<unsigned*>(s_dyn);                                                              // this CTA's placed bits: flushed long ago
         bool ok = true;
         for (int i = tid; i < D; i += FT) {
@@ -718,8 +759,8 @@ cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st) {
     if (tile > FT) tile = FT;
     fl.tile_nodes = tile;
     // the header (tables, runs) always; then whole levels of the pod structure, top down, while they fit
-    fl.stage_bytes = pb.fp_off[4];
-    for (int l = 5; l <= 8; ++l) if (need(pb.fp_off[l], tile) <= FUSED_SMEM) fl.stage_bytes = pb.fp_off[l];
+    fl.stage_bytes = pb.fp_off[FP_L3];
+    for (int l = FP_L3 + 1; l <= FP_END; ++l) if (need(pb.fp_off[l], tile) <= FUSED_SMEM) fl.stage_bytes = pb.fp_off[l];
     if (need(fl.stage_bytes, tile) > FUSED_SMEM) return cudaErrorInvalidValue;
     int blocks = (n_nodes + tile - 1) / tile;
     if (blocks > sms) blocks = sms;

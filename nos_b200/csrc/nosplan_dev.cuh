@@ -39,6 +39,12 @@ static_assert(sizeof(RunRec) == 48, "RunRec layout");
 // memory bytes >> mem_shift; exact because every pod request is a multiple of the unit); F_NONE marks a pod that can never be
 // placed (PreFilter verdict false, or padding) and, in the minima, a group without an eligible pod.
 constexpr int FRUN_MAX = 64;                 // runs the fused kernel keeps in shared memory
+// sections of the blob behind the header (indices into DevProblem::fp_off; FP_END is the total size).  Per group of eight
+// positions there are, besides the minima: FP_SFX, the minima over the rest of the run from this group on ("nothing from here
+// to the end of the run fits any more" is one test), and FP_CUM, {cpu, memory, count} summed over the eligible pods from the
+// head of the run through this group plus the group's eligibility mask ("the whole head of the run fits" is one test per
+// group, no pod is looked at); sums saturate at F_NONE.
+constexpr int FP_L3 = 4, FP_L2 = 5, FP_L1 = 6, FP_SFX = 7, FP_CUM = 8, FP_PODS = 9, FP_END = 10, FP_NOFF = 11;
 constexpr int F_NONE = 0x7fffffff;
 constexpr int F_REM_MAX = 0x7ffffffe;        // largest remaining capacity representable; larger node values reject the fused plan
 constexpr int F_COST_LIMIT = 1 << 28;        // pod costs stay below this so that eight of them sum without overflow
@@ -173,8 +179,8 @@ struct DevProblem {
                                      //      the lacking vector (by wave parity)  [3] candidate nodes  [4] waves run
     // single-launch Plan() (fused.cu): padded pod costs, their minima per 8 and per 64 positions, runs, units
     const unsigned char* fp_blob;
-    int fp_off[9];                   // byte offsets in the blob: key masks, model ranges, runs, runs per profile (geometry rows
-                                     // at 0), minima per 512 / 64 / 8, pods, total
+    int fp_off[FP_NOFF];             // byte offsets in the blob: key masks, model ranges, runs, runs per profile (geometry rows
+                                     // at 0), minima per 512 / 64 / 8 positions, suffix minima, cumulative sums, pods, total
     int fp_n_runs, fp_pad_pods, fp_cpu_shift, fp_mem_shift;
     unsigned fp_rset;                // profiles some pod requests: the lacking set the fused kernel speculates on
     int whole_snapshot;              // the node-parallel pass covers every node on this rank (no exchange needed)
