@@ -169,6 +169,36 @@ int nosplan_changed_nodes(nosplan_t* h, int32_t* node_idx, int32_t capacity, int
  * otherwise Go 1.18's sort.SliceStable (insertion sort of 20 + symMerge) is executed step for step.  Needs no GPU. */
 int nosplan_host_pod_order(const nosplan_snapshot* snap, const nosplan_pods* pods, int32_t* order_out);
 
+/* nosplan_plan with the node side in COMPACT form: one record per node, one contiguous array, one DMA -- 128 + 24*G (+ 16 per
+ * other scalar resource) bytes per node against ~490 in the SoA form of nosplan_snapshot (G = 8, K = 7), expanded on the GPU
+ * into the arrays the kernels read (128 + 24*G rounded up to 16).  Same semantics, errors and outputs as nosplan_plan; the snapshot stays resident for
+ * nosplan_plan_resident / nosplan_update_nodes exactly as after nosplan_plan.  Replaces the same reference inputs as
+ * nosplan_snapshot (internal/partitioning/core/interface.go:53-65); the cgo packer fills records instead of twelve slices.
+ * Limits: K <= 8 profiles, model ids < 256, slice-column values < 2^31.  Record layout (little-endian):
+ *     0  int32  gpu_count, allowed_pods, num_pods, 0
+ *    16  int64  allocatable cpu (milli), memory, ephemeral-storage; requested cpu, memory, ephemeral-storage
+ *    64  int32  allocatable of slice columns 0..7, requested of slice columns 0..7  (columns >= K: 0)
+ *   128  int64  allocatable of the n_other scalar columns, then requested of them
+ *   128 + 16*n_other, for each GPU slot g < G (24 bytes):
+ *        uint8 used[8], uint8 free[8], uint8 used key mask, uint8 free key mask, uint8 model id, uint8 0, uint16 memory GB, uint16 0
+ *   padded with zeros to a multiple of 16 bytes.  The per-node checks of nosplan_plan (GPU count, model ids) are made on the
+ *   GPU: a malformed record is reported by the same call, after its kernels have run, and nothing of that call is kept. */
+typedef struct nosplan_snapshot_compact {
+    int32_t kind, n_profiles;
+    const int32_t* profile_mem_gb;     /* [K] as in nosplan_snapshot */
+    const int32_t* profile_gi;         /* [K] */
+    int32_t n_models;
+    const int32_t* model_geom_offset;  /* [n_models+1] */
+    const uint8_t* geom_counts;        /* [rows][16] */
+    int32_t n_nodes, gpus_per_node, n_other;
+    int32_t record_bytes;              /* must equal nosplan_compact_record_bytes(gpus_per_node, n_other) */
+    const uint8_t* records;            /* [N][record_bytes], nodes in byte-wise name order */
+} nosplan_snapshot_compact;
+int32_t nosplan_compact_record_bytes(int32_t gpus_per_node, int32_t n_other);
+int nosplan_plan_compact(nosplan_t* h, const nosplan_snapshot_compact* snap, const nosplan_pods* pods,
+                         const uint8_t* prefilter_ok, int32_t filter_mode,
+                         nosplan_partitioning* out, nosplan_stats* stats);
+
 /* The same call split in three so the planning kernels can be timed with the snapshot resident in
  * HBM: upload() packs and copies, run() launches the kernels on the handle's stream (repeatable),
  * download() copies the plan back.  cuda_stream of the handle is exposed for CUDA-event timing. */

@@ -27,7 +27,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
     "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_upload_pods", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply", "nosplan_quota_state_prefilter",
-    "nosplan_quota_recompute_sharded",
+    "nosplan_quota_recompute_sharded", "nosplan_plan_compact", "nosplan_compact_record_bytes",
 ]
 SLICE_TOTALS_BYTES = 256
 SLICED_NOT_APPLICABLE = 1
@@ -60,6 +60,50 @@ class CSnapshot(C.Structure):
         ("n_other", C.c_int32), ("node_alloc", C.c_void_p), ("node_requested", C.c_void_p),
         ("node_allowed_pods", C.c_void_p), ("node_num_pods", C.c_void_p),
     ]
+
+
+class CSnapshotCompact(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int32), ("n_profiles", C.c_int32), ("profile_mem_gb", C.c_void_p), ("profile_gi", C.c_void_p),
+        ("n_models", C.c_int32), ("model_geom_offset", C.c_void_p), ("geom_counts", C.c_void_p),
+        ("n_nodes", C.c_int32), ("gpus_per_node", C.c_int32), ("n_other", C.c_int32), ("record_bytes", C.c_int32),
+        ("records", C.c_void_p),
+    ]
+
+
+def compact_record_bytes(gpus_per_node: int, n_other: int) -> int:
+    return (128 + 16 * n_other + 24 * gpus_per_node + 15) & ~15
+
+
+def compact_records(s: PackedSnapshot, out: np.ndarray = None) -> np.ndarray:
+    """The node side of `s` as [N][record_bytes] uint8 (layout in include/nosplan.h, nosplan_snapshot_compact): what a packer
+    writes instead of the twelve SoA arrays.  K <= 8 profiles, model ids < 256."""
+    N, G, K, n_other = s.n_nodes, s.gpus_per_node, s.n_profiles, len(s.other_resources)
+    if K > 8:
+        raise ValueError("the compact form holds 8 profiles")
+    rb = compact_record_bytes(G, n_other)
+    rec = out if out is not None else np.zeros((N, rb), np.uint8)
+    rec[:] = 0
+    head = rec[:, 0:16].view(np.int32)
+    head[:, 0], head[:, 1], head[:, 2] = s.node_gpu_count, s.node_allowed_pods, s.node_num_pods
+    base = rec[:, 16:64].view(np.int64)
+    base[:, 0:3], base[:, 3:6] = s.node_alloc[:, 0:3], s.node_requested[:, 0:3]
+    sl = rec[:, 64:128].view(np.int32)
+    sl[:, 0:K], sl[:, 8:8 + K] = s.node_alloc[:, 3:3 + K], s.node_requested[:, 3:3 + K]
+    if n_other:
+        ot = rec[:, 128:128 + 16 * n_other].view(np.int64)
+        ot[:, 0:n_other], ot[:, n_other:2 * n_other] = s.node_alloc[:, 3 + K:], s.node_requested[:, 3 + K:]
+    g0 = 128 + 16 * n_other
+    gp = rec[:, g0:g0 + 24 * G].reshape(N, G, 24)
+    gp[:, :, 0:8] = np.asarray(s.gpu_used).reshape(N, G, 16)[:, :, 0:8]
+    gp[:, :, 8:16] = np.asarray(s.gpu_free).reshape(N, G, 16)[:, :, 0:8]
+    gp[:, :, 16] = np.asarray(s.gpu_used_mask).reshape(N, G) & 0xff
+    gp[:, :, 17] = np.asarray(s.gpu_free_mask).reshape(N, G) & 0xff
+    gp[:, :, 18] = np.asarray(s.gpu_model).reshape(N, G) & 0xff
+    mem = np.asarray(s.gpu_memory_gb).reshape(N, G).astype(np.uint16)
+    gp[:, :, 20] = mem & 0xff
+    gp[:, :, 21] = mem >> 8
+    return rec
 
 
 class CPods(C.Structure):
@@ -383,6 +427,72 @@ class Engine:
         self._snap = snap
         del k1, k2, k3
         return cnt, msk, st.as_dict()
+
+    def prepared_plan(self, snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0, out=None, resident=False):
+        """The C structs of one nosplan_plan (or nosplan_plan_resident) call built once: -> call() that does nothing but enter
+        the C-ABI (returns the raw return code; raise through .check), and result() -> (gpu_count, gpu_mask, stats dict).
+        For timing the call itself, not this Python wrapper."""
+        cs, k1 = c_snapshot(snap)
+        cp, k2 = c_pods(pods)
+        cout, cnt, msk = alloc_partitioning(snap, out)
+        st = CStats()
+        pre, k3 = self._pre(prefilter_ok, pods.n_pods)
+        lib, h = self.lib, self.h
+        lib.nosplan_plan_resident.argtypes = [C.c_void_p, C.POINTER(CPods), C.c_void_p, C.c_int32, C.POINTER(CPartitioning), C.POINTER(CStats)]
+        lib.nosplan_plan_resident.restype = C.c_int
+        a_cs, a_cp, a_out, a_st = C.byref(cs), C.byref(cp), C.byref(cout), C.byref(st)
+        if resident:
+            def call():
+                return lib.nosplan_plan_resident(h, a_cp, pre, filter_mode, a_out, a_st)
+        else:
+            def call():
+                return lib.nosplan_plan(h, a_cs, a_cp, pre, filter_mode, a_out, a_st)
+        call.keep = (cs, cp, cout, st, k1, k2, k3, snap, pods)
+        call.check = lambda rc: self._check(rc, "nosplan_plan")
+        call.result = lambda: (cnt, msk, st.as_dict())
+        self._snap = snap
+        return call
+
+    def prepared_plan_compact(self, snap: PackedSnapshot, records: np.ndarray, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0, out=None):
+        """nosplan_plan_compact with its C structs built once (see prepared_plan): `records` = compact_records(snap), possibly
+        in page-locked memory."""
+        keep = []
+
+        def p(a, dt):
+            addr, arr = _ptr(a, dt)
+            keep.append(arr)
+            return addr
+        cc = CSnapshotCompact()
+        cc.kind, cc.n_profiles = snap.kind, snap.n_profiles
+        cc.profile_mem_gb, cc.profile_gi = p(snap.profile_mem_gb, np.int32), p(snap.profile_gi, np.int32)
+        cc.n_models = len(snap.models)
+        cc.model_geom_offset, cc.geom_counts = p(snap.model_geom_offset, np.int32), p(snap.geom_counts, np.uint8)
+        cc.n_nodes, cc.gpus_per_node, cc.n_other = snap.n_nodes, snap.gpus_per_node, len(snap.other_resources)
+        cc.record_bytes = records.shape[1] if records.ndim == 2 and records.shape[0] else compact_record_bytes(snap.gpus_per_node, len(snap.other_resources))
+        cc.records = records.ctypes.data
+        cp, k2 = c_pods(pods)
+        cout, cnt, msk = alloc_partitioning(snap, out)
+        st = CStats()
+        pre, k3 = self._pre(prefilter_ok, pods.n_pods)
+        lib, h = self.lib, self.h
+        lib.nosplan_plan_compact.argtypes = [C.c_void_p, C.POINTER(CSnapshotCompact), C.POINTER(CPods), C.c_void_p, C.c_int32,
+                                             C.POINTER(CPartitioning), C.POINTER(CStats)]
+        lib.nosplan_plan_compact.restype = C.c_int
+        a_cc, a_cp, a_out, a_st = C.byref(cc), C.byref(cp), C.byref(cout), C.byref(st)
+
+        def call():
+            return lib.nosplan_plan_compact(h, a_cc, a_cp, pre, filter_mode, a_out, a_st)
+        call.keep = (cc, cp, cout, st, keep, k2, k3, snap, pods, records)
+        call.check = lambda rc: self._check(rc, "nosplan_plan_compact")
+        call.result = lambda: (cnt, msk, st.as_dict())
+        self._snap = snap
+        return call
+
+    def plan_compact(self, snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0, out=None, records=None):
+        """nosplan_plan_compact: the node side as one array of records.  -> (gpu_count, gpu_mask, stats dict)"""
+        call = self.prepared_plan_compact(snap, records if records is not None else compact_records(snap), pods, prefilter_ok, filter_mode, out)
+        call.check(call())
+        return call.result()
 
     def plan_resident(self, pods: PackedPods, prefilter_ok=None, filter_mode: int = 0, out=None):
         """nosplan_plan_resident: new pods against the snapshot the last plan() / upload() left in HBM."""

@@ -18,6 +18,7 @@
 
 namespace nsp {
 void launch_prepass(const DevProblem& pb, cudaStream_t st);
+void launch_expand_nodes(const DevProblem& pb, const void* records, int record_bytes, int n_models, int32_t* d_flag, cudaStream_t st);
 void launch_tracker_init(const DevProblem& pb, cudaStream_t st);
 cudaError_t launch_sweep(const DevProblem& pb, int32_t* cand_idx, cudaStream_t st);
 cudaError_t launch_parallel(const DevProblem& pb, int max_blocks, cudaStream_t st);
@@ -151,7 +152,7 @@ int ensure(nosplan* h, size_t dev_bytes, size_t stage_bytes, size_t out_bytes, s
         h->d_cap = cap;
     }
     if (stage_bytes > h->h_cap) {
-        if (h->h_stage) CU(h, cudaFreeHost(h->h_stage));
+        if (h->h_stage) { CU(h, cudaStreamSynchronize(h->stream)); CU(h, cudaFreeHost(h->h_stage)); }   // a queued copy may still read it
         h->h_stage = nullptr; h->h_cap = 0;
         size_t cap = stage_bytes + stage_bytes / 4 + (1 << 20);
         CU(h, cudaMallocHost(&h->h_stage, cap));
@@ -316,6 +317,8 @@ int nosplan_create(int cuda_device, nosplan_t** out) {
         return NOSPLAN_E_CUDA;
     }
     h->sms = sms;
+    if (cudaMalloc(&h->d_flag, 256) != cudaSuccess || cudaMallocHost(&h->h_flag, 256) != cudaSuccess) { delete h; return NOSPLAN_E_CUDA; }
+    h->h_flag[0] = -1;
     for (auto& e : h->ev)
         if (cudaEventCreate(&e) != cudaSuccess) { delete h; return NOSPLAN_E_CUDA; }
     *out = h;
@@ -329,6 +332,8 @@ void nosplan_destroy(nosplan_t* h) {
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     for (auto& e : h->dbg_ev) if (e) cudaEventDestroy(e);
     if (h->d_arena) cudaFree(h->d_arena);
+    if (h->d_flag) cudaFree(h->d_flag);
+    if (h->h_flag) cudaFreeHost(h->h_flag);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->qctx) nosplan_quota_ctx_free(h->qctx);
@@ -494,6 +499,23 @@ static void stage_classic_pods(nosplan* h, const nosplan_pods* pods, int K) {
     std::memcpy(S + L.run_chunk_off, h->v_chunk_off.data(), 4 * ((size_t)n_runs + 1));
 }
 
+// the node sections of the arena: the same offsets for every upload of a snapshot of this shape
+static void layout_nodes(Layout& L, size_t& o, int n_models, int n_rows, int N, int G, int R, bool mig) {
+    auto put = [&](size_t& field, size_t bytes) { field = o; o = al(o + bytes); };
+    const size_t NG = (size_t)N * G;
+    put(L.model_off, sizeof(int32_t) * (n_models + 1));
+    put(L.geom, 16 * (size_t)n_rows);
+    put(L.node_gpu_count, 4 * (size_t)N);
+    // only the array of the snapshot's kind travels (model ids: MIG, memory sizes: MPS); the other pointer aliases it, its
+    // values are read into registers by shared code and never used
+    if (mig) { put(L.gpu_model, 4 * NG); L.gpu_mem = L.gpu_model; } else { put(L.gpu_mem, 4 * NG); L.gpu_model = L.gpu_mem; }
+    put(L.gpu_used, 16 * NG); put(L.gpu_free, 16 * NG);
+    put(L.gpu_umask, 2 * NG); put(L.gpu_fmask, 2 * NG);
+    put(L.node_alloc, 8 * (size_t)N * R); put(L.node_req, 8 * (size_t)N * R);
+    put(L.node_allowed, 4 * (size_t)N); put(L.node_npods, 4 * (size_t)N);
+    L.nodes_end = o;
+}
+
 // keep: the node arrays of the last full upload are still in the arena and are planned against again (s = &h->res_snap)
 static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok,
                        int32_t filter_mode, bool keep) {
@@ -536,17 +558,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     Layout L; size_t o = 0;
     auto put = [&](size_t& field, size_t bytes) { field = o; o = al(o + bytes); };
     const size_t NG = (size_t)N * G;
-    put(L.model_off, sizeof(int32_t) * (n_models + 1));
-    put(L.geom, 16 * (size_t)n_rows);
-    put(L.node_gpu_count, 4 * (size_t)N);
-    // only the array of the snapshot's kind travels (model ids: MIG, memory sizes: MPS); the other pointer aliases it, its
-    // values are read into registers by shared code and never used
-    if (mig) { put(L.gpu_model, 4 * NG); L.gpu_mem = L.gpu_model; } else { put(L.gpu_mem, 4 * NG); L.gpu_model = L.gpu_mem; }
-    put(L.gpu_used, 16 * NG); put(L.gpu_free, 16 * NG);
-    put(L.gpu_umask, 2 * NG); put(L.gpu_fmask, 2 * NG);
-    put(L.node_alloc, 8 * (size_t)N * R); put(L.node_req, 8 * (size_t)N * R);
-    put(L.node_allowed, 4 * (size_t)N); put(L.node_npods, 4 * (size_t)N);
-    L.nodes_end = o;
+    layout_nodes(L, o, n_models, n_rows, N, G, R, mig);
     // small per-run state, twice: run k works in copy k & 1 while its k_prepass clears the other one for run k + 1, so no
     // reset is queued in front of a run (the large tracker tables below are cleared by k_prepass for its own run)
     put(L.tot, 8 * KP); put(L.lack, 4 * KP); put(L.stats, sizeof(DevStats));
@@ -1434,6 +1446,100 @@ int nosplan_plan(nosplan_t* h, const nosplan_snapshot* snap, const nosplan_pods*
     if (rc != NOSPLAN_OK) { if (h->direct_h2d) cudaStreamSynchronize(h->stream); h->lazy_valid = false; return rc; }
     rc = nosplan_download(h, out, stats);            // a rejected single-launch plan is re-planned inside this call
     h->lazy_valid = false;
+    return rc;
+}
+
+int32_t nosplan_compact_record_bytes(int32_t gpus_per_node, int32_t n_other) {
+    if (gpus_per_node < 1 || gpus_per_node > NOSPLAN_MAX_GPUS || n_other < 0 || n_other > NOSPLAN_MAX_OTHER) return -1;
+    return (128 + 16 * n_other + 24 * gpus_per_node + 15) & ~15;            // records stay 16-byte aligned
+}
+
+// nosplan_plan with the node side as one array of records: one DMA, k_expand_nodes writes the node sections of the arena, and
+// from there on the call is nosplan_plan_resident on the snapshot just expanded.
+int nosplan_plan_compact(nosplan_t* h, const nosplan_snapshot_compact* c, const nosplan_pods* pods, const uint8_t* prefilter_ok,
+                         int32_t filter_mode, nosplan_partitioning* out, nosplan_stats* stats) {
+    if (!h) return NOSPLAN_E_INVALID;
+    if (!c || !pods) return fail(h, NOSPLAN_E_INVALID, "null snapshot or pods");
+    const int K = c->n_profiles, N = c->n_nodes, G = c->gpus_per_node, n_other = c->n_other;
+    if (c->kind != NOSPLAN_KIND_MIG && c->kind != NOSPLAN_KIND_MPS) return fail(h, NOSPLAN_E_INVALID, "unknown kind %d", c->kind);
+    if (K < 0 || N < 0 || G < 1 || n_other < 0) return fail(h, NOSPLAN_E_INVALID, "negative size");
+    if (K > 8) return fail(h, NOSPLAN_E_LIMIT, "%d profiles: the compact form holds 8 (use nosplan_plan)", K);
+    if (G > NOSPLAN_MAX_GPUS) return fail(h, NOSPLAN_E_LIMIT, "%d GPUs per node > NOSPLAN_MAX_GPUS", G);
+    if (n_other > NOSPLAN_MAX_OTHER) return fail(h, NOSPLAN_E_LIMIT, "%d other resources > NOSPLAN_MAX_OTHER", n_other);
+    const int rec = nosplan_compact_record_bytes(G, n_other);
+    if (c->record_bytes != rec) return fail(h, NOSPLAN_E_INVALID, "record_bytes %d, expected %d", c->record_bytes, rec);
+    if (N > 0 && !c->records) return fail(h, NOSPLAN_E_INVALID, "null records");
+    const bool mig = c->kind == NOSPLAN_KIND_MIG;
+    const int n_models = mig ? c->n_models : 0;
+    if (n_models < 0 || n_models > MAX_MODELS || n_models > 256) return fail(h, NOSPLAN_E_LIMIT, "%d GPU models", n_models);
+    const int n_rows = (mig && n_models > 0) ? c->model_geom_offset[n_models] : 0;
+    if (n_rows < 0 || n_rows > MAX_ROWS) return fail(h, NOSPLAN_E_LIMIT, "%d geometry rows > %d", n_rows, MAX_ROWS);
+    const int R = 3 + K + n_other;
+    CU(h, cudaSetDevice(h->device));
+    h->nodes_resident = false; h->uploaded = h->ran = h->pre_done = false;
+    Layout L; size_t o = 0;
+    layout_nodes(L, o, n_models, n_rows, N, G, R, mig);
+    const size_t rec_bytes = (size_t)N * rec, o_rec = L.nodes_end;
+    cudaPointerAttributes at;
+    const bool direct = rec_bytes >= (128u << 10) && cudaPointerGetAttributes(&at, c->records) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    (void)cudaGetLastError();
+    int rc = ensure(h, o_rec + al(rec_bytes) + 4096, al(L.node_gpu_count) + (direct ? 0 : al(rec_bytes)) + 4096, 0);
+    if (rc != NOSPLAN_OK) return rc;
+    unsigned char* S = h->h_stage; unsigned char* A = h->d_arena;
+    if (n_models > 0) std::memcpy(S + L.model_off, c->model_geom_offset, sizeof(int32_t) * (n_models + 1));
+    else std::memset(S + L.model_off, 0, sizeof(int32_t));
+    if (n_rows) std::memcpy(S + L.geom, c->geom_counts, 16 * (size_t)n_rows);
+    CU(h, cudaMemcpyAsync(A, S, L.node_gpu_count, cudaMemcpyHostToDevice, h->stream));          // the two small tables
+    if (rec_bytes) {
+        if (direct) CU(h, cudaMemcpyAsync(A + o_rec, c->records, rec_bytes, cudaMemcpyHostToDevice, h->stream));
+        else {
+            std::memcpy(S + al(L.node_gpu_count), c->records, rec_bytes);
+            CU(h, cudaMemcpyAsync(A + o_rec, S + al(L.node_gpu_count), rec_bytes, cudaMemcpyHostToDevice, h->stream));
+        }
+        (void)cudaStreamQuery(h->stream);
+    }
+    DevProblem pb; std::memset(&pb, 0, sizeof pb);
+    pb.kind = c->kind; pb.K = K; pb.R = R; pb.n_other = n_other; pb.N = N; pb.G = G;
+    pb.node_gpu_count = (const int32_t*)(A + L.node_gpu_count);
+    pb.gpu_model = (const int32_t*)(A + L.gpu_model); pb.gpu_mem = (const int32_t*)(A + L.gpu_mem);
+    pb.gpu_used = (const uint4*)(A + L.gpu_used); pb.gpu_free = (const uint4*)(A + L.gpu_free);
+    pb.gpu_umask = (const uint16_t*)(A + L.gpu_umask); pb.gpu_fmask = (const uint16_t*)(A + L.gpu_fmask);
+    pb.node_alloc = (const long long*)(A + L.node_alloc); pb.node_req = (const long long*)(A + L.node_req);
+    pb.node_allowed_pods = (const int32_t*)(A + L.node_allowed); pb.node_num_pods = (const int32_t*)(A + L.node_npods);
+    CU(h, cudaMemsetAsync(h->d_flag, 0xff, 8, h->stream));                 // [0] first bad node (INT_MAX-ish = none), [1] what was wrong
+    launch_expand_nodes(pb, A + o_rec, rec, n_models, h->d_flag, h->stream);
+    CU(h, cudaGetLastError());
+    // the checks nosplan_upload makes per node are made by k_expand_nodes (the records are strided: a host pass over them costs
+    // more than the DMA saves); its verdict travels to pinned host memory behind the kernel and is read after the call's sync
+    CU(h, cudaMemcpyAsync(h->h_flag, h->d_flag, 8, cudaMemcpyDeviceToHost, h->stream));
+    // what nosplan_plan_resident needs: shape and small tables on the host, the node sections where upload_impl expects them
+    nosplan_snapshot& r = h->res_snap;
+    std::memset(&r, 0, sizeof r);
+    r.kind = c->kind; r.n_profiles = K; r.n_models = n_models; r.n_nodes = N; r.gpus_per_node = G; r.n_other = n_other;
+    h->res_pmem.assign(c->profile_mem_gb, c->profile_mem_gb + K); h->res_pgi.assign(c->profile_gi, c->profile_gi + K);
+    h->res_model_off.assign(n_models > 0 ? c->model_geom_offset : nullptr, n_models > 0 ? c->model_geom_offset + n_models + 1 : nullptr);
+    h->res_geom.assign(n_rows ? c->geom_counts : nullptr, n_rows ? c->geom_counts + 16 * (size_t)n_rows : nullptr);
+    r.profile_mem_gb = h->res_pmem.data(); r.profile_gi = h->res_pgi.data();
+    r.model_geom_offset = h->res_model_off.data(); r.geom_counts = h->res_geom.data();
+    const size_t offs[11] = {L.node_gpu_count, L.gpu_model, L.gpu_mem, L.gpu_used, L.gpu_free, L.gpu_umask, L.gpu_fmask,
+                             L.node_alloc, L.node_req, L.node_allowed, L.node_npods};
+    std::memcpy(h->res_off, offs, sizeof offs);
+    h->res_nodes_end = L.nodes_end;
+    h->nodes_resident = true;
+    h->compact_h2d = L.node_gpu_count + rec_bytes;
+    h->in_plan = true;
+    rc = upload_impl(h, &h->res_snap, pods, prefilter_ok, filter_mode, true);
+    h->in_plan = false;
+    if (rc != NOSPLAN_OK) { cudaStreamSynchronize(h->stream); h->lazy_valid = false; return rc; }
+    h->h2d_bytes += h->compact_h2d;
+    rc = h->pre_done ? run_post(h) : nosplan_run(h);
+    if (rc != NOSPLAN_OK) { cudaStreamSynchronize(h->stream); h->lazy_valid = false; return rc; }
+    rc = nosplan_download(h, out, stats);
+    h->lazy_valid = false;
+    if (h->h_flag[0] != -1) {                                // a record was malformed: whatever was planned is void
+        h->nodes_resident = false; h->uploaded = h->ran = false;
+        return fail(h, NOSPLAN_E_INVALID, h->h_flag[1] == 1 ? "node %d: gpu count out of range" : "node %d: GPU model id out of range", h->h_flag[0]);
+    }
     return rc;
 }
 

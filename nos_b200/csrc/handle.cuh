@@ -60,7 +60,8 @@ struct nosplan {
     int sms = 148, par_blocks = 148 * 4, wave_blocks = 148 * 4;   // SM count and resident-wave grid sizes of this handle's device
     size_t out_count_bytes = 0, out_mask_bytes = 0;
     int launches = 0;
-    size_t h2d_bytes = 0;
+    size_t h2d_bytes = 0, compact_h2d = 0;
+    int32_t* d_flag = nullptr; int32_t* h_flag = nullptr;       // nosplan_plan_compact: first malformed record, found on the GPU
     nosplan_quota_ctx* qctx = nullptr;
     nosplan_quota_ctx* ectx = nullptr;          // the resident quota state of nosplan_quota_state_begin / apply
     nosplan_quota_ctx* pctx = nullptr;          // the preemption entry points' own scratch: holds the resident cluster state

@@ -264,6 +264,59 @@ void launch_slice_pack_totals(const DevProblem& pb, void* block, cudaStream_t st
 void launch_slice_combine_totals(const DevProblem& pb, const void* gathered, int world, const PeerWait& wait, cudaStream_t st) {
     k_slice_combine_totals<<<1, 32, 0, st>>>(pb, static_cast<const unsigned char*>(gathered), world, wait);
 }
+// nosplan_plan_compact: one record per node (layout in include/nosplan.h) -> the node sections of the arena.  One warp per node:
+// lanes 0..G-1 expand the GPU slots (two 128-bit rows, masks, model / memory), all lanes the account columns.
+__global__ void __launch_bounds__(256) k_expand_nodes(DevProblem pb, const unsigned char* records, int record_bytes, int n_models, int32_t* flag) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= pb.N) return;
+    const unsigned char* rec = records + (size_t)i * record_bytes;
+    const int K = pb.K, R = pb.R, G = pb.G, n_other = pb.n_other;
+    const int ng = *reinterpret_cast<const int32_t*>(rec);
+    if (ng < 0 || ng > pb.G) {                                // what nosplan_upload refuses per node; the lowest node index is reported
+        if (lane == 0 && (unsigned)i < (unsigned)atomicMin(reinterpret_cast<unsigned*>(flag), (unsigned)i)) flag[1] = 1;
+    }
+    if (lane == 0) {
+        const int4 c = *reinterpret_cast<const int4*>(rec);
+        const_cast<int32_t*>(pb.node_gpu_count)[i] = min(max(c.x, 0), pb.G);
+        const_cast<int32_t*>(pb.node_allowed_pods)[i] = c.y;
+        const_cast<int32_t*>(pb.node_num_pods)[i] = c.z;
+    }
+    long long* alloc = const_cast<long long*>(pb.node_alloc) + (size_t)i * R;
+    long long* req = const_cast<long long*>(pb.node_req) + (size_t)i * R;
+    if (lane < 3) {
+        alloc[lane] = reinterpret_cast<const long long*>(rec + 16)[lane];
+        req[lane] = reinterpret_cast<const long long*>(rec + 16)[3 + lane];
+    }
+    if (lane < K) {
+        alloc[3 + lane] = reinterpret_cast<const int32_t*>(rec + 64)[lane];
+        req[3 + lane] = reinterpret_cast<const int32_t*>(rec + 64)[8 + lane];
+    }
+    if (lane < n_other) {
+        alloc[3 + K + lane] = reinterpret_cast<const long long*>(rec + 128)[lane];
+        req[3 + K + lane] = reinterpret_cast<const long long*>(rec + 128)[n_other + lane];
+    }
+    if (lane < G) {
+        const unsigned char* g = rec + 128 + 16 * (size_t)n_other + 24 * (size_t)lane;
+        const uint2 u = *reinterpret_cast<const uint2*>(g), f = *reinterpret_cast<const uint2*>(g + 8);
+        const unsigned t = *reinterpret_cast<const unsigned*>(g + 16), m = *reinterpret_cast<const unsigned*>(g + 20);
+        const size_t x = (size_t)i * G + lane;
+        const_cast<uint4*>(pb.gpu_used)[x] = make_uint4(u.x, u.y, 0u, 0u);
+        const_cast<uint4*>(pb.gpu_free)[x] = make_uint4(f.x, f.y, 0u, 0u);
+        const_cast<uint16_t*>(pb.gpu_umask)[x] = (uint16_t)(t & 0xffu);
+        const_cast<uint16_t*>(pb.gpu_fmask)[x] = (uint16_t)((t >> 8) & 0xffu);
+        if (pb.kind == NOSPLAN_KIND_MIG) {
+            const int model = (int)((t >> 16) & 0xffu);
+            if (lane < ng && model >= n_models && (unsigned)i < (unsigned)atomicMin(reinterpret_cast<unsigned*>(flag), (unsigned)i)) flag[1] = 2;
+            const_cast<int32_t*>(pb.gpu_model)[x] = min(model, max(n_models - 1, 0));
+        }
+        else const_cast<int32_t*>(pb.gpu_mem)[x] = (int32_t)(m & 0xffffu);
+    }
+}
+void launch_expand_nodes(const DevProblem& pb, const void* records, int record_bytes, int n_models, int32_t* flag, cudaStream_t st) {
+    if (pb.N > 0) k_expand_nodes<<<(pb.N + 7) / 8, 256, 0, st>>>(pb, static_cast<const unsigned char*>(records), record_bytes, n_models, flag);
+}
+
 void launch_prepass(const DevProblem& pb, cudaStream_t st) {
     if (pb.N > 0) {
         int blocks = (pb.N + PRE_NODES - 1) / PRE_NODES;      // one tile of 32 nodes per block, grid-stride beyond 8 waves
