@@ -47,7 +47,7 @@ def balanced(text, start, open_ch, close_ch):
 def header_model(path):
     h = strip_comments(open(path).read())
     funcs = {}
-    for m in re.finditer(r"\b(?:int|void|int64_t|const char\s*\*|void\s*\*)\s*(nosplan_\w+)\s*\(", h):
+    for m in re.finditer(r"\b(?:int|void|int32_t|int64_t|const char\s*\*|void\s*\*)\s*(nosplan_\w+)\s*\(", h):
         args = balanced(h, m.end() - 1, "(", ")")
         n = 0 if args.strip() in ("", "void") else len(split_args(args))
         funcs[m.group(1)] = n

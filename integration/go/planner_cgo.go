@@ -398,13 +398,51 @@ func (pk *packer) pack(kind C.int32_t, snapshot Snapshot, pods []v1.Pod) error {
 	return nil
 }
 
+// records is the node side in the compact form of nosplan_snapshot_compact (include/nosplan.h): one record per node, one DMA,
+// expanded on the GPU -- about half the bytes of the SoA arrays.  Written here from the arrays pack() has just filled, for
+// brevity; a packer that targets only this form writes the records directly while it walks the nodes.
+func (pk *packer) records(b *pinned) ([]byte, int) {
+	N, G, K, nOther := len(pk.names), pk.G, len(pk.profiles), len(pk.others)
+	R := 3 + K + nOther
+	rb := int(C.nosplan_compact_record_bytes(C.int32_t(G), C.int32_t(nOther)))
+	rec := b.bytes(N * rb)
+	for i := range rec {
+		rec[i] = 0
+	}
+	for i := 0; i < N; i++ {
+		r := rec[i*rb : (i+1)*rb]
+		head := unsafe.Slice((*int32)(unsafe.Pointer(&r[0])), 4)
+		head[0], head[1], head[2] = pk.gpuCount[i], pk.allowed[i], pk.nPods[i]
+		base := unsafe.Slice((*int64)(unsafe.Pointer(&r[16])), 6)
+		copy(base[0:3], pk.alloc[i*R:i*R+3])
+		copy(base[3:6], pk.req[i*R:i*R+3])
+		sl := unsafe.Slice((*int32)(unsafe.Pointer(&r[64])), 16)
+		for k := 0; k < K; k++ {
+			sl[k], sl[8+k] = int32(pk.alloc[i*R+3+k]), int32(pk.req[i*R+3+k])
+		}
+		if nOther > 0 {
+			ot := unsafe.Slice((*int64)(unsafe.Pointer(&r[128])), 2*nOther)
+			copy(ot[0:nOther], pk.alloc[i*R+3+K:(i+1)*R])
+			copy(ot[nOther:2*nOther], pk.req[i*R+3+K:(i+1)*R])
+		}
+		for j := 0; j < G; j++ {
+			x, g := i*G+j, r[128+16*nOther+24*j:]
+			copy(g[0:8], pk.used[16*x:16*x+8])
+			copy(g[8:16], pk.free[16*x:16*x+8])
+			g[16], g[17], g[18] = uint8(pk.uMask[x]), uint8(pk.fMask[x]), uint8(pk.gpuModel[x])
+			g[20], g[21] = uint8(pk.gpuMem[x]), uint8(pk.gpuMem[x]>>8)
+		}
+	}
+	return rec, rb
+}
+
 // cudaPlanner implements core.Planner on the engine.
 type cudaPlanner struct {
 	h         *C.nosplan_t
 	kind      C.int32_t // NOSPLAN_KIND_MIG | NOSPLAN_KIND_MPS
 	framework framework.Framework
 	pk        packer
-	pre       pinned
+	pre, rec  pinned
 }
 
 // NewCudaPlanner is what mig.NewPlanner / mps.NewPlanner return instead of core.NewPlanner(partitionCalculator, sliceCalculator,
@@ -454,7 +492,19 @@ func (p *cudaPlanner) Plan(ctx context.Context, snapshot Snapshot, pods []v1.Pod
 	}
 	out := C.nosplan_partitioning{gpu_count: pu8(pk.outCount), gpu_mask: pu16(pk.outMask)}
 	var st C.nosplan_stats
-	if rc := C.nosplan_plan(p.h, &snap, &cp, pu8(pre), C.NOSPLAN_FILTER_RESOURCES_FIT, &out, &st); rc != 0 {
+	if len(pk.profiles) <= 8 && len(pk.models) <= 256 {
+		// the compact form: same plan, about half the bytes over PCIe
+		rec, rb := pk.records(&p.rec)
+		cs := C.nosplan_snapshot_compact{
+			kind: p.kind, n_profiles: C.int32_t(len(pk.profiles)), profile_mem_gb: p32(pk.profMem), profile_gi: p32(pk.profGI),
+			n_models: C.int32_t(len(pk.models)), model_geom_offset: p32(pk.modelOff), geom_counts: pu8(pk.geom),
+			n_nodes: C.int32_t(len(pk.names)), gpus_per_node: C.int32_t(pk.G), n_other: C.int32_t(len(pk.others)),
+			record_bytes: C.int32_t(rb), records: pu8(rec),
+		}
+		if rc := C.nosplan_plan_compact(p.h, &cs, &cp, pu8(pre), C.NOSPLAN_FILTER_RESOURCES_FIT, &out, &st); rc != 0 {
+			return PartitioningPlan{}, fmt.Errorf("nosplan_plan_compact: %s", C.GoString(C.nosplan_last_error(p.h)))
+		}
+	} else if rc := C.nosplan_plan(p.h, &snap, &cp, pu8(pre), C.NOSPLAN_FILTER_RESOURCES_FIT, &out, &st); rc != 0 {
 		return PartitioningPlan{}, fmt.Errorf("nosplan_plan: %s", C.GoString(C.nosplan_last_error(p.h)))
 	}
 	// state.PartitioningState (internal/partitioning/state/partitioning.go:24-40): zero-count keys are kept (mask bit set)
