@@ -124,6 +124,10 @@ typedef struct nosplan_stats {
     int64_t h2d_bytes, d2h_bytes;      /* bytes copied by upload() / download() */
     int32_t fused;                     /* 1: the plan is the single-launch kernel's (path == 1), 0: the classic kernel sequence's */
     int32_t fused_reject;              /* != 0: the single-launch kernel ran first and rejected its own hypothesis (reason bits) */
+    int32_t gate_replayed;             /* some node's accounts disagree with its GPUs: nodes were planned in parallel without the
+                                          cluster-wide gate (core/snapshot.go:132-165), the gate was replayed in name order, and this
+                                          many nodes (>= 0) had to be planned again with it; -1: no replay took place */
+    int32_t reserved0;
 } nosplan_stats;
 
 /* Create an engine bound to one CUDA device.  Replaces: mig.NewPlanner / mps.NewPlanner

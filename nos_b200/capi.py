@@ -127,7 +127,7 @@ class CStats(C.Structure):
         ("waves", C.c_int32),
         ("kernel_launches", C.c_int32), ("path", C.c_int32),
         ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-        ("fused", C.c_int32), ("fused_reject", C.c_int32),
+        ("fused", C.c_int32), ("fused_reject", C.c_int32), ("gate_replayed", C.c_int32), ("reserved0", C.c_int32),
     ]
 
     def as_dict(self):

@@ -574,6 +574,8 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     put(L.cand_flag, (size_t)N); put(L.cand_idx, 4 * (size_t)N);
     put(L.out_count, 16 * NG); put(L.out_mask, 2 * NG);
     L.out_end = o;
+    // gate replay records (sweep.cu): written before they are read, never cleared
+    put(L.rec_dw, 8 * (size_t)N * KP); put(L.rec_pl, 8 * (size_t)N * KP); put(L.rec_fl, 4 * (size_t)N); put(L.gate_state, 8 * (KP + 2));
     put(L.pod_cpu, 8 * (size_t)P); put(L.pod_mem, 8 * (size_t)P); put(L.pod_eph, 8 * (size_t)P);
     put(L.pod_key, 4 * (size_t)P); put(L.pod_flags, 4 * (size_t)P);
     put(L.pod_sptr, 4 * ((size_t)P + 1)); put(L.pod_scol, 4 * (size_t)nnz); put(L.pod_sqty, 8 * (size_t)nnz);
@@ -670,6 +672,8 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     pb.cand_flag = (uint8_t*)(A + L.cand_flag);
     pb.out_count = (uint4*)(A + L.out_count); pb.out_mask = (uint16_t*)(A + L.out_mask);
     h->d_cand_idx = (int32_t*)(A + L.cand_idx);
+    pb.rec_dw = (long long*)(A + L.rec_dw); pb.rec_pn = (int2*)(A + L.rec_pl); pb.rec_fl = (int32_t*)(A + L.rec_fl);
+    pb.gate_state = (long long*)(A + L.gate_state);
     h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot; h->small_bytes = small_bytes;
     h->run_parity = 1; h->bound_copy = 0;                    // pb points at copy 0; the first run flips to it
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
@@ -1073,7 +1077,7 @@ static int run_post(nosplan* h) {
     CU(h, cudaGetLastError());
     // single GPU: where the node-parallel pass can run at all, its last CTA verifies it and k_plan_waves (which returns at
     // once when the pass stands) holds both fallbacks; other problems go straight to k_plan_sweep
-    const bool work = h->pb.fast_eligible && h->pb.N > 0 && h->pb.P > 0;
+    const bool work = h->pb.N > 0 && h->pb.P > 0;
     if (work) {
         DevProblem p2 = h->pb;
         p2.verify_inline = 1;
@@ -1424,6 +1428,7 @@ int nosplan_download(nosplan_t* h, nosplan_partitioning* out, nosplan_stats* sta
         stats->kernel_launches = h->launches;
         stats->fused = h->last_fused ? 1 : 0;
         stats->fused_reject = h->fused_reject;
+        stats->gate_replayed = (h->pb.slice_mode || h->last_fused) ? -1 : ds.gate_again - 1;
         stats->h2d_bytes = (int64_t)h->h2d_bytes;
         stats->d2h_bytes = (int64_t)(h->out_count_bytes + h->out_mask_bytes + sizeof(DevStats));
     }

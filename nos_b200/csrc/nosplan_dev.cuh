@@ -78,6 +78,7 @@ struct DevStats {
     long long candidates, visited_nodes, geometry_evals, placements, candidate_nodes;
     int lacking_at_start, lacking_at_end;
     int path, pad;             // 1: node-parallel pass stood, 0: sequential sweep
+    int gate_again, pad2;      // nodes processed a second time, with the cluster-wide gate, after the gate replay (sweep.cu)
 };
 
 // ---- exchange over peer memory (slice mode on NVLink-connected GPUs, one process per GPU) ------------------------------
@@ -177,6 +178,13 @@ struct DevProblem {
     int32_t* next_node;              // [4]  [0] work counter of the node-parallel pass, [1] / [2] CTAs of k_prepass / k_plan_parallel done
     int32_t* wave;                   // [8]  [0] k_plan_sweep hands the plan to k_plan_waves  [1],[2] first node of the wave that changes
                                      //      the lacking vector (by wave parity)  [3] candidate nodes  [4] waves run
+    // gate replay (sweep.cu, gate_scan): what a node processed WITHOUT the cluster-wide gate did to the slice columns, kept when
+    // some node's accounts disagree with its GPUs, so that the gate can be checked afterwards in name order
+    long long* rec_dw;               // [N][KP] Allocatable from the geometry minus the snapshot's (mig/node.go:172-174)
+    int2* rec_pn;                    // [N][KP] .x devices the node's new pods took, per profile; .y most devices the gate would have had to
+                                     //         grant at any GPU.AddPod attempt of the node (>= .x: failed attempts of multi-profile pods count)
+    int32_t* rec_fl;                 // [N]     1 | updated << 1 | pods added << 2
+    long long* gate_state;           // [KP + 2] waves: sum(alloc - requested) per slice column, `committed`, first node that fails the gate
     // single-launch Plan() (fused.cu): padded pod costs, their minima per 8 and per 64 positions, runs, units
     const unsigned char* fp_blob;
     int fp_off[FP_NOFF];             // byte offsets in the blob: key masks, model ranges, runs, runs per profile (geometry rows

@@ -56,6 +56,7 @@ struct WarpScratch {       // per-warp shared memory
     SNode nd;
     uint4 pack[2];         // min(required, 255) and the required >= 256 mask, one byte per profile
     long long Dg[KP], allocF[KP], reqF[KP];
+    int need[KP];          // gate-less modes: most devices of a profile the gate would have had to grant a multi-profile pod (see gate_scan)
 };
 
 struct Tables {            // CTA-wide shared memory, read-only after the prologue
@@ -345,12 +346,15 @@ __device__ __forceinline__ void tracker_remove(const DevProblem& pb, int key, un
 // One candidate node, start to finish.  `ws.nd` holds the node.  Returns the number of pods added.
 //   lack      lane p: SliceTracker.lackingSlices[p] (PAR: SATURATED on the lacking profiles, never modified)
 //   D         lane p: cluster-wide sum(Allocatable - Requested) of slice column p (unused when PAR)
-template <int MODE>
+//   GATE      the cluster-wide gate (core/snapshot.go:132-165) is evaluated.  Always in the sequential sweep; in the other
+//             modes it is vacuous when every node's accounts agree with its GPUs, and where they do not the node is first
+//             processed without it, leaving a record (write_gate_record) from which gate_scan decides afterwards, in name order, whether the
+//             gate would have made a difference -- only then is the node processed again with GATE set
+template <int MODE, bool GATE = (MODE == M_SEQ)>
 __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& ws, const Tables& tb, const PodCache* pc,
                                             unsigned* removed, int& lack, long long& D, bool& committed,
                                             long long& st_evals, long long& st_place, int lane, int& dirty, bool& upd_out) {
     constexpr bool PAR = MODE == M_PAR;        // saturated view: geometry of all GPUs at once, global placed bitmap
-    constexpr bool GATE = MODE == M_SEQ;       // the cluster-wide gate (core/snapshot.go:132-165); vacuous in the other modes
     SNode& nd = ws.nd;
     const bool mig = pb.kind == NOSPLAN_KIND_MIG;
     const int K = pb.K, fm = pb.filter_mode;
@@ -387,7 +391,7 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     if (lane < K)
         for (int g = 0; g < ng; ++g) newA += (long long)bytes(nd.used[g])[lane] + bytes(nd.free_[g])[lane];
     const long long allocF = upd ? newA : oldA;                // Allocatable of the forked entry the pods are added to
-    if (lane < KP) { ws.allocF[lane] = allocF; ws.reqF[lane] = oldR; ws.Dg[lane] = GATE ? D - oldA + allocF : 0; }
+    if (lane < KP) { ws.allocF[lane] = allocF; ws.reqF[lane] = oldR; ws.Dg[lane] = GATE ? D - oldA + allocF : 0; ws.need[lane] = 0; }
     long long remc = nd.alloc[0] - nd.req[0], remm = nd.alloc[1] - nd.req[1], reme = nd.alloc[2] - nd.req[2];
     const bool podcount_ok = nd.npods + 1 <= nd.allowed;
     // no pod requests ephemeral storage and the node is not over-committed on it: every `0 <= reme` test holds
@@ -609,6 +613,9 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
                     }
                 }
                 if (!ok) continue;
+                // GPU.AddPod is attempted, and a failed attempt may leave devices moved: without the gate, note what it would
+                // have had to grant for this attempt (devices of the profile taken so far on this node + this pod's)
+                if (!GATE && q_l > 0) ws.need[lane] = max(ws.need[lane], (int)(ws.reqF[lane] - oldR) + q_l);
                 bool placed = false, moved = false;                // Node.AddPod: GPUs in order, profiles ascending
                 for (int g = 0; g < ng && !placed; ++g) {
                     const int fr = (lane < KP) ? (int)bytes(nd.free_[g])[lane] : 0;
@@ -655,6 +662,24 @@ __device__ __forceinline__ int process_node(const DevProblem& pb, WarpScratch& w
     return added;
 }
 
+// What gate_scan replays for a node that process_node has just taken WITHOUT the gate: Allocatable from the geometry minus the
+// snapshot's (devices only move from free to used while pods are added, so the sum is still the one UpdateGeometryFor left),
+// the devices its new pods took, and the outcome.
+__device__ __forceinline__ void write_gate_record(const DevProblem& pb, const WarpScratch& ws, int lane, int added, bool upd) {
+    const SNode& nd = ws.nd;
+    if (lane < KP) {
+        long long newA = 0;
+        if (lane < pb.K)
+            for (int g = 0; g < nd.ng; ++g)
+                newA += (long long)reinterpret_cast<const uint8_t*>(&nd.used[g])[lane] + reinterpret_cast<const uint8_t*>(&nd.free_[g])[lane];
+        const long long oldA = (lane < pb.K) ? nd.alloc[3 + lane] : 0, oldR = (lane < pb.K) ? nd.req[3 + lane] : 0;
+        const int pl = (int)(ws.reqF[lane] - oldR);
+        pb.rec_dw[(size_t)nd.idx * KP + lane] = newA - oldA;
+        pb.rec_pn[(size_t)nd.idx * KP + lane] = make_int2(pl, max(pl, ws.need[lane]));
+    }
+    if (lane == 0) pb.rec_fl[nd.idx] = 1 | (upd ? 2 : 0) | (added << 2);
+}
+
 __device__ __forceinline__ void load_tables(const DevProblem& pb, Tables& tb, int tid, int nthreads) {
     if (pb.kind != NOSPLAN_KIND_MIG) return;
     for (int r = tid; r < pb.n_rows; r += nthreads) { uint4 row = pb.geom[r]; tb.geom[r] = row; tb.gmask[r] = nz_mask(row); }
@@ -669,7 +694,9 @@ __device__ __forceinline__ void load_tables(const DevProblem& pb, Tables& tb, in
 // Is the node-parallel pass applicable?  lane p evaluates profile p; warp-uniform result.
 // Saturation bound: one GPU holds at most M_p devices of profile p (allowed geometries / memory, or its t0 free
 // count), a node has at most G GPUs, so lack[p] > (G+2)*M_p keeps every comparison against `required` one-sided.
-__device__ __forceinline__ bool fast_applicable(const DevProblem& pb, int lack_p, int lane) {
+// any_accounts: also when some node's accounts disagree with its GPUs or a pod class asks for several profiles (the pass then
+// leaves records for the gate replay)
+__device__ __forceinline__ bool fast_applicable(const DevProblem& pb, int lack_p, int lane, bool any_accounts = false) {
     bool ok = true;
     if (lane < KP && lack_p > 0) {
         int sat = pb.sat_m[lane];
@@ -678,7 +705,94 @@ __device__ __forceinline__ bool fast_applicable(const DevProblem& pb, int lack_p
         ok = sat >= 0 && (long long)lack_p > (long long)(pb.G + 2) * m;
     }
     const bool any_lack = __ballot_sync(FULL, lane < KP && lack_p > 0) != 0;
-    return __all_sync(FULL, ok) && any_lack && pb.fast_eligible && pb.gflags[0] == 0;
+    return __all_sync(FULL, ok) && any_lack && (any_accounts || (pb.fast_eligible && pb.gflags[0] == 0));
+}
+
+// ---- gate replay.  Nodes [a, b) were processed without the cluster-wide gate (core/snapshot.go:132-165) and left records.
+// The gate compares, per requested profile, the running cluster total D[p] = sum(Allocatable - Requested) with the pod's
+// quantity, in front of GPU.AddPod.  While a node is processed the total only shrinks (by the devices its pods take), so every
+// attempt of the node passes the gate iff D + dA - need >= 0, need = the largest (devices taken so far + the pod's own) over
+// the attempts that matter: the placements (a pod GPU.AddPod refuses cleanly is skipped whatever the gate says) and, for pods
+// asking for several profiles, every attempt -- a refused one may leave devices moved (mig/gpu.go:234-245), which the gate
+// would have prevented.  Walks the candidates in name order, 32 per step (lane = node, warp scans of the per-node change of
+// D under the Commit / Revert rules of process_node), and stops at the first node with an attempt that would not have passed:
+// returns it (b: none) with D (lane p: profile p) and `committed` as they are in front of that node.
+template <bool COHERENT>
+__device__ __forceinline__ int gate_scan(const DevProblem& pb, int a, int b, unsigned profs, long long& D, bool& committed, int lane) {
+    // COHERENT: the records were written by other SMs inside this kernel (waves): read them at L2
+    auto ld_dw = [&](int i, int p) { const long long* q = &pb.rec_dw[(size_t)i * KP + p]; return COHERENT ? __ldcg(q) : *q; };
+    auto ld_pn = [&](int i, int p) { const int2* q = &pb.rec_pn[(size_t)i * KP + p]; return COHERENT ? __ldcg(q) : *q; };
+    const int n_prof = __popc(profs);
+    for (int base = a; base < b; base += 32) {
+        const int i = base + lane;
+        const bool on = i < b && __ldcg(reinterpret_cast<const unsigned char*>(pb.cand_flag) + i) != 0;
+        const int fl = on ? (COHERENT ? __ldcg(&pb.rec_fl[i]) : pb.rec_fl[i]) : 0;
+        const bool added = (fl >> 2) > 0, upd = (fl & 2) != 0;
+        const unsigned cb = __ballot_sync(FULL, added);
+        const bool comm_before = committed || (cb & ((1u << lane) - 1)) != 0;
+        // one profile: the node's change of D[p] under the Commit / Revert rules, its inclusive scan over the 32 nodes, and
+        // whether some attempt of the node would have failed the gate
+        auto step = [&](int p, long long dw, int2 pn, long long& incl, bool& bad) {
+            const long long g = upd ? dw : 0;                                  // Allocatable of the forked entry minus the snapshot's
+            const long long delta = !on ? 0 : added ? g - pn.x : (comm_before ? 0 : dw);
+            incl = delta;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const long long t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+            const long long Dp = __shfl_sync(FULL, D, p);
+            bad = on && pn.y > 0 && Dp + incl - delta + g - pn.y < 0;
+        };
+        auto apply = [&](int p, long long incl, int v) {
+            const long long tot = v == 0 ? 0 : __shfl_sync(FULL, incl, v - 1);
+            if (lane == p) D += tot;
+        };
+        int v = 32;
+        if (n_prof <= 4) {                                      // the usual case: every load of the step in flight at once
+            int pp[4]; long long dw[4], incl[4]; int2 pn[4];
+            unsigned m = profs;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { pp[k] = m ? __ffs(m) - 1 : -1; m &= m - 1; }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const bool ld = on && pp[k] >= 0; dw[k] = ld ? ld_dw(i, pp[k]) : 0; pn[k] = ld ? ld_pn(i, pp[k]) : make_int2(0, 0); }
+            bool viol = false;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (pp[k] >= 0) { bool bad; step(pp[k], dw[k], pn[k], incl[k], bad); viol = viol || bad; }
+            const unsigned vm = __ballot_sync(FULL, viol);
+            v = vm ? __ffs(vm) - 1 : 32;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (pp[k] >= 0) apply(pp[k], incl[k], v);
+        } else {
+            bool viol = false;
+            for (unsigned m = profs; m; m &= m - 1) {
+                const int p = __ffs(m) - 1;
+                long long incl; bool bad;
+                step(p, on ? ld_dw(i, p) : 0, on ? ld_pn(i, p) : make_int2(0, 0), incl, bad);
+                viol = viol || bad;
+            }
+            const unsigned vm = __ballot_sync(FULL, viol);
+            v = vm ? __ffs(vm) - 1 : 32;
+            for (unsigned m = profs; m; m &= m - 1) {
+                const int p = __ffs(m) - 1;
+                long long incl; bool bad;
+                step(p, on ? ld_dw(i, p) : 0, on ? ld_pn(i, p) : make_int2(0, 0), incl, bad);
+                apply(p, incl, v);
+            }
+        }
+        committed = committed || (cb & (v == 32 ? FULL : ((1u << v) - 1))) != 0;
+        if (v < 32) return base + v;
+    }
+    return b;
+}
+
+// profiles some pending pod requests: the only slice columns the gate ever looks at
+__device__ __forceinline__ unsigned requested_profiles(const DevProblem& pb, int lane) {
+    unsigned m = 0;
+    for (int r = lane; r < pb.n_runs; r += 32) {
+        const RunRec& rr = pb.runs[r];
+        if (rr.n_ent == 1) m |= 1u << rr.p_single;
+        else if (rr.n_ent > 1)
+            for (int p = 0; p < KP; ++p) if (rr.q[p]) m |= 1u << p;
+    }
+    return __reduce_or_sync(FULL, m);
 }
 
 }  // namespace
@@ -706,7 +820,11 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     build_run_masks(s_runs, pc.n_cached, s_masks, tid, blockDim.x);
     cudaGridDependencySynchronize();
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;
-    const bool applicable = fast_applicable(pb, lack0, lane);
+    // single GPU, some node's accounts disagree with its GPUs or a pod class asks for several profiles (GPU.AddPod may then fail
+    // half-way and leave devices moved, which the gate would have prevented): the pass runs without the gate and leaves records;
+    // k_plan_waves replays the gate over them in name order (mode 3) and processes again the few nodes where it matters
+    const bool gate_spec = pb.verify_inline && !pb.xf_on && (pb.gflags[0] != 0 || !pb.fast_eligible);
+    const bool applicable = fast_applicable(pb, lack0, lane, gate_spec);
     if (!applicable) {
         if (pb.verify_inline && blockIdx.x == 0 && tid == 0) pb.wave[0] = 2;     // k_plan_waves takes the plan from here
         if (!pb.xf_on) return;
@@ -731,7 +849,8 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
         store_node(ws.nd, nr, i, lane);
         __syncwarp();
         ++visited;
-        process_node<M_PAR>(pb, ws, tb, &pc, pb.placed, lack, D, committed, st_evals, st_place, lane, dirty_unused, upd_unused);
+        const int added = process_node<M_PAR>(pb, ws, tb, &pc, pb.placed, lack, D, committed, st_evals, st_place, lane, dirty_unused, upd_unused);
+        if (gate_spec) write_gate_record(pb, ws, lane, added, upd_unused);
     }
     if (lane == 0 && visited) {
         atomicAdd(&pb.acc[0], (unsigned long long)st_place);
@@ -741,6 +860,7 @@ __global__ void __launch_bounds__(128, PAR_MIN_BLOCKS) k_plan_parallel(DevProble
     // single GPU: the CTA that finishes last verifies the saturation hypothesis on the final lacking vector (what
     // k_plan_sweep does for the sharded drivers) and either publishes the counters or hands the plan to k_plan_waves
     if (pb.verify_inline && applicable && last_block_done(&pb.next_node[2]) && warp == 0) {
+        if (gate_spec) { if (lane == 0) pb.wave[0] = 3; return; }
         const int le = lack0 - ((lane < KP) ? __ldcg(&pb.lack_dec[lane]) : 0);
         const bool ok = fast_applicable(pb, lack0 > 0 ? le : 0, lane) && __all_sync(FULL, !(lane < KP && lack0 > 0) || le > 0);
         const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0)), lack_end = __popc(__ballot_sync(FULL, le > 0));
@@ -1023,6 +1143,72 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
     const int lack0 = (lane < KP) ? pb.lack[lane] : 0;        // the vector at t0: nothing on this path has touched it yet
     const int lack_start = __popc(__ballot_sync(FULL, lack0 > 0));
     bool as_waves = true;
+    // some node's accounts disagree with its GPUs, or a pod class asks for several profiles: the cluster-wide gate is not implied
+    // by GPU.AddPod, or has a say in what a failed GPU.AddPod leaves behind; it is replayed over the records the gate-less passes
+    // leave (gate_scan)
+    const bool gate_on = pb.gflags[0] != 0 || !pb.fast_eligible;
+    int chain_cands = -1;                                      // >= 0: mode 3 fell through to the chain with this many candidates
+    if (mode == 3) {
+        // ---- the node-parallel pass ran without the gate.  One warp replays the gate in name order; a node whose pods would
+        //      not all have passed it is processed again, with the gate, on the exact running totals.
+        if (blockIdx.x != 0 || warp != 0) return;
+        WarpScratch& cw = ws_all[0];
+        const unsigned profs = requested_profiles(pb, lane);
+        int lack = lack0 > 0 ? SATURATED : 0, dirty_unused = 0, again = 0;
+        long long D = (lane < KP) ? pb.tot[lane] : 0, ev_unused = 0, pl_diff = 0;
+        bool committed = false, upd_unused = false;
+        for (int from = 0;;) {
+            const int v = gate_scan<false>(pb, from, pb.N, profs, D, committed, lane);
+            if (v >= pb.N) break;
+            const int spec_added = pb.rec_fl[v] >> 2;
+            NodeRegs nr;
+            load_node(pb, v, lane, nr);
+            store_node(cw.nd, nr, v, lane);
+            if (lane < nr.ng) {                                 // GetPartitioningState again: the gate-less pass may have written the row
+                const int x = v * pb.G + lane;
+                pb.out_count[x] = add_bytes(pb.gpu_used[x], pb.gpu_free[x]);
+                pb.out_mask[x] = pb.gpu_umask[x] | pb.gpu_fmask[x];
+            }
+            __syncwarp();
+            long long pl = 0;
+            process_node<M_PAR, true>(pb, cw, tb, &pc, pb.placed, lack, D, committed, ev_unused, pl, lane, dirty_unused, upd_unused);
+            pl_diff += pl - spec_added;
+            ++again;
+            from = v + 1;
+        }
+        // the saturation hypothesis, as the last CTA of k_plan_parallel checks it.  Keys only the gate-less run of a node placed
+        // stay in the bitmap: the final vector can come out smaller than it is, never larger, so a plan that stands here stands.
+        const int le = lack0 - ((lane < KP) ? __ldcg(&pb.lack_dec[lane]) : 0);
+        const bool ok = fast_applicable(pb, lack0 > 0 ? le : 0, lane, true) && __all_sync(FULL, !(lane < KP && lack0 > 0) || le > 0);
+        const int lack_end = __popc(__ballot_sync(FULL, le > 0));
+        if (ok) {
+            if (lane == 0) {
+                DevStats* st = pb.stats;
+                const long long vis = (long long)__ldcg(&pb.acc[2]);
+                st->visited_nodes = vis; st->candidates = vis * pb.P; st->candidate_nodes = vis;
+                st->geometry_evals = (long long)__ldcg(&pb.acc[1]);
+                st->placements = (long long)__ldcg(&pb.acc[0]) + pl_diff;
+                st->lacking_at_start = lack_start; st->lacking_at_end = lack_end;
+                st->path = 1; st->pad = 0; st->gate_again = again + 1;
+            }
+            return;
+        }
+        // saturation lost on the way: drop the speculative plan; the chain below runs it from the untouched t0 state
+        int c = 0;
+        for (int i = lane; i < pb.N; i += 32) c += pb.cand_flag[i] != 0;
+        chain_cands = __reduce_add_sync(FULL, c);
+        for (int x = lane; x < pb.N * pb.G; x += 32) {
+            const int i = x / pb.G, j = x - i * pb.G;
+            if (j < pb.node_gpu_count[i]) {
+                pb.out_count[x] = add_bytes(pb.gpu_used[x], pb.gpu_free[x]);
+                pb.out_mask[x] = pb.gpu_umask[x] | pb.gpu_fmask[x];
+            }
+        }
+        for (int w = lane; w < (pb.n_keys + 31) / 32; w += 32) pb.placed[w] = 0;
+        if (lane == 0) pb.stats->lacking_at_start = lack_start;
+        __syncwarp();
+        as_waves = false;
+    }
     if (mode == 2) {
         // the node-parallel pass was rejected or did not apply (single-GPU driver): drop whatever it wrote, then choose
         // between waves and the single-warp chain exactly as k_plan_sweep does for the sharded drivers
@@ -1038,9 +1224,9 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
         if (gtid < 4) pb.acc[gtid] = 0;
         long long total = 0;
         for (int p = 0; p < KP; ++p) total += max(0, __shfl_sync(FULL, lack0, p));
-        as_waves = pb.gflags[0] == 0 && lack_start > 0 && total * 45 < (long long)pb.N * 17;
+        as_waves = lack_start > 0 && total * 45 < (long long)pb.N * 17;
     }
-    {   // len(GetCandidateNodes()) for the stats; first-change slots start at "none"
+    if (chain_cands < 0) {   // len(GetCandidateNodes()) for the stats; first-change slots start at "none"
         int c = 0;
         for (int i = blockIdx.x * blockDim.x + tid; i < pb.N; i += gridDim.x * blockDim.x) c += pb.cand_flag[i] != 0;
         c = __reduce_add_sync(FULL, c);
@@ -1050,8 +1236,8 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
             atomicAdd(&pb.wave[3], s_cnt[0] + s_cnt[1] + s_cnt[2] + s_cnt[3]);
             if (blockIdx.x == 0) { pb.wave[1] = INT_MAX; pb.wave[2] = INT_MAX; pb.stats->lacking_at_start = lack_start; }
         }
+        grid.sync();
     }
-    grid.sync();
 
     if (!as_waves) {
         // ---- the chain: one warp, nodes in name order, exact lacking vector, gate and removed-set as in k_plan_sweep (the
@@ -1075,7 +1261,7 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
         if (lane == 0) {
             DevStats* st = pb.stats;
             st->visited_nodes = vis; st->candidates = vis * pb.P; st->geometry_evals = ev; st->placements = pl;
-            st->candidate_nodes = lack_start > 0 ? __ldcg(&pb.wave[3]) : 0;   // not reached on the early return (planner.go:80-83)
+            st->candidate_nodes = lack_start > 0 ? (chain_cands >= 0 ? chain_cands : __ldcg(&pb.wave[3])) : 0;   // not reached on the early return (planner.go:80-83)
             st->lacking_at_start = lack_start; st->lacking_at_end = lack_end; st->path = 0;
         }
         return;
@@ -1103,15 +1289,17 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
             ++vis; ++seen;
             process_node<M_SEQ>(pb, ws, tb, &pc, pb.placed, lack, Dc, comm, ev, pl, lane, dirty_unused, upd_unused);
         }
-        if (lane < KP) pb.lack[lane] = lack;
+        if (lane < KP) { pb.lack[lane] = lack; pb.gate_state[lane] = Dc; }
         if (lane == 0) {
             pb.acc[0] += (unsigned long long)pl; pb.acc[1] += (unsigned long long)ev; pb.acc[2] += (unsigned long long)vis;
             pb.wave[4] = i;
+            pb.gate_state[KP] = comm ? 1 : 0;
         }
         __threadfence();
     }
     grid.sync();
-    int a = __ldcg(&pb.wave[4]), n_waves = 0;
+    int a = __ldcg(&pb.wave[4]), n_waves = 0, n_again = 0;
+    const unsigned profs = gate_on ? requested_profiles(pb, lane) : 0u;
     for (;;) {
         const int lack = (lane < KP) ? __ldcg(&pb.lack[lane]) : 0;
         if (a >= pb.N || __ballot_sync(FULL, lack > 0) == 0) break;          // planner.go:94-97
@@ -1128,19 +1316,43 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
             store_node(ws.nd, nr, i, lane);
             __syncwarp();
             added = process_node<M_SPEC>(pb, ws, tb, &pc, pb.placed, lk, D, committed, ev, pl, lane, dirty, upd);
+            if (gate_on) write_gate_record(pb, ws, lane, added, upd);
             if (dirty && lane == 0) atomicMin(first_change, i);
         }
         grid.sync();
         // ---- phase 2
-        const int f = __ldcg(first_change);
-        const int last_valid = min(f, a + total_warps - 1);
+        int f = __ldcg(first_change);
+        int last_valid = min(f, a + total_warps - 1);
+        if (gate_on) {
+            // the gate, replayed over the nodes in front of f (or over the whole wave): the first node whose pods would not all
+            // have passed it ends the wave in f's place and is processed again with the gate, on the exact running totals
+            const int scan_end = min(f <= last_valid ? f : last_valid + 1, pb.N);
+            if (gw == 0) {
+                long long Dg = (lane < KP) ? __ldcg(&pb.gate_state[lane]) : 0;
+                bool cm = __ldcg(&pb.gate_state[KP]) != 0;
+                const int g = gate_scan<true>(pb, a, scan_end, profs, Dg, cm, lane);
+                if (lane < KP) pb.gate_state[lane] = Dg;
+                if (lane == 0) { pb.gate_state[KP] = cm ? 1 : 0; pb.gate_state[KP + 1] = g; }
+                __threadfence();
+            }
+            grid.sync();
+            const int g = (int)__ldcg(&pb.gate_state[KP + 1]);
+            if (g < scan_end) { f = g; last_valid = g; if (i == g) ++n_again; }
+        }
         if (have && i <= last_valid) {
             if (i == f) {
                 store_node(ws.nd, nr, i, lane);                              // phase 1 moved devices around in the copy
                 __syncwarp();
                 ev = 0; pl = 0; lk = lack;
                 int d2 = 0;
-                process_node<M_COMMIT>(pb, ws, tb, &pc, pb.placed, lk, D, committed, ev, pl, lane, d2, upd);
+                if (gate_on) {
+                    long long Dg = (lane < KP) ? __ldcg(&pb.gate_state[lane]) : 0;
+                    bool cm = __ldcg(&pb.gate_state[KP]) != 0;
+                    process_node<M_COMMIT, true>(pb, ws, tb, &pc, pb.placed, lk, Dg, cm, ev, pl, lane, d2, upd);
+                    if (lane < KP) pb.gate_state[lane] = Dg;
+                    if (lane == 0) pb.gate_state[KP] = cm ? 1 : 0;
+                } else
+                    process_node<M_COMMIT>(pb, ws, tb, &pc, pb.placed, lk, D, committed, ev, pl, lane, d2, upd);
                 if (lane < KP) pb.lack[lane] = lk;
             } else if (added > 0 && upd && lane < ws.nd.ng) {                // partitioningState[n] = GetPartitioning(n) (planner.go:138)
                 const int x = i * pb.G + lane;
@@ -1158,6 +1370,7 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
         atomicAdd(&pb.acc[0], (unsigned long long)st_place);
         atomicAdd(&pb.acc[1], (unsigned long long)st_evals);
         atomicAdd(&pb.acc[2], (unsigned long long)st_visited);
+        if (n_again) atomicAdd(&pb.stats->gate_again, n_again);
     }
     grid.sync();
     if (gw == 0) {
@@ -1173,6 +1386,7 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
             st->lacking_at_end = lack_end;
             st->path = 0;
             st->pad = n_waves;
+            if (gate_on) atomicAdd(&st->gate_again, 1);       // count + 1: 0 means no replay took place
         }
     }
 }
@@ -1196,7 +1410,7 @@ cudaError_t sweep_prepare_device(int* par_blocks, int* wave_blocks) {
 }
 
 cudaError_t launch_parallel(const DevProblem& pb, int max_blocks, cudaStream_t st) {
-    const bool work = pb.fast_eligible && pb.N > 0 && pb.P > 0 && pb.node_hi > pb.node_lo;
+    const bool work = (pb.fast_eligible || pb.verify_inline) && pb.N > 0 && pb.P > 0 && pb.node_hi > pb.node_lo;
     if (!work && !pb.xf_on) return cudaSuccess;            // fused slice mode: the kernel still pushes this rank's (empty) block
     int blocks = work ? (pb.node_hi - pb.node_lo + 3) / 4 : 1;
     if (blocks > max_blocks) blocks = max_blocks;
@@ -1229,7 +1443,7 @@ void launch_shard_combine(const DevProblem& pb, const void* gathered, int world,
 
 // always queued behind k_plan_sweep for problems the waves can take; returns at once unless k_plan_sweep handed over
 cudaError_t launch_waves(const DevProblem& pb, int max_blocks, cudaStream_t st) {
-    if (!pb.fast_eligible || pb.N == 0 || pb.P == 0 || pb.slice_mode) return cudaSuccess;
+    if ((!pb.fast_eligible && !pb.verify_inline) || pb.N == 0 || pb.P == 0 || pb.slice_mode) return cudaSuccess;
     int blocks = (pb.N + 3) / 4;
     if (blocks > max_blocks) blocks = max_blocks;
     DevProblem arg = pb;

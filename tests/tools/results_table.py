@@ -94,7 +94,10 @@ print("`saturating`: no demanded profile has a free device at t0 and demand exce
 print()
 print("| config | regime | filter | nodes x GPUs, pods | candidates | path | GPU Plan() p50 / p95 (µs) | GPU candidates/s | GPU end-to-end p50 (µs) | CPU incremental port (ms) | CPU candidates/s | parity |")
 print("|---|---|---|---|---|---|---|---|---|---|---|---|")
+ONLY = [a[7:] for a in sys.argv if a.startswith("--only=")]
 for name, kind, n, g, p, seed in CONFIGS:
+    if ONLY and not any(o in name for o in ONLY):
+        continue
     for regime in (("saturating", "satisfiable") if ("pods" not in name and name != "C1") else ("saturating",)):
         for fm, fname in ((pk.FILTER_NONE, "none"), (pk.FILTER_RESOURCES_FIT, "resources_fit")) if ("pods" not in name or "1000 pods" in name and "," not in name[12:]) else ((pk.FILTER_RESOURCES_FIT, "resources_fit"),):
             snap, pods = make(name, kind, n, g, p, seed, regime)
@@ -104,6 +107,8 @@ for name, kind, n, g, p, seed in CONFIGS:
                 st[k] == ost[k] for k in ("candidates", "visited_nodes", "placements", "geometry_evals", "lacking_at_end"))
             c = st["candidates"]
             path = "single launch" if st["fused"] else ("node-parallel" if st["path"] == 1 else (f"sequential, {st['waves']} waves" if st["waves"] else "sequential"))
+            if st.get("gate_replayed", -1) >= 0:
+                path += f", gate replayed ({st['gate_replayed']} nodes planned again)"
             if st["fused_reject"]:
                 path += f" (single launch rejected: {st['fused_reject']})"
             n, g = snap.n_nodes, snap.gpus_per_node
