@@ -576,6 +576,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     L.out_end = o;
     // gate replay records (sweep.cu): written before they are read, never cleared
     put(L.rec_dw, 8 * (size_t)N * KP); put(L.rec_pl, 8 * (size_t)N * KP); put(L.rec_fl, 4 * (size_t)N); put(L.gate_state, 8 * (KP + 2));
+    put(L.rec_chunk, 32 * (size_t)KP * ((size_t)N / 32 + 2)); put(L.rec_chunk_fl, 4 * ((size_t)N / 32 + 2));
     put(L.pod_cpu, 8 * (size_t)P); put(L.pod_mem, 8 * (size_t)P); put(L.pod_eph, 8 * (size_t)P);
     put(L.pod_key, 4 * (size_t)P); put(L.pod_flags, 4 * (size_t)P);
     put(L.pod_sptr, 4 * ((size_t)P + 1)); put(L.pod_scol, 4 * (size_t)nnz); put(L.pod_sqty, 8 * (size_t)nnz);
@@ -674,6 +675,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     h->d_cand_idx = (int32_t*)(A + L.cand_idx);
     pb.rec_dw = (long long*)(A + L.rec_dw); pb.rec_pn = (int2*)(A + L.rec_pl); pb.rec_fl = (int32_t*)(A + L.rec_fl);
     pb.gate_state = (long long*)(A + L.gate_state);
+    pb.rec_chunk = (long long*)(A + L.rec_chunk); pb.rec_chunk_fl = (int32_t*)(A + L.rec_chunk_fl);
     h->d_work = A + L.tot; h->work_bytes = L.work_end - L.tot; h->small_bytes = small_bytes;
     h->run_parity = 1; h->bound_copy = 0;                    // pb points at copy 0; the first run flips to it
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;

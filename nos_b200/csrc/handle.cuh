@@ -12,7 +12,7 @@ namespace nsp {
 struct Layout {            // byte offsets into the arena / staging buffer
     size_t model_off, geom, node_gpu_count, gpu_model, gpu_mem, gpu_used, gpu_free, gpu_umask, gpu_fmask,
         node_alloc, node_req, node_allowed, node_npods, nodes_end,
-        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, wave, work_end, cand_flag, cand_idx, rec_dw, rec_pl, rec_fl, gate_state, out_count, out_mask, out_end,
+        tot, lack, stats, maxfree, gflags, acc, lack_dec, next_node, wave, work_end, cand_flag, cand_idx, rec_dw, rec_pl, rec_fl, rec_chunk, rec_chunk_fl, gate_state, out_count, out_mask, out_end,
         pod_cpu, pod_mem, pod_eph, pod_key, pod_flags, pod_sptr, pod_scol, pod_sqty, runs, run_chunk_off,
         cmin_cpu, cmin_mem, cmin_eph, fp_blob, upload_end, placed, entry_lack, total;
 };

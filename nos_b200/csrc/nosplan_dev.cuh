@@ -184,6 +184,8 @@ struct DevProblem {
     int2* rec_pn;                    // [N][KP] .x devices the node's new pods took, per profile; .y most devices the gate would have had to
                                      //         grant at any GPU.AddPod attempt of the node (>= .x: failed attempts of multi-profile pods count)
     int32_t* rec_fl;                 // [N]     1 | updated << 1 | pods added << 2
+    long long* rec_chunk;            // [N/32 + 1][KP][4] the same per 32 nodes: change of D and smallest slack, with / without an earlier Commit
+    int32_t* rec_chunk_fl;           // [N/32 + 1] some node of the chunk added a pod
     long long* gate_state;           // [KP + 2] waves: sum(alloc - requested) per slice column, `committed`, first node that fails the gate
     // single-launch Plan() (fused.cu): padded pod costs, their minima per 8 and per 64 positions, runs, units
     const unsigned char* fp_blob;

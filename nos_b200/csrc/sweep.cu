@@ -783,6 +783,144 @@ __device__ __forceinline__ int gate_scan(const DevProblem& pb, int a, int b, uns
     return b;
 }
 
+// ---- the same, two levels.  gate_chunks (every warp of the grid, one chunk of 32 nodes at a time) condenses the records of a
+// chunk, per requested profile, into the chunk's total change of D and the smallest slack any attempt of its nodes leaves
+// relative to D at the chunk's start -- once for a Commit having happened before the chunk (1) and once for none (0: nodes in
+// front of the chunk's first adding node then leave their re-partitioned self behind, planner.go:144-149 with the aliasing of
+// DESIGN.md section 4).  chunk_scan (one warp, lane = chunk) walks 32 chunks per step exactly as gate_scan walks nodes and
+// stops at the first chunk with a node that would not have passed; gate_find puts the two together.
+constexpr long long GATE_INF = (1ll << 62);
+
+__device__ __forceinline__ long long warp_min_ll(long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const long long t = __shfl_xor_sync(FULL, v, o); v = t < v ? t : v; }
+    return v;
+}
+
+template <bool COHERENT>
+__device__ __forceinline__ void gate_chunks(const DevProblem& pb, int a, int b, unsigned profs, int lane, int gw, int total_warps) {
+    const int n_chunks = (b - a + 31) >> 5;
+    for (int c = gw; c < n_chunks; c += total_warps) {
+        const int i = a + 32 * c + lane;
+        const bool on = i < b && __ldcg(reinterpret_cast<const unsigned char*>(pb.cand_flag) + i) != 0;
+        const int fl = on ? (COHERENT ? __ldcg(&pb.rec_fl[i]) : pb.rec_fl[i]) : 0;
+        const bool added = (fl >> 2) > 0, upd = (fl & 2) != 0;
+        const unsigned cb = __ballot_sync(FULL, added);
+        const bool before_first = (cb & ((1u << lane) - 1)) == 0;      // no node of the chunk in front of this one added a pod
+        for (unsigned m = profs; m; m &= m - 1) {
+            const int p = __ffs(m) - 1;
+            long long dw = 0; int2 pn = make_int2(0, 0);
+            if (on) {
+                const long long* qd = &pb.rec_dw[(size_t)i * KP + p]; const int2* qp = &pb.rec_pn[(size_t)i * KP + p];
+                dw = COHERENT ? __ldcg(qd) : *qd; pn = COHERENT ? __ldcg(qp) : *qp;
+            }
+            const long long g = upd ? dw : 0;
+            const long long d1 = !on ? 0 : added ? g - pn.x : 0;
+            const long long d0 = !on ? 0 : added ? g - pn.x : (before_first ? dw : 0);
+            long long i0 = d0, i1 = d1;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long t0 = __shfl_up_sync(FULL, i0, o), t1 = __shfl_up_sync(FULL, i1, o);
+                if (lane >= o) { i0 += t0; i1 += t1; }
+            }
+            const bool chk = on && pn.y > 0;
+            const long long m0 = warp_min_ll(chk ? i0 - d0 + g - pn.y : GATE_INF), m1 = warp_min_ll(chk ? i1 - d1 + g - pn.y : GATE_INF);
+            if (lane == 31) {
+                long long* q = pb.rec_chunk + ((size_t)c * KP + p) * 4;
+                q[0] = i0; q[1] = i1; q[2] = m0; q[3] = m1;
+            }
+        }
+        if (lane == 0) pb.rec_chunk_fl[c] = cb != 0;
+    }
+}
+
+// chunks [c_lo, c_hi), at most 32: first chunk with a node that fails the gate (c_hi: none); D and `committed` advanced to its start
+__device__ __forceinline__ int chunk_scan(const DevProblem& pb, int c_lo, int c_hi, unsigned profs, long long& D, bool& committed, int lane) {
+    const int c = c_lo + lane;
+    const bool on = c < c_hi;
+    const unsigned cb = __ballot_sync(FULL, on && __ldcg(&pb.rec_chunk_fl[on ? c : c_lo]) != 0);
+    const bool comm_before = committed || (cb & ((1u << lane) - 1)) != 0;
+    auto load = [&](int p, long long& T, long long& M) {
+        T = 0; M = GATE_INF;
+        if (on) {
+            const long long* q = pb.rec_chunk + ((size_t)c * KP + p) * 4;
+            T = __ldcg(q + (comm_before ? 1 : 0)); M = __ldcg(q + (comm_before ? 3 : 2));
+        }
+    };
+    auto step = [&](int p, long long T, long long M, long long& incl, bool& bad) {
+        incl = T;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const long long t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+        const long long Dp = __shfl_sync(FULL, D, p);
+        bad = on && M < GATE_INF && Dp + incl - T + M < 0;
+    };
+    auto apply = [&](int p, long long incl, int u) {
+        const long long tot = u == 0 ? 0 : __shfl_sync(FULL, incl, u - 1);
+        if (lane == p) D += tot;
+    };
+    int u = 32;
+    if (__popc(profs) <= 4) {                                   // the usual case: every load of the step in flight at once
+        int pp[4]; long long T[4], M[4], incl[4];
+        unsigned m = profs;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { pp[k] = m ? __ffs(m) - 1 : -1; m &= m - 1; }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { T[k] = 0; M[k] = GATE_INF; if (pp[k] >= 0) load(pp[k], T[k], M[k]); }
+        bool viol = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (pp[k] >= 0) { bool bad; step(pp[k], T[k], M[k], incl[k], bad); viol = viol || bad; }
+        const unsigned vm = __ballot_sync(FULL, viol);
+        u = vm ? __ffs(vm) - 1 : 32;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (pp[k] >= 0) apply(pp[k], incl[k], u);
+    } else {
+        bool viol = false;
+        for (unsigned m = profs; m; m &= m - 1) {
+            const int p = __ffs(m) - 1;
+            long long T, M, incl; bool bad;
+            load(p, T, M); step(p, T, M, incl, bad);
+            viol = viol || bad;
+        }
+        const unsigned vm = __ballot_sync(FULL, viol);
+        u = vm ? __ffs(vm) - 1 : 32;
+        for (unsigned m = profs; m; m &= m - 1) {
+            const int p = __ffs(m) - 1;
+            long long T, M, incl; bool bad;
+            load(p, T, M); step(p, T, M, incl, bad);
+            apply(p, incl, u);
+        }
+    }
+    committed = committed || (cb & (u == 32 ? FULL : ((1u << u) - 1))) != 0;
+    return min(c_lo + u, c_hi);
+}
+
+// first node of [from, b) that fails the gate (b: none), given the chunk summaries of [a, b) (chunks count from a); D and
+// `committed` are those in front of `from` on entry and in front of the returned node on exit
+template <bool COHERENT>
+__device__ __forceinline__ int gate_find(const DevProblem& pb, int a, int b, int from, unsigned profs, long long& D, bool& committed, int lane) {
+    const int n_chunks = (b - a + 31) >> 5;
+    while (from < b) {
+        const int c = (from - a) >> 5;
+        if ((from - a) & 31) {                                  // the rest of a chunk, node by node
+            const int end = min(b, a + 32 * (c + 1));
+            const int v = gate_scan<COHERENT>(pb, from, end, profs, D, committed, lane);
+            if (v < end) return v;
+            from = end;
+            continue;
+        }
+        const int c_hi = min(c + 32, n_chunks);
+        const int u = chunk_scan(pb, c, c_hi, profs, D, committed, lane);
+        from = min(b, a + 32 * u);
+        if (u < c_hi) {
+            const int end = min(b, from + 32);
+            const int v = gate_scan<COHERENT>(pb, from, end, profs, D, committed, lane);
+            if (v < end) return v;
+            from = end;
+        }
+    }
+    return b;
+}
+
 // profiles some pending pod requests: the only slice columns the gate ever looks at
 __device__ __forceinline__ unsigned requested_profiles(const DevProblem& pb, int lane) {
     unsigned m = 0;
@@ -1151,14 +1289,16 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
     if (mode == 3) {
         // ---- the node-parallel pass ran without the gate.  One warp replays the gate in name order; a node whose pods would
         //      not all have passed it is processed again, with the gate, on the exact running totals.
+        const unsigned profs = requested_profiles(pb, lane);
+        gate_chunks<false>(pb, 0, pb.N, profs, lane, blockIdx.x * (blockDim.x >> 5) + warp, gridDim.x * (blockDim.x >> 5));
+        grid.sync();
         if (blockIdx.x != 0 || warp != 0) return;
         WarpScratch& cw = ws_all[0];
-        const unsigned profs = requested_profiles(pb, lane);
         int lack = lack0 > 0 ? SATURATED : 0, dirty_unused = 0, again = 0;
         long long D = (lane < KP) ? pb.tot[lane] : 0, ev_unused = 0, pl_diff = 0;
         bool committed = false, upd_unused = false;
         for (int from = 0;;) {
-            const int v = gate_scan<false>(pb, from, pb.N, profs, D, committed, lane);
+            const int v = gate_find<false>(pb, 0, pb.N, from, profs, D, committed, lane);
             if (v >= pb.N) break;
             const int spec_added = pb.rec_fl[v] >> 2;
             NodeRegs nr;
@@ -1327,10 +1467,12 @@ __global__ void __launch_bounds__(128, 4) k_plan_waves(DevProblem pb) {
             // the gate, replayed over the nodes in front of f (or over the whole wave): the first node whose pods would not all
             // have passed it ends the wave in f's place and is processed again with the gate, on the exact running totals
             const int scan_end = min(f <= last_valid ? f : last_valid + 1, pb.N);
+            gate_chunks<true>(pb, a, scan_end, profs, lane, gw, total_warps);
+            grid.sync();
             if (gw == 0) {
                 long long Dg = (lane < KP) ? __ldcg(&pb.gate_state[lane]) : 0;
                 bool cm = __ldcg(&pb.gate_state[KP]) != 0;
-                const int g = gate_scan<true>(pb, a, scan_end, profs, Dg, cm, lane);
+                const int g = gate_find<true>(pb, a, scan_end, a, profs, Dg, cm, lane);
                 if (lane < KP) pb.gate_state[lane] = Dg;
                 if (lane == 0) { pb.gate_state[KP] = cm ? 1 : 0; pb.gate_state[KP + 1] = g; }
                 __threadfence();
