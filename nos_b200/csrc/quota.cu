@@ -18,6 +18,7 @@
 #include <string>
 #include <vector>
 
+#include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 
@@ -50,6 +51,9 @@ struct DevQuota {
     long long* chunk_sum;      // [chunks][QR] column sums of a chunk, then (in place) the running sum before the chunk
     int n_chunk_bound;
     long long fuse_ts_min, fuse_prio_min; int fuse_tbits, fuse_pbits;   // single-sort labelling (k_label_keys pass 1)
+    // labelling by buckets (k_label_scatter / k_label_segments): quota e owns buckets [b_first[e], b_first[e + 1]), a pod's bucket
+    // inside its quota is (creationTimestamp - min) >> b_shift[e]; per bucket: quota row, column sums, "sums published" flag
+    int n_buckets; const int32_t *b_first, *b_shift, *b_quota; long long* seg_sum; int32_t *seg_flag, *seg_ticket, *seg_overflow;
     // label changes (patchCapacityInfoIfDifferent): per sorted position, pod index << 1 | over-quota and "differs from the label on the pod"
     const uint8_t* cur_label; int32_t* chg_packed; uint8_t* chg_flag;
 };
@@ -497,6 +501,274 @@ __global__ void __launch_bounds__(256) k_label_chunk_prefix(DevQuota q) {
     if (lane < q.R) q.operator_used[(size_t)e * q.R + lane] = (q.min_mask[e] >> lane & 1) ? mine : 0;
 }
 
+// ---- labelling without a device-wide sort.  The most significant sort key is the quota row, and everything that follows --
+// ties, running sums, labels -- happens inside one quota.  The host, which counts the pods of every quota anyway, cuts a quota
+// with many pods into 2^k BUCKETS by the leading bits of creationTimestamp - min (the next sort key, so buckets are in order and
+// a tie group never straddles two), aiming at a few hundred pods per bucket.  Then:
+//   k_label_scatter   (cooperative) counting sort by bucket: per-CTA histogram in shared memory whose atomicAdd results are the
+//                     pods' ranks inside (CTA, bucket); one global atomicAdd per touched (CTA, bucket) reserves the CTA's stretch
+//                     of the bucket; after the grid barrier every CTA scans the counts itself and writes its pods'
+//                     (creationTimestamp - min | priority - min, pod) pairs to their slots.  Order inside a bucket: arbitrary.
+//   k_label_segments  one CTA per bucket (taken in order through a ticket): column sums of the bucket published at once (they do
+//                     not depend on the order), the bucket sorted in shared memory (bitonic, key then pod index: the order a
+//                     stable sort of the pods in index order gives), tie groups put in the comparator's order
+//                     (elasticquota.go:93-103), the sums of the quota's earlier buckets collected, running sums of the requests
+//                     per column against Min (elasticquota.go:44-60), labels, status.used.
+// A bucket with more than SEG_MAX pods (timestamps bunched together) raises seg_overflow: the host repeats the call with the
+// device-wide sort.
+constexpr int SCAT_THREADS = 256, SCAT_ITEMS = 8, SEG_NB_MAX = 8000, SEG_MAX = 2048, SEG_TARGET = 128, SEG_THREADS = 128;
+
+__device__ __forceinline__ int label_bucket(const DevQuota& q, int i) {      // q.n_buckets: no quota
+    const int ns = q.r_ns[i];
+    const int e = (ns >= 0 && ns < q.NS) ? q.ns_quota[ns] : -1;
+    if (e < 0) return q.n_buckets;
+    const int first = q.b_first[e], n_sub = q.b_first[e + 1] - first;
+    const unsigned long long t = (unsigned long long)(q.r_ts[i] - q.fuse_ts_min) >> q.b_shift[e];
+    return first + (int)min((unsigned long long)(n_sub - 1), t);
+}
+
+__global__ void __launch_bounds__(SCAT_THREADS) k_label_scatter(DevQuota q, int tile) {
+    extern __shared__ int s_i[];                               // [3][n_buckets + 2]
+    const int NB = q.n_buckets;
+    int* s_hist = s_i; int* s_base = s_i + (NB + 2); int* s_off = s_base + (NB + 2);
+    __shared__ int s_wtot[SCAT_THREADS / 32];
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lo = blockIdx.x * tile, hi = min(q.Pr, lo + tile);
+    for (int k = tid; k <= NB; k += SCAT_THREADS) s_hist[k] = 0;
+    __syncthreads();
+    int b_[SCAT_ITEMS], r_[SCAT_ITEMS];
+#pragma unroll
+    for (int u = 0; u < SCAT_ITEMS; ++u) {
+        const int i = lo + u * SCAT_THREADS + tid;
+        b_[u] = -1; r_[u] = 0;
+        if (i < hi) { b_[u] = label_bucket(q, i); r_[u] = atomicAdd(&s_hist[b_[u]], 1); }
+    }
+    __syncthreads();
+    for (int k = tid; k < NB; k += SCAT_THREADS) { const int c = s_hist[k]; s_base[k] = c ? atomicAdd(&q.seg_count[k], c) : 0; }
+    grid.sync();
+    // exclusive scan of the bucket counts, by every CTA for itself: contiguous bins per thread, warp scan, warp totals
+    const int per = (NB + SCAT_THREADS - 1) / SCAT_THREADS;
+    int mine = 0;
+    for (int k = tid * per; k < min(NB, (tid + 1) * per); ++k) mine += __ldcg(&q.seg_count[k]);
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) s_wtot[warp] = incl;
+    __syncthreads();
+    int before = incl - mine;
+    for (int w = 0; w < warp; ++w) before += s_wtot[w];
+    for (int k = tid * per; k < min(NB, (tid + 1) * per); ++k) {
+        s_off[k] = before;
+        if (blockIdx.x == 0) q.seg_off[k] = before;
+        before += __ldcg(&q.seg_count[k]);
+    }
+    if (blockIdx.x == 0 && tid == SCAT_THREADS - 1) q.seg_off[NB] = before;        // pods that have a quota
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < SCAT_ITEMS; ++u) {
+        const int i = lo + u * SCAT_THREADS + tid;
+        if (b_[u] < 0) continue;
+        if (b_[u] == NB) { q.over_quota[i] = 0; continue; }
+        const int slot = s_off[b_[u]] + s_base[b_[u]] + r_[u];
+        q.key_a[slot] = ((unsigned long long)(q.r_ts[i] - q.fuse_ts_min) << q.fuse_pbits) | (unsigned long long)((long long)q.r_prio[i] - q.fuse_prio_min);
+        q.val_a[slot] = i;
+    }
+}
+
+__global__ void __launch_bounds__(SEG_THREADS) k_label_segments(DevQuota q) {
+    __shared__ unsigned long long sk[SEG_MAX];
+    __shared__ int sv[SEG_MAX];
+    __shared__ long long s_warp[SEG_THREADS / 32][QR];
+    __shared__ long long s_carry[QR];
+    __shared__ int s_bucket;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_bucket = atomicAdd(q.seg_ticket, 1);       // buckets in order: the ones a CTA waits for below have started
+    __syncthreads();
+    const int b = s_bucket;
+    const int e = q.b_quota[b];
+    const int x0 = q.seg_off[b], n = q.seg_off[b + 1] - x0;
+    const int b0 = q.b_first[e];
+    const bool last = b + 1 == q.b_first[e + 1];
+    if (n > SEG_MAX) {                                          // timestamps bunched together: the host repeats with the device-wide sort
+        if (tid == 0) { *q.seg_overflow = 1; __threadfence(); atomicExch(&q.seg_flag[b], 1); }
+        return;
+    }
+    if (tid < QR) s_carry[tid] = 0;
+    if (q.b_first[e + 1] - b0 == 1) {
+        // the quota's only bucket: nobody waits for its sums
+        for (int k = tid; k < n; k += SEG_THREADS) { sk[k] = q.key_a[x0 + k]; sv[k] = q.val_a[x0 + k]; }
+    } else {
+        // ---- this bucket's column sums, published before anything else
+        long long v[QR];
+#pragma unroll
+        for (int c = 0; c < QR; ++c) v[c] = 0;
+        for (int k = tid; k < n; k += SEG_THREADS) {
+            const int i = q.val_a[x0 + k];
+            sk[k] = q.key_a[x0 + k]; sv[k] = i;
+#pragma unroll
+            for (int c = 0; c < QR; ++c) if (c < q.R) v[c] += quota_req_scalar(q, i, c);
+        }
+#pragma unroll
+        for (int c = 0; c < QR; ++c) {
+            if (c >= q.R) break;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v[c] += __shfl_xor_sync(0xffffffffu, v[c], o);
+            if (lane == 0) s_warp[warp][c] = v[c];
+        }
+        __syncthreads();
+        if (tid < q.R) {
+            long long t = 0;
+            for (int w = 0; w < SEG_THREADS / 32; ++w) t += s_warp[w][tid];
+            q.seg_sum[(size_t)b * QR + tid] = t;
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) atomicExch(&q.seg_flag[b], 1);
+    }
+    // ---- sort.  Warps without a pod of the bucket have nothing left to do (a barrier does not wait for threads that exited).
+    int np2 = 32;
+    while (np2 < n) np2 <<= 1;
+    const int n_warps = min(SEG_THREADS / 32, max(1, (n + 31) >> 5));
+    if (warp >= n_warps) return;
+    for (int k = n + tid; k < np2; k += 32 * n_warps) { sk[k] = ~0ull; sv[k] = INT_MAX; }
+    __syncthreads();
+    for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int h = tid; h < (np2 >> 1); h += 32 * n_warps) {       // one compare-exchange per thread: the pair (t, t | j)
+                const int t = ((h & ~(j - 1)) << 1) | (h & (j - 1)), u = t | j;
+                const unsigned long long ka = sk[t], kb = sk[u];
+                const int va = sv[t], vb = sv[u];
+                const bool gt = ka > kb || (ka == kb && va > vb);
+                if (gt == ((t & k) == 0)) { sk[t] = kb; sk[u] = ka; sv[t] = vb; sv[u] = va; }
+            }
+            if (np2 > 64 || j > 16) __syncthreads(); else __syncwarp();
+        }
+    __syncthreads();
+    // ---- tie groups (same creationTimestamp and priority): one thread per group, stable insertion sort with the comparator
+    for (int x = tid; x < n; x += 32 * n_warps) {
+        if (x > 0 && sk[x - 1] == sk[x]) continue;              // not a group leader
+        int end = x + 1;
+        while (end < n && sk[end] == sk[x]) ++end;
+        if (end - x < 2) continue;
+        bool amb = false;
+        for (int i = x + 1; i < end; ++i) {
+            const int v = sv[i];
+            int j = i;
+            while (j > x && tie_less(q, v, sv[j - 1], &amb)) { sv[j] = sv[j - 1]; --j; }
+            sv[j] = v;
+        }
+        for (int i = x; i < end && !amb; ++i)                   // the partial order must be a chain inside the group
+            for (int j = i + 1; j < end; ++j) { bool t = false; tie_less(q, sv[i], sv[j], &t); amb |= t; }
+        if (amb) *q.ambiguous = 1;
+    }
+    // ---- the quota's earlier buckets: their sums are the running sum this bucket starts from
+    {   // one earlier bucket per thread: all the flags and sums are in flight at once
+        long long acc[QR];
+#pragma unroll
+        for (int c = 0; c < QR; ++c) acc[c] = 0;
+        for (int p = b0 + tid; p < b; p += 32 * n_warps) {
+            while (*reinterpret_cast<volatile int32_t*>(&q.seg_flag[p]) == 0) __nanosleep(32);
+            __threadfence();
+#pragma unroll
+            for (int c = 0; c < QR; ++c) if (c < q.R) acc[c] += __ldcg(&q.seg_sum[(size_t)p * QR + c]);
+        }
+        __syncthreads();                                        // s_warp is free again (the sort and the tie groups are done)
+#pragma unroll
+        for (int c = 0; c < QR; ++c) {
+            if (c >= q.R) break;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+            if (lane == 0) s_warp[warp][c] = acc[c];
+        }
+        __syncthreads();
+        if (tid < q.R) { long long t = 0; for (int w = 0; w < n_warps; ++w) t += s_warp[w][tid]; s_carry[tid] = t; }
+        __syncthreads();
+    }
+    // ---- running sums in order, SEG_THREADS pods per step
+    // Alongside: reserveResource of the same pods into the quota's Used (elasticquotainfo.go:194-200, 276-292; what k_quota_used
+    // does with atomics when the labelling is not by buckets): Memory, MilliCPU and the scalars the request names.
+    const unsigned mm = q.min_mask[e];
+    long long uacc[QR], own = 0;
+    unsigned macc = 0;
+#pragma unroll
+    for (int c = 0; c < QR; ++c) uacc[c] = 0;
+    for (int base = 0; base < n; base += 32 * n_warps) {
+        const int x = base + tid;
+        const int i = x < n ? sv[x] : -1;
+        long long v[QR];
+#pragma unroll
+        for (int c = 0; c < QR; ++c) v[c] = (i >= 0 && c < q.R) ? quota_req_scalar(q, i, c) : 0;
+        if (i >= 0) {
+            unsigned rm = 0;
+            if (q.r_mask) rm = q.r_mask[i] & SCALAR_BITS;
+            else {
+#pragma unroll
+                for (int c = 4; c < QR; ++c) if (c < q.R && c != q.gm && v[c] != 0) rm |= 1u << c;
+            }
+            if (q.gm >= 0) rm |= 1u << q.gm;
+            macc |= rm;
+#pragma unroll
+            for (int c = 4; c < QR; ++c) if (rm >> c & 1) uacc[c] += v[c];
+        }
+#pragma unroll
+        for (int c = 0; c < QR; ++c) {
+            if (c >= q.R) break;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long t = __shfl_up_sync(0xffffffffu, v[c], o);
+                if (lane >= o) v[c] += t;
+            }
+            if (lane == 31) s_warp[warp][c] = v[c];
+        }
+        __syncthreads();
+        if (tid < q.R) {                                        // warp totals -> what precedes each warp; the step's total into the carry
+            long long run = s_carry[tid];
+            own -= run;
+            for (int w = 0; w < n_warps; ++w) { const long long t = s_warp[w][tid]; s_warp[w][tid] = run; run += t; }
+            s_carry[tid] = run;
+            own += run;
+        }
+        __syncthreads();
+        bool in_quota = true;
+#pragma unroll
+        for (int c = 0; c < QR; ++c) {
+            if (c >= q.R) break;
+            if ((mm >> c & 1) && v[c] + s_warp[warp][c] > q.qmin[(size_t)e * q.R + c]) in_quota = false;
+        }
+        if (i >= 0) {
+            q.over_quota[i] = in_quota ? 0 : 1;
+            if (q.cur_label) {
+                q.chg_packed[x0 + x] = (i << 1) | (in_quota ? 0 : 1);
+                q.chg_flag[x0 + x] = q.cur_label[i] != (in_quota ? NOSPLAN_LABEL_IN_QUOTA : NOSPLAN_LABEL_OVER_QUOTA);
+            }
+        }
+        __syncthreads();
+    }
+    if (last && tid < q.R) q.operator_used[(size_t)e * q.R + tid] = (mm >> tid & 1) ? s_carry[tid] : 0;
+    // Used: this bucket's share
+#pragma unroll
+    for (int c = 4; c < QR; ++c) {
+        if (c >= q.R) break;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) uacc[c] += __shfl_xor_sync(0xffffffffu, uacc[c], o);
+        if (lane == 0) s_warp[warp][c] = uacc[c];
+    }
+    macc = __reduce_or_sync(0xffffffffu, macc);
+    if (lane == 0) s_warp[warp][0] = (long long)macc;
+    __syncthreads();
+    if (tid < q.R && tid != 2 && tid != 3) {
+        long long t = own;                                      // Memory, MilliCPU: every pod's
+        if (tid >= 4) { t = 0; for (int w = 0; w < n_warps; ++w) t += s_warp[w][tid]; }
+        if (t != 0) atomicAdd((unsigned long long*)&q.used[(size_t)e * q.R + tid], (unsigned long long)t);
+    }
+    if (tid == 0) {
+        unsigned m = 0;
+        for (int w = 0; w < n_warps; ++w) m |= (unsigned)s_warp[w][0];
+        if (m & ~q.used_mask[e]) atomicOr(&q.used_mask[e], m);
+    }
+}
+
 }  // namespace nsp
 
 using namespace nsp;
@@ -540,17 +812,19 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
                  o_rns = put(4 * (size_t)Pr), o_rreq = put(8 * (size_t)Pr * R), o_rmask = put(4 * (size_t)Pr),
                  o_rprio = put(4 * (size_t)Pr), o_rts = put(8 * (size_t)Pr), o_rrank = put(4 * (size_t)Pr),
                  o_pns = put(4 * (size_t)Pp), o_preq = put(8 * (size_t)Pp * R), o_pmask = put(4 * (size_t)Pp),
-                 o_cur = put(want_changes ? (size_t)Pr : 0);
+                 o_cur = put(want_changes ? (size_t)Pr : 0),
+                 o_bfirst = put(4 * ((size_t)E + 2)), o_bshift = put(4 * ((size_t)E + 1)), o_bquota = put(4 * ((size_t)SEG_NB_MAX + 1));
     const size_t upload_end = o;
     // outputs (contiguous, one D2H)
     const size_t o_used = put(8 * ER), o_umask = put(4 * (size_t)E), o_amin = put(8 * QR), o_aused = put(8 * QR), o_aover = put(8 * QR),
                  o_amask = put(16), o_guar = put(8 * ER), o_pref = put((size_t)Pp), o_over = put((size_t)Pr), o_opused = put(8 * ER),
-                 o_amb = put(16), o_nsel = put(16);
+                 o_amb = put(16), o_nsel = put(16), o_ovf = put(16);
     const size_t out_end = o;
     const size_t o_sel = put(want_changes ? 4 * (size_t)Pr : 0);   // fetched by a second copy of exactly n_changes entries
     const size_t o_packed = put(want_changes ? 4 * (size_t)Pr : 0), o_flag = put(want_changes ? (size_t)Pr : 0);
     const size_t o_keya = put(8 * (size_t)Pr), o_keyb = put(8 * (size_t)Pr), o_vala = put(4 * (size_t)Pr), o_valb = put(4 * (size_t)Pr),
-                 o_segc = put(4 * ((size_t)E + 1)), o_sego = put(4 * ((size_t)E + 2)), o_choff = put(4 * ((size_t)E + 2));
+                 o_segc = put(4 * ((size_t)std::max(E, SEG_NB_MAX) + 2)), o_sego = put(4 * ((size_t)std::max(E, SEG_NB_MAX) + 2)),
+                 o_choff = put(4 * ((size_t)E + 2)), o_segsum = put(8 * (size_t)QR * (SEG_NB_MAX + 1)), o_segflag = put(4 * ((size_t)SEG_NB_MAX + 2));
     const int n_chunk_bound = Pr / 256 + E + 1;                 // every quota's last chunk may be partial
     const size_t o_chsum = put(8 * (size_t)n_chunk_bound * QR);
     size_t cub_bytes = 0;
@@ -581,6 +855,50 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     if (want_changes) cp(o_cur, lc->current, (size_t)Pr);
     if (Pp) { cp(o_pns, pending->ns, 4 * (size_t)Pp); cp(o_preq, pending->request, 8 * (size_t)Pp * R); cp(o_pmask, pending->request_mask, 4 * (size_t)Pp); }
 
+    // ---- host analysis of the labelling keys, in front of the copies so that no kernel ever waits for it
+    static thread_local bool force_global_sort = false;
+    int ebits = 1; while ((1ll << ebits) <= E) ++ebits;
+    long long tmin = LLONG_MAX, tmax = LLONG_MIN, pmin = LLONG_MAX, pmax = LLONG_MIN;
+    bool have_keys = false, ts_ok = false, by_buckets = false;
+    int tbits = 64, pbits = 32, n_buckets = 0;
+    if (want_label) {
+    // ranges of the two inner keys (host scan of the caller's arrays): if quota | timestamp | priority fit one 64-bit word
+    // a single radix sort over exactly the bits in use replaces the three stable passes
+    have_keys = running->creation_ts && running->priority;
+    // ... and the number of pods in every quota: the labelling then needs no device-wide sort (k_label_scatter)
+    static thread_local std::vector<int32_t> seg_n;
+    const bool count_segs = have_keys && E <= SEG_NB_MAX && !force_global_sort && !getenv("NOSPLAN_QUOTA_GLOBAL_SORT");
+    if (count_segs) seg_n.assign((size_t)E + 1, 0);
+    int32_t* seg_np = count_segs ? seg_n.data() : nullptr;
+    for (int i = 0; have_keys && i < Pr; ++i) {
+        const long long t = running->creation_ts[i], pr = running->priority[i];
+        tmin = std::min(tmin, t); tmax = std::max(tmax, t); pmin = std::min(pmin, pr); pmax = std::max(pmax, pr);
+        if (seg_np) { const int ns = running->ns[i]; const int e = (ns >= 0 && ns < NS) ? qs->ns_quota[ns] : -1; ++seg_np[e < 0 ? E : e]; }
+    }
+    auto bits_of = [](unsigned long long range) { int b = 1; while (b < 64 && (range >> b)) ++b; return b; };
+    ts_ok = have_keys && (unsigned long long)tmax - (unsigned long long)tmin < (1ull << 62);
+    tbits = ts_ok ? bits_of((unsigned long long)(tmax - tmin)) : 64; pbits = bits_of((unsigned long long)(pmax - pmin));
+    // buckets: a quota with more than 2 * SEG_TARGET pods is cut by the leading bits of its pods' timestamps
+    by_buckets = count_segs && ts_ok && tbits + pbits <= 64;
+    if (by_buckets) {
+        int32_t* bf = (int32_t*)(S + o_bfirst); int32_t* bs = (int32_t*)(S + o_bshift); int32_t* bq = (int32_t*)(S + o_bquota);
+        // about SEG_TARGET pods per bucket (small buckets: short sorts, even CTAs); more where that would be too many buckets
+        for (int target = SEG_TARGET; ; target *= 2) {
+            n_buckets = 0;
+            bool fits = true;
+            for (int e = 0; e < E && fits; ++e) {
+                int lg = 0;
+                while (lg < tbits && ((long long)target << lg) < seg_np[e] && seg_np[e] > 2 * target) ++lg;
+                bf[e] = n_buckets; bs[e] = tbits - lg;
+                if (n_buckets + (1 << lg) > SEG_NB_MAX) { fits = false; break; }
+                for (int k = 0; k < (1 << lg); ++k) bq[n_buckets++] = e;
+            }
+            if (fits) { bf[E] = n_buckets; break; }
+            if (target >= SEG_MAX / 2) { by_buckets = false; break; }
+        }
+    }
+    }
+
     cudaEvent_t* ev = nullptr;
     QCU(quota_ctx_events(ctx, &ev));
     QCU(cudaEventRecord(ev[0], st));
@@ -608,14 +926,40 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     q.seg_count = (int32_t*)(A + o_segc); q.seg_off = (int32_t*)(A + o_sego);
     q.chunk_off = (int32_t*)(A + o_choff); q.chunk_sum = (long long*)(A + o_chsum); q.n_chunk_bound = n_chunk_bound;
     if (want_changes) { q.cur_label = A + o_cur; q.chg_packed = (int32_t*)(A + o_packed); q.chg_flag = A + o_flag; }
+    q.b_first = (const int32_t*)(A + o_bfirst); q.b_shift = (const int32_t*)(A + o_bshift); q.b_quota = (const int32_t*)(A + o_bquota);
+    q.seg_sum = (long long*)(A + o_segsum); q.seg_flag = (int32_t*)(A + o_segflag); q.seg_ticket = q.seg_flag + SEG_NB_MAX + 1;
+    q.seg_overflow = (int32_t*)(A + o_ovf);
 
     int n_launch = 0;
+    bool used_buckets = false;                                 // the labelling ran by buckets: seg_overflow must be looked at
     // Used starts from used_init (scalar key set from used_mask)
     // (pods split between ranks: used_init is counted on the first rank only, the others start from zero)
     const bool take_init = !hook || hook->first_rank;
     if (ER && take_init) QCU(cudaMemcpyAsync(q.used, q.used_init, 8 * ER, cudaMemcpyDeviceToDevice, st));
     if (E && take_init) QCU(cudaMemcpyAsync(q.used_mask, q.used_mask_in, 4 * (size_t)E, cudaMemcpyDeviceToDevice, st));
-    if (Pr && E) {
+    // the labelling by buckets (k_label_scatter / k_label_segments) also accounts Used: its grid -- at most SCAT_ITEMS * SCAT_THREADS
+    // pods per CTA, every CTA resident (grid barrier)
+    int scat_grid = 0;
+    const size_t scat_dyn = 12 * ((size_t)n_buckets + 2);
+    if (by_buckets) {
+        int sms = 148, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (cudaFuncSetAttribute(k_label_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, 12 * (SEG_NB_MAX + 2)) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_label_scatter, SCAT_THREADS, scat_dyn) == cudaSuccess && per_sm > 0) {
+            const int need = (Pr + SCAT_ITEMS * SCAT_THREADS - 1) / (SCAT_ITEMS * SCAT_THREADS);
+            const int want = std::max(need, std::min(2 * sms, (Pr + SCAT_THREADS - 1) / SCAT_THREADS));
+            if (need <= sms * per_sm) scat_grid = std::min(want, sms * per_sm);
+        }
+    }
+    if (scat_grid > 0) {
+        q.fuse_ts_min = tmin; q.fuse_prio_min = pmin; q.fuse_tbits = tbits; q.fuse_pbits = pbits; q.n_buckets = n_buckets;
+        int tile = (Pr + scat_grid - 1) / scat_grid;
+        void* args[] = {&q, &tile};
+        QCU(cudaLaunchCooperativeKernel((const void*)k_label_scatter, dim3(scat_grid), dim3(SCAT_THREADS), args, scat_dyn, st));
+        k_label_segments<<<n_buckets, SEG_THREADS, 0, st>>>(q);
+        n_launch += 2;
+        used_buckets = true;
+    } else if (Pr && E) {
         const size_t tab = 8 * ER;
         const int use_smem = tab <= 96 * 1024;
         QCU(cudaFuncSetAttribute(k_quota_used, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
@@ -637,18 +981,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         const int gb = (Pr + 255) / 256;
         cub::DoubleBuffer<unsigned long long> dk(q.key_a, q.key_b); cub::DoubleBuffer<int32_t> dv(q.val_a, q.val_b);
         size_t tb = cub_bytes;
-        int ebits = 1; while ((1ll << ebits) <= E) ++ebits;
-        // ranges of the two inner keys (host scan of the caller's arrays): if quota | timestamp | priority fit one 64-bit word
-        // a single radix sort over exactly the bits in use replaces the three stable passes
-        long long tmin = LLONG_MAX, tmax = LLONG_MIN, pmin = LLONG_MAX, pmax = LLONG_MIN;
-        const bool have_keys = running->creation_ts && running->priority;
-        for (int i = 0; have_keys && i < Pr; ++i) {
-            const long long t = running->creation_ts[i], pr = running->priority[i];
-            tmin = std::min(tmin, t); tmax = std::max(tmax, t); pmin = std::min(pmin, pr); pmax = std::max(pmax, pr);
-        }
-        auto bits_of = [](unsigned long long range) { int b = 1; while (b < 64 && (range >> b)) ++b; return b; };
-        const bool ts_ok = have_keys && (unsigned long long)tmax - (unsigned long long)tmin < (1ull << 62);
-        const int tbits = ts_ok ? bits_of((unsigned long long)(tmax - tmin)) : 64, pbits = bits_of((unsigned long long)(pmax - pmin));
+        if (!used_buckets) {
         if (ts_ok && ebits + tbits + pbits <= 64) {
             q.fuse_ts_min = tmin; q.fuse_prio_min = pmin; q.fuse_tbits = tbits; q.fuse_pbits = pbits;
             k_label_keys<<<gb, 256, 0, st>>>(q, 1);
@@ -669,6 +1002,7 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
         k_label_chunk_prefix<<<(E + 7) / 8, 256, 0, st>>>(q);
         k_label_chunks<<<cgrid, LABEL_CHUNK, 0, st>>>(q, dv.Current(), 1);
         n_launch += 11;
+        }
         if (want_changes) {                                    // sorted positions whose label differs, compacted in order
             size_t sb = cub_bytes;
             QCU(cub::DeviceSelect::Flagged(A + o_cub, sb, (const int32_t*)q.chg_packed, (const uint8_t*)q.chg_flag, (int32_t*)(A + o_sel),
@@ -687,9 +1021,21 @@ extern "C" int nosplan_quota_recompute_impl(int device, cudaStream_t st, nosplan
     span(out->guaranteed, o_guar, 8 * ER); span(out->prefilter, o_pref, (size_t)Pp);
     if (want_label) { span(out->over_quota, o_over, (size_t)Pr); span(out->operator_used, o_opused, 8 * ER); span(out->ambiguous_order, o_amb, 16); }
     if (want_changes) span(lc, o_nsel, 16);
+    if (used_buckets) span(out, o_ovf, 4);
     if (d_hi > d_lo) QCU(cudaMemcpyAsync(S + (d_lo - upload_end), A + d_lo, d_hi - d_lo, cudaMemcpyDeviceToHost, st));
     QCU(cudaEventRecord(ev[3], st));
     QCU(cudaStreamSynchronize(st));
+    if (used_buckets) {
+        int32_t ovf = 0;
+        std::memcpy(&ovf, S + (o_ovf - upload_end), 4);
+        if (ovf) {                                             // a bucket beyond SEG_MAX pods: once more, with the device-wide sort
+            force_global_sort = true;
+            const int rc = nosplan_quota_recompute_impl(device, st, ctx, err, qs, running, pending, out, ms_h2d, ms_k, ms_d2h, launches, h2d_bytes,
+                                                        d2h_bytes, lc, hook);
+            force_global_sort = false;
+            return rc;
+        }
+    }
     auto back = [&](void* dst, size_t at, size_t bytes) { if (dst && bytes) std::memcpy(dst, S + (at - upload_end), bytes); };
     back(out->used, o_used, 8 * ER); back(out->used_mask, o_umask, 4 * (size_t)E);
     back(out->agg_min, o_amin, 8 * (size_t)R); back(out->agg_used, o_aused, 8 * (size_t)R); back(out->agg_overquota, o_aover, 8 * (size_t)R);

@@ -110,6 +110,36 @@ def test_labelling_with_key_ranges_beyond_one_word(eng):
         compare(got, ol.quota(pq, run, pend), f"wide keys seed {seed}")
 
 
+def test_labelling_by_segments_and_by_global_sort_agree(eng):
+    """The labelling sorts inside buckets (counting sort by quota and leading timestamp bits, one CTA per bucket) and falls back
+    to a device-wide radix sort when a bucket overflows (or under NOSPLAN_QUOTA_GLOBAL_SORT): same labels, same status.used
+    either way; including tie groups and one quota holding most of the pods."""
+    import os
+    rng = np.random.default_rng(77)
+    for n_q, n_run, seed, squeeze in ((500, 100_000, 0xC4, False), (60, 30_000, 5, False), (7, 9000, 6, True), (300, 2500, 7, False), (1, 2048, 8, False)):
+        pq, run, pend = synth.quota_state(n_q, n_run, 100, seed=seed)
+        if squeeze:                                       # most pods in one namespace: beyond the segment limit -> global sort
+            run.ns[: n_run * 3 // 4] = run.ns[0]
+        # tie groups; in the squeezed case thousands of pods of one quota share a timestamp, more than one bucket holds:
+        # the bucket path gives up on the device and the call is repeated with the global sort
+        tie = rng.random(n_run) < (0.3 if squeeze else 0.002)
+        run.creation_ts[tie] = run.creation_ts[rng.integers(0, n_run, int(tie.sum())) // 50 * 50]
+        if squeeze:
+            run.creation_ts[: n_run // 3] = run.creation_ts[0]
+        run.priority[rng.random(n_run) < 0.5] = 0
+        exp = ol.quota(pq, run, pend)
+        got, st1 = eng.quota_recompute(pq, run, pend)
+        compare(got, exp, f"segments {n_q} x {n_run}")
+        os.environ["NOSPLAN_QUOTA_GLOBAL_SORT"] = "1"
+        try:
+            got2, st2 = eng.quota_recompute(pq, run, pend)
+        finally:
+            del os.environ["NOSPLAN_QUOTA_GLOBAL_SORT"]
+        compare(got2, exp, f"global sort {n_q} x {n_run}")
+        if not squeeze and n_run / n_q < 1000:
+            assert st1["kernel_launches"] < st2["kernel_launches"]
+
+
 def test_sharded_entry_point_with_one_rank():
     """nosplan_quota_recompute_sharded with a one-rank communicator: the NCCL all-reduce / all-gather + fold of a single rank
     must leave the rows as nosplan_quota_recompute computes them (the two-rank form runs in tests/run_sharded_nccl.py)."""
