@@ -31,6 +31,9 @@
 // SliceTracker.Remove (core/tracker.go:67-88) is one bit per pod POSITION (tracker keys are unique on this path), OR-ed in
 // shared memory and flushed once per CTA; the final lacking vector is rebuilt from the bitmap by the last CTA.
 #include <climits>
+#ifdef NOSPLAN_FUSED_PROFILE
+#include <cstdio>
+#endif
 
 #include "nosplan_dev.cuh"
 
@@ -462,6 +465,12 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
     const int n_nodes = pb.node_hi - pb.node_lo;
     const int n_tiles = (n_nodes + fl.tile_nodes - 1) / fl.tile_nodes;
     bool hdr_ready = false, staged_ready = fl.stage_bytes <= pb.fp_off[FP_L3];
+#ifdef NOSPLAN_FUSED_PROFILE
+    long long tk[8]; tk[0] = clock64();
+#define TICK(k) tk[k] = clock64()
+#else
+#define TICK(k)
+#endif
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int base = pb.node_lo + tile * fl.tile_nodes;
         const int count = min(fl.tile_nodes, pb.node_hi - base);
@@ -474,7 +483,9 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
             hdr_ready = true;
         }
         __syncthreads();
+        TICK(1);
         if (!staged_ready) { mbar_wait(&s_bar[1], 0); staged_ready = true; }
+        TICK(2);
         // ---- phase 2: node nl on lane nl / NW of warp nl % NW -- a small tile spreads over all warps, a few lanes each, so
         //      that a warp's chain is the longest of a few nodes, not of 32
         {
@@ -492,6 +503,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
             }
         }
         __syncthreads();
+        TICK(3);
         // ---- phase 3: the geometry after the update, for nodes that added a pod (planner.go:138)
         for (int g = tid; g < count * 8; g += FT) {
             const int nl = g >> 3, jj = g & 7;
@@ -504,6 +516,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
             pb.out_mask[x] = (uint16_t)((v >> 16) | s_gmask[br]);
         }
         __syncthreads();
+        TICK(4);
     }
     if (!hdr_ready) mbar_wait(&s_bar[0], 0);          // a CTA without tiles still has to see its copies land before it exits
     if (!staged_ready) mbar_wait(&s_bar[1], 0);
@@ -563,6 +576,12 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
         const unsigned b = s_bits[w];
         if (b) atomicOr(&pb.placed[w], b);
     }
+#ifdef NOSPLAN_FUSED_PROFILE
+    TICK(5);
+    if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x / 2 || blockIdx.x == gridDim.x - 1))
+        printf("[fused profile] cta %d: phase1 %lld  wait-stage %lld  phase2 %lld  phase3 %lld  epilogue %lld cycles\n", blockIdx.x,
+               tk[1] - tk[0], tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4]);
+#endif
 }
 
 __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch fl) {
@@ -632,18 +651,31 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
         unsigned* s_or = reinterpret_cast<unsigned*>(s_dyn);                                                              // this CTA's placed bits: flushed long ago
         bool ok = true;
         for (int i = tid; i < D; i += FT) {
-            unsigned acc_or = 0;
-            for (int r = 0; r < W; ++r) {
-                const volatile uint2* src = reinterpret_cast<const volatile uint2*>(me + box_ll(par, r, pb.xf_box.xb_max)) + i;
-                unsigned vx, vy, spins = 0;
-                for (;;) {
-                    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(vx), "=r"(vy) : "l"(src) : "memory");
-                    if (vy == epoch) break;
-                    if (++spins > (1u << 22)) { ok = false; vx = 0; break; }
+            // the W words of this index, one per rank: all loads in flight together, only the late ones are asked for again
+            unsigned vx[PEER_MAX], pending = (1u << W) - 1u, spins = 0;
+            while (pending) {
+                unsigned vy[PEER_MAX];
+#pragma unroll
+                for (int r = 0; r < PEER_MAX; ++r)
+                    if (pending >> r & 1) {
+                        const volatile uint2* src = reinterpret_cast<const volatile uint2*>(me + box_ll(par, r, pb.xf_box.xb_max)) + i;
+                        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(vx[r]), "=r"(vy[r]) : "l"(src) : "memory");
+                    }
+#pragma unroll
+                for (int r = 0; r < PEER_MAX; ++r)
+                    if ((pending >> r & 1) && vy[r] == epoch) pending &= ~(1u << r);
+                if (pending) {
+                    if (++spins > (1u << 22)) { ok = false; break; }
                     if (spins > 64) __nanosleep(200);
                 }
-                if (i < FUSED_LL_HDR) s_hdr[r * FUSED_LL_HDR + i] = vx; else acc_or |= vx;
             }
+            unsigned acc_or = 0;
+#pragma unroll
+            for (int r = 0; r < PEER_MAX; ++r)
+                if (r < W) {
+                    const unsigned v = (pending >> r & 1) ? 0u : vx[r];
+                    if (i < FUSED_LL_HDR) s_hdr[r * FUSED_LL_HDR + i] = v; else acc_or |= v;
+                }
             if (i >= FUSED_LL_HDR) s_or[i - FUSED_LL_HDR] = acc_or;
         }
         if (!__syncthreads_and(ok)) {
