@@ -681,7 +681,9 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     h->out_count_bytes = 16 * NG; h->out_mask_bytes = 2 * NG;
     // Node-side conditions of the single-launch plan (fused.cu); the pod-side ones follow below.  Where it can still apply,
     // k_prepass is not queued early: the fused kernel does that work itself once the pods are on the device.
-    bool fused_ok = mig && G <= 8 && P > 0 && !getenv("NOSPLAN_NO_FUSED");
+    // (MPS as well: slicing.GPU.UpdateGeometryFor per GPU lane; NOSPLAN_NO_FUSED_MPS keeps MPS on the classic kernels)
+    bool fused_ok = (mig || !getenv("NOSPLAN_NO_FUSED_MPS")) && G <= 8 && P > 0 && !getenv("NOSPLAN_NO_FUSED");
+    for (int p = 0; p < K && fused_ok && !mig; ++p) if (s->profile_mem_gb[p] <= 0) fused_ok = false;
     for (int r = 0; r < n_rows && fused_ok; ++r)
         for (int p = 0; p < 16; ++p) if (s->geom_counts[16 * (size_t)r + p] > 31) { fused_ok = false; break; }
     if (h->in_plan && !fused_ok) { rc = run_pre(h, true); if (rc != NOSPLAN_OK) return rc; }

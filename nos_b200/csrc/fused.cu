@@ -87,19 +87,32 @@ __device__ __forceinline__ unsigned byte_at(unsigned lo, unsigned hi, int p) {  
     return ((p < 4 ? lo : hi) >> ((p & 3) * 8)) & 0xffu;
 }
 
+__device__ __forceinline__ unsigned get_byte(const uint4& v, int p) {
+    const unsigned w = p < 8 ? (p < 4 ? v.x : v.y) : (p < 12 ? v.z : v.w);
+    return (w >> ((p & 3) * 8)) & 0xffu;
+}
+__device__ __forceinline__ void add_byte(uint4& v, int p, unsigned d) {     // no carry: the caller checks the counts afterwards
+    const unsigned b = d << ((p & 3) * 8);
+    if (p < 4) v.x += b; else if (p < 8) v.y += b; else if (p < 12) v.z += b; else v.w += b;
+}
+__device__ __forceinline__ unsigned byte_spread(unsigned nibble) {           // bit b of the nibble -> 0xff in byte b
+    return ((nibble & 1u) * 0xffu) | ((nibble >> 1 & 1u) * 0xff00u) | ((nibble >> 2 & 1u) * 0xff0000u) | ((nibble >> 3 & 1u) * 0xff000000u);
+}
+
 struct Acc {                                          // what a thread accumulates over all its tiles
     long long D0 = 0, D1 = 0;                         // sum(alloc - requested) of slice columns j and j + 8
     uint4 mf = make_uint4(0, 0, 0, 0);                // byte-wise max of the free counts seen
     unsigned flags = 0;
     long long place = 0, evals = 0;
     int visited = 0;
+    int maxmem = 0;                                   // MPS: largest GPU memory seen (bounds the devices one GPU can hold)
 };
 
 // ---- phase 1 for one node: lane j of the 8-lane group = GPU j.  Executed by whole warps (converged).
 template <bool WIDE>
 __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool node_on, int j, int gsh, const uint4* s_geom,
                                             const uint16_t* s_gmask, const int* s_off, const unsigned (&Lw)[4], int n_req,
-                                            NodeS* ns, unsigned* gs, Acc& a, unsigned long long* hdr_bar) {
+                                            NodeS* ns, unsigned* gs, uint4* gfree, Acc& a, unsigned long long* hdr_bar) {
     const int G = pb.G, K = pb.K, R = pb.R;
     const bool fit = pb.filter_mode == NOSPLAN_FILTER_RESOURCES_FIT;
     int ng = 0;
@@ -123,13 +136,14 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
             const int x = i * G + j;
             used = pb.gpu_used[x]; fre = pb.gpu_free[x];
             um = pb.gpu_umask[x]; fm = pb.gpu_fmask[x];
-            model = pb.gpu_model[x];
+            model = pb.gpu_model[x];                   // MPS: the same array holds the GPU's memory in GB (gpu_mem aliases it)
         }
         ng = min(max(ng_raw, 0), G);
-        if (j >= ng) { used = make_uint4(0, 0, 0, 0); fre = used; um = fm = 0; }
-        model = min(max(model, 0), max(pb.n_models - 1, 0));
+        if (j >= ng) { used = make_uint4(0, 0, 0, 0); fre = used; um = fm = 0; model = 0; }
+        if (pb.kind == NOSPLAN_KIND_MIG) model = min(max(model, 0), max(pb.n_models - 1, 0));
     }
     const bool has = j < ng;
+    const bool mps = pb.kind != NOSPLAN_KIND_MIG;
     // ---- k_prepass duties: totals, largest free count, node accounts against the GPU maps
     a.D0 += a0 - r0; a.D1 += a1 - r1;
     if (((used.x | used.y | fre.x | fre.y | (WIDE ? (used.z | used.w | fre.z | fre.w) : 0u)) & 0xe0e0e0e0u) != 0) a.flags |= FREJ_COUNTS;
@@ -164,7 +178,45 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
     unsigned best = 0;
     bool allowed = false;
     int nrows = 0, row0 = 0;
-    if (has && pb.n_models > 0) { row0 = s_off[model]; nrows = s_off[model + 1] - row0; }
+    if (has && !mps && pb.n_models > 0) { row0 = s_off[model]; nrows = s_off[model + 1] - row0; }
+    // ---- MPS: slicing.GPU.UpdateGeometryFor (pkg/gpu/slicing/gpu.go:162-232), thread-serial over the profiles of this lane's GPU.
+    //      Under the hypothesis every requested profile is missing by more than a GPU can hold, so `min(missing, spare / size)`
+    //      is `spare / size`; the rest is mps_gpu_update of sweep.cu line by line: spare capacity first, then ALL originally-free
+    //      keys are deleted (also what was just created on one of them), the profile is created again in what that freed, and
+    //      the deleted keys are restored all-or-nothing per profile in id order.
+    unsigned fm_new = fm;
+    bool mps_upd = false, mps_free = false;
+    if (mps && has) {
+        const int mem = model;
+        a.maxmem = max(a.maxmem, mem);
+        auto mem_used = [&](const uint4& f) {
+            int t = 0;
+            for (int p = 0; p < K; ++p) t += pb.pmem[p] * (int)(get_byte(used, p) + get_byte(f, p));
+            return t;
+        };
+        mps_free = fm != 0 || (mem - mem_used(fre) >= 1);               // HasFreeCapacity (slicing/gpu.go:131-141)
+        const uint4 ofree = fre;
+        const unsigned omask = fm & ((1u << K) - 1u);
+        const uint4 keep = make_uint4(~byte_spread(omask & 15u), ~byte_spread(omask >> 4 & 15u), ~byte_spread(omask >> 8 & 15u), ~byte_spread(omask >> 12 & 15u));
+        for (unsigned m = pb.fp_rset; m; m &= m - 1) {
+            const int mp = __ffs(m) - 1, msize = pb.pmem[mp];
+            int spare = mem - mem_used(fre);
+            if (spare >= 1) { const int c = spare / msize; if (c > 0) { add_byte(fre, mp, (unsigned)c); fm_new |= 1u << mp; mps_upd = true; } }
+            fre.x &= keep.x; fre.y &= keep.y; fre.z &= keep.z; fre.w &= keep.w;
+            fm_new &= ~omask;
+            spare = mem - mem_used(fre);
+            if (spare >= 1) { const int c = spare / msize; if (c > 0) { add_byte(fre, mp, (unsigned)c); fm_new |= 1u << mp; mps_upd = true; spare -= c * msize; } }
+            for (unsigned rest = omask; rest; rest &= rest - 1) {
+                const int k = __ffs(rest) - 1;
+                const int of = (int)get_byte(ofree, k), need = pb.pmem[k] * of;
+                if (spare >= need) { add_byte(fre, k, (unsigned)of); fm_new |= 1u << k; spare -= need; }
+            }
+            // a count beyond 31 would carry in the byte-wise sums below (and beyond 255 has already wrapped): not for this kernel
+            if (((fre.x | fre.y | fre.z | fre.w) & 0xe0e0e0e0u) != 0 || spare < -(1 << 24)) a.flags |= FREJ_COUNTS;
+        }
+    }
+    uint4 fre_mps = fre;                              // MPS: the GPU after the update (kept only for a candidate node, below)
+    if (mps) fre = make_uint4(cnt0.x - used.x, cnt0.y - used.y, cnt0.z - used.z, cnt0.w - used.w);
     for (int r = 0; r < nrows; ++r) {
         const uint4 row = s_geom[row0 + r];
         const unsigned tx = (row.x | HI) - used.x, ty = (row.y | HI) - used.y;   // bit 7 of a byte: row >= used
@@ -184,7 +236,7 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
             allowed |= same && s_gmask[row0 + r] == gm0;
         }
     }
-    const bool has_free = has && (fm != 0 || !allowed);
+    const bool has_free = has && (mps ? mps_free : (fm != 0 || !allowed));
     const bool candidate = (__ballot_sync(FULL, has_free) >> gsh & 0xffu) != 0;
     int br = 0xffff;
     if (candidate && best) {
@@ -192,7 +244,14 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
         const uint4 row = s_geom[br];
         fre = make_uint4(row.x - used.x, row.y - used.y, WIDE ? row.z - used.z : 0u, WIDE ? row.w - used.w : 0u);   // zero kept (:141)
     }
-    const bool upd = (__ballot_sync(FULL, br != 0xffff) >> gsh & 0xffu) != 0;
+    bool upd_g = br != 0xffff;
+    if (mps && candidate && has) {
+        const bool changed = fre_mps.x != fre.x || fre_mps.y != fre.y || fre_mps.z != fre.z || fre_mps.w != fre.w || fm_new != fm;
+        fre = fre_mps; fm = fm_new;
+        upd_g = mps_upd;
+        if (changed) br = 0xfffe;                     // phase 3 takes the row from the per-GPU copy of `fre`, not from a table row
+    }
+    const bool upd = (__ballot_sync(FULL, upd_g) >> gsh & 0xffu) != 0;
     // free devices per profile on the node after the update
     unsigned cx = has ? fre.x : 0u, cy = has ? fre.y : 0u, cz = (WIDE && has) ? fre.z : 0u, cw = (WIDE && has) ? fre.w : 0u;
 #pragma unroll
@@ -200,7 +259,7 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
         cx += __shfl_xor_sync(FULL, cx, o); cy += __shfl_xor_sync(FULL, cy, o);
         if (WIDE) { cz += __shfl_xor_sync(FULL, cz, o); cw += __shfl_xor_sync(FULL, cw, o); }
     }
-    if (candidate && has) a.evals += (long long)nrows * n_req;
+    if (candidate && has) a.evals += mps ? (long long)n_req : (long long)nrows * n_req;
     if (node_on) {
         // partitioningState[n] as it was (planner.go:72); phase 3 overwrites the rows of nodes that add a pod after an update
         if (has) {
@@ -208,7 +267,8 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
             pb.out_count[x] = cnt0;
             pb.out_mask[x] = (uint16_t)gm0;
         }
-        *gs = (unsigned)br | (um << 16);
+        *gs = (unsigned)br | ((mps ? (um | fm) : um) << 16);
+        if (mps) *gfree = fre;
         if (j == 0) {
             NodeS s;
             s.remc = s.remm = F_REM_MAX;
@@ -401,7 +461,10 @@ __device__ __forceinline__ void fused_verify(const DevProblem& pb, const FRun* r
             const bool requested = (pb.fp_rset >> lane & 1u) != 0;
             ok = requested == (l0 > 0);
             if (requested) {                                          // saturation at the start and at the end (fast_applicable of sweep.cu)
-                const long long m = max(pb.sat_m[lane], *reinterpret_cast<const volatile int*>(&maxfree[lane]));
+                int sat = pb.sat_m[lane];
+                if (pb.kind != NOSPLAN_KIND_MIG)        // devices of this size the largest GPU can hold (fast_applicable of sweep.cu)
+                    sat = pb.pmem[lane] > 0 ? *reinterpret_cast<const volatile int*>(&pb.gflags[1]) / pb.pmem[lane] : (1 << 30);
+                const long long m = max(sat, *reinterpret_cast<const volatile int*>(&maxfree[lane]));
                 ok = ok && le > 0 && le > (long long)(pb.G + 2) * m && l0 < (1ll << 30);
             }
         }
@@ -438,6 +501,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
     const unsigned char* s_blob = s_dyn + o_blob;
     NodeS* s_node = reinterpret_cast<NodeS*>(s_dyn + o_blob + (size_t)fl.stage_bytes);
     unsigned* s_gpu = reinterpret_cast<unsigned*>(s_node + fl.tile_nodes);
+    uint4* s_gfree = reinterpret_cast<uint4*>(s_gpu + 8 * fl.tile_nodes);        // MPS only: every GPU's free counts after the update
     const uint4* s_geom = reinterpret_cast<const uint4*>(s_blob);
     const uint16_t* s_gmask = reinterpret_cast<const uint16_t*>(s_blob + pb.fp_off[0]);
     const int* s_off = reinterpret_cast<const int*>(s_blob + pb.fp_off[1]);
@@ -478,8 +542,8 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
         for (int g0 = 0; g0 < count * 8; g0 += FT) {
             const int g = g0 + tid, nl = g >> 3;
             const bool on = nl < count;
-            node_phase1<WIDE>(pb, base + nl, on, j, gsh, s_geom, s_gmask, s_off, Lw, n_req, &s_node[on ? nl : 0], &s_gpu[on ? g : 0], a,
-                              hdr_ready ? nullptr : &s_bar[0]);
+            node_phase1<WIDE>(pb, base + nl, on, j, gsh, s_geom, s_gmask, s_off, Lw, n_req, &s_node[on ? nl : 0], &s_gpu[on ? g : 0],
+                              &s_gfree[on ? g : 0], a, hdr_ready ? nullptr : &s_bar[0]);
             hdr_ready = true;
         }
         __syncthreads();
@@ -512,6 +576,12 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
             const int br = (int)(v & 0xffffu);
             if (br == 0xffff) continue;
             const int x = (base + nl) * pb.G + jj;
+            if (br == 0xfffe) {                       // MPS: used + free after the update, the keys of both maps
+                const uint4 u = pb.gpu_used[x], f = s_gfree[g];
+                pb.out_count[x] = make_uint4(u.x + f.x, u.y + f.y, u.z + f.z, u.w + f.w);
+                pb.out_mask[x] = (uint16_t)(v >> 16);
+                continue;
+            }
             pb.out_count[x] = s_geom[br];
             pb.out_mask[x] = (uint16_t)((v >> 16) | s_gmask[br]);
         }
@@ -523,6 +593,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
 
     // ---- reduction of what the threads accumulated: one shared-memory slot per warp
     if (__any_sync(FULL, a.flags != 0)) { const unsigned f = __reduce_or_sync(FULL, a.flags); if (lane == 0) atomicOr(&s_flags[0], (int)f); }
+    if (pb.kind != NOSPLAN_KIND_MIG) { const int mm = __reduce_max_sync(FULL, a.maxmem); if (lane == 0 && mm > 0) atomicMax(&pb.gflags[1], mm); }
 #pragma unroll
     for (int o = 8; o < 32; o <<= 1) {                 // lanes with the same j across the warp's four groups
         a.D0 += __shfl_xor_sync(FULL, a.D0, o); a.D1 += __shfl_xor_sync(FULL, a.D1, o);
@@ -782,11 +853,12 @@ cudaError_t fused_prepare_device() {
 cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st) {
     const int n_nodes = pb.node_hi - pb.node_lo;
     const size_t bits = (((size_t)(pb.fp_pad_pods >> 5) * 4) + 15) & ~(size_t)15;
-    auto need = [&](int stage_bytes, int tile_nodes) { return bits + (size_t)stage_bytes + (size_t)tile_nodes * (sizeof(NodeS) + 32); };
-    // one resident wave when the nodes allow it: the smallest tile (multiple of 8, at least 64 nodes) that covers them
+    const size_t per_node = sizeof(NodeS) + 32 + (pb.kind != NOSPLAN_KIND_MIG ? 128 : 0);      // MPS keeps every GPU's free counts for phase 3
+    auto need = [&](int stage_bytes, int tile_nodes) { return bits + (size_t)stage_bytes + (size_t)tile_nodes * per_node; };
+    // one resident wave when the nodes allow it: the smallest tile (at least 64 nodes) that covers them with one CTA per SM
+    // (10 000 nodes on 148 SMs: 68 nodes per CTA, 148 CTAs)
     FusedLaunch fl;
     int tile = (n_nodes + sms - 1) / sms;
-    tile = (tile + 7) & ~7;
     if (tile < 64) tile = 64;
     if (tile > FT) tile = FT;
     fl.tile_nodes = tile;

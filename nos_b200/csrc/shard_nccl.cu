@@ -232,7 +232,7 @@ extern "C" int nosplan_run_sliced(nosplan_t* h) {
     nosplan_shard_ctx* c = h->sctx;
     if (!c) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sliced before nosplan_shard_init");
     if (!h->uploaded) return nosplan_fail(h, NOSPLAN_E_INVALID, "nosplan_run_sliced before nosplan_upload");
-    if (!h->fused_ok) return run_sliced_classic(h);
+    if (!h->fused_ok || h->pb.kind != NOSPLAN_KIND_MIG) return run_sliced_classic(h);      // the one-kernel exchange carries no GPU-memory maximum (MPS)
     SCU(h, cudaSetDevice(h->device));
     const int W = c->world;
     const size_t xb = nsp::fused_exchange_bytes(h->pb);

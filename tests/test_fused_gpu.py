@@ -125,7 +125,8 @@ def test_not_eligible_goes_straight_to_the_classic_sequence(eng):
     _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "duplicate keys")
     assert st["fused"] == 0 and st["fused_reject"] == 0
     s, p = synth.mps_cluster(100, 8, 600, seed=12)
-    _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "mps")
+    p.scalar_qty[:] = 2                                               # two devices per pod: the first-fit GPU choice shows in the plan
+    _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "mps, quantity 2")
     assert st["fused"] == 0 and st["fused_reject"] == 0
     s, p = synth.mig_cluster(100, 8, 600, seed=12)
     p.base[3, 2] = 1 << 20                                            # an ephemeral-storage request
@@ -211,3 +212,39 @@ def test_fused_north_star_size(eng):
     s, p = synth.mig_cluster(10000, 8, 10000, seed=0xC5)
     _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "10k x 10k")
     assert st["fused"] == 1 and st["kernel_launches"] == 1
+
+
+@pytest.mark.parametrize("fm", [pk.FILTER_NONE, pk.FILTER_REJECT_ALL, pk.FILTER_RESOURCES_FIT], ids=["none", "reject", "fit"])
+@pytest.mark.parametrize("shape", [(1, 1, 200), (16, 8, 700), (17, 3, 900), (200, 8, 1000), (1000, 8, 5000), (5000, 8, 20000)])
+def test_fused_mps(eng, shape, fm):
+    """MPS: slicing.GPU.UpdateGeometryFor (pkg/gpu/slicing/gpu.go:162-232) per GPU lane inside the single-launch kernel --
+    spare capacity, the delete-all-free-keys quirk, all-or-nothing restore -- against the oracle and the classic kernels."""
+    s, p = synth.mps_cluster(*shape, seed=0x30 + shape[0])
+    cnt, msk, st = check(eng, s, p, None, fm, f"mps {shape}")
+    assert st["fused"] == 1 and st["kernel_launches"] == 1, st
+    ccnt, cmsk, cst = classic(eng, s, p, None, fm)
+    assert cst["fused"] == 0 and np.array_equal(cnt, ccnt) and np.array_equal(msk, cmsk)
+    for k in COUNTERS:
+        assert st[k] == cst[k]
+
+
+def test_fused_mps_odd_shapes(eng):
+    """GPUs of different sizes, free slices of several sizes in place, a PreFilter vector, tight nodes, satisfiable demand."""
+    rng = np.random.default_rng(3)
+    for seed in range(6):
+        n = int(rng.integers(30, 400))
+        s, p = synth.mps_cluster(n, int(rng.integers(1, 9)), int(rng.integers(200, 4000)), seed=0x60 + seed,
+                                 gpu_memory_mb=int(rng.choice([24576, 40960, 81920])))
+        s.gpu_memory_gb[rng.random(s.gpu_memory_gb.shape) < 0.3] = 48
+        pre = (rng.random(p.n_pods) < 0.7).astype(np.uint8)
+        s.node_requested[:, 0] = rng.integers(0, 64001, s.n_nodes)
+        for fm in (pk.FILTER_NONE, pk.FILTER_RESOURCES_FIT):
+            check(eng, s, p, pre, fm, f"mps odd {seed} fm {fm}")
+    s, p = synth.mps_cluster(300, 8, 1500, seed=5, regime="satisfiable")
+    _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "mps satisfiable")
+    s, p = synth.mps_cluster(300, 8, 1500, seed=5)
+    p2 = synth.mps_cluster(300, 8, 900, seed=6)[1]
+    check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "mps, then resident")
+    rcnt, rmsk, rst = eng.plan_resident(p2, None, pk.FILTER_RESOURCES_FIT)
+    o = ol.plan(s, p2, None, pk.FILTER_RESOURCES_FIT, ol.INCREMENTAL)
+    assert np.array_equal(rcnt, o[0]) and np.array_equal(rmsk, o[1]) and rst["placements"] == o[2]["placements"]
