@@ -31,6 +31,7 @@
 // SliceTracker.Remove (core/tracker.go:67-88) is one bit per pod POSITION (tracker keys are unique on this path), OR-ed in
 // shared memory and flushed once per CTA; the final lacking vector is rebuilt from the bitmap by the last CTA.
 #include <climits>
+#include <cstdlib>
 #ifdef NOSPLAN_FUSED_PROFILE
 #include <cstdio>
 #endif
@@ -855,10 +856,10 @@ cudaError_t launch_fused(const DevProblem& pb, int sms, cudaStream_t st) {
     const size_t bits = (((size_t)(pb.fp_pad_pods >> 5) * 4) + 15) & ~(size_t)15;
     const size_t per_node = sizeof(NodeS) + 32 + (pb.kind != NOSPLAN_KIND_MIG ? 128 : 0);      // MPS keeps every GPU's free counts for phase 3
     auto need = [&](int stage_bytes, int tile_nodes) { return bits + (size_t)stage_bytes + (size_t)tile_nodes * per_node; };
-    // one resident wave when the nodes allow it: the smallest tile (at least 64 nodes) that covers them with one CTA per SM
-    // (10 000 nodes on 148 SMs: 68 nodes per CTA, 148 CTAs)
+    // one resident wave when the nodes allow it: the smallest tile (multiple of 8, at least 64 nodes) that covers them
     FusedLaunch fl;
     int tile = (n_nodes + sms - 1) / sms;
+    tile = (tile + 7) & ~7;                    // 72 nodes, 139 CTAs at 10 000 nodes: measured no slower than 68 nodes on all 148 SMs
     if (tile < 64) tile = 64;
     if (tile > FT) tile = FT;
     fl.tile_nodes = tile;
