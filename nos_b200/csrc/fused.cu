@@ -110,7 +110,7 @@ struct Acc {                                          // what a thread accumulat
 };
 
 // ---- phase 1 for one node: lane j of the 8-lane group = GPU j.  Executed by whole warps (converged).
-template <bool WIDE>
+template <bool WIDE, bool MPS>
 __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool node_on, int j, int gsh, const uint4* s_geom,
                                             const uint16_t* s_gmask, const int* s_off, const unsigned (&Lw)[4], int n_req,
                                             NodeS* ns, unsigned* gs, uint4* gfree, Acc& a, unsigned long long* hdr_bar) {
@@ -141,10 +141,10 @@ __device__ __forceinline__ void node_phase1(const DevProblem& pb, int i, bool no
         }
         ng = min(max(ng_raw, 0), G);
         if (j >= ng) { used = make_uint4(0, 0, 0, 0); fre = used; um = fm = 0; model = 0; }
-        if (pb.kind == NOSPLAN_KIND_MIG) model = min(max(model, 0), max(pb.n_models - 1, 0));
+        if (!MPS) model = min(max(model, 0), max(pb.n_models - 1, 0));
     }
     const bool has = j < ng;
-    const bool mps = pb.kind != NOSPLAN_KIND_MIG;
+    constexpr bool mps = MPS;                         // compile-time: the MIG instantiation carries none of the MPS code
     // ---- k_prepass duties: totals, largest free count, node accounts against the GPU maps
     a.D0 += a0 - r0; a.D1 += a1 - r1;
     if (((used.x | used.y | fre.x | fre.y | (WIDE ? (used.z | used.w | fre.z | fre.w) : 0u)) & 0xe0e0e0e0u) != 0) a.flags |= FREJ_COUNTS;
@@ -491,7 +491,7 @@ __device__ __forceinline__ void fused_verify(const DevProblem& pb, const FRun* r
 
 struct FusedLaunch { int tile_nodes, stage_bytes; };
 
-template <bool WIDE>
+template <bool WIDE, bool MPS>
 __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaunch fl, unsigned char* s_dyn, unsigned long long (*s_wD)[KP],
                                            unsigned (*s_wmf)[4], unsigned long long (*s_wcnt)[4], int* s_flags, int* s_pref, unsigned long long* s_bar) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, j = lane & 7, gsh = (lane >> 3) * 8;
@@ -543,7 +543,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
         for (int g0 = 0; g0 < count * 8; g0 += FT) {
             const int g = g0 + tid, nl = g >> 3;
             const bool on = nl < count;
-            node_phase1<WIDE>(pb, base + nl, on, j, gsh, s_geom, s_gmask, s_off, Lw, n_req, &s_node[on ? nl : 0], &s_gpu[on ? g : 0],
+            node_phase1<WIDE, MPS>(pb, base + nl, on, j, gsh, s_geom, s_gmask, s_off, Lw, n_req, &s_node[on ? nl : 0], &s_gpu[on ? g : 0],
                               &s_gfree[on ? g : 0], a, hdr_ready ? nullptr : &s_bar[0]);
             hdr_ready = true;
         }
@@ -577,7 +577,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
             const int br = (int)(v & 0xffffu);
             if (br == 0xffff) continue;
             const int x = (base + nl) * pb.G + jj;
-            if (br == 0xfffe) {                       // MPS: used + free after the update, the keys of both maps
+            if (MPS && br == 0xfffe) {                // MPS: used + free after the update, the keys of both maps
                 const uint4 u = pb.gpu_used[x], f = s_gfree[g];
                 pb.out_count[x] = make_uint4(u.x + f.x, u.y + f.y, u.z + f.z, u.w + f.w);
                 pb.out_mask[x] = (uint16_t)(v >> 16);
@@ -594,7 +594,7 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
 
     // ---- reduction of what the threads accumulated: one shared-memory slot per warp
     if (__any_sync(FULL, a.flags != 0)) { const unsigned f = __reduce_or_sync(FULL, a.flags); if (lane == 0) atomicOr(&s_flags[0], (int)f); }
-    if (pb.kind != NOSPLAN_KIND_MIG) { const int mm = __reduce_max_sync(FULL, a.maxmem); if (lane == 0 && mm > 0) atomicMax(&pb.gflags[1], mm); }
+    if (MPS) { const int mm = __reduce_max_sync(FULL, a.maxmem); if (lane == 0 && mm > 0) atomicMax(&pb.gflags[1], mm); }
 #pragma unroll
     for (int o = 8; o < 32; o <<= 1) {                 // lanes with the same j across the warp's four groups
         a.D0 += __shfl_xor_sync(FULL, a.D0, o); a.D1 += __shfl_xor_sync(FULL, a.D1, o);
@@ -690,8 +690,13 @@ __global__ void __launch_bounds__(FT, 1) k_plan_fused(DevProblem pb, FusedLaunch
     if (blockIdx.x == 0) for (int x = tid; x < pb.zero_next_n8; x += FT) pb.zero_next[x] = 0;
     __syncthreads();
 
-    if (pb.K > 8) fused_body<true>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
-    else fused_body<false>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
+    if (pb.kind == NOSPLAN_KIND_MIG) {
+        if (pb.K > 8) fused_body<true, false>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
+        else fused_body<false, false>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
+    } else {
+        if (pb.K > 8) fused_body<true, true>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
+        else fused_body<false, true>(pb, fl, s_dyn, s_wD, s_wmf, s_wcnt, s_flags, s_pref, s_bar);
+    }
 
     // ---- the CTA that finishes last either verifies the hypothesis on the final state (single GPU: what k_plan_sweep does for
     //      the classic path) or, in slice mode, ships this rank's part of that state to every rank in ONE block
