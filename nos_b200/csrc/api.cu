@@ -770,6 +770,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
             or_cpu |= (unsigned long long)bc; or_mem |= (unsigned long long)bm;
             max_cpu = std::max(max_cpu, bc); max_mem = std::max(max_mem, bm);
         }
+        lap("pods: pass A");
         // profiles present: the comparator must be a strict weak order on them, and no two of them may share a rank
         const int32_t* pmem = s->profile_mem_gb; const int32_t* pgi = s->profile_gi;
         auto smaller = [=](int x, int y) { if (pmem[x] < pmem[y]) return true; return mig && pgi[x] < pgi[y]; };
@@ -837,7 +838,9 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         if (L.total > bound) return false;
         h->lay = L;
         unsigned char* B = S + L.fp_blob;
+        lap("pods: runs");
         blob_begin(B, fp_off, s, n_rows, n_models);
+        lap("pods: begin");
         int32_t* fpod = (int32_t*)(B + fp_off[FP_PODS]);
         int cur[FRUN_MAX];
         for (int r = 0; r < nr; ++r) cur[r] = fr[r].pos0;
@@ -847,7 +850,9 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
             fpod[2 * (size_t)x] = (int32_t)(pods->base[3 * (size_t)i] >> cs);
             fpod[2 * (size_t)x + 1] = (int32_t)(pods->base[3 * (size_t)i + 1] >> ms);
         }
+        lap("pods: pass B");
         blob_finish(B, fp_off, fr, nr);
+        lap("pods: finish");
         lazy = true; up_from = L.fp_blob;
         h->classic_staged = false;
         h->lazy_valid = true; h->lazy_pods = *pods; h->lazy_pre = prefilter_ok; h->lazy_filter = filter_mode;
