@@ -16,6 +16,8 @@
 //   phase 1  8 lanes per node, lane = GPU (all lanes of a warp converged, 8-lane shuffles):
 //            mig.GPU.UpdateGeometryFor (pkg/gpu/mig/gpu.go:158-212) -- each lane walks the allowed geometries of ITS GPU: SWAR
 //            "row >= used" on 4 profiles per word, score = dp4a(row - used, lacking mask), strict > in table order;
+//            for an MPS snapshot (template parameter) slicing.GPU.UpdateGeometryFor (pkg/gpu/slicing/gpu.go:162-232) instead,
+//            thread-serial over the profiles of the lane's GPU;
 //            k_prepass's duties (HasFreeCapacity, totals, largest free count, accounts against GPU maps); the node's free
 //            devices per profile after the update (byte-wise sum over its GPUs) go to shared memory for phase 2
 //   phase 2  ONE THREAD PER NODE: tryAddPod over all pods (planner.go:116-141) with NodeResourcesFit.  The pods are
@@ -31,7 +33,6 @@
 // SliceTracker.Remove (core/tracker.go:67-88) is one bit per pod POSITION (tracker keys are unique on this path), OR-ed in
 // shared memory and flushed once per CTA; the final lacking vector is rebuilt from the bitmap by the last CTA.
 #include <climits>
-#include <cstdlib>
 #ifdef NOSPLAN_FUSED_PROFILE
 #include <cstdio>
 #endif
