@@ -723,6 +723,15 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     //      B writes each pod's (cpu, memory) pair straight to its position of the padded space.  Anything this does not cover
     //      -- an invalid pod, several scalar entries, quantities above one, shared tracker keys, priority levels that mix
     //      slice-less and sliced pods -- leaves it to the general path below, which also reports the errors.
+    // The single-launch kernel's hypothesis needs lack[p] > (G+2)*M_p for every requested profile, and lack[p] can never exceed
+    // the devices of p all pods ask for together: a pod list too short for that is not worth the attempt (MIG: M_p from the
+    // geometry tables; MPS: unknown here, the GPU memory sizes are not looked at on the host)
+    auto can_saturate = [&](int prof, long long asked) {
+        if (!mig) return true;
+        int m = 0;
+        for (int r = 0; r < n_rows; ++r) m = std::max(m, (int)s->geom_counts[16 * (size_t)r + prof]);
+        return asked > (long long)(G + 2) * m;
+    };
     bool fast_done = false;
     if (fused_ok && h->in_plan && P > 0 && !getenv("NOSPLAN_NO_FAST_PODS")) fast_done = [&]() -> bool {
         constexpr int LV_MAX = 64, NB = KP + 1;
@@ -800,6 +809,12 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         }
         int prof_by_rank[KP], n_present = 0;
         for (int r = 0; r < KP; ++r) for (int x = 0; x < K; ++x) if (present[x] && rank_of[x] == r) prof_by_rank[n_present++] = x;
+        for (int x = 0; x < K; ++x) {
+            if (!present[x]) continue;
+            long long asked = 0;
+            for (const Level& l : levels) asked += l.cnt[x + 1];
+            if (!can_saturate(x, asked)) return false;                   // the general path stages the pods for the classic kernels
+        }
         // runs = non-empty buckets, priority descending, then profile rank
         int lv_order[LV_MAX];
         const int n_lv = (int)levels.size();
@@ -971,6 +986,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         //      entry per pod, only cpu / memory / slice requests, and requests that fit the compact int32 units
         fused_ok = fused_ok && single_profile_classes && n_runs <= FRUN_MAX && keys_unique && any_eph == 0 && !any_zero &&
                    !(any_other && filter_mode == NOSPLAN_FILTER_RESOURCES_FIT) && max_q <= 1;
+        for (int x = 0; x < K && fused_ok; ++x) if (sum_q[x] > 0 && !can_saturate(x, sum_q[x])) fused_ok = false;
         if (fused_ok) {
             cpu_shift = or_cpu ? __builtin_ctzll(or_cpu) : 0; mem_shift = or_mem ? __builtin_ctzll(or_mem) : 0;
             fused_ok = (max_cpu >> cpu_shift) < F_COST_LIMIT && (max_mem >> mem_shift) < F_COST_LIMIT;

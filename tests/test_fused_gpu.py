@@ -128,6 +128,9 @@ def test_not_eligible_goes_straight_to_the_classic_sequence(eng):
     p.scalar_qty[:] = 2                                               # two devices per pod: the first-fit GPU choice shows in the plan
     _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "mps, quantity 2")
     assert st["fused"] == 0 and st["fused_reject"] == 0
+    s, p = synth.mig_cluster(500, 8, 40, seed=12)                     # 40 pods cannot lack more than (G+2)*M_p devices of anything
+    _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "too few pods to saturate")
+    assert st["fused"] == 0 and st["fused_reject"] == 0
     s, p = synth.mig_cluster(100, 8, 600, seed=12)
     p.base[3, 2] = 1 << 20                                            # an ephemeral-storage request
     _, _, st = check(eng, s, p, None, pk.FILTER_RESOURCES_FIT, "ephemeral")
