@@ -645,9 +645,9 @@ __device__ __forceinline__ void fused_body(const DevProblem& pb, const FusedLaun
         }
     }
     __syncthreads();
-    for (int w = tid; w < n_words; w += FT) {
-        const unsigned b = s_bits[w];
-        if (b) atomicOr(&pb.placed[w], b);
+    for (int w = tid; w < n_words; w += FT) {        // every node places the same first pods: most words are already set by the CTAs
+        const unsigned b = s_bits[w];                 // that finished earlier, and a read costs no turn in the word's atomic queue
+        if (b && (b & ~__ldcg(&pb.placed[w]))) atomicOr(&pb.placed[w], b);
     }
 #ifdef NOSPLAN_FUSED_PROFILE
     TICK(5);
