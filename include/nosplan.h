@@ -173,6 +173,15 @@ int nosplan_changed_nodes(nosplan_t* h, int32_t* node_idx, int32_t capacity, int
  * otherwise Go 1.18's sort.SliceStable (insertion sort of 20 + symMerge) is executed step for step.  Needs no GPU. */
 int nosplan_host_pod_order(const nosplan_snapshot* snap, const nosplan_pods* pods, int32_t* order_out);
 
+/* Host-only: the pod structure the single-launch kernel reads (runs of identical requests in NewPodSorter order, (cpu, memory)
+ * pairs in padded positions, minima per 8 / 64 / 512 positions, suffix minima, cumulative sums), staged exactly as nosplan_plan
+ * stages it, into the caller's buffer -- so that the staging can be checked and timed without a GPU.  meta[0..10] = byte offsets
+ * of the sections (geometry key masks, model ranges, run records, runs per profile, then the five levels, the pods, the end),
+ * meta[11..15] = runs, padded positions, cpu shift, memory shift, requested-profile set.  Returns the size in bytes (also when
+ * `blob` is NULL or too small: nothing is written then), 0 when these pods take the general path, < 0 on error. */
+int64_t nosplan_host_stage_pods(const nosplan_snapshot* snap, const nosplan_pods* pods, const uint8_t* prefilter_ok,
+                                uint8_t* blob, int64_t capacity, int32_t* meta);
+
 /* nosplan_plan with the node side in COMPACT form: one record per node, one contiguous array, one DMA -- 128 + 24*G (+ 16 per
  * other scalar resource) bytes per node against ~490 in the SoA form of nosplan_snapshot (G = 8, K = 7), expanded on the GPU
  * into the arrays the kernels read (128 + 24*G rounded up to 16).  Same semantics, errors and outputs as nosplan_plan; the snapshot stays resident for

@@ -23,7 +23,7 @@ EXPORTED_SYMBOLS = [
     "nosplan_lacking_static", "nosplan_quota_recompute", "nosplan_quota_victims",
     "nosplan_shard_exchange_bytes", "nosplan_shard_begin", "nosplan_shard_end", "nosplan_device_outputs",
     "nosplan_nccl_unique_id", "nosplan_shard_init", "nosplan_run_sharded", "nosplan_download_sharded",
-    "nosplan_host_pod_order", "nosplan_set_kernel_events",
+    "nosplan_host_pod_order", "nosplan_host_stage_pods", "nosplan_set_kernel_events",
     "nosplan_slice_begin", "nosplan_slice_mid", "nosplan_run_sliced", "nosplan_parse_annotations", "nosplan_shard_transport",
     "nosplan_preempt_dryrun", "nosplan_quota_label_changes", "nosplan_slice_chain_bytes", "nosplan_slice_chain",
     "nosplan_plan_resident", "nosplan_update_nodes", "nosplan_upload_pods", "nosplan_changed_nodes", "nosplan_preempt_dryrun_again", "nosplan_quota_state_begin", "nosplan_quota_state_apply", "nosplan_quota_state_prefilter",
@@ -45,6 +45,36 @@ def host_pod_order(snap: PackedSnapshot, pods: PackedPods, lib_path: str = None)
     if rc != 0:
         raise NosplanError(f"nosplan_host_pod_order failed ({rc})")
     return order[:pods.n_pods]
+
+
+STAGE_META = ("key_masks", "model_ranges", "runs", "runs_per_profile", "l3", "l2", "l1", "sfx", "cum", "pods", "end")
+
+
+def host_stage_pods(snap: PackedSnapshot, pods: PackedPods, prefilter_ok=None, lib_path: str = None, repeat: int = 1):
+    """nosplan_host_stage_pods: the pod structure of the single-launch kernel as nosplan_plan stages it (host only, no GPU).
+    -> (blob uint8 array, meta dict with the section offsets, n_runs, pad_pods, cpu_shift, mem_shift, rset), or (None, None)
+    when these pods take the general path.  repeat > 1 stages that many times (for timing)."""
+    lib = C.CDLL(lib_path or LIB_PATH)
+    lib.nosplan_host_stage_pods.argtypes = [C.POINTER(CSnapshot), C.POINTER(CPods), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    lib.nosplan_host_stage_pods.restype = C.c_int64
+    cs, k1 = c_snapshot(snap)
+    cp, k2 = c_pods(pods)
+    pre = None if prefilter_ok is None else np.ascontiguousarray(prefilter_ok, np.uint8)
+    meta = np.zeros(16, np.int32)
+    need = lib.nosplan_host_stage_pods(C.byref(cs), C.byref(cp), None if pre is None else pre.ctypes.data, None, 0, meta.ctypes.data)
+    if need < 0:
+        raise NosplanError(f"nosplan_host_stage_pods failed ({need})")
+    if need == 0:
+        return None, None
+    blob = np.zeros(need, np.uint8)
+    for _ in range(max(1, repeat)):
+        got = lib.nosplan_host_stage_pods(C.byref(cs), C.byref(cp), None if pre is None else pre.ctypes.data, blob.ctypes.data, need, meta.ctypes.data)
+    assert got == need
+    m = {name: int(meta[k]) for k, name in enumerate(STAGE_META)}
+    m.update(n_runs=int(meta[11]), pad_pods=int(meta[12]), cpu_shift=int(meta[13]), mem_shift=int(meta[14]), rset=int(meta[15]) & 0xffffffff)
+    return blob, m
+
+
 STATIC_MAX_KEYS = 16384
 
 

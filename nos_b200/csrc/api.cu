@@ -460,6 +460,184 @@ static void blob_finish(unsigned char* B, const int* fp_off, FRun* fr, int nr) {
     std::memcpy(B + fp_off[2], fr, sizeof(FRun) * (size_t)nr);
 }
 
+// ---- the pods of the single-launch kernel in two passes over the caller's arrays, no sort (host only; nosplan_host_stage_pods
+// exposes it to CPU tests).  Where NewPodSorter's comparator (core/util.go:34-73) is a strict weak order on what is present,
+// its order is a bucket order -- priority descending, then the rank of the requested profile, ties in original order -- so
+// pass A validates, classifies and counts per bucket, and pass B writes every pod's pair straight to its padded position.
+struct FastPlan {
+    int n_keys = 0, n_runs = 0, n_chunks = 0, cpu_shift = 0, mem_shift = 0, pad_pods = 0;
+    unsigned rset = 0;
+    FRun fr[FRUN_MAX];
+    int run_of[64 * (KP + 1)];
+};
+// pass A.  false: not this path (the general path takes the pods, and reports what is wrong with them if anything is)
+template <class CanSaturate>
+static bool fast_pods_plan(const nosplan_snapshot* s, const nosplan_pods* pods, int nnz, bool mig, std::vector<uint16_t>& bk,
+                           std::vector<uint8_t>& key_seen, const CanSaturate& can_saturate, FastPlan& out) {
+    const int K = s->n_profiles, P = pods->n_pods;
+    constexpr int LV_MAX = 64, NB = KP + 1;
+    struct Level { int32_t prio; int cnt[NB]; };
+    Level levels[LV_MAX];
+    int n_lv = 0;
+    bk.resize(P);
+    key_seen.assign(P, 0);
+    unsigned long long or_cpu = 0, or_mem = 0;
+    long long max_cpu = 0, max_mem = 0;
+    int max_key = -1;
+    int32_t lv_prio[LV_MAX];
+    {   // local copies of the array pointers: the byte stores below may alias anything as far as the compiler knows
+        const int32_t* __restrict sptr = pods->scalar_ptr; const int32_t* __restrict scol = pods->scalar_col;
+        const int64_t* __restrict sqty = pods->scalar_qty; const int64_t* __restrict base = pods->base;
+        const int32_t* __restrict tkey = pods->tracker_key; const int32_t* __restrict prios = pods->priority;
+        uint16_t* __restrict bkp = bk.data(); uint8_t* __restrict seen = key_seen.data();
+        int cnt[LV_MAX * NB];                              // pods per (priority level, profile) bucket, filled level by level
+        int a = sptr[0];
+        for (int i = 0; i < P; ++i) {
+            const int a1 = sptr[i + 1], n = a1 - a;
+            int pr = -1;
+            if (n == 1) {
+                if (a < 0 || a >= nnz) return false;
+                const int col = scol[a];
+                if (col < 3 || col >= 3 + K || sqty[a] != 1) return false;
+                pr = col - 3;
+            } else if (n != 0) return false;
+            a = a1;
+            const long long bc = base[3 * (size_t)i], bm = base[3 * (size_t)i + 1], be = base[3 * (size_t)i + 2];
+            if ((bc | bm) < 0 || be != 0 || (n == 0 && (bc | bm) == 0)) return false;
+            const int k = tkey[i];
+            if ((unsigned)k >= (unsigned)P || seen[k]) return false;
+            seen[k] = 1;
+            max_key = std::max(max_key, k);
+            const int32_t prio = prios[i];
+            // few distinct priorities: compare with all of them, no data-dependent branch (the priorities arrive in random order)
+            int hit = -1;
+            for (int q = 0; q < n_lv; ++q) hit = lv_prio[q] == prio ? q : hit;
+            if (hit < 0) {
+                if (n_lv >= LV_MAX) return false;
+                std::memset(cnt + n_lv * NB, 0, sizeof(int) * NB);
+                lv_prio[n_lv] = prio;
+                hit = n_lv++;
+            }
+            const int b = hit * NB + pr + 1;
+            cnt[b]++;
+            bkp[i] = (uint16_t)b;
+            or_cpu |= (unsigned long long)bc; or_mem |= (unsigned long long)bm;
+            max_cpu = std::max(max_cpu, bc); max_mem = std::max(max_mem, bm);
+        }
+        for (int q = 0; q < n_lv; ++q) { levels[q].prio = lv_prio[q]; std::memcpy(levels[q].cnt, cnt + q * NB, sizeof(int) * NB); }
+    }
+    // profiles present: the comparator must be a strict weak order on them, and no two of them may share a rank
+    const int32_t* pmem = s->profile_mem_gb; const int32_t* pgi = s->profile_gi;
+    auto smaller = [=](int x, int y) { if (pmem[x] < pmem[y]) return true; return mig && pgi[x] < pgi[y]; };
+    bool present[KP] = {false};
+    for (int q = 0; q < n_lv; ++q) {
+        const Level& l = levels[q];
+        bool sliced = false;
+        for (int pr = 0; pr < K; ++pr) if (l.cnt[pr + 1]) { present[pr] = true; sliced = true; }
+        if (l.cnt[0] && sliced) return false;                         // slice-less pods are incomparable to everything
+    }
+    int rank_of[KP] = {0};
+    unsigned ranks_used = 0;
+    for (int x = 0; x < K; ++x) {
+        if (!present[x]) continue;
+        for (int y = 0; y < K; ++y) {
+            if (!present[y]) continue;
+            if (smaller(x, y) && smaller(y, x)) return false;
+            if (smaller(y, x)) ++rank_of[x];
+            for (int z = 0; z < K; ++z) {
+                if (!present[z]) continue;
+                if (smaller(x, y) && smaller(y, z) && !smaller(x, z)) return false;
+                const bool ixy = !smaller(x, y) && !smaller(y, x), iyz = !smaller(y, z) && !smaller(z, y), ixz = !smaller(x, z) && !smaller(z, x);
+                if (ixy && iyz && !ixz) return false;
+            }
+        }
+        if (ranks_used >> rank_of[x] & 1u) return false;
+        ranks_used |= 1u << rank_of[x];
+    }
+    int prof_by_rank[KP], n_present = 0;
+    for (int r = 0; r < KP; ++r) for (int x = 0; x < K; ++x) if (present[x] && rank_of[x] == r) prof_by_rank[n_present++] = x;
+    for (int x = 0; x < K; ++x) {
+        if (!present[x]) continue;
+        long long asked = 0;
+        for (int q = 0; q < n_lv; ++q) asked += levels[q].cnt[x + 1];
+        if (!can_saturate(x, asked)) return false;                   // the general path stages the pods for the classic kernels
+    }
+    // runs = non-empty buckets, priority descending, then profile rank
+    int lv_order[LV_MAX];
+    for (int q = 0; q < n_lv; ++q) lv_order[q] = q;
+    std::sort(lv_order, lv_order + n_lv, [&](int x, int y) { return levels[x].prio > levels[y].prio; });
+    int nr = 0, pos = 0, chunks = 0;
+    unsigned rs = 0;
+    for (int q = 0; q < n_lv; ++q) {
+        const Level& l = levels[lv_order[q]];
+        for (int c = -1; c < n_present; ++c) {
+            const int pr = c < 0 ? -1 : prof_by_rank[c], cnt = l.cnt[pr + 1];
+            if (!cnt) continue;
+            if (nr >= FRUN_MAX) return false;
+            FRun f; std::memset(&f, 0, sizeof f);
+            f.pos0 = pos; f.nblk = (cnt + 63) >> 6; f.n_real = cnt; f.p = pr; f.q = pr >= 0 ? 1 : 0; f.min_c = f.min_m = F_NONE;
+            out.run_of[lv_order[q] * NB + pr + 1] = nr;
+            out.fr[nr++] = f;
+            pos += f.nblk * 64; chunks += (cnt + 31) >> 5;
+            if (pr >= 0) rs |= 1u << pr;
+        }
+    }
+    const int cs = or_cpu ? __builtin_ctzll(or_cpu) : 0, ms = or_mem ? __builtin_ctzll(or_mem) : 0;
+    if ((max_cpu >> cs) >= F_COST_LIMIT || (max_mem >> ms) >= F_COST_LIMIT || pos > fused_max_pad_pods() || rs == 0) return false;
+    out.n_keys = max_key + 1; out.n_runs = nr; out.n_chunks = chunks; out.cpu_shift = cs; out.mem_shift = ms; out.pad_pods = pos; out.rset = rs;
+    return true;
+}
+// pass B into a blob that blob_begin has prepared (original order == order inside a bucket), then everything derived from the pairs
+static void fast_pods_fill(const nosplan_pods* pods, const uint8_t* prefilter_ok, const std::vector<uint16_t>& bk, FastPlan& fp,
+                           unsigned char* B, const int* fp_off) {
+    const int P = pods->n_pods, cs = fp.cpu_shift, ms = fp.mem_shift;
+    int32_t* fpod = (int32_t*)(B + fp_off[FP_PODS]);
+    int cur[FRUN_MAX];
+    for (int r = 0; r < fp.n_runs; ++r) cur[r] = fp.fr[r].pos0;
+    for (int i = 0; i < P; ++i) {
+        const int x = cur[fp.run_of[bk[i]]]++;
+        if (prefilter_ok && !prefilter_ok[i]) continue;
+        fpod[2 * (size_t)x] = (int32_t)(pods->base[3 * (size_t)i] >> cs);
+        fpod[2 * (size_t)x + 1] = (int32_t)(pods->base[3 * (size_t)i + 1] >> ms);
+    }
+    blob_finish(B, fp_off, fp.fr, fp.n_runs);
+}
+
+// Host-only: the pod structure of the single-launch kernel exactly as nosplan_plan stages it (layout in nosplan_dev.cuh), into the
+// caller's buffer.  meta[0..10] = byte offsets of the sections, then runs, padded positions, cpu shift, memory shift, requested set.
+// Returns the blob's size in bytes, 0 when the two-pass path does not take these pods, < 0 on error.  Needs no GPU.
+extern "C" int64_t nosplan_host_stage_pods(const nosplan_snapshot* s, const nosplan_pods* pods, const uint8_t* prefilter_ok, uint8_t* blob,
+                                           int64_t capacity, int32_t* meta) {
+    if (!s || !pods || !meta) return NOSPLAN_E_INVALID;
+    const int K = s->n_profiles, P = pods->n_pods;
+    if (K < 0 || K > NOSPLAN_MAX_PROFILES || P <= 0) return NOSPLAN_E_INVALID;
+    const bool mig = s->kind == NOSPLAN_KIND_MIG;
+    const int n_models = mig ? s->n_models : 0;
+    const int n_rows = (mig && n_models > 0) ? s->model_geom_offset[n_models] : 0;
+    static thread_local std::vector<uint16_t> bk;
+    static thread_local std::vector<uint8_t> key_seen;
+    static const bool trace = getenv("NOSPLAN_TRACE") != nullptr;       // NOSPLAN_TRACE=1: microseconds per phase on stderr
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+    FastPlan fp;
+    auto always = [](int, long long) { return true; };
+    const auto t0 = now();
+    if (!fast_pods_plan(s, pods, pods->scalar_ptr[P], mig, bk, key_seen, always, fp)) return 0;
+    const auto t1 = now();
+    int fp_off[FP_NOFF];
+    blob_layout(n_rows, n_models, fp.n_runs, fp.pad_pods, fp_off);
+    for (int k = 0; k < FP_NOFF; ++k) meta[k] = fp_off[k];
+    meta[FP_NOFF] = fp.n_runs; meta[FP_NOFF + 1] = fp.pad_pods; meta[FP_NOFF + 2] = fp.cpu_shift; meta[FP_NOFF + 3] = fp.mem_shift;
+    meta[FP_NOFF + 4] = (int32_t)fp.rset;
+    if (!blob || capacity < fp_off[FP_END]) return fp_off[FP_END];
+    const auto t2 = now();
+    blob_begin(blob, fp_off, s, n_rows, n_models);
+    const auto t3 = now();
+    fast_pods_fill(pods, prefilter_ok, bk, fp, blob, fp_off);
+    if (trace) fprintf(stderr, "[nosplan_host_stage_pods] pass A %.1f us, begin %.1f us, pass B + finish %.1f us\n", us(t0, t1), us(t2, t3), us(t3, now()));
+    return fp_off[FP_END];
+}
+
 // The classic kernels' view of the pods, in NewPodSorter order (h->v_order): request columns, tracker keys, flags, CSR of the
 // scalar entries, the run records and per-chunk (32 pods, run-relative) minima of the requests of the PreFilter-ok pods -- the
 // kernels skip chunks in which no pod can pass NodeResourcesFit.  An all-zero request passes regardless (fit.go short-circuit):
@@ -734,114 +912,12 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
     };
     bool fast_done = false;
     if (fused_ok && h->in_plan && P > 0 && !getenv("NOSPLAN_NO_FAST_PODS")) fast_done = [&]() -> bool {
-        constexpr int LV_MAX = 64, NB = KP + 1;
-        struct Level { int32_t prio; int cnt[NB]; };
-        Level levels_store[LV_MAX];
-        struct { Level* d; size_t n; size_t size() const { return n; } Level& operator[](size_t k) { return d[k]; }
-                 const Level& operator[](size_t k) const { return d[k]; } void push_back(const Level& l) { d[n++] = l; }
-                 Level* begin() { return d; } Level* end() { return d + n; } } levels{levels_store, 0};
-        std::vector<uint16_t>& bk = h->v_bucket; bk.resize(P);
-        std::vector<uint8_t>& key_seen = h->v_key_seen; key_seen.assign(P, 0);
-        unsigned long long or_cpu = 0, or_mem = 0;
-        long long max_cpu = 0, max_mem = 0;
-        int max_key = -1;
-        size_t last = 0;
-        int32_t lv_prio[LV_MAX]; int n_lv_seen = 0;
-        for (int i = 0; i < P; ++i) {
-            const int a = pods->scalar_ptr[i], n = pods->scalar_ptr[i + 1] - a;
-            int pr = -1;
-            if (n == 1) {
-                const int col = pods->scalar_col[a];
-                if (a < 0 || a >= nnz || col < 3 || col >= 3 + K || pods->scalar_qty[a] != 1) return false;
-                pr = col - 3;
-            } else if (n != 0) return false;
-            const long long bc = pods->base[3 * (size_t)i], bm = pods->base[3 * (size_t)i + 1], be = pods->base[3 * (size_t)i + 2];
-            if ((bc | bm) < 0 || be != 0 || (n == 0 && (bc | bm) == 0)) return false;
-            const int k = pods->tracker_key[i];
-            if (k < 0 || k >= P || key_seen[k]) return false;
-            key_seen[k] = 1;
-            max_key = std::max(max_key, k);
-            const int32_t prio = pods->priority[i];
-            {   // few distinct priorities: compare with all of them, no data-dependent branch (the priorities arrive in random order)
-                int hit = -1;
-                for (int q = 0; q < n_lv_seen; ++q) hit = lv_prio[q] == prio ? q : hit;
-                if (hit < 0) {
-                    if (n_lv_seen >= LV_MAX) return false;
-                    Level l; l.prio = prio; std::memset(l.cnt, 0, sizeof l.cnt);
-                    levels.push_back(l);
-                    lv_prio[n_lv_seen] = prio;
-                    hit = n_lv_seen++;
-                }
-                last = (size_t)hit;
-            }
-            levels[last].cnt[pr + 1]++;
-            bk[i] = (uint16_t)(last * NB + pr + 1);
-            or_cpu |= (unsigned long long)bc; or_mem |= (unsigned long long)bm;
-            max_cpu = std::max(max_cpu, bc); max_mem = std::max(max_mem, bm);
-        }
+        FastPlan fp;
+        if (!fast_pods_plan(s, pods, nnz, mig, h->v_bucket, h->v_key_seen, can_saturate, fp)) return false;
         lap("pods: pass A");
-        // profiles present: the comparator must be a strict weak order on them, and no two of them may share a rank
-        const int32_t* pmem = s->profile_mem_gb; const int32_t* pgi = s->profile_gi;
-        auto smaller = [=](int x, int y) { if (pmem[x] < pmem[y]) return true; return mig && pgi[x] < pgi[y]; };
-        bool present[KP] = {false};
-        for (const Level& l : levels) {
-            bool sliced = false;
-            for (int pr = 0; pr < K; ++pr) if (l.cnt[pr + 1]) { present[pr] = true; sliced = true; }
-            if (l.cnt[0] && sliced) return false;                         // slice-less pods are incomparable to everything
-        }
-        int rank_of[KP] = {0};
-        unsigned ranks_used = 0;
-        for (int x = 0; x < K; ++x) {
-            if (!present[x]) continue;
-            for (int y = 0; y < K; ++y) {
-                if (!present[y]) continue;
-                if (smaller(x, y) && smaller(y, x)) return false;
-                if (smaller(y, x)) ++rank_of[x];
-                for (int z = 0; z < K; ++z) {
-                    if (!present[z]) continue;
-                    if (smaller(x, y) && smaller(y, z) && !smaller(x, z)) return false;
-                    const bool ixy = !smaller(x, y) && !smaller(y, x), iyz = !smaller(y, z) && !smaller(z, y), ixz = !smaller(x, z) && !smaller(z, x);
-                    if (ixy && iyz && !ixz) return false;
-                }
-            }
-            if (ranks_used >> rank_of[x] & 1u) return false;
-            ranks_used |= 1u << rank_of[x];
-        }
-        int prof_by_rank[KP], n_present = 0;
-        for (int r = 0; r < KP; ++r) for (int x = 0; x < K; ++x) if (present[x] && rank_of[x] == r) prof_by_rank[n_present++] = x;
-        for (int x = 0; x < K; ++x) {
-            if (!present[x]) continue;
-            long long asked = 0;
-            for (const Level& l : levels) asked += l.cnt[x + 1];
-            if (!can_saturate(x, asked)) return false;                   // the general path stages the pods for the classic kernels
-        }
-        // runs = non-empty buckets, priority descending, then profile rank
-        int lv_order[LV_MAX];
-        const int n_lv = (int)levels.size();
-        for (int q = 0; q < n_lv; ++q) lv_order[q] = q;
-        std::sort(lv_order, lv_order + n_lv, [&](int x, int y) { return levels[x].prio > levels[y].prio; });
-        FRun fr[FRUN_MAX];
-        int run_of[LV_MAX * NB];
-        int nr = 0, pos = 0, chunks = 0;
-        unsigned rs = 0;
-        for (int q = 0; q < n_lv; ++q) {
-            const Level& l = levels[lv_order[q]];
-            for (int c = -1; c < n_present; ++c) {
-                const int pr = c < 0 ? -1 : prof_by_rank[c], cnt = l.cnt[pr + 1];
-                if (!cnt) continue;
-                if (nr >= FRUN_MAX) return false;
-                FRun f; std::memset(&f, 0, sizeof f);
-                f.pos0 = pos; f.nblk = (cnt + 63) >> 6; f.n_real = cnt; f.p = pr; f.q = pr >= 0 ? 1 : 0; f.min_c = f.min_m = F_NONE;
-                run_of[lv_order[q] * NB + pr + 1] = nr;
-                fr[nr++] = f;
-                pos += f.nblk * 64; chunks += (cnt + 31) >> 5;
-                if (pr >= 0) rs |= 1u << pr;
-            }
-        }
-        const int cs = or_cpu ? __builtin_ctzll(or_cpu) : 0, ms = or_mem ? __builtin_ctzll(or_mem) : 0;
-        if ((max_cpu >> cs) >= F_COST_LIMIT || (max_mem >> ms) >= F_COST_LIMIT || pos > fused_max_pad_pods() || rs == 0) return false;
         // layout, part 2 (the classic sections keep their room: a rejected plan stages them later), then the blob
-        n_keys = max_key + 1; n_runs = nr; n_chunks = chunks; cpu_shift = cs; mem_shift = ms; pad_pods = pos; rset = rs;
+        n_keys = fp.n_keys; n_runs = fp.n_runs; n_chunks = fp.n_chunks; cpu_shift = fp.cpu_shift; mem_shift = fp.mem_shift;
+        pad_pods = fp.pad_pods; rset = fp.rset;
         single_profile_classes = true; any_eph = 0;
         o = part1_end;
         put(L.runs, sizeof(RunRec) * (size_t)n_runs);
@@ -853,21 +929,10 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         if (L.total > bound) return false;
         h->lay = L;
         unsigned char* B = S + L.fp_blob;
-        lap("pods: runs");
         blob_begin(B, fp_off, s, n_rows, n_models);
         lap("pods: begin");
-        int32_t* fpod = (int32_t*)(B + fp_off[FP_PODS]);
-        int cur[FRUN_MAX];
-        for (int r = 0; r < nr; ++r) cur[r] = fr[r].pos0;
-        for (int i = 0; i < P; ++i) {                                     // pass B: original order == order inside a bucket
-            const int x = cur[run_of[bk[i]]]++;
-            if (prefilter_ok && !prefilter_ok[i]) continue;
-            fpod[2 * (size_t)x] = (int32_t)(pods->base[3 * (size_t)i] >> cs);
-            fpod[2 * (size_t)x + 1] = (int32_t)(pods->base[3 * (size_t)i + 1] >> ms);
-        }
-        lap("pods: pass B");
-        blob_finish(B, fp_off, fr, nr);
-        lap("pods: finish");
+        fast_pods_fill(pods, prefilter_ok, h->v_bucket, fp, B, fp_off);
+        lap("pods: pass B, finish");
         lazy = true; up_from = L.fp_blob;
         h->classic_staged = false;
         h->lazy_valid = true; h->lazy_pods = *pods; h->lazy_pre = prefilter_ok; h->lazy_filter = filter_mode;
