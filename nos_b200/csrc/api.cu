@@ -414,8 +414,9 @@ static void blob_layout(int n_rows, int n_models, int n_runs, int pad_pods, int*
     fp_off[FP_PODS] = fp_off[FP_CUM] + a16(16 * (size_t)n1);
     fp_off[FP_END] = fp_off[FP_PODS] + a16(8 * (size_t)pad_pods);
 }
-// header tables; every pair of the minima and of the pods starts as F_NONE ("no eligible pod")
-static void blob_begin(unsigned char* B, const int* fp_off, const nosplan_snapshot* s, int n_rows, int n_models) {
+// header tables; every pair of the minima and of the pods starts as F_NONE ("no eligible pod").  minima_only: the caller writes
+// every pod position itself (fast_pods_fill), and blob_finish writes every per-8 section, so only the two upper levels need it
+static void blob_begin(unsigned char* B, const int* fp_off, const nosplan_snapshot* s, int n_rows, int n_models, bool minima_only = false) {
     std::memset(B, 0, (size_t)fp_off[FP_L3]);
     if (n_rows) std::memcpy(B, s->geom_counts, 16 * (size_t)n_rows);
     for (int r = 0; r < n_rows; ++r) {
@@ -424,7 +425,7 @@ static void blob_begin(unsigned char* B, const int* fp_off, const nosplan_snapsh
         ((uint16_t*)(B + fp_off[0]))[r] = m;
     }
     if (n_models > 0) std::memcpy(B + fp_off[1], s->model_geom_offset, 4 * ((size_t)n_models + 1));
-    std::fill((int32_t*)(B + fp_off[FP_L3]), (int32_t*)(B + fp_off[FP_END]), (int32_t)F_NONE);
+    std::fill((int32_t*)(B + fp_off[FP_L3]), (int32_t*)(B + fp_off[minima_only ? FP_L1 : FP_END]), (int32_t)F_NONE);
 }
 // the pod pairs are in place: minima per 8 / 64 / 512 positions, suffix minima and cumulative sums per run, run records
 static void blob_finish(unsigned char* B, const int* fp_off, FRun* fr, int nr) {
@@ -438,10 +439,11 @@ static void blob_finish(unsigned char* B, const int* fp_off, FRun* fr, int nr) {
         long long sc = 0, sm = 0; int cnt = 0;
         for (int x8 = x0; x8 < x1; ++x8) {
             int32_t mc = F_NONE, mm = F_NONE; unsigned elig = 0;
-            for (int k = 0; k < 8; ++k) {
-                const int32_t c = fpod[2 * ((size_t)x8 * 8 + k)], m = fpod[2 * ((size_t)x8 * 8 + k) + 1];
-                if (c == F_NONE) continue;
-                mc = std::min(mc, c); mm = std::min(mm, m); elig |= 1u << k; sc += c; sm += m; ++cnt;
+            const int32_t* g = fpod + 16 * (size_t)x8;
+            for (int k = 0; k < 8; ++k) {                      // no branch: an ineligible position is (F_NONE, F_NONE), neutral for the minima
+                const int32_t c = g[2 * k], m = g[2 * k + 1];
+                const int v = c != F_NONE;
+                mc = std::min(mc, c); mm = std::min(mm, m); elig |= (unsigned)v << k; sc += v ? c : 0; sm += v ? m : 0; cnt += v;
             }
             l1[2 * (size_t)x8] = mc; l1[2 * (size_t)x8 + 1] = mm;
             int32_t* cu = cum + 4 * (size_t)x8;
@@ -593,12 +595,18 @@ static void fast_pods_fill(const nosplan_pods* pods, const uint8_t* prefilter_ok
     const int P = pods->n_pods, cs = fp.cpu_shift, ms = fp.mem_shift;
     int32_t* fpod = (int32_t*)(B + fp_off[FP_PODS]);
     int cur[FRUN_MAX];
-    for (int r = 0; r < fp.n_runs; ++r) cur[r] = fp.fr[r].pos0;
+    for (int r = 0; r < fp.n_runs; ++r) {                  // the padding behind every run; the pods' own positions below
+        const FRun& f = fp.fr[r];
+        cur[r] = f.pos0;
+        std::fill(fpod + 2 * (size_t)(f.pos0 + f.n_real), fpod + 2 * (size_t)(f.pos0 + f.nblk * 64), (int32_t)F_NONE);
+    }
+    const int64_t* __restrict base = pods->base;
+    const uint16_t* __restrict bkp = bk.data();
     for (int i = 0; i < P; ++i) {
-        const int x = cur[fp.run_of[bk[i]]]++;
-        if (prefilter_ok && !prefilter_ok[i]) continue;
-        fpod[2 * (size_t)x] = (int32_t)(pods->base[3 * (size_t)i] >> cs);
-        fpod[2 * (size_t)x + 1] = (int32_t)(pods->base[3 * (size_t)i + 1] >> ms);
+        const int x = cur[fp.run_of[bkp[i]]]++;
+        const bool ok = !prefilter_ok || prefilter_ok[i];
+        fpod[2 * (size_t)x] = ok ? (int32_t)(base[3 * (size_t)i] >> cs) : (int32_t)F_NONE;
+        fpod[2 * (size_t)x + 1] = ok ? (int32_t)(base[3 * (size_t)i + 1] >> ms) : (int32_t)F_NONE;
     }
     blob_finish(B, fp_off, fp.fr, fp.n_runs);
 }
@@ -631,7 +639,7 @@ extern "C" int64_t nosplan_host_stage_pods(const nosplan_snapshot* s, const nosp
     meta[FP_NOFF + 4] = (int32_t)fp.rset;
     if (!blob || capacity < fp_off[FP_END]) return fp_off[FP_END];
     const auto t2 = now();
-    blob_begin(blob, fp_off, s, n_rows, n_models);
+    blob_begin(blob, fp_off, s, n_rows, n_models, true);
     const auto t3 = now();
     fast_pods_fill(pods, prefilter_ok, bk, fp, blob, fp_off);
     if (trace) fprintf(stderr, "[nosplan_host_stage_pods] pass A %.1f us, begin %.1f us, pass B + finish %.1f us\n", us(t0, t1), us(t2, t3), us(t3, now()));
@@ -929,7 +937,7 @@ static int upload_impl(nosplan_t* h, const nosplan_snapshot* s, const nosplan_po
         if (L.total > bound) return false;
         h->lay = L;
         unsigned char* B = S + L.fp_blob;
-        blob_begin(B, fp_off, s, n_rows, n_models);
+        blob_begin(B, fp_off, s, n_rows, n_models, true);
         lap("pods: begin");
         fast_pods_fill(pods, prefilter_ok, h->v_bucket, fp, B, fp_off);
         lap("pods: pass B, finish");
