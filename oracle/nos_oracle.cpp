@@ -12,6 +12,9 @@
 //                           "reference algorithm" CPU baseline.
 //   NOS_ORACLE_INCREMENTAL  same results with running cluster totals and no cloning (the derived
 //                           state rules are written out in plan_incremental); used at full size.
+// A third mode, NOS_ORACLE_DEVICE_MODEL, is NOT a restatement of the reference: it restates, in this file's terms, the algorithm
+// the CUDA path uses where the cluster-wide gate is not vacuous (plan_device_model), so that its exactness against
+// plan_incremental is checked on the CPU too (tests/test_device_model.py).  Nothing times or ships it.
 // Pinning: this file is checked against oracle/nos_model.py (the dict/string model that reproduces every
 // golden vector ported from the reference's tests, tests/golden/) on the golden cases and on thousands
 // of randomised small snapshots.
@@ -29,6 +32,7 @@
 
 #define NOS_ORACLE_FAITHFUL 0
 #define NOS_ORACLE_INCREMENTAL 1
+#define NOS_ORACLE_DEVICE_MODEL 2     /* model of the CUDA path's gate replay (see plan_device_model); tests only */
 
 namespace {
 
@@ -321,6 +325,7 @@ struct Problem {
     std::vector<uint8_t> pre_ok;
     int n_keys;
     int filter_mode;
+    int n_models = 0;      // MIG: models in the geometry table (the device model's saturation bound reads every row)
 };
 
 int build(const nosplan_snapshot* s, const nosplan_pods* p, const uint8_t* prefilter_ok, int filter_mode, Problem& pb) {
@@ -329,6 +334,7 @@ int build(const nosplan_snapshot* s, const nosplan_pods* p, const uint8_t* prefi
     pb.c = Ctx{s->kind, s->n_profiles, 3 + s->n_profiles + s->n_other, s->profile_mem_gb, s->profile_gi,
                s->model_geom_offset, s->geom_counts};
     pb.N = s->n_nodes; pb.G = s->gpus_per_node; pb.P = p->n_pods; pb.filter_mode = filter_mode;
+    pb.n_models = s->kind == NOSPLAN_KIND_MIG ? s->n_models : 0;
     const int R = pb.c.R, G = pb.G;
     pb.nodes.resize(pb.N);
     for (int i = 0; i < pb.N; ++i) {
@@ -546,6 +552,135 @@ int plan_incremental(Problem& pb, nosplan_partitioning* out, nosplan_stats* st) 
     return NOSPLAN_OK;
 }
 
+// ---------------------------------------------------------------- model of the DEVICE algorithm (CPU tests only)
+// Not a restatement of the reference: a restatement, in the oracle's own terms, of what the CUDA path does when node accounts
+// disagree with the GPUs or pods ask for several profiles (nos_b200/csrc/sweep.cu: k_plan_parallel without the cluster-wide gate,
+// write_gate_record, gate_scan, re-planning with the gate) -- so that the exactness argument of DESIGN.md section 4 is checked
+// against plan_incremental on the CPU as well.  Every candidate node is planned from its t0 state with a SATURATED lacking vector
+// and no gate, leaving (dW, placed, need, added, updated); the gate is then replayed in name order over those records with the
+// running totals under the Commit / Revert rules, and a node with an attempt the gate would have refused is planned again with
+// the gate on the exact totals.  Returns 1 ("not applicable": the device would fall back to the exact sweep) when the lacking
+// vector is not saturated at t0 or at the end.
+struct DevRec {
+    int64_t dW[KP], pl[KP], need[KP];
+    bool upd = false, added = false;
+    int placements = 0;
+    int64_t evals = 0;
+    Node F;
+    std::vector<int> keys;
+};
+
+static DevRec device_node(const Problem& pb, const std::vector<int>& order, int i, const int32_t* sat_lack, bool gate, const int64_t* Dtot) {
+    const Ctx& c = pb.c;
+    const Node& D = pb.nodes[i];
+    DevRec r;
+    std::memset(r.dW, 0, sizeof r.dW); std::memset(r.pl, 0, sizeof r.pl); std::memset(r.need, 0, sizeof r.need);
+    Node W = D;
+    r.upd = node_update_geometry(c, W, sat_lack, r.evals);
+    r.F = W;
+    if (!r.upd) std::memcpy(r.F.alloc, D.alloc, sizeof r.F.alloc);
+    for (int p = 0; p < c.K; ++p) r.dW[p] = W.alloc[3 + p] - D.alloc[3 + p];
+    for (int oi : order) {
+        const PodReq& pr = pb.pods[oi];
+        if (gate) {                                                       // core/snapshot.go:132-165 on the running totals
+            bool lacks = false;
+            for (int e = 0; e < pr.n_slice; ++e) {
+                const int p = pr.sp[e];
+                const int64_t avail = std::max<int64_t>(0, Dtot[p] + (r.upd ? r.dW[p] : 0) - (r.F.req[3 + p] - D.req[3 + p]));
+                if (avail < pr.sq[e]) lacks = true;
+            }
+            if (lacks) continue;
+        }
+        if (!pb.pre_ok[oi]) continue;
+        if (pb.filter_mode == NOSPLAN_FILTER_REJECT_ALL) continue;
+        if (pb.filter_mode == NOSPLAN_FILTER_RESOURCES_FIT && !resources_fit(r.F, pr)) continue;
+        if (!gate && pr.n_slice > 1)                                      // a refused attempt may leave devices moved: note what the gate would have had to grant
+            for (int e = 0; e < pr.n_slice; ++e) r.need[pr.sp[e]] = std::max(r.need[pr.sp[e]], r.F.req[3 + pr.sp[e]] - D.req[3 + pr.sp[e]] + pr.sq[e]);
+        if (!node_add_pod(c, r.F, pr)) continue;
+        r.keys.push_back(pb.tkey[oi]);
+        ++r.placements; r.added = true;
+    }
+    for (int p = 0; p < c.K; ++p) { r.pl[p] = r.F.req[3 + p] - D.req[3 + p]; if (!gate) r.need[p] = std::max(r.need[p], r.pl[p]); }
+    return r;
+}
+
+int plan_device_model(Problem& pb, nosplan_partitioning* out, nosplan_stats* st) {
+    const Ctx& c = pb.c; const int N = pb.N, G = pb.G, P = pb.P, R = c.R;
+    const std::vector<Node>& D = pb.nodes;
+    for (int i = 0; i < N; ++i) write_partitioning(D[i], i, G, out);
+    int64_t A[RMAX] = {0}, Rq[RMAX] = {0};
+    for (int i = 0; i < N; ++i) for (int k = 0; k < R; ++k) { A[k] += D[i].alloc[k]; Rq[k] += D[i].req[k]; }
+    Tracker tr; std::memset(tr.lack, 0, sizeof tr.lack); tr.entry.assign((size_t)pb.n_keys * KP, 0);
+    for (int i = 0; i < P; ++i) {
+        int32_t l[KP] = {0};
+        pod_lacks(pb.pods[i], A, Rq, l);
+        for (int p = 0; p < KP; ++p) { tr.lack[p] += l[p]; tr.entry[(size_t)pb.tkey[i] * KP + p] += l[p]; }
+    }
+    st->lacking_at_start = tr.count();
+    st->gate_replayed = -1;
+    if (tr.empty()) { st->lacking_at_end = 0; return NOSPLAN_OK; }
+    // the saturation bound of fast_applicable (sweep.cu): lack[p] > (G+2) * max(devices of p one GPU can hold, largest free count)
+    int64_t bound[KP] = {0};
+    int maxmem = 0;
+    for (int i = 0; i < N; ++i) for (int j = 0; j < D[i].ng; ++j) maxmem = std::max(maxmem, D[i].g[j].mem);
+    for (int p = 0; p < c.K; ++p) {
+        int m = 0;
+        if (c.kind == NOSPLAN_KIND_MIG) { const int rows = c.geom_off ? c.geom_off[pb.n_models] : 0; for (int r = 0; r < rows; ++r) m = std::max(m, (int)c.geom[16 * (size_t)r + p]); }
+        else m = c.pmem[p] > 0 ? maxmem / c.pmem[p] : (1 << 30);
+        for (int i = 0; i < N; ++i) for (int j = 0; j < D[i].ng; ++j) m = std::max(m, (int)D[i].g[j].free_[p]);
+        bound[p] = (int64_t)(G + 2) * m;
+    }
+    auto saturated = [&](const int32_t* lack) {
+        for (int p = 0; p < c.K; ++p) if (tr.lack[p] > 0 && !(lack[p] > 0 && (int64_t)lack[p] > bound[p])) return false;
+        return true;
+    };
+    if (!saturated(tr.lack)) return 1;
+    int32_t sat_lack[KP];
+    for (int p = 0; p < KP; ++p) sat_lack[p] = tr.lack[p] > 0 ? (1 << 29) : 0;
+    std::vector<int> order = sort_pods(pb);
+    std::vector<int> cands;
+    for (int i = 0; i < N; ++i) if (node_has_free_capacity(c, D[i])) cands.push_back(i);
+    st->candidate_nodes = (int64_t)cands.size();
+    st->visited_nodes = (int64_t)cands.size();
+    st->candidates = st->visited_nodes * P;
+    // ---- every node on its own, without the gate
+    std::vector<DevRec> rec(cands.size());
+    for (size_t k = 0; k < cands.size(); ++k) rec[k] = device_node(pb, order, cands[k], sat_lack, false, nullptr);
+    // ---- the gate, replayed in name order
+    int64_t Dtot[KP];
+    for (int p = 0; p < KP; ++p) Dtot[p] = p < c.K ? A[3 + p] - Rq[3 + p] : 0;
+    bool committed = false;
+    int again = 0;
+    std::vector<uint8_t> placed((size_t)pb.n_keys, 0);
+    for (size_t k = 0; k < cands.size(); ++k) {
+        DevRec* r = &rec[k];
+        st->geometry_evals += r->evals;
+        for (int key : r->keys) placed[key] = 1;                                  // keys only the gate-less run placed stay set (as on the device)
+        bool refused = false;
+        for (int p = 0; p < c.K; ++p) if (r->need[p] > 0 && Dtot[p] + (r->upd ? r->dW[p] : 0) - r->need[p] < 0) refused = true;
+        DevRec exact;
+        if (refused) { exact = device_node(pb, order, cands[k], sat_lack, true, Dtot); r = &exact; ++again; for (int key : r->keys) placed[key] = 1; }
+        if (r->added) {
+            for (int p = 0; p < c.K; ++p) Dtot[p] += (r->upd ? r->dW[p] : 0) - r->pl[p];
+            committed = true;
+            if (r->upd) write_partitioning(r->F, cands[k], G, out);
+        } else if (!committed) {
+            for (int p = 0; p < c.K; ++p) Dtot[p] += r->dW[p];
+        }
+        st->placements += r->placements;
+    }
+    int32_t le[KP];
+    for (int p = 0; p < KP; ++p) le[p] = tr.lack[p];
+    for (int key = 0; key < pb.n_keys; ++key) if (placed[key]) for (int p = 0; p < KP; ++p) le[p] -= std::max(0, tr.entry[(size_t)key * KP + p]);
+    if (!saturated(le)) return 1;
+    int cnt = 0;
+    for (int p = 0; p < KP; ++p) cnt += le[p] > 0;
+    st->lacking_at_end = cnt;
+    st->gate_replayed = again;
+    st->path = 1;
+    return NOSPLAN_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -557,7 +692,7 @@ int nos_oracle_plan(const nosplan_snapshot* s, const nosplan_pods* p, const uint
     if (rc != NOSPLAN_OK) return rc;
     nosplan_stats st; std::memset(&st, 0, sizeof st);
     auto t0 = std::chrono::steady_clock::now();
-    rc = mode == NOS_ORACLE_FAITHFUL ? plan_faithful(pb, out, &st) : plan_incremental(pb, out, &st);
+    rc = mode == NOS_ORACLE_FAITHFUL ? plan_faithful(pb, out, &st) : mode == NOS_ORACLE_DEVICE_MODEL ? plan_device_model(pb, out, &st) : plan_incremental(pb, out, &st);
     auto t1 = std::chrono::steady_clock::now();
     if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
     if (stats) *stats = st;
