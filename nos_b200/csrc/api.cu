@@ -619,9 +619,13 @@ extern "C" int64_t nosplan_host_stage_pods(const nosplan_snapshot* s, const nosp
     if (!s || !pods || !meta) return NOSPLAN_E_INVALID;
     const int K = s->n_profiles, P = pods->n_pods;
     if (K < 0 || K > NOSPLAN_MAX_PROFILES || P <= 0) return NOSPLAN_E_INVALID;
+    if (!pods->scalar_ptr || !pods->base || !pods->priority || !pods->tracker_key || !s->profile_mem_gb || !s->profile_gi) return NOSPLAN_E_INVALID;
+    if (pods->scalar_ptr[P] < 0 || (pods->scalar_ptr[P] > 0 && (!pods->scalar_col || !pods->scalar_qty))) return NOSPLAN_E_INVALID;
     const bool mig = s->kind == NOSPLAN_KIND_MIG;
     const int n_models = mig ? s->n_models : 0;
+    if (n_models < 0 || n_models > MAX_MODELS || (n_models > 0 && (!s->model_geom_offset || !s->geom_counts))) return NOSPLAN_E_INVALID;
     const int n_rows = (mig && n_models > 0) ? s->model_geom_offset[n_models] : 0;
+    if (n_rows < 0 || n_rows > MAX_ROWS) return NOSPLAN_E_LIMIT;
     static thread_local std::vector<uint16_t> bk;
     static thread_local std::vector<uint8_t> key_seen;
     static const bool trace = getenv("NOSPLAN_TRACE") != nullptr;       // NOSPLAN_TRACE=1: microseconds per phase on stderr
