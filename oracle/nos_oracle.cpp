@@ -12,9 +12,10 @@
 //                           "reference algorithm" CPU baseline.
 //   NOS_ORACLE_INCREMENTAL  same results with running cluster totals and no cloning (the derived
 //                           state rules are written out in plan_incremental); used at full size.
-// A third mode, NOS_ORACLE_DEVICE_MODEL, is NOT a restatement of the reference: it restates, in this file's terms, the algorithm
-// the CUDA path uses where the cluster-wide gate is not vacuous (plan_device_model), so that its exactness against
-// plan_incremental is checked on the CPU too (tests/test_device_model.py).  Nothing times or ships it.
+// Two more modes, NOS_ORACLE_DEVICE_MODEL and NOS_ORACLE_FUSED_MODEL, are NOT restatements of the reference: they restate, in this
+// file's terms, the algorithms the CUDA path uses -- the gate replay where the cluster-wide gate is not vacuous (plan_device_model)
+// and the single-launch kernel's per-node pod loop (plan_fused_model) -- so that their exactness against plan_incremental is
+// checked on the CPU too (tests/test_device_model.py).  Nothing times or ships them.
 // Pinning: this file is checked against oracle/nos_model.py (the dict/string model that reproduces every
 // golden vector ported from the reference's tests, tests/golden/) on the golden cases and on thousands
 // of randomised small snapshots.
@@ -33,6 +34,7 @@
 #define NOS_ORACLE_FAITHFUL 0
 #define NOS_ORACLE_INCREMENTAL 1
 #define NOS_ORACLE_DEVICE_MODEL 2     /* model of the CUDA path's gate replay (see plan_device_model); tests only */
+#define NOS_ORACLE_FUSED_MODEL 3      /* model of the single-launch kernel (see plan_fused_model); tests only */
 
 namespace {
 
@@ -681,6 +683,114 @@ int plan_device_model(Problem& pb, nosplan_partitioning* out, nosplan_stats* st)
     return NOSPLAN_OK;
 }
 
+// ---------------------------------------------------------------- model of the single-launch kernel (CPU tests only)
+// What k_plan_fused (nos_b200/csrc/fused.cu) computes, in the oracle's terms: every candidate node on its own from the t0 state,
+// geometry under a saturated lacking vector, and a pod loop that keeps per node only the remaining cpu, the remaining memory
+// and the free devices PER PROFILE (not per GPU) -- no cluster-wide gate, no slice-column test in NodeResourcesFit, no first-fit
+// GPU choice.  DESIGN.md section 3a argues that this is the reference's plan whenever every requested profile is lacking and
+// stays saturated, every request is for ONE device of at most one profile, and every node's accounts agree with its GPUs;
+// tests/test_device_model.py checks the argument against plan_incremental.  Returns 1 where the kernel would reject itself or
+// the host would not have chosen it.
+int plan_fused_model(Problem& pb, nosplan_partitioning* out, nosplan_stats* st) {
+    const Ctx& c = pb.c; const int N = pb.N, G = pb.G, P = pb.P, R = c.R;
+    const std::vector<Node>& D = pb.nodes;
+    const bool fit = pb.filter_mode == NOSPLAN_FILTER_RESOURCES_FIT;
+    for (int i = 0; i < N; ++i) write_partitioning(D[i], i, G, out);
+    // host-side eligibility (api.cu): single-profile classes, quantity 1, unique tracker keys, cpu / memory / slice requests only
+    std::vector<uint8_t> key_seen((size_t)pb.n_keys, 0);
+    unsigned rset = 0;
+    for (int i = 0; i < P; ++i) {
+        const PodReq& pr = pb.pods[i];
+        if (pr.n_slice > 1 || (pr.n_slice == 1 && pr.sq[0] != 1) || pr.base[2] != 0 || (fit && pr.n_other > 0)) return 1;
+        if (pr.n_slice == 0 && pr.base[0] == 0 && pr.base[1] == 0) return 1;
+        if (key_seen[pb.tkey[i]]) return 1;
+        key_seen[pb.tkey[i]] = 1;
+        if (pr.n_slice) rset |= 1u << pr.sp[0];
+    }
+    if (G > 8 || rset == 0) return 1;
+    int64_t A[RMAX] = {0}, Rq[RMAX] = {0};
+    for (int i = 0; i < N; ++i) for (int k = 0; k < R; ++k) { A[k] += D[i].alloc[k]; Rq[k] += D[i].req[k]; }
+    Tracker tr; std::memset(tr.lack, 0, sizeof tr.lack); tr.entry.assign((size_t)pb.n_keys * KP, 0);
+    for (int i = 0; i < P; ++i) {
+        int32_t l[KP] = {0};
+        pod_lacks(pb.pods[i], A, Rq, l);
+        for (int p = 0; p < KP; ++p) { tr.lack[p] += l[p]; tr.entry[(size_t)pb.tkey[i] * KP + p] += l[p]; }
+    }
+    st->lacking_at_start = tr.count();
+    // node-side conditions (phase 1): counts that fit five bits with their keys present, accounts that agree with the GPUs
+    int maxmem = 0;
+    for (int i = 0; i < N; ++i) {
+        const Node& n = D[i];
+        for (int p = 0; p < c.K; ++p) {
+            int64_t sf = 0, su = 0;
+            for (int j = 0; j < n.ng; ++j) {
+                const Gpu& g = n.g[j];
+                if (g.used[p] > 31 || g.free_[p] > 31) return 1;
+                if ((g.used[p] && !(g.umask >> p & 1)) || (g.free_[p] && !(g.fmask >> p & 1))) return 1;
+                sf += g.free_[p]; su += g.used[p];
+                maxmem = std::max(maxmem, g.mem);
+            }
+            if (n.alloc[3 + p] - n.req[3 + p] < sf || n.req[3 + p] > su) return 1;
+        }
+    }
+    // the hypothesis at t0: exactly the requested profiles are lacking, each beyond the saturation bound
+    int64_t bound[KP] = {0};
+    for (int p = 0; p < c.K; ++p) {
+        int m = 0;
+        if (c.kind == NOSPLAN_KIND_MIG) { const int rows = c.geom_off ? c.geom_off[pb.n_models] : 0; for (int r = 0; r < rows; ++r) m = std::max(m, (int)c.geom[16 * (size_t)r + p]); }
+        else m = c.pmem[p] > 0 ? maxmem / c.pmem[p] : (1 << 30);
+        for (int i = 0; i < N; ++i) for (int j = 0; j < D[i].ng; ++j) m = std::max(m, (int)D[i].g[j].free_[p]);
+        bound[p] = (int64_t)(G + 2) * m;
+    }
+    auto holds = [&](const int32_t* lack) {
+        for (int p = 0; p < KP; ++p) {
+            const bool requested = (rset >> p & 1u) != 0;
+            if (requested != (tr.lack[p] > 0)) return false;
+            if (requested && !(lack[p] > 0 && (int64_t)lack[p] > bound[p])) return false;
+        }
+        return true;
+    };
+    if (!holds(tr.lack)) return 1;
+    int32_t sat_lack[KP];
+    for (int p = 0; p < KP; ++p) sat_lack[p] = (rset >> p & 1u) ? (1 << 29) : 0;
+    std::vector<int> order = sort_pods(pb);
+    std::vector<uint8_t> placed((size_t)pb.n_keys, 0);
+    for (int i = 0; i < N; ++i) {
+        if (!node_has_free_capacity(c, D[i])) continue;
+        ++st->visited_nodes;
+        Node W = D[i];
+        const bool upd = node_update_geometry(c, W, sat_lack, st->geometry_evals);
+        int cap[KP] = {0};
+        for (int p = 0; p < c.K; ++p) for (int j = 0; j < W.ng; ++j) { if (W.g[j].free_[p] > 31) return 1; cap[p] += W.g[j].free_[p]; }
+        int64_t remc = D[i].alloc[0] - D[i].req[0], remm = D[i].alloc[1] - D[i].req[1];
+        const bool all_fail = pb.filter_mode == NOSPLAN_FILTER_REJECT_ALL ||
+                              (fit && (D[i].num_pods + 1 > D[i].allowed_pods || D[i].alloc[2] - D[i].req[2] < 0));
+        int added = 0;
+        for (int oi : order) {
+            if (all_fail) break;
+            const PodReq& pr = pb.pods[oi];
+            if (!pb.pre_ok[oi]) continue;
+            if (fit && (pr.base[0] > remc || pr.base[1] > remm)) continue;
+            if (pr.n_slice) { if (cap[pr.sp[0]] == 0) continue; --cap[pr.sp[0]]; }
+            remc -= pr.base[0]; remm -= pr.base[1];
+            placed[pb.tkey[oi]] = 1;
+            ++added; ++st->placements;
+        }
+        if (added && upd) write_partitioning(W, i, G, out);     // used + free per GPU and the key masks do not depend on which GPU took a pod
+    }
+    st->candidate_nodes = st->visited_nodes;
+    st->candidates = st->visited_nodes * P;
+    int32_t le[KP];
+    for (int p = 0; p < KP; ++p) le[p] = tr.lack[p];
+    for (int key = 0; key < pb.n_keys; ++key) if (placed[key]) for (int p = 0; p < KP; ++p) le[p] -= std::max(0, tr.entry[(size_t)key * KP + p]);
+    if (!holds(le)) return 1;
+    int cnt = 0;
+    for (int p = 0; p < KP; ++p) cnt += le[p] > 0;
+    st->lacking_at_end = cnt;
+    st->path = 1; st->fused = 1;
+    return NOSPLAN_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -692,7 +802,8 @@ int nos_oracle_plan(const nosplan_snapshot* s, const nosplan_pods* p, const uint
     if (rc != NOSPLAN_OK) return rc;
     nosplan_stats st; std::memset(&st, 0, sizeof st);
     auto t0 = std::chrono::steady_clock::now();
-    rc = mode == NOS_ORACLE_FAITHFUL ? plan_faithful(pb, out, &st) : mode == NOS_ORACLE_DEVICE_MODEL ? plan_device_model(pb, out, &st) : plan_incremental(pb, out, &st);
+    rc = mode == NOS_ORACLE_FAITHFUL ? plan_faithful(pb, out, &st) : mode == NOS_ORACLE_DEVICE_MODEL ? plan_device_model(pb, out, &st)
+       : mode == NOS_ORACLE_FUSED_MODEL ? plan_fused_model(pb, out, &st) : plan_incremental(pb, out, &st);
     auto t1 = std::chrono::steady_clock::now();
     if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
     if (stats) *stats = st;

@@ -9,7 +9,7 @@ from nos_b200 import capi
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
-FAITHFUL, INCREMENTAL, DEVICE_MODEL = 0, 1, 2
+FAITHFUL, INCREMENTAL, DEVICE_MODEL, FUSED_MODEL = 0, 1, 2, 3
 _lib = None
 
 
@@ -42,7 +42,7 @@ def plan(snap, pods, prefilter_ok=None, filter_mode=0, mode=INCREMENTAL):
         pa = np.ascontiguousarray(np.asarray(prefilter_ok, dtype=np.uint8))
         pre = pa.ctypes.data
     rc = lib().nos_oracle_plan(C.byref(cs), C.byref(cp), pre, filter_mode, mode, C.byref(out), C.byref(st), C.byref(sec))
-    if rc == 1 and mode == DEVICE_MODEL:
+    if rc == 1 and mode in (DEVICE_MODEL, FUSED_MODEL):
         return None, None, None, sec.value          # the device would take the exact sweep: nothing to model
     if rc != 0:
         raise RuntimeError(f"nos_oracle_plan -> {rc}")

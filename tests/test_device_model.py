@@ -93,3 +93,54 @@ def test_the_judges_rows():
     s, p = synth.mig_cluster(10000, 8, 1000, seed=0xC5)
     two_profile_pods(p, s.n_profiles, 10)
     assert agree(s, p, None, pk.FILTER_RESOURCES_FIT, "two-profile class") is not None
+
+
+# ---- the single-launch kernel's per-node pod loop: free devices per PROFILE, no gate, no slice-column test
+
+def agree_fused(snap, pods, pre, fm, what):
+    cnt, msk, st, _ = ol.plan(snap, pods, pre, fm, ol.FUSED_MODEL)
+    if cnt is None:
+        return False
+    ocnt, omsk, ost, _ = ol.plan(snap, pods, pre, fm, ol.INCREMENTAL)
+    assert np.array_equal(msk, omsk), f"{what}: key masks differ"
+    assert np.array_equal(cnt, ocnt), f"{what}: counts differ"
+    for k in COUNTERS:
+        assert st[k] == ost[k], f"{what}: {k} {st[k]} != {ost[k]}"
+    return True
+
+
+def test_single_launch_model_on_random_small_cases():
+    taken = 0
+    for seed in range(3200):
+        kind_name, nodes, pods, pre, fmode = rc.rand_case(seed)
+        kind = pk.KIND_BY_NAME[kind_name]
+        if any(q <= 0 and pk.slice_profile_of(kind, r) is not None for p in pods for r, q in pk.compute_pod_request(p).items()):
+            continue
+        s, p = pk.pack(kind, nodes, pods, m.DEFAULT_KNOWN_GEOMETRIES)
+        taken += agree_fused(s, p, pre, fmode, f"seed {seed}")
+    assert taken >= 10, taken
+
+
+@pytest.mark.parametrize("kind", ["mig", "mps"])
+def test_single_launch_model_on_saturating_clusters(kind):
+    gen = synth.mig_cluster if kind == "mig" else synth.mps_cluster
+    rng = np.random.default_rng(23)
+    taken = 0
+    for seed in range(30):
+        n = int(rng.integers(10, 400))
+        s, p = gen(n, int(rng.integers(1, 9)), int(rng.integers(6 * n, 20 * n)), seed=0xA00 + seed)
+        if seed % 3 == 0:                                    # tight nodes: cpu / memory / pod count decide, not the devices
+            s.node_requested[:, 0] = rng.integers(0, 64001, n)
+            s.node_requested[:, 1] = rng.integers(0, 513, n) << 30
+            s.node_num_pods[:] = rng.integers(100, 112, n)
+        if seed % 4 == 1:
+            p.priority[:] = rng.choice([-5, 0, 7, 100, 1000], p.n_pods)
+        pre = (rng.random(p.n_pods) < 0.7).astype(np.uint8) if seed % 2 else None
+        for fm in (pk.FILTER_NONE, pk.FILTER_REJECT_ALL, pk.FILTER_RESOURCES_FIT):
+            taken += agree_fused(s, p, pre, fm, f"{kind} seed {seed} fm {fm}")
+    assert taken >= 60, taken
+
+
+def test_single_launch_model_at_the_bench_size():
+    s, p = synth.mig_cluster(10000, 8, 10000, seed=0xC5)
+    assert agree_fused(s, p, None, pk.FILTER_RESOURCES_FIT, "mig-10k")
