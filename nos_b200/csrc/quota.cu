@@ -668,7 +668,13 @@ __global__ void __launch_bounds__(SEG_THREADS) k_label_segments(DevQuota q) {
 #pragma unroll
         for (int c = 0; c < QR; ++c) acc[c] = 0;
         for (int p = b0 + tid; p < b; p += 32 * n_warps) {
-            while (*reinterpret_cast<volatile int32_t*>(&q.seg_flag[p]) == 0) __nanosleep(32);
+            // the bucket waited for holds a lower ticket, so it is running or done; the wait is bounded all the same (half a
+            // second), and a wait that runs out makes the host repeat the call with the device-wide sort
+            unsigned spins = 0;
+            while (*reinterpret_cast<volatile int32_t*>(&q.seg_flag[p]) == 0) {
+                if (++spins > (1u << 24)) { *q.seg_overflow = 1; break; }
+                __nanosleep(32);
+            }
             __threadfence();
 #pragma unroll
             for (int c = 0; c < QR; ++c) if (c < q.R) acc[c] += __ldcg(&q.seg_sum[(size_t)p * QR + c]);
